@@ -1,0 +1,747 @@
+// deepore_b200 pileup encoder -- hand-written CUDA for sm_100a.
+//
+// Replaces /root/reference/src/utils/Pileup.py : Pileup.__init__ (:21-93), iterateReads (:152-163),
+// parseRead (:174-264), generatePileupImage/encodeColumn (:268-317) and savePileupRGB (:336-361) for a
+// batch of windows, bit-exactly (tests/test_encoder_gpu.py).
+//
+// Formulation (DESIGN.md "encoder"): parseRead's state machine is closed-form per CIGAR op -- op j that
+// starts at reference position A_j with length n emits its step i at column A_j (i==0) or
+// A_j + dRef*(i-1) (i>=1), reading query index qp_j + dRead*i (qp lags by one: it starts at -1) and
+// reference character ref[rel], rel = rel0 + number of earlier in-window M/D steps of the read.  The
+// block-skip test of :214 never changes what is emitted, so every op is handled by the same rule.
+// That turns the scatter into an ORDERED GATHER: one CTA per window; reads are visited in file order;
+// one thread owns one pileup column (pass 0) / one image row (passes 1-2) and pulls its own entries out
+// of each read, so per-(row,category) order is (read order, step order) with no atomics and no sort:
+//
+//   prep kernel   per read: first aligned position, bam_endpos, soft-clip extent; per op: exclusive
+//                 prefix sums of reference / query advance (lets a window enter a long read in O(log ops))
+//   pass 0        per column: populated?  longest insert anchored here  -> row map (sparse column axis,
+//                 insert rows spliced after their anchor, Pileup.py:295-317)
+//   pass 1        per image row: entry count per category (A,C,G,T,D,M,N / insert rows A,C,G,T,N)
+//   pass 2        per image row: place each quality byte at base[category] + running rank (first W-1 kept)
+//   emit          RGBA rows written with 16-byte stores: colour from the category boundaries, alpha from the
+//                 staged quality bytes, filler elsewhere.  120 000 B per default window; this is the
+//                 HBM-bound part.
+#include <limits.h>
+#include <stdarg.h>
+
+#include "common.cuh"
+
+namespace dp {
+
+static thread_local char g_err[512];
+void set_error(const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+// Pileup.calculateQuality (Pileup.py:166-171): int(round((1-10**(q/-10))*255)), q = min(baseQ, mapQ).
+// Table generated with the reference's own Python expression (tests/test_oracle_pins.py checks it);
+// every q >= 28 maps to 255.
+__constant__ uint8_t c_qlut[256];
+static const uint8_t h_qlut_head[28] = {0,   52,  94,  127, 153, 174, 191, 204, 215, 223, 230, 235, 239, 242,
+                                        245, 247, 249, 250, 251, 252, 252, 253, 253, 254, 254, 254, 254, 254};
+static bool g_lut_ready[64] = {false};
+
+static int ensure_lut() {
+    int dev = 0;
+    DP_CUDA_CHECK(cudaGetDevice(&dev));
+    if (dev < 64 && g_lut_ready[dev]) return DP_OK;
+    uint8_t lut[256];
+    for (int i = 0; i < 256; i++) lut[i] = i < 28 ? h_qlut_head[i] : 255;
+    DP_CUDA_CHECK(cudaMemcpyToSymbol(c_qlut, lut, 256));
+    if (dev < 64) g_lut_ready[dev] = true;
+    return DP_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// categories in sortingKey order (Pileup.py:66-73): A C G T D M N ; inserts use A C G T N (0,1,2,3,6)
+enum { CAT_A = 0, CAT_C = 1, CAT_G = 2, CAT_T = 3, CAT_D = 4, CAT_M = 5, CAT_N = 6, NCAT = 7 };
+
+// RGBA little-endian words with alpha 0 (SNPtoRGB, Pileup.py:56-64)
+__device__ __forceinline__ uint32_t cat_rgb(int cat) {
+    // A (255,0,0) C (255,255,0) G (0,255,0) T (0,0,255) D (0,255,255) M (255,255,255) N (0,0,0)
+    const uint32_t t[NCAT] = {0x000000FFu, 0x0000FFFFu, 0x0000FF00u, 0x00FF0000u, 0x00FFFF00u, 0x00FFFFFFu, 0x00000000u};
+    return t[cat];
+}
+// 4-bit BAM code -> category of the read character, or -1 (KeyError in the reference)
+// "=ACMGRSVTWYHKDBN": A=1 C=2 G=4 T=8 N=15
+__device__ __forceinline__ int cat_of_code(int code) {
+    switch (code) {
+    case 1: return CAT_A; case 2: return CAT_C; case 4: return CAT_G; case 8: return CAT_T; case 15: return CAT_N;
+    default: return -1;
+    }
+}
+__device__ __forceinline__ int ascii_of_code(int code) { return "=ACMGRSVTWYHKDBN"[code]; }
+__device__ __forceinline__ int cat_of_ascii(int ch) {
+    switch (ch) {
+    case 'A': return CAT_A; case 'C': return CAT_C; case 'G': return CAT_G; case 'T': return CAT_T; case 'N': return CAT_N;
+    default: return -1;
+    }
+}
+
+struct ReadAux {      // per read, produced by the prep kernel
+    int ref_start;    // get_reference_positions()[0] (Pileup.py:191) or INT_MIN when the read has no M/=/X base
+    int endpos;       // bam_endpos (dep/htslib/sam.c:347-353)
+    int aln_start;    // query_alignment_start: leading soft clip (H skipped)
+    int aln_len;      // len(query_alignment_sequence)
+};
+
+__device__ __forceinline__ int warp_incl_scan(int v, int lane) {
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        int t = __shfl_up_sync(0xffffffffu, v, d);
+        if (lane >= d) v += t;
+    }
+    return v;
+}
+
+// deltaRef / deltaRead of Pileup.py:47-48 : only M,D,N advance the reference; only M,I advance the query
+__device__ __forceinline__ bool op_adv_ref(int op) { return op == 0 || op == 2 || op == 3; }
+__device__ __forceinline__ bool op_adv_read(int op) { return op == 0 || op == 1; }
+
+// ------------------------------------------------------------------------------------------------
+// prep: one warp per read
+__global__ void __launch_bounds__(256) prep_reads_kernel(dp_reads R, ReadAux *__restrict__ aux,
+                                                         int *__restrict__ RP, int *__restrict__ QP) {
+    const int lane = threadIdx.x & 31;
+    const int r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (r >= R.n_reads) return;
+    const int64_t c0 = R.cigar_off[r];
+    const int nops = (int)(R.cigar_off[r + 1] - c0);
+    const int pos = R.pos[r];
+    int carryR = 0, carryQ = 0, carryH = 0, carryDN = 0;
+    int ref_start = INT_MIN;
+    for (int base = 0; base < nops; base += 32) {
+        const int j = base + lane;
+        const uint32_t w = j < nops ? R.cigar[c0 + j] : 0u;
+        const int op = w & 15, n = (int)(w >> 4);
+        const int dR = op_adv_ref(op) ? n : 0;
+        const int dQ = op_adv_read(op) ? n : 0;
+        const int dH = (op == 0 || op == 2 || op == 3 || op == 7 || op == 8) ? n : 0;   // bam_cigar2rlen
+        const int dDN = (op == 2 || op == 3) ? n : 0;
+        const int iR = warp_incl_scan(dR, lane), iQ = warp_incl_scan(dQ, lane);
+        const int iH = warp_incl_scan(dH, lane), iDN = warp_incl_scan(dDN, lane);
+        if (j < nops) {
+            RP[c0 + r + j] = carryR + iR - dR;               // nops+1 entries per read, base c0 + r
+            QP[c0 + j] = carryQ + iQ - dQ;
+        }
+        const bool aligned = j < nops && (op == 0 || op == 7 || op == 8) && n > 0;
+        const unsigned m = __ballot_sync(0xffffffffu, aligned);
+        if (ref_start == INT_MIN && m) {
+            const int f = __ffs(m) - 1;
+            const int dn_before = __shfl_sync(0xffffffffu, iDN - dDN, f);
+            ref_start = pos + carryDN + dn_before;
+        }
+        carryR += __shfl_sync(0xffffffffu, iR, 31);
+        carryQ += __shfl_sync(0xffffffffu, iQ, 31);
+        carryH += __shfl_sync(0xffffffffu, iH, 31);
+        carryDN += __shfl_sync(0xffffffffu, iDN, 31);
+    }
+    if (lane == 0) {
+        RP[c0 + r + nops] = carryR;
+        ReadAux a;
+        a.ref_start = ref_start;
+        a.endpos = (!(R.flag[r] & 4) && nops > 0) ? pos + carryH : pos + 1;
+        int s = 0, e = R.l_seq[r];
+        for (int c = 0; c < nops; c++) {
+            const uint32_t w = R.cigar[c0 + c];
+            const int op = w & 15;
+            if (op == 5) continue;
+            if (op == 4) s += (int)(w >> 4); else break;
+        }
+        for (int c = nops - 1; c >= 0; c--) {
+            const uint32_t w = R.cigar[c0 + c];
+            const int op = w & 15;
+            if (op == 5) continue;
+            if (op == 4) e -= (int)(w >> 4); else break;
+        }
+        a.aln_start = s;
+        a.aln_len = e - s > 0 ? e - s : 0;
+        aux[r] = a;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+constexpr int ENC_THREADS = 256;
+constexpr int ENC_WARPS = ENC_THREADS / 32;
+constexpr int SEG_CAP = 64;        // staged ops per read per round
+constexpr int CAND_BLOCK = 256;    // candidate reads filtered per compaction round
+
+struct __align__(16) SegOp {
+    int sA;        // column (relative to queryStart) of the op's first reference position
+    int n;         // op length
+    int qp;        // readPosition at op start (lags by one: -1 + query bases consumed so far)
+    short rel;     // relativeIndexRef at op start
+    uint8_t op;
+    uint8_t pad;
+};
+struct SegHdr {
+    long long seq_off, qual_off;
+    int aln_start, aln_len, l_seq, mapq;
+    int nops;      // staged ops in this slot (0 = nothing)
+    int more;      // read has further relevant ops beyond this round
+    int next_j;    // op index (within the read) at which the next round starts
+    int next_A, next_qp, next_rel;   // carried state for the next round
+    int c0lo, c0hi;                  // cigar base offset (split int64)
+};
+
+struct EncArgs {
+    dp_reads R;
+    const ReadAux *aux;
+    const int *RP;
+    const int *QP;
+    const int32_t *win_qs, *win_lo, *win_hi;
+    const uint8_t *ref;
+    long long ref_base, ref_len;
+    int L, W, H, mapq_cut;
+    uint8_t *out_img;
+    int32_t *out_rowpos, *out_rowins, *out_status;
+};
+
+// Stage one round (<= SEG_CAP ops) of read r into slot (hdr, ops).  One warp.
+// first==true: locate the first relevant op by binary search on the reference-advance prefix; else
+// continue from the state saved in hdr.
+__device__ void stage_read(const EncArgs &a, int r, int qs, int qe, bool first, SegHdr *hdr, SegOp *ops, int lane) {
+    int j0, A0, qp0, rel0;
+    long long c0;
+    int nops_total;
+    if (first) {
+        const ReadAux ax = a.aux[r];
+        c0 = a.R.cigar_off[r];
+        nops_total = (int)(a.R.cigar_off[r + 1] - c0);
+        const int refStart = ax.ref_start;
+        // first op whose end (refStart + RP[j+1]) >= qs : everything before it emits nothing in-window.
+        // RP has nops+1 entries per read (base c0 + r); warp-cooperative 32-ary lower bound on RP[j+1].
+        const long long rpb = c0 + r;
+        const int T = qs - refStart;
+        int lo = 0, hi = nops_total;                          // answer in [lo, hi]
+        while (lo < hi) {
+            const int len = hi - lo;
+            const int step = (len + 31) >> 5;
+            const int jk = min(lo + (lane + 1) * step - 1, hi - 1);
+            const bool before = a.RP[rpb + jk + 1] < T;
+            const int k = __popc(__ballot_sync(0xffffffffu, before));
+            if (k == 32) { lo = hi; break; }
+            const int nlo = lo + k * step;
+            const int nhi = min(lo + (k + 1) * step, hi) - 1;  // block k's probe is not-before => answer <= nhi
+            lo = nlo; hi = max(nhi, nlo);
+        }
+        j0 = lo;
+        if (j0 < nops_total) {
+            A0 = refStart + a.RP[rpb + j0] - qs;
+            qp0 = -1 + a.QP[c0 + j0];
+        } else { A0 = 0; qp0 = 0; }
+        rel0 = refStart > qs ? refStart - qs - 1 : 0;        // Pileup.py:203-204
+        if (lane == 0) {
+            hdr->seq_off = a.R.seq_off[r];
+            hdr->qual_off = a.R.qual_off[r];
+            hdr->aln_start = ax.aln_start;
+            hdr->aln_len = ax.aln_len;
+            hdr->l_seq = a.R.l_seq[r];
+            hdr->mapq = a.R.mapq[r];
+            hdr->c0lo = (int)(c0 & 0xffffffffll);
+            hdr->c0hi = (int)(c0 >> 32);
+        }
+    } else {
+        j0 = hdr->next_j; A0 = hdr->next_A; qp0 = hdr->next_qp; rel0 = hdr->next_rel;
+        c0 = ((long long)hdr->c0hi << 32) | (unsigned int)hdr->c0lo;
+        nops_total = (int)(a.R.cigar_off[r + 1] - c0);
+    }
+    __syncwarp();
+    const int Lwin = qe - qs;
+    int staged = 0;
+    int more = 0;
+    int carryA = A0, carryQ = qp0, carryRel = rel0;
+    int j = j0;
+    for (int round = 0; round < SEG_CAP / 32; round++) {
+        const int jj = j + lane;
+        const bool valid = jj < nops_total;
+        const uint32_t w = valid ? a.R.cigar[c0 + jj] : 0u;
+        const int op = w & 15, n = (int)(w >> 4);
+        const int dR = op_adv_ref(op) ? n : 0;
+        const int dQ = op_adv_read(op) ? n : 0;
+        const int iR = warp_incl_scan(dR, lane), iQ = warp_incl_scan(dQ, lane);
+        const int sA = carryA + iR - dR;
+        const int qp = carryQ + iQ - dQ;
+        // in-window M/D steps of this op (advance of relativeIndexRef, Pileup.py:252)
+        int inwin = 0;
+        if (valid && (op == 0 || op == 2) && n > 0) {
+            inwin = (sA >= 0 && sA < Lwin) ? 1 : 0;
+            const int lo_i = max(1, 1 - sA);                 // col_i = sA + i - 1 >= 0
+            const int hi_i = min(n - 1, Lwin - sA);          // col_i <= Lwin-1
+            if (hi_i >= lo_i) inwin += hi_i - lo_i + 1;
+        }
+        const int iW = warp_incl_scan(inwin, lane);
+        const int rel = carryRel + iW - inwin;
+        const bool relevant = valid && sA < Lwin;            // ops starting at/after queryEnd emit nothing
+        const unsigned mrel = __ballot_sync(0xffffffffu, relevant);
+        // relevant lanes form a prefix (sA is monotone)
+        const int cnt = __popc(mrel);
+        if (relevant) {
+            SegOp so;
+            so.sA = sA; so.n = n; so.qp = qp; so.rel = (short)min(rel, 32000); so.op = (uint8_t)op; so.pad = 0;
+            ops[staged + lane] = so;
+        }
+        staged += cnt;
+        carryA += __shfl_sync(0xffffffffu, iR, 31);
+        carryQ += __shfl_sync(0xffffffffu, iQ, 31);
+        carryRel += __shfl_sync(0xffffffffu, iW, 31);
+        j += 32;
+        if (cnt < 32) { more = 0; break; }
+        if (j >= nops_total) { more = 0; break; }
+        more = 1;                                            // possibly more relevant ops
+    }
+    if (lane == 0) {
+        hdr->nops = staged;
+        hdr->more = more;
+        hdr->next_j = j; hdr->next_A = carryA; hdr->next_qp = carryQ; hdr->next_rel = carryRel;
+    }
+    __syncwarp();
+}
+
+// Python indexing of readSequence / readQualities (negative index wraps once)
+struct ReadCtx {
+    const uint8_t *seq4;
+    const uint8_t *qual;
+    long long seq_off, qual_off;
+    int aln_start, aln_len, l_seq, mapq;
+};
+__device__ __forceinline__ int read_code(const ReadCtx &c, int idx, int &err) {
+    if (idx < 0) idx += c.aln_len;
+    if (idx < 0 || idx >= c.aln_len) { err = DP_EINDEX; return 15; }
+    const int k = idx + c.aln_start;
+    const uint8_t b = __ldg(c.seq4 + c.seq_off + (k >> 1));
+    return (k & 1) ? (b & 15) : (b >> 4);
+}
+__device__ __forceinline__ int read_q(const ReadCtx &c, int idx, int &err) {
+    if (idx < 0) idx += c.l_seq;
+    if (idx < 0 || idx >= c.l_seq) { err = DP_EINDEX; return 0; }
+    const int bq = __ldg(c.qual + c.qual_off + idx);
+    return c_qlut[min(bq, c.mapq)];
+}
+
+// first staged op with key > P, key = (advancing && n>0) ? end column : start column + 1
+__device__ __forceinline__ int seg_lower_bound(const SegOp *ops, int nops, int P) {
+    int lo = 0, hi = nops;
+    while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        const SegOp o = ops[mid];
+        const bool adv = op_adv_ref(o.op) && o.n > 0;
+        const int key = adv ? o.sA + o.n : o.sA + 1;
+        if (key <= P) lo = mid + 1; else hi = mid;
+    }
+    return lo;
+}
+
+// MODE 0: mark (populated, max insert length)   MODE 1: count   MODE 2: place
+// Anchor rows/columns: kins == 0.  Insert rows: kins = k+1.
+template <int MODE>
+__device__ __forceinline__ void visit_slot(const EncArgs &a, const SegHdr *hdr, const SegOp *ops, int P, int kins,
+                                           const uint8_t *s_ref, int Lwin, int &populated, int &max_ins,
+                                           int *cnt, const int *base, int *run, uint8_t *qrow, int Wm1, int &err) {
+    const int nops = hdr->nops;
+    if (nops == 0) return;
+    int j = seg_lower_bound(ops, nops, P);
+    if (j >= nops) return;
+    ReadCtx rc;
+    rc.seq4 = a.R.seq4; rc.qual = a.R.qual;
+    rc.seq_off = hdr->seq_off; rc.qual_off = hdr->qual_off;
+    rc.aln_start = hdr->aln_start; rc.aln_len = hdr->aln_len; rc.l_seq = hdr->l_seq; rc.mapq = hdr->mapq;
+    for (; j < nops; j++) {
+        const SegOp o = ops[j];
+        if (o.sA > P) break;
+        const int op = o.op, n = o.n;
+        if (n <= 0) continue;
+        if (op == 1) {                                       // insert (Pileup.py:220-230), anchor = sA, needs A > qs
+            if (o.sA != P || P <= 0) continue;
+            if (MODE == 0) { max_ins = max(max_ins, n); continue; }
+            if (kins == 0 || kins > n) continue;
+            const int idx = o.qp + kins;                     // readPosition+1+k
+            // slices (not indexing): idx >= 0 always; a short slice raises IndexError at [k]
+            if (idx >= rc.aln_len || idx >= rc.l_seq) { err = DP_EINDEX; continue; }
+            const int code = read_code(rc, idx, err);
+            const int cat = cat_of_code(code);
+            if (cat < 0) { err = DP_EKEY; continue; }
+            if (MODE == 1) cnt[cat]++;
+            if (MODE == 2) {
+                const int slot = base[cat] + run[cat]++;
+                if (slot < Wm1) qrow[1 + slot] = (uint8_t)read_q(rc, idx, err);
+            }
+            continue;
+        }
+        if (kins != 0) continue;                             // insert rows only take insert ops
+        const bool adv = op_adv_ref(op);
+        int i_first, i_count;                                // steps of this op that land on column P
+        if (adv) {
+            if (P == o.sA) { i_first = 0; i_count = n >= 2 ? 2 : 1; }
+            else { i_first = P - o.sA + 1; i_count = (i_first <= n - 1) ? 1 : 0; }
+        } else {
+            if (o.sA != P) continue;
+            i_first = 0; i_count = (op == 4) ? 1 : n;        // soft clip: one step, then break (:257-258)
+        }
+        if (i_count == 0) continue;
+        if (MODE == 0) { populated = 1; continue; }
+        const int dq = (op == 0) ? 1 : 0;                    // deltaRead for non-insert ops: only M
+        const bool md = (op == 0 || op == 2);
+        if (!adv) {
+            // i_count identical entries: query index and relativeIndexRef do not move
+            const int code = read_code(rc, o.qp, err);
+            const int rel = o.rel;
+            if (rel < 0 || rel > Lwin) { err = DP_EINDEX; continue; }
+            const int fc = s_ref[rel];
+            const int rch = ascii_of_code(code);
+            const int cat = (rch == fc) ? CAT_M : cat_of_code(code);
+            if (cat < 0) { err = DP_EKEY; continue; }
+            if (MODE == 1) cnt[cat] += i_count;
+            if (MODE == 2) {
+                const int q = read_q(rc, o.qp, err);
+                for (int t = 0; t < i_count; t++) {
+                    const int slot = base[cat] + run[cat]++;
+                    if (slot < Wm1) qrow[1 + slot] = (uint8_t)q; else break;
+                }
+            }
+            continue;
+        }
+        // in-window steps of this op before step i (advance of rel inside the op)
+        const int in0 = (o.sA >= 0 && o.sA < Lwin) ? 1 : 0;
+        const int lo_i = max(1, 1 - o.sA);
+        for (int t = 0; t < i_count; t++) {
+            const int i = i_first + t;
+            const int idx = o.qp + dq * i;
+            int rel = o.rel;
+            if (md && i > 0) rel += in0 + max(0, i - lo_i);
+            if (rel < 0 || rel > Lwin) { err = DP_EINDEX; continue; }
+            int cat;
+            if (op == 2) {
+                cat = CAT_D;                                 // getPileupEncoding (:128-134)
+                if (MODE == 1) {                             // the reference still indexes seq/qual (:240,:243)
+                    int e2 = 0; (void)read_code(rc, idx, e2); if (e2) err = e2;
+                }
+            } else {
+                const int code = read_code(rc, idx, err);
+                const int fc = s_ref[rel];
+                cat = (ascii_of_code(code) == fc) ? CAT_M : cat_of_code(code);
+                if (cat < 0) { err = DP_EKEY; continue; }
+            }
+            if (MODE == 1) cnt[cat]++;
+            if (MODE == 2) {
+                const int slot = base[cat] + run[cat]++;
+                if (slot < Wm1) qrow[1 + slot] = (uint8_t)read_q(rc, idx, err);
+            }
+        }
+    }
+}
+
+template <int MODE>
+__device__ void run_pass(const EncArgs &a, int qs, int qe, int lo, int hi, SegHdr *s_hdr, SegOp *s_ops, int *s_cand,
+                         int *s_ncand, int *s_flags, const uint8_t *s_ref, int P, int kins, bool active,
+                         int &populated, int &max_ins, int *cnt, const int *base, int *run, uint8_t *qrow, int Wm1,
+                         int &err) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int Lwin = qe - qs;
+    for (int cb = lo; cb < hi; cb += CAND_BLOCK) {
+        // ---- ordered compaction of the candidates that pass fetch (hts.c:2242) + mapq (:160) + aligned (:187)
+        const int r = cb + tid;
+        bool keep = false;
+        if (r < hi) {
+            const ReadAux ax = a.aux[r];
+            keep = a.R.pos[r] < qe && ax.endpos > qs && (int)a.R.mapq[r] >= a.mapq_cut && ax.ref_start != INT_MIN;
+        }
+        const unsigned bal = __ballot_sync(0xffffffffu, keep);
+        if (lane == 0) s_flags[warp] = __popc(bal);
+        __syncthreads();
+        int off = 0, total = 0;
+        for (int w = 0; w < ENC_WARPS; w++) { const int c = s_flags[w]; if (w < warp) off += c; total += c; }
+        if (keep) s_cand[off + __popc(bal & ((1u << lane) - 1))] = r;
+        __syncthreads();
+        // ---- chunks of ENC_WARPS reads: stage (one warp per read) then visit (one thread per column/row)
+        for (int ch = 0; ch < total; ch += ENC_WARPS) {
+            const int nslots = min(ENC_WARPS, total - ch);
+            if (warp < nslots) stage_read(a, s_cand[ch + warp], qs, qe, true, &s_hdr[warp], &s_ops[warp * SEG_CAP], lane);
+            else if (lane == 0) { s_hdr[warp].nops = 0; s_hdr[warp].more = 0; }
+            __syncthreads();
+            int any_more = 0;
+            for (int w = 0; w < nslots; w++) any_more |= s_hdr[w].more;
+            if (!any_more) {
+                if (active)
+                    for (int w = 0; w < nslots; w++)
+                        visit_slot<MODE>(a, &s_hdr[w], &s_ops[w * SEG_CAP], P, kins, s_ref, Lwin, populated, max_ins,
+                                         cnt, base, run, qrow, Wm1, err);
+                __syncthreads();
+            } else {
+                // rare: a read with more than SEG_CAP relevant ops -> strictly serial over the chunk's reads
+                for (int w = 0; w < nslots; w++) {
+                    while (true) {
+                        if (active)
+                            visit_slot<MODE>(a, &s_hdr[w], &s_ops[w * SEG_CAP], P, kins, s_ref, Lwin, populated,
+                                             max_ins, cnt, base, run, qrow, Wm1, err);
+                        __syncthreads();
+                        const int more = s_hdr[w].more;
+                        __syncthreads();
+                        if (!more) break;
+                        if (warp == w) stage_read(a, s_cand[ch + w], qs, qe, false, &s_hdr[w], &s_ops[w * SEG_CAP], lane);
+                        __syncthreads();
+                    }
+                }
+            }
+        }
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(ENC_THREADS) encode_windows_kernel(EncArgs a) {
+    extern __shared__ __align__(16) uint8_t smem[];
+    const int tid = threadIdx.x;
+    const int w = blockIdx.x;
+    const int L = a.L, W = a.W, H = a.H;
+    const int qs = a.win_qs[w];
+    const int qe = qs + L;
+    const int lo = a.win_lo[w], hi = a.win_hi[w];
+
+    // ---- shared memory carve-up
+    uint8_t *p = smem;
+    SegOp *s_ops = (SegOp *)p;            p += sizeof(SegOp) * ENC_WARPS * SEG_CAP;
+    SegHdr *s_hdr = (SegHdr *)p;          p += sizeof(SegHdr) * ENC_WARPS;
+    int *s_cand = (int *)p;               p += sizeof(int) * CAND_BLOCK;
+    int *s_rowstart = (int *)p;           p += sizeof(int) * (ENC_THREADS + 4);
+    int *s_flags = (int *)p;              p += sizeof(int) * 16;
+    short *s_rowcol = (short *)p;         p += sizeof(short) * ENC_THREADS;
+    short *s_rowk = (short *)p;           p += sizeof(short) * ENC_THREADS;
+    unsigned short *s_cum = (unsigned short *)p; p += sizeof(unsigned short) * ENC_THREADS * 8;
+    unsigned short *s_maxins = (unsigned short *)p; p += sizeof(unsigned short) * ENC_THREADS;
+    uint8_t *s_ref = p;                   p += ((L + 1 + 15) / 16) * 16;
+    uint8_t *s_rowref = p;                p += ENC_THREADS;
+    uint8_t *s_q = p;                     // [H][W] quality bytes (pixel 0 unused)
+    int *s_err = &s_flags[8];
+    int *s_nrows = &s_flags[9];
+    int *s_ncand = &s_flags[10];
+
+    if (tid == 0) { *s_err = 0; *s_nrows = 0; }
+    // window must lie inside the supplied reference: refSequence = ref[qs .. qe] (L+1 chars, Pileup.py:41)
+    const long long roff = (long long)qs - a.ref_base;
+    const bool ref_ok = roff >= 0 && roff + L + 1 <= a.ref_len;
+    for (int i = tid; i < L + 1; i += ENC_THREADS) s_ref[i] = ref_ok ? a.ref[roff + i] : (uint8_t)'N';
+    __syncthreads();
+
+    int err = ref_ok ? 0 : DP_EINVAL;
+    int cnt[NCAT], base[NCAT], run[NCAT];
+#pragma unroll
+    for (int c = 0; c < NCAT; c++) { cnt[c] = 0; base[c] = 0; run[c] = 0; }
+
+    // ---- pass 0: one thread per column
+    int populated = 0, max_ins = 0;
+    {
+        const bool active = tid < L;
+        run_pass<0>(a, qs, qe, lo, hi, s_hdr, s_ops, s_cand, s_ncand, s_flags, s_ref, tid, 0, active, populated, max_ins,
+                    cnt, base, run, nullptr, W - 1, err);
+    }
+    // ---- row map: rows = populated columns in ascending order, each followed by its insert rows (:295-317)
+    {
+        const int nrows_here = (tid < L && populated) ? 1 + max_ins : 0;
+        s_rowstart[tid] = nrows_here;
+        s_maxins[tid] = (unsigned short)min(max_ins, 65535);
+        s_rowcol[tid] = -1; s_rowk[tid] = 0; s_rowref[tid] = 'N';
+        __syncthreads();
+        if (tid == 0) {                      // L <= 256: a serial scan is ~200 adds
+            int acc = 0, anchors = 0;
+            for (int c = 0; c < L; c++) {
+                const int v = s_rowstart[c];
+                s_rowstart[c] = acc;
+                if (v) {
+                    // reference pixel of an anchor row: refSequence[c'] with 'I' spliced at every insert row
+                    // (:315) == original ref[#anchor rows before it]
+                    if (acc < ENC_THREADS) s_rowref[acc] = s_ref[anchors];
+                    anchors++;
+                }
+                acc += v;
+            }
+            *s_nrows = acc;
+        }
+        __syncthreads();
+        if (tid < L && populated) {
+            const int r0 = s_rowstart[tid];
+            for (int k = 0; k <= max_ins; k++) {
+                const int y = r0 + k;
+                if (y >= H) break;
+                s_rowcol[y] = (short)tid; s_rowk[y] = (short)k;
+            }
+        }
+        __syncthreads();
+    }
+    const int nrows = min(*s_nrows, H);
+    // ---- passes 1 and 2: one thread per image row
+    {
+        const bool active = tid < nrows;
+        const int P = active ? s_rowcol[tid] : 0;
+        const int kins = active ? s_rowk[tid] : 0;
+        int dummy_p = 0, dummy_m = 0;
+        run_pass<1>(a, qs, qe, lo, hi, s_hdr, s_ops, s_cand, s_ncand, s_flags, s_ref, P, kins, active, dummy_p, dummy_m, cnt,
+                    base, run, nullptr, W - 1, err);
+        int acc = 0;
+#pragma unroll
+        for (int c = 0; c < NCAT; c++) { base[c] = acc; acc += cnt[c]; if (acc < 0) acc = INT_MAX / 2; }
+        if (tid < H) {
+#pragma unroll
+            for (int c = 0; c < NCAT; c++) s_cum[tid * 8 + c] = (unsigned short)min(base[c] + cnt[c], W - 1);
+            s_cum[tid * 8 + 7] = 0;
+        }
+        uint8_t *qrow = s_q + (size_t)tid * W;
+        run_pass<2>(a, qs, qe, lo, hi, s_hdr, s_ops, s_cand, s_ncand, s_flags, s_ref, P, kins, active, dummy_p, dummy_m, cnt,
+                    base, run, active ? qrow : nullptr, W - 1, err);
+    }
+    if (err) atomicMin(s_err, err);         // codes are negative; keep the most severe deterministic choice
+    __syncthreads();
+
+    // reference pixel must be a legal colour key (KeyError at :281 otherwise)
+    // ---- emit: RGBA rows, 16-byte stores
+    uint8_t *img = a.out_img + (size_t)w * H * W * 4;
+    const int quads_per_row = W / 4;        // W % 4 == 0 enforced by the host
+    const int total_quads = H * quads_per_row;
+    int bad_ref = 0;
+    for (int qd = tid; qd < total_quads; qd += ENC_THREADS) {
+        const int y = qd / quads_per_row;
+        const int x0 = (qd - y * quads_per_row) * 4;
+        uint32_t px[4];
+        if (y >= nrows) {
+            px[0] = px[1] = px[2] = px[3] = 0xFF000000u;
+        } else {
+            const bool ins = s_rowk[y] != 0;
+            const uint32_t filler = ins ? 0xFFFF00FFu : 0xFF000000u;      // 'I' (255,0,255) / none (0,0,0), alpha 255
+            const unsigned short *cum = &s_cum[y * 8];
+            const int tot = cum[6];
+#pragma unroll
+            for (int t = 0; t < 4; t++) {
+                const int x = x0 + t;
+                uint32_t v;
+                if (x == 0) {
+                    if (ins) v = 0xFFFF00FFu;
+                    else {
+                        const int ch = s_rowref[y];
+                        const int cat = cat_of_ascii(ch);
+                        if (cat < 0) { bad_ref = 1; v = 0xFF000000u; }
+                        else v = cat_rgb(cat) | 0xFF000000u;
+                    }
+                } else {
+                    const int e = x - 1;
+                    if (e >= tot) v = filler;
+                    else {
+                        int cat = 0;
+#pragma unroll
+                        for (int c = 0; c < 6; c++) cat += (e >= cum[c]) ? 1 : 0;
+                        v = cat_rgb(cat) | ((uint32_t)s_q[(size_t)y * W + x] << 24);
+                    }
+                }
+                px[t] = v;
+            }
+        }
+        *reinterpret_cast<uint4 *>(img + ((size_t)y * W + x0) * 4) = make_uint4(px[0], px[1], px[2], px[3]);
+    }
+    if (bad_ref) atomicMin(s_err, (int)DP_EKEY);
+    for (int y = tid; y < H; y += ENC_THREADS) {
+        if (a.out_rowpos) a.out_rowpos[(size_t)w * H + y] = (y < nrows) ? qs + s_rowcol[y] : -1;
+        if (a.out_rowins) a.out_rowins[(size_t)w * H + y] = (y < nrows) ? s_rowk[y] : 0;
+    }
+    __syncthreads();
+    if (tid == 0 && a.out_status) a.out_status[w] = *s_err;
+}
+
+static size_t encoder_smem_bytes(const dp_encode_params *p) {
+    const int L = 2 * p->flank + 1;
+    size_t s = 0;
+    s += sizeof(SegOp) * ENC_WARPS * SEG_CAP;
+    s += sizeof(SegHdr) * ENC_WARPS;
+    s += sizeof(int) * CAND_BLOCK;
+    s += sizeof(int) * (ENC_THREADS + 4);
+    s += sizeof(int) * 16;
+    s += sizeof(short) * ENC_THREADS * 2;
+    s += sizeof(unsigned short) * ENC_THREADS * 8;
+    s += sizeof(unsigned short) * ENC_THREADS;
+    s += ((L + 1 + 15) / 16) * 16;
+    s += ENC_THREADS;
+    s += (size_t)p->window_cutoff * p->coverage_cutoff;
+    return s + 16;
+}
+
+}  // namespace dp
+
+// ================================================================================================
+extern "C" {
+
+const char *dp_last_error(void) { return dp::g_err; }
+int dp_version(void) { return 100; }
+int dp_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+int dp_set_quality_lut(const uint8_t lut[256]) {
+    if (!lut) return DP_EINVAL;
+    DP_CUDA_CHECK(cudaMemcpyToSymbol(dp::c_qlut, lut, 256));
+    int dev = 0;
+    DP_CUDA_CHECK(cudaGetDevice(&dev));
+    if (dev < 64) dp::g_lut_ready[dev] = true;
+    return DP_OK;
+}
+
+int64_t dp_encode_workspace_bytes(int32_t n_reads, int64_t n_cigar, int32_t n_windows, const dp_encode_params *p) {
+    (void)n_windows; (void)p;
+    int64_t b = 0;
+    b += dp::align_up((int64_t)sizeof(dp::ReadAux) * (n_reads > 0 ? n_reads : 1), 256);
+    b += dp::align_up((int64_t)sizeof(int) * (n_cigar + n_reads + 1), 256);   /* RP: nops+1 per read */
+    b += dp::align_up((int64_t)sizeof(int) * (n_cigar + 1), 256);             /* QP */
+    return b;
+}
+
+int dp_encode_windows(const dp_reads *reads, int32_t n_windows, const int32_t *win_qs, const int32_t *win_lo,
+                      const int32_t *win_hi, const uint8_t *ref, int64_t ref_base, int64_t ref_len,
+                      const dp_encode_params *p, uint8_t *out_img, int32_t *out_rowpos, int32_t *out_rowins,
+                      int32_t *out_status, void *workspace, int64_t workspace_bytes, void *stream) {
+    DP_REQUIRE(reads && p && out_img, "null argument");
+    DP_REQUIRE(n_windows >= 0 && reads->n_reads >= 0, "negative extent");
+    if (n_windows == 0) return DP_OK;
+    DP_REQUIRE(win_qs && win_lo && win_hi && ref, "null argument");
+    const int L = 2 * p->flank + 1;
+    DP_REQUIRE(p->flank >= 0 && L <= dp::ENC_THREADS, "flankLength must satisfy 2*flank+1 <= 256");
+    DP_REQUIRE(p->window_cutoff >= 1 && p->window_cutoff <= dp::ENC_THREADS, "windowCutoff must be in [1,256]");
+    DP_REQUIRE(p->coverage_cutoff >= 4 && p->coverage_cutoff % 4 == 0 && p->coverage_cutoff <= 1024,
+               "coverageCutoff must be a multiple of 4 in [4,1024]");
+    cudaStream_t st = (cudaStream_t)stream;
+    int rc = dp::ensure_lut();
+    if (rc) return rc;
+
+    const int64_t n_cigar = reads->n_cigar;
+    DP_REQUIRE(n_cigar >= 0, "negative n_cigar");
+    const int64_t need = dp_encode_workspace_bytes(reads->n_reads, n_cigar, n_windows, p);
+    DP_REQUIRE(workspace && workspace_bytes >= need, "workspace too small (dp_encode_workspace_bytes)");
+    uint8_t *wp = (uint8_t *)workspace;
+    dp::ReadAux *aux = (dp::ReadAux *)wp;
+    wp += dp::align_up((int64_t)sizeof(dp::ReadAux) * (reads->n_reads > 0 ? reads->n_reads : 1), 256);
+    int *RP = (int *)wp;
+    wp += dp::align_up((int64_t)sizeof(int) * (n_cigar + reads->n_reads + 1), 256);
+    int *QP = (int *)wp;
+
+    if (reads->n_reads > 0) {
+        const int warps_per_block = 8;
+        const int blocks = (reads->n_reads + warps_per_block - 1) / warps_per_block;
+        dp::prep_reads_kernel<<<blocks, 256, 0, st>>>(*reads, aux, RP, QP);
+        DP_CUDA_CHECK(cudaGetLastError());
+    }
+    dp::EncArgs a;
+    a.R = *reads; a.aux = aux; a.RP = RP; a.QP = QP;
+    a.win_qs = win_qs; a.win_lo = win_lo; a.win_hi = win_hi;
+    a.ref = ref; a.ref_base = ref_base; a.ref_len = ref_len;
+    a.L = L; a.W = p->coverage_cutoff; a.H = p->window_cutoff; a.mapq_cut = p->map_quality_cutoff;
+    a.out_img = out_img; a.out_rowpos = out_rowpos; a.out_rowins = out_rowins; a.out_status = out_status;
+    const size_t smem = dp::encoder_smem_bytes(p);
+    DP_REQUIRE(smem <= 227 * 1024, "coverageCutoff*windowCutoff too large for shared-memory staging");
+    DP_CUDA_CHECK(cudaFuncSetAttribute(dp::encode_windows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    dp::encode_windows_kernel<<<n_windows, dp::ENC_THREADS, smem, st>>>(a);
+    DP_CUDA_CHECK(cudaGetLastError());
+    return DP_OK;
+}
+
+}  // extern "C"

@@ -34,6 +34,7 @@ extern "C" {
  * dp_* functions (HOST pointers for the dpo_* oracle twin in oracle/pileup_oracle.h). */
 typedef struct dp_reads {
     int32_t        n_reads;
+    int64_t        n_cigar;    /* total CIGAR ops == cigar_off[n_reads] (known to the host reader)      */
     const int32_t *pos;        /* [n_reads]   0-based leftmost coordinate (core.pos)                  */
     const uint16_t*flag;       /* [n_reads]   only BAM_FUNMAP (0x4) is consulted (bam_endpos)          */
     const uint8_t *mapq;       /* [n_reads]                                                            */

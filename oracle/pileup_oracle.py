@@ -16,7 +16,7 @@ QUALITY_LUT = np.array([int(round((1 - (10 ** ((q) / -10))) * 255)) for q in ran
 
 
 class _Reads(C.Structure):
-    _fields_ = [("n_reads", C.c_int32), ("pos", C.c_void_p), ("flag", C.c_void_p), ("mapq", C.c_void_p),
+    _fields_ = [("n_reads", C.c_int32), ("n_cigar", C.c_int64), ("pos", C.c_void_p), ("flag", C.c_void_p), ("mapq", C.c_void_p),
                 ("l_seq", C.c_void_p), ("cigar_off", C.c_void_p), ("cigar", C.c_void_p),
                 ("seq_off", C.c_void_p), ("seq4", C.c_void_p), ("qual_off", C.c_void_p), ("qual", C.c_void_p)]
 
@@ -27,7 +27,8 @@ class _Params(C.Structure):
 
 
 def build(force=False):
-    if force or not os.path.isfile(LIB) or os.path.getmtime(LIB) < os.path.getmtime(os.path.join(HERE, "pileup_oracle.c")):
+    deps = [os.path.join(HERE, "pileup_oracle.c"), os.path.join(HERE, "..", "include", "deepore_b200.h")]
+    if force or not os.path.isfile(LIB) or any(os.path.getmtime(LIB) < os.path.getmtime(d) for d in deps):
         subprocess.check_call(["make", "-C", HERE, "-s"])
     return LIB
 
@@ -61,7 +62,7 @@ def encode_windows(reads, win_qs, win_lo, win_hi, ref, ref_base, flank=100, cove
         keep.append(a)
         return _ptr(a)
 
-    R = _Reads(int(reads.pos.shape[0]), c(reads.pos, np.int32), c(reads.flag, np.uint16), c(reads.mapq, np.uint8),
+    R = _Reads(int(reads.pos.shape[0]), int(reads.cigar.shape[0]), c(reads.pos, np.int32), c(reads.flag, np.uint16), c(reads.mapq, np.uint8),
                c(reads.l_seq, np.int32), c(reads.cigar_off, np.int64), c(reads.cigar, np.uint32),
                c(reads.seq_off, np.int64), c(reads.seq4, np.uint8), c(reads.qual_off, np.int64),
                c(reads.qual, np.uint8))
