@@ -19,70 +19,115 @@ import numpy as np
 
 from . import _lib
 from .reads import ReadBatch, BamFile, FastaFile
+from .workload import IntervalShard, make_shard
 
 
-def _reads_struct(dev: dict, rb: ReadBatch) -> _lib.Reads:
-    return _lib.Reads(rb.n_reads, rb.n_cigar, dev["pos"].data_ptr(), dev["flag"].data_ptr(), dev["mapq"].data_ptr(),
-                      dev["l_seq"].data_ptr(), dev["cigar_off"].data_ptr(), dev["cigar"].data_ptr(),
-                      dev["seq_off"].data_ptr(), dev["seq4"].data_ptr(), dev["qual_off"].data_ptr(),
-                      dev["qual"].data_ptr())
+_FIELDS = ("pos", "flag", "mapq", "l_seq", "cigar_off", "cigar", "seq_off", "seq4", "qual_off", "qual")
 
 
-class EncoderPlan:
-    """Device-resident inputs of one contig interval + reusable workspace; `run()` launches the kernels."""
+def _align(x, a=256):
+    return (x + a - 1) // a * a
 
-    def __init__(self, reads: ReadBatch, ref: np.ndarray, ref_base: int, flank: int = 100, coverageCutoff: int = 200,
-                 windowCutoff: int = 150, mapQualityCutoff: int = 20, device="cuda"):
+
+class ShardBuffers:
+    """One IntervalShard packed into ONE pinned host buffer and ONE device buffer (256-byte aligned
+    sections), so that handing a shard to the GPU is a single cudaMemcpyAsync."""
+
+    def __init__(self, shard: IntervalShard, device="cuda", pin: bool = True):
+        import torch
+        self.torch = torch
+        self.shard = shard
+        self.device = torch.device(device)
+        rb = shard.reads
+        arrays = [(n, getattr(rb, n)) for n in _FIELDS]
+        arrays += [("ref", shard.ref), ("win_qs", shard.win_qs), ("win_lo", shard.win_lo), ("win_hi", shard.win_hi)]
+        self.off = {}
+        total = 0
+        for n, a in arrays:
+            self.off[n] = total
+            total += _align(max(int(a.nbytes), 16))
+        self.nbytes = total
+        host = torch.empty(total, dtype=torch.uint8)
+        if pin and self.device.type == "cuda":
+            host = host.pin_memory()
+        hv = host.numpy()
+        for n, a in arrays:
+            b = np.ascontiguousarray(a).view(np.uint8).reshape(-1)
+            hv[self.off[n]:self.off[n] + b.shape[0]] = b
+        self.host = host
+        self.dev = torch.empty(total, dtype=torch.uint8, device=self.device)
+        base = self.dev.data_ptr()
+        p = {n: base + o for n, o in self.off.items()}
+        self.rstruct = _lib.Reads(rb.n_reads, rb.n_cigar, p["pos"], p["flag"], p["mapq"], p["l_seq"], p["cigar_off"],
+                                  p["cigar"], p["seq_off"], p["seq4"], p["qual_off"], p["qual"])
+        self.ptr = p
+        self.n_windows = shard.n_windows
+        self.ref_base = int(shard.ref_base)
+        self.ref_len = int(shard.ref.shape[0])
+
+    def upload(self, non_blocking: bool = True):
+        """Host -> device copy of the whole shard on the current stream."""
+        self.dev.copy_(self.host, non_blocking=non_blocking)
+        return self
+
+
+class Encoder:
+    """Launches the encoder kernels (C-ABI dp_encode_windows) for uploaded shards."""
+
+    def __init__(self, flank: int = 100, coverageCutoff: int = 200, windowCutoff: int = 150,
+                 mapQualityCutoff: int = 20, device="cuda"):
         import torch
         _lib.require_cuda()
         self.torch = torch
         self.device = torch.device(device)
-        self.reads = reads
         self.params = _lib.EncodeParams(flank, coverageCutoff, windowCutoff, mapQualityCutoff)
         self.flank, self.W, self.H = flank, coverageCutoff, windowCutoff
-        self.ref_base = int(ref_base)
-        self.ref_len = int(ref.shape[0])
-        with torch.cuda.device(self.device):
-            self.dev = reads.to_device(self.device)
-            self.ref_dev = torch.from_numpy(np.ascontiguousarray(ref, dtype=np.uint8)).pin_memory().to(self.device, non_blocking=True)
-            self.rstruct = _reads_struct(self.dev, reads)
-            nbytes = _lib.lib().dp_encode_workspace_bytes(reads.n_reads, reads.n_cigar, 0, C.byref(self.params))
-            self.workspace = torch.empty(max(int(nbytes), 256), dtype=torch.uint8, device=self.device)
+        self.workspace = None
 
-    def run(self, win_qs, win_lo, win_hi, out_img=None, want_rowmap=True, stream=None):
-        """win_* : int32 device tensors [Nw].  Returns (img uint8[Nw,H,W,4], rowpos, rowins, status)."""
+    def _workspace(self, n_reads, n_cigar):
+        need = int(_lib.lib().dp_encode_workspace_bytes(n_reads, n_cigar, 0, C.byref(self.params)))
+        if self.workspace is None or self.workspace.numel() < need:
+            self.workspace = self.torch.empty(max(need, 256), dtype=self.torch.uint8, device=self.device)
+        return self.workspace
+
+    def encode(self, sb: ShardBuffers, out_img=None, rowpos=None, rowins=None, status=None, want_rowmap=True,
+               stream=None):
+        """Returns (img uint8[Nw,H,W,4], rowpos int32[Nw,H], rowins int32[Nw,H], status int32[Nw]), all on
+        the device; nothing is synchronised."""
         torch = self.torch
-        nw = int(win_qs.shape[0])
+        nw = sb.n_windows
+        dev = self.device
         if out_img is None:
-            out_img = torch.empty((nw, self.H, self.W, 4), dtype=torch.uint8, device=self.device)
-        rowpos = torch.empty((nw, self.H), dtype=torch.int32, device=self.device) if want_rowmap else None
-        rowins = torch.empty((nw, self.H), dtype=torch.int32, device=self.device) if want_rowmap else None
-        status = torch.empty((nw,), dtype=torch.int32, device=self.device)
-        st = stream if stream is not None else torch.cuda.current_stream(self.device)
+            out_img = torch.empty((nw, self.H, self.W, 4), dtype=torch.uint8, device=dev)
+        if want_rowmap:
+            if rowpos is None:
+                rowpos = torch.empty((nw, self.H), dtype=torch.int32, device=dev)
+            if rowins is None:
+                rowins = torch.empty((nw, self.H), dtype=torch.int32, device=dev)
+        if status is None:
+            status = torch.empty((nw,), dtype=torch.int32, device=dev)
+        ws = self._workspace(sb.rstruct.n_reads, sb.rstruct.n_cigar)
+        st = stream if stream is not None else torch.cuda.current_stream(dev)
         rc = _lib.lib().dp_encode_windows(
-            C.byref(self.rstruct), nw, win_qs.data_ptr(), win_lo.data_ptr(), win_hi.data_ptr(),
-            self.ref_dev.data_ptr(), self.ref_base, self.ref_len, C.byref(self.params),
-            out_img.data_ptr(), rowpos.data_ptr() if want_rowmap else None,
-            rowins.data_ptr() if want_rowmap else None, status.data_ptr(),
-            self.workspace.data_ptr(), self.workspace.numel(), C.c_void_p(st.cuda_stream))
+            C.byref(sb.rstruct), nw, sb.ptr["win_qs"], sb.ptr["win_lo"], sb.ptr["win_hi"], sb.ptr["ref"],
+            sb.ref_base, sb.ref_len, C.byref(self.params), out_img.data_ptr(),
+            rowpos.data_ptr() if want_rowmap else None, rowins.data_ptr() if want_rowmap else None,
+            status.data_ptr(), ws.data_ptr(), ws.numel(), C.c_void_p(st.cuda_stream))
         _lib.check(rc, "dp_encode_windows")
-        return out_img, rowpos, rowins, status
+        return out_img, (rowpos if want_rowmap else None), (rowins if want_rowmap else None), status
 
 
 def encode_windows(reads: ReadBatch, win_qs: np.ndarray, ref: np.ndarray, ref_base: int, flank: int = 100,
                    coverageCutoff: int = 200, windowCutoff: int = 150, mapQualityCutoff: int = 20, device="cuda",
                    want_rowmap: bool = True):
-    """Host-buffer convenience: uploads, encodes every window, returns device tensors
+    """Host-buffer convenience: packs the shard, uploads, encodes every window, returns device tensors
     (img uint8[Nw,H,W,4], rowpos int32[Nw,H], rowins int32[Nw,H], status int32[Nw])."""
-    import torch
-    plan = EncoderPlan(reads, ref, ref_base, flank, coverageCutoff, windowCutoff, mapQualityCutoff, device)
-    win_qs = np.ascontiguousarray(win_qs, dtype=np.int32)
-    lo, hi = reads.window_ranges(win_qs, flank)
-    dev = plan.device
-    q = torch.from_numpy(win_qs).to(dev)
-    l = torch.from_numpy(lo).to(dev)
-    h = torch.from_numpy(hi).to(dev)
-    return plan.run(q, l, h, want_rowmap=want_rowmap)
+    _lib.require_cuda()
+    shard = make_shard(reads, np.ascontiguousarray(ref, dtype=np.uint8), int(ref_base),
+                       np.ascontiguousarray(win_qs, dtype=np.int32), flank)
+    sb = ShardBuffers(shard, device).upload()
+    enc = Encoder(flank, coverageCutoff, windowCutoff, mapQualityCutoff, device)
+    return enc.encode(sb, want_rowmap=want_rowmap)
 
 
 _STATUS_EXC = {_lib.DP_EKEY: KeyError, _lib.DP_EINDEX: IndexError, _lib.DP_EINVAL: ValueError}

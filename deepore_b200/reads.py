@@ -146,6 +146,19 @@ class ReadBatch:
             self._dev[key] = d
         return self._dev[key]
 
+    def slice(self, r0: int, r1: int) -> "ReadBatch":
+        """Records [r0, r1) as a self-contained batch (offsets rebased) -- what a host reader hands over for
+        one genomic interval."""
+        r0 = max(0, int(r0)); r1 = max(r0, min(int(r1), self.n_reads))
+        c0, c1 = int(self.cigar_off[r0]), int(self.cigar_off[r1])
+        s0, s1 = int(self.seq_off[r0]), int(self.seq_off[r1])
+        q0, q1 = int(self.qual_off[r0]), int(self.qual_off[r1])
+        return ReadBatch(contig=self.contig, pos=self.pos[r0:r1].copy(), flag=self.flag[r0:r1].copy(),
+                         mapq=self.mapq[r0:r1].copy(), l_seq=self.l_seq[r0:r1].copy(),
+                         cigar_off=self.cigar_off[r0:r1 + 1] - c0, cigar=self.cigar[c0:c1].copy(),
+                         seq_off=self.seq_off[r0:r1 + 1] - s0, seq4=self.seq4[s0:s1].copy(),
+                         qual_off=self.qual_off[r0:r1 + 1] - q0, qual=self.qual[q0:q1].copy())
+
     def nbytes(self) -> int:
         return sum(getattr(self, n).nbytes for n in
                    ("pos", "flag", "mapq", "l_seq", "cigar_off", "cigar", "seq_off", "seq4", "qual_off", "qual"))
