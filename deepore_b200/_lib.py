@@ -29,6 +29,14 @@ class EncodeParams(C.Structure):
                 ("map_quality_cutoff", C.c_int32)]
 
 
+class ModelWeights(C.Structure):
+    _fields_ = [("in_ch", C.c_int32), ("width", C.c_int32), ("hidden", C.c_int32), ("n_class", C.c_int32),
+                ("seq_len", C.c_int32), ("n_layers", C.c_int32), ("fold_w", C.c_void_p), ("fold_b", C.c_void_p),
+                ("gru_w_ih", (C.c_void_p * 2) * 3), ("gru_w_hh", (C.c_void_p * 2) * 3),
+                ("gru_b_ih", (C.c_void_p * 2) * 3), ("gru_b_hh", (C.c_void_p * 2) * 3),
+                ("fc1_w", C.c_void_p), ("fc1_b", C.c_void_p)]
+
+
 _lib = None
 
 
@@ -53,6 +61,19 @@ def lib():
                                     C.c_int64, C.c_void_p]
     L.dp_set_quality_lut.restype = C.c_int
     L.dp_set_quality_lut.argtypes = [C.c_void_p]
+    L.dp_model_create.restype = C.c_int
+    L.dp_model_create.argtypes = [C.c_void_p, C.c_int64, C.c_int32, C.POINTER(C.c_void_p)]
+    L.dp_model_destroy.restype = C.c_int
+    L.dp_model_destroy.argtypes = [C.c_void_p]
+    L.dp_model_forward_rows.restype = C.c_int
+    L.dp_model_forward_rows.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.dp_vote.restype = C.c_int
+    L.dp_vote.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.dp_model_peek.restype = C.c_int
+    L.dp_model_peek.argtypes = [C.c_void_p, C.c_int32, C.c_int64, C.c_void_p]
+    L.dp_gemm_bf16.restype = C.c_int
+    L.dp_gemm_bf16.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32,
+                               C.c_int64, C.c_int64, C.c_int64, C.c_int32, C.c_void_p]
     _lib = L
     return L
 

@@ -1,0 +1,524 @@
+// deePore model forward on B200: C-ABI (include/deepore_b200.h, dp_model_*) over the tcgen05 kernels of tc_gemm.cu.
+//
+// Replaces /root/reference/src/modules/model.py Model.forward (:137-156) and the decode loop of
+// /root/reference/src/test.py (:59-89) for whole pileup images:
+//
+//   u8 image rows [n_rows][W*4]  --convert-->  bf16 (values 0..255 are exact in bf16)
+//   folded CNN+Linear operator   y[row][t][:] = sum_s Weff[t][s] . img[row+s] + beff[t]       (one tcgen05 GEMM, K = 3*W*4)
+//        The five residual blocks contain convolutions and eval-mode BatchNorm only (model.py:93-105: no activation),
+//        so CNN + reinterpreting view (:144-149) + cnn_fc_rnn (:151) is ONE affine map of the three input rows; the host
+//        composes it once per checkpoint (deepore_b200/fold.py) and the /255 of ToTensor is folded in as well.
+//   3 x bidirectional GRU        9 gru_step launches (3 layers x 3 time steps, both directions per launch), h0 of layer k =
+//        h_n of layer k-1 (model.py:124-135), directions summed
+//   fc1 + argmax                 logits[row][t][c] (model.py:154-155), first maximum wins (torch.topk, test.py:68)
+//   vote                         3-way majority over (row-2,t=2),(row-1,t=1),(row,t=0), smallest class on a 3-way tie
+//                                (test.py:23-24,71-82)
+#include <math.h>
+#include <stdlib.h>
+
+#include <vector>
+
+#include "tc_gemm.cuh"
+
+namespace dp {
+
+constexpr int HP = 512;            // padded hidden size
+constexpr int NSLOT_BF = 30;       // bf16 arena slots  (y: 0..2; layer k: 3+9k + {hf 0..2, hb 3..5, xn 6..8})
+constexpr int NSLOT_F32 = 18;      // fp32 state slots  (layer k: 6k + {hf 0..2, hb 3..5})
+
+static inline uint16_t f2bf(float f) {
+    uint32_t u;
+    memcpy(&u, &f, 4);
+    if ((u & 0x7fffffffu) > 0x7f800000u) return (uint16_t)((u >> 16) | 0x40);
+    u += 0x7fffu + ((u >> 16) & 1u);
+    return (uint16_t)(u >> 16);
+}
+static inline float bf2f(uint16_t h) {
+    uint32_t u = (uint32_t)h << 16;
+    float f;
+    memcpy(&f, &u, 4);
+    return f;
+}
+
+struct Model {
+    int in_ch, width, hidden, n_class, seq_len, n_layers;
+    int row_elems;                 // width * in_ch (800)
+    int kfold_pad;                 // per-row-slot K of the folded operator padded to 64 (832)
+    int precise;
+    long long mcap;                // row capacity (multiple of 128)
+    int device;
+    // device buffers
+    __nv_bfloat16 *img_bf = nullptr;      // [mcap + 128][row_elems]
+    __nv_bfloat16 *arena = nullptr;       // [NSLOT_BF][mcap][HP]
+    __nv_bfloat16 *arena_lo = nullptr;    // precise only
+    float *state = nullptr;               // [NSLOT_F32][mcap][HP]
+    __nv_bfloat16 *w_fold = nullptr;      // [3*HP][kcols_fold]
+    float *b_fold = nullptr;              // [3*HP]
+    __nv_bfloat16 *w_gru = nullptr;       // [n_layers*2*3*HP][kcols_gru]
+    float *b_gru = nullptr;               // [n_layers*2][4][HP]
+    float *w_fc1 = nullptr, *b_fc1 = nullptr;   // [n_class][HP], [n_class]
+    KChunk *tables = nullptr;
+    int fold_tab_off = 0, fold_tab_n = 0;
+    int gru_tab_off[3][3][2], gru_tab_n[3][3][2];
+    long long kcols_fold = 0, kcols_gru = 0;
+    CUtensorMap tm_img, tm_arena, tm_arena_lo, tm_wfold, tm_wgru;
+};
+
+static void free_model(Model *m) {
+    if (!m) return;
+    cudaFree(m->img_bf); cudaFree(m->arena); cudaFree(m->arena_lo); cudaFree(m->state); cudaFree(m->w_fold);
+    cudaFree(m->b_fold); cudaFree(m->w_gru); cudaFree(m->b_gru); cudaFree(m->w_fc1); cudaFree(m->b_fc1);
+    cudaFree(m->tables);
+    delete m;
+}
+
+static inline int bf_slot_y(int t) { return t; }
+static inline int bf_slot_hf(int k, int t) { return 3 + 9 * k + t; }
+static inline int bf_slot_hb(int k, int t) { return 3 + 9 * k + 3 + t; }
+static inline int bf_slot_xn(int k, int t) { return 3 + 9 * k + 6 + t; }
+static inline int f32_slot_hf(int k, int t) { return 6 * k + t; }
+static inline int f32_slot_hb(int k, int t) { return 6 * k + 3 + t; }
+
+// ------------------------------------------------------------------------------------------------
+// small CUDA-core kernels around the GEMMs
+
+// u8 -> bf16, 16 bytes in / 32 bytes out per thread (exact: integers <= 255 fit the 8-bit bf16 significand)
+__global__ void __launch_bounds__(256) u8_to_bf16_kernel(const uint4 *__restrict__ in, uint4 *__restrict__ out, long long n16) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n16) return;
+    const uint4 v = __ldg(in + i);
+    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+    uint32_t o[8];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const float b0 = (float)(w[k] & 0xff), b1 = (float)((w[k] >> 8) & 0xff);
+        const float b2 = (float)((w[k] >> 16) & 0xff), b3 = (float)(w[k] >> 24);
+        __nv_bfloat162 p0 = __floats2bfloat162_rn(b0, b1), p1 = __floats2bfloat162_rn(b2, b3);
+        o[2 * k] = *reinterpret_cast<uint32_t *>(&p0);
+        o[2 * k + 1] = *reinterpret_cast<uint32_t *>(&p1);
+    }
+    out[2 * i] = make_uint4(o[0], o[1], o[2], o[3]);
+    out[2 * i + 1] = make_uint4(o[4], o[5], o[6], o[7]);
+}
+
+// fc1 (model.py:90,154) + top-1 (test.py:68): one warp per (row, t).  out = hf + hb of the last GRU layer (fp32).
+__global__ void __launch_bounds__(256) fc1_argmax_kernel(const float *__restrict__ hf, const float *__restrict__ hb,
+                                                         long long slot_stride, const float *__restrict__ w,
+                                                         const float *__restrict__ b, int n_class, int seq_len,
+                                                         long long n_rows, float *__restrict__ logits,
+                                                         uint8_t *__restrict__ pred) {
+    const long long wid = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (wid >= n_rows * seq_len) return;
+    const long long m = wid / seq_len;
+    const int t = (int)(wid % seq_len);
+    const float *pf = hf + t * slot_stride + m * HP;
+    const float *pb = hb + t * slot_stride + m * HP;
+    float x[HP / 32];
+#pragma unroll
+    for (int i = 0; i < HP / 32; i++) x[i] = pf[lane + 32 * i] + pb[lane + 32 * i];
+    float best = 0.f;
+    int besti = 0;
+    for (int c = 0; c < n_class; c++) {
+        float acc = 0.f;
+#pragma unroll
+        for (int i = 0; i < HP / 32; i++) acc = fmaf(x[i], __ldg(w + c * HP + lane + 32 * i), acc);
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, d);
+        acc += __ldg(b + c);
+        if (lane == 0 && logits) logits[(m * seq_len + t) * n_class + c] = acc;
+        if (c == 0 || acc > best) { best = acc; besti = c; }
+    }
+    if (lane == 0 && pred) pred[m * seq_len + t] = (uint8_t)besti;
+}
+
+// 3-way vote (test.py:71-82, most_common :23-24).  pred [n_windows][H][3]; calls [n_windows][H] int8, -1 where the
+// reference scores nothing (rows 0,1 and the last rows without a full 3-row window).
+__global__ void __launch_bounds__(256) vote_kernel(const uint8_t *__restrict__ pred, int n_windows, int H,
+                                                   int8_t *__restrict__ calls, const uint8_t *__restrict__ labels,
+                                                   unsigned long long *__restrict__ confusion, int n_class) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (long long)n_windows * H) return;
+    const int row = (int)(i % H);
+    const long long wbase = (i / H) * H;
+    int call = -1;
+    if (row >= 2 && row + 3 <= H) {
+        const int a = pred[(wbase + row - 2) * 3 + 2], b = pred[(wbase + row - 1) * 3 + 1], c = pred[(wbase + row) * 3 + 0];
+        // mode; all distinct -> max(set(l), key=l.count) walks the set of small ints in ascending order -> smallest
+        if (a == b || a == c) call = a;
+        else if (b == c) call = b;
+        else call = min(a, min(b, c));
+        if (labels && confusion) {
+            const int t = labels[i];
+            if (t < n_class && call < n_class) atomicAdd(&confusion[t * n_class + call], 1ull);
+        }
+    }
+    calls[i] = (int8_t)call;
+}
+
+}  // namespace dp
+
+// ================================================================================================
+// host side: weight packing, chunk tables, launches
+namespace dp {
+
+template <typename T>
+static int upload(T **dst, const std::vector<T> &src) {
+    DP_CUDA_CHECK(cudaMalloc((void **)dst, src.size() * sizeof(T)));
+    DP_CUDA_CHECK(cudaMemcpy(*dst, src.data(), src.size() * sizeof(T), cudaMemcpyHostToDevice));
+    return DP_OK;
+}
+
+// bf16 hi part, and the bf16 of the remainder when `lo` is wanted (split precision)
+static inline void split_bf16(float v, uint16_t &hi, uint16_t &lo) {
+    hi = f2bf(v);
+    lo = f2bf(v - bf2f(hi));
+}
+
+static int build_model(Model *m, const dp_model_weights *w) {
+    const int S = m->seq_len, Hd = m->hidden, RE = m->row_elems, KP = m->kfold_pad;
+    const int passes_b = m->precise ? 2 : 1;
+    // ---- folded operator: rows t*HP + h, columns s*KP + (w*in_ch + ch); lo copy (precise) after the hi columns
+    const long long kfold = (long long)S * KP;
+    m->kcols_fold = kfold * passes_b;
+    {
+        std::vector<uint16_t> B((size_t)S * HP * m->kcols_fold, 0);
+        std::vector<float> bias((size_t)S * HP, 0.f);
+        for (int t = 0; t < S; t++)
+            for (int h = 0; h < Hd; h++) {
+                const float *src = w->fold_w + ((size_t)t * Hd + h) * S * RE;
+                uint16_t *row = &B[((size_t)t * HP + h) * m->kcols_fold];
+                for (int s = 0; s < S; s++)
+                    for (int e = 0; e < RE; e++) {
+                        uint16_t hi, lo;
+                        split_bf16(src[(size_t)s * RE + e], hi, lo);
+                        row[(size_t)s * KP + e] = hi;
+                        if (m->precise) row[kfold + (size_t)s * KP + e] = lo;
+                    }
+                bias[(size_t)t * HP + h] = w->fold_b[(size_t)t * Hd + h];
+            }
+        int rc = upload((uint16_t **)&m->w_fold, B);
+        if (rc) return rc;
+        rc = upload(&m->b_fold, bias);
+        if (rc) return rc;
+    }
+    // ---- GRU: rows ((k*2+d)*8 + ub)*192 + gate*64 + j  <- unit u = ub*64+j; columns [W_ih | W_hh] (512 each)
+    const long long kgru = 2 * HP;
+    m->kcols_gru = kgru * passes_b;
+    {
+        const int L = m->n_layers;
+        std::vector<uint16_t> B((size_t)L * 2 * 3 * HP * m->kcols_gru, 0);
+        std::vector<float> bias((size_t)L * 2 * 4 * HP, 0.f);
+        for (int k = 0; k < L; k++)
+            for (int d = 0; d < 2; d++) {
+                const float *wih = w->gru_w_ih[k][d], *whh = w->gru_w_hh[k][d];
+                const float *bih = w->gru_b_ih[k][d], *bhh = w->gru_b_hh[k][d];
+                for (int u = 0; u < Hd; u++) {
+                    const int ub = u / 64, j = u % 64;
+                    for (int gate = 0; gate < 3; gate++) {
+                        const size_t r = ((size_t)(k * 2 + d) * 8 + ub) * 192 + gate * 64 + j;
+                        uint16_t *row = &B[r * m->kcols_gru];
+                        const float *si = wih + ((size_t)gate * Hd + u) * Hd, *sh = whh + ((size_t)gate * Hd + u) * Hd;
+                        for (int c = 0; c < Hd; c++) {
+                            uint16_t hi, lo;
+                            split_bf16(si[c], hi, lo);
+                            row[c] = hi;
+                            if (m->precise) row[kgru + c] = lo;
+                            split_bf16(sh[c], hi, lo);
+                            row[HP + c] = hi;
+                            if (m->precise) row[kgru + HP + c] = lo;
+                        }
+                    }
+                    float *bb = &bias[(size_t)(k * 2 + d) * 4 * HP];
+                    bb[0 * HP + u] = bih[u] + bhh[u];
+                    bb[1 * HP + u] = bih[Hd + u] + bhh[Hd + u];
+                    bb[2 * HP + u] = bih[2 * Hd + u];
+                    bb[3 * HP + u] = bhh[2 * Hd + u];
+                }
+            }
+        int rc = upload((uint16_t **)&m->w_gru, B);
+        if (rc) return rc;
+        rc = upload(&m->b_gru, bias);
+        if (rc) return rc;
+    }
+    {
+        std::vector<float> W((size_t)m->n_class * HP, 0.f), b(m->n_class);
+        for (int c = 0; c < m->n_class; c++) {
+            for (int u = 0; u < Hd; u++) W[(size_t)c * HP + u] = w->fc1_w[(size_t)c * Hd + u];
+            b[c] = w->fc1_b[c];
+        }
+        int rc = upload(&m->w_fc1, W);
+        if (rc) return rc;
+        rc = upload(&m->b_fc1, b);
+        if (rc) return rc;
+    }
+    // ---- K-chunk tables
+    std::vector<KChunk> tab;
+    const int nfc = KP / 64;
+    m->fold_tab_off = 0;
+    for (int pass = 0; pass < passes_b; pass++)      // the u8 image is exact in bf16: only the weights are split
+        for (int s = 0; s < S; s++)
+            for (int i = 0; i < nfc; i++) tab.push_back(KChunk{0, 64 * i, s, (int)(pass * kfold) + s * KP + 64 * i});
+    m->fold_tab_n = (int)tab.size();
+    const long long mc = m->mcap;
+    for (int k = 0; k < m->n_layers; k++)
+        for (int st = 0; st < 3; st++)
+            for (int d = 0; d < 2; d++) {
+                const int t = d == 0 ? st : 2 - st;
+                const int xslot = k == 0 ? bf_slot_y(t) : bf_slot_xn(k - 1, t);
+                int hslot = -1;                      // -1: h_prev is zero (layer 0, first step)
+                if (st > 0) hslot = d == 0 ? bf_slot_hf(k, t - 1) : bf_slot_hb(k, t + 1);
+                else if (k > 0) hslot = d == 0 ? bf_slot_hf(k - 1, 2) : bf_slot_hb(k - 1, 0);
+                m->gru_tab_off[k][st][d] = (int)tab.size();
+                // input chunks first (the MMA issuer relies on it), then hidden chunks.  a_src: 1 = arena, 2 = arena_lo
+                const int npass = m->precise ? 3 : 1;
+                for (int pass = 0; pass < npass; pass++) {       // (hi,hi) (hi,lo) (lo,hi)
+                    const int asrc = pass == 2 ? 2 : 1, boff = pass == 1 ? (int)kgru : 0;
+                    for (int i = 0; i < HP / 64; i++)
+                        tab.push_back(KChunk{asrc | (0 << 8), 64 * i, (int)(xslot * mc), boff + 64 * i});
+                }
+                if (hslot >= 0)
+                    for (int pass = 0; pass < npass; pass++) {
+                        const int asrc = pass == 2 ? 2 : 1, boff = pass == 1 ? (int)kgru : 0;
+                        for (int i = 0; i < HP / 64; i++)
+                            tab.push_back(KChunk{asrc | (1 << 8), 64 * i, (int)(hslot * mc), boff + HP + 64 * i});
+                    }
+                m->gru_tab_n[k][st][d] = (int)tab.size() - m->gru_tab_off[k][st][d];
+            }
+    int rc = upload(&m->tables, tab);
+    if (rc) return rc;
+    // ---- activations
+    DP_CUDA_CHECK(cudaMalloc((void **)&m->img_bf, (size_t)(mc + 128) * RE * 2));
+    DP_CUDA_CHECK(cudaMemset(m->img_bf, 0, (size_t)(mc + 128) * RE * 2));
+    DP_CUDA_CHECK(cudaMalloc((void **)&m->arena, (size_t)NSLOT_BF * mc * HP * 2));
+    DP_CUDA_CHECK(cudaMemset(m->arena, 0, (size_t)NSLOT_BF * mc * HP * 2));
+    if (m->precise) {
+        DP_CUDA_CHECK(cudaMalloc((void **)&m->arena_lo, (size_t)NSLOT_BF * mc * HP * 2));
+        DP_CUDA_CHECK(cudaMemset(m->arena_lo, 0, (size_t)NSLOT_BF * mc * HP * 2));
+    }
+    DP_CUDA_CHECK(cudaMalloc((void **)&m->state, (size_t)NSLOT_F32 * mc * HP * 4));
+    DP_CUDA_CHECK(cudaMemset(m->state, 0, (size_t)NSLOT_F32 * mc * HP * 4));
+    // ---- tensor maps
+    rc = make_tmap_bf16_2d(&m->tm_img, m->img_bf, (uint64_t)(mc + 128), (uint64_t)RE, (uint64_t)RE * 2, 128);
+    if (rc) return rc;
+    rc = make_tmap_bf16_2d(&m->tm_arena, m->arena, (uint64_t)NSLOT_BF * mc, HP, HP * 2, 128);
+    if (rc) return rc;
+    if (m->precise) rc = make_tmap_bf16_2d(&m->tm_arena_lo, m->arena_lo, (uint64_t)NSLOT_BF * mc, HP, HP * 2, 128);
+    else m->tm_arena_lo = m->tm_arena;
+    if (rc) return rc;
+    rc = make_tmap_bf16_2d(&m->tm_wfold, m->w_fold, (uint64_t)S * HP, (uint64_t)m->kcols_fold, (uint64_t)m->kcols_fold * 2, 256);
+    if (rc) return rc;
+    rc = make_tmap_bf16_2d(&m->tm_wgru, m->w_gru, (uint64_t)m->n_layers * 2 * 3 * HP, (uint64_t)m->kcols_gru,
+                           (uint64_t)m->kcols_gru * 2, 192);
+    return rc;
+}
+
+static int forward_rows(Model *m, const uint8_t *img, long long n_rows, float *logits, uint8_t *pred, cudaStream_t st) {
+    const int RE = m->row_elems, S = m->seq_len;
+    const long long mc = m->mcap;
+    // 1. u8 -> bf16 (plus seq_len-1 zero rows after the last one so trailing windows see zeros, not stale data)
+    {
+        const long long n16 = n_rows * RE / 16;
+        u8_to_bf16_kernel<<<(unsigned)((n16 + 255) / 256), 256, 0, st>>>((const uint4 *)img, (uint4 *)m->img_bf, n16);
+        DP_CUDA_CHECK(cudaGetLastError());
+        DP_CUDA_CHECK(cudaMemsetAsync(m->img_bf + n_rows * RE, 0, (size_t)(S - 1) * RE * 2, st));
+    }
+    const int tiles_m = (int)((n_rows + 127) / 128);
+    const CUtensorMap tmA[4] = {m->tm_img, m->tm_arena, m->tm_arena_lo, m->tm_arena};
+    // 2. folded CNN + Linear
+    {
+        GemmArgs g;
+        memset(&g, 0, sizeof(g));
+        g.chunks = m->tables + m->fold_tab_off;
+        g.n_chunks = m->fold_tab_n;
+        g.M = (int)n_rows; g.N = S * HP;
+        g.tiles_m = tiles_m; g.tiles_n = (S * HP) / 256;
+        g.epi.bias = m->b_fold;
+        g.epi.out = m->arena;
+        g.epi.out_lo = m->precise ? m->arena_lo : nullptr;
+        g.epi.ldc = HP; g.epi.out_fp32 = 0;
+        g.epi.nblk = HP; g.epi.nblk_stride = mc * HP;
+        int rc = launch_gemm_bf16(tmA, &m->tm_wfold, g, 256, st);
+        if (rc) return rc;
+    }
+    // 3. GRU layers
+    for (int k = 0; k < m->n_layers; k++)
+        for (int sg = 0; sg < 3; sg++) {
+            GruArgs g;
+            memset(&g, 0, sizeof(g));
+            g.n_prob = 2; g.M = (int)n_rows; g.tiles_m = tiles_m;
+            for (int d = 0; d < 2; d++) {
+                GruProblem &P = g.prob[d];
+                const int t = d == 0 ? sg : 2 - sg;
+                P.chunks = m->tables + m->gru_tab_off[k][sg][d];
+                P.n_chunks = m->gru_tab_n[k][sg][d];
+                P.b_row_base = (k * 2 + d) * 3 * HP;
+                P.bias = m->b_gru + (size_t)(k * 2 + d) * 4 * HP;
+                int hs = -1;
+                if (sg > 0) hs = d == 0 ? f32_slot_hf(k, t - 1) : f32_slot_hb(k, t + 1);
+                else if (k > 0) hs = d == 0 ? f32_slot_hf(k - 1, 2) : f32_slot_hb(k - 1, 0);
+                P.h_prev = hs >= 0 ? m->state + (size_t)hs * mc * HP : nullptr;
+                const int os = d == 0 ? f32_slot_hf(k, t) : f32_slot_hb(k, t);
+                const int ob = d == 0 ? bf_slot_hf(k, t) : bf_slot_hb(k, t);
+                P.h_out = m->state + (size_t)os * mc * HP;
+                P.h_out_bf = m->arena + (size_t)ob * mc * HP;
+                P.h_out_lo = m->precise ? m->arena_lo + (size_t)ob * mc * HP : nullptr;
+                if (sg == 2 && k + 1 < m->n_layers) {
+                    // sum of directions (model.py:131-133) -> bf16 input of the next layer
+                    if (d == 0) {
+                        P.partner = m->state + (size_t)f32_slot_hb(k, 2) * mc * HP;
+                        P.xsum = m->arena + (size_t)bf_slot_xn(k, 2) * mc * HP;
+                        P.partner2 = m->state + (size_t)f32_slot_hb(k, 1) * mc * HP;
+                        P.xsum2 = m->arena + (size_t)bf_slot_xn(k, 1) * mc * HP;
+                        if (m->precise) {
+                            P.xsum_lo = m->arena_lo + (size_t)bf_slot_xn(k, 2) * mc * HP;
+                            P.xsum2_lo = m->arena_lo + (size_t)bf_slot_xn(k, 1) * mc * HP;
+                        }
+                    } else {
+                        P.partner = m->state + (size_t)f32_slot_hf(k, 0) * mc * HP;
+                        P.xsum = m->arena + (size_t)bf_slot_xn(k, 0) * mc * HP;
+                        if (m->precise) P.xsum_lo = m->arena_lo + (size_t)bf_slot_xn(k, 0) * mc * HP;
+                    }
+                }
+            }
+            int rc = launch_gru_step(tmA, &m->tm_wgru, g, st);
+            if (rc) return rc;
+        }
+    // 4. fc1 + argmax on the fp32 states of the last layer
+    if (logits || pred) {
+        const int k = m->n_layers - 1;
+        const long long warps = n_rows * S;
+        const unsigned blocks = (unsigned)((warps * 32 + 255) / 256);
+        fc1_argmax_kernel<<<blocks, 256, 0, st>>>(m->state + (size_t)f32_slot_hf(k, 0) * mc * HP,
+                                                  m->state + (size_t)f32_slot_hb(k, 0) * mc * HP, mc * HP, m->w_fc1,
+                                                  m->b_fc1, m->n_class, S, n_rows, logits, pred);
+        DP_CUDA_CHECK(cudaGetLastError());
+    }
+    return DP_OK;
+}
+
+}  // namespace dp
+
+// ================================================================================================
+struct dp_model {
+    dp::Model *m;
+};
+
+extern "C" {
+
+int dp_model_create(const dp_model_weights *w, int64_t max_rows, int32_t precision, dp_model **out) {
+    DP_REQUIRE(w && out, "null argument");
+    DP_REQUIRE(w->fold_w && w->fold_b && w->fc1_w && w->fc1_b, "null weight pointer");
+    DP_REQUIRE(w->seq_len == 3, "seq_len must be 3 (test.py:48)");
+    DP_REQUIRE(w->hidden >= 1 && w->hidden <= dp::HP, "hidden size must be <= 512");
+    DP_REQUIRE(w->n_layers >= 1 && w->n_layers <= DP_MAX_GRU_LAYERS, "1..3 GRU layers");
+    DP_REQUIRE(w->n_class >= 1 && w->n_class <= 16, "n_class must be in [1,16]");
+    DP_REQUIRE(w->in_ch >= 1 && w->width >= 1 && (w->in_ch * w->width) % 16 == 0, "width*in_ch must be a multiple of 16");
+    DP_REQUIRE(max_rows >= 1 && max_rows <= (1ll << 24), "max_rows out of range");
+    DP_REQUIRE(precision == 0 || precision == 1, "precision must be 0 (bf16) or 1 (split bf16)");
+    for (int k = 0; k < w->n_layers; k++)
+        for (int d = 0; d < 2; d++)
+            DP_REQUIRE(w->gru_w_ih[k][d] && w->gru_w_hh[k][d] && w->gru_b_ih[k][d] && w->gru_b_hh[k][d], "null GRU weight");
+    dp::Model *m = new dp::Model();
+    m->in_ch = w->in_ch; m->width = w->width; m->hidden = w->hidden; m->n_class = w->n_class;
+    m->seq_len = w->seq_len; m->n_layers = w->n_layers;
+    m->row_elems = w->in_ch * w->width;
+    m->kfold_pad = (m->row_elems + 63) / 64 * 64;
+    m->precise = precision;
+    m->mcap = (max_rows + 127) / 128 * 128;
+    // the arena row coordinate (slot * mcap + row) must fit the int32 TMA coordinate
+    if ((long long)dp::NSLOT_BF * m->mcap >= (1ll << 31)) { delete m; dp::set_error("max_rows too large"); return DP_EINVAL; }
+    if (cudaGetDevice(&m->device) != cudaSuccess) { delete m; dp::set_error("no CUDA device"); return DP_ECUDA; }
+    const int rc = dp::build_model(m, w);
+    if (rc) { dp::free_model(m); return rc; }
+    if (cudaDeviceSynchronize() != cudaSuccess) { dp::free_model(m); dp::set_error("model upload failed"); return DP_ECUDA; }
+    dp_model *h = new dp_model();
+    h->m = m;
+    *out = h;
+    return DP_OK;
+}
+
+int dp_model_destroy(dp_model *h) {
+    if (!h) return DP_OK;
+    dp::free_model(h->m);
+    delete h;
+    return DP_OK;
+}
+
+int dp_model_forward_rows(dp_model *h, const uint8_t *img, int64_t n_rows, float *logits, uint8_t *pred, void *stream) {
+    DP_REQUIRE(h && h->m, "null model");
+    DP_REQUIRE(n_rows >= 0 && n_rows <= h->m->mcap, "n_rows exceeds the model's max_rows");
+    if (n_rows == 0) return DP_OK;
+    DP_REQUIRE(img, "null image");
+    DP_REQUIRE(((uintptr_t)img & 15) == 0, "img must be 16-byte aligned");
+    return dp::forward_rows(h->m, img, n_rows, logits, pred, (cudaStream_t)stream);
+}
+
+int dp_vote(const uint8_t *pred, int32_t n_windows, int32_t H, int32_t n_class, int8_t *calls, const uint8_t *labels,
+            unsigned long long *confusion, void *stream) {
+    DP_REQUIRE(n_windows >= 0 && H >= 0, "negative extent");
+    if (n_windows == 0 || H == 0) return DP_OK;
+    DP_REQUIRE(pred && calls, "null argument");
+    const long long n = (long long)n_windows * H;
+    dp::vote_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(pred, n_windows, H, calls, labels,
+                                                                                  confusion, n_class);
+    DP_CUDA_CHECK(cudaGetLastError());
+    return DP_OK;
+}
+
+int dp_model_peek(dp_model *h, int32_t what, int64_t n_rows, float *host_out) {
+    DP_REQUIRE(h && h->m && host_out, "null argument");
+    dp::Model *m = h->m;
+    DP_REQUIRE(n_rows >= 0 && n_rows <= m->mcap, "n_rows out of range");
+    DP_CUDA_CHECK(cudaDeviceSynchronize());
+    const size_t n = (size_t)n_rows * dp::HP;
+    if (what >= 0 && what < 3) {
+        std::vector<uint16_t> tmp(n);
+        DP_CUDA_CHECK(cudaMemcpy(tmp.data(), m->arena + (size_t)dp::bf_slot_y(what) * m->mcap * dp::HP, n * 2, cudaMemcpyDeviceToHost));
+        for (size_t i = 0; i < n; i++) host_out[i] = dp::bf2f(tmp[i]);
+        if (m->precise) {
+            DP_CUDA_CHECK(cudaMemcpy(tmp.data(), m->arena_lo + (size_t)dp::bf_slot_y(what) * m->mcap * dp::HP, n * 2, cudaMemcpyDeviceToHost));
+            for (size_t i = 0; i < n; i++) host_out[i] += dp::bf2f(tmp[i]);
+        }
+        return DP_OK;
+    }
+    const int k = what / 100, d = (what / 10) % 10, t = what % 10;
+    DP_REQUIRE(what >= 100 && k >= 1 && k <= m->n_layers && d < 2 && t < 3, "unknown peek id");
+    const int slot = d == 0 ? dp::f32_slot_hf(k - 1, t) : dp::f32_slot_hb(k - 1, t);
+    DP_CUDA_CHECK(cudaMemcpy(host_out, m->state + (size_t)slot * m->mcap * dp::HP, n * 4, cudaMemcpyDeviceToHost));
+    return DP_OK;
+}
+
+int dp_gemm_bf16(const void *A, int64_t lda, const void *B, int64_t ldb, const float *bias, void *out, int64_t ldc,
+                 int32_t out_fp32, int64_t M, int64_t N, int64_t K, int32_t block_n, void *stream) {
+    DP_REQUIRE(A && B && out, "null argument");
+    DP_REQUIRE(M >= 1 && N >= 16 && N % 16 == 0 && K >= 1, "need M >= 1, N a multiple of 16, K >= 1");
+    DP_REQUIRE(lda % 8 == 0 && ldb % 8 == 0 && ldc % 8 == 0, "leading dimensions must be multiples of 8 elements");
+    DP_REQUIRE(block_n == 128 || block_n == 256, "block_n must be 128 or 256");
+    CUtensorMap tmA[4], tmB;
+    int rc = dp::make_tmap_bf16_2d(&tmA[0], A, (uint64_t)M, (uint64_t)K, (uint64_t)lda * 2, 128);
+    if (rc) return rc;
+    tmA[1] = tmA[2] = tmA[3] = tmA[0];
+    rc = dp::make_tmap_bf16_2d(&tmB, B, (uint64_t)N, (uint64_t)K, (uint64_t)ldb * 2, (uint32_t)block_n);
+    if (rc) return rc;
+    const int nch = (int)((K + 63) / 64);
+    std::vector<dp::KChunk> tab(nch);
+    for (int i = 0; i < nch; i++) tab[i] = dp::KChunk{0, 64 * i, 0, 64 * i};
+    dp::KChunk *dtab = nullptr;
+    DP_CUDA_CHECK(cudaMalloc((void **)&dtab, sizeof(dp::KChunk) * nch));
+    DP_CUDA_CHECK(cudaMemcpyAsync(dtab, tab.data(), sizeof(dp::KChunk) * nch, cudaMemcpyHostToDevice, (cudaStream_t)stream));
+    DP_CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream));      // tab is pageable host memory
+    dp::GemmArgs g;
+    memset(&g, 0, sizeof(g));
+    g.chunks = dtab; g.n_chunks = nch; g.M = (int)M; g.N = (int)N;
+    g.tiles_m = (int)((M + 127) / 128); g.tiles_n = (int)((N + block_n - 1) / block_n);
+    g.epi.bias = bias; g.epi.out = out; g.epi.ldc = ldc; g.epi.out_fp32 = out_fp32;
+    rc = dp::launch_gemm_bf16(tmA, &tmB, g, block_n, (cudaStream_t)stream);
+    cudaError_t e = cudaStreamSynchronize((cudaStream_t)stream);
+    cudaFree(dtab);
+    if (rc) return rc;
+    if (e != cudaSuccess) { dp::set_error("dp_gemm_bf16: %s", cudaGetErrorString(e)); return DP_ECUDA; }
+    return DP_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,507 @@
+// Tensor-core kernels of the deePore model forward -- hand-written tcgen05 / TMEM / TMA for sm_100a.
+// See tc_gemm.cuh for what each kernel computes and which reference code it replaces.
+//
+// CTA anatomy (both kernels, 256 threads, one CTA per SM, persistent over a static tile list):
+//   warp 0    TMA producer: one elected lane walks the K-chunk table and fills a ring of smem stages
+//   warp 1    MMA issuer:   one elected lane issues tcgen05.mma per stage, commits stage -> empty barrier,
+//                           commits the finished accumulator -> tmem_full barrier
+//   warp 2    TMEM allocator (512 columns = two accumulator stages)
+//   warps 4-7 epilogue:     tcgen05.ld their 32 accumulator rows, apply the epilogue, store to HBM, release
+//                           the accumulator stage
+#include "tc_gemm.cuh"
+
+namespace dp {
+
+using namespace tc;
+
+// ------------------------------------------------------------------------------------------------
+// host: tensor maps through the runtime's driver entry point (no link-time dependency on libcuda)
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn g_encode = nullptr;
+
+int make_tmap_bf16_2d(CUtensorMap *out, const void *base, uint64_t rows, uint64_t cols, uint64_t pitch_bytes,
+                      uint32_t box_rows) {
+    if (!g_encode) {
+        void *fn = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        DP_CUDA_CHECK(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres));
+        if (!fn || qres != cudaDriverEntryPointSuccess) {
+            set_error("cuTensorMapEncodeTiled is not available from this driver");
+            return DP_ECUDA;
+        }
+        g_encode = (EncodeTiledFn)fn;
+    }
+    cuuint64_t gdim[2] = {cols, rows};
+    cuuint64_t gstr[1] = {pitch_bytes};
+    cuuint32_t box[2] = {64, box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = g_encode(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void *>(base), gdim, gstr, box, estr,
+                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        set_error("cuTensorMapEncodeTiled failed (%d): rows=%llu cols=%llu pitch=%llu box_rows=%u", (int)r,
+                  (unsigned long long)rows, (unsigned long long)cols, (unsigned long long)pitch_bytes, box_rows);
+        return DP_ECUDA;
+    }
+    return DP_OK;
+}
+
+int device_sm_count() {
+    static int cached[64] = {0};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return 148;
+    if (dev < 64 && cached[dev]) return cached[dev];
+    int n = 148;
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    if (dev < 64) cached[dev] = n;
+    return n;
+}
+
+// ------------------------------------------------------------------------------------------------
+constexpr int TC_THREADS = 256;
+constexpr int BM = 128;            // accumulator rows per tile = TMEM lanes
+constexpr int BK = 64;             // bf16 elements per K chunk = one 128-byte swizzle row
+constexpr int A_STAGE_BYTES = BM * BK * 2;   // 16 KB
+
+struct PipeState {
+    int stage;
+    uint32_t phase;
+    __device__ __forceinline__ void advance(int nstages) {
+        if (++stage == nstages) { stage = 0; phase ^= 1u; }
+    }
+};
+
+__device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
+    __nv_bfloat162 t = __floats2bfloat162_rn(a, b);
+    return *reinterpret_cast<uint32_t *>(&t);
+}
+__device__ __forceinline__ float bf16_round(float a) { return __bfloat162float(__float2bfloat16_rn(a)); }
+
+template <int BN>
+struct GemmCfg {
+    static constexpr int B_STAGE_BYTES = BN * BK * 2;
+    static constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
+    static constexpr int STAGES = (BN >= 256) ? 4 : 6;
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+};
+
+// ================================================================================================
+// generic table-driven GEMM
+template <int BN>
+__global__ void __launch_bounds__(TC_THREADS, 1)
+gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1,
+                 const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmA3,
+                 const __grid_constant__ CUtensorMap tmB, const GemmArgs g) {
+    using Cfg = GemmCfg<BN>;
+    constexpr int STAGES = Cfg::STAGES;
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    const uint32_t bar_base = smem_base + STAGES * Cfg::STAGE_BYTES;
+    // barriers: full[STAGES], empty[STAGES], tmem_full[2], tmem_empty[2]; then the TMEM base address word
+    auto full_bar = [&](int s) { return bar_base + 8u * s; };
+    auto empty_bar = [&](int s) { return bar_base + 8u * (STAGES + s); };
+    auto tfull_bar = [&](int s) { return bar_base + 8u * (2 * STAGES + s); };
+    auto tempty_bar = [&](int s) { return bar_base + 8u * (2 * STAGES + 2 + s); };
+    const uint32_t tmem_slot = bar_base + 8u * (2 * STAGES + 4);
+    uint32_t *tmem_slot_ptr = reinterpret_cast<uint32_t *>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int n_tiles = g.tiles_m * g.tiles_n;
+
+    if (warp == 0 && lane == 0) {
+        prefetch_tmap(&tmA0); prefetch_tmap(&tmA1); prefetch_tmap(&tmA2); prefetch_tmap(&tmA3); prefetch_tmap(&tmB);
+    }
+    if (warp == 1 && lane == 0) {
+        for (int s = 0; s < STAGES; s++) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
+        for (int s = 0; s < 2; s++) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), 4); }
+        fence_barrier_init();
+    }
+    if (warp == 2) { tmem_alloc(tmem_slot, 512); tmem_relinquish(); }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot_ptr;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            PipeState ps{0, 0};
+            for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+                const int m0 = (tile / g.tiles_n) * BM, n0 = (tile % g.tiles_n) * BN;
+                for (int kc = 0; kc < g.n_chunks; kc++) {
+                    const KChunk c = g.chunks[kc];
+                    const int src = c.a_src & 0xff;
+                    const CUtensorMap *ma = src == 0 ? &tmA0 : src == 1 ? &tmA1 : src == 2 ? &tmA2 : &tmA3;
+                    mbar_wait(empty_bar(ps.stage), ps.phase ^ 1u);
+                    mbar_expect_tx(full_bar(ps.stage), Cfg::STAGE_BYTES);
+                    const uint32_t sa = smem_base + ps.stage * Cfg::STAGE_BYTES;
+                    tma_load_2d(sa, ma, full_bar(ps.stage), c.a_col, m0 + c.a_drow);
+                    tma_load_2d(sa + A_STAGE_BYTES, &tmB, full_bar(ps.stage), c.b_col, n0);
+                    ps.advance(STAGES);
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            constexpr uint32_t idesc = make_idesc_bf16(BM, BN);
+            PipeState ps{0, 0};
+            int as = 0; uint32_t aphase = 0;
+            for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+                mbar_wait(tempty_bar(as), aphase ^ 1u);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + as * BN;
+                for (int kc = 0; kc < g.n_chunks; kc++) {
+                    mbar_wait(full_bar(ps.stage), ps.phase);
+                    tc_fence_after();
+                    const uint32_t sa = smem_base + ps.stage * Cfg::STAGE_BYTES;
+                    const uint64_t da = make_smem_desc_sw128(sa), db = make_smem_desc_sw128(sa + A_STAGE_BYTES);
+#pragma unroll
+                    for (int k = 0; k < BK / 16; k++)
+                        umma_bf16(d_tmem, da + 2u * k, db + 2u * k, idesc, (kc | k) != 0);
+                    umma_commit(empty_bar(ps.stage));
+                    ps.advance(STAGES);
+                }
+                umma_commit(tfull_bar(as));
+                if (++as == 2) { as = 0; aphase ^= 1u; }
+            }
+        }
+    } else if (warp >= 4) {
+        const int wq = warp - 4;
+        const GemmEpilogue &e = g.epi;
+        int as = 0; uint32_t aphase = 0;
+        for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+            const int m0 = (tile / g.tiles_n) * BM, n0 = (tile % g.tiles_n) * BN;
+            const int m = m0 + wq * 32 + lane;
+            mbar_wait(tfull_bar(as), aphase);
+            tc_fence_after();
+            const bool row_ok = m < g.M;
+            bool row_zero = false;
+            if (e.mask_period > 0) { const int r = m % e.mask_period; row_zero = r < e.mask_lo || r >= e.mask_hi; }
+            const uint32_t taddr = tmem_base + as * BN + ((uint32_t)(wq * 32) << 16);
+#pragma unroll 1
+            for (int cb = 0; cb < BN / 16; cb++) {
+                const int n = n0 + cb * 16;
+                if (n >= g.N) break;                       // warp-uniform
+                uint32_t v[16];
+                tmem_ld16(taddr + cb * 16, v);
+                tmem_ld_wait();
+                if (!row_ok) continue;
+                float f[16];
+#pragma unroll
+                for (int i = 0; i < 16; i++) f[i] = __uint_as_float(v[i]);
+                if (e.bias) {
+#pragma unroll
+                    for (int i = 0; i < 16; i += 4) {
+                        const float4 b = __ldg(reinterpret_cast<const float4 *>(e.bias + n + i));
+                        f[i] += b.x; f[i + 1] += b.y; f[i + 2] += b.z; f[i + 3] += b.w;
+                    }
+                }
+                if (e.residual) {
+                    const uint4 *rp = reinterpret_cast<const uint4 *>(e.residual + (long long)m * e.res_ld + n);
+#pragma unroll
+                    for (int h = 0; h < 2; h++) {
+                        const uint4 r = __ldg(rp + h);
+                        const uint32_t w[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+                        for (int i = 0; i < 4; i++) {
+                            const __nv_bfloat162 p = *reinterpret_cast<const __nv_bfloat162 *>(&w[i]);
+                            f[h * 8 + 2 * i] += __low2float(p);
+                            f[h * 8 + 2 * i + 1] += __high2float(p);
+                        }
+                    }
+                }
+                if (row_zero) {
+#pragma unroll
+                    for (int i = 0; i < 16; i++) f[i] = 0.f;
+                }
+                long long off = (long long)m * e.ldc;
+                if (e.nblk > 0) off += (long long)(n / e.nblk) * e.nblk_stride + (n % e.nblk); else off += n;
+                if (e.out_fp32) {
+                    float4 *op = reinterpret_cast<float4 *>(reinterpret_cast<float *>(e.out) + off);
+#pragma unroll
+                    for (int i = 0; i < 4; i++) op[i] = make_float4(f[4 * i], f[4 * i + 1], f[4 * i + 2], f[4 * i + 3]);
+                } else {
+                    uint32_t p[8];
+#pragma unroll
+                    for (int i = 0; i < 8; i++) p[i] = pack_bf16(f[2 * i], f[2 * i + 1]);
+                    uint4 *op = reinterpret_cast<uint4 *>(reinterpret_cast<__nv_bfloat16 *>(e.out) + off);
+                    op[0] = make_uint4(p[0], p[1], p[2], p[3]);
+                    op[1] = make_uint4(p[4], p[5], p[6], p[7]);
+                    if (e.out_lo) {
+#pragma unroll
+                        for (int i = 0; i < 8; i++)
+                            p[i] = pack_bf16(f[2 * i] - bf16_round(f[2 * i]), f[2 * i + 1] - bf16_round(f[2 * i + 1]));
+                        uint4 *lp = reinterpret_cast<uint4 *>(e.out_lo + off);
+                        lp[0] = make_uint4(p[0], p[1], p[2], p[3]);
+                        lp[1] = make_uint4(p[4], p[5], p[6], p[7]);
+                    }
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(tempty_bar(as));
+            if (++as == 2) { as = 0; aphase ^= 1u; }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) { tc_fence_after(); tmem_dealloc(tmem_base, 512); }
+}
+
+template <int BN>
+static int launch_gemm_t(const CUtensorMap *tmA, const CUtensorMap *tmB, const GemmArgs &g, cudaStream_t st) {
+    using Cfg = GemmCfg<BN>;
+    static bool attr_done[64] = {false};
+    int dev = 0;
+    DP_CUDA_CHECK(cudaGetDevice(&dev));
+    if (dev >= 64 || !attr_done[dev]) {
+        DP_CUDA_CHECK(cudaFuncSetAttribute(gemm_bf16_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
+        if (dev < 64) attr_done[dev] = true;
+    }
+    const int n_tiles = g.tiles_m * g.tiles_n;
+    if (n_tiles <= 0) return DP_OK;
+    const int grid = n_tiles < device_sm_count() ? n_tiles : device_sm_count();
+    gemm_bf16_kernel<BN><<<grid, TC_THREADS, Cfg::SMEM_BYTES, st>>>(tmA[0], tmA[1], tmA[2], tmA[3], *tmB, g);
+    DP_CUDA_CHECK(cudaGetLastError());
+    return DP_OK;
+}
+
+int launch_gemm_bf16(const CUtensorMap *tmA, const CUtensorMap *tmB, const GemmArgs &g, int block_n, cudaStream_t st) {
+    if (block_n == 256) return launch_gemm_t<256>(tmA, tmB, g, st);
+    if (block_n == 128) return launch_gemm_t<128>(tmA, tmB, g, st);
+    set_error("launch_gemm_bf16: block_n must be 128 or 256");
+    return DP_EINVAL;
+}
+
+// ================================================================================================
+// GRU time step (both directions).  Tile = (problem, 128 rows, block of 64 hidden units).  Weight tile rows are
+// gate-major [r 64 | z 64 | n 64] = 192 rows; accumulator columns per stage: [0,64) r, [64,128) z, [128,192) W_in x,
+// [192,256) W_hn h.  Input chunks issue one N=192 MMA; hidden chunks an N=128 MMA onto r,z plus an N=64 MMA onto
+// the separate W_hn h columns (torch.nn.GRU: n = tanh(W_in x + b_in + r * (W_hn h + b_hn))).
+constexpr int GRU_UB = 64;                          // hidden units per tile
+constexpr int GRU_BROWS = 3 * GRU_UB;               // 192 weight rows per tile
+constexpr int GRU_B_STAGE_BYTES = GRU_BROWS * BK * 2;   // 24 KB
+constexpr int GRU_STAGE_BYTES = A_STAGE_BYTES + GRU_B_STAGE_BYTES;   // 40 KB
+constexpr int GRU_STAGES = 5;
+constexpr int GRU_SMEM_BYTES = GRU_STAGES * GRU_STAGE_BYTES + 1024 + 256;
+constexpr int GRU_HP = 512;                         // padded hidden size (row pitch of every state buffer)
+constexpr int GRU_NUB = GRU_HP / GRU_UB;            // 8 unit blocks
+
+__device__ __forceinline__ float sigmoid_acc(float x) { return __fdividef(1.f, 1.f + __expf(-x)); }
+__device__ __forceinline__ float tanh_acc(float x) {
+    const float e = __expf(2.f * x);
+    return 1.f - __fdividef(2.f, e + 1.f);
+}
+
+__device__ __forceinline__ void store_bf16x16(__nv_bfloat16 *dst, const float (&f)[16]) {
+    uint32_t p[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) p[i] = pack_bf16(f[2 * i], f[2 * i + 1]);
+    uint4 *op = reinterpret_cast<uint4 *>(dst);
+    op[0] = make_uint4(p[0], p[1], p[2], p[3]);
+    op[1] = make_uint4(p[4], p[5], p[6], p[7]);
+}
+__device__ __forceinline__ void store_bf16x16_lo(__nv_bfloat16 *dst, const float (&f)[16]) {
+    float r[16];
+#pragma unroll
+    for (int i = 0; i < 16; i++) r[i] = f[i] - bf16_round(f[i]);
+    store_bf16x16(dst, r);
+}
+__device__ __forceinline__ void load_f32x16(const float *src, float (&f)[16]) {
+    const float4 *p = reinterpret_cast<const float4 *>(src);
+#pragma unroll
+    for (int i = 0; i < 4; i++) { const float4 t = p[i]; f[4 * i] = t.x; f[4 * i + 1] = t.y; f[4 * i + 2] = t.z; f[4 * i + 3] = t.w; }
+}
+
+__global__ void __launch_bounds__(TC_THREADS, 1)
+gru_step_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1,
+                const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmA3,
+                const __grid_constant__ CUtensorMap tmB, const GruArgs g) {
+    constexpr int STAGES = GRU_STAGES;
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    const uint32_t bar_base = smem_base + STAGES * GRU_STAGE_BYTES;
+    auto full_bar = [&](int s) { return bar_base + 8u * s; };
+    auto empty_bar = [&](int s) { return bar_base + 8u * (STAGES + s); };
+    auto tfull_bar = [&](int s) { return bar_base + 8u * (2 * STAGES + s); };
+    auto tempty_bar = [&](int s) { return bar_base + 8u * (2 * STAGES + 2 + s); };
+    const uint32_t tmem_slot = bar_base + 8u * (2 * STAGES + 4);
+    uint32_t *tmem_slot_ptr = reinterpret_cast<uint32_t *>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int tiles_per_prob = g.tiles_m * GRU_NUB;
+    const int n_tiles = tiles_per_prob * g.n_prob;
+
+    if (warp == 0 && lane == 0) {
+        prefetch_tmap(&tmA0); prefetch_tmap(&tmA1); prefetch_tmap(&tmA2); prefetch_tmap(&tmA3); prefetch_tmap(&tmB);
+    }
+    if (warp == 1 && lane == 0) {
+        for (int s = 0; s < STAGES; s++) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
+        for (int s = 0; s < 2; s++) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), 4); }
+        fence_barrier_init();
+    }
+    if (warp == 2) { tmem_alloc(tmem_slot, 512); tmem_relinquish(); }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot_ptr;
+
+    // tile -> (problem, m block, unit block): unit block fastest so the 8 CTAs sharing an A tile run together
+    if (warp == 0) {
+        if (lane == 0) {
+            PipeState ps{0, 0};
+            for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+                const int pi = tile / tiles_per_prob, rem = tile % tiles_per_prob;
+                const GruProblem &P = g.prob[pi];
+                const int m0 = (rem / GRU_NUB) * BM, ub = rem % GRU_NUB;
+                const int brow = P.b_row_base + ub * GRU_BROWS;
+                for (int kc = 0; kc < P.n_chunks; kc++) {
+                    const KChunk c = P.chunks[kc];
+                    const int src = c.a_src & 0xff;
+                    const CUtensorMap *ma = src == 0 ? &tmA0 : src == 1 ? &tmA1 : src == 2 ? &tmA2 : &tmA3;
+                    mbar_wait(empty_bar(ps.stage), ps.phase ^ 1u);
+                    mbar_expect_tx(full_bar(ps.stage), GRU_STAGE_BYTES);
+                    const uint32_t sa = smem_base + ps.stage * GRU_STAGE_BYTES;
+                    tma_load_2d(sa, ma, full_bar(ps.stage), c.a_col, m0 + c.a_drow);
+                    tma_load_2d(sa + A_STAGE_BYTES, &tmB, full_bar(ps.stage), c.b_col, brow);
+                    ps.advance(STAGES);
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            constexpr uint32_t idesc192 = make_idesc_bf16(BM, 192);
+            constexpr uint32_t idesc128 = make_idesc_bf16(BM, 128);
+            constexpr uint32_t idesc64 = make_idesc_bf16(BM, 64);
+            PipeState ps{0, 0};
+            int as = 0; uint32_t aphase = 0;
+            for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+                const GruProblem &P = g.prob[tile / tiles_per_prob];
+                mbar_wait(tempty_bar(as), aphase ^ 1u);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + as * 256;
+                uint32_t acc_rz = 0, acc_nx = 0, acc_nh = 0;      // has this column group been written yet?
+                for (int kc = 0; kc < P.n_chunks; kc++) {
+                    const int kind = (P.chunks[kc].a_src >> 8) & 0xff;
+                    mbar_wait(full_bar(ps.stage), ps.phase);
+                    tc_fence_after();
+                    const uint32_t sa = smem_base + ps.stage * GRU_STAGE_BYTES;
+                    const uint64_t da = make_smem_desc_sw128(sa), db = make_smem_desc_sw128(sa + A_STAGE_BYTES);
+                    const uint64_t dbn = make_smem_desc_sw128(sa + A_STAGE_BYTES + 128 * 128);   // rows 128..191 (n gate)
+                    if (kind == 0) {
+                        // r,z and nx columns share one instruction, so they must share the accumulate flag:
+                        // input chunks come first in the table (host guarantees it), hence acc_rz == acc_nx here.
+#pragma unroll
+                        for (int k = 0; k < BK / 16; k++)
+                            umma_bf16(d_tmem, da + 2u * k, db + 2u * k, idesc192, acc_nx | (uint32_t)k);
+                        acc_rz = 1; acc_nx = 1;
+                    } else {
+#pragma unroll
+                        for (int k = 0; k < BK / 16; k++) {
+                            umma_bf16(d_tmem, da + 2u * k, db + 2u * k, idesc128, acc_rz | (uint32_t)k);
+                            umma_bf16(d_tmem + 192, da + 2u * k, dbn + 2u * k, idesc64, acc_nh | (uint32_t)k);
+                        }
+                        acc_rz = 1; acc_nh = 1;
+                    }
+                    umma_commit(empty_bar(ps.stage));
+                    ps.advance(STAGES);
+                }
+                umma_commit(tfull_bar(as));
+                if (++as == 2) { as = 0; aphase ^= 1u; }
+            }
+        }
+    } else if (warp >= 4) {
+        const int wq = warp - 4;
+        int as = 0; uint32_t aphase = 0;
+        for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+            const int pi = tile / tiles_per_prob, rem = tile % tiles_per_prob;
+            const GruProblem &P = g.prob[pi];
+            const int m0 = (rem / GRU_NUB) * BM, ub = rem % GRU_NUB;
+            const int m = m0 + wq * 32 + lane;
+            const bool row_ok = m < g.M;
+            bool has_h = false;
+            for (int kc = 0; kc < P.n_chunks; kc++) has_h |= ((P.chunks[kc].a_src >> 8) & 0xff) != 0;
+            mbar_wait(tfull_bar(as), aphase);
+            tc_fence_after();
+            const uint32_t taddr = tmem_base + as * 256 + ((uint32_t)(wq * 32) << 16);
+#pragma unroll 1
+            for (int cb = 0; cb < GRU_UB / 16; cb++) {
+                const int u = ub * GRU_UB + cb * 16;              // first hidden unit of this group
+                uint32_t vr[16], vz[16], vx[16], vh[16];
+                tmem_ld16(taddr + cb * 16, vr);
+                tmem_ld16(taddr + 64 + cb * 16, vz);
+                tmem_ld16(taddr + 128 + cb * 16, vx);
+                if (has_h) tmem_ld16(taddr + 192 + cb * 16, vh);
+                tmem_ld_wait();
+                if (!row_ok) continue;
+                const long long ro = (long long)m * GRU_HP + u;
+                float hp[16];
+                if (P.h_prev) load_f32x16(P.h_prev + ro, hp);
+                else {
+#pragma unroll
+                    for (int i = 0; i < 16; i++) hp[i] = 0.f;
+                }
+                float hn[16];
+#pragma unroll
+                for (int i = 0; i < 16; i++) {
+                    const float br = __ldg(P.bias + u + i), bz = __ldg(P.bias + GRU_HP + u + i);
+                    const float bin = __ldg(P.bias + 2 * GRU_HP + u + i), bhn = __ldg(P.bias + 3 * GRU_HP + u + i);
+                    const float r = sigmoid_acc(__uint_as_float(vr[i]) + br);
+                    const float z = sigmoid_acc(__uint_as_float(vz[i]) + bz);
+                    const float hh = (has_h ? __uint_as_float(vh[i]) : 0.f) + bhn;
+                    const float nn = tanh_acc(__uint_as_float(vx[i]) + bin + r * hh);
+                    hn[i] = (1.f - z) * nn + z * hp[i];
+                }
+                {
+                    float4 *op = reinterpret_cast<float4 *>(P.h_out + ro);
+#pragma unroll
+                    for (int i = 0; i < 4; i++) op[i] = make_float4(hn[4 * i], hn[4 * i + 1], hn[4 * i + 2], hn[4 * i + 3]);
+                }
+                if (P.h_out_bf) store_bf16x16(P.h_out_bf + ro, hn);
+                if (P.h_out_lo) store_bf16x16_lo(P.h_out_lo + ro, hn);
+                if (P.partner) {
+                    float pt[16];
+                    load_f32x16(P.partner + ro, pt);
+#pragma unroll
+                    for (int i = 0; i < 16; i++) pt[i] += hn[i];
+                    store_bf16x16(P.xsum + ro, pt);
+                    if (P.xsum_lo) store_bf16x16_lo(P.xsum_lo + ro, pt);
+                }
+                if (P.partner2) {
+                    float pt[16];
+                    load_f32x16(P.partner2 + ro, pt);
+#pragma unroll
+                    for (int i = 0; i < 16; i++) pt[i] += hp[i];
+                    store_bf16x16(P.xsum2 + ro, pt);
+                    if (P.xsum2_lo) store_bf16x16_lo(P.xsum2_lo + ro, pt);
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(tempty_bar(as));
+            if (++as == 2) { as = 0; aphase ^= 1u; }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) { tc_fence_after(); tmem_dealloc(tmem_base, 512); }
+}
+
+int launch_gru_step(const CUtensorMap *tmA, const CUtensorMap *tmB, const GruArgs &g, cudaStream_t st) {
+    static bool attr_done[64] = {false};
+    int dev = 0;
+    DP_CUDA_CHECK(cudaGetDevice(&dev));
+    if (dev >= 64 || !attr_done[dev]) {
+        DP_CUDA_CHECK(cudaFuncSetAttribute(gru_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, GRU_SMEM_BYTES));
+        if (dev < 64) attr_done[dev] = true;
+    }
+    const int n_tiles = g.tiles_m * GRU_NUB * g.n_prob;
+    if (n_tiles <= 0) return DP_OK;
+    const int grid = n_tiles < device_sm_count() ? n_tiles : device_sm_count();
+    gru_step_kernel<<<grid, TC_THREADS, GRU_SMEM_BYTES, st>>>(tmA[0], tmA[1], tmA[2], tmA[3], *tmB, g);
+    DP_CUDA_CHECK(cudaGetLastError());
+    return DP_OK;
+}
+
+}  // namespace dp

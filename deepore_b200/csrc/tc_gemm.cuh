@@ -1,0 +1,73 @@
+// Tensor-core kernels of the model forward (sm_100a): declarations shared by tc_gemm.cu and model.cu.
+//
+//   gemm_bf16     persistent, warp-specialised tcgen05 GEMM  D[M,N] = sum_chunks A_src[m0+drow.., col..+64] . B[n0.., bcol..+64]^T
+//                 (bf16 operands staged by TMA with 128-byte swizzle, fp32 accumulators in TMEM, double-buffered so the
+//                 epilogue of tile i overlaps the MMAs of tile i+1).  The K loop is TABLE DRIVEN: every 64-wide K chunk
+//                 names its A source (up to 4 tensor maps), A column, A row shift and B column.  That one mechanism gives
+//                 plain GEMMs, the 3-row sliding window of the folded CNN operator (row shift 0/1/2), (1x3) convolutions as
+//                 implicit GEMM (row shift -1/0/+1), skip-path fusion (second A source) and split-bf16 (hi/lo) precision.
+//   gru_step      one time step of a bidirectional GRU layer for both directions: [x_t | h_prev] . [W_ih | W_hh]^T with the
+//                 r/z/n gate accumulators side by side in TMEM and the gate math, state update and direction sum in the
+//                 epilogue (replaces torch.nn.GRU at /root/reference/src/modules/model.py:83-87,124-135).
+#pragma once
+#include "common.cuh"
+#include "tc_common.cuh"
+
+namespace dp {
+
+struct KChunk {          // one 64-element slice of the contraction
+    int32_t a_src;       // bits 0-7: A tensor map index (0..3); bits 8-15: kind (GRU: 0 = input chunk, 1 = hidden chunk)
+    int32_t a_col;       // A column (elements)
+    int32_t a_drow;      // added to the tile's first row (may be negative: TMA zero-fills out of bounds)
+    int32_t b_col;       // B column (elements)
+};
+
+struct GemmEpilogue {
+    const float *bias;                 // [N] fp32 or null
+    const __nv_bfloat16 *residual;     // optional [M][res_ld] bf16 added before the store
+    long long res_ld;
+    void *out;                         // bf16 or fp32, row pitch ldc elements
+    __nv_bfloat16 *out_lo;             // optional bf16 remainder (x - bf16(x)) for split precision, same layout as out
+    long long ldc;
+    int out_fp32;
+    int nblk;                          // >0: column n is stored at (n / nblk) * nblk_stride + n % nblk
+    long long nblk_stride;
+    int mask_period, mask_lo, mask_hi; // period>0: rows with (m % period) outside [lo,hi) are stored as ZERO (conv padding)
+};
+
+struct GemmArgs {
+    const KChunk *chunks;
+    int n_chunks;
+    int M, N;
+    int tiles_m, tiles_n;
+    GemmEpilogue epi;
+};
+
+struct GruProblem {
+    const KChunk *chunks;
+    int n_chunks;
+    int b_row_base;                    // first row of this (layer, direction) in the stacked weight matrix
+    const float *bias;                 // [4][512]: b_ir+b_hr, b_iz+b_hz, b_in, b_hn (zero padded)
+    const float *h_prev;               // fp32 [M][512] or null (zeros)
+    float *h_out;                      // fp32 [M][512]
+    __nv_bfloat16 *h_out_bf;           // bf16 [M][512]: A operand of the next step
+    __nv_bfloat16 *h_out_lo;           // optional split-precision remainder
+    const float *partner;              // optional: xsum = h_new + partner   (sum of directions, model.py:131-133)
+    __nv_bfloat16 *xsum, *xsum_lo;
+    const float *partner2;             // optional: xsum2 = h_prev + partner2
+    __nv_bfloat16 *xsum2, *xsum2_lo;
+};
+
+struct GruArgs {
+    GruProblem prob[2];
+    int n_prob;
+    int M;
+    int tiles_m;                       // per problem: tiles_m * 8 unit blocks
+};
+
+int launch_gemm_bf16(const CUtensorMap *tmA /*[4]*/, const CUtensorMap *tmB, const GemmArgs &g, int block_n,
+                     cudaStream_t st);
+int launch_gru_step(const CUtensorMap *tmA /*[4]*/, const CUtensorMap *tmB, const GruArgs &g, cudaStream_t st);
+int device_sm_count();
+
+}  // namespace dp

@@ -1,0 +1,136 @@
+"""Composes the affine front of the deePore model into one operator per time step.
+
+/root/reference/src/modules/model.py: the five residual blocks (`residual_layer`, :93-105, applied at :138-142)
+hold only convolutions and eval-mode BatchNorm -- there is no activation anywhere in the CNN -- and they are followed
+by a reinterpreting `view` (:144-149) and the Linear `cnn_fc_rnn` (:151).  So for the three image rows x[s] of one
+forward call
+
+    y[t] = cnn_fc_rnn(feat[t]) = fold_b[t] + sum_s fold_w[t][:, s] . x[s]            t, s in {0,1,2}
+
+exactly (up to floating-point reassociation).  This module builds fold_w / fold_b in float64 once per checkpoint
+(host-side weight preparation, like folding BatchNorm into a convolution); the CUDA path then evaluates the whole
+front as a single tensor-core GEMM with K = 3*W*C_in instead of 16 convolutions + a K=51200 GEMM per call.
+
+Structure used (so the fold costs seconds, not minutes): a (1x3) convolution stack has a receptive field of +-15
+columns, so away from the borders the linear part of the row map is one 31-tap kernel; only the 15 columns next to
+each border see the zero padding of the intermediate layers and are evaluated separately on a short strip.
+"""
+from __future__ import annotations
+
+from typing import Dict, Tuple
+
+import numpy as np
+
+BN_EPS = 1e-5        # torch.nn.BatchNorm2d default (model.py:70)
+N_BLOCKS = 5         # model.py:138-142
+RF = 3 * N_BLOCKS    # receptive-field radius of the conv stack: 3 convs per block, +-1 each
+
+
+def _t(a):
+    import torch
+    return torch.as_tensor(np.asarray(a, dtype=np.float64))
+
+
+def _prep(state: Dict[str, np.ndarray]):
+    """BatchNorm scale/shift and squeezed conv weights as float64 torch tensors."""
+    s = {k: _t(v) for k, v in state.items()}
+    scale = s["batchNorm.weight"] / (s["batchNorm.running_var"] + BN_EPS).sqrt()
+    shift = s["batchNorm.bias"] - s["batchNorm.running_mean"] * scale
+    P = dict(scale=scale, shift=shift,
+             incp0=s["incpConv0.weight"][:, :, 0, :], incp1=s["incpConv1.weight"][:, :, 0, :],
+             conv0=s["conv0.weight"][:, :, 0, :], conv1=s["conv1.weight"][:, :, 0, :],
+             conv2=s["conv2.weight"][:, :, 0, :], conv3=s["conv3.weight"][:, :, 0, :],
+             b2=s["conv2.bias"], b3=s["conv3.bias"])
+    return P
+
+
+def row_map(x, P, affine: bool = True):
+    """The CNN applied to image rows x [B, C_in, width] -> [B, 256, width] (model.py:93-105,138-142; kernel height 1 =>
+    rows are independent).  affine=False drops every bias / BatchNorm shift (the linear part)."""
+    import torch.nn.functional as F
+    sc = P["scale"][None, :, None]
+    sh = P["shift"][None, :, None] if affine else 0.0
+    b2 = P["b2"] if affine else None
+    b3 = P["b3"] if affine else None
+
+    def bn(v):
+        return v * sc + sh
+    for layer in range(N_BLOCKS):
+        if layer == 0:
+            skip = bn(F.conv1d(x, P["incp0"]))
+            c1 = bn(F.conv1d(x, P["conv0"], padding=1))
+        else:
+            skip = F.conv1d(x, P["incp1"])
+            c1 = bn(F.conv1d(x, P["conv1"], padding=1))
+        c2 = bn(F.conv1d(c1, P["conv2"], bias=b2, padding=1))
+        c3 = F.conv1d(c2, P["conv3"], bias=b3, padding=1)
+        x = skip + c3
+    return x
+
+
+def fold_front(state: Dict[str, np.ndarray], in_ch: int, width: int, seq_len: int = 3) -> Tuple[np.ndarray, np.ndarray]:
+    """state: numpy arrays keyed like Model.state_dict() (batchNorm.*, incpConv0/1.weight, conv0..3.*, cnn_fc_rnn.*).
+
+    Returns (fold_w float32 [seq_len][hidden][seq_len][width][in_ch], fold_b float32 [seq_len][hidden]) acting on RAW
+    uint8 pixel values (the 1/255 of torchvision ToTensor, dataset.py:52 / test.py:28, is folded in)."""
+    import torch
+    P = _prep(state)
+    C = P["conv2"].shape[0]
+    Wd, S = width, seq_len
+    Wfc = _t(state["cnn_fc_rnn.weight"])            # [hidden][C*width]
+    bfc = _t(state["cnn_fc_rnn.bias"])
+    Hd = Wfc.shape[0]
+    assert Wfc.shape[1] == C * Wd, "cnn_fc_rnn expects coverage_depth*output_channel inputs (model.py:79)"
+    assert Wd > 4 * RF + 2, "width too small for the border/interior split"
+
+    with torch.no_grad():
+        # ---- response to the zero row (all biases): row independent
+        b_map = row_map(torch.zeros(1, in_ch, Wd, dtype=torch.float64), P, affine=True)[0]       # [C][Wd]
+        # ---- linear part on strips next to each border; strip width covers basis column + full receptive field
+        SW = 3 * RF + 1                              # 46
+        nb = RF + 1                                  # basis columns 0..15 (left) / width-16..width-1 (right)
+        eye = torch.zeros(nb * in_ch, in_ch, SW, dtype=torch.float64)
+        for p in range(nb):
+            for ch in range(in_ch):
+                eye[p * in_ch + ch, ch, p] = 1.0
+        R_left = row_map(eye, P, affine=False).reshape(nb, in_ch, C, SW)        # basis at strip column p
+        R_right = row_map(eye.flip(-1), P, affine=False).reshape(nb, in_ch, C, SW)   # basis at strip column SW-1-p
+        # interior 31-tap kernel: basis at column RF of the left strip never feels a border
+        Kint = R_left[RF][:, :, 0:2 * RF + 1]        # [in_ch][C][d+RF], response at column RF+d
+
+        Wfc3 = Wfc.reshape(Hd, C, Wd)
+        fold_w = torch.zeros(S, Hd, S, Wd, in_ch, dtype=torch.float64)
+        fold_b = torch.zeros(S, Hd, dtype=torch.float64)
+        for t in range(S):
+            # feat[t][c*Wd + j] = cnn[c][(3j+t)//Wd][(3j+t)%Wd]   (the reinterpreting view)
+            jj = torch.arange(Wd)
+            flat = S * jj + t
+            srow, wcol = flat // Wd, flat % Wd
+            fold_b[t] = bfc + torch.einsum("hcj,cj->h", Wfc3, b_map[:, wcol])
+            for s in range(S):
+                js = jj[srow == s]
+                if js.numel() == 0:
+                    continue
+                ws = wcol[js]                          # CNN column read by each selected j
+                # A[c][j][ch][w'] = d cnn[c][ws[j]] / d x[ch][w']
+                A = torch.zeros(C, js.numel(), in_ch, Wd, dtype=torch.float64)
+                for idx in range(js.numel()):
+                    w = int(ws[idx])
+                    lo, hi = max(0, w - RF), min(Wd - 1, w + RF)
+                    wp = torch.arange(lo, hi + 1)
+                    A[:, idx, :, lo:hi + 1] = Kint[:, :, (w - wp) + RF].permute(1, 0, 2)
+                    for wq in range(0, min(RF, Wd)):                      # basis columns feeling the left border
+                        A[:, idx, :, wq] = R_left[wq][:, :, w].t() if w < SW else 0.0
+                    for p in range(0, RF):                                # ... and the right border
+                        wq = Wd - 1 - p
+                        k = w - (Wd - SW)                                 # strip column of CNN column w
+                        A[:, idx, :, wq] = R_right[p][:, :, k].t() if k >= 0 else 0.0
+                G = Wfc3[:, :, js].reshape(Hd, C * js.numel())
+                fold_w[t, :, s] = (G @ A.reshape(C * js.numel(), in_ch * Wd)).reshape(Hd, in_ch, Wd).permute(0, 2, 1)
+    return (fold_w / 255.0).numpy().astype(np.float32), fold_b.numpy().astype(np.float32)
+
+
+def fold_from_module(model) -> Tuple[np.ndarray, np.ndarray]:
+    """Convenience for an nn.Module with the reference's attribute names (modules.model.Model)."""
+    sd = {k: v.detach().cpu().double().numpy() for k, v in model.state_dict().items()}
+    return fold_front(sd, int(model.input_channel), int(model.coverage_depth), 3)

@@ -1,0 +1,231 @@
+"""`Model` -- drop-in for modules.model.Model of the reference (/root/reference/src/modules/model.py:59-156) whose
+forward runs on the hand-written sm_100a kernels behind the C-ABI (include/deepore_b200.h, dp_model_*).
+
+Same constructor signature and defaults (model.py:60), same registered tensors (so `state_dict()` has the reference's
+17 keys), same unregistered `rnns` list of (name, nn.GRU) pairs (model.py:82-88), `init_hidden` (:114-116) and
+`forward(x, hidden) -> (N, T, class_n)` raw logits (:137-156).  A whole-object pickle written by the reference's
+`torch.save(model)` (train.py:194) unpickles into this class when deepore_b200/compat is on sys.path (it provides the
+module name `modules.model`), because only attribute names and nn submodules are stored in the pickle.
+
+There is no CPU path: forward raises unless the model and its input live on a CUDA device.
+
+Beyond the reference API, `forward_windows` / `call_windows` take whole uint8 pileup images as the encoder emits
+them and evaluate every sliding 3-row window (test.py:59-66) plus argmax and the 3-way vote (test.py:68-89) in one
+pass -- that is the path bench.py measures.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional
+
+import numpy as np
+import torch
+import torch.nn as nn
+
+from . import _lib
+from . import fold as _fold
+from . import modelio
+
+PRECISION = {"bf16": 0, "bf16x3": 1}
+
+
+class _Engine:
+    """Owns one dp_model handle (weights folded, packed and resident on one device)."""
+
+    def __init__(self, state, in_ch, width, hidden, n_layers, n_class, max_rows, precision, device):
+        _lib.require_cuda()
+        self.device = torch.device(device)
+        self.max_rows = int(max_rows)
+        self.n_class, self.seq_len, self.hidden = n_class, 3, hidden
+        self.width, self.in_ch = width, in_ch
+        fw, fb = _fold.fold_front(state, in_ch, width, 3)
+        keep = [np.ascontiguousarray(fw, dtype=np.float32), np.ascontiguousarray(fb, dtype=np.float32)]
+        w = _lib.ModelWeights()
+        w.in_ch, w.width, w.hidden, w.n_class, w.seq_len, w.n_layers = in_ch, width, hidden, n_class, 3, n_layers
+        w.fold_w, w.fold_b = keep[0].ctypes.data, keep[1].ctypes.data
+        for k in range(n_layers):
+            for d, suf in enumerate(("", "_reverse")):
+                for field, nm in (("gru_w_ih", "weight_ih_l0"), ("gru_w_hh", "weight_hh_l0"),
+                                  ("gru_b_ih", "bias_ih_l0"), ("gru_b_hh", "bias_hh_l0")):
+                    a = np.ascontiguousarray(state["rnns.%d.%s%s" % (k, nm, suf)], dtype=np.float32)
+                    keep.append(a)
+                    getattr(w, field)[k][d] = a.ctypes.data
+        a = np.ascontiguousarray(state["fc1.weight"], dtype=np.float32); keep.append(a); w.fc1_w = a.ctypes.data
+        a = np.ascontiguousarray(state["fc1.bias"], dtype=np.float32); keep.append(a); w.fc1_b = a.ctypes.data
+        h = C.c_void_p()
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().dp_model_create(C.byref(w), self.max_rows, int(precision), C.byref(h)), "dp_model_create")
+        self.handle = h
+
+    def __del__(self):
+        try:
+            if getattr(self, "handle", None):
+                _lib.lib().dp_model_destroy(self.handle)
+                self.handle = None
+        except Exception:
+            pass
+
+    def forward_rows(self, img_rows: torch.Tensor, want_logits=True, want_pred=True, logits=None, pred=None):
+        """img_rows uint8 [n_rows, width, in_ch] on this device -> (logits fp32 [n_rows,3,n_class], pred u8 [n_rows,3])"""
+        assert img_rows.dtype == torch.uint8 and img_rows.is_cuda and img_rows.is_contiguous()
+        n = int(img_rows.shape[0])
+        if n > self.max_rows:
+            raise _lib.DeeporeError("forward_rows: %d rows exceed the engine capacity %d" % (n, self.max_rows))
+        if want_logits and logits is None:
+            logits = torch.empty((n, 3, self.n_class), dtype=torch.float32, device=self.device)
+        if want_pred and pred is None:
+            pred = torch.empty((n, 3), dtype=torch.uint8, device=self.device)
+        st = torch.cuda.current_stream(self.device)
+        with torch.cuda.device(self.device):
+            rc = _lib.lib().dp_model_forward_rows(self.handle, img_rows.data_ptr(), n,
+                                                  logits.data_ptr() if logits is not None else None,
+                                                  pred.data_ptr() if pred is not None else None,
+                                                  C.c_void_p(st.cuda_stream))
+        _lib.check(rc, "dp_model_forward_rows")
+        return logits, pred
+
+    def peek(self, what: int, n_rows: int) -> np.ndarray:
+        out = np.empty((n_rows, 512), dtype=np.float32)
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().dp_model_peek(self.handle, what, n_rows, out.ctypes.data), "dp_model_peek")
+        return out
+
+
+def vote(pred: torch.Tensor, n_windows: int, H: int, n_class: int = 3, labels: Optional[torch.Tensor] = None,
+         confusion: Optional[torch.Tensor] = None):
+    """dp_vote: pred uint8 [n_windows*H, 3] -> calls int8 [n_windows, H]; optional confusion int64 [n_class, n_class]
+    accumulated as confusion[label][call] += 1 (test.py:82)."""
+    assert pred.is_cuda and pred.dtype == torch.uint8 and pred.is_contiguous()
+    calls = torch.empty((n_windows, H), dtype=torch.int8, device=pred.device)
+    if labels is not None:
+        labels = labels.to(device=pred.device, dtype=torch.uint8).contiguous()
+        if confusion is None:
+            confusion = torch.zeros((n_class, n_class), dtype=torch.int64, device=pred.device)
+    st = torch.cuda.current_stream(pred.device)
+    with torch.cuda.device(pred.device):
+        rc = _lib.lib().dp_vote(pred.data_ptr(), n_windows, H, n_class, calls.data_ptr(),
+                                labels.data_ptr() if labels is not None else None,
+                                confusion.data_ptr() if confusion is not None else None, C.c_void_p(st.cuda_stream))
+    _lib.check(rc, "dp_vote")
+    return calls, confusion
+
+
+class Model(nn.Module):
+    def __init__(self, input_channel=3, output_channel=256, coverage_depth=50, hidden_size=500, hidden_layer=3, class_n=3,
+                 bidirectional=True):
+        super().__init__()
+        self.input_channel = input_channel
+        self.output_channel = output_channel
+        self.coverage_depth = coverage_depth
+        self.classN = class_n
+        self.hidden_size = hidden_size
+        self.hidden_layer = hidden_layer
+        self.bidirectional = bidirectional
+        self.direction = 2 if bidirectional else 1
+        # registered tensors: names and shapes of model.py:70-79,90 (the weights are the checkpoint's, not ours)
+        self.batchNorm = nn.BatchNorm2d(output_channel)
+        self.incpConv0 = nn.Conv2d(input_channel, output_channel, (1, 1), bias=False)
+        self.incpConv1 = nn.Conv2d(output_channel, output_channel, (1, 1), bias=False)
+        self.conv0 = nn.Conv2d(input_channel, output_channel, (1, 3), padding=(0, 1), bias=False)
+        self.conv1 = nn.Conv2d(output_channel, output_channel, (1, 3), padding=(0, 1), bias=False)
+        self.conv2 = nn.Conv2d(output_channel, output_channel, (1, 3), padding=(0, 1), bias=True)
+        self.conv3 = nn.Conv2d(output_channel, output_channel, (1, 3), padding=(0, 1), bias=True)
+        self.cnn_fc_rnn = nn.Linear(coverage_depth * output_channel, hidden_size)
+        # plain list, like the reference (model.py:82-88): not in state_dict(), not moved by .cuda()
+        self.rnns = [("%d" % k, nn.GRU(input_size=hidden_size, hidden_size=hidden_size, bidirectional=bidirectional))
+                     for k in range(hidden_layer)]
+        self.fc1 = nn.Linear(hidden_size, class_n)
+        self.inference_log_softmax = nn.LogSoftmax(dim=-1)
+
+    # ------------------------------------------------------------------ reference API
+    def init_hidden(self, batch_size):
+        weight = next(self.parameters()).data
+        return weight.new_zeros(self.direction * self.hidden_layer, batch_size, self.hidden_size)
+
+    def forward(self, x, hidden=None):
+        """x (N, C, 3, W) float in [0,1] as ToTensor makes it (values k/255) -> raw logits (N, 3, class_n)."""
+        if not x.is_cuda:
+            raise _lib.DeeporeError("deepore_b200 Model.forward needs CUDA tensors (no CPU fallback); call .cuda() "
+                                    "and pass gpu_mode=True to test.py")
+        if x.dim() != 4 or x.size(2) != 3:
+            raise _lib.DeeporeError("forward expects (N, C, 3, W): seq_len is 3 on this path (test.py:48)")
+        if hidden is not None and bool((hidden[:2] != 0).any()):
+            raise _lib.DeeporeError("a non-zero initial hidden state is not supported (test.py:53 always passes zeros)")
+        q = torch.round(x * 255.0)
+        if bool(((x * 255.0 - q).abs() > 1e-3).any()) or bool((q < 0).any()) or bool((q > 255).any()):
+            raise _lib.DeeporeError("forward expects 8-bit pileup tensors scaled by ToTensor (values k/255)")
+        rows = q.to(torch.uint8).permute(0, 2, 3, 1).contiguous().view(-1, x.size(3), x.size(1))   # [N*3, W, C]
+        eng = self.engine(rows.shape[0], x.device)
+        logits, _ = eng.forward_rows(rows, want_logits=True, want_pred=False)
+        return logits.view(x.size(0), 3, 3, self.classN)[:, 0].contiguous()
+
+    # ------------------------------------------------------------------ B200 path
+    def numpy_state(self):
+        return modelio.state_from_module(self)
+
+    def engine(self, n_rows: int, device, precision: Optional[str] = None) -> _Engine:
+        precision = precision or getattr(self, "_precision", "bf16")
+        key = (str(device), precision, tuple((p.data_ptr(), p._version) for p in self._all_tensors()))
+        eng = self.__dict__.get("_engine")
+        if eng is None or self.__dict__.get("_engine_key") != key or eng.max_rows < n_rows:
+            cap = max(int(n_rows), 128, eng.max_rows if eng is not None and self.__dict__.get("_engine_key") == key else 0)
+            if eng is not None:
+                self.__dict__["_engine"] = None
+                del eng
+            eng = _Engine(self.numpy_state(), self.input_channel, self.coverage_depth, self.hidden_size, self.hidden_layer,
+                          self.classN, cap, PRECISION[precision], device)
+            self.__dict__["_engine"] = eng
+            self.__dict__["_engine_key"] = key
+        return eng
+
+    def set_precision(self, precision: str):
+        assert precision in PRECISION
+        self.__dict__["_precision"] = precision
+        return self
+
+    def _all_tensors(self):
+        for p in self.parameters():
+            yield p
+        for b in self.buffers():
+            yield b
+        for _, rnn in self.rnns:
+            for p in rnn.parameters():
+                yield p
+
+    def forward_windows(self, img: torch.Tensor, want_logits: bool = True):
+        """img uint8 [Nw, H, W, C] (the encoder's output) on a CUDA device.  Returns (logits fp32 [Nw, H, 3, class_n] or
+        None, pred uint8 [Nw, H, 3]); entry [w, r] is forward call r of test.py:59-66 (rows r..r+2); the last two rows of
+        each window have no full 3-row window inside the image and must be ignored."""
+        assert img.dim() == 4 and img.dtype == torch.uint8
+        nw, H = int(img.shape[0]), int(img.shape[1])
+        rows = img.contiguous().view(nw * H, img.shape[2], img.shape[3])
+        eng = self.engine(nw * H, img.device)
+        logits, pred = eng.forward_rows(rows, want_logits=want_logits, want_pred=True)
+        return (logits.view(nw, H, 3, self.classN) if logits is not None else None), pred.view(nw, H, 3)
+
+    def call_windows(self, img: torch.Tensor, labels: Optional[torch.Tensor] = None,
+                     confusion: Optional[torch.Tensor] = None):
+        """Encoder images -> calls int8 [Nw, H] (class per image row, -1 for unscored rows) [+ confusion tensor]."""
+        nw, H = int(img.shape[0]), int(img.shape[1])
+        _, pred = self.forward_windows(img, want_logits=False)
+        return vote(pred.view(nw * H, 3), nw, H, self.classN, labels, confusion)
+
+    def __getstate__(self):
+        d = dict(self.__dict__)
+        d.pop("_engine", None)
+        d.pop("_engine_key", None)
+        return d
+
+
+def from_state(state, device="cuda", precision="bf16") -> Model:
+    """Model(input_channel=4, coverage_depth=200) (the parity configuration) filled from a numpy state."""
+    width = int(state["cnn_fc_rnn.weight"].shape[1] // state["conv2.weight"].shape[0])
+    m = Model(input_channel=int(state["conv0.weight"].shape[1]), output_channel=int(state["conv2.weight"].shape[0]),
+              coverage_depth=width, hidden_size=int(state["fc1.weight"].shape[1]),
+              hidden_layer=sum(1 for k in state if k.endswith("weight_ih_l0")), class_n=int(state["fc1.weight"].shape[0]))
+    modelio.load_into_module(m, state)
+    m.eval()
+    m.set_precision(precision)
+    if str(device).startswith("cuda"):
+        m = m.cuda(device) if isinstance(device, int) else m.to(device)
+    return m

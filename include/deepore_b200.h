@@ -91,6 +91,72 @@ int dp_encode_windows(const dp_reads *reads, int32_t n_windows, const int32_t *w
  * (Pileup.py:166-171); evaluated once on the host with the reference's own expression and uploaded. */
 int dp_set_quality_lut(const uint8_t lut[256]);
 
+/* ================================================================================================
+ * Model forward: replaces modules.model.Model.forward (src/modules/model.py:137-156) and the sliding
+ * 3-row decode loop of src/test.py:59-89.
+ *
+ * dp_model_weights carries HOST pointers to fp32 tensors in torch layout:
+ *   fold_w / fold_b   the CNN + reinterpreting view + cnn_fc_rnn part of the forward (model.py:138-151) composed
+ *                     into ONE affine operator per time step -- legal because the five residual blocks hold only
+ *                     convolutions and eval-mode BatchNorm (no activation, model.py:93-105):
+ *                       y[t][h] = fold_b[t][h] + sum_{s,w,ch} fold_w[t][h][s][w][ch] * pixel_u8[row+s][w][ch]
+ *                     (s = row slot 0..seq_len-1; the 1/255 of ToTensor, dataset.py:52, is folded in).  The host helper
+ *                     deepore_b200/fold.py builds it from a Model's state in float64.
+ *   gru_*             rnns[k][1].{weight_ih,weight_hh,bias_ih,bias_hh}_l0[_reverse]  (model.py:83-87; gate order r,z,n)
+ *   fc1_*             fc1.{weight,bias}  (model.py:90)
+ */
+#define DP_MAX_GRU_LAYERS 3
+typedef struct dp_model_weights {
+    int32_t in_ch;        /* 4   */
+    int32_t width;        /* coverage_depth = 200 */
+    int32_t hidden;       /* 500 */
+    int32_t n_class;      /* 3   */
+    int32_t seq_len;      /* 3 (test.py:48) */
+    int32_t n_layers;     /* 3 bidirectional GRU layers */
+    const float *fold_w;  /* [seq_len][hidden][seq_len][width][in_ch] */
+    const float *fold_b;  /* [seq_len][hidden] */
+    const float *gru_w_ih[DP_MAX_GRU_LAYERS][2];   /* [3*hidden][hidden]; [.][0] forward, [.][1] reverse */
+    const float *gru_w_hh[DP_MAX_GRU_LAYERS][2];   /* [3*hidden][hidden] */
+    const float *gru_b_ih[DP_MAX_GRU_LAYERS][2];   /* [3*hidden] */
+    const float *gru_b_hh[DP_MAX_GRU_LAYERS][2];   /* [3*hidden] */
+    const float *fc1_w;   /* [n_class][hidden] */
+    const float *fc1_b;   /* [n_class] */
+} dp_model_weights;
+
+typedef struct dp_model dp_model;   /* opaque; immutable after creation, shared by all streams of its device */
+
+/* precision: 0 = bf16 operands / fp32 accumulate (tensor cores, one pass); 1 = split-bf16 (hi+lo operands, three
+ * passes, fp32-class accuracy).  max_rows = capacity in image rows per forward call (n_windows * windowCutoff). */
+int dp_model_create(const dp_model_weights *w, int64_t max_rows, int32_t precision, dp_model **out);
+int dp_model_destroy(dp_model *m);
+
+/*
+ * dp_model_forward_rows -- every 3-row window of a stack of pileup image rows in one pass.
+ *   img      device uint8 [n_rows][width][in_ch]: the encoder's out_img viewed as rows (n_windows*H rows)
+ *   logits   optional device fp32 [n_rows][seq_len][n_class]: logits[r] = Model.forward(rows r..r+seq_len-1)
+ *            (rows whose window runs past n_rows see zero rows there)
+ *   pred     optional device uint8 [n_rows][seq_len]: argmax over classes (torch.topk(1), first maximum)
+ */
+int dp_model_forward_rows(dp_model *m, const uint8_t *img, int64_t n_rows, float *logits, uint8_t *pred, void *stream);
+
+/*
+ * dp_vote -- test.py:71-89: calls[w][row] = mode(pred[w][row-2][2], pred[w][row-1][1], pred[w][row][0]) for
+ * 2 <= row <= H-3 (smallest class on a three-way tie), -1 elsewhere; optional confusion[label][call] += 1.
+ *   pred [n_windows][H][3] uint8 (dp_model_forward_rows with n_rows = n_windows*H), calls [n_windows][H] int8,
+ *   labels optional [n_windows][H] uint8, confusion optional [n_class*n_class] uint64 (accumulated, not cleared)
+ */
+int dp_vote(const uint8_t *pred, int32_t n_windows, int32_t H, int32_t n_class, int8_t *calls, const uint8_t *labels,
+            unsigned long long *confusion, void *stream);
+
+/* Debug/inspection: copy an internal activation of the last forward to the host as fp32 [n_rows][512].
+ * what: 0..2 = y[t] (folded CNN+Linear output); 100*k+10*d+t = GRU layer k hidden state, d=0 forward / 1 reverse. */
+int dp_model_peek(dp_model *m, int32_t what, int64_t n_rows, float *host_out);
+
+/* Plain dense GEMM on the same tcgen05 kernel (parity tests): out[M][N] = A[M][K] . B[N][K]^T + bias, device bf16
+ * row-major operands (lda, ldb in elements, multiples of 8), out bf16 or fp32 (ldc), N multiple of 16. */
+int dp_gemm_bf16(const void *A, int64_t lda, const void *B, int64_t ldb, const float *bias, void *out, int64_t ldc,
+                 int32_t out_fp32, int64_t M, int64_t N, int64_t K, int32_t block_n, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,113 @@
+"""Parity of the CUDA model path (C-ABI dp_model_*) against outputs of the UNMODIFIED reference model
+(tests/golden/model_seed7.npz) and against the numpy oracle.
+
+Tolerances: logits max-abs <= 2e-2 in bf16 mode (bf16 operands, fp32 accumulate; logit scale
+~3) and <= 2e-4 in split-bf16 mode; argmax and votes identical wherever the reference's top-2 margin exceeds twice
+the logit tolerance."""
+import os
+
+import numpy as np
+import pytest
+
+torch = pytest.importorskip("torch")
+pytestmark = pytest.mark.gpu
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "model_seed7.npz")
+TOL = {"bf16": 2e-2, "bf16x3": 2e-4}
+
+
+@pytest.fixture(scope="module")
+def gold():
+    return np.load(GOLD)
+
+
+def _model(precision):
+    from deepore_b200 import model, modelio
+    return model.from_state(modelio.seeded_state(7), "cuda", precision)
+
+
+@pytest.mark.parametrize("precision", ["bf16", "bf16x3"])
+def test_front_and_logits_vs_reference(gold, precision):
+    m = _model(precision)
+    img = torch.from_numpy(gold["img"]).cuda()
+    logits, pred = m.forward_windows(img)
+    torch.cuda.synchronize()
+    # stage 1: folded CNN + Linear (y) of window 0 against the reference's cnn_fc_rnn output
+    eng = m.engine(img.shape[0] * img.shape[1], img.device)
+    ytol = 2e-2 if precision == "bf16" else 2e-4
+    for t in range(3):
+        y = eng.peek(t, 150)[:148, :500]
+        err = np.abs(y - gold["y_window0"][:, t]).max()
+        assert err < ytol, "y[t=%d] max abs err %g" % (t, err)
+        assert np.abs(eng.peek(t, 150)[:148, 500:]).max() == 0.0
+    # stage 2: logits of every call of every window
+    lg = logits.cpu().numpy()[:, :148]
+    err = np.abs(lg - gold["logits"]).max()
+    assert err < TOL[precision], "logits max abs err %g" % err
+    # stage 3: argmax where the reference margin is decisive
+    srt = np.sort(gold["logits"], axis=-1)
+    decisive = (srt[..., -1] - srt[..., -2]) > 2 * TOL[precision]
+    pr = pred.cpu().numpy()[:, :148]
+    assert np.array_equal(pr[decisive], gold["pred"][decisive])
+    assert decisive.mean() > 0.9
+
+
+def test_votes_and_confusion(gold):
+    import model_oracle as mo
+    from deepore_b200 import model
+    pred = np.zeros((4, 150, 3), np.uint8)
+    pred[:, :148] = gold["pred"]
+    rng = np.random.default_rng(5)
+    pred[3] = rng.integers(0, 3, size=(150, 3))          # exercises pairs and three-way ties
+    labels = rng.integers(0, 3, size=(4, 150)).astype(np.uint8)
+    calls, conf = model.vote(torch.from_numpy(pred).cuda().view(-1, 3), 4, 150, 3, torch.from_numpy(labels).cuda())
+    calls = calls.cpu().numpy()
+    want = np.stack([mo.vote(pred[i, :148]) for i in range(4)])
+    assert np.array_equal(calls, want)
+    assert np.array_equal(calls[:3], gold["calls"][:3])
+    cw = np.zeros((3, 3), np.int64)
+    for i in range(4):
+        for r in range(150):
+            if want[i, r] >= 0:
+                cw[labels[i, r], want[i, r]] += 1
+    assert np.array_equal(conf.cpu().numpy(), cw)
+
+
+def test_forward_api_matches_forward_windows(gold):
+    """Model.forward(x, hidden) (the reference call, test.py:63-66) == the batched path, call by call."""
+    m = _model("bf16")
+    img = torch.from_numpy(gold["img"][:2]).cuda()
+    logits, _ = m.forward_windows(img)
+    images = (img.permute(0, 3, 1, 2).float() / 255.0).contiguous()
+    hidden = m.init_hidden(2)
+    for row in (0, 7, 147):
+        out = m(images[:, :, row:row + 3, :], hidden)
+        assert out.shape == (2, 3, 3)
+        assert torch.equal(out, logits[:, row])
+
+
+def test_oracle_on_random_images():
+    """Random legal pileup tensors through CUDA vs the layer-by-layer numpy oracle."""
+    import model_oracle as mo
+    from deepore_b200 import modelio
+    st = modelio.seeded_state(11)
+    from deepore_b200 import model
+    m = model.from_state(st, "cuda", "bf16x3")
+    rng = np.random.default_rng(3)
+    img = np.zeros((1, 150, 200, 4), np.uint8)
+    img[..., :3] = rng.integers(0, 2, size=(1, 150, 200, 3)) * 255
+    img[..., 3] = rng.integers(0, 256, size=(1, 150, 200))
+    logits, _ = m.forward_windows(torch.from_numpy(img).cuda())
+    calls = [0, 1, 73, 146, 147]
+    want = mo.forward_image(st, img[0], calls=calls)
+    got = logits.cpu().numpy()[0][calls]
+    assert np.abs(got - want).max() < 2e-4
+
+
+def test_empty_and_capacity():
+    m = _model("bf16")
+    img = torch.zeros((0, 150, 200, 4), dtype=torch.uint8, device="cuda")
+    logits, pred = m.forward_windows(img)
+    assert logits.shape == (0, 150, 3, 3)
+    with pytest.raises(Exception):
+        m(torch.zeros(1, 4, 3, 200))          # CPU tensor: no fallback

@@ -1,0 +1,72 @@
+"""CPU tests (no GPU): the numpy model oracle is pinned against outputs of the UNMODIFIED reference model
+(tests/golden/model_seed7.npz, written by oracle/make_model_golden.py), and the host-side operator fold is checked
+against the oracle's layer-by-layer evaluation."""
+import os
+
+import numpy as np
+import pytest
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "model_seed7.npz")
+
+
+@pytest.fixture(scope="module")
+def gold():
+    return np.load(GOLD)
+
+
+@pytest.fixture(scope="module")
+def state(gold):
+    from deepore_b200 import modelio
+    return modelio.seeded_state(int(gold["seed"]))
+
+
+CALLS = [0, 1, 2, 3, 4, 60, 61, 62, 145, 146, 147]
+
+
+def test_oracle_matches_reference_logits(gold, state):
+    import model_oracle as mo
+    for wi in (0, 2):
+        logits, y = mo.forward_image(state, gold["img"][wi], calls=CALLS, return_y=True)
+        ref = gold["logits"][wi][CALLS]
+        assert np.abs(logits - ref).max() < 2e-5          # reference is fp32, oracle fp64
+        if wi == 0:
+            assert np.abs(y - gold["y_window0"][CALLS]).max() < 1e-5
+
+
+def test_oracle_vote_matches_reference_loop(gold):
+    import model_oracle as mo
+    for wi in range(gold["pred"].shape[0]):
+        assert np.array_equal(mo.argmax_first(gold["logits"][wi]), gold["pred"][wi])
+        assert np.array_equal(mo.vote(gold["pred"][wi]), gold["calls"][wi])
+    # three-way tie -> smallest class; pairs -> the pair
+    p = np.zeros((5, 3), np.uint8)
+    p[0, 2], p[1, 1], p[2, 0] = 2, 1, 0          # row 2: votes (2,1,0) -> 0
+    p[1, 2], p[2, 1], p[3, 0] = 1, 2, 2          # row 3: votes (1,2,2) -> 2
+    v = mo.vote(p)
+    assert v[2] == 0 and v[3] == 2 and v[0] == -1 and v[1] == -1 and v[5] == -1 and v[6] == -1
+
+
+def test_fold_equals_layered_front(gold, state):
+    """fold_w/fold_b reproduce cnn_fc_rnn(feat) of the reference for every call of window 0 (fp64 fold, fp32 ref)."""
+    from deepore_b200 import fold
+    fw, fb = fold.fold_front(state, 4, 200, 3)
+    img = gold["img"][0].astype(np.float64)
+    calls = np.arange(148)
+    x = np.stack([img[r:r + 3] for r in calls])                      # [148,3,200,4]
+    y = np.einsum("thswc,nswc->nth", fw.astype(np.float64), x, optimize=True) + fb[None]
+    assert np.abs(y - gold["y_window0"]).max() < 1e-5
+
+
+def test_fold_linearity_and_border_columns(state):
+    """The folded operator must equal the layered oracle on inputs that light up single pixels at the borders
+    (columns 0, 14, 15, 184, 185, 199), where the zero padding of the intermediate layers matters."""
+    import model_oracle as mo
+    from deepore_b200 import fold
+    fw, fb = fold.fold_front(state, 4, 200, 3)
+    rng = np.random.default_rng(3)
+    img = np.zeros((3, 200, 4), np.uint8)
+    for col in (0, 1, 14, 15, 16, 100, 183, 184, 185, 198, 199):
+        img[rng.integers(0, 3), col, rng.integers(0, 4)] = rng.integers(1, 256)
+    _, y = mo.forward_image(state, img, calls=[0], return_y=True)
+    yf = np.einsum("thswc,swc->th", fw.astype(np.float64), img.astype(np.float64)) + fb
+    assert np.abs(yf - y[0]).max() < 1e-6
