@@ -2,17 +2,18 @@
 """bench.py -- measures the deePore hot path on B200 (driver contract: see DESIGN.md "measurement").
 
 One STEP = one interval shard (`--windows` consecutive windows of BASELINE.json configs[1]: synthetic 30x
-nanopore-length reads over a 9 Mb reference, window centres every 100 bp) pushed through the hot path:
-pileup encode (+ model forward and vote when `--stage e2e`).  Successive steps take successive intervals,
-so every step's inputs and outputs are new (outputs of one step, 120 kB/window, exceed L2).
+nanopore-length reads over a 9 Mb reference, window centres every 100 bp) pushed through the whole hot path:
+pileup encode -> CNN/GRU forward over every sliding 3-row window -> argmax -> 3-way vote (`--stage encode` stops after
+the encoder).  Successive steps take successive intervals, so every step's inputs and outputs are new (the pileup
+tensors of one step, 120 kB/window, exceed L2).
 
   value   genomic positions/s with the step's inputs already resident in HBM
   e2e     the same metric through the public host-buffer API: pinned host shard -> one H2D copy -> kernels
           -> D2H of the per-window result, all inside the timed region
   roofline / cpu_baseline / clocks / gpu_launches: as the contract asks
 
-`--impl reference` times the CPU implementation of the same path (oracle port of the reference's Pileup.py;
-the reference itself is Python + pysam and cannot travel to the GPU box) on all host cores.
+`--impl reference` times the CPU implementation of the same path (oracle ports of the reference's Pileup.py and
+model.py; the reference itself is Python + pysam + /root/reference and cannot travel to the GPU box) on all host cores.
 """
 from __future__ import annotations
 
@@ -97,6 +98,14 @@ class ClockSampler:
 
 
 # ----------------------------------------------------------------------------------------------------
+WORKLOAD = "configs[1]: synthetic 30x nanopore-length reads over 9Mb reference, window centres every %d bp"
+MODEL_SEED = 7
+# algorithmic FLOPs (2*MAC, unpadded sizes) of the schedule the CUDA path executes -- DESIGN.md "model roofline"
+FLOP_FOLD_PER_ROW = 2.0 * 2400 * 1500                 # folded CNN+Linear: K = 3 rows * 200 * 4, N = 3 * 500
+FLOP_GRU_STEP_PER_ROW = 2 * (2.0 * 500 * 1500) * 2    # one launch: both directions, input + hidden products
+FLOP_GRU_STEP0_PER_ROW = 2 * (2.0 * 500 * 1500)       # layer 0, first step: h_prev == 0, hidden product skipped
+
+
 def cpu_encode_rate(shard, seconds_budget=12.0, threads=None):
     """Oracle port (oracle/pileup_oracle.c, a C restatement of Pileup.py) on the host cores: windows/s.
     ctypes releases the GIL, so one Python thread per core drives one slice of the sample."""
@@ -104,26 +113,55 @@ def cpu_encode_rate(shard, seconds_budget=12.0, threads=None):
     import pileup_oracle as po
     po.lib()
     threads = threads or os.cpu_count() or 1
-    # calibrate on a few windows, then size the sample to the budget
     n0 = min(shard.n_windows, 16)
     t = time.perf_counter()
     po.encode_windows(shard.reads, shard.win_qs[:n0], shard.win_lo[:n0], shard.win_hi[:n0], shard.ref, shard.ref_base)
     per = max((time.perf_counter() - t) / n0, 1e-6)
     n = int(min(shard.n_windows, max(threads * 8, seconds_budget / per * threads)))
     idx = np.array_split(np.arange(n), threads)
+    out = [None] * threads
 
-    def work(ix):
+    def work(k, ix):
         if ix.size:
-            po.encode_windows(shard.reads, shard.win_qs[ix], shard.win_lo[ix], shard.win_hi[ix], shard.ref,
-                              shard.ref_base)
-    ths = [threading.Thread(target=work, args=(ix,)) for ix in idx]
+            out[k] = po.encode_windows(shard.reads, shard.win_qs[ix], shard.win_lo[ix], shard.win_hi[ix], shard.ref,
+                                       shard.ref_base)[0]
+    ths = [threading.Thread(target=work, args=(k, ix)) for k, ix in enumerate(idx)]
     t = time.perf_counter()
     for th in ths:
         th.start()
     for th in ths:
         th.join()
     dt = time.perf_counter() - t
-    return n / dt, n, threads, dt
+    first = next(o for o in out if o is not None)
+    return n / dt, n, threads, dt, first
+
+
+def cpu_model_rate(images, n_windows=2):
+    """Oracle port of model.py + the test.py decode (oracle/model_oracle.py, numpy float32 on the BLAS threads):
+    windows/s for whole-image inference (CNN once per image row, the cheapest correct CPU schedule)."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import model_oracle as mo
+    from deepore_b200 import modelio
+    st = modelio.seeded_state(MODEL_SEED)
+    n = min(n_windows, images.shape[0])
+    t = time.perf_counter()
+    for i in range(n):
+        lg = mo.forward_image(st, images[i], dtype=np.float32)
+        mo.vote(mo.argmax_first(lg))
+    dt = time.perf_counter() - t
+    return n / dt, n, dt
+
+
+def cpu_path_rate(shard, stage, enc_budget=8.0, model_windows=2):
+    """positions/s of the CPU port for encode (+ model): per-window times of the two stages add up."""
+    wps_e, n_e, threads, dt_e, imgs = cpu_encode_rate(shard, seconds_budget=enc_budget)
+    sec_per_window = 1.0 / wps_e
+    sample = "%d windows encoded by oracle/pileup_oracle.c on %d threads (%.1f s)" % (n_e, threads, dt_e)
+    if stage != "encode":
+        wps_m, n_m, dt_m = cpu_model_rate(imgs, model_windows)
+        sec_per_window += 1.0 / wps_m
+        sample += "; %d of them through oracle/model_oracle.py (numpy fp32, BLAS threads, %.1f s)" % (n_m, dt_m)
+    return 1.0 / sec_per_window, threads, sample
 
 
 def run_reference(args, rank, world):
@@ -132,26 +170,26 @@ def run_reference(args, rank, world):
         return
     from deepore_b200.workload import SyntheticWorkload
     wl = SyntheticWorkload(stride=args.stride)
-    nsh = 1
-    sh = wl.shards(0, min(args.windows, 2048), nsh)[0]
-    threads = os.cpu_count() or 1
-    rates = []
-    budget = max(2.0, min(20.0, 120.0 / max(1, args.steps + args.warmup)))
-    n = 0
+    sh = wl.shards(0, min(args.windows, 2048), 1)[0]
+    total = max(1, args.steps + args.warmup)
+    enc_budget = max(1.0, min(8.0, 60.0 / total))
+    mw = 2 if total <= 6 else 1
+    rates, threads, sample = [], 1, ""
+    t0 = time.perf_counter()
     for i in range(args.warmup + args.steps):
-        wps, n, threads, dt = cpu_encode_rate(sh, seconds_budget=budget, threads=threads)
+        wps, threads, sample = cpu_path_rate(sh, args.stage, enc_budget, mw)
         if i >= args.warmup:
             rates.append(wps)
     wps = float(np.mean(rates))
     val = wps * args.stride
     line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * n / wps, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-            "config": {"workload": "configs[1]: synthetic 30x nanopore-length reads over 9Mb reference, stride %d"
-                       % args.stride, "stage": args.stage, "windows_per_step": n},
-            "cpu_baseline": {"value": val, "unit": UNIT, "cores": threads, "kind": "port",
-                             "sample": "%d windows of the first shard per step, oracle/pileup_oracle.c on %d threads"
-                             % (n, threads)},
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * (time.perf_counter() - t0) / total,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "u8" if args.stage == "encode" else "f32", "data": "synthetic",
+            "config": {"workload": WORKLOAD % args.stride, "stage": args.stage,
+                       "note": "bounded sample per step; CPU ports of Pileup.py / model.py (the reference is Python and "
+                               "needs /root/reference + pysam, absent on the GPU box)"},
+            "cpu_baseline": {"value": val, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
             "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
 
@@ -163,8 +201,11 @@ def main():
     ap.add_argument("--steps", type=int, default=8)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--stage", default="encode", choices=["encode", "e2e"])
-    ap.add_argument("--windows", type=int, default=8192, help="windows per step (interval shard size)")
+    ap.add_argument("--stage", default="e2e", choices=["e2e", "encode"],
+                    help="e2e = encode + model + vote (the metric); encode = pileup encoder only")
+    ap.add_argument("--windows", type=int, default=2048, help="windows per step (interval shard size)")
+    ap.add_argument("--model-chunk", type=int, default=512, help="windows per model forward call")
+    ap.add_argument("--precision", default="bf16", choices=["bf16", "bf16x3"])
     ap.add_argument("--stride", type=int, default=100)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
@@ -190,7 +231,7 @@ def main():
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
 
-    # ---- workload: rank r owns a contiguous run of shards (weak scaling: fixed work per GPU)
+    # ---- workload: rank r owns a contiguous run of interval shards (weak scaling: fixed work per GPU, no collective)
     nsteps = args.steps + args.warmup
     wl = SyntheticWorkload(stride=args.stride)
     first = rank * nsteps * args.windows
@@ -201,20 +242,42 @@ def main():
     enc = Encoder(device=dev)
     nw = args.windows
     H, W = enc.H, enc.W
-    # two rotating output sets (the model consumes one while the next is encoded)
+    with_model = args.stage == "e2e"
+    mchunk = min(args.model_chunk, nw)
+    model = eng = None
+    if with_model:
+        from deepore_b200 import model as dmodel, modelio
+        model = dmodel.from_state(modelio.seeded_state(MODEL_SEED), dev, args.precision)
+        eng = model.engine(mchunk * H, dev)
+    # two rotating output sets (step i+1 may be encoded while step i's results drain to the host)
     outs = [dict(img=torch.empty((nw, H, W, 4), dtype=torch.uint8, device=dev),
                  rowpos=torch.empty((nw, H), dtype=torch.int32, device=dev),
                  rowins=torch.empty((nw, H), dtype=torch.int32, device=dev),
-                 status=torch.empty((nw,), dtype=torch.int32, device=dev)) for _ in range(2)]
+                 status=torch.empty((nw,), dtype=torch.int32, device=dev),
+                 pred=torch.empty((nw * H, 3), dtype=torch.uint8, device=dev),
+                 calls=torch.empty((nw, H), dtype=torch.int8, device=dev)) for _ in range(2)]
     host_status = torch.empty((nw,), dtype=torch.int32).pin_memory()
     host_rowpos = torch.empty((nw, H), dtype=torch.int32).pin_memory()
+    host_calls = torch.empty((nw, H), dtype=torch.int8).pin_memory()
+    import ctypes as C
 
     def step_device(i):
         sb = bufs[i]
         o = outs[i & 1]
         n = sb.n_windows
         enc.encode(sb, o["img"][:n], o["rowpos"][:n], o["rowins"][:n], o["status"][:n])
-        return 2  # launches: prep_reads_kernel + encode_windows_kernel
+        launches = 2                                   # prep_reads_kernel + encode_windows_kernel
+        if with_model:
+            rows = o["img"].view(nw * H, W, 4)
+            for c0 in range(0, n, mchunk):
+                c1 = min(n, c0 + mchunk)
+                eng.forward_rows(rows[c0 * H:c1 * H], want_logits=False, want_pred=True, pred=o["pred"][c0 * H:c1 * H])
+                launches += 12                         # u8->bf16, folded GEMM, 9 GRU steps, fc1+argmax
+            st = torch.cuda.current_stream(dev)
+            _lib.check(_lib.lib().dp_vote(o["pred"].data_ptr(), n, H, 3, o["calls"].data_ptr(), None, None,
+                                          C.c_void_p(st.cuda_stream)), "dp_vote")
+            launches += 1
+        return launches
 
     def step_e2e(i):
         sb = bufs[i]
@@ -224,6 +287,8 @@ def main():
         n = sb.n_windows
         host_status[:n].copy_(o["status"][:n], non_blocking=True)
         host_rowpos[:n].copy_(o["rowpos"][:n], non_blocking=True)
+        if with_model:
+            host_calls[:n].copy_(o["calls"][:n], non_blocking=True)
         return k
 
     def barrier():
@@ -232,39 +297,54 @@ def main():
             dist.barrier()
         torch.cuda.synchronize(dev)
 
-    def timed(fn, sampler=None):
+    def timed(fn, sampler=None, profile=False):
         for b in bufs:
             b.upload()
         for i in range(args.warmup):
             fn(i)
         barrier()
+        if profile and eng is not None:
+            eng.profile(True)
         if sampler:
             sampler.start()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         launches = 0
-        per_step = []
-        evs = []
+        enc_evs = []
         e0.record()
         for i in range(args.warmup, nsteps):
-            a = torch.cuda.Event(enable_timing=True); b = torch.cuda.Event(enable_timing=True)
-            a.record()
             launches += fn(i)
-            b.record()
-            evs.append((a, b))
         e1.record()
         barrier()
         clocks = sampler.stop() if sampler else None
+        prof = None
+        if profile and eng is not None:
+            prof = eng.profile_read()
+            eng.profile(False)
         ms = e0.elapsed_time(e1)
-        per_step = [a.elapsed_time(b) for a, b in evs]
         if world > 1:
             t = torch.tensor([ms], dtype=torch.float64, device=dev)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             ms = float(t.item())
-        return ms, launches, clocks, per_step
+        return ms, launches, clocks, prof
+
+    def time_encoder_alone():
+        """Average duration of the encoder launch pair over the timed shards (CUDA events on the launching stream)."""
+        evs = []
+        for i in range(args.warmup, nsteps):
+            sb, o = bufs[i], outs[i & 1]
+            n = sb.n_windows
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            enc.encode(sb, o["img"][:n], o["rowpos"][:n], o["rowins"][:n], o["status"][:n])
+            b.record()
+            evs.append((a, b))
+        torch.cuda.synchronize(dev)
+        return float(np.mean([a.elapsed_time(b) for a, b in evs]))
 
     sampler = ClockSampler(local_rank) if rank == 0 else None
-    ms_dev, launches, clocks, per_step = timed(step_device, sampler)
+    ms_dev, launches, clocks, prof = timed(step_device, sampler, profile=True)
     ms_e2e, _, _, _ = timed(step_e2e)
+    enc_ms = time_encoder_alone()
 
     win_timed = sum(b.n_windows for b in bufs[args.warmup:])
     tot_windows = win_timed * world
@@ -274,30 +354,49 @@ def main():
     if rank == 0:
         peaks = load_peaks()
         alg = sum(algorithmic_bytes(sh) for sh in shards[args.warmup:])
-        # the encode kernel pair is the whole device step at --stage encode: its mean duration per launch
-        kern_ms = float(np.mean(per_step))
-        achieved = alg / args.steps / (kern_ms * 1e-3) / 1e9
+        enc_achieved = alg / args.steps / (enc_ms * 1e-3) / 1e9
+        enc_roof = {"bound": "hbm", "achieved": enc_achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                    "frac": enc_achieved / peaks["hbm_gbs"], "traffic": None, "peak_source": peaks["source"],
+                    "kernel": "prep_reads_kernel+encode_windows_kernel", "ms_per_launch": enc_ms,
+                    "algorithmic_bytes_per_window": alg / max(1, win_timed)}
         h2d = int(np.mean([b.nbytes for b in bufs[args.warmup:]]))
-        d2h = int(nw * 4 + nw * H * 4)
+        d2h = int(nw * 4 + nw * H * 4 + (nw * H if with_model else 0))
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": ms_dev / args.steps, "higher_is_better": True,
-                "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-                "config": {"workload": "configs[1]: synthetic 30x nanopore-length reads over 9Mb reference, "
-                           "window centres every %d bp" % args.stride, "stage": args.stage,
-                           "windows_per_step": nw, "l2": "each step reads a new shard and writes %.0f MB (> L2)"
-                           % (nw * H * W * 4 / 1e6)},
+                "scaling": "weak", "vs_baseline": None, "dtype": args.precision if with_model else "u8",
+                "data": "synthetic",
+                "config": {"workload": WORKLOAD % args.stride, "stage": args.stage, "windows_per_step": nw,
+                           "model_chunk_windows": mchunk if with_model else None,
+                           "weights": "random init, modelio.seeded_state(%d)" % MODEL_SEED if with_model else None,
+                           "l2": "every step reads a new shard and writes %.0f MB of pileup tensors (> L2)"
+                                 % (nw * H * W * 4 / 1e6)},
                 "windows_per_s": tot_windows / (ms_dev * 1e-3),
-                "roofline": {"bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                             "frac": achieved / peaks["hbm_gbs"], "traffic": None, "peak_source": peaks["source"],
-                             "kernel": "prep_reads_kernel+encode_windows_kernel",
-                             "algorithmic_bytes_per_window": alg / max(1, win_timed)},
                 "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
                 "gpu_launches": launches, "clocks": clocks}
+        if with_model and prof:
+            g_ms, g_n = prof["gru_step"]
+            rows_per_launch = mchunk * H
+            n_layers = 3
+            flop_per_launch = rows_per_launch * ((n_layers * 3 - 1) * FLOP_GRU_STEP_PER_ROW + FLOP_GRU_STEP0_PER_ROW) / (n_layers * 3)
+            ach = flop_per_launch / (g_ms / max(1, g_n) * 1e-3) / 1e12
+            line["roofline"] = {"bound": "tensor", "achieved": ach, "peak": peaks["bf16_tflops_sustained"],
+                                "unit": "TFLOP/s", "frac": ach / peaks["bf16_tflops_sustained"], "traffic": None,
+                                "peak_source": peaks["source"] + " (sustained bf16)", "kernel": "gru_step_kernel",
+                                "ms_per_launch": g_ms / max(1, g_n), "launches": g_n,
+                                "algorithmic_flop_per_launch": flop_per_launch,
+                                "share_of_step": g_ms / ms_dev}
+            f_ms, f_n = prof["fold_gemm"]
+            fach = rows_per_launch * FLOP_FOLD_PER_ROW / (f_ms / max(1, f_n) * 1e-3) / 1e12
+            line["kernels"] = {k: {"ms_total": v[0], "launches": v[1], "share_of_step": v[0] / ms_dev} for k, v in prof.items()}
+            line["kernels"]["fold_gemm"]["achieved_tflops"] = fach
+            line["kernels"]["encoder"] = {"ms_per_launch_pair": enc_ms, "share_of_step": enc_ms * args.steps / ms_dev}
+            line["roofline_encoder"] = enc_roof
+        else:
+            line["roofline"] = enc_roof
         if not args.no_cpu_baseline:
-            wps, n, threads, dt = cpu_encode_rate(shards[args.warmup], seconds_budget=12.0)
-            line["cpu_baseline"] = {"value": wps * args.stride, "unit": UNIT, "cores": threads, "kind": "port",
-                                    "sample": "%d windows of the first timed shard, oracle/pileup_oracle.c "
-                                              "(C restatement of Pileup.py) on %d threads, %.1f s" % (n, threads, dt)}
+            val, threads, sample = cpu_path_rate(shards[args.warmup], args.stage)
+            line["cpu_baseline"] = {"value": val * args.stride, "unit": UNIT, "cores": threads, "kind": "port",
+                                    "sample": sample}
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

@@ -71,6 +71,10 @@ def lib():
     L.dp_vote.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     L.dp_model_peek.restype = C.c_int
     L.dp_model_peek.argtypes = [C.c_void_p, C.c_int32, C.c_int64, C.c_void_p]
+    L.dp_model_profile.restype = C.c_int
+    L.dp_model_profile.argtypes = [C.c_void_p, C.c_int32]
+    L.dp_model_profile_read.restype = C.c_int
+    L.dp_model_profile_read.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
     L.dp_gemm_bf16.restype = C.c_int
     L.dp_gemm_bf16.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32,
                                C.c_int64, C.c_int64, C.c_int64, C.c_int32, C.c_void_p]

@@ -62,7 +62,11 @@ struct Model {
     int gru_tab_off[3][3][2], gru_tab_n[3][3][2];
     long long kcols_fold = 0, kcols_gru = 0;
     CUtensorMap tm_img, tm_arena, tm_arena_lo, tm_wfold, tm_wgru;
+    // optional per-kernel timing (bench.py roofline): one event per launch boundary, harvested by dp_model_profile_read
+    int profile = 0;
+    std::vector<cudaEvent_t> prof_events;      // PROF_MARKS events per profiled forward call
 };
+constexpr int PROF_MARKS = 14;                 // start, convert, fold, 9 x gru_step (up to), fc1, (spare)
 
 static void free_model(Model *m) {
     if (!m) return;
@@ -316,6 +320,20 @@ static int build_model(Model *m, const dp_model_weights *w) {
 static int forward_rows(Model *m, const uint8_t *img, long long n_rows, float *logits, uint8_t *pred, cudaStream_t st) {
     const int RE = m->row_elems, S = m->seq_len;
     const long long mc = m->mcap;
+    size_t prof_base = 0;
+    int prof_i = 0;
+    if (m->profile) {
+        prof_base = m->prof_events.size();
+        for (int i = 0; i < PROF_MARKS; i++) {
+            cudaEvent_t e;
+            DP_CUDA_CHECK(cudaEventCreate(&e));
+            m->prof_events.push_back(e);
+        }
+    }
+    auto mark = [&]() {
+        if (m->profile && prof_i < PROF_MARKS) cudaEventRecord(m->prof_events[prof_base + prof_i++], st);
+    };
+    mark();
     // 1. u8 -> bf16 (plus seq_len-1 zero rows after the last one so trailing windows see zeros, not stale data)
     {
         const long long n16 = n_rows * RE / 16;
@@ -323,6 +341,7 @@ static int forward_rows(Model *m, const uint8_t *img, long long n_rows, float *l
         DP_CUDA_CHECK(cudaGetLastError());
         DP_CUDA_CHECK(cudaMemsetAsync(m->img_bf + n_rows * RE, 0, (size_t)(S - 1) * RE * 2, st));
     }
+    mark();
     const int tiles_m = (int)((n_rows + 127) / 128);
     const CUtensorMap tmA[4] = {m->tm_img, m->tm_arena, m->tm_arena_lo, m->tm_arena};
     // 2. folded CNN + Linear
@@ -341,6 +360,7 @@ static int forward_rows(Model *m, const uint8_t *img, long long n_rows, float *l
         int rc = launch_gemm_bf16(tmA, &m->tm_wfold, g, 256, st);
         if (rc) return rc;
     }
+    mark();
     // 3. GRU layers
     for (int k = 0; k < m->n_layers; k++)
         for (int sg = 0; sg < 3; sg++) {
@@ -383,6 +403,7 @@ static int forward_rows(Model *m, const uint8_t *img, long long n_rows, float *l
             }
             int rc = launch_gru_step(tmA, &m->tm_wgru, g, st);
             if (rc) return rc;
+            mark();
         }
     // 4. fc1 + argmax on the fp32 states of the last layer
     if (logits || pred) {
@@ -394,6 +415,7 @@ static int forward_rows(Model *m, const uint8_t *img, long long n_rows, float *l
                                                   m->b_fc1, m->n_class, S, n_rows, logits, pred);
         DP_CUDA_CHECK(cudaGetLastError());
     }
+    while (m->profile && prof_i < PROF_MARKS) mark();     // unused marks collapse onto the end
     return DP_OK;
 }
 
@@ -486,6 +508,33 @@ int dp_model_peek(dp_model *h, int32_t what, int64_t n_rows, float *host_out) {
     DP_REQUIRE(what >= 100 && k >= 1 && k <= m->n_layers && d < 2 && t < 3, "unknown peek id");
     const int slot = d == 0 ? dp::f32_slot_hf(k - 1, t) : dp::f32_slot_hb(k - 1, t);
     DP_CUDA_CHECK(cudaMemcpy(host_out, m->state + (size_t)slot * m->mcap * dp::HP, n * 4, cudaMemcpyDeviceToHost));
+    return DP_OK;
+}
+
+int dp_model_profile(dp_model *h, int32_t enable) {
+    DP_REQUIRE(h && h->m, "null model");
+    h->m->profile = enable ? 1 : 0;
+    return DP_OK;
+}
+
+int dp_model_profile_read(dp_model *h, float ms[4], int32_t launches[4]) {
+    DP_REQUIRE(h && h->m && ms && launches, "null argument");
+    dp::Model *m = h->m;
+    for (int i = 0; i < 4; i++) { ms[i] = 0.f; launches[i] = 0; }
+    DP_CUDA_CHECK(cudaDeviceSynchronize());
+    const int n_gru = m->n_layers * 3;
+    for (size_t b = 0; b + dp::PROF_MARKS <= m->prof_events.size(); b += dp::PROF_MARKS) {
+        for (int i = 0; i + 1 < dp::PROF_MARKS; i++) {
+            float t = 0.f;
+            if (cudaEventElapsedTime(&t, m->prof_events[b + i], m->prof_events[b + i + 1]) != cudaSuccess) { cudaGetLastError(); continue; }
+            const int cat = i == 0 ? 0 : i == 1 ? 1 : i < 2 + n_gru ? 2 : i == 2 + n_gru ? 3 : -1;
+            if (cat < 0) continue;
+            ms[cat] += t;
+            launches[cat] += 1;
+        }
+    }
+    for (cudaEvent_t e : m->prof_events) cudaEventDestroy(e);
+    m->prof_events.clear();
     return DP_OK;
 }
 

@@ -84,6 +84,18 @@ class _Engine:
         _lib.check(rc, "dp_model_forward_rows")
         return logits, pred
 
+    def profile(self, enable: bool):
+        _lib.check(_lib.lib().dp_model_profile(self.handle, 1 if enable else 0), "dp_model_profile")
+
+    def profile_read(self):
+        """-> {name: (milliseconds, launches)} accumulated since the last read (synchronises the device)."""
+        ms = (C.c_float * 4)()
+        n = (C.c_int32 * 4)()
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().dp_model_profile_read(self.handle, ms, n), "dp_model_profile_read")
+        names = ("u8_to_bf16", "fold_gemm", "gru_step", "fc1_argmax")
+        return {k: (float(ms[i]), int(n[i])) for i, k in enumerate(names)}
+
     def peek(self, what: int, n_rows: int) -> np.ndarray:
         out = np.empty((n_rows, 512), dtype=np.float32)
         with torch.cuda.device(self.device):

@@ -152,6 +152,13 @@ int dp_vote(const uint8_t *pred, int32_t n_windows, int32_t H, int32_t n_class, 
  * what: 0..2 = y[t] (folded CNN+Linear output); 100*k+10*d+t = GRU layer k hidden state, d=0 forward / 1 reverse. */
 int dp_model_peek(dp_model *m, int32_t what, int64_t n_rows, float *host_out);
 
+/* Per-kernel device timing for the roofline report (CUDA events on the launching stream around each launch of
+ * dp_model_forward_rows while enabled).  dp_model_profile_read synchronises the device and returns accumulated
+ * milliseconds and launch counts for: [0] u8->bf16 convert, [1] folded CNN+Linear GEMM, [2] GRU steps, [3] fc1+argmax,
+ * then clears the accumulators. */
+int dp_model_profile(dp_model *m, int32_t enable);
+int dp_model_profile_read(dp_model *m, float ms[4], int32_t launches[4]);
+
 /* Plain dense GEMM on the same tcgen05 kernel (parity tests): out[M][N] = A[M][K] . B[N][K]^T + bias, device bf16
  * row-major operands (lda, ldb in elements, multiples of 8), out bf16 or fp32 (ldc), N multiple of 16. */
 int dp_gemm_bf16(const void *A, int64_t lda, const void *B, int64_t ldb, const float *bias, void *out, int64_t ldc,

@@ -23,14 +23,14 @@ def _conv1x3(x, w, b=None):
     xp[:, :, 1:W + 1] = x
     out = np.zeros((R, w.shape[0], W), dtype=x.dtype)
     for k in range(3):
-        out += np.einsum("oc,rcw->row", w[:, :, 0, k], xp[:, :, k:k + W], optimize=True)
+        out += np.matmul(w[None, :, :, 0, k], xp[:, :, k:k + W])       # batched [Cout,Cin] @ [Cin,W] (BLAS)
     if b is not None:
         out += b[None, :, None]
     return out
 
 
 def _conv1x1(x, w):
-    return np.einsum("oc,rcw->row", w[:, :, 0, 0], x, optimize=True)
+    return np.matmul(w[None, :, :, 0, 0], x)
 
 
 def cnn_rows(state: Dict[str, np.ndarray], rows_u8: np.ndarray, dtype=np.float64) -> np.ndarray:
