@@ -366,7 +366,7 @@ static int forward_rows(Model *m, const uint8_t *img, long long n_rows, float *l
         for (int sg = 0; sg < 3; sg++) {
             GruArgs g;
             memset(&g, 0, sizeof(g));
-            g.n_prob = 2; g.M = (int)n_rows; g.tiles_m = tiles_m;
+            g.n_prob = 2; g.M = (int)n_rows; g.tiles_m = tiles_m; g.fast_act = m->precise ? 0 : 1;
             for (int d = 0; d < 2; d++) {
                 GruProblem &P = g.prob[d];
                 const int t = d == 0 ? sg : 2 - sg;

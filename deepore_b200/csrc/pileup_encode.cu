@@ -24,6 +24,7 @@
 //                 HBM-bound part.
 #include <limits.h>
 #include <stdarg.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 
@@ -44,6 +45,7 @@ __constant__ uint8_t c_qlut[256];
 static const uint8_t h_qlut_head[28] = {0,   52,  94,  127, 153, 174, 191, 204, 215, 223, 230, 235, 239, 242,
                                         245, 247, 249, 250, 251, 252, 252, 253, 253, 254, 254, 254, 254, 254};
 static bool g_lut_ready[64] = {false};
+static bool g_lut_flat = true;      // table constant from index 28 on (true for the reference's formula): v2 codes need it
 
 static int ensure_lut() {
     int dev = 0;
@@ -492,10 +494,12 @@ __device__ void run_pass(const EncArgs &a, int qs, int qe, int lo, int hi, SegHd
     }
 }
 
-__global__ void __launch_bounds__(ENC_THREADS) encode_windows_kernel(EncArgs a) {
+__global__ void __launch_bounds__(ENC_THREADS) encode_windows_kernel(EncArgs a, const int *__restrict__ win_count,
+                                                                     const int *__restrict__ win_list) {
     extern __shared__ __align__(16) uint8_t smem[];
     const int tid = threadIdx.x;
-    const int w = blockIdx.x;
+    if (win_list && (int)blockIdx.x >= *win_count) return;      // fallback launch: only the listed windows
+    const int w = win_list ? win_list[blockIdx.x] : blockIdx.x;
     const int L = a.L, W = a.W, H = a.H;
     const int qs = a.win_qs[w];
     const int qe = qs + L;
@@ -648,6 +652,433 @@ __global__ void __launch_bounds__(ENC_THREADS) encode_windows_kernel(EncArgs a) 
     if (tid == 0 && a.out_status) a.out_status[w] = *s_err;
 }
 
+// ================================================================================================
+// Encoder v2 (fast path).  Same closed form as v1, different work distribution:
+//   generate   one WARP per read (8 reads in flight per CTA): locate the read's first in-window op (32-ary search on
+//              the prefix sums), stage its <= 64 in-window ops, then lanes sweep the window's columns and write a
+//              one-byte code (category << 5 | quality index) per entry into shared-memory planes [entry][slot][column];
+//              inserted bases go to a byte pool addressed through an insert plane.
+//   walk       one THREAD per column reads its codes in slot (= file) order: pass A counts per category, pass B places
+//              each code at base[category] + running rank -- (read order, step order) without atomics or sorting.
+//              Up to 32 reads are held per batch; when a window has more, pass B regenerates batch by batch.
+//   emit       as v1, colour and alpha decoded from the code byte.
+// Anything outside the fast path's envelope (ops other than M/I/D/S, zero-length ops, > 64 in-window ops per read,
+// > 3 entries of one read on one column, two insertions of a read at one anchor, insert rows deeper than the image,
+// any condition on which the reference raises) marks the window for the exact v1 kernel, which then recomputes it.
+constexpr int V2_THREADS = 256;
+constexpr int V2_WARPS = V2_THREADS / 32;
+constexpr int V2_SLOTS = 32;          // reads per batch
+constexpr int V2_CS = 208;            // column stride of the code planes (>= window length)
+constexpr int V2_OPS = 64;            // staged ops per read
+constexpr int V2_POOL = 2048;         // inserted-base codes per batch
+constexpr int V2_NREC = 254;          // insert records per batch (plane byte = record + 1)
+constexpr int V2_CAND = 512;          // surviving reads held per round
+constexpr int V2_QMAX = 28;           // quality index clamp: the table is flat from here on (checked on the host)
+constexpr uint8_t V2_NONE = 0xFF;
+
+struct __align__(4) Op2 {
+    int sA;              // column of the op's first reference position, relative to queryStart
+    int qp;              // readPosition at op start
+    unsigned short n;    // length, clamped to 65535 (only compared against window-sized quantities)
+    unsigned short relop;// relativeIndexRef at op start (clamped to 4095) << 4 | op
+};
+__device__ __forceinline__ int op2_op(const Op2 &o) { return o.relop & 15; }
+__device__ __forceinline__ int op2_rel(const Op2 &o) { return o.relop >> 4; }
+
+struct V2Shared {
+    uint8_t *plane;      // [4][V2_SLOTS][V2_CS]: entry 0..2 codes, then the insert plane
+    uint8_t *pool;       // [V2_POOL]
+    uint32_t *rec;       // [V2_NREC + 2]: n << 16 | pool offset
+    Op2 *ops;            // [V2_WARPS][V2_OPS]
+    const uint8_t *ref;  // [L+1]
+    int *nrec, *npool, *fallback;
+};
+
+__device__ __forceinline__ uint8_t v2_code(int cat, int q) { return (uint8_t)((cat << 5) | min(q, V2_QMAX)); }
+
+// One warp: all entries of read r that land in window [qs, qs+Lwin) -> planes of `slot`.
+__device__ void v2_gen_read(const EncArgs &a, const V2Shared &S, int r, int slot, int qs, int Lwin, int lane, int warp) {
+    Op2 *ops = S.ops + warp * V2_OPS;
+    const ReadAux ax = a.aux[r];
+    const long long c0 = a.R.cigar_off[r];
+    const int nops_total = (int)(a.R.cigar_off[r + 1] - c0);
+    const int refStart = ax.ref_start;
+    const long long seq_off = a.R.seq_off[r], qual_off = a.R.qual_off[r];
+    const int aln_start = ax.aln_start, aln_len = ax.aln_len, l_seq = a.R.l_seq[r], mapq = a.R.mapq[r];
+    // ---- first op whose end reaches the window (as stage_read)
+    const long long rpb = c0 + r;
+    int j0;
+    {
+        const int T = qs - refStart;
+        int lo = 0, hi = nops_total;
+        while (lo < hi) {
+            const int len = hi - lo;
+            const int step = (len + 31) >> 5;
+            const int jk = min(lo + (lane + 1) * step - 1, hi - 1);
+            const bool before = a.RP[rpb + jk + 1] < T;
+            const int k = __popc(__ballot_sync(0xffffffffu, before));
+            if (k == 32) { lo = hi; break; }
+            const int nlo = lo + k * step;
+            const int nhi = min(lo + (k + 1) * step, hi) - 1;
+            lo = nlo; hi = max(nhi, nlo);
+        }
+        j0 = lo;
+    }
+    int carryA = 0, carryQ = 0, carryRel = refStart > qs ? refStart - qs - 1 : 0;
+    if (j0 < nops_total) { carryA = refStart + a.RP[rpb + j0] - qs; carryQ = -1 + a.QP[c0 + j0]; }
+    // ---- stage the in-window ops
+    int staged = 0;
+    bool bad = false;
+    for (int round = 0; round < V2_OPS / 32 + 1; round++) {
+        const int jj = j0 + round * 32 + lane;
+        const bool valid = jj < nops_total;
+        const uint32_t w = valid ? a.R.cigar[c0 + jj] : 0u;
+        const int op = w & 15, n = (int)(w >> 4);
+        const int dR = op_adv_ref(op) ? n : 0, dQ = op_adv_read(op) ? n : 0;
+        const int iR = warp_incl_scan(dR, lane), iQ = warp_incl_scan(dQ, lane);
+        const int sA = carryA + iR - dR, qp = carryQ + iQ - dQ;
+        int inwin = 0;
+        if (valid && (op == 0 || op == 2) && n > 0) {
+            inwin = (sA >= 0 && sA < Lwin) ? 1 : 0;
+            const int lo_i = max(1, 1 - sA), hi_i = min(n - 1, Lwin - sA);
+            if (hi_i >= lo_i) inwin += hi_i - lo_i + 1;
+        }
+        const int iW = warp_incl_scan(inwin, lane);
+        const int rel = carryRel + iW - inwin;
+        const bool relevant = valid && sA < Lwin;
+        const int cnt = __popc(__ballot_sync(0xffffffffu, relevant));      // a prefix of the lanes (sA is monotone)
+        if (relevant) {
+            if (round == V2_OPS / 32) bad = true;                          // more than V2_OPS in-window ops
+            else {
+                if (!(op == 0 || op == 1 || op == 2 || op == 4) || n == 0) bad = true;
+                Op2 o;
+                o.sA = sA; o.qp = qp; o.n = (unsigned short)min(n, 65535);
+                o.relop = (unsigned short)((max(0, min(rel, 4095)) << 4) | op);
+                ops[staged + lane] = o;
+            }
+        }
+        if (round < V2_OPS / 32) staged += cnt;
+        carryA += __shfl_sync(0xffffffffu, iR, 31);
+        carryQ += __shfl_sync(0xffffffffu, iQ, 31);
+        carryRel += __shfl_sync(0xffffffffu, iW, 31);
+        if (cnt < 32) break;
+    }
+    __syncwarp();
+    const uint8_t *seqp = a.R.seq4 + seq_off, *qualp = a.R.qual + qual_off;
+    uint8_t *p0 = S.plane + (size_t)slot * V2_CS, *p1 = p0 + V2_SLOTS * V2_CS, *p2 = p1 + V2_SLOTS * V2_CS;
+    uint8_t *pi = p2 + V2_SLOTS * V2_CS;
+    // ---- columns
+    for (int P = lane; P < Lwin; P += 32) {
+        uint8_t code[3] = {V2_NONE, V2_NONE, V2_NONE};
+        int ne = 0;
+        int lo = 0, hi = staged;                      // first op with key > P (key as in seg_lower_bound)
+        while (lo < hi) {
+            const int mid = (lo + hi) >> 1;
+            const Op2 o = ops[mid];
+            const int oo = op2_op(o);
+            const int key = (oo == 0 || oo == 2) ? o.sA + o.n : o.sA + 1;
+            if (key <= P) lo = mid + 1; else hi = mid;
+        }
+        for (int j = lo; j < staged; j++) {
+            const Op2 o = ops[j];
+            if (o.sA > P) break;
+            const int op = op2_op(o), n = o.n;
+            if (op == 1) continue;
+            int i_first, i_count;
+            if (op == 4) { if (o.sA != P) continue; i_first = 0; i_count = 1; }
+            else if (P == o.sA) { i_first = 0; i_count = n >= 2 ? 2 : 1; }
+            else { i_first = P - o.sA + 1; i_count = (i_first <= n - 1) ? 1 : 0; }
+            const int in0 = (o.sA >= 0 && o.sA < Lwin) ? 1 : 0, lo_i = max(1, 1 - o.sA);
+            for (int t = 0; t < i_count; t++) {
+                const int i = i_first + t;
+                int idx = o.qp + (op == 0 ? i : 0);
+                int rel = op2_rel(o);
+                if (op != 4 && i > 0) rel += in0 + max(0, i - lo_i);
+                int si = idx < 0 ? idx + aln_len : idx, qi = idx < 0 ? idx + l_seq : idx;
+                if (rel < 0 || rel > Lwin || si < 0 || si >= aln_len || qi < 0 || qi >= l_seq) { bad = true; continue; }
+                const int k = si + aln_start;
+                const uint8_t b = __ldg(seqp + (k >> 1));
+                const int nib = (k & 1) ? (b & 15) : (b >> 4);
+                int cat;
+                if (op == 2) cat = CAT_D;
+                else {
+                    cat = (ascii_of_code(nib) == S.ref[rel]) ? CAT_M : cat_of_code(nib);
+                    if (cat < 0) { bad = true; continue; }
+                }
+                const int q = min((int)__ldg(qualp + qi), mapq);
+                if (ne < 3) code[ne] = v2_code(cat, q); else bad = true;
+                ne++;
+            }
+        }
+        p0[P] = code[0]; p1[P] = code[1]; p2[P] = code[2];
+    }
+    // ---- insertions (Pileup.py:220-230): anchor column sA in [1, Lwin)
+    for (int jj = lane; jj < staged; jj += 32) {
+        const Op2 o = ops[jj];
+        if (op2_op(o) != 1 || o.sA < 1 || o.sA >= Lwin) continue;
+        const int n = o.n;
+        bool dup = n >= 65535;
+        for (int b = jj - 1; b >= 0 && ops[b].sA == o.sA; b--) dup |= op2_op(ops[b]) == 1;
+        const int first = o.qp + 1, last = o.qp + n;
+        if (dup || first < 0 || last >= aln_len || last >= l_seq) { bad = true; continue; }
+        const int rec = atomicAdd(S.nrec, 1);
+        const int off = atomicAdd(S.npool, n);
+        if (rec >= V2_NREC || off + n > V2_POOL) { bad = true; continue; }
+        S.rec[rec] = ((uint32_t)n << 16) | (uint32_t)off;
+        pi[o.sA] = (uint8_t)(rec + 1);
+        for (int k2 = 0; k2 < n; k2++) {
+            const int k = first + k2 + aln_start;
+            const uint8_t b = __ldg(seqp + (k >> 1));
+            const int nib = (k & 1) ? (b & 15) : (b >> 4);
+            const int cat = cat_of_code(nib);
+            if (cat < 0) { bad = true; break; }
+            S.pool[off + k2] = v2_code(cat, min((int)__ldg(qualp + first + k2), mapq));
+        }
+    }
+    if (bad) *S.fallback = 1;
+}
+
+__global__ void __launch_bounds__(V2_THREADS, 3)
+encode_windows_v2_kernel(EncArgs a, int *__restrict__ fb_count, int *__restrict__ fb_list) {
+    extern __shared__ __align__(16) uint8_t smem[];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int w = blockIdx.x;
+    const int L = a.L, W = a.W, H = a.H;
+    const int qs = a.win_qs[w], qe = qs + L;
+    const int lo = a.win_lo[w], hi = a.win_hi[w];
+
+    // ---- shared memory carve-up (16-byte aligned sections)
+    uint8_t *p = smem;
+    uint8_t *s_plane = p;                          p += 4 * V2_SLOTS * V2_CS;
+    uint8_t *s_q = p;                              p += ((H * W + 15) / 16) * 16;      // [H][W] code bytes (pixel 0 unused)
+    Op2 *s_ops = (Op2 *)p;                         p += sizeof(Op2) * V2_WARPS * V2_OPS;
+    uint32_t *s_rec = (uint32_t *)p;               p += 4 * 256;
+    uint8_t *s_pool = p;                           p += V2_POOL;
+    int *s_cand = (int *)p;                        p += 4 * V2_CAND;
+    unsigned short *s_cnt = (unsigned short *)p;   p += 2 * NCAT * V2_CS;              // [cat][col] counts, then running ranks
+    unsigned short *s_rowstart = (unsigned short *)p; p += 2 * V2_CS;
+    unsigned short *s_ord = (unsigned short *)p;   p += 2 * V2_CS;                     // anchor ordinal of a populated column
+    short *s_rowcol = (short *)p;                  p += 2 * 256;
+    short *s_rowk = (short *)p;                    p += 2 * 256;
+    unsigned short *s_rowcnt = (unsigned short *)p; p += 2 * 256;
+    uint8_t *s_ref = p;                            p += 224;
+    uint8_t *s_rowref = p;                         p += 256;
+    int *s_misc = (int *)p;                        // [0] fallback [1] nrec [2] npool [3] ncand [4..12] warp sums [13] nrows
+    int *s_fallback = &s_misc[0], *s_nrec = &s_misc[1], *s_npool = &s_misc[2], *s_ncand = &s_misc[3];
+    int *s_wsum = &s_misc[4], *s_nrows = &s_misc[13];
+
+    V2Shared S;
+    S.plane = s_plane; S.pool = s_pool; S.rec = s_rec; S.ops = s_ops; S.ref = s_ref;
+    S.nrec = s_nrec; S.npool = s_npool; S.fallback = s_fallback;
+
+    const long long roff = (long long)qs - a.ref_base;
+    const bool ref_ok = roff >= 0 && roff + L + 1 <= a.ref_len;
+    if (tid == 0) { *s_fallback = ref_ok ? 0 : 1; *s_ncand = 0; }
+    for (int i = tid; i < L + 1; i += V2_THREADS) s_ref[i] = ref_ok ? a.ref[roff + i] : (uint8_t)'N';
+    for (int i = tid; i < NCAT * V2_CS; i += V2_THREADS) s_cnt[i] = 0;
+    for (int i = tid; i < 256; i += V2_THREADS) { s_rowcnt[i] = 0; s_rowcol[i] = -1; s_rowk[i] = 0; s_rowref[i] = 'N'; }
+    __syncthreads();
+
+    int populated = 0, max_ins = 0;                 // column state of thread tid (tid < L)
+    int n_batches = 0;                              // batches generated in pass A (uniform)
+    int my_row = -1;
+
+    // pass 0 = count (A), pass 1 = place (B)
+    for (int pass = 0; pass < 2; pass++) {
+        const bool reuse = pass == 1 && n_batches == 1;       // codes of the only batch are still in the planes
+        int cb = lo;
+        bool more_cands = !reuse && cb < hi;
+        bool first_round = true;
+        while (more_cands || (reuse && first_round)) {
+            first_round = false;
+            int total;
+            if (!reuse) {
+                // ---- ordered compaction of surviving reads (hts.c:2242 overlap, mapq cut, has an aligned base) into s_cand
+                if (tid == 0) *s_ncand = 0;
+                __syncthreads();
+                while (cb < hi && *s_ncand + V2_THREADS <= V2_CAND) {
+                    const int r = cb + tid;
+                    bool keep = false;
+                    if (r < hi) {
+                        const ReadAux ax = a.aux[r];
+                        keep = a.R.pos[r] < qe && ax.endpos > qs && (int)a.R.mapq[r] >= a.mapq_cut && ax.ref_start != INT_MIN;
+                    }
+                    const unsigned bal = __ballot_sync(0xffffffffu, keep);
+                    if (lane == 0) s_wsum[warp] = __popc(bal);
+                    __syncthreads();
+                    int off = *s_ncand, tot = 0;
+                    for (int k = 0; k < V2_WARPS; k++) { const int c = s_wsum[k]; if (k < warp) off += c; tot += c; }
+                    if (keep) s_cand[off + __popc(bal & ((1u << lane) - 1))] = r;
+                    __syncthreads();
+                    if (tid == 0) *s_ncand += tot;
+                    cb += V2_THREADS;
+                    __syncthreads();
+                }
+                total = *s_ncand;
+                more_cands = cb < hi;
+            } else total = 0;
+            const int nb = reuse ? 1 : (total + V2_SLOTS - 1) / V2_SLOTS;
+            for (int b = 0; b < nb; b++) {
+                const int nslots = reuse ? V2_SLOTS : min(V2_SLOTS, total - b * V2_SLOTS);
+                if (!reuse) {
+                    // ---- clear the planes (entry planes NONE, insert plane 0) and the batch counters
+                    uint4 *pl = reinterpret_cast<uint4 *>(s_plane);
+                    const int n16 = 3 * V2_SLOTS * V2_CS / 16, m16 = 4 * V2_SLOTS * V2_CS / 16;
+                    for (int i = tid; i < m16; i += V2_THREADS)
+                        pl[i] = i < n16 ? make_uint4(~0u, ~0u, ~0u, ~0u) : make_uint4(0u, 0u, 0u, 0u);
+                    if (tid == 0) { *s_nrec = 0; *s_npool = 0; }
+                    __syncthreads();
+                    for (int s = warp; s < nslots; s += V2_WARPS)
+                        v2_gen_read(a, S, s_cand[b * V2_SLOTS + s], s, qs, L, lane, warp);
+                    __syncthreads();
+                    if (pass == 0) n_batches++;
+                }
+                // ---- walk: thread tid owns column tid
+                if (tid < L) {
+                    const uint8_t *c0 = s_plane + tid, *ci = s_plane + 3 * V2_SLOTS * V2_CS + tid;
+                    if (pass == 0) {
+                        for (int s = 0; s < nslots; s++) {
+#pragma unroll
+                            for (int e = 0; e < 3; e++) {
+                                const uint8_t c = c0[(e * V2_SLOTS + s) * V2_CS];
+                                if (c == V2_NONE) break;
+                                s_cnt[(c >> 5) * V2_CS + tid]++;
+                                populated = 1;
+                            }
+                            const int ir = ci[s * V2_CS];
+                            if (ir) max_ins = max(max_ins, (int)(s_rec[ir - 1] >> 16));
+                        }
+                    } else if (my_row >= 0) {
+                        uint8_t *qrow = s_q + (size_t)my_row * W;
+                        for (int s = 0; s < nslots; s++) {
+#pragma unroll
+                            for (int e = 0; e < 3; e++) {
+                                const uint8_t c = c0[(e * V2_SLOTS + s) * V2_CS];
+                                if (c == V2_NONE) break;
+                                const int pos = s_cnt[(c >> 5) * V2_CS + tid]++;
+                                if (pos < W - 1) qrow[1 + pos] = c;
+                            }
+                            const int ir = ci[s * V2_CS];
+                            if (ir) {
+                                const uint32_t rc = s_rec[ir - 1];
+                                const int n = rc >> 16, off = rc & 0xffff;
+                                for (int k = 0; k < n; k++) {
+                                    const int y = my_row + 1 + k;
+                                    if (y >= H) break;
+                                    const int pos = s_rowcnt[y]++;
+                                    if (pos < W - 1) s_q[(size_t)y * W + 1 + pos] = s_pool[off + k];
+                                    else *s_fallback = 1;      // deeper than the image: the category sort needs all entries
+                                }
+                            }
+                        }
+                    }
+                }
+                __syncthreads();
+            }
+        }
+        if (pass == 0) {
+            // ---- row map (Pileup.py:295-317): rows = populated columns ascending, each followed by its insert rows
+            const int mine = (tid < L && populated) ? min(1 + max_ins, 300) : 0;   // clamp: only rows < H <= 256 matter
+            const int pop = (tid < L && populated) ? 1 : 0;
+            int v = mine | (pop << 16);                                  // two scans in one word (rows < 65536)
+            const int incl = warp_incl_scan(v, lane);
+            if (lane == 31) s_wsum[warp] = incl;
+            __syncthreads();
+            int base = 0;
+            for (int k = 0; k < warp; k++) base += s_wsum[k];
+            const int excl = base + incl - v;
+            const int rstart = excl & 0xffff, ord = excl >> 16;
+            if (tid == V2_THREADS - 1) *s_nrows = (base + incl) & 0xffff;
+            if (tid < L && populated) {
+                s_rowstart[tid] = (unsigned short)rstart;
+                s_ord[tid] = (unsigned short)ord;
+                if (cat_of_ascii(s_ref[ord]) < 0) *s_fallback = 1;       // KeyError at Pileup.py:281 on the reference pixel
+                if (rstart < H) {
+                    my_row = rstart;
+                    s_rowref[rstart] = s_ref[ord];
+                    for (int k = 0; k <= max_ins; k++) {
+                        const int y = rstart + k;
+                        if (y >= H) break;
+                        s_rowcol[y] = (short)tid; s_rowk[y] = (short)k;
+                    }
+                    // counts -> first slot of each category (sortingKey order A,C,G,T,D,M,N), total -> row count
+                    int acc = 0;
+#pragma unroll
+                    for (int c = 0; c < NCAT; c++) { const int n = s_cnt[c * V2_CS + tid]; s_cnt[c * V2_CS + tid] = (unsigned short)acc; acc = min(acc + n, 65535); }
+                    s_rowcnt[rstart] = (unsigned short)min(acc, W - 1);
+                }
+            }
+            __syncthreads();
+        }
+    }
+    const int nrows = min(*s_nrows, H);
+    // ---- insert rows: stable sort by category (A,C,G,T,N) of the codes appended in read order
+    if (tid < nrows && s_rowk[tid] != 0) {
+        uint8_t *row = s_q + (size_t)tid * W + 1;
+        const int n = min((int)s_rowcnt[tid], W - 1);
+        for (int i = 1; i < n; i++) {
+            const uint8_t c = row[i];
+            int j = i - 1;
+            while (j >= 0 && (row[j] >> 5) > (c >> 5)) { row[j + 1] = row[j]; j--; }
+            row[j + 1] = c;
+        }
+    }
+    __syncthreads();
+    if (*s_fallback) {
+        if (tid == 0) {
+            const int k = atomicAdd(fb_count, 1);
+            fb_list[k] = w;
+            if (a.out_status) a.out_status[w] = 0;
+        }
+        return;                                      // the exact kernel rewrites this window
+    }
+    // ---- emit: RGBA rows, 16-byte stores
+    uint8_t *img = a.out_img + (size_t)w * H * W * 4;
+    const int quads_per_row = W / 4;
+    const int total_quads = H * quads_per_row;
+    for (int qd = tid; qd < total_quads; qd += V2_THREADS) {
+        const int y = qd / quads_per_row;
+        const int x0 = (qd - y * quads_per_row) * 4;
+        uint32_t px[4];
+        if (y >= nrows) {
+            px[0] = px[1] = px[2] = px[3] = 0xFF000000u;
+        } else {
+            const bool ins = s_rowk[y] != 0;
+            const uint32_t filler = ins ? 0xFFFF00FFu : 0xFF000000u;
+            const int tot = min((int)s_rowcnt[y], W - 1);
+            const uint32_t codes = *reinterpret_cast<const uint32_t *>(s_q + (size_t)y * W + x0);
+#pragma unroll
+            for (int t = 0; t < 4; t++) {
+                const int x = x0 + t;
+                uint32_t v;
+                if (x == 0) v = ins ? 0xFFFF00FFu : (cat_rgb(cat_of_ascii(s_rowref[y])) | 0xFF000000u);
+                else if (x - 1 >= tot) v = filler;
+                else {
+                    const uint32_t c = (codes >> (8 * t)) & 0xffu;
+                    v = cat_rgb((int)(c >> 5)) | ((uint32_t)c_qlut[c & 31u] << 24);
+                }
+                px[t] = v;
+            }
+        }
+        *reinterpret_cast<uint4 *>(img + ((size_t)y * W + x0) * 4) = make_uint4(px[0], px[1], px[2], px[3]);
+    }
+    for (int y = tid; y < H; y += V2_THREADS) {
+        if (a.out_rowpos) a.out_rowpos[(size_t)w * H + y] = (y < nrows) ? qs + s_rowcol[y] : -1;
+        if (a.out_rowins) a.out_rowins[(size_t)w * H + y] = (y < nrows) ? s_rowk[y] : 0;
+    }
+    if (tid == 0 && a.out_status) a.out_status[w] = 0;
+}
+
+static size_t encoder_v2_smem_bytes(const dp_encode_params *p) {
+    size_t s = 0;
+    s += 4 * V2_SLOTS * V2_CS;
+    s += ((size_t)p->window_cutoff * p->coverage_cutoff + 15) / 16 * 16;
+    s += sizeof(Op2) * V2_WARPS * V2_OPS;
+    s += 4 * 256 + V2_POOL + 4 * V2_CAND;
+    s += 2 * NCAT * V2_CS + 2 * V2_CS * 2 + 2 * 256 * 3 + 224 + 256 + 64;
+    return s;
+}
+
 static size_t encoder_smem_bytes(const dp_encode_params *p) {
     const int L = 2 * p->flank + 1;
     size_t s = 0;
@@ -684,15 +1115,19 @@ int dp_set_quality_lut(const uint8_t lut[256]) {
     int dev = 0;
     DP_CUDA_CHECK(cudaGetDevice(&dev));
     if (dev < 64) dp::g_lut_ready[dev] = true;
+    bool flat = true;
+    for (int i = 28; i < 256; i++) flat = flat && lut[i] == lut[28];
+    dp::g_lut_flat = flat;
     return DP_OK;
 }
 
 int64_t dp_encode_workspace_bytes(int32_t n_reads, int64_t n_cigar, int32_t n_windows, const dp_encode_params *p) {
-    (void)n_windows; (void)p;
+    (void)p;
     int64_t b = 0;
     b += dp::align_up((int64_t)sizeof(dp::ReadAux) * (n_reads > 0 ? n_reads : 1), 256);
     b += dp::align_up((int64_t)sizeof(int) * (n_cigar + n_reads + 1), 256);   /* RP: nops+1 per read */
     b += dp::align_up((int64_t)sizeof(int) * (n_cigar + 1), 256);             /* QP */
+    b += dp::align_up((int64_t)sizeof(int) * ((n_windows > 0 ? n_windows : 0) + 64), 256);   /* fallback count + list */
     return b;
 }
 
@@ -723,6 +1158,8 @@ int dp_encode_windows(const dp_reads *reads, int32_t n_windows, const int32_t *w
     int *RP = (int *)wp;
     wp += dp::align_up((int64_t)sizeof(int) * (n_cigar + reads->n_reads + 1), 256);
     int *QP = (int *)wp;
+    wp += dp::align_up((int64_t)sizeof(int) * (n_cigar + 1), 256);
+    int *fb = (int *)wp;                                       /* fb[0] = count, fb[64..] = window list */
 
     if (reads->n_reads > 0) {
         const int warps_per_block = 8;
@@ -739,7 +1176,22 @@ int dp_encode_windows(const dp_reads *reads, int32_t n_windows, const int32_t *w
     const size_t smem = dp::encoder_smem_bytes(p);
     DP_REQUIRE(smem <= 227 * 1024, "coverageCutoff*windowCutoff too large for shared-memory staging");
     DP_CUDA_CHECK(cudaFuncSetAttribute(dp::encode_windows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    dp::encode_windows_kernel<<<n_windows, dp::ENC_THREADS, smem, st>>>(a);
+    // fast path (v2) when the geometry fits its shared-memory planes; windows it cannot take are listed for v1
+    static int force_v1 = -1;
+    if (force_v1 < 0) { const char *e = getenv("DP_ENCODER"); force_v1 = (e && !strcmp(e, "v1")) ? 1 : 0; }
+    const size_t smem2 = dp::encoder_v2_smem_bytes(p);
+    const bool use_v2 = !force_v1 && dp::g_lut_flat && L <= dp::V2_CS && p->window_cutoff <= 256 &&
+                        p->coverage_cutoff <= 256 && smem2 <= 100 * 1024;
+    if (!use_v2) {
+        dp::encode_windows_kernel<<<n_windows, dp::ENC_THREADS, smem, st>>>(a, nullptr, nullptr);
+        DP_CUDA_CHECK(cudaGetLastError());
+        return DP_OK;
+    }
+    DP_CUDA_CHECK(cudaMemsetAsync(fb, 0, sizeof(int), st));
+    DP_CUDA_CHECK(cudaFuncSetAttribute(dp::encode_windows_v2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
+    dp::encode_windows_v2_kernel<<<n_windows, dp::V2_THREADS, smem2, st>>>(a, fb, fb + 64);
+    DP_CUDA_CHECK(cudaGetLastError());
+    dp::encode_windows_kernel<<<n_windows, dp::ENC_THREADS, smem, st>>>(a, fb, fb + 64);
     DP_CUDA_CHECK(cudaGetLastError());
     return DP_OK;
 }

@@ -8,6 +8,8 @@
 //   warp 2    TMEM allocator (512 columns = two accumulator stages)
 //   warps 4-7 epilogue:     tcgen05.ld their 32 accumulator rows, apply the epilogue, store to HBM, release
 //                           the accumulator stage
+#include <stdlib.h>
+
 #include "tc_gemm.cuh"
 
 namespace dp {
@@ -294,6 +296,20 @@ __device__ __forceinline__ float tanh_acc(float x) {
     return 1.f - __fdividef(2.f, e + 1.f);
 }
 
+// MUFU.TANH: ~2^-11 relative error -- below the bf16 operand rounding of the one-pass mode, not used in split mode
+__device__ __forceinline__ float tanh_fast(float x) {
+    float y;
+    asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+template <bool FAST>
+__device__ __forceinline__ float act_sigmoid(float x) {
+    if (FAST) return fmaf(0.5f, tanh_fast(0.5f * x), 0.5f);
+    return sigmoid_acc(x);
+}
+template <bool FAST>
+__device__ __forceinline__ float act_tanh(float x) { return FAST ? tanh_fast(x) : tanh_acc(x); }
+
 __device__ __forceinline__ void store_bf16x16(__nv_bfloat16 *dst, const float (&f)[16]) {
     uint32_t p[8];
 #pragma unroll
@@ -314,7 +330,10 @@ __device__ __forceinline__ void load_f32x16(const float *src, float (&f)[16]) {
     for (int i = 0; i < 4; i++) { const float4 t = p[i]; f[4 * i] = t.x; f[4 * i + 1] = t.y; f[4 * i + 2] = t.z; f[4 * i + 3] = t.w; }
 }
 
-__global__ void __launch_bounds__(TC_THREADS, 1)
+constexpr int GRU_THREADS = 384;                    // warps 0-3 as in the GEMM, warps 4-11 epilogue (two per TMEM lane quarter)
+
+template <bool FAST_ACT>
+__global__ void __launch_bounds__(GRU_THREADS, 1)
 gru_step_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1,
                 const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmA3,
                 const __grid_constant__ CUtensorMap tmB, const GruArgs g) {
@@ -338,7 +357,7 @@ gru_step_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
     }
     if (warp == 1 && lane == 0) {
         for (int s = 0; s < STAGES; s++) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
-        for (int s = 0; s < 2; s++) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), 4); }
+        for (int s = 0; s < 2; s++) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), 8); }
         fence_barrier_init();
     }
     if (warp == 2) { tmem_alloc(tmem_slot, 512); tmem_relinquish(); }
@@ -396,6 +415,10 @@ gru_step_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
                         for (int k = 0; k < BK / 16; k++)
                             umma_bf16(d_tmem, da + 2u * k, db + 2u * k, idesc192, acc_nx | (uint32_t)k);
                         acc_rz = 1; acc_nx = 1;
+                    } else if (g.debug == 2) {
+#pragma unroll
+                        for (int k = 0; k < BK / 16; k++)
+                            umma_bf16(d_tmem, da + 2u * k, db + 2u * k, idesc192, 1u);
                     } else {
 #pragma unroll
                         for (int k = 0; k < BK / 16; k++) {
@@ -412,7 +435,9 @@ gru_step_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
             }
         }
     } else if (warp >= 4) {
-        const int wq = warp - 4;
+        // 8 epilogue warps: warp w reads TMEM lanes 32*(w%4).. (hardware lane-quarter rule) and handles unit groups
+        // cb = 2*half, 2*half+1 of the tile's 64 hidden units, half = (w-4)/4.
+        const int wq = warp & 3, half = (warp - 4) >> 2;
         int as = 0; uint32_t aphase = 0;
         for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
             const int pi = tile / tiles_per_prob, rem = tile % tiles_per_prob;
@@ -422,11 +447,24 @@ gru_step_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
             const bool row_ok = m < g.M;
             bool has_h = false;
             for (int kc = 0; kc < P.n_chunks; kc++) has_h |= ((P.chunks[kc].a_src >> 8) & 0xff) != 0;
+            // everything that does not depend on the accumulator is fetched BEFORE waiting for the MMAs
+            float hp[2][16];
+#pragma unroll
+            for (int c2 = 0; c2 < 2; c2++) {
+                const long long ro = (long long)m * GRU_HP + ub * GRU_UB + (half * 2 + c2) * 16;
+                if (P.h_prev && row_ok) load_f32x16(P.h_prev + ro, hp[c2]);
+                else {
+#pragma unroll
+                    for (int i = 0; i < 16; i++) hp[c2][i] = 0.f;
+                }
+            }
             mbar_wait(tfull_bar(as), aphase);
             tc_fence_after();
             const uint32_t taddr = tmem_base + as * 256 + ((uint32_t)(wq * 32) << 16);
-#pragma unroll 1
-            for (int cb = 0; cb < GRU_UB / 16; cb++) {
+#pragma unroll
+            for (int c2 = 0; c2 < 2; c2++) {
+                if (g.debug == 1) break;
+                const int cb = half * 2 + c2;
                 const int u = ub * GRU_UB + cb * 16;              // first hidden unit of this group
                 uint32_t vr[16], vz[16], vx[16], vh[16];
                 tmem_ld16(taddr + cb * 16, vr);
@@ -436,22 +474,16 @@ gru_step_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
                 tmem_ld_wait();
                 if (!row_ok) continue;
                 const long long ro = (long long)m * GRU_HP + u;
-                float hp[16];
-                if (P.h_prev) load_f32x16(P.h_prev + ro, hp);
-                else {
-#pragma unroll
-                    for (int i = 0; i < 16; i++) hp[i] = 0.f;
-                }
                 float hn[16];
 #pragma unroll
                 for (int i = 0; i < 16; i++) {
                     const float br = __ldg(P.bias + u + i), bz = __ldg(P.bias + GRU_HP + u + i);
                     const float bin = __ldg(P.bias + 2 * GRU_HP + u + i), bhn = __ldg(P.bias + 3 * GRU_HP + u + i);
-                    const float r = sigmoid_acc(__uint_as_float(vr[i]) + br);
-                    const float z = sigmoid_acc(__uint_as_float(vz[i]) + bz);
+                    const float r = act_sigmoid<FAST_ACT>(__uint_as_float(vr[i]) + br);
+                    const float z = act_sigmoid<FAST_ACT>(__uint_as_float(vz[i]) + bz);
                     const float hh = (has_h ? __uint_as_float(vh[i]) : 0.f) + bhn;
-                    const float nn = tanh_acc(__uint_as_float(vx[i]) + bin + r * hh);
-                    hn[i] = (1.f - z) * nn + z * hp[i];
+                    const float nn = act_tanh<FAST_ACT>(__uint_as_float(vx[i]) + bin + r * hh);
+                    hn[i] = fmaf(z, hp[c2][i] - nn, nn);          // (1-z)*n + z*h
                 }
                 {
                     float4 *op = reinterpret_cast<float4 *>(P.h_out + ro);
@@ -472,7 +504,7 @@ gru_step_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
                     float pt[16];
                     load_f32x16(P.partner2 + ro, pt);
 #pragma unroll
-                    for (int i = 0; i < 16; i++) pt[i] += hp[i];
+                    for (int i = 0; i < 16; i++) pt[i] += hp[c2][i];
                     store_bf16x16(P.xsum2 + ro, pt);
                     if (P.xsum2_lo) store_bf16x16_lo(P.xsum2_lo + ro, pt);
                 }
@@ -488,18 +520,24 @@ gru_step_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
     if (warp == 2) { tc_fence_after(); tmem_dealloc(tmem_base, 512); }
 }
 
-int launch_gru_step(const CUtensorMap *tmA, const CUtensorMap *tmB, const GruArgs &g, cudaStream_t st) {
+int launch_gru_step(const CUtensorMap *tmA, const CUtensorMap *tmB, const GruArgs &g_in, cudaStream_t st) {
     static bool attr_done[64] = {false};
     int dev = 0;
     DP_CUDA_CHECK(cudaGetDevice(&dev));
     if (dev >= 64 || !attr_done[dev]) {
-        DP_CUDA_CHECK(cudaFuncSetAttribute(gru_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, GRU_SMEM_BYTES));
+        DP_CUDA_CHECK(cudaFuncSetAttribute(gru_step_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, GRU_SMEM_BYTES));
+        DP_CUDA_CHECK(cudaFuncSetAttribute(gru_step_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, GRU_SMEM_BYTES));
         if (dev < 64) attr_done[dev] = true;
     }
+    static int dbg = -1;
+    if (dbg < 0) { const char *e = getenv("DP_GRU_DEBUG"); dbg = e ? atoi(e) : 0; }
+    GruArgs g = g_in;
+    g.debug = dbg;
     const int n_tiles = g.tiles_m * GRU_NUB * g.n_prob;
     if (n_tiles <= 0) return DP_OK;
     const int grid = n_tiles < device_sm_count() ? n_tiles : device_sm_count();
-    gru_step_kernel<<<grid, TC_THREADS, GRU_SMEM_BYTES, st>>>(tmA[0], tmA[1], tmA[2], tmA[3], *tmB, g);
+    if (g.fast_act) gru_step_kernel<true><<<grid, GRU_THREADS, GRU_SMEM_BYTES, st>>>(tmA[0], tmA[1], tmA[2], tmA[3], *tmB, g);
+    else gru_step_kernel<false><<<grid, GRU_THREADS, GRU_SMEM_BYTES, st>>>(tmA[0], tmA[1], tmA[2], tmA[3], *tmB, g);
     DP_CUDA_CHECK(cudaGetLastError());
     return DP_OK;
 }

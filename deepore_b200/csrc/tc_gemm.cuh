@@ -63,6 +63,8 @@ struct GruArgs {
     int n_prob;
     int M;
     int tiles_m;                       // per problem: tiles_m * 8 unit blocks
+    int debug;                         // timing experiments only (env DP_GRU_DEBUG): 1 skip epilogue math, 2 one MMA per k-step
+    int fast_act;                      // 1: MUFU.TANH activations (one-pass bf16 mode); 0: exp-based (split-bf16 mode)
 };
 
 int launch_gemm_bf16(const CUtensorMap *tmA /*[4]*/, const CUtensorMap *tmB, const GemmArgs &g, int block_n,
