@@ -61,7 +61,8 @@ struct Model {
     int fold_tab_off = 0, fold_tab_n = 0;
     int gru_tab_off[3][3][2], gru_tab_n[3][3][2];
     long long kcols_fold = 0, kcols_gru = 0;
-    CUtensorMap tm_img, tm_arena, tm_arena_lo, tm_wfold, tm_wgru;
+    CUtensorMap tm_img, tm_arena, tm_arena_lo, tm_wfold, tm_wgru, tm_wgru128, tm_wgru64;
+    int gru_2cta = 1;              // CTA-pair GRU kernel (env DP_GRU=1cta selects the single-CTA kernel)
     // optional per-kernel timing (bench.py roofline): one event per launch boundary, harvested by dp_model_profile_read
     int profile = 0;
     std::vector<cudaEvent_t> prof_events;      // PROF_MARKS events per profiled forward call
@@ -116,17 +117,28 @@ __global__ void __launch_bounds__(256) fc1_argmax_kernel(const float *__restrict
     if (wid >= n_rows * seq_len) return;
     const long long m = wid / seq_len;
     const int t = (int)(wid % seq_len);
-    const float *pf = hf + t * slot_stride + m * HP;
-    const float *pb = hb + t * slot_stride + m * HP;
+    // fp32 states live in the blocked layout of gru_state_off (tc_gemm.cu): lane handles unit groups 4*(lane+32j)
+    const float *pf = hf + t * slot_stride, *pb = hb + t * slot_stride;
     float x[HP / 32];
 #pragma unroll
-    for (int i = 0; i < HP / 32; i++) x[i] = pf[lane + 32 * i] + pb[lane + 32 * i];
+    for (int j = 0; j < HP / 128; j++) {
+        const int u = 4 * (lane + 32 * j);
+        const long long mb = m >> 7;
+        const int r = (int)(m & 127), ub = u >> 6, cb = (u >> 4) & 3, k = (u >> 2) & 3;
+        const long long off = ((((mb * 8 + ub) * 4 + cb) * 4 + k) * 128 + r) * 4;
+        const float4 a = *reinterpret_cast<const float4 *>(pf + off), b4 = *reinterpret_cast<const float4 *>(pb + off);
+        x[4 * j] = a.x + b4.x; x[4 * j + 1] = a.y + b4.y; x[4 * j + 2] = a.z + b4.z; x[4 * j + 3] = a.w + b4.w;
+    }
     float best = 0.f;
     int besti = 0;
     for (int c = 0; c < n_class; c++) {
         float acc = 0.f;
 #pragma unroll
-        for (int i = 0; i < HP / 32; i++) acc = fmaf(x[i], __ldg(w + c * HP + lane + 32 * i), acc);
+        for (int j = 0; j < HP / 128; j++) {
+            const float4 wv = __ldg(reinterpret_cast<const float4 *>(w + c * HP + 4 * (lane + 32 * j)));
+            acc = fmaf(x[4 * j], wv.x, acc); acc = fmaf(x[4 * j + 1], wv.y, acc);
+            acc = fmaf(x[4 * j + 2], wv.z, acc); acc = fmaf(x[4 * j + 3], wv.w, acc);
+        }
 #pragma unroll
         for (int d = 16; d > 0; d >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, d);
         acc += __ldg(b + c);
@@ -314,6 +326,14 @@ static int build_model(Model *m, const dp_model_weights *w) {
     if (rc) return rc;
     rc = make_tmap_bf16_2d(&m->tm_wgru, m->w_gru, (uint64_t)m->n_layers * 2 * 3 * HP, (uint64_t)m->kcols_gru,
                            (uint64_t)m->kcols_gru * 2, 192);
+    if (rc) return rc;
+    rc = make_tmap_bf16_2d(&m->tm_wgru128, m->w_gru, (uint64_t)m->n_layers * 2 * 3 * HP, (uint64_t)m->kcols_gru,
+                           (uint64_t)m->kcols_gru * 2, 128);
+    if (rc) return rc;
+    rc = make_tmap_bf16_2d(&m->tm_wgru64, m->w_gru, (uint64_t)m->n_layers * 2 * 3 * HP, (uint64_t)m->kcols_gru,
+                           (uint64_t)m->kcols_gru * 2, 64);
+    const char *e = getenv("DP_GRU");
+    m->gru_2cta = (e && !strcmp(e, "1cta")) ? 0 : 1;
     return rc;
 }
 
@@ -401,7 +421,8 @@ static int forward_rows(Model *m, const uint8_t *img, long long n_rows, float *l
                     }
                 }
             }
-            int rc = launch_gru_step(tmA, &m->tm_wgru, g, st);
+            int rc = m->gru_2cta ? launch_gru_step2(tmA, &m->tm_wgru128, &m->tm_wgru64, g, st)
+                                 : launch_gru_step(tmA, &m->tm_wgru, g, st);
             if (rc) return rc;
             mark();
         }
@@ -507,7 +528,15 @@ int dp_model_peek(dp_model *h, int32_t what, int64_t n_rows, float *host_out) {
     const int k = what / 100, d = (what / 10) % 10, t = what % 10;
     DP_REQUIRE(what >= 100 && k >= 1 && k <= m->n_layers && d < 2 && t < 3, "unknown peek id");
     const int slot = d == 0 ? dp::f32_slot_hf(k - 1, t) : dp::f32_slot_hb(k - 1, t);
-    DP_CUDA_CHECK(cudaMemcpy(host_out, m->state + (size_t)slot * m->mcap * dp::HP, n * 4, cudaMemcpyDeviceToHost));
+    const size_t nb = (size_t)((n_rows + 127) / 128 * 128) * dp::HP;
+    std::vector<float> tmp(nb);
+    DP_CUDA_CHECK(cudaMemcpy(tmp.data(), m->state + (size_t)slot * m->mcap * dp::HP, nb * 4, cudaMemcpyDeviceToHost));
+    for (long long r = 0; r < n_rows; r++)
+        for (int u = 0; u < dp::HP; u++) {
+            const long long mb = r >> 7;
+            const int rr = (int)(r & 127), ub = u >> 6, cb = (u >> 4) & 3, k = (u >> 2) & 3, e = u & 3;
+            host_out[(size_t)r * dp::HP + u] = tmp[(size_t)(((((mb * 8 + ub) * 4 + cb) * 4 + k) * 128 + rr) * 4 + e)];
+        }
     return DP_OK;
 }
 

@@ -330,6 +330,99 @@ __device__ __forceinline__ void load_f32x16(const float *src, float (&f)[16]) {
     for (int i = 0; i < 4; i++) { const float4 t = p[i]; f[4 * i] = t.x; f[4 * i + 1] = t.y; f[4 * i + 2] = t.z; f[4 * i + 3] = t.w; }
 }
 
+
+// ---- GRU epilogue, shared by the 1-CTA and the CTA-pair kernel ----------------------------------------------------
+// fp32 state layout (private to these kernels, fc1_argmax_kernel and dp_model_peek): BLOCKED so that one warp
+// instruction moves 512 contiguous bytes.  Row m, unit u -> mb = m/128, r = m%128, ub = u/64, cb = (u/16)%4,
+// k = (u/4)%4, e = u%4:   offset = ((((mb*8 + ub)*4 + cb)*4 + k)*128 + r)*4 + e.
+// (Thread = accumulator row holds 16 consecutive units = 4 float4; the k-th float4 of 32 consecutive rows is contiguous.)
+__host__ __device__ __forceinline__ long long gru_state_off(long long m, int u) {
+    const long long mb = m >> 7;
+    const int r = (int)(m & 127), ub = u >> 6, cb = (u >> 4) & 3, k = (u >> 2) & 3, e = u & 3;
+    return ((((mb * 8 + ub) * 4 + cb) * 4 + k) * 128 + r) * 4 + e;
+}
+__device__ __forceinline__ void state_load16(const float *base, long long m, int u0, float (&f)[16]) {
+    const float4 *p = reinterpret_cast<const float4 *>(base + gru_state_off(m, u0));
+#pragma unroll
+    for (int k = 0; k < 4; k++) { const float4 t = p[k * 128]; f[4 * k] = t.x; f[4 * k + 1] = t.y; f[4 * k + 2] = t.z; f[4 * k + 3] = t.w; }
+}
+__device__ __forceinline__ void state_store16(float *base, long long m, int u0, const float (&f)[16]) {
+    float4 *p = reinterpret_cast<float4 *>(base + gru_state_off(m, u0));
+#pragma unroll
+    for (int k = 0; k < 4; k++) p[k * 128] = make_float4(f[4 * k], f[4 * k + 1], f[4 * k + 2], f[4 * k + 3]);
+}
+// bf16 row-major [row][512] store of 16 units per row for the warp's 32 rows, full 32-byte sectors per instruction:
+// lanes 2j / 2j+1 write the two halves of row j's 32 bytes (values fetched from lane j by shuffle).  All 32 lanes call.
+__device__ __forceinline__ void rows_store_bf16(__nv_bfloat16 *base, long long m_warp0, int u0, const float (&f)[16], int M,
+                                                int lane, bool lo_part) {
+    uint32_t p[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+        float a = f[2 * i], b = f[2 * i + 1];
+        if (lo_part) { a -= bf16_round(a); b -= bf16_round(b); }
+        p[i] = pack_bf16(a, b);
+    }
+#pragma unroll
+    for (int h2 = 0; h2 < 2; h2++) {
+        const int src = h2 * 16 + (lane >> 1);
+        uint32_t v[4];
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            const uint32_t a = __shfl_sync(0xffffffffu, p[i], src), b = __shfl_sync(0xffffffffu, p[4 + i], src);
+            v[i] = (lane & 1) ? b : a;
+        }
+        const long long row = m_warp0 + src;
+        if (row < M) *reinterpret_cast<uint4 *>(base + row * GRU_HP + u0 + (lane & 1) * 8) = make_uint4(v[0], v[1], v[2], v[3]);
+    }
+}
+
+// Gate math + state update + stores for one group of 16 hidden units of the warp's 32 rows.
+template <bool FAST_ACT>
+__device__ __forceinline__ void gru_finish16(const GruProblem &P, int M, long long m_warp0, int lane, int u0,
+                                             const uint32_t (&vr)[16], const uint32_t (&vz)[16], const uint32_t (&vx)[16],
+                                             const uint32_t (&vh)[16], bool has_h, const float (&hp)[16]) {
+    const long long m = m_warp0 + lane;
+    const bool row_ok = m < M;
+    float hn[16];
+#pragma unroll
+    for (int i = 0; i < 16; i++) {
+        const float br = __ldg(P.bias + u0 + i), bz = __ldg(P.bias + GRU_HP + u0 + i);
+        const float bin = __ldg(P.bias + 2 * GRU_HP + u0 + i), bhn = __ldg(P.bias + 3 * GRU_HP + u0 + i);
+        const float r = act_sigmoid<FAST_ACT>(__uint_as_float(vr[i]) + br);
+        const float z = act_sigmoid<FAST_ACT>(__uint_as_float(vz[i]) + bz);
+        const float hh = (has_h ? __uint_as_float(vh[i]) : 0.f) + bhn;
+        const float nn = act_tanh<FAST_ACT>(__uint_as_float(vx[i]) + bin + r * hh);
+        hn[i] = fmaf(z, hp[i] - nn, nn);                  // (1-z)*n + z*h
+    }
+    if (row_ok) state_store16(P.h_out, m, u0, hn);
+    if (P.h_out_bf) rows_store_bf16(P.h_out_bf, m_warp0, u0, hn, M, lane, false);
+    if (P.h_out_lo) rows_store_bf16(P.h_out_lo, m_warp0, u0, hn, M, lane, true);
+    if (P.partner) {                                       // sum of directions (model.py:131-133)
+        float pt[16];
+        if (row_ok) state_load16(P.partner, m, u0, pt);
+        else {
+#pragma unroll
+            for (int i = 0; i < 16; i++) pt[i] = 0.f;
+        }
+#pragma unroll
+        for (int i = 0; i < 16; i++) pt[i] += hn[i];
+        rows_store_bf16(P.xsum, m_warp0, u0, pt, M, lane, false);
+        if (P.xsum_lo) rows_store_bf16(P.xsum_lo, m_warp0, u0, pt, M, lane, true);
+    }
+    if (P.partner2) {
+        float pt[16];
+        if (row_ok) state_load16(P.partner2, m, u0, pt);
+        else {
+#pragma unroll
+            for (int i = 0; i < 16; i++) pt[i] = 0.f;
+        }
+#pragma unroll
+        for (int i = 0; i < 16; i++) pt[i] += hp[i];
+        rows_store_bf16(P.xsum2, m_warp0, u0, pt, M, lane, false);
+        if (P.xsum2_lo) rows_store_bf16(P.xsum2_lo, m_warp0, u0, pt, M, lane, true);
+    }
+}
+
 constexpr int GRU_THREADS = 384;                    // warps 0-3 as in the GEMM, warps 4-11 epilogue (two per TMEM lane quarter)
 
 template <bool FAST_ACT>
@@ -443,16 +536,15 @@ gru_step_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
             const int pi = tile / tiles_per_prob, rem = tile % tiles_per_prob;
             const GruProblem &P = g.prob[pi];
             const int m0 = (rem / GRU_NUB) * BM, ub = rem % GRU_NUB;
-            const int m = m0 + wq * 32 + lane;
-            const bool row_ok = m < g.M;
+            const long long m_warp0 = m0 + wq * 32;
+            const long long m = m_warp0 + lane;
             bool has_h = false;
             for (int kc = 0; kc < P.n_chunks; kc++) has_h |= ((P.chunks[kc].a_src >> 8) & 0xff) != 0;
             // everything that does not depend on the accumulator is fetched BEFORE waiting for the MMAs
             float hp[2][16];
 #pragma unroll
             for (int c2 = 0; c2 < 2; c2++) {
-                const long long ro = (long long)m * GRU_HP + ub * GRU_UB + (half * 2 + c2) * 16;
-                if (P.h_prev && row_ok) load_f32x16(P.h_prev + ro, hp[c2]);
+                if (P.h_prev && m < g.M && g.debug != 5) state_load16(P.h_prev, m, ub * GRU_UB + (half * 2 + c2) * 16, hp[c2]);
                 else {
 #pragma unroll
                     for (int i = 0; i < 16; i++) hp[c2][i] = 0.f;
@@ -465,49 +557,13 @@ gru_step_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
             for (int c2 = 0; c2 < 2; c2++) {
                 if (g.debug == 1) break;
                 const int cb = half * 2 + c2;
-                const int u = ub * GRU_UB + cb * 16;              // first hidden unit of this group
                 uint32_t vr[16], vz[16], vx[16], vh[16];
                 tmem_ld16(taddr + cb * 16, vr);
                 tmem_ld16(taddr + 64 + cb * 16, vz);
                 tmem_ld16(taddr + 128 + cb * 16, vx);
                 if (has_h) tmem_ld16(taddr + 192 + cb * 16, vh);
                 tmem_ld_wait();
-                if (!row_ok) continue;
-                const long long ro = (long long)m * GRU_HP + u;
-                float hn[16];
-#pragma unroll
-                for (int i = 0; i < 16; i++) {
-                    const float br = __ldg(P.bias + u + i), bz = __ldg(P.bias + GRU_HP + u + i);
-                    const float bin = __ldg(P.bias + 2 * GRU_HP + u + i), bhn = __ldg(P.bias + 3 * GRU_HP + u + i);
-                    const float r = act_sigmoid<FAST_ACT>(__uint_as_float(vr[i]) + br);
-                    const float z = act_sigmoid<FAST_ACT>(__uint_as_float(vz[i]) + bz);
-                    const float hh = (has_h ? __uint_as_float(vh[i]) : 0.f) + bhn;
-                    const float nn = act_tanh<FAST_ACT>(__uint_as_float(vx[i]) + bin + r * hh);
-                    hn[i] = fmaf(z, hp[c2][i] - nn, nn);          // (1-z)*n + z*h
-                }
-                {
-                    float4 *op = reinterpret_cast<float4 *>(P.h_out + ro);
-#pragma unroll
-                    for (int i = 0; i < 4; i++) op[i] = make_float4(hn[4 * i], hn[4 * i + 1], hn[4 * i + 2], hn[4 * i + 3]);
-                }
-                if (P.h_out_bf) store_bf16x16(P.h_out_bf + ro, hn);
-                if (P.h_out_lo) store_bf16x16_lo(P.h_out_lo + ro, hn);
-                if (P.partner) {
-                    float pt[16];
-                    load_f32x16(P.partner + ro, pt);
-#pragma unroll
-                    for (int i = 0; i < 16; i++) pt[i] += hn[i];
-                    store_bf16x16(P.xsum + ro, pt);
-                    if (P.xsum_lo) store_bf16x16_lo(P.xsum_lo + ro, pt);
-                }
-                if (P.partner2) {
-                    float pt[16];
-                    load_f32x16(P.partner2 + ro, pt);
-#pragma unroll
-                    for (int i = 0; i < 16; i++) pt[i] += hp[c2][i];
-                    store_bf16x16(P.xsum2 + ro, pt);
-                    if (P.xsum2_lo) store_bf16x16_lo(P.xsum2_lo + ro, pt);
-                }
+                gru_finish16<FAST_ACT>(P, g.M, m_warp0, lane, ub * GRU_UB + cb * 16, vr, vz, vx, vh, has_h, hp[c2]);
             }
             tc_fence_before();
             __syncwarp();
@@ -518,6 +574,200 @@ gru_step_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
     tc_fence_before();
     __syncthreads();
     if (warp == 2) { tc_fence_after(); tmem_dealloc(tmem_base, 512); }
+}
+
+// ================================================================================================
+// GRU time step on CTA PAIRS (cta_group::2).  The single-CTA kernel above is shared-memory-bandwidth bound: every
+// 128x192x16 MMA reads 10 KB of operands while TMA writes the next stage into the same shared memory.  Here a cluster
+// of two CTAs computes a 256-row x 64-unit tile with ONE M=256, N=256 instruction per 16-wide k step:
+//   * each CTA stages its own 128 rows of A and only HALF of the B rows, so shared-memory traffic per FLOP halves;
+//   * the weight tile is presented as 256 logical rows so that input and hidden chunks both need a single MMA:
+//       input chunk  [W_ir | W_iz | W_in |  0  ]   hidden chunk  [W_hr | W_hz |  0  | W_hn]
+//     CTA 0 supplies logical rows 0..127 (r,z), CTA 1 rows 128..255: its 64 real rows always sit in the middle of a
+//     192-row region whose outer thirds are zeroed once, and the descriptor starts at row 64 (input) or 0 (hidden).
+//     The zero quarter costs 25 % of the tensor-pipe time, far less than the second MMA + second A read it replaces;
+//   * accumulator columns per CTA: [r 64 | z 64 | W_in x 64 | W_hn h 64], so the epilogue is that of the 1-CTA kernel.
+// Barriers: `full` (leader only; both CTAs' TMA bytes are credited to it), `empty` / `tmem_full` (per CTA, released by
+// the leader's multicast tcgen05.commit), `tmem_empty` (leader, 16 arrivals: 8 epilogue warps of each CTA).
+constexpr int GRU2_STAGE_BYTES = A_STAGE_BYTES + GRU_B_STAGE_BYTES;   // 16 KB A + 24 KB B region (192 rows)
+constexpr int GRU2_STAGES = 5;
+constexpr int GRU2_SMEM_BYTES = GRU2_STAGES * GRU2_STAGE_BYTES + 1024 + 256;
+constexpr uint32_t GRU2_TX_BYTES = 2 * A_STAGE_BYTES + 128 * 128 + 64 * 128;   // both A tiles + 128 + 64 weight rows
+
+template <bool FAST_ACT>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GRU_THREADS, 1)
+gru_step2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1,
+                 const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmA3,
+                 const __grid_constant__ CUtensorMap tmB128, const __grid_constant__ CUtensorMap tmB64, const GruArgs g) {
+    constexpr int STAGES = GRU2_STAGES;
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    const uint32_t bar_base = smem_base + STAGES * GRU2_STAGE_BYTES;
+    auto full_bar = [&](int s) { return bar_base + 8u * s; };
+    auto empty_bar = [&](int s) { return bar_base + 8u * (STAGES + s); };
+    auto tfull_bar = [&](int s) { return bar_base + 8u * (2 * STAGES + s); };
+    auto tempty_bar = [&](int s) { return bar_base + 8u * (2 * STAGES + 2 + s); };
+    const uint32_t tmem_slot = bar_base + 8u * (2 * STAGES + 4);
+    uint8_t *smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));          // generic pointer to the aligned base
+    uint32_t *tmem_slot_ptr = reinterpret_cast<uint32_t *>(smem_gen + (tmem_slot - smem_base));
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t rank = cluster_ctarank();
+    const int pair = blockIdx.x >> 1, n_pairs = gridDim.x >> 1;
+    const int tiles_per_prob = g.tiles_m * GRU_NUB;                           // tiles_m counts 256-row blocks here
+    const int n_tiles = tiles_per_prob * g.n_prob;
+
+    if (warp == 0 && lane == 0) {
+        prefetch_tmap(&tmA0); prefetch_tmap(&tmA1); prefetch_tmap(&tmA2); prefetch_tmap(&tmA3);
+        prefetch_tmap(&tmB128); prefetch_tmap(&tmB64);
+    }
+    if (warp == 1 && lane == 0) {
+        for (int s = 0; s < STAGES; s++) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
+        for (int s = 0; s < 2; s++) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), 16); }
+        fence_barrier_init();
+    }
+    if (warp == 2) { tmem_alloc_2sm(tmem_slot, 512); tmem_relinquish_2sm(); }
+    if (rank == 1) {
+        // zero the outer thirds (rows 0..63 and 128..191) of every stage's weight region, once
+        for (int s = 0; s < STAGES; s++) {
+            uint4 *b = reinterpret_cast<uint4 *>(smem_gen + s * GRU2_STAGE_BYTES + A_STAGE_BYTES);
+            for (int i = threadIdx.x; i < 64 * 128 / 16; i += GRU_THREADS) {
+                b[i] = make_uint4(0u, 0u, 0u, 0u);
+                b[128 * 128 / 16 + i] = make_uint4(0u, 0u, 0u, 0u);
+            }
+        }
+        fence_proxy_async_smem();
+    }
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot_ptr;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            PipeState ps{0, 0};
+            for (int tile = pair; tile < n_tiles; tile += n_pairs) {
+                const int pi = tile / tiles_per_prob, rem = tile % tiles_per_prob;
+                const GruProblem &P = g.prob[pi];
+                const int m0 = (rem / GRU_NUB) * 256 + (int)rank * BM, ub = rem % GRU_NUB;
+                const int brow = P.b_row_base + ub * GRU_BROWS;
+                for (int kc = 0; kc < P.n_chunks; kc++) {
+                    const KChunk c = P.chunks[kc];
+                    const int src = c.a_src & 0xff, kind = (c.a_src >> 8) & 0xff;
+                    const CUtensorMap *ma = src == 0 ? &tmA0 : src == 1 ? &tmA1 : src == 2 ? &tmA2 : &tmA3;
+                    mbar_wait(empty_bar(ps.stage), ps.phase ^ 1u);
+                    if (rank == 0) mbar_expect_tx(full_bar(ps.stage), GRU2_TX_BYTES);
+                    const uint32_t sa = smem_base + ps.stage * GRU2_STAGE_BYTES;
+                    const uint32_t sb = sa + A_STAGE_BYTES;
+                    tma_load_2d_2sm(sa, ma, full_bar(ps.stage), c.a_col, m0 + c.a_drow);
+                    if (rank == 0) tma_load_2d_2sm(sb + (kind == 0 ? 64u * 128u : 0u), &tmB128, full_bar(ps.stage), c.b_col, brow);
+                    else tma_load_2d_2sm(sb + 64u * 128u, &tmB64, full_bar(ps.stage), c.b_col, brow + 128);
+                    ps.advance(STAGES);
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0 && rank == 0) {
+            constexpr uint32_t idesc = make_idesc_bf16(256, 256);
+            PipeState ps{0, 0};
+            int as = 0; uint32_t aphase = 0;
+            for (int tile = pair; tile < n_tiles; tile += n_pairs) {
+                const GruProblem &P = g.prob[tile / tiles_per_prob];
+                mbar_wait(tempty_bar(as), aphase ^ 1u);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + as * 256;
+                for (int kc = 0; kc < P.n_chunks; kc++) {
+                    const int kind = (P.chunks[kc].a_src >> 8) & 0xff;
+                    mbar_wait(full_bar(ps.stage), ps.phase);
+                    tc_fence_after();
+                    const uint32_t sa = smem_base + ps.stage * GRU2_STAGE_BYTES;
+                    const uint64_t da = make_smem_desc_sw128(sa);
+                    const uint64_t db = make_smem_desc_sw128(sa + A_STAGE_BYTES + (kind == 0 ? 64u * 128u : 0u));
+#pragma unroll
+                    for (int k = 0; k < BK / 16; k++)
+                        umma_bf16_2sm(d_tmem, da + 2u * k, db + 2u * k, idesc, (uint32_t)(kc | k));
+                    umma_commit_mc(empty_bar(ps.stage), 3);
+                    ps.advance(STAGES);
+                }
+                umma_commit_mc(tfull_bar(as), 3);
+                if (++as == 2) { as = 0; aphase ^= 1u; }
+            }
+        }
+    } else if (warp >= 4) {
+        // 8 epilogue warps: warp w reads TMEM lanes 32*(w%4).. (hardware lane-quarter rule) and handles unit groups
+        // cb = 2*half, 2*half+1 of the tile's 64 hidden units, half = (w-4)/4.
+        const int wq = warp & 3, half = (warp - 4) >> 2;
+        int as = 0; uint32_t aphase = 0;
+        for (int tile = pair; tile < n_tiles; tile += n_pairs) {
+            const int pi = tile / tiles_per_prob, rem = tile % tiles_per_prob;
+            const GruProblem &P = g.prob[pi];
+            const int m0 = (rem / GRU_NUB) * 256 + (int)rank * BM, ub = rem % GRU_NUB;
+            const long long m_warp0 = m0 + wq * 32;
+            const long long m = m_warp0 + lane;
+            const bool has_h = true;
+            // everything that does not depend on the accumulator is fetched BEFORE waiting for the MMAs
+            float hp[2][16];
+#pragma unroll
+            for (int c2 = 0; c2 < 2; c2++) {
+                if (P.h_prev && m < g.M && g.debug != 5) state_load16(P.h_prev, m, ub * GRU_UB + (half * 2 + c2) * 16, hp[c2]);
+                else {
+#pragma unroll
+                    for (int i = 0; i < 16; i++) hp[c2][i] = 0.f;
+                }
+            }
+            mbar_wait(tfull_bar(as), aphase);
+            tc_fence_after();
+            const uint32_t taddr = tmem_base + as * 256 + ((uint32_t)(wq * 32) << 16);
+#pragma unroll
+            for (int c2 = 0; c2 < 2; c2++) {
+                if (g.debug == 1) break;
+                const int cb = half * 2 + c2;
+                uint32_t vr[16], vz[16], vx[16], vh[16];
+                tmem_ld16(taddr + cb * 16, vr);
+                tmem_ld16(taddr + 64 + cb * 16, vz);
+                tmem_ld16(taddr + 128 + cb * 16, vx);
+                if (has_h) tmem_ld16(taddr + 192 + cb * 16, vh);
+                tmem_ld_wait();
+                gru_finish16<FAST_ACT>(P, g.M, m_warp0, lane, ub * GRU_UB + cb * 16, vr, vz, vx, vh, has_h, hp[c2]);
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_cluster(tempty_bar(as), 0);
+            if (++as == 2) { as = 0; aphase ^= 1u; }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();
+    if (warp == 2) { tc_fence_after(); tmem_dealloc_2sm(tmem_base, 512); }
+}
+
+int launch_gru_step2(const CUtensorMap *tmA, const CUtensorMap *tmB128, const CUtensorMap *tmB64, const GruArgs &g_in,
+                     cudaStream_t st) {
+    static bool attr_done[64] = {false};
+    int dev = 0;
+    DP_CUDA_CHECK(cudaGetDevice(&dev));
+    if (dev >= 64 || !attr_done[dev]) {
+        DP_CUDA_CHECK(cudaFuncSetAttribute(gru_step2_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, GRU2_SMEM_BYTES));
+        DP_CUDA_CHECK(cudaFuncSetAttribute(gru_step2_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, GRU2_SMEM_BYTES));
+        if (dev < 64) attr_done[dev] = true;
+    }
+    static int dbg = -1;
+    if (dbg < 0) { const char *e = getenv("DP_GRU_DEBUG"); dbg = e ? atoi(e) : 0; }
+    GruArgs g = g_in;
+    g.debug = dbg;
+    g.tiles_m = (g.M + 255) / 256;
+    const int n_tiles = g.tiles_m * GRU_NUB * g.n_prob;
+    if (n_tiles <= 0) return DP_OK;
+    const int max_pairs = device_sm_count() / 2;
+    const int pairs = n_tiles < max_pairs ? n_tiles : max_pairs;
+    if (g.fast_act)
+        gru_step2_kernel<true><<<2 * pairs, GRU_THREADS, GRU2_SMEM_BYTES, st>>>(tmA[0], tmA[1], tmA[2], tmA[3], *tmB128, *tmB64, g);
+    else
+        gru_step2_kernel<false><<<2 * pairs, GRU_THREADS, GRU2_SMEM_BYTES, st>>>(tmA[0], tmA[1], tmA[2], tmA[3], *tmB128, *tmB64, g);
+    DP_CUDA_CHECK(cudaGetLastError());
+    return DP_OK;
 }
 
 int launch_gru_step(const CUtensorMap *tmA, const CUtensorMap *tmB, const GruArgs &g_in, cudaStream_t st) {

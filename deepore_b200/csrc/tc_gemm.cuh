@@ -70,6 +70,9 @@ struct GruArgs {
 int launch_gemm_bf16(const CUtensorMap *tmA /*[4]*/, const CUtensorMap *tmB, const GemmArgs &g, int block_n,
                      cudaStream_t st);
 int launch_gru_step(const CUtensorMap *tmA /*[4]*/, const CUtensorMap *tmB, const GruArgs &g, cudaStream_t st);
+// CTA-pair (cta_group::2) version: tmB128 / tmB64 are maps of the same weight matrix with 128- and 64-row boxes
+int launch_gru_step2(const CUtensorMap *tmA /*[4]*/, const CUtensorMap *tmB128, const CUtensorMap *tmB64, const GruArgs &g,
+                     cudaStream_t st);
 int device_sm_count();
 
 }  // namespace dp

@@ -1,8 +1,9 @@
 #!/bin/bash
-# timing experiments on the GRU step kernel (results are WRONG under DP_GRU_DEBUG; timing only)
-for d in 0 1 2 3; do
-  echo "== DP_GRU_DEBUG=$d"
-  DP_GRU_DEBUG=$d timeout 200 python bench.py --steps 3 --warmup 3 --no-cpu-baseline 2>&1 | python -c "
+# timing experiments on the GRU step kernels (results are WRONG under DP_GRU_DEBUG != 0; timing only)
+for cfg in "2cta 0" "2cta 1" "1cta 0" "1cta 1"; do
+  set -- $cfg
+  echo "== DP_GRU=$1 DP_GRU_DEBUG=$2"
+  DP_GRU=$1 DP_GRU_DEBUG=$2 timeout 200 python bench.py --steps 3 --warmup 3 --no-cpu-baseline 2>&1 | python -c "
 import sys,json
 for ln in sys.stdin:
     if ln.startswith('{'):
