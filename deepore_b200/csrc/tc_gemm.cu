@@ -380,21 +380,27 @@ __device__ __forceinline__ void rows_store_bf16(__nv_bfloat16 *base, long long m
 template <bool FAST_ACT>
 __device__ __forceinline__ void gru_finish16(const GruProblem &P, int M, long long m_warp0, int lane, int u0,
                                              const uint32_t (&vr)[16], const uint32_t (&vz)[16], const uint32_t (&vx)[16],
-                                             const uint32_t (&vh)[16], bool has_h, const float (&hp)[16]) {
+                                             const uint32_t (&vh)[16], bool has_h, const float (&hp)[16], int dbg = 0) {
     const long long m = m_warp0 + lane;
     const bool row_ok = m < M;
     float hn[16];
 #pragma unroll
     for (int i = 0; i < 16; i++) {
-        const float br = __ldg(P.bias + u0 + i), bz = __ldg(P.bias + GRU_HP + u0 + i);
-        const float bin = __ldg(P.bias + 2 * GRU_HP + u0 + i), bhn = __ldg(P.bias + 3 * GRU_HP + u0 + i);
+        float br = 0.f, bz = 0.f, bin = 0.f, bhn = 0.f;
+        if (dbg != 9) {
+            br = __ldg(P.bias + u0 + i); bz = __ldg(P.bias + GRU_HP + u0 + i);
+            bin = __ldg(P.bias + 2 * GRU_HP + u0 + i); bhn = __ldg(P.bias + 3 * GRU_HP + u0 + i);
+        }
+        if (dbg == 8) { hn[i] = __uint_as_float(vr[i]) + __uint_as_float(vz[i]) + __uint_as_float(vx[i]) + br + bz + bin + bhn + hp[i]; continue; }
         const float r = act_sigmoid<FAST_ACT>(__uint_as_float(vr[i]) + br);
         const float z = act_sigmoid<FAST_ACT>(__uint_as_float(vz[i]) + bz);
         const float hh = (has_h ? __uint_as_float(vh[i]) : 0.f) + bhn;
         const float nn = act_tanh<FAST_ACT>(__uint_as_float(vx[i]) + bin + r * hh);
         hn[i] = fmaf(z, hp[i] - nn, nn);                  // (1-z)*n + z*h
     }
+    if (dbg == 6) { if (hn[3] == 123.456f) P.h_out[0] = hn[1]; return; }
     if (row_ok) state_store16(P.h_out, m, u0, hn);
+    if (dbg == 7) return;
     if (P.h_out_bf) rows_store_bf16(P.h_out_bf, m_warp0, u0, hn, M, lane, false);
     if (P.h_out_lo) rows_store_bf16(P.h_out_lo, m_warp0, u0, hn, M, lane, true);
     if (P.partner) {                                       // sum of directions (model.py:131-133)
@@ -563,7 +569,7 @@ gru_step_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
                 tmem_ld16(taddr + 128 + cb * 16, vx);
                 if (has_h) tmem_ld16(taddr + 192 + cb * 16, vh);
                 tmem_ld_wait();
-                gru_finish16<FAST_ACT>(P, g.M, m_warp0, lane, ub * GRU_UB + cb * 16, vr, vz, vx, vh, has_h, hp[c2]);
+                gru_finish16<FAST_ACT>(P, g.M, m_warp0, lane, ub * GRU_UB + cb * 16, vr, vz, vx, vh, has_h, hp[c2], g.debug);
             }
             tc_fence_before();
             __syncwarp();
@@ -729,7 +735,7 @@ gru_step2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
                 tmem_ld16(taddr + 128 + cb * 16, vx);
                 if (has_h) tmem_ld16(taddr + 192 + cb * 16, vh);
                 tmem_ld_wait();
-                gru_finish16<FAST_ACT>(P, g.M, m_warp0, lane, ub * GRU_UB + cb * 16, vr, vz, vx, vh, has_h, hp[c2]);
+                gru_finish16<FAST_ACT>(P, g.M, m_warp0, lane, ub * GRU_UB + cb * 16, vr, vz, vx, vh, has_h, hp[c2], g.debug);
             }
             tc_fence_before();
             __syncwarp();

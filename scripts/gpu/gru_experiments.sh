@@ -1,6 +1,6 @@
 #!/bin/bash
 # timing experiments on the GRU step kernels (results are WRONG under DP_GRU_DEBUG != 0; timing only)
-for cfg in "2cta 0" "2cta 1" "1cta 0" "1cta 1"; do
+for cfg in "1cta 6" "1cta 7" "1cta 8" "1cta 9" "1cta 5"; do
   set -- $cfg
   echo "== DP_GRU=$1 DP_GRU_DEBUG=$2"
   DP_GRU=$1 DP_GRU_DEBUG=$2 timeout 200 python bench.py --steps 3 --warmup 3 --no-cpu-baseline 2>&1 | python -c "
