@@ -45,7 +45,7 @@ __constant__ uint8_t c_qlut[256];
 static const uint8_t h_qlut_head[28] = {0,   52,  94,  127, 153, 174, 191, 204, 215, 223, 230, 235, 239, 242,
                                         245, 247, 249, 250, 251, 252, 252, 253, 253, 254, 254, 254, 254, 254};
 static bool g_lut_ready[64] = {false};
-static bool g_lut_flat = true;      // table constant from index 28 on (true for the reference's formula): v2 codes need it
+static bool g_lut_flat = true;      // table constant from index 28 on (true for the reference's formula): v3 codes need it
 
 static int ensure_lut() {
     int dev = 0;
@@ -105,9 +105,33 @@ __device__ __forceinline__ bool op_adv_ref(int op) { return op == 0 || op == 2 |
 __device__ __forceinline__ bool op_adv_read(int op) { return op == 0 || op == 1; }
 
 // ------------------------------------------------------------------------------------------------
+// Per-read digest for the fast path (v3), written by the prep kernel.  `clean` reads are those on which the
+// reference cannot raise and whose CIGAR stays inside the fast path's closed form: ops M/I/D/S only, no
+// zero-length op, S only as first/last op, no I next to an I or an S, first non-S op is M, query advance equal
+// to the aligned length, every base in {A,C,G,T,N}.  A window that meets any other read is recomputed by the
+// exact (v1) kernel.
+struct __align__(16) ReadInfo {
+    int ref_start;     // first aligned reference position (INT_MIN: none)
+    int endk;          // bam_endpos, or INT_MIN when the read can never contribute (mapq < cut, no aligned base)
+    int aln_start;     // leading soft clip
+    int aln_len;       // len(query_alignment_sequence)
+    int l_seq;
+    int mapq28;        // min(mapq, 28): the quality table is flat from 28 on
+    int nops;
+    int flags;         // bit 0: clean; bits 8..15: checkpoint shift
+    long long c0;      // cigar offset
+    long long seq_off;
+    long long qual_off;
+    int span;          // reference advance of the whole CIGAR (Pileup.py deltaRef rule)
+    int pad;
+};
+constexpr int RI_CLEAN = 1;
+
 // prep: one warp per read
 __global__ void __launch_bounds__(256) prep_reads_kernel(dp_reads R, ReadAux *__restrict__ aux,
-                                                         int *__restrict__ RP, int *__restrict__ QP) {
+                                                         int *__restrict__ RP, int *__restrict__ QP,
+                                                         ReadInfo *__restrict__ info, int *__restrict__ ckpt,
+                                                         int *__restrict__ endk, int mapq_cut) {
     const int lane = threadIdx.x & 31;
     const int r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (r >= R.n_reads) return;
@@ -116,6 +140,8 @@ __global__ void __launch_bounds__(256) prep_reads_kernel(dp_reads R, ReadAux *__
     const int pos = R.pos[r];
     int carryR = 0, carryQ = 0, carryH = 0, carryDN = 0;
     int ref_start = INT_MIN;
+    bool dirty = false;
+    const int op_first = nops > 0 ? (int)(R.cigar[c0] & 15) : -1;
     for (int base = 0; base < nops; base += 32) {
         const int j = base + lane;
         const uint32_t w = j < nops ? R.cigar[c0 + j] : 0u;
@@ -129,6 +155,13 @@ __global__ void __launch_bounds__(256) prep_reads_kernel(dp_reads R, ReadAux *__
         if (j < nops) {
             RP[c0 + r + j] = carryR + iR - dR;               // nops+1 entries per read, base c0 + r
             QP[c0 + j] = carryQ + iQ - dQ;
+            // ---- fast-path envelope
+            const int opp = j > 0 ? (int)(R.cigar[c0 + j - 1] & 15) : -1;
+            const int opn = j + 1 < nops ? (int)(R.cigar[c0 + j + 1] & 15) : -1;
+            if (!(op == 0 || op == 1 || op == 2 || op == 4) || n == 0) dirty = true;
+            if (op == 4 && !(j == 0 || j == nops - 1)) dirty = true;
+            if (op == 1 && (opp == 1 || opp == 4 || opn == 1 || opn == 4)) dirty = true;
+            if (op != 0 && op != 4 && (j == 0 || (j == 1 && op_first == 4))) dirty = true;   // first non-S op must be M
         }
         const bool aligned = j < nops && (op == 0 || op == 7 || op == 8) && n > 0;
         const unsigned m = __ballot_sync(0xffffffffu, aligned);
@@ -142,27 +175,73 @@ __global__ void __launch_bounds__(256) prep_reads_kernel(dp_reads R, ReadAux *__
         carryH += __shfl_sync(0xffffffffu, iH, 31);
         carryDN += __shfl_sync(0xffffffffu, iDN, 31);
     }
+    // ---- soft-clip extents (lane-uniform, short loops)
+    const int l_seq = R.l_seq[r];
+    int s = 0, e = l_seq;
+    for (int c = 0; c < nops; c++) {
+        const uint32_t w = R.cigar[c0 + c];
+        const int op = w & 15;
+        if (op == 5) continue;
+        if (op == 4) s += (int)(w >> 4); else break;
+    }
+    for (int c = nops - 1; c >= 0; c--) {
+        const uint32_t w = R.cigar[c0 + c];
+        const int op = w & 15;
+        if (op == 5) continue;
+        if (op == 4) e -= (int)(w >> 4); else break;
+    }
+    const int aln_len = e - s > 0 ? e - s : 0;
+    const int endpos = (!(R.flag[r] & 4) && nops > 0) ? pos + carryH : pos + 1;
+    // ---- every base the reference may index must be a colour key (A,C,G,T,N)
+    const int64_t so = R.seq_off[r];
+    for (int k = lane; k < l_seq; k += 32) {
+        const uint8_t b = R.seq4[so + (k >> 1)];
+        const int nib = (k & 1) ? (b & 15) : (b >> 4);
+        if (!((0x8116u >> nib) & 1u)) dirty = true;
+    }
+    if (carryQ != aln_len || aln_len <= 0 || ref_start != pos || carryR <= 0) dirty = true;
+    dirty = __any_sync(0xffffffffu, dirty);
+    // ---- checkpoints: ckpt[m] = first op j with RP[j+1] >= m << k ; at most nops/4 + 1 of them per read
+    int k = 6;
+    while ((carryR >> k) > (nops >> 2)) k++;
+    const int64_t ckb = (c0 >> 2) + r;
+    {
+        int cR = 0;
+        for (int base = 0; base < nops; base += 32) {
+            const int j = base + lane;
+            const uint32_t w = j < nops ? R.cigar[c0 + j] : 0u;
+            const int op = w & 15, n = (int)(w >> 4);
+            const int dR = op_adv_ref(op) ? n : 0;
+            const int iR = warp_incl_scan(dR, lane);
+            if (dR > 0) {
+                const int a0 = cR + iR - dR, b0 = cR + iR;
+                for (int m = (a0 >> k) + 1; m <= (b0 >> k); m++) ckpt[ckb + m] = j;
+            }
+            cR += __shfl_sync(0xffffffffu, iR, 31);
+        }
+    }
     if (lane == 0) {
+        ckpt[ckb] = 0;
         RP[c0 + r + nops] = carryR;
         ReadAux a;
         a.ref_start = ref_start;
-        a.endpos = (!(R.flag[r] & 4) && nops > 0) ? pos + carryH : pos + 1;
-        int s = 0, e = R.l_seq[r];
-        for (int c = 0; c < nops; c++) {
-            const uint32_t w = R.cigar[c0 + c];
-            const int op = w & 15;
-            if (op == 5) continue;
-            if (op == 4) s += (int)(w >> 4); else break;
-        }
-        for (int c = nops - 1; c >= 0; c--) {
-            const uint32_t w = R.cigar[c0 + c];
-            const int op = w & 15;
-            if (op == 5) continue;
-            if (op == 4) e -= (int)(w >> 4); else break;
-        }
+        a.endpos = endpos;
         a.aln_start = s;
-        a.aln_len = e - s > 0 ? e - s : 0;
+        a.aln_len = aln_len;
         aux[r] = a;
+        const int mq = R.mapq[r];
+        const bool contributes = mq >= mapq_cut && ref_start != INT_MIN;
+        ReadInfo ri;
+        ri.ref_start = ref_start;
+        ri.endk = contributes ? endpos : INT_MIN;
+        ri.aln_start = s; ri.aln_len = aln_len; ri.l_seq = l_seq;
+        ri.mapq28 = mq < 28 ? mq : 28;
+        ri.nops = nops;
+        ri.flags = (dirty ? 0 : RI_CLEAN) | (k << 8);
+        ri.c0 = c0; ri.seq_off = so; ri.qual_off = R.qual_off[r];
+        ri.span = carryR; ri.pad = 0;
+        info[r] = ri;
+        endk[r] = ri.endk;
     }
 }
 
@@ -195,6 +274,9 @@ struct EncArgs {
     const ReadAux *aux;
     const int *RP;
     const int *QP;
+    const ReadInfo *info;      // fast path (v3) digest, checkpoints and filtered end positions
+    const int *ckpt;
+    const int *endk;
     const int32_t *win_qs, *win_lo, *win_hi;
     const uint8_t *ref;
     long long ref_base, ref_len;
@@ -653,193 +735,259 @@ __global__ void __launch_bounds__(ENC_THREADS) encode_windows_kernel(EncArgs a, 
 }
 
 // ================================================================================================
-// Encoder v2 (fast path).  Same closed form as v1, different work distribution:
-//   generate   one WARP per read (8 reads in flight per CTA): locate the read's first in-window op (32-ary search on
-//              the prefix sums), stage its <= 64 in-window ops, then lanes sweep the window's columns and write a
-//              one-byte code (category << 5 | quality index) per entry into shared-memory planes [entry][slot][column];
-//              inserted bases go to a byte pool addressed through an insert plane.
-//   walk       one THREAD per column reads its codes in slot (= file) order: pass A counts per category, pass B places
-//              each code at base[category] + running rank -- (read order, step order) without atomics or sorting.
-//              Up to 32 reads are held per batch; when a window has more, pass B regenerates batch by batch.
-//   emit       as v1, colour and alpha decoded from the code byte.
-// Anything outside the fast path's envelope (ops other than M/I/D/S, zero-length ops, > 64 in-window ops per read,
-// > 3 entries of one read on one column, two insertions of a read at one anchor, insert rows deeper than the image,
-// any condition on which the reference raises) marks the window for the exact v1 kernel, which then recomputes it.
-constexpr int V2_THREADS = 256;
-constexpr int V2_WARPS = V2_THREADS / 32;
-constexpr int V2_SLOTS = 32;          // reads per batch
-constexpr int V2_CS = 208;            // column stride of the code planes (>= window length)
-constexpr int V2_OPS = 64;            // staged ops per read
-constexpr int V2_POOL = 2048;         // inserted-base codes per batch
-constexpr int V2_NREC = 254;          // insert records per batch (plane byte = record + 1)
-constexpr int V2_CAND = 512;          // surviving reads held per round
-constexpr int V2_QMAX = 28;           // quality index clamp: the table is flat from here on (checked on the host)
-constexpr uint8_t V2_NONE = 0xFF;
+// Encoder v3 (fast path).  Same closed form as v1, specialised to `clean` reads (ReadInfo) so that nothing in the
+// inner loops can raise, and restricted to the pileup columns that reach the image:
+//   scan      one warp per read, lane per CIGAR op (entered through the per-read checkpoints, no search): insert
+//             lengths per anchor column and a coverage difference array -> which columns are populated, how many image
+//             rows each takes (anchor + insert rows, Pileup.py:295-317) and hence the last column that is still inside
+//             the windowCutoff rows (Lgen).  With 3 % insertions only ~70 of the 201 columns are ever drawn.
+//   generate  one warp per read: op-parallel part (first step of every M/D op, soft-clip step, inserted bases) and
+//             column-parallel part (each lane walks a run of consecutive columns through the staged M/D ops) write one
+//             code byte (category << 5 | quality index) per entry into shared-memory planes [kind][read slot][column];
+//             per-(category, column) counts are taken with shared-memory atomics on the way.
+//   place     one THREAD per column reads its codes in slot (= file) order and puts each at base[category] + running
+//             rank -- (read order, step order) without sorting; the 7 running ranks live in two packed registers.
+//   emit      filler quads straight from registers, entry quads through a 256-entry code -> RGBA table.
+// For clean reads relativeIndexRef has the closed form  rel = column - (step == 0) + shift, where shift = 1 iff an
+// M/D op of the read starts exactly at queryStart (Pileup.py:203-204,252 and SURVEY.md A.1 "shifted by +1").
+// Anything outside the envelope (a read that is not clean, an illegal reference character, more reads / inserted
+// bases than the shared-memory planes hold, insert rows deeper than the image) marks the window for the exact v1
+// kernel, which then recomputes it.
+constexpr int V3_THREADS = 256;
+constexpr int V3_WARPS = V3_THREADS / 32;
+constexpr int V3_SLOTS = 40;          // reads per batch
+constexpr int V3_CS = 208;            // column stride of the planes (>= window length)
+constexpr int V3_MAXC = 192;          // surviving reads per window
+constexpr int V3_MD = 64;             // staged M/D ops per read
+constexpr int V3_POOL = 2048;         // inserted-base codes per batch
+constexpr int V3_NREC = 253;          // insert records per batch (plane byte = record + 1; 255 = soft-clip step)
+constexpr int V3_QMAX = 28;
+constexpr uint8_t V3_NONE = 0xFF;
+constexpr uint8_t V3_FILL_NONE = (6 << 5) | 29;   // (0,0,0,255)
+constexpr uint8_t V3_FILL_INS = (7 << 5) | 29;    // (255,0,255,255)
 
-struct __align__(4) Op2 {
-    int sA;              // column of the op's first reference position, relative to queryStart
-    int qp;              // readPosition at op start
-    unsigned short n;    // length, clamped to 65535 (only compared against window-sized quantities)
-    unsigned short relop;// relativeIndexRef at op start (clamped to 4095) << 4 | op
-};
-__device__ __forceinline__ int op2_op(const Op2 &o) { return o.relop & 15; }
-__device__ __forceinline__ int op2_rel(const Op2 &o) { return o.relop >> 4; }
-
-struct V2Shared {
-    uint8_t *plane;      // [4][V2_SLOTS][V2_CS]: entry 0..2 codes, then the insert plane
-    uint8_t *pool;       // [V2_POOL]
-    uint32_t *rec;       // [V2_NREC + 2]: n << 16 | pool offset
-    Op2 *ops;            // [V2_WARPS][V2_OPS]
-    const uint8_t *ref;  // [L+1]
-    int *nrec, *npool, *fallback;
+struct __align__(8) Md3 {
+    int qadj;            // M: query index of column c is qadj + c ; D: the frozen query index
+    short sA;            // first column of the op (clamped below at -1)
+    short endD;          // (one past the last reference column, clamped) << 1 | isD
 };
 
-__device__ __forceinline__ uint8_t v2_code(int cat, int q) { return (uint8_t)((cat << 5) | min(q, V2_QMAX)); }
+struct V3S {
+    uint8_t *q;                  // [H][W] codes per image row (pixel 0 = reference)
+    uint8_t *p1, *p0, *pi;       // [V3_SLOTS][V3_CS] step>=1 codes, step-0 codes, insert record / soft-clip marker
+    uint32_t *cnt;               // [NCAT][V3_CS/2] two 16-bit counters per word
+    Md3 *md;                     // [V3_WARPS][V3_MD]
+    uint32_t *lut;               // [256] code -> RGBA
+    uint8_t *pool;               // [V3_POOL]
+    uint32_t *rec;               // [256] n << 16 | pool offset
+    int *cand, *j0;              // [V3_MAXC]
+    int *cov, *maxins;           // [V3_CS + 8], [V3_CS]
+    uint8_t *refc;               // [224] 4-bit codes of refSequence
+    uint8_t *scode;              // [V3_SLOTS][2] soft-clip step codes (leading, trailing)
+    short *scol;                 // [V3_SLOTS][2]
+    int *misc;                   // [0] fallback [1] nrec [2] npool [3] Lgen [4] nrows [5] hasS [8..16] warp sums [16..24] warp sums 2
+};
 
-// One warp: all entries of read r that land in window [qs, qs+Lwin) -> planes of `slot`.
-__device__ void v2_gen_read(const EncArgs &a, const V2Shared &S, int r, int slot, int qs, int Lwin, int lane, int warp) {
-    Op2 *ops = S.ops + warp * V2_OPS;
-    const ReadAux ax = a.aux[r];
-    const long long c0 = a.R.cigar_off[r];
-    const int nops_total = (int)(a.R.cigar_off[r + 1] - c0);
-    const int refStart = ax.ref_start;
-    const long long seq_off = a.R.seq_off[r], qual_off = a.R.qual_off[r];
-    const int aln_start = ax.aln_start, aln_len = ax.aln_len, l_seq = a.R.l_seq[r], mapq = a.R.mapq[r];
-    // ---- first op whose end reaches the window (as stage_read)
-    const long long rpb = c0 + r;
-    int j0;
-    {
-        const int T = qs - refStart;
-        int lo = 0, hi = nops_total;
-        while (lo < hi) {
-            const int len = hi - lo;
-            const int step = (len + 31) >> 5;
-            const int jk = min(lo + (lane + 1) * step - 1, hi - 1);
-            const bool before = a.RP[rpb + jk + 1] < T;
-            const int k = __popc(__ballot_sync(0xffffffffu, before));
-            if (k == 32) { lo = hi; break; }
-            const int nlo = lo + k * step;
-            const int nhi = min(lo + (k + 1) * step, hi) - 1;
-            lo = nlo; hi = max(nhi, nlo);
-        }
-        j0 = lo;
-    }
-    int carryA = 0, carryQ = 0, carryRel = refStart > qs ? refStart - qs - 1 : 0;
-    if (j0 < nops_total) { carryA = refStart + a.RP[rpb + j0] - qs; carryQ = -1 + a.QP[c0 + j0]; }
-    // ---- stage the in-window ops
-    int staged = 0;
-    bool bad = false;
-    for (int round = 0; round < V2_OPS / 32 + 1; round++) {
-        const int jj = j0 + round * 32 + lane;
-        const bool valid = jj < nops_total;
-        const uint32_t w = valid ? a.R.cigar[c0 + jj] : 0u;
-        const int op = w & 15, n = (int)(w >> 4);
-        const int dR = op_adv_ref(op) ? n : 0, dQ = op_adv_read(op) ? n : 0;
-        const int iR = warp_incl_scan(dR, lane), iQ = warp_incl_scan(dQ, lane);
-        const int sA = carryA + iR - dR, qp = carryQ + iQ - dQ;
-        int inwin = 0;
-        if (valid && (op == 0 || op == 2) && n > 0) {
-            inwin = (sA >= 0 && sA < Lwin) ? 1 : 0;
-            const int lo_i = max(1, 1 - sA), hi_i = min(n - 1, Lwin - sA);
-            if (hi_i >= lo_i) inwin += hi_i - lo_i + 1;
-        }
-        const int iW = warp_incl_scan(inwin, lane);
-        const int rel = carryRel + iW - inwin;
-        const bool relevant = valid && sA < Lwin;
-        const int cnt = __popc(__ballot_sync(0xffffffffu, relevant));      // a prefix of the lanes (sA is monotone)
-        if (relevant) {
-            if (round == V2_OPS / 32) bad = true;                          // more than V2_OPS in-window ops
-            else {
-                if (!(op == 0 || op == 1 || op == 2 || op == 4) || n == 0) bad = true;
-                Op2 o;
-                o.sA = sA; o.qp = qp; o.n = (unsigned short)min(n, 65535);
-                o.relop = (unsigned short)((max(0, min(rel, 4095)) << 4) | op);
-                ops[staged + lane] = o;
-            }
-        }
-        if (round < V2_OPS / 32) staged += cnt;
-        carryA += __shfl_sync(0xffffffffu, iR, 31);
-        carryQ += __shfl_sync(0xffffffffu, iQ, 31);
-        carryRel += __shfl_sync(0xffffffffu, iW, 31);
-        if (cnt < 32) break;
-    }
-    __syncwarp();
-    const uint8_t *seqp = a.R.seq4 + seq_off, *qualp = a.R.qual + qual_off;
-    uint8_t *p0 = S.plane + (size_t)slot * V2_CS, *p1 = p0 + V2_SLOTS * V2_CS, *p2 = p1 + V2_SLOTS * V2_CS;
-    uint8_t *pi = p2 + V2_SLOTS * V2_CS;
-    // ---- columns
-    for (int P = lane; P < Lwin; P += 32) {
-        uint8_t code[3] = {V2_NONE, V2_NONE, V2_NONE};
-        int ne = 0;
-        int lo = 0, hi = staged;                      // first op with key > P (key as in seg_lower_bound)
-        while (lo < hi) {
-            const int mid = (lo + hi) >> 1;
-            const Op2 o = ops[mid];
-            const int oo = op2_op(o);
-            const int key = (oo == 0 || oo == 2) ? o.sA + o.n : o.sA + 1;
-            if (key <= P) lo = mid + 1; else hi = mid;
-        }
-        for (int j = lo; j < staged; j++) {
-            const Op2 o = ops[j];
-            if (o.sA > P) break;
-            const int op = op2_op(o), n = o.n;
-            if (op == 1) continue;
-            int i_first, i_count;
-            if (op == 4) { if (o.sA != P) continue; i_first = 0; i_count = 1; }
-            else if (P == o.sA) { i_first = 0; i_count = n >= 2 ? 2 : 1; }
-            else { i_first = P - o.sA + 1; i_count = (i_first <= n - 1) ? 1 : 0; }
-            const int in0 = (o.sA >= 0 && o.sA < Lwin) ? 1 : 0, lo_i = max(1, 1 - o.sA);
-            for (int t = 0; t < i_count; t++) {
-                const int i = i_first + t;
-                int idx = o.qp + (op == 0 ? i : 0);
-                int rel = op2_rel(o);
-                if (op != 4 && i > 0) rel += in0 + max(0, i - lo_i);
-                int si = idx < 0 ? idx + aln_len : idx, qi = idx < 0 ? idx + l_seq : idx;
-                if (rel < 0 || rel > Lwin || si < 0 || si >= aln_len || qi < 0 || qi >= l_seq) { bad = true; continue; }
-                const int k = si + aln_start;
-                const uint8_t b = __ldg(seqp + (k >> 1));
-                const int nib = (k & 1) ? (b & 15) : (b >> 4);
-                int cat;
-                if (op == 2) cat = CAT_D;
-                else {
-                    cat = (ascii_of_code(nib) == S.ref[rel]) ? CAT_M : cat_of_code(nib);
-                    if (cat < 0) { bad = true; continue; }
-                }
-                const int q = min((int)__ldg(qualp + qi), mapq);
-                if (ne < 3) code[ne] = v2_code(cat, q); else bad = true;
-                ne++;
-            }
-        }
-        p0[P] = code[0]; p1[P] = code[1]; p2[P] = code[2];
-    }
-    // ---- insertions (Pileup.py:220-230): anchor column sA in [1, Lwin)
-    for (int jj = lane; jj < staged; jj += 32) {
-        const Op2 o = ops[jj];
-        if (op2_op(o) != 1 || o.sA < 1 || o.sA >= Lwin) continue;
-        const int n = o.n;
-        bool dup = n >= 65535;
-        for (int b = jj - 1; b >= 0 && ops[b].sA == o.sA; b--) dup |= op2_op(ops[b]) == 1;
-        const int first = o.qp + 1, last = o.qp + n;
-        if (dup || first < 0 || last >= aln_len || last >= l_seq) { bad = true; continue; }
-        const int rec = atomicAdd(S.nrec, 1);
-        const int off = atomicAdd(S.npool, n);
-        if (rec >= V2_NREC || off + n > V2_POOL) { bad = true; continue; }
-        S.rec[rec] = ((uint32_t)n << 16) | (uint32_t)off;
-        pi[o.sA] = (uint8_t)(rec + 1);
-        for (int k2 = 0; k2 < n; k2++) {
-            const int k = first + k2 + aln_start;
-            const uint8_t b = __ldg(seqp + (k >> 1));
-            const int nib = (k & 1) ? (b & 15) : (b >> 4);
-            const int cat = cat_of_code(nib);
-            if (cat < 0) { bad = true; break; }
-            S.pool[off + k2] = v2_code(cat, min((int)__ldg(qualp + first + k2), mapq));
-        }
-    }
-    if (bad) *S.fallback = 1;
+__device__ __forceinline__ int v3_cat_of_nib(int nib) { return nib == 15 ? CAT_N : __ffs(nib) - 1; }
+__device__ __forceinline__ void v3_count(const V3S &S, int cat, int c) {
+    atomicAdd(&S.cnt[(cat * V3_CS + c) >> 1], 1u << ((c & 1) << 4));
+}
+__device__ __forceinline__ int v3_nib(const uint8_t *__restrict__ seqp, int k) {
+    const uint8_t b = __ldg(seqp + (k >> 1));
+    return (b >> ((~k & 1) << 2)) & 15;
 }
 
-__global__ void __launch_bounds__(V2_THREADS, 3)
-encode_windows_v2_kernel(EncArgs a, int *__restrict__ fb_count, int *__restrict__ fb_list) {
+// scan: one warp; coverage difference array and insert lengths of read `r`; first relevant op -> S.j0[ci]
+__device__ void v3_scan_read(const EncArgs &a, const V3S &S, int ci, int qs, int L, int lane) {
+    const int r = S.cand[ci];
+    const ReadInfo *ri = a.info + r;
+    const int ref_start = ri->ref_start, nops = ri->nops;
+    const long long c0 = ri->c0;
+    const long long rpb = c0 + r;
+    int j = S.j0[ci];
+    int j0 = -1;
+    while (j < nops) {
+        const int jj = j + lane;
+        const bool valid = jj < nops;
+        const uint32_t w = valid ? __ldg(a.R.cigar + c0 + jj) : 0u;
+        const int rp = valid ? __ldg(a.RP + rpb + jj) : 0;
+        const int op = w & 15, n = (int)(w >> 4);
+        const int sA = ref_start + rp - qs;
+        const bool md = op == 0 || op == 2;
+        const bool relevant = valid && sA < L;
+        const bool live = relevant && !(sA + (md ? n : 0) < 0);
+        const unsigned lm = __ballot_sync(0xffffffffu, valid && !(sA + (md ? n : 0) < 0));
+        if (j0 < 0 && lm) j0 = j + __ffs(lm) - 1;
+        if (live) {
+            if (op == 1) {
+                if (sA >= 1) atomicMax(&S.maxins[sA], min(n, 512));
+            } else {
+                const int lo = max(sA, 0);
+                const int hi = md ? min(max(sA + 1, sA + n - 1), L) : sA + 1;
+                if (lo < hi) { atomicAdd(&S.cov[lo], 1); atomicAdd(&S.cov[hi], -1); }
+            }
+        }
+        if (__popc(__ballot_sync(0xffffffffu, relevant)) < 32) break;
+        j += 32;
+    }
+    if (lane == 0) S.j0[ci] = j0 < 0 ? nops : j0;
+}
+
+// generate: one warp; every entry of read S.cand[ci] on columns [0, Lgen) -> planes of `slot`
+__device__ void v3_gen_read(const EncArgs &a, const V3S &S, int ci, int slot, int qs, int Lgen, bool count, int lane,
+                            int warp) {
+    const int r = S.cand[ci];
+    const ReadInfo *ri = a.info + r;
+    const int ref_start = ri->ref_start, nops = ri->nops;
+    const int aln_start = ri->aln_start, aln_len = ri->aln_len, l_seq = ri->l_seq, mapq28 = ri->mapq28;
+    const long long c0 = ri->c0;
+    const long long rpb = c0 + r;
+    const uint8_t *__restrict__ seqp = a.R.seq4 + ri->seq_off;
+    const uint8_t *__restrict__ qualp = a.R.qual + ri->qual_off;
+    Md3 *md = S.md + warp * V3_MD;
+    uint8_t *p1 = S.p1 + slot * V3_CS, *p0 = S.p0 + slot * V3_CS, *pi = S.pi + slot * V3_CS;
+    const unsigned lt = (1u << lane) - 1u;
+    int nmd = 0, shift = 0;
+    bool bad = false;
+    int j = S.j0[ci];
+    for (int round = 0; j < nops; round++, j += 32) {
+        const int jj = j + lane;
+        const bool valid = jj < nops;
+        const uint32_t w = valid ? __ldg(a.R.cigar + c0 + jj) : 0u;
+        const int rp = valid ? __ldg(a.RP + rpb + jj) : 0;
+        const int qp = valid ? __ldg(a.QP + c0 + jj) - 1 : 0;
+        const int op = w & 15, n = (int)(w >> 4);
+        const int sA = ref_start + rp - qs;
+        const bool relevant = valid && sA < Lgen;
+        const bool isMD = relevant && (op == 0 || op == 2);
+        const unsigned z = __ballot_sync(0xffffffffu, isMD && sA == 0);
+        if (round == 0) shift = z ? 1 : 0; else if (z) bad = true;
+        // ---- staged M/D ops (column-parallel part below)
+        const unsigned mdm = __ballot_sync(0xffffffffu, isMD);
+        if (isMD) {
+            const int k = nmd + __popc(mdm & lt);
+            if (k < V3_MD) {
+                Md3 m;
+                m.qadj = op == 0 ? qp - sA + 1 : qp;
+                m.sA = (short)max(sA, -1);
+                m.endD = (short)((min(sA + n, 400) << 1) | (op == 2 ? 1 : 0));
+                md[k] = m;
+            } else bad = true;
+        }
+        nmd += __popc(mdm);
+        // ---- op-parallel part
+        if (relevant && sA >= 0) {
+            if (op == 0 || op == 2 || op == 4) {
+                // step 0 of the op: previous query base (index -1 wraps, Python), reference character one to the left
+                const int si = qp < 0 ? qp + aln_len : qp, qi = qp < 0 ? qp + l_seq : qp;
+                const int rel = sA - 1 + shift;
+                if (rel < 0 || si < 0 || qi < 0) bad = true;
+                else {
+                    const int nib = v3_nib(seqp, si + aln_start);
+                    const int q = min((int)__ldg(qualp + qi), mapq28);
+                    const int cat = op == 2 ? CAT_D : (nib == S.refc[rel] ? CAT_M : v3_cat_of_nib(nib));
+                    const uint8_t code = (uint8_t)((cat << 5) | q);
+                    if (op == 4) {
+                        const int which = jj == 0 ? 0 : 1;
+                        S.scode[slot * 2 + which] = code;
+                        S.scol[slot * 2 + which] = (short)sA;
+                        pi[sA] = 255;
+                        S.misc[5] = 1;
+                    } else p0[sA] = code;
+                    if (count) v3_count(S, cat, sA);
+                }
+            } else if (op == 1 && sA >= 1) {
+                // insertion anchored at column sA (Pileup.py:220-230): bases qp+1 .. qp+n
+                const int rec = atomicAdd(&S.misc[1], 1);
+                const int off = atomicAdd(&S.misc[2], n);
+                if (rec >= V3_NREC || off + n > V3_POOL || n > 0xffff) bad = true;
+                else {
+                    S.rec[rec] = ((uint32_t)n << 16) | (uint32_t)off;
+                    pi[sA] = (uint8_t)(rec + 1);
+                    for (int k2 = 0; k2 < n; k2++) {
+                        const int idx = qp + 1 + k2;
+                        const int nib = v3_nib(seqp, idx + aln_start);
+                        S.pool[off + k2] = (uint8_t)((v3_cat_of_nib(nib) << 5) | min((int)__ldg(qualp + idx), mapq28));
+                    }
+                }
+            }
+        }
+        if (__popc(__ballot_sync(0xffffffffu, relevant)) < 32) break;
+    }
+    __syncwarp();
+    // ---- column-parallel part: steps >= 1 of the M/D ops; lane owns columns [cA, cA + cpl)
+    const int cpl = (Lgen + 31) >> 5;
+    const int cA = lane * cpl;
+    if (nmd > V3_MD) nmd = V3_MD;
+    if (nmd > 0 && cA < Lgen) {
+        int jm = 0;                                   // last staged op with sA <= cA (0 if none)
+#pragma unroll
+        for (int step = V3_MD / 2; step; step >>= 1) {
+            const int t = jm + step;
+            if (t < nmd && md[t].sA <= cA) jm = t;
+        }
+        Md3 m = md[jm];
+        int end = m.endD >> 1;
+        const int cEnd = min(cA + cpl, Lgen);
+        for (int c = cA; c < cEnd; c++) {
+            if (c >= end && jm + 1 < nmd) { jm++; m = md[jm]; end = m.endD >> 1; }
+            if (c >= m.sA && c < end - 1) {
+                const bool isD = m.endD & 1;
+                const int idx = m.qadj + (isD ? 0 : c);
+                const int q = min((int)__ldg(qualp + idx), mapq28);
+                int cat = CAT_D;
+                if (!isD) {
+                    const int nib = v3_nib(seqp, idx + aln_start);
+                    cat = nib == S.refc[c + shift] ? CAT_M : v3_cat_of_nib(nib);
+                }
+                p1[c] = (uint8_t)((cat << 5) | q);
+                if (count) v3_count(S, cat, c);
+            }
+        }
+    }
+    if (bad) S.misc[0] = 1;
+}
+
+// place: thread `c` owns column c (image row my_row); codes of the batch's slots in file order
+__device__ __forceinline__ void v3_place(uint8_t code, uint32_t &lo, uint32_t &hi, uint8_t *qrow, int Wm1) {
+    const int cat = code >> 5;
+    const int pos = (int)(__byte_perm(lo, hi, (uint32_t)cat) & 0xffu);
+    if (pos < Wm1) {
+        qrow[pos] = code;
+        const uint32_t inc = 1u << ((cat & 3) << 3);
+        if (cat < 4) lo += inc; else hi += inc;
+    }
+}
+
+__device__ void v3_walk(const V3S &S, int c, int my_row, int nslots, int W, int H, uint32_t &lo, uint32_t &hi,
+                        unsigned short *s_rowcnt) {
+    uint8_t *qrow = S.q + (size_t)my_row * W + 1;
+    const uint8_t *p1 = S.p1 + c, *p0 = S.p0 + c, *pi = S.pi + c;
+    const int Wm1 = W - 1;
+    for (int s = 0; s < nslots; s++) {
+        const uint8_t c1 = p1[s * V3_CS], c0 = p0[s * V3_CS], ir = pi[s * V3_CS];
+        if (ir == 255) {
+            const int which = S.scol[s * 2] == c ? 0 : 1;
+            v3_place(S.scode[s * 2 + which], lo, hi, qrow, Wm1);
+        }
+        if (c0 != V3_NONE) v3_place(c0, lo, hi, qrow, Wm1);
+        if (c1 != V3_NONE) v3_place(c1, lo, hi, qrow, Wm1);
+        if (ir != 0 && ir != 255) {
+            const uint32_t rc = S.rec[ir - 1];
+            const int n = rc >> 16, off = rc & 0xffff;
+            for (int k = 0; k < n; k++) {
+                const int y = my_row + 1 + k;
+                if (y >= H) break;
+                const int pos = s_rowcnt[y]++;
+                if (pos < Wm1) S.q[(size_t)y * W + 1 + pos] = S.pool[off + k];
+                else S.misc[0] = 1;                  // deeper than the image: the category sort needs every entry
+            }
+        }
+    }
+}
+
+__global__ void __launch_bounds__(V3_THREADS, 3)
+encode_windows_v3_kernel(EncArgs a, int *__restrict__ fb_count, int *__restrict__ fb_list, uint32_t qmagic) {
     extern __shared__ __align__(16) uint8_t smem[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int w = blockIdx.x;
@@ -847,174 +995,185 @@ encode_windows_v2_kernel(EncArgs a, int *__restrict__ fb_count, int *__restrict_
     const int qs = a.win_qs[w], qe = qs + L;
     const int lo = a.win_lo[w], hi = a.win_hi[w];
 
-    // ---- shared memory carve-up (16-byte aligned sections)
+    // ---- shared memory carve-up (16-byte aligned sections first)
     uint8_t *p = smem;
-    uint8_t *s_plane = p;                          p += 4 * V2_SLOTS * V2_CS;
-    uint8_t *s_q = p;                              p += ((H * W + 15) / 16) * 16;      // [H][W] code bytes (pixel 0 unused)
-    Op2 *s_ops = (Op2 *)p;                         p += sizeof(Op2) * V2_WARPS * V2_OPS;
-    uint32_t *s_rec = (uint32_t *)p;               p += 4 * 256;
-    uint8_t *s_pool = p;                           p += V2_POOL;
-    int *s_cand = (int *)p;                        p += 4 * V2_CAND;
-    unsigned short *s_cnt = (unsigned short *)p;   p += 2 * NCAT * V2_CS;              // [cat][col] counts, then running ranks
-    unsigned short *s_rowstart = (unsigned short *)p; p += 2 * V2_CS;
-    unsigned short *s_ord = (unsigned short *)p;   p += 2 * V2_CS;                     // anchor ordinal of a populated column
+    V3S S;
+    S.q = p;                                       p += ((H * W + 15) / 16) * 16;
+    S.p1 = p;                                      p += V3_SLOTS * V3_CS;
+    S.p0 = p;                                      p += V3_SLOTS * V3_CS;
+    S.pi = p;                                      p += V3_SLOTS * V3_CS;
+    S.cnt = (uint32_t *)p;                         p += 4 * (NCAT * V3_CS / 2);
+    S.md = (Md3 *)p;                               p += sizeof(Md3) * V3_WARPS * V3_MD;
+    S.lut = (uint32_t *)p;                         p += 4 * 256;
+    S.rec = (uint32_t *)p;                         p += 4 * 256;
+    S.pool = p;                                    p += V3_POOL;
+    S.cand = (int *)p;                             p += 4 * V3_MAXC;
+    S.j0 = (int *)p;                               p += 4 * V3_MAXC;
+    S.cov = (int *)p;                              p += 4 * (V3_CS + 8);
+    S.maxins = (int *)p;                           p += 4 * V3_CS;
+    S.misc = (int *)p;                             p += 4 * 32;
+    unsigned short *s_rowstart = (unsigned short *)p; p += 2 * V3_CS;
     short *s_rowcol = (short *)p;                  p += 2 * 256;
     short *s_rowk = (short *)p;                    p += 2 * 256;
     unsigned short *s_rowcnt = (unsigned short *)p; p += 2 * 256;
-    uint8_t *s_ref = p;                            p += 224;
+    S.scol = (short *)p;                           p += 2 * V3_SLOTS * 2;
+    S.scode = p;                                   p += V3_SLOTS * 2;
+    S.refc = p;                                    p += 224;
     uint8_t *s_rowref = p;                         p += 256;
-    int *s_misc = (int *)p;                        // [0] fallback [1] nrec [2] npool [3] ncand [4..12] warp sums [13] nrows
-    int *s_fallback = &s_misc[0], *s_nrec = &s_misc[1], *s_npool = &s_misc[2], *s_ncand = &s_misc[3];
-    int *s_wsum = &s_misc[4], *s_nrows = &s_misc[13];
+    int *s_wsum = &S.misc[8], *s_wsum2 = &S.misc[16];
 
-    V2Shared S;
-    S.plane = s_plane; S.pool = s_pool; S.rec = s_rec; S.ops = s_ops; S.ref = s_ref;
-    S.nrec = s_nrec; S.npool = s_npool; S.fallback = s_fallback;
-
+    // ---- setup
     const long long roff = (long long)qs - a.ref_base;
     const bool ref_ok = roff >= 0 && roff + L + 1 <= a.ref_len;
-    if (tid == 0) { *s_fallback = ref_ok ? 0 : 1; *s_ncand = 0; }
-    for (int i = tid; i < L + 1; i += V2_THREADS) s_ref[i] = ref_ok ? a.ref[roff + i] : (uint8_t)'N';
-    for (int i = tid; i < NCAT * V2_CS; i += V2_THREADS) s_cnt[i] = 0;
-    for (int i = tid; i < 256; i += V2_THREADS) { s_rowcnt[i] = 0; s_rowcol[i] = -1; s_rowk[i] = 0; s_rowref[i] = 'N'; }
+    if (tid < 32) S.misc[tid] = 0;
     __syncthreads();
+    if (tid == 0 && !ref_ok) S.misc[0] = 1;
+    for (int i = tid; i < L + 1; i += V3_THREADS) {
+        const int ch = ref_ok ? a.ref[roff + i] : 'N';
+        int code = 0;
+        switch (ch) { case 'A': code = 1; break; case 'C': code = 2; break; case 'G': code = 4; break;
+                      case 'T': code = 8; break; case 'N': code = 15; break; default: break; }
+        if (code == 0) S.misc[0] = 1;                // KeyError at Pileup.py:281 if it becomes a reference pixel
+        S.refc[i] = (uint8_t)code;
+    }
+    {
+        // code -> RGBA (SNPtoRGB, Pileup.py:56-64); category 7 = insert colour; index 29.. = alpha 255
+        const uint32_t rgb[8] = {0x000000FFu, 0x0000FFFFu, 0x0000FF00u, 0x00FF0000u, 0x00FFFF00u, 0x00FFFFFFu, 0x00000000u, 0x00FF00FFu};
+        const int qi = tid & 31;
+        uint32_t col = 0;
+#pragma unroll
+        for (int k = 0; k < 8; k++) if ((tid >> 5) == k) col = rgb[k];
+        S.lut[tid] = col | ((uint32_t)(qi <= V3_QMAX ? c_qlut[qi] : 255) << 24);
+    }
+    for (int i = tid; i < NCAT * V3_CS / 2; i += V3_THREADS) S.cnt[i] = 0;
+    for (int i = tid; i < V3_CS + 8; i += V3_THREADS) S.cov[i] = 0;
+    for (int i = tid; i < V3_CS; i += V3_THREADS) S.maxins[i] = 0;
+    s_rowcnt[tid] = 0; s_rowcol[tid] = -1; s_rowk[tid] = 0; s_rowref[tid] = V3_FILL_NONE;
 
-    int populated = 0, max_ins = 0;                 // column state of thread tid (tid < L)
-    int n_batches = 0;                              // batches generated in pass A (uniform)
+    // ---- ordered compaction of the reads that pysam.fetch would return and parseRead would keep
+    int ncand = 0;
+    for (int cb = lo; cb < hi; cb += V3_THREADS) {
+        const int r = cb + tid;
+        const bool keep = r < hi && a.R.pos[r] < qe && a.endk[r] > qs;
+        const unsigned bal = __ballot_sync(0xffffffffu, keep);
+        __syncthreads();
+        if (lane == 0) s_wsum[warp] = __popc(bal);
+        __syncthreads();
+        int off = ncand, tot = 0;
+#pragma unroll
+        for (int k = 0; k < V3_WARPS; k++) { const int c = s_wsum[k]; if (k < warp) off += c; tot += c; }
+        const int idx = off + __popc(bal & ((1u << lane) - 1u));
+        if (keep && idx < V3_MAXC) S.cand[idx] = r;
+        ncand += tot;
+    }
+    __syncthreads();
+    if (ncand > V3_MAXC) { if (tid == 0) S.misc[0] = 1; ncand = 0; }
+    // ---- per read: clean?  first op to look at (checkpoint of the read's CIGAR)
+    if (tid < ncand) {
+        const int r = S.cand[tid];
+        const ReadInfo *ri = a.info + r;
+        const int flags = ri->flags;
+        if (!(flags & RI_CLEAN)) S.misc[0] = 1;
+        const int T = qs - ri->ref_start;
+        int jc = 0;
+        if (T > 0 && (flags & RI_CLEAN)) {
+            const int k = (flags >> 8) & 31;
+            jc = __ldg(a.ckpt + (ri->c0 >> 2) + r + (min(T, ri->span) >> k));
+        }
+        S.j0[tid] = jc;
+    }
+    __syncthreads();
+    if (S.misc[0]) ncand = 0;                         // bail out early: the exact kernel takes the window
+    // ---- scan: coverage and insert lengths -> row map
+    for (int ci = warp; ci < ncand; ci += V3_WARPS) v3_scan_read(a, S, ci, qs, L, lane);
+    __syncthreads();
     int my_row = -1;
-
-    // pass 0 = count (A), pass 1 = place (B)
-    for (int pass = 0; pass < 2; pass++) {
-        const bool reuse = pass == 1 && n_batches == 1;       // codes of the only batch are still in the planes
-        int cb = lo;
-        bool more_cands = !reuse && cb < hi;
-        bool first_round = true;
-        while (more_cands || (reuse && first_round)) {
-            first_round = false;
-            int total;
-            if (!reuse) {
-                // ---- ordered compaction of surviving reads (hts.c:2242 overlap, mapq cut, has an aligned base) into s_cand
-                if (tid == 0) *s_ncand = 0;
-                __syncthreads();
-                while (cb < hi && *s_ncand + V2_THREADS <= V2_CAND) {
-                    const int r = cb + tid;
-                    bool keep = false;
-                    if (r < hi) {
-                        const ReadAux ax = a.aux[r];
-                        keep = a.R.pos[r] < qe && ax.endpos > qs && (int)a.R.mapq[r] >= a.mapq_cut && ax.ref_start != INT_MIN;
-                    }
-                    const unsigned bal = __ballot_sync(0xffffffffu, keep);
-                    if (lane == 0) s_wsum[warp] = __popc(bal);
-                    __syncthreads();
-                    int off = *s_ncand, tot = 0;
-                    for (int k = 0; k < V2_WARPS; k++) { const int c = s_wsum[k]; if (k < warp) off += c; tot += c; }
-                    if (keep) s_cand[off + __popc(bal & ((1u << lane) - 1))] = r;
-                    __syncthreads();
-                    if (tid == 0) *s_ncand += tot;
-                    cb += V2_THREADS;
-                    __syncthreads();
-                }
-                total = *s_ncand;
-                more_cands = cb < hi;
-            } else total = 0;
-            const int nb = reuse ? 1 : (total + V2_SLOTS - 1) / V2_SLOTS;
-            for (int b = 0; b < nb; b++) {
-                const int nslots = reuse ? V2_SLOTS : min(V2_SLOTS, total - b * V2_SLOTS);
-                if (!reuse) {
-                    // ---- clear the planes (entry planes NONE, insert plane 0) and the batch counters
-                    uint4 *pl = reinterpret_cast<uint4 *>(s_plane);
-                    const int n16 = 3 * V2_SLOTS * V2_CS / 16, m16 = 4 * V2_SLOTS * V2_CS / 16;
-                    for (int i = tid; i < m16; i += V2_THREADS)
-                        pl[i] = i < n16 ? make_uint4(~0u, ~0u, ~0u, ~0u) : make_uint4(0u, 0u, 0u, 0u);
-                    if (tid == 0) { *s_nrec = 0; *s_npool = 0; }
-                    __syncthreads();
-                    for (int s = warp; s < nslots; s += V2_WARPS)
-                        v2_gen_read(a, S, s_cand[b * V2_SLOTS + s], s, qs, L, lane, warp);
-                    __syncthreads();
-                    if (pass == 0) n_batches++;
-                }
-                // ---- walk: thread tid owns column tid
-                if (tid < L) {
-                    const uint8_t *c0 = s_plane + tid, *ci = s_plane + 3 * V2_SLOTS * V2_CS + tid;
-                    if (pass == 0) {
-                        for (int s = 0; s < nslots; s++) {
-#pragma unroll
-                            for (int e = 0; e < 3; e++) {
-                                const uint8_t c = c0[(e * V2_SLOTS + s) * V2_CS];
-                                if (c == V2_NONE) break;
-                                s_cnt[(c >> 5) * V2_CS + tid]++;
-                                populated = 1;
-                            }
-                            const int ir = ci[s * V2_CS];
-                            if (ir) max_ins = max(max_ins, (int)(s_rec[ir - 1] >> 16));
-                        }
-                    } else if (my_row >= 0) {
-                        uint8_t *qrow = s_q + (size_t)my_row * W;
-                        for (int s = 0; s < nslots; s++) {
-#pragma unroll
-                            for (int e = 0; e < 3; e++) {
-                                const uint8_t c = c0[(e * V2_SLOTS + s) * V2_CS];
-                                if (c == V2_NONE) break;
-                                const int pos = s_cnt[(c >> 5) * V2_CS + tid]++;
-                                if (pos < W - 1) qrow[1 + pos] = c;
-                            }
-                            const int ir = ci[s * V2_CS];
-                            if (ir) {
-                                const uint32_t rc = s_rec[ir - 1];
-                                const int n = rc >> 16, off = rc & 0xffff;
-                                for (int k = 0; k < n; k++) {
-                                    const int y = my_row + 1 + k;
-                                    if (y >= H) break;
-                                    const int pos = s_rowcnt[y]++;
-                                    if (pos < W - 1) s_q[(size_t)y * W + 1 + pos] = s_pool[off + k];
-                                    else *s_fallback = 1;      // deeper than the image: the category sort needs all entries
-                                }
-                            }
-                        }
-                    }
-                }
-                __syncthreads();
+    {
+        const int cv = tid < L ? S.cov[tid] : 0;
+        const int inc1 = warp_incl_scan(cv, lane);
+        if (lane == 31) s_wsum[warp] = inc1;
+        __syncthreads();
+        int b1 = 0;
+        for (int k = 0; k < warp; k++) b1 += s_wsum[k];
+        const bool pop = tid < L && (b1 + inc1) > 0;
+        const int mi = pop ? S.maxins[tid] : 0;
+        const int v = pop ? min(1 + mi, 300) | (1 << 16) : 0;          // rows here | populated (two scans in one word)
+        const int inc2 = warp_incl_scan(v, lane);
+        if (lane == 31) s_wsum2[warp] = inc2;
+        __syncthreads();
+        int b2 = 0;
+        for (int k = 0; k < warp; k++) b2 += s_wsum2[k];
+        const int excl = b2 + inc2 - v;
+        const int rstart = excl & 0xffff, ord = excl >> 16;
+        if (tid == V3_THREADS - 1) S.misc[4] = (b2 + inc2) & 0xffff;
+        if (pop && rstart < H) {
+            my_row = rstart;
+            atomicMax(&S.misc[3], tid + 1);
+            s_rowref[rstart] = (uint8_t)((v3_cat_of_nib(S.refc[ord] ? S.refc[ord] : 15) << 5) | 29);
+            for (int k = 0; k <= mi; k++) {
+                const int y = rstart + k;
+                if (y >= H) break;
+                s_rowcol[y] = (short)tid; s_rowk[y] = (short)k;
             }
         }
-        if (pass == 0) {
-            // ---- row map (Pileup.py:295-317): rows = populated columns ascending, each followed by its insert rows
-            const int mine = (tid < L && populated) ? min(1 + max_ins, 300) : 0;   // clamp: only rows < H <= 256 matter
-            const int pop = (tid < L && populated) ? 1 : 0;
-            int v = mine | (pop << 16);                                  // two scans in one word (rows < 65536)
-            const int incl = warp_incl_scan(v, lane);
-            if (lane == 31) s_wsum[warp] = incl;
-            __syncthreads();
-            int base = 0;
-            for (int k = 0; k < warp; k++) base += s_wsum[k];
-            const int excl = base + incl - v;
-            const int rstart = excl & 0xffff, ord = excl >> 16;
-            if (tid == V2_THREADS - 1) *s_nrows = (base + incl) & 0xffff;
-            if (tid < L && populated) {
-                s_rowstart[tid] = (unsigned short)rstart;
-                s_ord[tid] = (unsigned short)ord;
-                if (cat_of_ascii(s_ref[ord]) < 0) *s_fallback = 1;       // KeyError at Pileup.py:281 on the reference pixel
-                if (rstart < H) {
-                    my_row = rstart;
-                    s_rowref[rstart] = s_ref[ord];
-                    for (int k = 0; k <= max_ins; k++) {
-                        const int y = rstart + k;
-                        if (y >= H) break;
-                        s_rowcol[y] = (short)tid; s_rowk[y] = (short)k;
-                    }
-                    // counts -> first slot of each category (sortingKey order A,C,G,T,D,M,N), total -> row count
-                    int acc = 0;
-#pragma unroll
-                    for (int c = 0; c < NCAT; c++) { const int n = s_cnt[c * V2_CS + tid]; s_cnt[c * V2_CS + tid] = (unsigned short)acc; acc = min(acc + n, 65535); }
-                    s_rowcnt[rstart] = (unsigned short)min(acc, W - 1);
+        __syncthreads();
+    }
+    const int Lgen = S.misc[3];
+    const int nrows = min(S.misc[4], H);
+
+    // ---- generate + place, V3_SLOTS reads per batch.  One batch: generate once (counting), then place.  More: a
+    // counting pass over all batches first, then each batch is generated again and placed.
+    const int nb = (ncand + V3_SLOTS - 1) / V3_SLOTS;
+    const bool multi = nb > 1;
+    const bool walker = tid < Lgen && my_row >= 0;
+    uint32_t run_lo = 0, run_hi = 0;
+    bool have_base = false;
+    for (int pass = 0; pass < (multi ? 2 : 1); pass++) {
+        for (int b = 0; b < nb; b++) {
+            const int nslots = min(V3_SLOTS, ncand - b * V3_SLOTS);
+            {
+                const int n16 = nslots * V3_CS / 16;
+                uint4 *q1 = reinterpret_cast<uint4 *>(S.p1), *q0 = reinterpret_cast<uint4 *>(S.p0);
+                uint4 *qi = reinterpret_cast<uint4 *>(S.pi);
+                for (int i = tid; i < n16; i += V3_THREADS) {
+                    q1[i] = make_uint4(~0u, ~0u, ~0u, ~0u);
+                    q0[i] = make_uint4(~0u, ~0u, ~0u, ~0u);
+                    qi[i] = make_uint4(0u, 0u, 0u, 0u);
                 }
+                if (tid == 0) { S.misc[1] = 0; S.misc[2] = 0; }
+                if (tid < nslots * 2) S.scol[tid] = -1;
             }
             __syncthreads();
+            for (int s = warp; s < nslots; s += V3_WARPS)
+                v3_gen_read(a, S, b * V3_SLOTS + s, s, qs, Lgen, pass == 0, lane, warp);
+            __syncthreads();
+            if (!multi || pass == 1) {
+                if (walker) {
+                    if (!have_base) {
+                        // counts -> first slot of each category (sortingKey order A,C,G,T,D,M,N), saturated at W
+                        int acc = 0;
+                        uint32_t blo = 0, bhi = 0;
+#pragma unroll
+                        for (int c = 0; c < NCAT; c++) {
+                            const uint32_t wv = S.cnt[(c * V3_CS + tid) >> 1];
+                            const int n = (wv >> ((tid & 1) << 4)) & 0xffff;
+                            const uint32_t bv = (uint32_t)min(acc, W - 1);
+                            if (c < 4) blo |= bv << (c << 3); else bhi |= bv << ((c - 4) << 3);
+                            acc += n;
+                        }
+                        run_lo = blo; run_hi = bhi;
+                        s_rowcnt[my_row] = (unsigned short)min(acc, W - 1);
+                        have_base = true;
+                    }
+                    v3_walk(S, tid, my_row, nslots, W, H, run_lo, run_hi, s_rowcnt);
+                }
+                __syncthreads();
+            }
         }
     }
-    const int nrows = min(*s_nrows, H);
     // ---- insert rows: stable sort by category (A,C,G,T,N) of the codes appended in read order
     if (tid < nrows && s_rowk[tid] != 0) {
-        uint8_t *row = s_q + (size_t)tid * W + 1;
+        uint8_t *row = S.q + (size_t)tid * W + 1;
         const int n = min((int)s_rowcnt[tid], W - 1);
         for (int i = 1; i < n; i++) {
             const uint8_t c = row[i];
@@ -1023,8 +1182,9 @@ encode_windows_v2_kernel(EncArgs a, int *__restrict__ fb_count, int *__restrict_
             row[j + 1] = c;
         }
     }
+    if (tid < nrows) S.q[(size_t)tid * W] = s_rowk[tid] != 0 ? V3_FILL_INS : s_rowref[tid];
     __syncthreads();
-    if (*s_fallback) {
+    if (S.misc[0]) {
         if (tid == 0) {
             const int k = atomicAdd(fb_count, 1);
             fb_list[k] = w;
@@ -1032,51 +1192,46 @@ encode_windows_v2_kernel(EncArgs a, int *__restrict__ fb_count, int *__restrict_
         }
         return;                                      // the exact kernel rewrites this window
     }
-    // ---- emit: RGBA rows, 16-byte stores
+    // ---- emit 1: filler quads straight from registers (16-byte stores)
     uint8_t *img = a.out_img + (size_t)w * H * W * 4;
-    const int quads_per_row = W / 4;
-    const int total_quads = H * quads_per_row;
-    for (int qd = tid; qd < total_quads; qd += V2_THREADS) {
-        const int y = qd / quads_per_row;
-        const int x0 = (qd - y * quads_per_row) * 4;
-        uint32_t px[4];
-        if (y >= nrows) {
-            px[0] = px[1] = px[2] = px[3] = 0xFF000000u;
-        } else {
-            const bool ins = s_rowk[y] != 0;
-            const uint32_t filler = ins ? 0xFFFF00FFu : 0xFF000000u;
-            const int tot = min((int)s_rowcnt[y], W - 1);
-            const uint32_t codes = *reinterpret_cast<const uint32_t *>(s_q + (size_t)y * W + x0);
-#pragma unroll
-            for (int t = 0; t < 4; t++) {
-                const int x = x0 + t;
-                uint32_t v;
-                if (x == 0) v = ins ? 0xFFFF00FFu : (cat_rgb(cat_of_ascii(s_rowref[y])) | 0xFF000000u);
-                else if (x - 1 >= tot) v = filler;
-                else {
-                    const uint32_t c = (codes >> (8 * t)) & 0xffu;
-                    v = cat_rgb((int)(c >> 5)) | ((uint32_t)c_qlut[c & 31u] << 24);
-                }
-                px[t] = v;
-            }
-        }
-        *reinterpret_cast<uint4 *>(img + ((size_t)y * W + x0) * 4) = make_uint4(px[0], px[1], px[2], px[3]);
+    const int qpr = W >> 2;                          // quads per row
+    const int total_quads = H * qpr;
+    for (int qd = tid; qd < total_quads; qd += V3_THREADS) {
+        const int y = (int)__umulhi((uint32_t)qd, qmagic);
+        const int x0 = (qd - y * qpr) << 2;
+        int tot = -1;
+        uint32_t fill = 0xFF000000u;
+        if (y < nrows) { tot = s_rowcnt[y]; if (s_rowk[y] != 0) fill = 0xFFFF00FFu; }
+        if (x0 > tot) *reinterpret_cast<uint4 *>(img + ((size_t)qd << 4)) = make_uint4(fill, fill, fill, fill);
     }
-    for (int y = tid; y < H; y += V2_THREADS) {
+    // ---- emit 2: quads that hold the reference pixel / entries: 16 lanes per image row
+    for (int y = tid >> 4; y < nrows; y += V3_THREADS / 16) {
+        const int tot = s_rowcnt[y];
+        const uint32_t fill = s_rowk[y] != 0 ? 0xFFFF00FFu : 0xFF000000u;
+        for (int x0 = (tid & 15) << 2; x0 <= tot; x0 += 64) {
+            const uint32_t codes = *reinterpret_cast<const uint32_t *>(S.q + (size_t)y * W + x0);
+            uint32_t px[4];
+#pragma unroll
+            for (int t = 0; t < 4; t++) px[t] = (x0 + t > tot) ? fill : S.lut[(codes >> (8 * t)) & 0xffu];
+            *reinterpret_cast<uint4 *>(img + (((size_t)y * W + x0) << 2)) = make_uint4(px[0], px[1], px[2], px[3]);
+        }
+    }
+    for (int y = tid; y < H; y += V3_THREADS) {
         if (a.out_rowpos) a.out_rowpos[(size_t)w * H + y] = (y < nrows) ? qs + s_rowcol[y] : -1;
         if (a.out_rowins) a.out_rowins[(size_t)w * H + y] = (y < nrows) ? s_rowk[y] : 0;
     }
     if (tid == 0 && a.out_status) a.out_status[w] = 0;
 }
 
-static size_t encoder_v2_smem_bytes(const dp_encode_params *p) {
+static size_t encoder_v3_smem_bytes(const dp_encode_params *p) {
     size_t s = 0;
-    s += 4 * V2_SLOTS * V2_CS;
     s += ((size_t)p->window_cutoff * p->coverage_cutoff + 15) / 16 * 16;
-    s += sizeof(Op2) * V2_WARPS * V2_OPS;
-    s += 4 * 256 + V2_POOL + 4 * V2_CAND;
-    s += 2 * NCAT * V2_CS + 2 * V2_CS * 2 + 2 * 256 * 3 + 224 + 256 + 64;
-    return s;
+    s += 3 * V3_SLOTS * V3_CS;
+    s += 4 * (NCAT * V3_CS / 2);
+    s += sizeof(Md3) * V3_WARPS * V3_MD;
+    s += 4 * 256 * 2 + V3_POOL + 4 * V3_MAXC * 2 + 4 * (V3_CS + 8) + 4 * V3_CS + 4 * 32;
+    s += 2 * V3_CS + 2 * 256 * 3 + 2 * V3_SLOTS * 2 + V3_SLOTS * 2 + 224 + 256;
+    return s + 16;
 }
 
 static size_t encoder_smem_bytes(const dp_encode_params *p) {
@@ -1128,7 +1283,22 @@ int64_t dp_encode_workspace_bytes(int32_t n_reads, int64_t n_cigar, int32_t n_wi
     b += dp::align_up((int64_t)sizeof(int) * (n_cigar + n_reads + 1), 256);   /* RP: nops+1 per read */
     b += dp::align_up((int64_t)sizeof(int) * (n_cigar + 1), 256);             /* QP */
     b += dp::align_up((int64_t)sizeof(int) * ((n_windows > 0 ? n_windows : 0) + 64), 256);   /* fallback count + list */
+    b += dp::align_up((int64_t)sizeof(dp::ReadInfo) * (n_reads > 0 ? n_reads : 1), 256);
+    b += dp::align_up((int64_t)sizeof(int) * ((n_cigar >> 2) + n_reads + 2), 256);           /* checkpoints */
+    b += dp::align_up((int64_t)sizeof(int) * (n_reads > 0 ? n_reads : 1), 256);              /* filtered endpos */
     return b;
+}
+
+int dp_encode_fallback_count(const void *workspace, int32_t n_reads, int64_t n_cigar, int32_t *out_count, void *stream) {
+    DP_REQUIRE(workspace && out_count && n_reads >= 0 && n_cigar >= 0, "bad argument");
+    const uint8_t *wp = (const uint8_t *)workspace;
+    wp += dp::align_up((int64_t)sizeof(dp::ReadAux) * (n_reads > 0 ? n_reads : 1), 256);
+    wp += dp::align_up((int64_t)sizeof(int) * (n_cigar + n_reads + 1), 256);
+    wp += dp::align_up((int64_t)sizeof(int) * (n_cigar + 1), 256);
+    cudaStream_t st = (cudaStream_t)stream;
+    DP_CUDA_CHECK(cudaMemcpyAsync(out_count, wp, sizeof(int), cudaMemcpyDeviceToHost, st));
+    DP_CUDA_CHECK(cudaStreamSynchronize(st));
+    return DP_OK;
 }
 
 int dp_encode_windows(const dp_reads *reads, int32_t n_windows, const int32_t *win_qs, const int32_t *win_lo,
@@ -1160,15 +1330,21 @@ int dp_encode_windows(const dp_reads *reads, int32_t n_windows, const int32_t *w
     int *QP = (int *)wp;
     wp += dp::align_up((int64_t)sizeof(int) * (n_cigar + 1), 256);
     int *fb = (int *)wp;                                       /* fb[0] = count, fb[64..] = window list */
+    wp += dp::align_up((int64_t)sizeof(int) * (n_windows + 64), 256);
+    dp::ReadInfo *info = (dp::ReadInfo *)wp;
+    wp += dp::align_up((int64_t)sizeof(dp::ReadInfo) * (reads->n_reads > 0 ? reads->n_reads : 1), 256);
+    int *ckpt = (int *)wp;
+    wp += dp::align_up((int64_t)sizeof(int) * ((n_cigar >> 2) + reads->n_reads + 2), 256);
+    int *endk = (int *)wp;
 
     if (reads->n_reads > 0) {
         const int warps_per_block = 8;
         const int blocks = (reads->n_reads + warps_per_block - 1) / warps_per_block;
-        dp::prep_reads_kernel<<<blocks, 256, 0, st>>>(*reads, aux, RP, QP);
+        dp::prep_reads_kernel<<<blocks, 256, 0, st>>>(*reads, aux, RP, QP, info, ckpt, endk, p->map_quality_cutoff);
         DP_CUDA_CHECK(cudaGetLastError());
     }
     dp::EncArgs a;
-    a.R = *reads; a.aux = aux; a.RP = RP; a.QP = QP;
+    a.R = *reads; a.aux = aux; a.RP = RP; a.QP = QP; a.info = info; a.ckpt = ckpt; a.endk = endk;
     a.win_qs = win_qs; a.win_lo = win_lo; a.win_hi = win_hi;
     a.ref = ref; a.ref_base = ref_base; a.ref_len = ref_len;
     a.L = L; a.W = p->coverage_cutoff; a.H = p->window_cutoff; a.mapq_cut = p->map_quality_cutoff;
@@ -1176,20 +1352,23 @@ int dp_encode_windows(const dp_reads *reads, int32_t n_windows, const int32_t *w
     const size_t smem = dp::encoder_smem_bytes(p);
     DP_REQUIRE(smem <= 227 * 1024, "coverageCutoff*windowCutoff too large for shared-memory staging");
     DP_CUDA_CHECK(cudaFuncSetAttribute(dp::encode_windows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    // fast path (v2) when the geometry fits its shared-memory planes; windows it cannot take are listed for v1
+    // fast path (v3) when the geometry fits its shared-memory planes; windows it cannot take are listed for v1
     static int force_v1 = -1;
     if (force_v1 < 0) { const char *e = getenv("DP_ENCODER"); force_v1 = (e && !strcmp(e, "v1")) ? 1 : 0; }
-    const size_t smem2 = dp::encoder_v2_smem_bytes(p);
-    const bool use_v2 = !force_v1 && dp::g_lut_flat && L <= dp::V2_CS && p->window_cutoff <= 256 &&
-                        p->coverage_cutoff <= 256 && smem2 <= 100 * 1024;
-    if (!use_v2) {
+    const size_t smem3 = dp::encoder_v3_smem_bytes(p);
+    const bool use_v3 = !force_v1 && dp::g_lut_flat && L <= dp::V3_CS && p->window_cutoff <= 256 &&
+                        p->coverage_cutoff >= 8 && p->coverage_cutoff <= 256 && smem3 <= 100 * 1024;
+    if (!use_v3) {
+        DP_CUDA_CHECK(cudaMemsetAsync(fb, 0xFF, sizeof(int), st));   /* fallback count -1: fast path not used */
         dp::encode_windows_kernel<<<n_windows, dp::ENC_THREADS, smem, st>>>(a, nullptr, nullptr);
         DP_CUDA_CHECK(cudaGetLastError());
         return DP_OK;
     }
     DP_CUDA_CHECK(cudaMemsetAsync(fb, 0, sizeof(int), st));
-    DP_CUDA_CHECK(cudaFuncSetAttribute(dp::encode_windows_v2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
-    dp::encode_windows_v2_kernel<<<n_windows, dp::V2_THREADS, smem2, st>>>(a, fb, fb + 64);
+    DP_CUDA_CHECK(cudaFuncSetAttribute(dp::encode_windows_v3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem3));
+    const uint32_t qpr = (uint32_t)p->coverage_cutoff / 4;
+    const uint32_t qmagic = (uint32_t)((0x100000000ull + qpr - 1) / qpr);
+    dp::encode_windows_v3_kernel<<<n_windows, dp::V3_THREADS, smem3, st>>>(a, fb, fb + 64, qmagic);
     DP_CUDA_CHECK(cudaGetLastError());
     dp::encode_windows_kernel<<<n_windows, dp::ENC_THREADS, smem, st>>>(a, fb, fb + 64);
     DP_CUDA_CHECK(cudaGetLastError());

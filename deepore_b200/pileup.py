@@ -114,7 +114,17 @@ class Encoder:
             rowpos.data_ptr() if want_rowmap else None, rowins.data_ptr() if want_rowmap else None,
             status.data_ptr(), ws.data_ptr(), ws.numel(), C.c_void_p(st.cuda_stream))
         _lib.check(rc, "dp_encode_windows")
+        self._last = (sb.rstruct.n_reads, sb.rstruct.n_cigar, st)
         return out_img, (rowpos if want_rowmap else None), (rowins if want_rowmap else None), status
+
+
+    def fallback_count(self) -> int:
+        """Windows of the last encode() that the fast kernel handed to the exact general kernel (diagnostic)."""
+        n_reads, n_cigar, st = self._last
+        out = C.c_int32(0)
+        _lib.check(_lib.lib().dp_encode_fallback_count(self.workspace.data_ptr(), n_reads, n_cigar, C.byref(out),
+                                                       C.c_void_p(st.cuda_stream)), "dp_encode_fallback_count")
+        return int(out.value)
 
 
 def encode_windows(reads: ReadBatch, win_qs: np.ndarray, ref: np.ndarray, ref_base: int, flank: int = 100,

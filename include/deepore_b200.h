@@ -87,6 +87,12 @@ int dp_encode_windows(const dp_reads *reads, int32_t n_windows, const int32_t *w
                       uint8_t *out_img, int32_t *out_rowpos, int32_t *out_rowins, int32_t *out_status,
                       void *workspace, int64_t workspace_bytes, void *stream);
 
+/* Diagnostics: how many windows of the LAST dp_encode_windows call on this workspace left the fast kernel's
+ * envelope and were recomputed by the exact general kernel (results are identical either way).  Synchronises
+ * the stream. */
+int dp_encode_fallback_count(const void *workspace, int32_t n_reads, int64_t n_cigar, int32_t *out_count,
+                             void *stream);
+
 /* The 256-entry quality table int(round((1-10**(q/-10))*255)) of Pileup.calculateQuality
  * (Pileup.py:166-171); evaluated once on the host with the reference's own expression and uploaded. */
 int dp_set_quality_lut(const uint8_t lut[256]);

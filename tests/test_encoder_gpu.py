@@ -74,3 +74,28 @@ def test_empty_inputs():
     # window outside the supplied reference -> DP_EINVAL status, no crash
     _, _, _, st2 = encode_windows(rb, np.asarray([700], np.int32), ref, 0)
     assert st2.cpu().numpy()[0] == -1
+
+
+def test_fast_path_takes_the_synthetic_windows():
+    """The fast kernel (not its exact fallback) must be what encodes ordinary windows, and both agree with the oracle."""
+    import pileup_oracle as po
+    from deepore_b200 import synth
+    from deepore_b200.pileup import Encoder, ShardBuffers
+    from deepore_b200.workload import make_shard
+    for cov, seed in ((30, 5), (100, 6)):
+        ref = synth.random_reference(30_000, seed=seed)
+        rb = synth.simulate_reads(ref, coverage=cov, seed=seed + 10)
+        wq = synth.window_starts(500, 29_500, stride=100)
+        shard = make_shard(rb, ref, 0, wq)
+        sb = ShardBuffers(shard, "cuda").upload()
+        enc = Encoder(device="cuda")
+        img, rowpos, rowins, status = enc.encode(sb)
+        torch.cuda.synchronize()
+        nfb = enc.fallback_count()
+        oimg, ost, orp, ori = po.encode_windows(shard.reads, shard.win_qs, shard.win_lo, shard.win_hi, shard.ref,
+                                                shard.ref_base, want_rowmap=True)
+        assert np.array_equal(status.cpu().numpy(), ost)
+        bad = [i for i in range(shard.n_windows) if not np.array_equal(img[i].cpu().numpy(), oimg[i])]
+        assert not bad, "coverage %d: windows differ: %s" % (cov, bad[:10])
+        assert np.array_equal(rowpos.cpu().numpy(), orp) and np.array_equal(rowins.cpu().numpy(), ori)
+        assert 0 <= nfb <= shard.n_windows // 10, "fast path handed %d of %d windows to the fallback" % (nfb, shard.n_windows)
