@@ -21,7 +21,8 @@ class DeeporeError(RuntimeError):
 class Reads(C.Structure):
     _fields_ = [("n_reads", C.c_int32), ("n_cigar", C.c_int64), ("pos", C.c_void_p), ("flag", C.c_void_p),
                 ("mapq", C.c_void_p), ("l_seq", C.c_void_p), ("cigar_off", C.c_void_p), ("cigar", C.c_void_p),
-                ("seq_off", C.c_void_p), ("seq4", C.c_void_p), ("qual_off", C.c_void_p), ("qual", C.c_void_p)]
+                ("seq_off", C.c_void_p), ("seq4", C.c_void_p), ("qual_off", C.c_void_p), ("qual", C.c_void_p),
+                ("n_bases", C.c_int64)]
 
 
 class EncodeParams(C.Structure):
@@ -54,7 +55,7 @@ def lib():
     L.dp_version.restype = C.c_int
     L.dp_device_count.restype = C.c_int
     L.dp_encode_workspace_bytes.restype = C.c_int64
-    L.dp_encode_workspace_bytes.argtypes = [C.c_int32, C.c_int64, C.c_int32, C.c_void_p]
+    L.dp_encode_workspace_bytes.argtypes = [C.c_int32, C.c_int64, C.c_int64, C.c_int32, C.c_void_p]
     L.dp_encode_windows.restype = C.c_int
     L.dp_encode_windows.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
                                     C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,

@@ -142,34 +142,51 @@ __global__ void __launch_bounds__(256) prep_reads_kernel(dp_reads R, ReadAux *__
     int ref_start = INT_MIN;
     bool dirty = false;
     const int op_first = nops > 0 ? (int)(R.cigar[c0] & 15) : -1;
-    for (int base = 0; base < nops; base += 32) {
-        const int j = base + lane;
-        const uint32_t w = j < nops ? R.cigar[c0 + j] : 0u;
-        const int op = w & 15, n = (int)(w >> 4);
-        const int dR = op_adv_ref(op) ? n : 0;
-        const int dQ = op_adv_read(op) ? n : 0;
-        const int dH = (op == 0 || op == 2 || op == 3 || op == 7 || op == 8) ? n : 0;   // bam_cigar2rlen
-        const int dDN = (op == 2 || op == 3) ? n : 0;
-        const int iR = warp_incl_scan(dR, lane), iQ = warp_incl_scan(dQ, lane);
-        const int iH = warp_incl_scan(dH, lane), iDN = warp_incl_scan(dDN, lane);
-        if (j < nops) {
-            RP[c0 + r + j] = carryR + iR - dR;               // nops+1 entries per read, base c0 + r
-            QP[c0 + j] = carryQ + iQ - dQ;
+    // each lane takes PK consecutive ops per round (the loads of a round are independent; one warp scan per quantity)
+    constexpr int PK = 4;
+    for (int base = 0; base < nops; base += 32 * PK) {
+        const int jb = base + lane * PK;
+        uint32_t w[PK + 2];                                  // w[0] = op before the lane's first, w[PK+1] = op after its last
+#pragma unroll
+        for (int t = 0; t < PK + 2; t++) {
+            const int j = jb + t - 1;
+            w[t] = (j >= 0 && j < nops) ? __ldg(R.cigar + c0 + j) : 0xFFFFFFFFu;
+        }
+        int sR = 0, sQ = 0, sH = 0, sDN = 0;
+#pragma unroll
+        for (int t = 1; t <= PK; t++) {
+            if (jb + t - 1 >= nops) continue;
+            const int op = w[t] & 15, n = (int)(w[t] >> 4);
+            sR += op_adv_ref(op) ? n : 0;
+            sQ += op_adv_read(op) ? n : 0;
+            sH += (op == 0 || op == 2 || op == 3 || op == 7 || op == 8) ? n : 0;   // bam_cigar2rlen
+            sDN += (op == 2 || op == 3) ? n : 0;
+        }
+        const int iR = warp_incl_scan(sR, lane), iQ = warp_incl_scan(sQ, lane);
+        const int iH = warp_incl_scan(sH, lane), iDN = warp_incl_scan(sDN, lane);
+        int eR = carryR + iR - sR, eQ = carryQ + iQ - sQ, eDN = carryDN + iDN - sDN;
+        int my_dn = INT_MIN;                                 // D/N advance before the lane's first aligned op
+#pragma unroll
+        for (int t = 1; t <= PK; t++) {
+            const int j = jb + t - 1;
+            if (j >= nops) continue;
+            const int op = w[t] & 15, n = (int)(w[t] >> 4);
+            RP[c0 + r + j] = eR;                             // nops+1 entries per read, base c0 + r
+            QP[c0 + j] = eQ;
             // ---- fast-path envelope
-            const int opp = j > 0 ? (int)(R.cigar[c0 + j - 1] & 15) : -1;
-            const int opn = j + 1 < nops ? (int)(R.cigar[c0 + j + 1] & 15) : -1;
+            const int opp = j > 0 ? (int)(w[t - 1] & 15) : -1;
+            const int opn = j + 1 < nops ? (int)(w[t + 1] & 15) : -1;
             if (!(op == 0 || op == 1 || op == 2 || op == 4) || n == 0) dirty = true;
             if (op == 4 && !(j == 0 || j == nops - 1)) dirty = true;
             if (op == 1 && (opp == 1 || opp == 4 || opn == 1 || opn == 4)) dirty = true;
             if (op != 0 && op != 4 && (j == 0 || (j == 1 && op_first == 4))) dirty = true;   // first non-S op must be M
+            if (my_dn == INT_MIN && (op == 0 || op == 7 || op == 8) && n > 0) my_dn = eDN;
+            eR += op_adv_ref(op) ? n : 0;
+            eQ += op_adv_read(op) ? n : 0;
+            eDN += (op == 2 || op == 3) ? n : 0;
         }
-        const bool aligned = j < nops && (op == 0 || op == 7 || op == 8) && n > 0;
-        const unsigned m = __ballot_sync(0xffffffffu, aligned);
-        if (ref_start == INT_MIN && m) {
-            const int f = __ffs(m) - 1;
-            const int dn_before = __shfl_sync(0xffffffffu, iDN - dDN, f);
-            ref_start = pos + carryDN + dn_before;
-        }
+        const unsigned m = __ballot_sync(0xffffffffu, my_dn != INT_MIN);
+        if (ref_start == INT_MIN && m) ref_start = pos + __shfl_sync(0xffffffffu, my_dn, __ffs(m) - 1);
         carryR += __shfl_sync(0xffffffffu, iR, 31);
         carryQ += __shfl_sync(0xffffffffu, iQ, 31);
         carryH += __shfl_sync(0xffffffffu, iH, 31);
@@ -192,13 +209,7 @@ __global__ void __launch_bounds__(256) prep_reads_kernel(dp_reads R, ReadAux *__
     }
     const int aln_len = e - s > 0 ? e - s : 0;
     const int endpos = (!(R.flag[r] & 4) && nops > 0) ? pos + carryH : pos + 1;
-    // ---- every base the reference may index must be a colour key (A,C,G,T,N)
-    const int64_t so = R.seq_off[r];
-    for (int k = lane; k < l_seq; k += 32) {
-        const uint8_t b = R.seq4[so + (k >> 1)];
-        const int nib = (k & 1) ? (b & 15) : (b >> 4);
-        if (!((0x8116u >> nib) & 1u)) dirty = true;
-    }
+    const int64_t so = R.seq_off[r], qo = R.qual_off[r];
     if (carryQ != aln_len || aln_len <= 0 || ref_start != pos || carryR <= 0) dirty = true;
     dirty = __any_sync(0xffffffffu, dirty);
     // ---- checkpoints: ckpt[m] = first op j with RP[j+1] >= m << k ; at most nops/4 + 1 of them per read
@@ -207,15 +218,26 @@ __global__ void __launch_bounds__(256) prep_reads_kernel(dp_reads R, ReadAux *__
     const int64_t ckb = (c0 >> 2) + r;
     {
         int cR = 0;
-        for (int base = 0; base < nops; base += 32) {
-            const int j = base + lane;
-            const uint32_t w = j < nops ? R.cigar[c0 + j] : 0u;
-            const int op = w & 15, n = (int)(w >> 4);
-            const int dR = op_adv_ref(op) ? n : 0;
-            const int iR = warp_incl_scan(dR, lane);
-            if (dR > 0) {
-                const int a0 = cR + iR - dR, b0 = cR + iR;
-                for (int m = (a0 >> k) + 1; m <= (b0 >> k); m++) ckpt[ckb + m] = j;
+        for (int base = 0; base < nops; base += 32 * PK) {
+            const int jb = base + lane * PK;
+            int dR[PK];
+            int sR = 0;
+#pragma unroll
+            for (int t = 0; t < PK; t++) {
+                const uint32_t w = jb + t < nops ? __ldg(R.cigar + c0 + jb + t) : 0u;
+                const int op = w & 15;
+                dR[t] = op_adv_ref(op) ? (int)(w >> 4) : 0;
+                sR += dR[t];
+            }
+            const int iR = warp_incl_scan(sR, lane);
+            int a0 = cR + iR - sR;
+#pragma unroll
+            for (int t = 0; t < PK; t++) {
+                if (dR[t] > 0) {
+                    const int b0 = a0 + dR[t];
+                    for (int m = (a0 >> k) + 1; m <= (b0 >> k); m++) ckpt[ckb + m] = jb + t;
+                    a0 = b0;
+                }
             }
             cR += __shfl_sync(0xffffffffu, iR, 31);
         }
@@ -238,10 +260,42 @@ __global__ void __launch_bounds__(256) prep_reads_kernel(dp_reads R, ReadAux *__
         ri.mapq28 = mq < 28 ? mq : 28;
         ri.nops = nops;
         ri.flags = (dirty ? 0 : RI_CLEAN) | (k << 8);
-        ri.c0 = c0; ri.seq_off = so; ri.qual_off = R.qual_off[r];
+        ri.c0 = c0; ri.seq_off = so; ri.qual_off = qo;
         ri.span = carryR; ri.pad = 0;
         info[r] = ri;
         endk[r] = ri.endk;
+    }
+}
+
+// Per-base code bytes of the fast path, one thread per query base (runs after prep_reads_kernel): entry idx of a
+// read pairs the base at ALIGNED index idx (query index idx + leading clip) with the quality at FULL-query index
+// idx -- the pairing parseRead makes (Pileup.py:184,197) -- as  own category << 5 | min(quality, mapq, 28).
+// A base outside {A,C,G,T,N} (KeyError in the reference) clears the read's clean flag.
+__global__ void __launch_bounds__(256) base_codes_kernel(dp_reads R, ReadInfo *__restrict__ info,
+                                                         uint8_t *__restrict__ code0) {
+    const int64_t n = R.n_bases;
+    for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < n; k += (int64_t)gridDim.x * blockDim.x) {
+        int lo = 0, hi = R.n_reads;                   // read r with qual_off[r] <= k < qual_off[r+1]
+        while (hi - lo > 1) {
+            const int mid = (lo + hi) >> 1;
+            if (__ldg(R.qual_off + mid) <= k) lo = mid; else hi = mid;
+        }
+        const int r = lo;
+        const ReadInfo *ri = info + r;
+        const int idx = (int)(k - ri->qual_off);
+        const int l_seq = ri->l_seq;
+        const uint8_t *seqp = R.seq4 + ri->seq_off;
+        const uint8_t b = __ldg(seqp + (idx >> 1));
+        const int nib = (idx & 1) ? (b & 15) : (b >> 4);
+        if (!((0x8116u >> nib) & 1u)) atomicAnd(&info[r].flags, ~RI_CLEAN);
+        const int kb = idx + ri->aln_start;
+        int cat = 0;
+        if (kb < l_seq) {
+            const uint8_t b2 = __ldg(seqp + (kb >> 1));
+            const int nib2 = (kb & 1) ? (b2 & 15) : (b2 >> 4);
+            cat = nib2 == 15 ? CAT_N : ((__ffs(nib2) - 1) & 3);
+        }
+        code0[k] = (uint8_t)((cat << 5) | min((int)__ldg(R.qual + k), ri->mapq28));
     }
 }
 
@@ -277,6 +331,7 @@ struct EncArgs {
     const ReadInfo *info;      // fast path (v3) digest, checkpoints and filtered end positions
     const int *ckpt;
     const int *endk;
+    const uint8_t *code0;      // per query base: own category << 5 | min(quality, mapq, 28), indexed like qual[]
     const int32_t *win_qs, *win_lo, *win_hi;
     const uint8_t *ref;
     long long ref_base, ref_len;
@@ -782,21 +837,15 @@ struct V3S {
     uint32_t *rec;               // [256] n << 16 | pool offset
     int *cand, *j0;              // [V3_MAXC]
     int *cov, *maxins;           // [V3_CS + 8], [V3_CS]
-    uint8_t *refc;               // [224] 4-bit codes of refSequence
+    uint8_t *refc;               // [224] categories (A,C,G,T,N) of refSequence
     uint8_t *scode;              // [V3_SLOTS][2] soft-clip step codes (leading, trailing)
     short *scol;                 // [V3_SLOTS][2]
     int *misc;                   // [0] fallback [1] nrec [2] npool [3] Lgen [4] nrows [5] hasS [8..16] warp sums [16..24] warp sums 2
 };
 
-__device__ __forceinline__ int v3_cat_of_nib(int nib) { return nib == 15 ? CAT_N : __ffs(nib) - 1; }
 __device__ __forceinline__ void v3_count(const V3S &S, int cat, int c) {
     atomicAdd(&S.cnt[(cat * V3_CS + c) >> 1], 1u << ((c & 1) << 4));
 }
-__device__ __forceinline__ int v3_nib(const uint8_t *__restrict__ seqp, int k) {
-    const uint8_t b = __ldg(seqp + (k >> 1));
-    return (b >> ((~k & 1) << 2)) & 15;
-}
-
 // scan: one warp; coverage difference array and insert lengths of read `r`; first relevant op -> S.j0[ci]
 __device__ void v3_scan_read(const EncArgs &a, const V3S &S, int ci, int qs, int L, int lane) {
     const int r = S.cand[ci];
@@ -839,11 +888,10 @@ __device__ void v3_gen_read(const EncArgs &a, const V3S &S, int ci, int slot, in
     const int r = S.cand[ci];
     const ReadInfo *ri = a.info + r;
     const int ref_start = ri->ref_start, nops = ri->nops;
-    const int aln_start = ri->aln_start, aln_len = ri->aln_len, l_seq = ri->l_seq, mapq28 = ri->mapq28;
+    const int aln_len = ri->aln_len, l_seq = ri->l_seq;
     const long long c0 = ri->c0;
     const long long rpb = c0 + r;
-    const uint8_t *__restrict__ seqp = a.R.seq4 + ri->seq_off;
-    const uint8_t *__restrict__ qualp = a.R.qual + ri->qual_off;
+    const uint8_t *__restrict__ codep = a.code0 + ri->qual_off;
     Md3 *md = S.md + warp * V3_MD;
     uint8_t *p1 = S.p1 + slot * V3_CS, *p0 = S.p0 + slot * V3_CS, *pi = S.pi + slot * V3_CS;
     const unsigned lt = (1u << lane) - 1u;
@@ -877,26 +925,27 @@ __device__ void v3_gen_read(const EncArgs &a, const V3S &S, int ci, int slot, in
         nmd += __popc(mdm);
         // ---- op-parallel part
         if (relevant && sA >= 0) {
-            if (op == 0 || op == 2 || op == 4) {
-                // step 0 of the op: previous query base (index -1 wraps, Python), reference character one to the left
-                const int si = qp < 0 ? qp + aln_len : qp, qi = qp < 0 ? qp + l_seq : qp;
+            if (op != 1) {
+                // step 0 of an M/D op, or the single step of a soft clip: previous query base (index -1 wraps like
+                // Python: last aligned base, last quality of the full query), reference character one to the left
                 const int rel = sA - 1 + shift;
-                if (rel < 0 || si < 0 || qi < 0) bad = true;
+                if (rel < 0) bad = true;
                 else {
-                    const int nib = v3_nib(seqp, si + aln_start);
-                    const int q = min((int)__ldg(qualp + qi), mapq28);
-                    const int cat = op == 2 ? CAT_D : (nib == S.refc[rel] ? CAT_M : v3_cat_of_nib(nib));
-                    const uint8_t code = (uint8_t)((cat << 5) | q);
+                    int cb;
+                    if (qp >= 0) cb = __ldg(codep + qp);
+                    else cb = (__ldg(codep + aln_len - 1) & 0xE0) | (__ldg(codep + l_seq - 1) & 31);
+                    int cat = cb >> 5;
+                    if (op == 2) cat = CAT_D; else if (cat == S.refc[rel]) cat = CAT_M;
+                    const uint8_t code = (uint8_t)((cat << 5) | (cb & 31));
                     if (op == 4) {
                         const int which = jj == 0 ? 0 : 1;
                         S.scode[slot * 2 + which] = code;
                         S.scol[slot * 2 + which] = (short)sA;
                         pi[sA] = 255;
-                        S.misc[5] = 1;
                     } else p0[sA] = code;
                     if (count) v3_count(S, cat, sA);
                 }
-            } else if (op == 1 && sA >= 1) {
+            } else if (sA >= 1) {
                 // insertion anchored at column sA (Pileup.py:220-230): bases qp+1 .. qp+n
                 const int rec = atomicAdd(&S.misc[1], 1);
                 const int off = atomicAdd(&S.misc[2], n);
@@ -904,11 +953,7 @@ __device__ void v3_gen_read(const EncArgs &a, const V3S &S, int ci, int slot, in
                 else {
                     S.rec[rec] = ((uint32_t)n << 16) | (uint32_t)off;
                     pi[sA] = (uint8_t)(rec + 1);
-                    for (int k2 = 0; k2 < n; k2++) {
-                        const int idx = qp + 1 + k2;
-                        const int nib = v3_nib(seqp, idx + aln_start);
-                        S.pool[off + k2] = (uint8_t)((v3_cat_of_nib(nib) << 5) | min((int)__ldg(qualp + idx), mapq28));
-                    }
+                    for (int k2 = 0; k2 < n; k2++) S.pool[off + k2] = __ldg(codep + qp + 1 + k2);
                 }
             }
         }
@@ -929,18 +974,15 @@ __device__ void v3_gen_read(const EncArgs &a, const V3S &S, int ci, int slot, in
         Md3 m = md[jm];
         int end = m.endD >> 1;
         const int cEnd = min(cA + cpl, Lgen);
+        const uint8_t *refs = S.refc + shift;
         for (int c = cA; c < cEnd; c++) {
             if (c >= end && jm + 1 < nmd) { jm++; m = md[jm]; end = m.endD >> 1; }
             if (c >= m.sA && c < end - 1) {
                 const bool isD = m.endD & 1;
-                const int idx = m.qadj + (isD ? 0 : c);
-                const int q = min((int)__ldg(qualp + idx), mapq28);
-                int cat = CAT_D;
-                if (!isD) {
-                    const int nib = v3_nib(seqp, idx + aln_start);
-                    cat = nib == S.refc[c + shift] ? CAT_M : v3_cat_of_nib(nib);
-                }
-                p1[c] = (uint8_t)((cat << 5) | q);
+                const int cb = __ldg(codep + m.qadj + (isD ? 0 : c));
+                int cat = cb >> 5;
+                if (isD) cat = CAT_D; else if (cat == refs[c]) cat = CAT_M;
+                p1[c] = (uint8_t)((cat << 5) | (cb & 31));
                 if (count) v3_count(S, cat, c);
             }
         }
@@ -987,7 +1029,7 @@ __device__ void v3_walk(const V3S &S, int c, int my_row, int nslots, int W, int 
 }
 
 __global__ void __launch_bounds__(V3_THREADS, 3)
-encode_windows_v3_kernel(EncArgs a, int *__restrict__ fb_count, int *__restrict__ fb_list, uint32_t qmagic) {
+encode_windows_v3_kernel(EncArgs a, int *__restrict__ fb_count, int *__restrict__ fb_list, int emit_mode) {
     extern __shared__ __align__(16) uint8_t smem[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int w = blockIdx.x;
@@ -1012,6 +1054,7 @@ encode_windows_v3_kernel(EncArgs a, int *__restrict__ fb_count, int *__restrict_
     S.cov = (int *)p;                              p += 4 * (V3_CS + 8);
     S.maxins = (int *)p;                           p += 4 * V3_CS;
     S.misc = (int *)p;                             p += 4 * 32;
+    uint32_t *s_fill = (uint32_t *)p;              p += 4 * 2 * 256;       // two constant filler rows (none / insert)
     unsigned short *s_rowstart = (unsigned short *)p; p += 2 * V3_CS;
     short *s_rowcol = (short *)p;                  p += 2 * 256;
     short *s_rowk = (short *)p;                    p += 2 * 256;
@@ -1030,10 +1073,10 @@ encode_windows_v3_kernel(EncArgs a, int *__restrict__ fb_count, int *__restrict_
     if (tid == 0 && !ref_ok) S.misc[0] = 1;
     for (int i = tid; i < L + 1; i += V3_THREADS) {
         const int ch = ref_ok ? a.ref[roff + i] : 'N';
-        int code = 0;
-        switch (ch) { case 'A': code = 1; break; case 'C': code = 2; break; case 'G': code = 4; break;
-                      case 'T': code = 8; break; case 'N': code = 15; break; default: break; }
-        if (code == 0) S.misc[0] = 1;                // KeyError at Pileup.py:281 if it becomes a reference pixel
+        int code = 7;
+        switch (ch) { case 'A': code = CAT_A; break; case 'C': code = CAT_C; break; case 'G': code = CAT_G; break;
+                      case 'T': code = CAT_T; break; case 'N': code = CAT_N; break; default: break; }
+        if (code == 7) S.misc[0] = 1;                // KeyError at Pileup.py:281 if it becomes a reference pixel
         S.refc[i] = (uint8_t)code;
     }
     {
@@ -1085,7 +1128,13 @@ encode_windows_v3_kernel(EncArgs a, int *__restrict__ fb_count, int *__restrict_
     __syncthreads();
     if (S.misc[0]) ncand = 0;                         // bail out early: the exact kernel takes the window
     // ---- scan: coverage and insert lengths -> row map
-    for (int ci = warp; ci < ncand; ci += V3_WARPS) v3_scan_read(a, S, ci, qs, L, lane);
+    for (;;) {                                        // warps draw reads from a shared counter (uneven CIGAR density)
+        int ci = 0;
+        if (lane == 0) ci = atomicAdd(&S.misc[6], 1);
+        ci = __shfl_sync(0xffffffffu, ci, 0);
+        if (ci >= ncand) break;
+        v3_scan_read(a, S, ci, qs, L, lane);
+    }
     __syncthreads();
     int my_row = -1;
     {
@@ -1109,7 +1158,7 @@ encode_windows_v3_kernel(EncArgs a, int *__restrict__ fb_count, int *__restrict_
         if (pop && rstart < H) {
             my_row = rstart;
             atomicMax(&S.misc[3], tid + 1);
-            s_rowref[rstart] = (uint8_t)((v3_cat_of_nib(S.refc[ord] ? S.refc[ord] : 15) << 5) | 29);
+            s_rowref[rstart] = (uint8_t)((S.refc[ord] << 5) | 29);
             for (int k = 0; k <= mi; k++) {
                 const int y = rstart + k;
                 if (y >= H) break;
@@ -1140,12 +1189,17 @@ encode_windows_v3_kernel(EncArgs a, int *__restrict__ fb_count, int *__restrict_
                     q0[i] = make_uint4(~0u, ~0u, ~0u, ~0u);
                     qi[i] = make_uint4(0u, 0u, 0u, 0u);
                 }
-                if (tid == 0) { S.misc[1] = 0; S.misc[2] = 0; }
+                if (tid == 0) { S.misc[1] = 0; S.misc[2] = 0; S.misc[7] = 0; }
                 if (tid < nslots * 2) S.scol[tid] = -1;
             }
             __syncthreads();
-            for (int s = warp; s < nslots; s += V3_WARPS)
+            for (;;) {
+                int s = 0;
+                if (lane == 0) s = atomicAdd(&S.misc[7], 1);
+                s = __shfl_sync(0xffffffffu, s, 0);
+                if (s >= nslots) break;
                 v3_gen_read(a, S, b * V3_SLOTS + s, s, qs, Lgen, pass == 0, lane, warp);
+            }
             __syncthreads();
             if (!multi || pass == 1) {
                 if (walker) {
@@ -1182,7 +1236,14 @@ encode_windows_v3_kernel(EncArgs a, int *__restrict__ fb_count, int *__restrict_
             row[j + 1] = c;
         }
     }
-    if (tid < nrows) S.q[(size_t)tid * W] = s_rowk[tid] != 0 ? V3_FILL_INS : s_rowref[tid];
+    if (tid < nrows) {
+        // pixel 0 (reference / insert colour) and filler codes up to the end of the last entry quad
+        const bool ins = s_rowk[tid] != 0;
+        uint8_t *row = S.q + (size_t)tid * W;
+        row[0] = ins ? V3_FILL_INS : s_rowref[tid];
+        const int tot = min((int)s_rowcnt[tid], W - 1);
+        for (int x = tot + 1; x < W && (x & 3); x++) row[x] = ins ? V3_FILL_INS : V3_FILL_NONE;
+    }
     __syncthreads();
     if (S.misc[0]) {
         if (tid == 0) {
@@ -1192,28 +1253,49 @@ encode_windows_v3_kernel(EncArgs a, int *__restrict__ fb_count, int *__restrict_
         }
         return;                                      // the exact kernel rewrites this window
     }
-    // ---- emit 1: filler quads straight from registers (16-byte stores)
+    // ---- emit 1: the filler tail of every row (and blank rows) -- one bulk copy (TMA) per row out of two constant
+    // filler rows in shared memory; emit_mode 1 = plain 16-byte stores instead (one thread per quad column)
     uint8_t *img = a.out_img + (size_t)w * H * W * 4;
     const int qpr = W >> 2;                          // quads per row
-    const int total_quads = H * qpr;
-    for (int qd = tid; qd < total_quads; qd += V3_THREADS) {
-        const int y = (int)__umulhi((uint32_t)qd, qmagic);
-        const int x0 = (qd - y * qpr) << 2;
-        int tot = -1;
-        uint32_t fill = 0xFF000000u;
-        if (y < nrows) { tot = s_rowcnt[y]; if (s_rowk[y] != 0) fill = 0xFFFF00FFu; }
-        if (x0 > tot) *reinterpret_cast<uint4 *>(img + ((size_t)qd << 4)) = make_uint4(fill, fill, fill, fill);
+    if (emit_mode == 0) {
+        for (int i = tid; i < W; i += V3_THREADS) { s_fill[i] = 0xFF000000u; s_fill[W + i] = 0xFFFF00FFu; }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        __syncthreads();
+        for (int y = tid; y < H; y += V3_THREADS) {
+            const int tot = y < nrows ? (int)s_rowcnt[y] : -1;
+            const int xq = ((tot + 4) >> 2) << 2;    // first pixel of the first all-filler quad
+            const int bytes = (W - xq) << 2;
+            if (bytes > 0) {
+                const uint32_t src = (uint32_t)__cvta_generic_to_shared(s_fill + ((y < nrows && s_rowk[y] != 0) ? W : 0));
+                uint8_t *dst = img + (((size_t)y * W + xq) << 2);
+                asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
+                             :: "l"(dst), "r"(src), "r"(bytes) : "memory");
+            }
+        }
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+    } else {
+        const int rpi = V3_THREADS / qpr;            // rows per iteration
+        const int ty = tid / qpr, tx = tid - ty * qpr;
+        if (ty < rpi) {
+            const int x0 = tx << 2;
+            for (int y = ty; y < H; y += rpi) {
+                int tot = -1;
+                uint32_t fill = 0xFF000000u;
+                if (y < nrows) { tot = s_rowcnt[y]; if (s_rowk[y] != 0) fill = 0xFFFF00FFu; }
+                if (x0 > tot) *reinterpret_cast<uint4 *>(img + (((size_t)y * W + x0) << 2)) = make_uint4(fill, fill, fill, fill);
+            }
+        }
     }
-    // ---- emit 2: quads that hold the reference pixel / entries: 16 lanes per image row
+    // ---- emit 2: quads that hold the reference pixel / entries: 16 lanes per image row, code -> RGBA by table
     for (int y = tid >> 4; y < nrows; y += V3_THREADS / 16) {
         const int tot = s_rowcnt[y];
-        const uint32_t fill = s_rowk[y] != 0 ? 0xFFFF00FFu : 0xFF000000u;
+        const uint8_t *row = S.q + (size_t)y * W;
+        uint8_t *orow = img + (((size_t)y * W) << 2);
         for (int x0 = (tid & 15) << 2; x0 <= tot; x0 += 64) {
-            const uint32_t codes = *reinterpret_cast<const uint32_t *>(S.q + (size_t)y * W + x0);
-            uint32_t px[4];
-#pragma unroll
-            for (int t = 0; t < 4; t++) px[t] = (x0 + t > tot) ? fill : S.lut[(codes >> (8 * t)) & 0xffu];
-            *reinterpret_cast<uint4 *>(img + (((size_t)y * W + x0) << 2)) = make_uint4(px[0], px[1], px[2], px[3]);
+            const uint32_t codes = *reinterpret_cast<const uint32_t *>(row + x0);
+            const uint32_t p0 = S.lut[codes & 0xffu], p1 = S.lut[(codes >> 8) & 0xffu];
+            const uint32_t p2 = S.lut[(codes >> 16) & 0xffu], p3 = S.lut[codes >> 24];
+            *reinterpret_cast<uint4 *>(orow + (x0 << 2)) = make_uint4(p0, p1, p2, p3);
         }
     }
     for (int y = tid; y < H; y += V3_THREADS) {
@@ -1221,6 +1303,7 @@ encode_windows_v3_kernel(EncArgs a, int *__restrict__ fb_count, int *__restrict_
         if (a.out_rowins) a.out_rowins[(size_t)w * H + y] = (y < nrows) ? s_rowk[y] : 0;
     }
     if (tid == 0 && a.out_status) a.out_status[w] = 0;
+    if (emit_mode == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // shared memory must outlive the copies
 }
 
 static size_t encoder_v3_smem_bytes(const dp_encode_params *p) {
@@ -1230,7 +1313,7 @@ static size_t encoder_v3_smem_bytes(const dp_encode_params *p) {
     s += 4 * (NCAT * V3_CS / 2);
     s += sizeof(Md3) * V3_WARPS * V3_MD;
     s += 4 * 256 * 2 + V3_POOL + 4 * V3_MAXC * 2 + 4 * (V3_CS + 8) + 4 * V3_CS + 4 * 32;
-    s += 2 * V3_CS + 2 * 256 * 3 + 2 * V3_SLOTS * 2 + V3_SLOTS * 2 + 224 + 256;
+    s += 2 * V3_CS + 2 * 256 * 3 + 2 * V3_SLOTS * 2 + V3_SLOTS * 2 + 224 + 256 + 4 * 2 * 256;
     return s + 16;
 }
 
@@ -1276,7 +1359,8 @@ int dp_set_quality_lut(const uint8_t lut[256]) {
     return DP_OK;
 }
 
-int64_t dp_encode_workspace_bytes(int32_t n_reads, int64_t n_cigar, int32_t n_windows, const dp_encode_params *p) {
+int64_t dp_encode_workspace_bytes(int32_t n_reads, int64_t n_cigar, int64_t n_bases, int32_t n_windows,
+                                  const dp_encode_params *p) {
     (void)p;
     int64_t b = 0;
     b += dp::align_up((int64_t)sizeof(dp::ReadAux) * (n_reads > 0 ? n_reads : 1), 256);
@@ -1286,6 +1370,7 @@ int64_t dp_encode_workspace_bytes(int32_t n_reads, int64_t n_cigar, int32_t n_wi
     b += dp::align_up((int64_t)sizeof(dp::ReadInfo) * (n_reads > 0 ? n_reads : 1), 256);
     b += dp::align_up((int64_t)sizeof(int) * ((n_cigar >> 2) + n_reads + 2), 256);           /* checkpoints */
     b += dp::align_up((int64_t)sizeof(int) * (n_reads > 0 ? n_reads : 1), 256);              /* filtered endpos */
+    b += dp::align_up((n_bases > 0 ? n_bases : 0) + 16, 256);                                /* per-base code bytes */
     return b;
 }
 
@@ -1320,7 +1405,8 @@ int dp_encode_windows(const dp_reads *reads, int32_t n_windows, const int32_t *w
 
     const int64_t n_cigar = reads->n_cigar;
     DP_REQUIRE(n_cigar >= 0, "negative n_cigar");
-    const int64_t need = dp_encode_workspace_bytes(reads->n_reads, n_cigar, n_windows, p);
+    DP_REQUIRE(reads->n_bases >= 0, "negative n_bases");
+    const int64_t need = dp_encode_workspace_bytes(reads->n_reads, n_cigar, reads->n_bases, n_windows, p);
     DP_REQUIRE(workspace && workspace_bytes >= need, "workspace too small (dp_encode_workspace_bytes)");
     uint8_t *wp = (uint8_t *)workspace;
     dp::ReadAux *aux = (dp::ReadAux *)wp;
@@ -1336,15 +1422,22 @@ int dp_encode_windows(const dp_reads *reads, int32_t n_windows, const int32_t *w
     int *ckpt = (int *)wp;
     wp += dp::align_up((int64_t)sizeof(int) * ((n_cigar >> 2) + reads->n_reads + 2), 256);
     int *endk = (int *)wp;
+    wp += dp::align_up((int64_t)sizeof(int) * (reads->n_reads > 0 ? reads->n_reads : 1), 256);
+    uint8_t *code0 = wp;
 
     if (reads->n_reads > 0) {
         const int warps_per_block = 8;
         const int blocks = (reads->n_reads + warps_per_block - 1) / warps_per_block;
         dp::prep_reads_kernel<<<blocks, 256, 0, st>>>(*reads, aux, RP, QP, info, ckpt, endk, p->map_quality_cutoff);
         DP_CUDA_CHECK(cudaGetLastError());
+        if (reads->n_bases > 0) {
+            const int64_t nb = (reads->n_bases + 255) / 256;
+            dp::base_codes_kernel<<<(unsigned)(nb < 148 * 64 ? nb : 148 * 64), 256, 0, st>>>(*reads, info, code0);
+            DP_CUDA_CHECK(cudaGetLastError());
+        }
     }
     dp::EncArgs a;
-    a.R = *reads; a.aux = aux; a.RP = RP; a.QP = QP; a.info = info; a.ckpt = ckpt; a.endk = endk;
+    a.R = *reads; a.aux = aux; a.RP = RP; a.QP = QP; a.info = info; a.ckpt = ckpt; a.endk = endk; a.code0 = code0;
     a.win_qs = win_qs; a.win_lo = win_lo; a.win_hi = win_hi;
     a.ref = ref; a.ref_base = ref_base; a.ref_len = ref_len;
     a.L = L; a.W = p->coverage_cutoff; a.H = p->window_cutoff; a.mapq_cut = p->map_quality_cutoff;
@@ -1366,9 +1459,9 @@ int dp_encode_windows(const dp_reads *reads, int32_t n_windows, const int32_t *w
     }
     DP_CUDA_CHECK(cudaMemsetAsync(fb, 0, sizeof(int), st));
     DP_CUDA_CHECK(cudaFuncSetAttribute(dp::encode_windows_v3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem3));
-    const uint32_t qpr = (uint32_t)p->coverage_cutoff / 4;
-    const uint32_t qmagic = (uint32_t)((0x100000000ull + qpr - 1) / qpr);
-    dp::encode_windows_v3_kernel<<<n_windows, dp::V3_THREADS, smem3, st>>>(a, fb, fb + 64, qmagic);
+    static int emit_mode = -1;                                 /* DP_ENC_EMIT=stg: plain stores instead of bulk copies */
+    if (emit_mode < 0) { const char *e = getenv("DP_ENC_EMIT"); emit_mode = (e && !strcmp(e, "stg")) ? 1 : 0; }
+    dp::encode_windows_v3_kernel<<<n_windows, dp::V3_THREADS, smem3, st>>>(a, fb, fb + 64, emit_mode);
     DP_CUDA_CHECK(cudaGetLastError());
     dp::encode_windows_kernel<<<n_windows, dp::ENC_THREADS, smem, st>>>(a, fb, fb + 64);
     DP_CUDA_CHECK(cudaGetLastError());

@@ -59,7 +59,7 @@ class ShardBuffers:
         base = self.dev.data_ptr()
         p = {n: base + o for n, o in self.off.items()}
         self.rstruct = _lib.Reads(rb.n_reads, rb.n_cigar, p["pos"], p["flag"], p["mapq"], p["l_seq"], p["cigar_off"],
-                                  p["cigar"], p["seq_off"], p["seq4"], p["qual_off"], p["qual"])
+                                  p["cigar"], p["seq_off"], p["seq4"], p["qual_off"], p["qual"], int(rb.qual.shape[0]))
         self.ptr = p
         self.n_windows = shard.n_windows
         self.ref_base = int(shard.ref_base)
@@ -84,8 +84,8 @@ class Encoder:
         self.flank, self.W, self.H = flank, coverageCutoff, windowCutoff
         self.workspace = None
 
-    def _workspace(self, n_reads, n_cigar, n_windows):
-        need = int(_lib.lib().dp_encode_workspace_bytes(n_reads, n_cigar, n_windows, C.byref(self.params)))
+    def _workspace(self, n_reads, n_cigar, n_bases, n_windows):
+        need = int(_lib.lib().dp_encode_workspace_bytes(n_reads, n_cigar, n_bases, n_windows, C.byref(self.params)))
         if self.workspace is None or self.workspace.numel() < need:
             self.workspace = self.torch.empty(max(need, 256), dtype=self.torch.uint8, device=self.device)
         return self.workspace
@@ -106,7 +106,7 @@ class Encoder:
                 rowins = torch.empty((nw, self.H), dtype=torch.int32, device=dev)
         if status is None:
             status = torch.empty((nw,), dtype=torch.int32, device=dev)
-        ws = self._workspace(sb.rstruct.n_reads, sb.rstruct.n_cigar, nw)
+        ws = self._workspace(sb.rstruct.n_reads, sb.rstruct.n_cigar, sb.rstruct.n_bases, nw)
         st = stream if stream is not None else torch.cuda.current_stream(dev)
         rc = _lib.lib().dp_encode_windows(
             C.byref(sb.rstruct), nw, sb.ptr["win_qs"], sb.ptr["win_lo"], sb.ptr["win_hi"], sb.ptr["ref"],

@@ -45,6 +45,7 @@ typedef struct dp_reads {
     const uint8_t *seq4;       /* 4-bit packed bases, high nibble first, alphabet "=ACMGRSVTWYHKDBN"   */
     const int64_t *qual_off;   /* [n_reads+1] byte offsets into qual[]; read i has l_seq bytes         */
     const uint8_t *qual;       /* phred bytes of the FULL query (soft clips included)                  */
+    int64_t        n_bases;    /* total query bases == qual_off[n_reads] (known to the host reader)     */
 } dp_reads;
 
 /* ---- encoder parameters == keyword arguments of PileUpGenerator.generatePileup (Pileup.py:418) */
@@ -78,7 +79,7 @@ int  dp_device_count(void);
  *   out_status   optional [n_windows] int32: 0 or a DP_E* code raised inside that window
  *   workspace    device scratch of at least dp_encode_workspace_bytes(...) bytes (may be NULL if 0)
  */
-int64_t dp_encode_workspace_bytes(int32_t n_reads, int64_t n_cigar, int32_t n_windows,
+int64_t dp_encode_workspace_bytes(int32_t n_reads, int64_t n_cigar, int64_t n_bases, int32_t n_windows,
                                   const dp_encode_params *p);
 int dp_encode_windows(const dp_reads *reads, int32_t n_windows, const int32_t *win_qs,
                       const int32_t *win_lo, const int32_t *win_hi,

@@ -18,7 +18,8 @@ QUALITY_LUT = np.array([int(round((1 - (10 ** ((q) / -10))) * 255)) for q in ran
 class _Reads(C.Structure):
     _fields_ = [("n_reads", C.c_int32), ("n_cigar", C.c_int64), ("pos", C.c_void_p), ("flag", C.c_void_p), ("mapq", C.c_void_p),
                 ("l_seq", C.c_void_p), ("cigar_off", C.c_void_p), ("cigar", C.c_void_p),
-                ("seq_off", C.c_void_p), ("seq4", C.c_void_p), ("qual_off", C.c_void_p), ("qual", C.c_void_p)]
+                ("seq_off", C.c_void_p), ("seq4", C.c_void_p), ("qual_off", C.c_void_p), ("qual", C.c_void_p),
+                ("n_bases", C.c_int64)]
 
 
 class _Params(C.Structure):
@@ -65,7 +66,7 @@ def encode_windows(reads, win_qs, win_lo, win_hi, ref, ref_base, flank=100, cove
     R = _Reads(int(reads.pos.shape[0]), int(reads.cigar.shape[0]), c(reads.pos, np.int32), c(reads.flag, np.uint16), c(reads.mapq, np.uint8),
                c(reads.l_seq, np.int32), c(reads.cigar_off, np.int64), c(reads.cigar, np.uint32),
                c(reads.seq_off, np.int64), c(reads.seq4, np.uint8), c(reads.qual_off, np.int64),
-               c(reads.qual, np.uint8))
+               c(reads.qual, np.uint8), int(reads.qual.shape[0]))
     P = _Params(flank, coverage_cutoff, window_cutoff, map_quality_cutoff)
     win_qs = np.ascontiguousarray(win_qs, dtype=np.int32)
     win_lo = np.ascontiguousarray(win_lo, dtype=np.int32)
