@@ -143,7 +143,7 @@ __global__ void __launch_bounds__(256) prep_reads_kernel(dp_reads R, ReadAux *__
     bool dirty = false;
     const int op_first = nops > 0 ? (int)(R.cigar[c0] & 15) : -1;
     // each lane takes PK consecutive ops per round (the loads of a round are independent; one warp scan per quantity)
-    constexpr int PK = 4;
+    constexpr int PK = 16;
     for (int base = 0; base < nops; base += 32 * PK) {
         const int jb = base + lane * PK;
         uint32_t w[PK + 2];                                  // w[0] = op before the lane's first, w[PK+1] = op after its last
@@ -273,29 +273,55 @@ __global__ void __launch_bounds__(256) prep_reads_kernel(dp_reads R, ReadAux *__
 // A base outside {A,C,G,T,N} (KeyError in the reference) clears the read's clean flag.
 __global__ void __launch_bounds__(256) base_codes_kernel(dp_reads R, ReadInfo *__restrict__ info,
                                                          uint8_t *__restrict__ code0) {
+    constexpr int BK = 16;                            // consecutive bases per thread: one read lookup, one 16-byte store
     const int64_t n = R.n_bases;
-    for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < n; k += (int64_t)gridDim.x * blockDim.x) {
-        int lo = 0, hi = R.n_reads;                   // read r with qual_off[r] <= k < qual_off[r+1]
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x * BK;
+    for (int64_t k0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * BK; k0 < n; k0 += stride) {
+        int lo = 0, hi = R.n_reads;                   // read r with qual_off[r] <= k0 < qual_off[r+1]
         while (hi - lo > 1) {
             const int mid = (lo + hi) >> 1;
-            if (__ldg(R.qual_off + mid) <= k) lo = mid; else hi = mid;
+            if (__ldg(R.qual_off + mid) <= k0) lo = mid; else hi = mid;
         }
-        const int r = lo;
-        const ReadInfo *ri = info + r;
-        const int idx = (int)(k - ri->qual_off);
-        const int l_seq = ri->l_seq;
-        const uint8_t *seqp = R.seq4 + ri->seq_off;
-        const uint8_t b = __ldg(seqp + (idx >> 1));
-        const int nib = (idx & 1) ? (b & 15) : (b >> 4);
-        if (!((0x8116u >> nib) & 1u)) atomicAnd(&info[r].flags, ~RI_CLEAN);
-        const int kb = idx + ri->aln_start;
-        int cat = 0;
-        if (kb < l_seq) {
-            const uint8_t b2 = __ldg(seqp + (kb >> 1));
-            const int nib2 = (kb & 1) ? (b2 & 15) : (b2 >> 4);
-            cat = nib2 == 15 ? CAT_N : ((__ffs(nib2) - 1) & 3);
+        int r = lo;
+        int64_t ro = 0, next = 0;
+        int l_seq = 0, aln_start = 0, mq28 = 0;
+        const uint8_t *seqp = nullptr;
+        bool illegal = false;
+        auto load_read = [&]() {
+            const ReadInfo *ri = info + r;
+            ro = ri->qual_off; l_seq = ri->l_seq; aln_start = ri->aln_start; mq28 = ri->mapq28;
+            seqp = R.seq4 + ri->seq_off;
+            next = ro + l_seq;
+            illegal = false;
+        };
+        load_read();
+        uint32_t out[BK / 4] = {0, 0, 0, 0};
+#pragma unroll
+        for (int t = 0; t < BK; t++) {
+            const int64_t k = k0 + t;
+            if (k >= n) break;
+            while (k >= next && r + 1 < R.n_reads) {
+                if (illegal) atomicAnd(&info[r].flags, ~RI_CLEAN);
+                r++;
+                load_read();
+            }
+            const int idx = (int)(k - ro);
+            const uint8_t b = __ldg(seqp + (idx >> 1));
+            const int nib = (idx & 1) ? (b & 15) : (b >> 4);
+            if (!((0x8116u >> nib) & 1u)) illegal = true;
+            const int kb = idx + aln_start;
+            int cat = 0;
+            if (kb < l_seq) {
+                const uint8_t b2 = __ldg(seqp + (kb >> 1));
+                const int nib2 = (kb & 1) ? (b2 & 15) : (b2 >> 4);
+                cat = nib2 == 15 ? CAT_N : ((__ffs(nib2) - 1) & 3);
+            }
+            const uint32_t code = (uint32_t)((cat << 5) | min((int)__ldg(R.qual + k), mq28));
+            out[t >> 2] |= code << ((t & 3) << 3);
         }
-        code0[k] = (uint8_t)((cat << 5) | min((int)__ldg(R.qual + k), ri->mapq28));
+        if (illegal) atomicAnd(&info[r].flags, ~RI_CLEAN);
+        if (k0 + BK <= n) *reinterpret_cast<uint4 *>(code0 + k0) = make_uint4(out[0], out[1], out[2], out[3]);
+        else for (int t = 0; k0 + t < n; t++) code0[k0 + t] = (uint8_t)(out[t >> 2] >> ((t & 3) << 3));
     }
 }
 
@@ -810,11 +836,14 @@ __global__ void __launch_bounds__(ENC_THREADS) encode_windows_kernel(EncArgs a, 
 // kernel, which then recomputes it.
 constexpr int V3_THREADS = 256;
 constexpr int V3_WARPS = V3_THREADS / 32;
-constexpr int V3_SLOTS = 40;          // reads per batch
+constexpr int V3_MAXSLOT = 128;       // most read slots per batch (the pool may hold fewer)
+// One shared-memory pool, carved per window: planes [slots][LS] words from the bottom (LS = drawn columns rounded up
+// to 16), image-row codes [rows][RS] bytes from the top (RS = deepest row rounded up to whole quads).
+constexpr int V3_POOL_BYTES = 38656;
 constexpr int V3_CS = 208;            // column stride of the planes (>= window length)
 constexpr int V3_MAXC = 192;          // surviving reads per window
-constexpr int V3_MD = 64;             // staged M/D ops per read
-constexpr int V3_POOL = 2048;         // inserted-base codes per batch
+constexpr int V3_MD = 48;             // staged M/D ops per read
+constexpr int V3_POOL = 1024;         // inserted-base codes per batch
 constexpr int V3_NREC = 253;          // insert records per batch (plane byte = record + 1; 255 = soft-clip step)
 constexpr int V3_QMAX = 28;
 constexpr uint8_t V3_NONE = 0xFF;
@@ -828,8 +857,8 @@ struct __align__(8) Md3 {
 };
 
 struct V3S {
-    uint8_t *q;                  // [H][W] codes per image row (pixel 0 = reference)
-    uint8_t *p1, *p0, *pi;       // [V3_SLOTS][V3_CS] step>=1 codes, step-0 codes, insert record / soft-clip marker
+    uint8_t *q;                  // [rows][RS] codes per image row (pixel 0 = reference)
+    uint32_t *pw;                // [slots][LS] per (read slot, column): step>=1 code | step-0 code << 8 | insert record / soft-clip marker << 16
     uint32_t *cnt;               // [NCAT][V3_CS/2] two 16-bit counters per word
     Md3 *md;                     // [V3_WARPS][V3_MD]
     uint32_t *lut;               // [256] code -> RGBA
@@ -838,8 +867,10 @@ struct V3S {
     int *cand, *j0;              // [V3_MAXC]
     int *cov, *maxins;           // [V3_CS + 8], [V3_CS]
     uint8_t *refc;               // [224] categories (A,C,G,T,N) of refSequence
-    uint8_t *scode;              // [V3_SLOTS][2] soft-clip step codes (leading, trailing)
-    short *scol;                 // [V3_SLOTS][2]
+    uint8_t *scode;              // [V3_MAXSLOT][2] soft-clip step codes (leading, trailing)
+    short *scol;                 // [V3_MAXSLOT][2]
+    unsigned short *rowstart;    // [V3_CS] first image row of a drawn column, 0xFFFF otherwise
+    int *rowcnt;                 // [256] entries per image row
     int *misc;                   // [0] fallback [1] nrec [2] npool [3] Lgen [4] nrows [5] hasS [8..16] warp sums [16..24] warp sums 2
 };
 
@@ -883,8 +914,8 @@ __device__ void v3_scan_read(const EncArgs &a, const V3S &S, int ci, int qs, int
 }
 
 // generate: one warp; every entry of read S.cand[ci] on columns [0, Lgen) -> planes of `slot`
-__device__ void v3_gen_read(const EncArgs &a, const V3S &S, int ci, int slot, int qs, int Lgen, bool count, int lane,
-                            int warp) {
+__device__ void v3_gen_read(const EncArgs &a, const V3S &S, int ci, int slot, int qs, int Lgen, int LS, int H, bool count,
+                            int lane, int warp) {
     const int r = S.cand[ci];
     const ReadInfo *ri = a.info + r;
     const int ref_start = ri->ref_start, nops = ri->nops;
@@ -893,7 +924,7 @@ __device__ void v3_gen_read(const EncArgs &a, const V3S &S, int ci, int slot, in
     const long long rpb = c0 + r;
     const uint8_t *__restrict__ codep = a.code0 + ri->qual_off;
     Md3 *md = S.md + warp * V3_MD;
-    uint8_t *p1 = S.p1 + slot * V3_CS, *p0 = S.p0 + slot * V3_CS, *pi = S.pi + slot * V3_CS;
+    uint8_t *pl = reinterpret_cast<uint8_t *>(S.pw + slot * LS);      // byte 0: step>=1, 1: step 0, 2: insert / soft clip
     const unsigned lt = (1u << lane) - 1u;
     int nmd = 0, shift = 0;
     bool bad = false;
@@ -941,8 +972,8 @@ __device__ void v3_gen_read(const EncArgs &a, const V3S &S, int ci, int slot, in
                         const int which = jj == 0 ? 0 : 1;
                         S.scode[slot * 2 + which] = code;
                         S.scol[slot * 2 + which] = (short)sA;
-                        pi[sA] = 255;
-                    } else p0[sA] = code;
+                        pl[sA * 4 + 2] = 255;
+                    } else pl[sA * 4 + 1] = code;
                     if (count) v3_count(S, cat, sA);
                 }
             } else if (sA >= 1) {
@@ -952,8 +983,11 @@ __device__ void v3_gen_read(const EncArgs &a, const V3S &S, int ci, int slot, in
                 if (rec >= V3_NREC || off + n > V3_POOL || n > 0xffff) bad = true;
                 else {
                     S.rec[rec] = ((uint32_t)n << 16) | (uint32_t)off;
-                    pi[sA] = (uint8_t)(rec + 1);
+                    pl[sA * 4 + 2] = (uint8_t)(rec + 1);
                     for (int k2 = 0; k2 < n; k2++) S.pool[off + k2] = __ldg(codep + qp + 1 + k2);
+                    const int y0 = S.rowstart[sA];
+                    if (count && y0 != 0xFFFF)
+                        for (int k2 = 0; k2 < n && y0 + 1 + k2 < H; k2++) atomicAdd(&S.rowcnt[y0 + 1 + k2], 1);
                 }
             }
         }
@@ -967,7 +1001,7 @@ __device__ void v3_gen_read(const EncArgs &a, const V3S &S, int ci, int slot, in
     if (nmd > 0 && cA < Lgen) {
         int jm = 0;                                   // last staged op with sA <= cA (0 if none)
 #pragma unroll
-        for (int step = V3_MD / 2; step; step >>= 1) {
+        for (int step = 32; step; step >>= 1) {
             const int t = jm + step;
             if (t < nmd && md[t].sA <= cA) jm = t;
         }
@@ -982,7 +1016,7 @@ __device__ void v3_gen_read(const EncArgs &a, const V3S &S, int ci, int slot, in
                 const int cb = __ldg(codep + m.qadj + (isD ? 0 : c));
                 int cat = cb >> 5;
                 if (isD) cat = CAT_D; else if (cat == refs[c]) cat = CAT_M;
-                p1[c] = (uint8_t)((cat << 5) | (cb & 31));
+                pl[c * 4] = (uint8_t)((cat << 5) | (cb & 31));
                 if (count) v3_count(S, cat, c);
             }
         }
@@ -991,44 +1025,74 @@ __device__ void v3_gen_read(const EncArgs &a, const V3S &S, int ci, int slot, in
 }
 
 // place: thread `c` owns column c (image row my_row); codes of the batch's slots in file order
-__device__ __forceinline__ void v3_place(uint8_t code, uint32_t &lo, uint32_t &hi, uint8_t *qrow, int Wm1) {
-    const int cat = code >> 5;
-    const int pos = (int)(__byte_perm(lo, hi, (uint32_t)cat) & 0xffu);
+__device__ __forceinline__ void v3_place(uint32_t code, uint32_t &lo, uint32_t &hi, uint8_t *qrow, int Wm1) {
+    const uint32_t cat = code >> 5;
+    const int pos = (int)(__byte_perm(lo, hi, cat) & 0xffu);
     if (pos < Wm1) {
-        qrow[pos] = code;
+        qrow[pos] = (uint8_t)code;
         const uint32_t inc = 1u << ((cat & 3) << 3);
         if (cat < 4) lo += inc; else hi += inc;
     }
 }
 
-__device__ void v3_walk(const V3S &S, int c, int my_row, int nslots, int W, int H, uint32_t &lo, uint32_t &hi,
-                        unsigned short *s_rowcnt) {
-    uint8_t *qrow = S.q + (size_t)my_row * W + 1;
-    const uint8_t *p1 = S.p1 + c, *p0 = S.p0 + c, *pi = S.pi + c;
+__device__ __forceinline__ void v3_walk(const V3S &S, int c, int my_row, int nslots, int LS, int RS, int W, int H,
+                                        uint32_t &lo, uint32_t &hi, const int *s_rowcnt, unsigned short *s_rowfill) {
+    uint8_t *qrow = S.q + my_row * RS + 1;
+    const uint32_t *pw = S.pw + c;
     const int Wm1 = W - 1;
     for (int s = 0; s < nslots; s++) {
-        const uint8_t c1 = p1[s * V3_CS], c0 = p0[s * V3_CS], ir = pi[s * V3_CS];
-        if (ir == 255) {
+        const uint32_t v = pw[s * LS];
+        const uint32_t c1 = v & 0xffu, c0 = (v >> 8) & 0xffu, ir = (v >> 16) & 0xffu;
+        if (ir == 255u) {
             const int which = S.scol[s * 2] == c ? 0 : 1;
             v3_place(S.scode[s * 2 + which], lo, hi, qrow, Wm1);
         }
         if (c0 != V3_NONE) v3_place(c0, lo, hi, qrow, Wm1);
         if (c1 != V3_NONE) v3_place(c1, lo, hi, qrow, Wm1);
-        if (ir != 0 && ir != 255) {
+        if (ir != 0u && ir != 255u) {
             const uint32_t rc = S.rec[ir - 1];
             const int n = rc >> 16, off = rc & 0xffff;
             for (int k = 0; k < n; k++) {
                 const int y = my_row + 1 + k;
                 if (y >= H) break;
-                const int pos = s_rowcnt[y]++;
-                if (pos < Wm1) S.q[(size_t)y * W + 1 + pos] = S.pool[off + k];
-                else S.misc[0] = 1;                  // deeper than the image: the category sort needs every entry
+                const int pos = s_rowfill[y]++;
+                if (s_rowcnt[y] > Wm1) S.misc[0] = 1;    // deeper than the image: the category sort needs every entry
+                else S.q[y * RS + 1 + pos] = S.pool[off + k];
             }
         }
     }
 }
 
-__global__ void __launch_bounds__(V3_THREADS, 3)
+// finish: the thread that owns a column sorts its insert rows, adds pixel 0 and filler codes up to the quad boundary
+// and writes the entry quads of its rows (16-byte stores through the code -> RGBA table)
+__device__ __forceinline__ void v3_finish_rows(const V3S &S, int my_row, int nown, int RS, int W, const int *s_rowcnt,
+                                               const short *s_rowk, uint8_t ref_code, uint8_t *img) {
+    for (int k = 0; k < nown; k++) {
+        const int y = my_row + k;
+        uint8_t *row = S.q + y * RS;
+        const int tot = min(s_rowcnt[y], W - 1);
+        const bool ins = k != 0;
+        if (ins) {                                    // stable sort by category (A,C,G,T,N) of codes appended in read order
+            for (int i = 2; i <= tot; i++) {
+                const uint8_t c = row[i];
+                int j = i - 1;
+                while (j >= 1 && (row[j] >> 5) > (c >> 5)) { row[j + 1] = row[j]; j--; }
+                row[j + 1] = c;
+            }
+        }
+        row[0] = ins ? V3_FILL_INS : ref_code;
+        for (int x = tot + 1; x & 3; x++) row[x] = ins ? V3_FILL_INS : V3_FILL_NONE;
+        uint8_t *orow = img + ((size_t)y * W << 2);
+        for (int x0 = 0; x0 <= tot; x0 += 4) {
+            const uint32_t codes = *reinterpret_cast<const uint32_t *>(row + x0);
+            const uint32_t p0 = S.lut[codes & 0xffu], p1 = S.lut[(codes >> 8) & 0xffu];
+            const uint32_t p2 = S.lut[(codes >> 16) & 0xffu], p3 = S.lut[codes >> 24];
+            *reinterpret_cast<uint4 *>(orow + (x0 << 2)) = make_uint4(p0, p1, p2, p3);
+        }
+    }
+}
+
+__global__ void __launch_bounds__(V3_THREADS, 4)
 encode_windows_v3_kernel(EncArgs a, int *__restrict__ fb_count, int *__restrict__ fb_list, int emit_mode) {
     extern __shared__ __align__(16) uint8_t smem[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -1040,10 +1104,9 @@ encode_windows_v3_kernel(EncArgs a, int *__restrict__ fb_count, int *__restrict_
     // ---- shared memory carve-up (16-byte aligned sections first)
     uint8_t *p = smem;
     V3S S;
-    S.q = p;                                       p += ((H * W + 15) / 16) * 16;
-    S.p1 = p;                                      p += V3_SLOTS * V3_CS;
-    S.p0 = p;                                      p += V3_SLOTS * V3_CS;
-    S.pi = p;                                      p += V3_SLOTS * V3_CS;
+    uint8_t *s_pool0 = p;                          p += V3_POOL_BYTES;
+    S.pw = (uint32_t *)s_pool0;
+    S.q = s_pool0;                                 // placed at the top of the pool once the row stride is known
     S.cnt = (uint32_t *)p;                         p += 4 * (NCAT * V3_CS / 2);
     S.md = (Md3 *)p;                               p += sizeof(Md3) * V3_WARPS * V3_MD;
     S.lut = (uint32_t *)p;                         p += 4 * 256;
@@ -1055,15 +1118,16 @@ encode_windows_v3_kernel(EncArgs a, int *__restrict__ fb_count, int *__restrict_
     S.maxins = (int *)p;                           p += 4 * V3_CS;
     S.misc = (int *)p;                             p += 4 * 32;
     uint32_t *s_fill = (uint32_t *)p;              p += 4 * 2 * 256;       // two constant filler rows (none / insert)
-    unsigned short *s_rowstart = (unsigned short *)p; p += 2 * V3_CS;
+    int *s_rowcnt = (int *)p;                      p += 4 * 256;           // entries per image row
+    S.rowstart = (unsigned short *)p;              p += 2 * V3_CS;         // first image row of a drawn column (0xFFFF: none)
     short *s_rowcol = (short *)p;                  p += 2 * 256;
     short *s_rowk = (short *)p;                    p += 2 * 256;
-    unsigned short *s_rowcnt = (unsigned short *)p; p += 2 * 256;
-    S.scol = (short *)p;                           p += 2 * V3_SLOTS * 2;
-    S.scode = p;                                   p += V3_SLOTS * 2;
+    unsigned short *s_rowfill = (unsigned short *)p; p += 2 * 256;         // running fill of insert rows
+    S.scol = (short *)p;                           p += 2 * V3_MAXSLOT * 2;
+    S.scode = p;                                   p += V3_MAXSLOT * 2;
     S.refc = p;                                    p += 224;
-    uint8_t *s_rowref = p;                         p += 256;
     int *s_wsum = &S.misc[8], *s_wsum2 = &S.misc[16];
+    S.rowcnt = s_rowcnt;
 
     // ---- setup
     const long long roff = (long long)qs - a.ref_base;
@@ -1090,8 +1154,10 @@ encode_windows_v3_kernel(EncArgs a, int *__restrict__ fb_count, int *__restrict_
     }
     for (int i = tid; i < NCAT * V3_CS / 2; i += V3_THREADS) S.cnt[i] = 0;
     for (int i = tid; i < V3_CS + 8; i += V3_THREADS) S.cov[i] = 0;
-    for (int i = tid; i < V3_CS; i += V3_THREADS) S.maxins[i] = 0;
-    s_rowcnt[tid] = 0; s_rowcol[tid] = -1; s_rowk[tid] = 0; s_rowref[tid] = V3_FILL_NONE;
+    for (int i = tid; i < V3_CS; i += V3_THREADS) { S.maxins[i] = 0; S.rowstart[i] = 0xFFFF; }
+    s_rowcnt[tid] = 0; s_rowcol[tid] = -1; s_rowk[tid] = 0; s_rowfill[tid] = 0;
+    s_fill[tid] = 0xFF000000u; s_fill[256 + tid] = 0xFFFF00FFu;
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 
     // ---- ordered compaction of the reads that pysam.fetch would return and parseRead would keep
     int ncand = 0;
@@ -1136,7 +1202,8 @@ encode_windows_v3_kernel(EncArgs a, int *__restrict__ fb_count, int *__restrict_
         v3_scan_read(a, S, ci, qs, L, lane);
     }
     __syncthreads();
-    int my_row = -1;
+    int my_row = -1, nown = 0;
+    uint8_t ref_code = V3_FILL_NONE;
     {
         const int cv = tid < L ? S.cov[tid] : 0;
         const int inc1 = warp_incl_scan(cv, lane);
@@ -1157,92 +1224,71 @@ encode_windows_v3_kernel(EncArgs a, int *__restrict__ fb_count, int *__restrict_
         if (tid == V3_THREADS - 1) S.misc[4] = (b2 + inc2) & 0xffff;
         if (pop && rstart < H) {
             my_row = rstart;
+            nown = min(1 + mi, H - rstart);
+            S.rowstart[tid] = (unsigned short)rstart;
             atomicMax(&S.misc[3], tid + 1);
-            s_rowref[rstart] = (uint8_t)((S.refc[ord] << 5) | 29);
-            for (int k = 0; k <= mi; k++) {
-                const int y = rstart + k;
-                if (y >= H) break;
-                s_rowcol[y] = (short)tid; s_rowk[y] = (short)k;
-            }
+            ref_code = (uint8_t)((S.refc[ord] << 5) | 29);
+            for (int k = 0; k < nown; k++) { s_rowcol[rstart + k] = (short)tid; s_rowk[rstart + k] = (short)k; }
         }
         __syncthreads();
     }
     const int Lgen = S.misc[3];
     const int nrows = min(S.misc[4], H);
+    // plane geometry for this window: stride = drawn columns rounded up, as many read slots as the pool holds
+    const int LS = max(16, (Lgen + 15) & ~15);
+    int slots = min(V3_MAXSLOT, V3_POOL_BYTES / (4 * LS));   // counting pass: the whole pool is planes
+    int nb = (ncand + slots - 1) / slots;
+    const bool walker = my_row >= 0;
+    uint8_t *img = a.out_img + (size_t)w * H * W * 4;
 
-    // ---- generate + place, V3_SLOTS reads per batch.  One batch: generate once (counting), then place.  More: a
-    // counting pass over all batches first, then each batch is generated again and placed.
-    const int nb = (ncand + V3_SLOTS - 1) / V3_SLOTS;
-    const bool multi = nb > 1;
-    const bool walker = tid < Lgen && my_row >= 0;
+    // ---- generate (counting).  One batch: its planes are kept for placement.  More: count over all batches first,
+    // then each batch is generated again and placed.
+    for (int b = 0; b < nb; b++) {
+        const int nslots = min(slots, ncand - b * slots);
+        {
+            uint4 *q4 = reinterpret_cast<uint4 *>(S.pw);
+            const int n16 = nslots * LS / 4;
+            for (int i = tid; i < n16; i += V3_THREADS) q4[i] = make_uint4(0xFFFFu, 0xFFFFu, 0xFFFFu, 0xFFFFu);
+            if (tid == 0) { S.misc[1] = 0; S.misc[2] = 0; S.misc[7] = 0; }
+            if (tid < nslots * 2) S.scol[tid] = -1;
+        }
+        __syncthreads();
+        for (;;) {
+            int s = 0;
+            if (lane == 0) s = atomicAdd(&S.misc[7], 1);
+            s = __shfl_sync(0xffffffffu, s, 0);
+            if (s >= nslots) break;
+            v3_gen_read(a, S, b * slots + s, s, qs, Lgen, LS, H, true, lane, warp);
+        }
+        __syncthreads();
+    }
+    // ---- counts -> first slot of each category (sortingKey order A,C,G,T,D,M,N), saturated at W; row stride of S.q
     uint32_t run_lo = 0, run_hi = 0;
-    bool have_base = false;
-    for (int pass = 0; pass < (multi ? 2 : 1); pass++) {
-        for (int b = 0; b < nb; b++) {
-            const int nslots = min(V3_SLOTS, ncand - b * V3_SLOTS);
-            {
-                const int n16 = nslots * V3_CS / 16;
-                uint4 *q1 = reinterpret_cast<uint4 *>(S.p1), *q0 = reinterpret_cast<uint4 *>(S.p0);
-                uint4 *qi = reinterpret_cast<uint4 *>(S.pi);
-                for (int i = tid; i < n16; i += V3_THREADS) {
-                    q1[i] = make_uint4(~0u, ~0u, ~0u, ~0u);
-                    q0[i] = make_uint4(~0u, ~0u, ~0u, ~0u);
-                    qi[i] = make_uint4(0u, 0u, 0u, 0u);
-                }
-                if (tid == 0) { S.misc[1] = 0; S.misc[2] = 0; S.misc[7] = 0; }
-                if (tid < nslots * 2) S.scol[tid] = -1;
-            }
-            __syncthreads();
-            for (;;) {
-                int s = 0;
-                if (lane == 0) s = atomicAdd(&S.misc[7], 1);
-                s = __shfl_sync(0xffffffffu, s, 0);
-                if (s >= nslots) break;
-                v3_gen_read(a, S, b * V3_SLOTS + s, s, qs, Lgen, pass == 0, lane, warp);
-            }
-            __syncthreads();
-            if (!multi || pass == 1) {
-                if (walker) {
-                    if (!have_base) {
-                        // counts -> first slot of each category (sortingKey order A,C,G,T,D,M,N), saturated at W
-                        int acc = 0;
-                        uint32_t blo = 0, bhi = 0;
+    if (walker) {
+        int acc = 0;
 #pragma unroll
-                        for (int c = 0; c < NCAT; c++) {
-                            const uint32_t wv = S.cnt[(c * V3_CS + tid) >> 1];
-                            const int n = (wv >> ((tid & 1) << 4)) & 0xffff;
-                            const uint32_t bv = (uint32_t)min(acc, W - 1);
-                            if (c < 4) blo |= bv << (c << 3); else bhi |= bv << ((c - 4) << 3);
-                            acc += n;
-                        }
-                        run_lo = blo; run_hi = bhi;
-                        s_rowcnt[my_row] = (unsigned short)min(acc, W - 1);
-                        have_base = true;
-                    }
-                    v3_walk(S, tid, my_row, nslots, W, H, run_lo, run_hi, s_rowcnt);
-                }
-                __syncthreads();
-            }
+        for (int c = 0; c < NCAT; c++) {
+            const uint32_t wv = S.cnt[(c * V3_CS + tid) >> 1];
+            const int n = (wv >> ((tid & 1) << 4)) & 0xffff;
+            const uint32_t bv = (uint32_t)min(acc, W - 1);
+            if (c < 4) run_lo |= bv << (c << 3); else run_hi |= bv << ((c - 4) << 3);
+            acc += n;
         }
+        s_rowcnt[my_row] = min(acc, W - 1);
+        int mx = min(acc, W - 1);
+        for (int k = 1; k < nown; k++) mx = max(mx, min(s_rowcnt[my_row + k], W - 1));
+        atomicMax(&S.misc[9], mx);
     }
-    // ---- insert rows: stable sort by category (A,C,G,T,N) of the codes appended in read order
-    if (tid < nrows && s_rowk[tid] != 0) {
-        uint8_t *row = S.q + (size_t)tid * W + 1;
-        const int n = min((int)s_rowcnt[tid], W - 1);
-        for (int i = 1; i < n; i++) {
-            const uint8_t c = row[i];
-            int j = i - 1;
-            while (j >= 0 && (row[j] >> 5) > (c >> 5)) { row[j + 1] = row[j]; j--; }
-            row[j + 1] = c;
-        }
-    }
-    if (tid < nrows) {
-        // pixel 0 (reference / insert colour) and filler codes up to the end of the last entry quad
-        const bool ins = s_rowk[tid] != 0;
-        uint8_t *row = S.q + (size_t)tid * W;
-        row[0] = ins ? V3_FILL_INS : s_rowref[tid];
-        const int tot = min((int)s_rowcnt[tid], W - 1);
-        for (int x = tot + 1; x < W && (x & 3); x++) row[x] = ins ? V3_FILL_INS : V3_FILL_NONE;
+    __syncthreads();
+    const int RS = (S.misc[9] + 4) & ~3;             // pixel 0 + entries, rounded up to whole quads
+    const int qbytes = (nrows * RS + 15) & ~15;
+    S.q = s_pool0 + V3_POOL_BYTES - qbytes;
+    // the counting pass's planes can be placed from directly when every read was in them and they clear the rows
+    const bool multi = !(nb == 1 && ncand * 4 * LS + qbytes <= V3_POOL_BYTES);
+    if (multi) {
+        slots = min(V3_MAXSLOT, (V3_POOL_BYTES - qbytes) / (4 * LS));
+        if (slots < 8 && slots < ncand) { if (tid == 0) S.misc[0] = 1; slots = 8; }
+        nb = (ncand + slots - 1) / slots;
     }
     __syncthreads();
     if (S.misc[0]) {
@@ -1251,22 +1297,18 @@ encode_windows_v3_kernel(EncArgs a, int *__restrict__ fb_count, int *__restrict_
             fb_list[k] = w;
             if (a.out_status) a.out_status[w] = 0;
         }
-        return;                                      // the exact kernel rewrites this window
+        return;                                      // the exact kernel recomputes this window
     }
     // ---- emit 1: the filler tail of every row (and blank rows) -- one bulk copy (TMA) per row out of two constant
-    // filler rows in shared memory; emit_mode 1 = plain 16-byte stores instead (one thread per quad column)
-    uint8_t *img = a.out_img + (size_t)w * H * W * 4;
-    const int qpr = W >> 2;                          // quads per row
+    // filler rows in shared memory, issued by the high threads while the low ones place; emit_mode 1 = plain stores
     if (emit_mode == 0) {
-        for (int i = tid; i < W; i += V3_THREADS) { s_fill[i] = 0xFF000000u; s_fill[W + i] = 0xFFFF00FFu; }
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-        __syncthreads();
-        for (int y = tid; y < H; y += V3_THREADS) {
-            const int tot = y < nrows ? (int)s_rowcnt[y] : -1;
+        const int y = V3_THREADS - 1 - tid;
+        if (y < H) {
+            const int tot = y < nrows ? s_rowcnt[y] : -1;
             const int xq = ((tot + 4) >> 2) << 2;    // first pixel of the first all-filler quad
             const int bytes = (W - xq) << 2;
             if (bytes > 0) {
-                const uint32_t src = (uint32_t)__cvta_generic_to_shared(s_fill + ((y < nrows && s_rowk[y] != 0) ? W : 0));
+                const uint32_t src = (uint32_t)__cvta_generic_to_shared(s_fill + ((y < nrows && s_rowk[y] != 0) ? 256 : 0));
                 uint8_t *dst = img + (((size_t)y * W + xq) << 2);
                 asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
                              :: "l"(dst), "r"(src), "r"(bytes) : "memory");
@@ -1274,6 +1316,7 @@ encode_windows_v3_kernel(EncArgs a, int *__restrict__ fb_count, int *__restrict_
         }
         asm volatile("cp.async.bulk.commit_group;" ::: "memory");
     } else {
+        const int qpr = W >> 2;
         const int rpi = V3_THREADS / qpr;            // rows per iteration
         const int ty = tid / qpr, tx = tid - ty * qpr;
         if (ty < rpi) {
@@ -1286,34 +1329,57 @@ encode_windows_v3_kernel(EncArgs a, int *__restrict__ fb_count, int *__restrict_
             }
         }
     }
-    // ---- emit 2: quads that hold the reference pixel / entries: 16 lanes per image row, code -> RGBA by table
-    for (int y = tid >> 4; y < nrows; y += V3_THREADS / 16) {
-        const int tot = s_rowcnt[y];
-        const uint8_t *row = S.q + (size_t)y * W;
-        uint8_t *orow = img + (((size_t)y * W) << 2);
-        for (int x0 = (tid & 15) << 2; x0 <= tot; x0 += 64) {
-            const uint32_t codes = *reinterpret_cast<const uint32_t *>(row + x0);
-            const uint32_t p0 = S.lut[codes & 0xffu], p1 = S.lut[(codes >> 8) & 0xffu];
-            const uint32_t p2 = S.lut[(codes >> 16) & 0xffu], p3 = S.lut[codes >> 24];
-            *reinterpret_cast<uint4 *>(orow + (x0 << 2)) = make_uint4(p0, p1, p2, p3);
+    // ---- place
+    if (!multi) {
+        if (walker) v3_walk(S, tid, my_row, ncand, LS, RS, W, H, run_lo, run_hi, s_rowcnt, s_rowfill);
+    } else {
+        for (int b = 0; b < nb; b++) {
+            const int nslots = min(slots, ncand - b * slots);
+            __syncthreads();
+            {
+                uint4 *q4 = reinterpret_cast<uint4 *>(S.pw);
+                const int n16 = nslots * LS / 4;
+                for (int i = tid; i < n16; i += V3_THREADS) q4[i] = make_uint4(0xFFFFu, 0xFFFFu, 0xFFFFu, 0xFFFFu);
+                if (tid == 0) { S.misc[1] = 0; S.misc[2] = 0; S.misc[7] = 0; }
+                if (tid < nslots * 2) S.scol[tid] = -1;
+            }
+            __syncthreads();
+            for (;;) {
+                int s = 0;
+                if (lane == 0) s = atomicAdd(&S.misc[7], 1);
+                s = __shfl_sync(0xffffffffu, s, 0);
+                if (s >= nslots) break;
+                v3_gen_read(a, S, b * slots + s, s, qs, Lgen, LS, H, false, lane, warp);
+            }
+            __syncthreads();
+            if (walker) v3_walk(S, tid, my_row, nslots, LS, RS, W, H, run_lo, run_hi, s_rowcnt, s_rowfill);
         }
     }
+    // ---- finish: each column's thread completes and writes its own rows
+    if (walker) v3_finish_rows(S, my_row, nown, RS, W, s_rowcnt, s_rowk, ref_code, img);
     for (int y = tid; y < H; y += V3_THREADS) {
         if (a.out_rowpos) a.out_rowpos[(size_t)w * H + y] = (y < nrows) ? qs + s_rowcol[y] : -1;
         if (a.out_rowins) a.out_rowins[(size_t)w * H + y] = (y < nrows) ? s_rowk[y] : 0;
     }
-    if (tid == 0 && a.out_status) a.out_status[w] = 0;
     if (emit_mode == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // shared memory must outlive the copies
+    __syncthreads();
+    if (tid == 0) {
+        if (S.misc[0]) {                             // an insert row deeper than the image turned up while placing
+            const int k = atomicAdd(fb_count, 1);
+            fb_list[k] = w;
+        }
+        if (a.out_status) a.out_status[w] = 0;
+    }
 }
 
 static size_t encoder_v3_smem_bytes(const dp_encode_params *p) {
+    (void)p;
     size_t s = 0;
-    s += ((size_t)p->window_cutoff * p->coverage_cutoff + 15) / 16 * 16;
-    s += 3 * V3_SLOTS * V3_CS;
+    s += V3_POOL_BYTES;
     s += 4 * (NCAT * V3_CS / 2);
     s += sizeof(Md3) * V3_WARPS * V3_MD;
     s += 4 * 256 * 2 + V3_POOL + 4 * V3_MAXC * 2 + 4 * (V3_CS + 8) + 4 * V3_CS + 4 * 32;
-    s += 2 * V3_CS + 2 * 256 * 3 + 2 * V3_SLOTS * 2 + V3_SLOTS * 2 + 224 + 256 + 4 * 2 * 256;
+    s += 4 * 2 * 256 + 4 * 256 + 2 * V3_CS + 2 * 256 * 3 + 2 * V3_MAXSLOT * 2 + V3_MAXSLOT * 2 + 224;
     return s + 16;
 }
 
@@ -1425,17 +1491,24 @@ int dp_encode_windows(const dp_reads *reads, int32_t n_windows, const int32_t *w
     wp += dp::align_up((int64_t)sizeof(int) * (reads->n_reads > 0 ? reads->n_reads : 1), 256);
     uint8_t *code0 = wp;
 
+    /* DP_ENC_TIMING=1: CUDA events around each kernel of this call, printed to stderr (synchronises; debugging aid) */
+    static int timing = -1;
+    if (timing < 0) { const char *e = getenv("DP_ENC_TIMING"); timing = (e && e[0] == '1') ? 1 : 0; }
+    cudaEvent_t ev[5];
+    if (timing) { for (int i = 0; i < 5; i++) cudaEventCreate(&ev[i]); cudaEventRecord(ev[0], st); }
     if (reads->n_reads > 0) {
         const int warps_per_block = 8;
         const int blocks = (reads->n_reads + warps_per_block - 1) / warps_per_block;
         dp::prep_reads_kernel<<<blocks, 256, 0, st>>>(*reads, aux, RP, QP, info, ckpt, endk, p->map_quality_cutoff);
         DP_CUDA_CHECK(cudaGetLastError());
         if (reads->n_bases > 0) {
-            const int64_t nb = (reads->n_bases + 255) / 256;
+            const int64_t nb = (reads->n_bases + 256 * 16 - 1) / (256 * 16);
+            if (timing) cudaEventRecord(ev[1], st);
             dp::base_codes_kernel<<<(unsigned)(nb < 148 * 64 ? nb : 148 * 64), 256, 0, st>>>(*reads, info, code0);
             DP_CUDA_CHECK(cudaGetLastError());
         }
     }
+    if (timing) cudaEventRecord(ev[2], st);
     dp::EncArgs a;
     a.R = *reads; a.aux = aux; a.RP = RP; a.QP = QP; a.info = info; a.ckpt = ckpt; a.endk = endk; a.code0 = code0;
     a.win_qs = win_qs; a.win_lo = win_lo; a.win_hi = win_hi;
@@ -1463,8 +1536,20 @@ int dp_encode_windows(const dp_reads *reads, int32_t n_windows, const int32_t *w
     if (emit_mode < 0) { const char *e = getenv("DP_ENC_EMIT"); emit_mode = (e && !strcmp(e, "stg")) ? 1 : 0; }
     dp::encode_windows_v3_kernel<<<n_windows, dp::V3_THREADS, smem3, st>>>(a, fb, fb + 64, emit_mode);
     DP_CUDA_CHECK(cudaGetLastError());
+    if (timing) cudaEventRecord(ev[3], st);
     dp::encode_windows_kernel<<<n_windows, dp::ENC_THREADS, smem, st>>>(a, fb, fb + 64);
     DP_CUDA_CHECK(cudaGetLastError());
+    if (timing) {
+        cudaEventRecord(ev[4], st);
+        cudaEventSynchronize(ev[4]);
+        float t[4] = {0, 0, 0, 0};
+        if (reads->n_reads > 0 && reads->n_bases > 0) { cudaEventElapsedTime(&t[0], ev[0], ev[1]); cudaEventElapsedTime(&t[1], ev[1], ev[2]); }
+        cudaEventElapsedTime(&t[2], ev[2], ev[3]);
+        cudaEventElapsedTime(&t[3], ev[3], ev[4]);
+        fprintf(stderr, "[dp_encode_windows] %d windows: prep %.3f ms, base codes %.3f ms, fast kernel %.3f ms, exact kernel %.3f ms\n",
+                n_windows, t[0], t[1], t[2], t[3]);
+        for (int i = 0; i < 5; i++) cudaEventDestroy(ev[i]);
+    }
     return DP_OK;
 }
 
