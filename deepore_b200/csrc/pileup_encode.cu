@@ -127,26 +127,32 @@ struct __align__(16) ReadInfo {
 };
 constexpr int RI_CLEAN = 1;
 
-// prep: one warp per read
+// prep: GW warps per read (1: short CIGARs, one warp per read; 8: long CIGARs, one block per read).  Each thread takes PK
+// consecutive ops per round (independent loads), scans run per warp and are stitched across the block's warps.
+template <int GW>
 __global__ void __launch_bounds__(256) prep_reads_kernel(dp_reads R, ReadAux *__restrict__ aux,
                                                          int *__restrict__ RP, int *__restrict__ QP,
                                                          ReadInfo *__restrict__ info, int *__restrict__ ckpt,
                                                          int *__restrict__ endk, int mapq_cut) {
-    const int lane = threadIdx.x & 31;
-    const int r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    constexpr int PK = 4;
+    constexpr int GT = GW * 32;                               // threads per read
+    __shared__ int s_part[8][4];                              // per-warp totals of a round
+    __shared__ int s_first[2];                                // first aligned op, D/N advance before it
+    const int lane = threadIdx.x & 31, wig = GW == 1 ? 0 : (threadIdx.x >> 5);
+    const int gt = wig * 32 + lane;
+    const int r = GW == 1 ? (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5) : (int)blockIdx.x;
     if (r >= R.n_reads) return;
     const int64_t c0 = R.cigar_off[r];
     const int nops = (int)(R.cigar_off[r + 1] - c0);
     const int pos = R.pos[r];
     int carryR = 0, carryQ = 0, carryH = 0, carryDN = 0;
-    int ref_start = INT_MIN;
+    int first_j = INT_MAX, first_dn = 0;                      // this thread's first aligned op
     bool dirty = false;
     const int op_first = nops > 0 ? (int)(R.cigar[c0] & 15) : -1;
-    // each lane takes PK consecutive ops per round (the loads of a round are independent; one warp scan per quantity)
-    constexpr int PK = 16;
-    for (int base = 0; base < nops; base += 32 * PK) {
-        const int jb = base + lane * PK;
-        uint32_t w[PK + 2];                                  // w[0] = op before the lane's first, w[PK+1] = op after its last
+    if (GW > 1) { if (threadIdx.x == 0) s_first[0] = INT_MAX; __syncthreads(); }
+    for (int base = 0; base < nops; base += GT * PK) {
+        const int jb = base + gt * PK;
+        uint32_t w[PK + 2];                                  // w[0] = op before the thread's first, w[PK+1] = op after its last
 #pragma unroll
         for (int t = 0; t < PK + 2; t++) {
             const int j = jb + t - 1;
@@ -164,8 +170,22 @@ __global__ void __launch_bounds__(256) prep_reads_kernel(dp_reads R, ReadAux *__
         }
         const int iR = warp_incl_scan(sR, lane), iQ = warp_incl_scan(sQ, lane);
         const int iH = warp_incl_scan(sH, lane), iDN = warp_incl_scan(sDN, lane);
-        int eR = carryR + iR - sR, eQ = carryQ + iQ - sQ, eDN = carryDN + iDN - sDN;
-        int my_dn = INT_MIN;                                 // D/N advance before the lane's first aligned op
+        int oR = 0, oQ = 0, oDN = 0;                          // totals of the warps before this one
+        int tR = __shfl_sync(0xffffffffu, iR, 31), tQ = __shfl_sync(0xffffffffu, iQ, 31);
+        int tH = __shfl_sync(0xffffffffu, iH, 31), tDN = __shfl_sync(0xffffffffu, iDN, 31);
+        if (GW > 1) {
+            if (lane == 31) { s_part[wig][0] = iR; s_part[wig][1] = iQ; s_part[wig][2] = iH; s_part[wig][3] = iDN; }
+            __syncthreads();
+            tR = tQ = tH = tDN = 0;
+#pragma unroll
+            for (int k = 0; k < GW; k++) {
+                const int pR = s_part[k][0], pQ = s_part[k][1], pH = s_part[k][2], pDN = s_part[k][3];
+                if (k < wig) { oR += pR; oQ += pQ; oDN += pDN; }
+                tR += pR; tQ += pQ; tH += pH; tDN += pDN;
+            }
+            __syncthreads();
+        }
+        int eR = carryR + oR + iR - sR, eQ = carryQ + oQ + iQ - sQ, eDN = carryDN + oDN + iDN - sDN;
 #pragma unroll
         for (int t = 1; t <= PK; t++) {
             const int j = jb + t - 1;
@@ -180,19 +200,30 @@ __global__ void __launch_bounds__(256) prep_reads_kernel(dp_reads R, ReadAux *__
             if (op == 4 && !(j == 0 || j == nops - 1)) dirty = true;
             if (op == 1 && (opp == 1 || opp == 4 || opn == 1 || opn == 4)) dirty = true;
             if (op != 0 && op != 4 && (j == 0 || (j == 1 && op_first == 4))) dirty = true;   // first non-S op must be M
-            if (my_dn == INT_MIN && (op == 0 || op == 7 || op == 8) && n > 0) my_dn = eDN;
+            if (first_j == INT_MAX && (op == 0 || op == 7 || op == 8) && n > 0) { first_j = j; first_dn = eDN; }
             eR += op_adv_ref(op) ? n : 0;
             eQ += op_adv_read(op) ? n : 0;
             eDN += (op == 2 || op == 3) ? n : 0;
         }
-        const unsigned m = __ballot_sync(0xffffffffu, my_dn != INT_MIN);
-        if (ref_start == INT_MIN && m) ref_start = pos + __shfl_sync(0xffffffffu, my_dn, __ffs(m) - 1);
-        carryR += __shfl_sync(0xffffffffu, iR, 31);
-        carryQ += __shfl_sync(0xffffffffu, iQ, 31);
-        carryH += __shfl_sync(0xffffffffu, iH, 31);
-        carryDN += __shfl_sync(0xffffffffu, iDN, 31);
+        carryR += tR; carryQ += tQ; carryH += tH; carryDN += tDN;
     }
-    // ---- soft-clip extents (lane-uniform, short loops)
+    // ---- first aligned reference position (get_reference_positions()[0], Pileup.py:191)
+    int ref_start = INT_MIN;
+    if (GW == 1) {
+        const unsigned m = __ballot_sync(0xffffffffu, first_j != INT_MAX);     // lanes hold ascending op ranges per round
+        int best = first_j;
+#pragma unroll
+        for (int d = 16; d; d >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, d));
+        const unsigned owner = __ballot_sync(0xffffffffu, first_j == best && first_j != INT_MAX);
+        if (m) ref_start = pos + __shfl_sync(0xffffffffu, first_dn, __ffs(owner) - 1);
+    } else {
+        if (first_j != INT_MAX) atomicMin(&s_first[0], first_j);
+        __syncthreads();
+        if (first_j != INT_MAX && first_j == s_first[0]) s_first[1] = first_dn;
+        __syncthreads();
+        if (s_first[0] != INT_MAX) ref_start = pos + s_first[1];
+    }
+    // ---- soft-clip extents (thread-uniform, short loops)
     const int l_seq = R.l_seq[r];
     int s = 0, e = l_seq;
     for (int c = 0; c < nops; c++) {
@@ -211,15 +242,15 @@ __global__ void __launch_bounds__(256) prep_reads_kernel(dp_reads R, ReadAux *__
     const int endpos = (!(R.flag[r] & 4) && nops > 0) ? pos + carryH : pos + 1;
     const int64_t so = R.seq_off[r], qo = R.qual_off[r];
     if (carryQ != aln_len || aln_len <= 0 || ref_start != pos || carryR <= 0) dirty = true;
-    dirty = __any_sync(0xffffffffu, dirty);
+    if (GW == 1) dirty = __any_sync(0xffffffffu, dirty); else dirty = __syncthreads_or(dirty);
     // ---- checkpoints: ckpt[m] = first op j with RP[j+1] >= m << k ; at most nops/4 + 1 of them per read
     int k = 6;
     while ((carryR >> k) > (nops >> 2)) k++;
     const int64_t ckb = (c0 >> 2) + r;
     {
         int cR = 0;
-        for (int base = 0; base < nops; base += 32 * PK) {
-            const int jb = base + lane * PK;
+        for (int base = 0; base < nops; base += GT * PK) {
+            const int jb = base + gt * PK;
             int dR[PK];
             int sR = 0;
 #pragma unroll
@@ -230,7 +261,16 @@ __global__ void __launch_bounds__(256) prep_reads_kernel(dp_reads R, ReadAux *__
                 sR += dR[t];
             }
             const int iR = warp_incl_scan(sR, lane);
-            int a0 = cR + iR - sR;
+            int oR = 0, tR = __shfl_sync(0xffffffffu, iR, 31);
+            if (GW > 1) {
+                if (lane == 31) s_part[wig][0] = iR;
+                __syncthreads();
+                tR = 0;
+#pragma unroll
+                for (int q = 0; q < GW; q++) { const int pR = s_part[q][0]; if (q < wig) oR += pR; tR += pR; }
+                __syncthreads();
+            }
+            int a0 = cR + oR + iR - sR;
 #pragma unroll
             for (int t = 0; t < PK; t++) {
                 if (dR[t] > 0) {
@@ -239,10 +279,10 @@ __global__ void __launch_bounds__(256) prep_reads_kernel(dp_reads R, ReadAux *__
                     a0 = b0;
                 }
             }
-            cR += __shfl_sync(0xffffffffu, iR, 31);
+            cR += tR;
         }
     }
-    if (lane == 0) {
+    if (gt == 0) {
         ckpt[ckb] = 0;
         RP[c0 + r + nops] = carryR;
         ReadAux a;
@@ -839,7 +879,7 @@ constexpr int V3_WARPS = V3_THREADS / 32;
 constexpr int V3_MAXSLOT = 128;       // most read slots per batch (the pool may hold fewer)
 // One shared-memory pool, carved per window: planes [slots][LS] words from the bottom (LS = drawn columns rounded up
 // to 16), image-row codes [rows][RS] bytes from the top (RS = deepest row rounded up to whole quads).
-constexpr int V3_POOL_BYTES = 38656;
+constexpr int V3_POOL_BYTES = 36352;
 constexpr int V3_CS = 208;            // column stride of the planes (>= window length)
 constexpr int V3_MAXC = 192;          // surviving reads per window
 constexpr int V3_MD = 48;             // staged M/D ops per read
@@ -859,7 +899,8 @@ struct __align__(8) Md3 {
 struct V3S {
     uint8_t *q;                  // [rows][RS] codes per image row (pixel 0 = reference)
     uint32_t *pw;                // [slots][LS] per (read slot, column): step>=1 code | step-0 code << 8 | insert record / soft-clip marker << 16
-    uint32_t *cnt;               // [NCAT][V3_CS/2] two 16-bit counters per word
+    uint32_t *cnt;               // [NCAT][256/2] 16-bit counters (two per word) per category and (slot group, column)
+    uint32_t *rowcg;             // [4][256/4] 8-bit counters (four per word): inserted bases per (slot group, image row)
     Md3 *md;                     // [V3_WARPS][V3_MD]
     uint32_t *lut;               // [256] code -> RGBA
     uint8_t *pool;               // [V3_POOL]
@@ -874,8 +915,8 @@ struct V3S {
     int *misc;                   // [0] fallback [1] nrec [2] npool [3] Lgen [4] nrows [5] hasS [8..16] warp sums [16..24] warp sums 2
 };
 
-__device__ __forceinline__ void v3_count(const V3S &S, int cat, int c) {
-    atomicAdd(&S.cnt[(cat * V3_CS + c) >> 1], 1u << ((c & 1) << 4));
+__device__ __forceinline__ void v3_count(const V3S &S, int cat, int gc) {      // gc = slot group * LS + column
+    atomicAdd(&S.cnt[(cat * 256 + gc) >> 1], 1u << ((gc & 1) << 4));
 }
 // scan: one warp; coverage difference array and insert lengths of read `r`; first relevant op -> S.j0[ci]
 __device__ void v3_scan_read(const EncArgs &a, const V3S &S, int ci, int qs, int L, int lane) {
@@ -914,8 +955,8 @@ __device__ void v3_scan_read(const EncArgs &a, const V3S &S, int ci, int qs, int
 }
 
 // generate: one warp; every entry of read S.cand[ci] on columns [0, Lgen) -> planes of `slot`
-__device__ void v3_gen_read(const EncArgs &a, const V3S &S, int ci, int slot, int qs, int Lgen, int LS, int H, bool count,
-                            int lane, int warp) {
+__device__ void v3_gen_read(const EncArgs &a, const V3S &S, int ci, int slot, int grp, int qs, int Lgen, int LS, int H,
+                            bool count, int lane, int warp) {
     const int r = S.cand[ci];
     const ReadInfo *ri = a.info + r;
     const int ref_start = ri->ref_start, nops = ri->nops;
@@ -974,7 +1015,7 @@ __device__ void v3_gen_read(const EncArgs &a, const V3S &S, int ci, int slot, in
                         S.scol[slot * 2 + which] = (short)sA;
                         pl[sA * 4 + 2] = 255;
                     } else pl[sA * 4 + 1] = code;
-                    if (count) v3_count(S, cat, sA);
+                    if (count) v3_count(S, cat, grp * LS + sA);
                 }
             } else if (sA >= 1) {
                 // insertion anchored at column sA (Pileup.py:220-230): bases qp+1 .. qp+n
@@ -987,7 +1028,10 @@ __device__ void v3_gen_read(const EncArgs &a, const V3S &S, int ci, int slot, in
                     for (int k2 = 0; k2 < n; k2++) S.pool[off + k2] = __ldg(codep + qp + 1 + k2);
                     const int y0 = S.rowstart[sA];
                     if (count && y0 != 0xFFFF)
-                        for (int k2 = 0; k2 < n && y0 + 1 + k2 < H; k2++) atomicAdd(&S.rowcnt[y0 + 1 + k2], 1);
+                        for (int k2 = 0; k2 < n && y0 + 1 + k2 < H; k2++) {
+                            const int y = y0 + 1 + k2;
+                            atomicAdd(&S.rowcg[(grp * 256 + y) >> 2], 1u << ((y & 3) << 3));
+                        }
                 }
             }
         }
@@ -1017,7 +1061,7 @@ __device__ void v3_gen_read(const EncArgs &a, const V3S &S, int ci, int slot, in
                 int cat = cb >> 5;
                 if (isD) cat = CAT_D; else if (cat == refs[c]) cat = CAT_M;
                 pl[c * 4] = (uint8_t)((cat << 5) | (cb & 31));
-                if (count) v3_count(S, cat, c);
+                if (count) v3_count(S, cat, grp * LS + c);
             }
         }
     }
@@ -1035,12 +1079,12 @@ __device__ __forceinline__ void v3_place(uint32_t code, uint32_t &lo, uint32_t &
     }
 }
 
-__device__ __forceinline__ void v3_walk(const V3S &S, int c, int my_row, int nslots, int LS, int RS, int W, int H,
-                                        uint32_t &lo, uint32_t &hi, const int *s_rowcnt, unsigned short *s_rowfill) {
+__device__ __forceinline__ void v3_walk(const V3S &S, int c, int my_row, int s0, int s1, int LS, int RS, int W, int H,
+                                        uint32_t &lo, uint32_t &hi, uint8_t *rowfill) {
     uint8_t *qrow = S.q + my_row * RS + 1;
     const uint32_t *pw = S.pw + c;
     const int Wm1 = W - 1;
-    for (int s = 0; s < nslots; s++) {
+    for (int s = s0; s < s1; s++) {
         const uint32_t v = pw[s * LS];
         const uint32_t c1 = v & 0xffu, c0 = (v >> 8) & 0xffu, ir = (v >> 16) & 0xffu;
         if (ir == 255u) {
@@ -1055,51 +1099,49 @@ __device__ __forceinline__ void v3_walk(const V3S &S, int c, int my_row, int nsl
             for (int k = 0; k < n; k++) {
                 const int y = my_row + 1 + k;
                 if (y >= H) break;
-                const int pos = s_rowfill[y]++;
-                if (s_rowcnt[y] > Wm1) S.misc[0] = 1;    // deeper than the image: the category sort needs every entry
-                else S.q[y * RS + 1 + pos] = S.pool[off + k];
+                const int pos = rowfill[y]++;
+                if (pos < Wm1 && pos < RS - 1) S.q[y * RS + 1 + pos] = S.pool[off + k];
             }
         }
     }
 }
 
-// finish: the thread that owns a column sorts its insert rows, adds pixel 0 and filler codes up to the quad boundary
-// and writes the entry quads of its rows (16-byte stores through the code -> RGBA table)
-__device__ __forceinline__ void v3_finish_rows(const V3S &S, int my_row, int nown, int RS, int W, const int *s_rowcnt,
-                                               const short *s_rowk, uint8_t ref_code, uint8_t *img) {
-    for (int k = 0; k < nown; k++) {
-        const int y = my_row + k;
-        uint8_t *row = S.q + y * RS;
-        const int tot = min(s_rowcnt[y], W - 1);
-        const bool ins = k != 0;
-        if (ins) {                                    // stable sort by category (A,C,G,T,N) of codes appended in read order
-            for (int i = 2; i <= tot; i++) {
-                const uint8_t c = row[i];
-                int j = i - 1;
-                while (j >= 1 && (row[j] >> 5) > (c >> 5)) { row[j + 1] = row[j]; j--; }
-                row[j + 1] = c;
-            }
+// finish: one thread per image row sorts an insert row, adds pixel 0 and filler codes up to the quad boundary and
+// writes the row's entry quads (16-byte stores through the code -> RGBA table)
+__device__ __forceinline__ void v3_finish_row(const V3S &S, int y, int tot, bool ins, uint8_t ref_code, int RS, int W,
+                                              uint8_t *img) {
+    uint8_t *row = S.q + y * RS;
+    if (ins) {                                        // stable sort by category (A,C,G,T,N) of codes appended in read order
+        for (int i = 2; i <= tot; i++) {
+            const uint8_t c = row[i];
+            int j = i - 1;
+            while (j >= 1 && (row[j] >> 5) > (c >> 5)) { row[j + 1] = row[j]; j--; }
+            row[j + 1] = c;
         }
-        row[0] = ins ? V3_FILL_INS : ref_code;
-        for (int x = tot + 1; x & 3; x++) row[x] = ins ? V3_FILL_INS : V3_FILL_NONE;
-        uint8_t *orow = img + ((size_t)y * W << 2);
-        for (int x0 = 0; x0 <= tot; x0 += 4) {
-            const uint32_t codes = *reinterpret_cast<const uint32_t *>(row + x0);
-            const uint32_t p0 = S.lut[codes & 0xffu], p1 = S.lut[(codes >> 8) & 0xffu];
-            const uint32_t p2 = S.lut[(codes >> 16) & 0xffu], p3 = S.lut[codes >> 24];
-            *reinterpret_cast<uint4 *>(orow + (x0 << 2)) = make_uint4(p0, p1, p2, p3);
-        }
+    }
+    row[0] = ins ? V3_FILL_INS : ref_code;
+    for (int x = tot + 1; x & 3; x++) row[x] = ins ? V3_FILL_INS : V3_FILL_NONE;
+    uint8_t *orow = img + ((size_t)y * W << 2);
+    for (int x0 = 0; x0 <= tot; x0 += 4) {
+        const uint32_t codes = *reinterpret_cast<const uint32_t *>(row + x0);
+        const uint32_t p0 = S.lut[codes & 0xffu], p1 = S.lut[(codes >> 8) & 0xffu];
+        const uint32_t p2 = S.lut[(codes >> 16) & 0xffu], p3 = S.lut[codes >> 24];
+        *reinterpret_cast<uint4 *>(orow + (x0 << 2)) = make_uint4(p0, p1, p2, p3);
     }
 }
 
 __global__ void __launch_bounds__(V3_THREADS, 4)
-encode_windows_v3_kernel(EncArgs a, int *__restrict__ fb_count, int *__restrict__ fb_list, int emit_mode) {
+encode_windows_v3_kernel(EncArgs a, int *__restrict__ fb_count, int *__restrict__ fb_list, int emit_mode,
+                         unsigned long long *__restrict__ dbg) {
     extern __shared__ __align__(16) uint8_t smem[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int w = blockIdx.x;
     const int L = a.L, W = a.W, H = a.H;
     const int qs = a.win_qs[w], qe = qs + L;
     const int lo = a.win_lo[w], hi = a.win_hi[w];
+    // phase clocks (debugging aid, DP_ENC_TIMING): thread 0 adds the cycles between marks to dbg[phase]
+    long long tmark = dbg ? clock64() : 0;
+#define V3_MARK(ph) do { if (dbg && tid == 0) { const long long t_ = clock64(); atomicAdd(&dbg[ph], (unsigned long long)(t_ - tmark)); tmark = t_; } } while (0)
 
     // ---- shared memory carve-up (16-byte aligned sections first)
     uint8_t *p = smem;
@@ -1107,7 +1149,8 @@ encode_windows_v3_kernel(EncArgs a, int *__restrict__ fb_count, int *__restrict_
     uint8_t *s_pool0 = p;                          p += V3_POOL_BYTES;
     S.pw = (uint32_t *)s_pool0;
     S.q = s_pool0;                                 // placed at the top of the pool once the row stride is known
-    S.cnt = (uint32_t *)p;                         p += 4 * (NCAT * V3_CS / 2);
+    S.cnt = (uint32_t *)p;                         p += 4 * (NCAT * 256 / 2);
+    S.rowcg = (uint32_t *)p;                       p += 4 * 256;
     S.md = (Md3 *)p;                               p += sizeof(Md3) * V3_WARPS * V3_MD;
     S.lut = (uint32_t *)p;                         p += 4 * 256;
     S.rec = (uint32_t *)p;                         p += 4 * 256;
@@ -1122,7 +1165,8 @@ encode_windows_v3_kernel(EncArgs a, int *__restrict__ fb_count, int *__restrict_
     S.rowstart = (unsigned short *)p;              p += 2 * V3_CS;         // first image row of a drawn column (0xFFFF: none)
     short *s_rowcol = (short *)p;                  p += 2 * 256;
     short *s_rowk = (short *)p;                    p += 2 * 256;
-    unsigned short *s_rowfill = (unsigned short *)p; p += 2 * 256;         // running fill of insert rows
+    uint8_t *s_rowfill = p;                        p += 4 * 256;           // [slot group][row] running fill of insert rows
+    uint8_t *s_rowref = p;                         p += 256;               // reference-pixel code of an anchor row
     S.scol = (short *)p;                           p += 2 * V3_MAXSLOT * 2;
     S.scode = p;                                   p += V3_MAXSLOT * 2;
     S.refc = p;                                    p += 224;
@@ -1152,10 +1196,11 @@ encode_windows_v3_kernel(EncArgs a, int *__restrict__ fb_count, int *__restrict_
         for (int k = 0; k < 8; k++) if ((tid >> 5) == k) col = rgb[k];
         S.lut[tid] = col | ((uint32_t)(qi <= V3_QMAX ? c_qlut[qi] : 255) << 24);
     }
-    for (int i = tid; i < NCAT * V3_CS / 2; i += V3_THREADS) S.cnt[i] = 0;
+    for (int i = tid; i < NCAT * 256 / 2; i += V3_THREADS) S.cnt[i] = 0;
+    S.rowcg[tid] = 0;
     for (int i = tid; i < V3_CS + 8; i += V3_THREADS) S.cov[i] = 0;
     for (int i = tid; i < V3_CS; i += V3_THREADS) { S.maxins[i] = 0; S.rowstart[i] = 0xFFFF; }
-    s_rowcnt[tid] = 0; s_rowcol[tid] = -1; s_rowk[tid] = 0; s_rowfill[tid] = 0;
+    s_rowcnt[tid] = 0; s_rowcol[tid] = -1; s_rowk[tid] = 0; s_rowref[tid] = V3_FILL_NONE;
     s_fill[tid] = 0xFF000000u; s_fill[256 + tid] = 0xFFFF00FFu;
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 
@@ -1177,6 +1222,7 @@ encode_windows_v3_kernel(EncArgs a, int *__restrict__ fb_count, int *__restrict_
     }
     __syncthreads();
     if (ncand > V3_MAXC) { if (tid == 0) S.misc[0] = 1; ncand = 0; }
+    V3_MARK(0);
     // ---- per read: clean?  first op to look at (checkpoint of the read's CIGAR)
     if (tid < ncand) {
         const int r = S.cand[tid];
@@ -1193,6 +1239,7 @@ encode_windows_v3_kernel(EncArgs a, int *__restrict__ fb_count, int *__restrict_
     }
     __syncthreads();
     if (S.misc[0]) ncand = 0;                         // bail out early: the exact kernel takes the window
+    V3_MARK(1);
     // ---- scan: coverage and insert lengths -> row map
     for (;;) {                                        // warps draw reads from a shared counter (uneven CIGAR density)
         int ci = 0;
@@ -1202,8 +1249,7 @@ encode_windows_v3_kernel(EncArgs a, int *__restrict__ fb_count, int *__restrict_
         v3_scan_read(a, S, ci, qs, L, lane);
     }
     __syncthreads();
-    int my_row = -1, nown = 0;
-    uint8_t ref_code = V3_FILL_NONE;
+    V3_MARK(2);
     {
         const int cv = tid < L ? S.cov[tid] : 0;
         const int inc1 = warp_incl_scan(cv, lane);
@@ -1223,22 +1269,24 @@ encode_windows_v3_kernel(EncArgs a, int *__restrict__ fb_count, int *__restrict_
         const int rstart = excl & 0xffff, ord = excl >> 16;
         if (tid == V3_THREADS - 1) S.misc[4] = (b2 + inc2) & 0xffff;
         if (pop && rstart < H) {
-            my_row = rstart;
-            nown = min(1 + mi, H - rstart);
+            const int nown = min(1 + mi, H - rstart);
             S.rowstart[tid] = (unsigned short)rstart;
             atomicMax(&S.misc[3], tid + 1);
-            ref_code = (uint8_t)((S.refc[ord] << 5) | 29);
+            s_rowref[rstart] = (uint8_t)((S.refc[ord] << 5) | 29);
             for (int k = 0; k < nown; k++) { s_rowcol[rstart + k] = (short)tid; s_rowk[rstart + k] = (short)k; }
         }
         __syncthreads();
     }
+    V3_MARK(3);
     const int Lgen = S.misc[3];
     const int nrows = min(S.misc[4], H);
     // plane geometry for this window: stride = drawn columns rounded up, as many read slots as the pool holds
     const int LS = max(16, (Lgen + 15) & ~15);
     int slots = min(V3_MAXSLOT, V3_POOL_BYTES / (4 * LS));   // counting pass: the whole pool is planes
     int nb = (ncand + slots - 1) / slots;
-    const bool walker = my_row >= 0;
+    // placement runs on G slot groups per column in parallel (thread = group * LS + column): counts are kept per group
+    const int G = nb == 1 ? max(1, min(4, V3_THREADS / LS)) : 1;
+    const int GS = max(1, (ncand + G - 1) / G);
     uint8_t *img = a.out_img + (size_t)w * H * W * 4;
 
     // ---- generate (counting).  One batch: its planes are kept for placement.  More: count over all batches first,
@@ -1258,26 +1306,54 @@ encode_windows_v3_kernel(EncArgs a, int *__restrict__ fb_count, int *__restrict_
             if (lane == 0) s = atomicAdd(&S.misc[7], 1);
             s = __shfl_sync(0xffffffffu, s, 0);
             if (s >= nslots) break;
-            v3_gen_read(a, S, b * slots + s, s, qs, Lgen, LS, H, true, lane, warp);
+            v3_gen_read(a, S, b * slots + s, s, s / GS, qs, Lgen, LS, H, true, lane, warp);
         }
         __syncthreads();
     }
-    // ---- counts -> first slot of each category (sortingKey order A,C,G,T,D,M,N), saturated at W; row stride of S.q
+    V3_MARK(4);
+    // ---- counts -> first slot of each category (sortingKey order A,C,G,T,D,M,N) for every (group, column) thread,
+    // saturated at W; totals per image row; row stride of S.q
+    const int wg = tid / LS, wc = tid - wg * LS;
+    int my_row = -1, nown = 0;
+    if (wg < G && wc < Lgen && S.rowstart[wc] != 0xFFFF) {
+        my_row = S.rowstart[wc];
+        nown = min(1 + S.maxins[wc], H - my_row);
+    }
+    const bool walker = my_row >= 0;
     uint32_t run_lo = 0, run_hi = 0;
     if (walker) {
         int acc = 0;
 #pragma unroll
         for (int c = 0; c < NCAT; c++) {
-            const uint32_t wv = S.cnt[(c * V3_CS + tid) >> 1];
-            const int n = (wv >> ((tid & 1) << 4)) & 0xffff;
-            const uint32_t bv = (uint32_t)min(acc, W - 1);
+            int before = 0, tot = 0;
+            for (int g = 0; g < G; g++) {
+                const int gc = c * 256 + g * LS + wc;
+                const int n = (S.cnt[gc >> 1] >> ((gc & 1) << 4)) & 0xffff;
+                if (g < wg) before += n;
+                tot += n;
+            }
+            const uint32_t bv = (uint32_t)min(acc + before, W - 1);
             if (c < 4) run_lo |= bv << (c << 3); else run_hi |= bv << ((c - 4) << 3);
-            acc += n;
+            acc += tot;
         }
-        s_rowcnt[my_row] = min(acc, W - 1);
         int mx = min(acc, W - 1);
-        for (int k = 1; k < nown; k++) mx = max(mx, min(s_rowcnt[my_row + k], W - 1));
-        atomicMax(&S.misc[9], mx);
+        if (wg == 0) s_rowcnt[my_row] = mx;
+        for (int k = 1; k < nown; k++) {             // insert rows of this column
+            const int y = my_row + k;
+            int before = 0, tot = 0;
+            for (int g = 0; g < G; g++) {
+                const int n = (S.rowcg[(g * 256 + y) >> 2] >> ((y & 3) << 3)) & 0xff;
+                if (g < wg) before += n;
+                tot += n;
+            }
+            s_rowfill[wg * 256 + y] = (uint8_t)before;
+            if (wg == 0) {
+                s_rowcnt[y] = tot;
+                if (tot > W - 1) S.misc[0] = 1;       // deeper than the image: the category sort needs every entry
+                mx = max(mx, min(tot, W - 1));
+            }
+        }
+        if (wg == 0) atomicMax(&S.misc[9], mx);
     }
     __syncthreads();
     const int RS = (S.misc[9] + 4) & ~3;             // pixel 0 + entries, rounded up to whole quads
@@ -1299,6 +1375,7 @@ encode_windows_v3_kernel(EncArgs a, int *__restrict__ fb_count, int *__restrict_
         }
         return;                                      // the exact kernel recomputes this window
     }
+    V3_MARK(5);
     // ---- emit 1: the filler tail of every row (and blank rows) -- one bulk copy (TMA) per row out of two constant
     // filler rows in shared memory, issued by the high threads while the low ones place; emit_mode 1 = plain stores
     if (emit_mode == 0) {
@@ -1329,9 +1406,10 @@ encode_windows_v3_kernel(EncArgs a, int *__restrict__ fb_count, int *__restrict_
             }
         }
     }
+    V3_MARK(6);
     // ---- place
     if (!multi) {
-        if (walker) v3_walk(S, tid, my_row, ncand, LS, RS, W, H, run_lo, run_hi, s_rowcnt, s_rowfill);
+        if (walker) v3_walk(S, wc, my_row, wg * GS, min((wg + 1) * GS, ncand), LS, RS, W, H, run_lo, run_hi, s_rowfill + wg * 256);
     } else {
         for (int b = 0; b < nb; b++) {
             const int nslots = min(slots, ncand - b * slots);
@@ -1349,37 +1427,36 @@ encode_windows_v3_kernel(EncArgs a, int *__restrict__ fb_count, int *__restrict_
                 if (lane == 0) s = atomicAdd(&S.misc[7], 1);
                 s = __shfl_sync(0xffffffffu, s, 0);
                 if (s >= nslots) break;
-                v3_gen_read(a, S, b * slots + s, s, qs, Lgen, LS, H, false, lane, warp);
+                v3_gen_read(a, S, b * slots + s, s, 0, qs, Lgen, LS, H, false, lane, warp);
             }
             __syncthreads();
-            if (walker) v3_walk(S, tid, my_row, nslots, LS, RS, W, H, run_lo, run_hi, s_rowcnt, s_rowfill);
+            if (walker && wg == 0) v3_walk(S, wc, my_row, 0, nslots, LS, RS, W, H, run_lo, run_hi, s_rowfill);
         }
     }
-    // ---- finish: each column's thread completes and writes its own rows
-    if (walker) v3_finish_rows(S, my_row, nown, RS, W, s_rowcnt, s_rowk, ref_code, img);
+    __syncthreads();
+    V3_MARK(7);
+    // ---- finish: one thread per image row
+    if (tid < nrows) v3_finish_row(S, tid, s_rowcnt[tid], s_rowk[tid] != 0, s_rowref[tid], RS, W, img);
     for (int y = tid; y < H; y += V3_THREADS) {
         if (a.out_rowpos) a.out_rowpos[(size_t)w * H + y] = (y < nrows) ? qs + s_rowcol[y] : -1;
         if (a.out_rowins) a.out_rowins[(size_t)w * H + y] = (y < nrows) ? s_rowk[y] : 0;
     }
+    if (tid == 0 && a.out_status) a.out_status[w] = 0;
+    V3_MARK(8);
     if (emit_mode == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // shared memory must outlive the copies
-    __syncthreads();
-    if (tid == 0) {
-        if (S.misc[0]) {                             // an insert row deeper than the image turned up while placing
-            const int k = atomicAdd(fb_count, 1);
-            fb_list[k] = w;
-        }
-        if (a.out_status) a.out_status[w] = 0;
-    }
+    V3_MARK(9);
+#undef V3_MARK
 }
 
 static size_t encoder_v3_smem_bytes(const dp_encode_params *p) {
     (void)p;
     size_t s = 0;
     s += V3_POOL_BYTES;
-    s += 4 * (NCAT * V3_CS / 2);
+    s += 4 * (NCAT * 256 / 2) + 4 * 256;                                   // cnt, rowcg
     s += sizeof(Md3) * V3_WARPS * V3_MD;
     s += 4 * 256 * 2 + V3_POOL + 4 * V3_MAXC * 2 + 4 * (V3_CS + 8) + 4 * V3_CS + 4 * 32;
-    s += 4 * 2 * 256 + 4 * 256 + 2 * V3_CS + 2 * 256 * 3 + 2 * V3_MAXSLOT * 2 + V3_MAXSLOT * 2 + 224;
+    s += 4 * 2 * 256 + 4 * 256 + 2 * V3_CS + 2 * 256 * 2 + 4 * 256 + 256;  // fill, rowcnt, rowstart, rowcol/rowk, rowfill, rowref
+    s += 2 * V3_MAXSLOT * 2 + V3_MAXSLOT * 2 + 224;
     return s + 16;
 }
 
@@ -1437,6 +1514,7 @@ int64_t dp_encode_workspace_bytes(int32_t n_reads, int64_t n_cigar, int64_t n_ba
     b += dp::align_up((int64_t)sizeof(int) * ((n_cigar >> 2) + n_reads + 2), 256);           /* checkpoints */
     b += dp::align_up((int64_t)sizeof(int) * (n_reads > 0 ? n_reads : 1), 256);              /* filtered endpos */
     b += dp::align_up((n_bases > 0 ? n_bases : 0) + 16, 256);                                /* per-base code bytes */
+    b += 256;                                                                                /* phase clocks (debug) */
     return b;
 }
 
@@ -1490,6 +1568,8 @@ int dp_encode_windows(const dp_reads *reads, int32_t n_windows, const int32_t *w
     int *endk = (int *)wp;
     wp += dp::align_up((int64_t)sizeof(int) * (reads->n_reads > 0 ? reads->n_reads : 1), 256);
     uint8_t *code0 = wp;
+    wp += dp::align_up((reads->n_bases > 0 ? reads->n_bases : 0) + 16, 256);
+    unsigned long long *dbg = (unsigned long long *)wp;
 
     /* DP_ENC_TIMING=1: CUDA events around each kernel of this call, printed to stderr (synchronises; debugging aid) */
     static int timing = -1;
@@ -1497,9 +1577,13 @@ int dp_encode_windows(const dp_reads *reads, int32_t n_windows, const int32_t *w
     cudaEvent_t ev[5];
     if (timing) { for (int i = 0; i < 5; i++) cudaEventCreate(&ev[i]); cudaEventRecord(ev[0], st); }
     if (reads->n_reads > 0) {
-        const int warps_per_block = 8;
-        const int blocks = (reads->n_reads + warps_per_block - 1) / warps_per_block;
-        dp::prep_reads_kernel<<<blocks, 256, 0, st>>>(*reads, aux, RP, QP, info, ckpt, endk, p->map_quality_cutoff);
+        if (n_cigar / reads->n_reads >= 96) {                  /* long CIGARs (long reads): one block per read */
+            dp::prep_reads_kernel<8><<<reads->n_reads, 256, 0, st>>>(*reads, aux, RP, QP, info, ckpt, endk, p->map_quality_cutoff);
+        } else {
+            const int warps_per_block = 8;
+            const int blocks = (reads->n_reads + warps_per_block - 1) / warps_per_block;
+            dp::prep_reads_kernel<1><<<blocks, 256, 0, st>>>(*reads, aux, RP, QP, info, ckpt, endk, p->map_quality_cutoff);
+        }
         DP_CUDA_CHECK(cudaGetLastError());
         if (reads->n_bases > 0) {
             const int64_t nb = (reads->n_bases + 256 * 16 - 1) / (256 * 16);
@@ -1534,7 +1618,8 @@ int dp_encode_windows(const dp_reads *reads, int32_t n_windows, const int32_t *w
     DP_CUDA_CHECK(cudaFuncSetAttribute(dp::encode_windows_v3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem3));
     static int emit_mode = -1;                                 /* DP_ENC_EMIT=stg: plain stores instead of bulk copies */
     if (emit_mode < 0) { const char *e = getenv("DP_ENC_EMIT"); emit_mode = (e && !strcmp(e, "stg")) ? 1 : 0; }
-    dp::encode_windows_v3_kernel<<<n_windows, dp::V3_THREADS, smem3, st>>>(a, fb, fb + 64, emit_mode);
+    if (timing) cudaMemsetAsync(dbg, 0, 256, st);
+    dp::encode_windows_v3_kernel<<<n_windows, dp::V3_THREADS, smem3, st>>>(a, fb, fb + 64, emit_mode, timing ? dbg : nullptr);
     DP_CUDA_CHECK(cudaGetLastError());
     if (timing) cudaEventRecord(ev[3], st);
     dp::encode_windows_kernel<<<n_windows, dp::ENC_THREADS, smem, st>>>(a, fb, fb + 64);
@@ -1549,6 +1634,11 @@ int dp_encode_windows(const dp_reads *reads, int32_t n_windows, const int32_t *w
         fprintf(stderr, "[dp_encode_windows] %d windows: prep %.3f ms, base codes %.3f ms, fast kernel %.3f ms, exact kernel %.3f ms\n",
                 n_windows, t[0], t[1], t[2], t[3]);
         for (int i = 0; i < 5; i++) cudaEventDestroy(ev[i]);
+        unsigned long long hd[16];
+        cudaMemcpy(hd, dbg, sizeof(hd), cudaMemcpyDeviceToHost);
+        fprintf(stderr, "[dp_encode_windows] fast kernel cycles/window by phase (setup+compact, info, scan, rowmap, gen, bases, emit1, place, finish, drain):");
+        for (int i = 0; i < 10; i++) fprintf(stderr, " %llu", hd[i] / (unsigned long long)n_windows);
+        fprintf(stderr, "\n");
     }
     return DP_OK;
 }
