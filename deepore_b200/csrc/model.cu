@@ -52,6 +52,8 @@ struct Model {
     __nv_bfloat16 *arena = nullptr;       // [NSLOT_BF][mcap][HP]
     __nv_bfloat16 *arena_lo = nullptr;    // precise only
     float *state = nullptr;               // [NSLOT_F32][mcap][HP]
+    int bf_state = 0;                     // one-pass bf16 mode on the CTA-pair kernel: number of leading GRU layers whose state
+                                          // lives in the bf16 rows only (no fp32 copy); DP_GRU_STATE = f32 | mixed | bf16
     __nv_bfloat16 *w_fold = nullptr;      // [3*HP][kcols_fold]
     float *b_fold = nullptr;              // [3*HP]
     __nv_bfloat16 *w_gru = nullptr;       // [n_layers*2*3*HP][kcols_gru]
@@ -61,7 +63,7 @@ struct Model {
     int fold_tab_off = 0, fold_tab_n = 0;
     int gru_tab_off[3][3][2], gru_tab_n[3][3][2];
     long long kcols_fold = 0, kcols_gru = 0;
-    CUtensorMap tm_img, tm_arena, tm_arena_lo, tm_wfold, tm_wgru, tm_wgru128, tm_wgru64;
+    CUtensorMap tm_img, tm_arena, tm_arena_lo, tm_wfold, tm_wgru, tm_wgru96, tm_wgru64, tm_wgru32;
     int gru_2cta = 1;              // CTA-pair GRU kernel (env DP_GRU=1cta selects the single-CTA kernel)
     // optional per-kernel timing (bench.py roofline): one event per launch boundary, harvested by dp_model_profile_read
     int profile = 0;
@@ -136,6 +138,48 @@ __global__ void __launch_bounds__(256) fc1_argmax_kernel(const float *__restrict
 #pragma unroll
         for (int j = 0; j < HP / 128; j++) {
             const float4 wv = __ldg(reinterpret_cast<const float4 *>(w + c * HP + 4 * (lane + 32 * j)));
+            acc = fmaf(x[4 * j], wv.x, acc); acc = fmaf(x[4 * j + 1], wv.y, acc);
+            acc = fmaf(x[4 * j + 2], wv.z, acc); acc = fmaf(x[4 * j + 3], wv.w, acc);
+        }
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, d);
+        acc += __ldg(b + c);
+        if (lane == 0 && logits) logits[(m * seq_len + t) * n_class + c] = acc;
+        if (c == 0 || acc > best) { best = acc; besti = c; }
+    }
+    if (lane == 0 && pred) pred[m * seq_len + t] = (uint8_t)besti;
+}
+
+// The same over the bf16 rows [row][512] of the arena (one-pass bf16 mode keeps no fp32 state): lane handles 16
+// consecutive units (32 bytes of hf and of hb).
+__global__ void __launch_bounds__(256) fc1_argmax_bf_kernel(const __nv_bfloat16 *__restrict__ hf,
+                                                            const __nv_bfloat16 *__restrict__ hb, long long slot_stride,
+                                                            const float *__restrict__ w, const float *__restrict__ b,
+                                                            int n_class, int seq_len, long long n_rows,
+                                                            float *__restrict__ logits, uint8_t *__restrict__ pred) {
+    const long long wid = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (wid >= n_rows * seq_len) return;
+    const long long m = wid / seq_len;
+    const int t = (int)(wid % seq_len);
+    const uint4 *pf = reinterpret_cast<const uint4 *>(hf + t * slot_stride + m * HP + lane * 16);
+    const uint4 *pb = reinterpret_cast<const uint4 *>(hb + t * slot_stride + m * HP + lane * 16);
+    const uint4 f0 = pf[0], f1 = pf[1], b0 = pb[0], b1 = pb[1];
+    const uint32_t fw[8] = {f0.x, f0.y, f0.z, f0.w, f1.x, f1.y, f1.z, f1.w};
+    const uint32_t bw[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+    float x[16];
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+        x[2 * i] = __uint_as_float(fw[i] << 16) + __uint_as_float(bw[i] << 16);
+        x[2 * i + 1] = __uint_as_float(fw[i] & 0xffff0000u) + __uint_as_float(bw[i] & 0xffff0000u);
+    }
+    float best = 0.f;
+    int besti = 0;
+    for (int c = 0; c < n_class; c++) {
+        float acc = 0.f;
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const float4 wv = __ldg(reinterpret_cast<const float4 *>(w + c * HP + lane * 16 + 4 * j));
             acc = fmaf(x[4 * j], wv.x, acc); acc = fmaf(x[4 * j + 1], wv.y, acc);
             acc = fmaf(x[4 * j + 2], wv.z, acc); acc = fmaf(x[4 * j + 3], wv.w, acc);
         }
@@ -327,13 +371,22 @@ static int build_model(Model *m, const dp_model_weights *w) {
     rc = make_tmap_bf16_2d(&m->tm_wgru, m->w_gru, (uint64_t)m->n_layers * 2 * 3 * HP, (uint64_t)m->kcols_gru,
                            (uint64_t)m->kcols_gru * 2, 192);
     if (rc) return rc;
-    rc = make_tmap_bf16_2d(&m->tm_wgru128, m->w_gru, (uint64_t)m->n_layers * 2 * 3 * HP, (uint64_t)m->kcols_gru,
-                           (uint64_t)m->kcols_gru * 2, 128);
+    rc = make_tmap_bf16_2d(&m->tm_wgru96, m->w_gru, (uint64_t)m->n_layers * 2 * 3 * HP, (uint64_t)m->kcols_gru,
+                           (uint64_t)m->kcols_gru * 2, 96);
+    if (rc) return rc;
+    rc = make_tmap_bf16_2d(&m->tm_wgru32, m->w_gru, (uint64_t)m->n_layers * 2 * 3 * HP, (uint64_t)m->kcols_gru,
+                           (uint64_t)m->kcols_gru * 2, 32);
     if (rc) return rc;
     rc = make_tmap_bf16_2d(&m->tm_wgru64, m->w_gru, (uint64_t)m->n_layers * 2 * 3 * HP, (uint64_t)m->kcols_gru,
                            (uint64_t)m->kcols_gru * 2, 64);
     const char *e = getenv("DP_GRU");
     m->gru_2cta = (e && !strcmp(e, "1cta")) ? 0 : 1;
+    const char *e3 = getenv("DP_GRU_STATE");            // "f32": keep the fp32 state copy also in one-pass bf16 mode
+    m->bf_state = 0;
+    if (m->gru_2cta && !m->precise && e3) {
+        if (!strcmp(e3, "bf16")) m->bf_state = m->n_layers;
+        else if (!strcmp(e3, "mixed")) m->bf_state = m->n_layers - 1;
+    }
     return rc;
 }
 
@@ -397,31 +450,43 @@ static int forward_rows(Model *m, const uint8_t *img, long long n_rows, float *l
                 int hs = -1;
                 if (sg > 0) hs = d == 0 ? f32_slot_hf(k, t - 1) : f32_slot_hb(k, t + 1);
                 else if (k > 0) hs = d == 0 ? f32_slot_hf(k - 1, 2) : f32_slot_hb(k - 1, 0);
-                P.h_prev = hs >= 0 ? m->state + (size_t)hs * mc * HP : nullptr;
+                int hsb = -1;                            // the same state in the bf16 arena
+                if (sg > 0) hsb = d == 0 ? bf_slot_hf(k, t - 1) : bf_slot_hb(k, t + 1);
+                else if (k > 0) hsb = d == 0 ? bf_slot_hf(k - 1, 2) : bf_slot_hb(k - 1, 0);
                 const int os = d == 0 ? f32_slot_hf(k, t) : f32_slot_hb(k, t);
                 const int ob = d == 0 ? bf_slot_hf(k, t) : bf_slot_hb(k, t);
-                P.h_out = m->state + (size_t)os * mc * HP;
+                // layer k reads h0 from layer k-1 (sg == 0): fp32 only if that layer kept one
+                const bool prev_f32 = sg > 0 ? k >= m->bf_state : (k - 1) >= m->bf_state;
+                if (hs >= 0 && prev_f32) P.h_prev = m->state + (size_t)hs * mc * HP;
+                else if (hsb >= 0) P.h_prev_bf = m->arena + (size_t)hsb * mc * HP;
+                P.h_out = k >= m->bf_state ? m->state + (size_t)os * mc * HP : nullptr;
                 P.h_out_bf = m->arena + (size_t)ob * mc * HP;
                 P.h_out_lo = m->precise ? m->arena_lo + (size_t)ob * mc * HP : nullptr;
                 if (sg == 2 && k + 1 < m->n_layers) {
                     // sum of directions (model.py:131-133) -> bf16 input of the next layer
                     if (d == 0) {
-                        P.partner = m->state + (size_t)f32_slot_hb(k, 2) * mc * HP;
+                        if (k < m->bf_state) {
+                            P.partner_bf = m->arena + (size_t)bf_slot_hb(k, 2) * mc * HP;
+                            P.partner2_bf = m->arena + (size_t)bf_slot_hb(k, 1) * mc * HP;
+                        } else {
+                            P.partner = m->state + (size_t)f32_slot_hb(k, 2) * mc * HP;
+                            P.partner2 = m->state + (size_t)f32_slot_hb(k, 1) * mc * HP;
+                        }
                         P.xsum = m->arena + (size_t)bf_slot_xn(k, 2) * mc * HP;
-                        P.partner2 = m->state + (size_t)f32_slot_hb(k, 1) * mc * HP;
                         P.xsum2 = m->arena + (size_t)bf_slot_xn(k, 1) * mc * HP;
                         if (m->precise) {
                             P.xsum_lo = m->arena_lo + (size_t)bf_slot_xn(k, 2) * mc * HP;
                             P.xsum2_lo = m->arena_lo + (size_t)bf_slot_xn(k, 1) * mc * HP;
                         }
                     } else {
-                        P.partner = m->state + (size_t)f32_slot_hf(k, 0) * mc * HP;
+                        if (k < m->bf_state) P.partner_bf = m->arena + (size_t)bf_slot_hf(k, 0) * mc * HP;
+                        else P.partner = m->state + (size_t)f32_slot_hf(k, 0) * mc * HP;
                         P.xsum = m->arena + (size_t)bf_slot_xn(k, 0) * mc * HP;
                         if (m->precise) P.xsum_lo = m->arena_lo + (size_t)bf_slot_xn(k, 0) * mc * HP;
                     }
                 }
             }
-            int rc = m->gru_2cta ? launch_gru_step2(tmA, &m->tm_wgru128, &m->tm_wgru64, g, st)
+            int rc = m->gru_2cta ? launch_gru_step2(tmA, &m->tm_wgru96, &m->tm_wgru64, &m->tm_wgru32, g, st)
                                  : launch_gru_step(tmA, &m->tm_wgru, g, st);
             if (rc) return rc;
             mark();
@@ -431,9 +496,14 @@ static int forward_rows(Model *m, const uint8_t *img, long long n_rows, float *l
         const int k = m->n_layers - 1;
         const long long warps = n_rows * S;
         const unsigned blocks = (unsigned)((warps * 32 + 255) / 256);
-        fc1_argmax_kernel<<<blocks, 256, 0, st>>>(m->state + (size_t)f32_slot_hf(k, 0) * mc * HP,
-                                                  m->state + (size_t)f32_slot_hb(k, 0) * mc * HP, mc * HP, m->w_fc1,
-                                                  m->b_fc1, m->n_class, S, n_rows, logits, pred);
+        if (k < m->bf_state)
+            fc1_argmax_bf_kernel<<<blocks, 256, 0, st>>>(m->arena + (size_t)bf_slot_hf(k, 0) * mc * HP,
+                                                         m->arena + (size_t)bf_slot_hb(k, 0) * mc * HP, mc * HP, m->w_fc1,
+                                                         m->b_fc1, m->n_class, S, n_rows, logits, pred);
+        else
+            fc1_argmax_kernel<<<blocks, 256, 0, st>>>(m->state + (size_t)f32_slot_hf(k, 0) * mc * HP,
+                                                      m->state + (size_t)f32_slot_hb(k, 0) * mc * HP, mc * HP, m->w_fc1,
+                                                      m->b_fc1, m->n_class, S, n_rows, logits, pred);
         DP_CUDA_CHECK(cudaGetLastError());
     }
     while (m->profile && prof_i < PROF_MARKS) mark();     // unused marks collapse onto the end
@@ -527,6 +597,13 @@ int dp_model_peek(dp_model *h, int32_t what, int64_t n_rows, float *host_out) {
     }
     const int k = what / 100, d = (what / 10) % 10, t = what % 10;
     DP_REQUIRE(what >= 100 && k >= 1 && k <= m->n_layers && d < 2 && t < 3, "unknown peek id");
+    if (k - 1 < m->bf_state) {
+        std::vector<uint16_t> tmp(n);
+        const int bslot = d == 0 ? dp::bf_slot_hf(k - 1, t) : dp::bf_slot_hb(k - 1, t);
+        DP_CUDA_CHECK(cudaMemcpy(tmp.data(), m->arena + (size_t)bslot * m->mcap * dp::HP, n * 2, cudaMemcpyDeviceToHost));
+        for (size_t i = 0; i < n; i++) host_out[i] = dp::bf2f(tmp[i]);
+        return DP_OK;
+    }
     const int slot = d == 0 ? dp::f32_slot_hf(k - 1, t) : dp::f32_slot_hb(k - 1, t);
     const size_t nb = (size_t)((n_rows + 127) / 128 * 128) * dp::HP;
     std::vector<float> tmp(nb);

@@ -157,7 +157,7 @@ __device__ __forceinline__ void mbar_arrive_cluster(uint32_t bar, uint32_t rank)
         "{\n"
         ".reg .b32 ra;\n"
         "mapa.shared::cluster.u32 ra, %0, %1;\n"
-        "mbarrier.arrive.release.cluster.shared::cluster.b64 _, [ra];\n"
+        "mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [ra];\n"
         "}\n"
         ::"r"(bar), "r"(rank) : "memory");
 }

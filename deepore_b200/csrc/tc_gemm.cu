@@ -376,6 +376,15 @@ __device__ __forceinline__ void rows_store_bf16(__nv_bfloat16 *base, long long m
     }
 }
 
+// 16 consecutive units of row m from bf16 rows [row][512] (32 bytes, two 16-byte loads)
+__device__ __forceinline__ void rows_load_bf16(const __nv_bfloat16 *base, long long m, int u0, float (&f)[16]) {
+    const uint4 *p = reinterpret_cast<const uint4 *>(base + m * GRU_HP + u0);
+    const uint4 a = p[0], b = p[1];
+    const uint32_t w[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+#pragma unroll
+    for (int i = 0; i < 8; i++) { f[2 * i] = __uint_as_float(w[i] << 16); f[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u); }
+}
+
 // Gate math + state update + stores for one group of 16 hidden units of the warp's 32 rows.
 template <bool FAST_ACT>
 __device__ __forceinline__ void gru_finish16(const GruProblem &P, int M, long long m_warp0, int lane, int u0,
@@ -399,13 +408,14 @@ __device__ __forceinline__ void gru_finish16(const GruProblem &P, int M, long lo
         hn[i] = fmaf(z, hp[i] - nn, nn);                  // (1-z)*n + z*h
     }
     if (dbg == 6) { if (hn[3] == 123.456f) P.h_out[0] = hn[1]; return; }
-    if (row_ok) state_store16(P.h_out, m, u0, hn);
+    if (row_ok && P.h_out) state_store16(P.h_out, m, u0, hn);
     if (dbg == 7) return;
     if (P.h_out_bf) rows_store_bf16(P.h_out_bf, m_warp0, u0, hn, M, lane, false);
     if (P.h_out_lo) rows_store_bf16(P.h_out_lo, m_warp0, u0, hn, M, lane, true);
-    if (P.partner) {                                       // sum of directions (model.py:131-133)
+    if (P.partner || P.partner_bf) {                       // sum of directions (model.py:131-133)
         float pt[16];
-        if (row_ok) state_load16(P.partner, m, u0, pt);
+        if (row_ok && P.partner) state_load16(P.partner, m, u0, pt);
+        else if (row_ok) rows_load_bf16(P.partner_bf, m, u0, pt);
         else {
 #pragma unroll
             for (int i = 0; i < 16; i++) pt[i] = 0.f;
@@ -415,9 +425,10 @@ __device__ __forceinline__ void gru_finish16(const GruProblem &P, int M, long lo
         rows_store_bf16(P.xsum, m_warp0, u0, pt, M, lane, false);
         if (P.xsum_lo) rows_store_bf16(P.xsum_lo, m_warp0, u0, pt, M, lane, true);
     }
-    if (P.partner2) {
+    if (P.partner2 || P.partner2_bf) {
         float pt[16];
-        if (row_ok) state_load16(P.partner2, m, u0, pt);
+        if (row_ok && P.partner2) state_load16(P.partner2, m, u0, pt);
+        else if (row_ok) rows_load_bf16(P.partner2_bf, m, u0, pt);
         else {
 #pragma unroll
             for (int i = 0; i < 16; i++) pt[i] = 0.f;
@@ -550,7 +561,7 @@ gru_step_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
             float hp[2][16];
 #pragma unroll
             for (int c2 = 0; c2 < 2; c2++) {
-                if (P.h_prev && m < g.M && g.debug != 5) state_load16(P.h_prev, m, ub * GRU_UB + (half * 2 + c2) * 16, hp[c2]);
+                if (P.h_prev && m < g.M && (g.debug & 0xff) != 5 && (g.debug & 0xff) != 1) state_load16(P.h_prev, m, ub * GRU_UB + (half * 2 + c2) * 16, hp[c2]);
                 else {
 #pragma unroll
                     for (int i = 0; i < 16; i++) hp[c2][i] = 0.f;
@@ -561,7 +572,7 @@ gru_step_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
             const uint32_t taddr = tmem_base + as * 256 + ((uint32_t)(wq * 32) << 16);
 #pragma unroll
             for (int c2 = 0; c2 < 2; c2++) {
-                if (g.debug == 1) break;
+                if ((g.debug & 0xff) == 1) break;
                 const int cb = half * 2 + c2;
                 uint32_t vr[16], vz[16], vx[16], vh[16];
                 tmem_ld16(taddr + cb * 16, vr);
@@ -569,7 +580,7 @@ gru_step_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
                 tmem_ld16(taddr + 128 + cb * 16, vx);
                 if (has_h) tmem_ld16(taddr + 192 + cb * 16, vh);
                 tmem_ld_wait();
-                gru_finish16<FAST_ACT>(P, g.M, m_warp0, lane, ub * GRU_UB + cb * 16, vr, vz, vx, vh, has_h, hp[c2], g.debug);
+                gru_finish16<FAST_ACT>(P, g.M, m_warp0, lane, ub * GRU_UB + cb * 16, vr, vz, vx, vh, has_h, hp[c2], g.debug & 0xff);
             }
             tc_fence_before();
             __syncwarp();
@@ -595,16 +606,25 @@ gru_step_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
 //   * accumulator columns per CTA: [r 64 | z 64 | W_in x 64 | W_hn h 64], so the epilogue is that of the 1-CTA kernel.
 // Barriers: `full` (leader only; both CTAs' TMA bytes are credited to it), `empty` / `tmem_full` (per CTA, released by
 // the leader's multicast tcgen05.commit), `tmem_empty` (leader, 16 arrivals: 8 epilogue warps of each CTA).
-constexpr int GRU2_STAGE_BYTES = A_STAGE_BYTES + GRU_B_STAGE_BYTES;   // 16 KB A + 24 KB B region (192 rows)
-constexpr int GRU2_STAGES = 5;
-constexpr int GRU2_SMEM_BYTES = GRU2_STAGES * GRU2_STAGE_BYTES + 1024 + 256;
-constexpr uint32_t GRU2_TX_BYTES = 2 * A_STAGE_BYTES + 128 * 128 + 64 * 128;   // both A tiles + 128 + 64 weight rows
+// Weight rows per CTA and chunk: 96.  Input chunk: ONE N=192 MMA over [r|z|n] rows split 96/96 between the CTAs ->
+// TMEM columns 0..191.  Hidden chunk: an N=128 MMA over [r|z] (64 rows per CTA, region rows 0..63) -> columns 0..127 and
+// an N=64 MMA over [n] (32 rows per CTA, region rows 64..95) -> columns 192..255 (W_hn.h stays separate because r
+// multiplies it).  No zero-padded operand rows: every MMA column is useful work.
+constexpr int GRU2_B_ROWS = 96;
+constexpr int GRU2_STAGE_BYTES = A_STAGE_BYTES + GRU2_B_ROWS * 128;   // 16 KB A + 12 KB B
+constexpr int GRU2_STAGES = 7;
+constexpr int GRU2_EPI_WARPS = 16;
+constexpr int GRU2_THREADS = 128 + 32 * GRU2_EPI_WARPS;   // warps 0-3: TMA producer, MMA issuer, TMEM allocator, spare
+constexpr int GRU2_MAX_CHUNKS = 48;                  // per problem: 16 K-chunks x 3 split-bf16 passes
+constexpr int GRU2_SMEM_BYTES = GRU2_STAGES * GRU2_STAGE_BYTES + 1024 + 256 + 2 * GRU2_MAX_CHUNKS * 16;
+constexpr uint32_t GRU2_TX_BYTES = 2 * A_STAGE_BYTES + 2 * GRU2_B_ROWS * 128;   // both CTAs' A tiles and weight rows
 
 template <bool FAST_ACT>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GRU_THREADS, 1)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GRU2_THREADS, 1)
 gru_step2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1,
                  const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmA3,
-                 const __grid_constant__ CUtensorMap tmB128, const __grid_constant__ CUtensorMap tmB64, const GruArgs g) {
+                 const __grid_constant__ CUtensorMap tmB96, const __grid_constant__ CUtensorMap tmB64,
+                 const __grid_constant__ CUtensorMap tmB32, const GruArgs g) {
     constexpr int STAGES = GRU2_STAGES;
     extern __shared__ uint8_t smem_raw[];
     const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -616,6 +636,9 @@ gru_step2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
     const uint32_t tmem_slot = bar_base + 8u * (2 * STAGES + 4);
     uint8_t *smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));          // generic pointer to the aligned base
     uint32_t *tmem_slot_ptr = reinterpret_cast<uint32_t *>(smem_gen + (tmem_slot - smem_base));
+    // the K-chunk tables of both problems, copied to shared memory once: the producer and the MMA issuer are single
+    // threads and a global load per chunk in their loops (hundreds of cycles, serialised) paced the whole pipeline
+    KChunk *s_chunks = reinterpret_cast<KChunk *>(smem_gen + STAGES * GRU2_STAGE_BYTES + 256);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t rank = cluster_ctarank();
@@ -625,25 +648,18 @@ gru_step2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
 
     if (warp == 0 && lane == 0) {
         prefetch_tmap(&tmA0); prefetch_tmap(&tmA1); prefetch_tmap(&tmA2); prefetch_tmap(&tmA3);
-        prefetch_tmap(&tmB128); prefetch_tmap(&tmB64);
+        prefetch_tmap(&tmB96); prefetch_tmap(&tmB64); prefetch_tmap(&tmB32);
     }
     if (warp == 1 && lane == 0) {
         for (int s = 0; s < STAGES; s++) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
-        for (int s = 0; s < 2; s++) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), 16); }
+        for (int s = 0; s < 2; s++) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), 2 * GRU2_EPI_WARPS); }
         fence_barrier_init();
     }
     if (warp == 2) { tmem_alloc_2sm(tmem_slot, 512); tmem_relinquish_2sm(); }
-    if (rank == 1) {
-        // zero the outer thirds (rows 0..63 and 128..191) of every stage's weight region, once
-        for (int s = 0; s < STAGES; s++) {
-            uint4 *b = reinterpret_cast<uint4 *>(smem_gen + s * GRU2_STAGE_BYTES + A_STAGE_BYTES);
-            for (int i = threadIdx.x; i < 64 * 128 / 16; i += GRU_THREADS) {
-                b[i] = make_uint4(0u, 0u, 0u, 0u);
-                b[128 * 128 / 16 + i] = make_uint4(0u, 0u, 0u, 0u);
-            }
-        }
-        fence_proxy_async_smem();
-    }
+    if (warp >= 4)
+        for (int pi = 0; pi < g.n_prob; pi++)
+            for (int i = threadIdx.x - 128; i < g.prob[pi].n_chunks && i < GRU2_MAX_CHUNKS; i += GRU2_THREADS - 128)
+                s_chunks[pi * GRU2_MAX_CHUNKS + i] = g.prob[pi].chunks[i];
     tc_fence_before();
     __syncthreads();
     cluster_sync_all();
@@ -659,40 +675,59 @@ gru_step2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
                 const int m0 = (rem / GRU_NUB) * 256 + (int)rank * BM, ub = rem % GRU_NUB;
                 const int brow = P.b_row_base + ub * GRU_BROWS;
                 for (int kc = 0; kc < P.n_chunks; kc++) {
-                    const KChunk c = P.chunks[kc];
+                    const KChunk c = s_chunks[pi * GRU2_MAX_CHUNKS + kc];
                     const int src = c.a_src & 0xff, kind = (c.a_src >> 8) & 0xff;
                     const CUtensorMap *ma = src == 0 ? &tmA0 : src == 1 ? &tmA1 : src == 2 ? &tmA2 : &tmA3;
                     mbar_wait(empty_bar(ps.stage), ps.phase ^ 1u);
-                    if (rank == 0) mbar_expect_tx(full_bar(ps.stage), GRU2_TX_BYTES);
+                    const int xm = g.debug >> 8;              // timing experiments: 1 no A loads, 4 no B loads
+                    if (rank == 0) mbar_expect_tx(full_bar(ps.stage), ((xm & 1) ? 0u : 2u * A_STAGE_BYTES) + ((xm & 4) ? 0u : 2u * GRU2_B_ROWS * 128u));
                     const uint32_t sa = smem_base + ps.stage * GRU2_STAGE_BYTES;
                     const uint32_t sb = sa + A_STAGE_BYTES;
-                    tma_load_2d_2sm(sa, ma, full_bar(ps.stage), c.a_col, m0 + c.a_drow);
-                    if (rank == 0) tma_load_2d_2sm(sb + (kind == 0 ? 64u * 128u : 0u), &tmB128, full_bar(ps.stage), c.b_col, brow);
-                    else tma_load_2d_2sm(sb + 64u * 128u, &tmB64, full_bar(ps.stage), c.b_col, brow + 128);
+                    if (!(xm & 1)) tma_load_2d_2sm(sa, ma, full_bar(ps.stage), c.a_col, m0 + c.a_drow);
+                    if (xm & 4) { }
+                    else if (kind == 0) tma_load_2d_2sm(sb, &tmB96, full_bar(ps.stage), c.b_col, brow + (int)rank * 96);
+                    else {
+                        tma_load_2d_2sm(sb, &tmB64, full_bar(ps.stage), c.b_col, brow + (int)rank * 64);
+                        tma_load_2d_2sm(sb + 64u * 128u, &tmB32, full_bar(ps.stage), c.b_col, brow + 128 + (int)rank * 32);
+                    }
                     ps.advance(STAGES);
                 }
             }
         }
     } else if (warp == 1) {
         if (lane == 0 && rank == 0) {
-            constexpr uint32_t idesc = make_idesc_bf16(256, 256);
+            constexpr uint32_t idesc192 = make_idesc_bf16(256, 192), idesc128 = make_idesc_bf16(256, 128);
+            constexpr uint32_t idesc64 = make_idesc_bf16(256, 64);
             PipeState ps{0, 0};
             int as = 0; uint32_t aphase = 0;
             for (int tile = pair; tile < n_tiles; tile += n_pairs) {
-                const GruProblem &P = g.prob[tile / tiles_per_prob];
+                const int pi = tile / tiles_per_prob;
+                const GruProblem &P = g.prob[pi];
                 mbar_wait(tempty_bar(as), aphase ^ 1u);
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + as * 256;
+                uint32_t nh_started = 0;                       // columns 192..255 are first written by the first hidden chunk
                 for (int kc = 0; kc < P.n_chunks; kc++) {
-                    const int kind = (P.chunks[kc].a_src >> 8) & 0xff;
+                    const int kind = (s_chunks[pi * GRU2_MAX_CHUNKS + kc].a_src >> 8) & 0xff;
                     mbar_wait(full_bar(ps.stage), ps.phase);
                     tc_fence_after();
                     const uint32_t sa = smem_base + ps.stage * GRU2_STAGE_BYTES;
                     const uint64_t da = make_smem_desc_sw128(sa);
-                    const uint64_t db = make_smem_desc_sw128(sa + A_STAGE_BYTES + (kind == 0 ? 64u * 128u : 0u));
+                    const uint64_t db = make_smem_desc_sw128(sa + A_STAGE_BYTES);
+                    if ((g.debug >> 8) & 2) {                  // timing experiment: no MMAs
+                    } else if (kind == 0) {                    // input chunks come first (model.cu chunk tables)
 #pragma unroll
-                    for (int k = 0; k < BK / 16; k++)
-                        umma_bf16_2sm(d_tmem, da + 2u * k, db + 2u * k, idesc, (uint32_t)(kc | k));
+                        for (int k = 0; k < BK / 16; k++)
+                            umma_bf16_2sm(d_tmem, da + 2u * k, db + 2u * k, idesc192, (uint32_t)(kc | k));
+                    } else {
+                        const uint64_t dbn = make_smem_desc_sw128(sa + A_STAGE_BYTES + 64u * 128u);
+#pragma unroll
+                        for (int k = 0; k < BK / 16; k++) {
+                            umma_bf16_2sm(d_tmem, da + 2u * k, db + 2u * k, idesc128, 1u);
+                            umma_bf16_2sm(d_tmem + 192, da + 2u * k, dbn + 2u * k, idesc64, nh_started | (uint32_t)k);
+                        }
+                        nh_started = 1;
+                    }
                     umma_commit_mc(empty_bar(ps.stage), 3);
                     ps.advance(STAGES);
                 }
@@ -701,9 +736,10 @@ gru_step2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
             }
         }
     } else if (warp >= 4) {
-        // 8 epilogue warps: warp w reads TMEM lanes 32*(w%4).. (hardware lane-quarter rule) and handles unit groups
-        // cb = 2*half, 2*half+1 of the tile's 64 hidden units, half = (w-4)/4.
-        const int wq = warp & 3, half = (warp - 4) >> 2;
+        // 16 epilogue warps: warp w reads TMEM lanes 32*(w%4).. (hardware lane-quarter rule) and handles the 16 hidden
+        // units cb = (w-4)/4 of the tile's 64.  The epilogue is latency-bound per warp (state / partner loads, stores), so
+        // its throughput comes from the number of warps in flight.
+        const int wq = warp & 3, cb = (warp - 4) >> 2;
         int as = 0; uint32_t aphase = 0;
         for (int tile = pair; tile < n_tiles; tile += n_pairs) {
             const int pi = tile / tiles_per_prob, rem = tile % tiles_per_prob;
@@ -711,35 +747,36 @@ gru_step2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
             const int m0 = (rem / GRU_NUB) * 256 + (int)rank * BM, ub = rem % GRU_NUB;
             const long long m_warp0 = m0 + wq * 32;
             const long long m = m_warp0 + lane;
-            const bool has_h = true;
+            const bool has_h = P.h_prev != nullptr || P.h_prev_bf != nullptr;   // else no hidden chunks: columns 192..255 are never written
+            const int dbg = g.debug & 0xff;
             // everything that does not depend on the accumulator is fetched BEFORE waiting for the MMAs
-            float hp[2][16];
+            float hp[16];
+            if (P.h_prev && m < g.M && dbg != 5 && dbg != 1) state_load16(P.h_prev, m, ub * GRU_UB + cb * 16, hp);
+            else if (P.h_prev_bf && m < g.M && dbg != 5 && dbg != 1) rows_load_bf16(P.h_prev_bf, m, ub * GRU_UB + cb * 16, hp);
+            else {
 #pragma unroll
-            for (int c2 = 0; c2 < 2; c2++) {
-                if (P.h_prev && m < g.M && g.debug != 5) state_load16(P.h_prev, m, ub * GRU_UB + (half * 2 + c2) * 16, hp[c2]);
-                else {
-#pragma unroll
-                    for (int i = 0; i < 16; i++) hp[c2][i] = 0.f;
-                }
+                for (int i = 0; i < 16; i++) hp[i] = 0.f;
             }
             mbar_wait(tfull_bar(as), aphase);
             tc_fence_after();
             const uint32_t taddr = tmem_base + as * 256 + ((uint32_t)(wq * 32) << 16);
-#pragma unroll
-            for (int c2 = 0; c2 < 2; c2++) {
-                if (g.debug == 1) break;
-                const int cb = half * 2 + c2;
+            if (dbg != 1) {
                 uint32_t vr[16], vz[16], vx[16], vh[16];
                 tmem_ld16(taddr + cb * 16, vr);
                 tmem_ld16(taddr + 64 + cb * 16, vz);
                 tmem_ld16(taddr + 128 + cb * 16, vx);
                 if (has_h) tmem_ld16(taddr + 192 + cb * 16, vh);
                 tmem_ld_wait();
-                gru_finish16<FAST_ACT>(P, g.M, m_warp0, lane, ub * GRU_UB + cb * 16, vr, vz, vx, vh, has_h, hp[c2], g.debug);
+                // the accumulator stage is free as soon as its values are in registers
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive_cluster(tempty_bar(as), 0);
+                gru_finish16<FAST_ACT>(P, g.M, m_warp0, lane, ub * GRU_UB + cb * 16, vr, vz, vx, vh, has_h, hp, dbg);
+            } else {
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive_cluster(tempty_bar(as), 0);
             }
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive_cluster(tempty_bar(as), 0);
             if (++as == 2) { as = 0; aphase ^= 1u; }
         }
     }
@@ -749,8 +786,8 @@ gru_step2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
     if (warp == 2) { tc_fence_after(); tmem_dealloc_2sm(tmem_base, 512); }
 }
 
-int launch_gru_step2(const CUtensorMap *tmA, const CUtensorMap *tmB128, const CUtensorMap *tmB64, const GruArgs &g_in,
-                     cudaStream_t st) {
+int launch_gru_step2(const CUtensorMap *tmA, const CUtensorMap *tmB96, const CUtensorMap *tmB64, const CUtensorMap *tmB32,
+                     const GruArgs &g_in, cudaStream_t st) {
     static bool attr_done[64] = {false};
     int dev = 0;
     DP_CUDA_CHECK(cudaGetDevice(&dev));
@@ -760,18 +797,23 @@ int launch_gru_step2(const CUtensorMap *tmA, const CUtensorMap *tmB128, const CU
         if (dev < 64) attr_done[dev] = true;
     }
     static int dbg = -1;
-    if (dbg < 0) { const char *e = getenv("DP_GRU_DEBUG"); dbg = e ? atoi(e) : 0; }
+    if (dbg < 0) {
+        const char *e = getenv("DP_GRU_DEBUG"); dbg = e ? atoi(e) : 0;
+        const char *e2 = getenv("DP_GRU_DEBUG2"); if (e2) dbg |= atoi(e2) << 8;
+    }
     GruArgs g = g_in;
     g.debug = dbg;
     g.tiles_m = (g.M + 255) / 256;
     const int n_tiles = g.tiles_m * GRU_NUB * g.n_prob;
     if (n_tiles <= 0) return DP_OK;
+    for (int i = 0; i < g.n_prob; i++)
+        if (g.prob[i].n_chunks > GRU2_MAX_CHUNKS) { set_error("gru_step2: too many K chunks"); return DP_EINVAL; }
     const int max_pairs = device_sm_count() / 2;
     const int pairs = n_tiles < max_pairs ? n_tiles : max_pairs;
     if (g.fast_act)
-        gru_step2_kernel<true><<<2 * pairs, GRU_THREADS, GRU2_SMEM_BYTES, st>>>(tmA[0], tmA[1], tmA[2], tmA[3], *tmB128, *tmB64, g);
+        gru_step2_kernel<true><<<2 * pairs, GRU2_THREADS, GRU2_SMEM_BYTES, st>>>(tmA[0], tmA[1], tmA[2], tmA[3], *tmB96, *tmB64, *tmB32, g);
     else
-        gru_step2_kernel<false><<<2 * pairs, GRU_THREADS, GRU2_SMEM_BYTES, st>>>(tmA[0], tmA[1], tmA[2], tmA[3], *tmB128, *tmB64, g);
+        gru_step2_kernel<false><<<2 * pairs, GRU2_THREADS, GRU2_SMEM_BYTES, st>>>(tmA[0], tmA[1], tmA[2], tmA[3], *tmB96, *tmB64, *tmB32, g);
     DP_CUDA_CHECK(cudaGetLastError());
     return DP_OK;
 }

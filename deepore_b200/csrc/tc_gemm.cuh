@@ -48,11 +48,14 @@ struct GruProblem {
     int n_chunks;
     int b_row_base;                    // first row of this (layer, direction) in the stacked weight matrix
     const float *bias;                 // [4][512]: b_ir+b_hr, b_iz+b_hz, b_in, b_hn (zero padded)
-    const float *h_prev;               // fp32 [M][512] or null (zeros)
-    float *h_out;                      // fp32 [M][512]
+    const float *h_prev;               // fp32 state (blocked layout) or null
+    const __nv_bfloat16 *h_prev_bf;    // bf16 [M][512] rows: previous state when no fp32 state is kept (one-pass bf16 mode);
+                                       // both null: h_prev == 0
+    float *h_out;                      // fp32 state (blocked layout); null in one-pass bf16 mode (the bf16 rows ARE the state)
     __nv_bfloat16 *h_out_bf;           // bf16 [M][512]: A operand of the next step
     __nv_bfloat16 *h_out_lo;           // optional split-precision remainder
     const float *partner;              // optional: xsum = h_new + partner   (sum of directions, model.py:131-133)
+    const __nv_bfloat16 *partner_bf, *partner2_bf;   // the same from bf16 rows (one-pass bf16 mode)
     __nv_bfloat16 *xsum, *xsum_lo;
     const float *partner2;             // optional: xsum2 = h_prev + partner2
     __nv_bfloat16 *xsum2, *xsum2_lo;
@@ -70,9 +73,9 @@ struct GruArgs {
 int launch_gemm_bf16(const CUtensorMap *tmA /*[4]*/, const CUtensorMap *tmB, const GemmArgs &g, int block_n,
                      cudaStream_t st);
 int launch_gru_step(const CUtensorMap *tmA /*[4]*/, const CUtensorMap *tmB, const GruArgs &g, cudaStream_t st);
-// CTA-pair (cta_group::2) version: tmB128 / tmB64 are maps of the same weight matrix with 128- and 64-row boxes
-int launch_gru_step2(const CUtensorMap *tmA /*[4]*/, const CUtensorMap *tmB128, const CUtensorMap *tmB64, const GruArgs &g,
-                     cudaStream_t st);
+// CTA-pair (cta_group::2) version: tmB96 / tmB64 / tmB32 are maps of the same weight matrix with 96-, 64- and 32-row boxes
+int launch_gru_step2(const CUtensorMap *tmA /*[4]*/, const CUtensorMap *tmB96, const CUtensorMap *tmB64,
+                     const CUtensorMap *tmB32, const GruArgs &g, cudaStream_t st);
 int device_sm_count();
 
 }  // namespace dp

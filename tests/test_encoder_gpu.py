@@ -99,3 +99,36 @@ def test_fast_path_takes_the_synthetic_windows():
         assert not bad, "coverage %d: windows differ: %s" % (cov, bad[:10])
         assert np.array_equal(rowpos.cpu().numpy(), orp) and np.array_equal(rowins.cpu().numpy(), ori)
         assert 0 <= nfb <= shard.n_windows // 10, "fast path handed %d of %d windows to the fallback" % (nfb, shard.n_windows)
+
+
+def test_bench_shard_of_config1_vs_oracle():
+    """A full bench step of BASELINE.json configs[1] (2048 windows of the 9 Mb / 30x workload, exactly what bench.py
+    times) and the 100x variant of configs[2] (512 windows): CUDA == oracle byte for byte, row maps and statuses too."""
+    import pileup_oracle as po
+    from deepore_b200.pileup import Encoder, ShardBuffers
+    from deepore_b200.workload import SyntheticWorkload
+    for cov, nwin in ((30.0, 2048), (100.0, 512)):
+        wl = SyntheticWorkload(coverage=cov) if cov == 30.0 else SyntheticWorkload(ref_len=1_000_000, coverage=cov)
+        shard = wl.shards(1000, nwin, 1)[0]
+        sb = ShardBuffers(shard, "cuda").upload()
+        enc = Encoder(device="cuda")
+        img, rowpos, rowins, status = enc.encode(sb)
+        torch.cuda.synchronize()
+        oimg, ost, orp, ori = po.encode_windows(shard.reads, shard.win_qs, shard.win_lo, shard.win_hi, shard.ref,
+                                                shard.ref_base, want_rowmap=True)
+        assert np.array_equal(status.cpu().numpy(), ost)
+        assert np.array_equal(img.cpu().numpy(), oimg)
+        assert np.array_equal(rowpos.cpu().numpy(), orp) and np.array_equal(rowins.cpu().numpy(), ori)
+        assert enc.fallback_count() <= nwin // 20
+
+
+def test_batch_partition_invariance():
+    """Size-independent property: a window's tensor does not depend on which other windows share its launch."""
+    from deepore_b200 import synth
+    from deepore_b200.pileup import encode_windows
+    ref = synth.random_reference(50_000, seed=21)
+    rb = synth.simulate_reads(ref, coverage=40, seed=22)
+    wq = synth.window_starts(1000, 49_000, stride=100)
+    whole = encode_windows(rb, wq, ref, 0)[0].cpu().numpy()
+    part = np.concatenate([encode_windows(rb, wq[a:a + 97], ref, 0)[0].cpu().numpy() for a in range(0, len(wq), 97)])
+    assert np.array_equal(whole, part)

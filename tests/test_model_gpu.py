@@ -111,3 +111,34 @@ def test_empty_and_capacity():
     assert logits.shape == (0, 150, 3, 3)
     with pytest.raises(Exception):
         m(torch.zeros(1, 4, 3, 200))          # CPU tensor: no fallback
+
+
+def test_bundled_windows_end_to_end_call_set():
+    """Whole path on the bundled NA12878 fixture: CUDA encoder -> CUDA model (split-bf16) -> vote, against the oracle
+    chain (reference-pinned images -> numpy float64 model -> vote).  No checkpoint ships with the reference, so the
+    weights are the seeded ones; the call set must be identical wherever the oracle's top-2 margin is decisive."""
+    import golden_util as gu
+    import model_oracle as mo
+    from deepore_b200 import model, modelio
+    from deepore_b200.pileup import encode_windows
+    g = gu.load("bundled_na12878")
+    pick = [0, 57, 131, 259]
+    img, rowpos, rowins, status = encode_windows(g.reads, g.win_qs[pick], g.ref, g.ref_base)
+    assert (status.cpu().numpy() == 0).all()
+    assert np.array_equal(img.cpu().numpy(), g.img[pick])
+    st = modelio.seeded_state(7)
+    m = model.from_state(st, "cuda", "bf16x3")
+    logits, pred = m.forward_windows(img)
+    calls, _ = model.vote(pred.view(-1, 3), len(pick), img.shape[1], 3)
+    torch.cuda.synchronize()
+    calls = calls.cpu().numpy()
+    for i, wi in enumerate(pick[:2]):                       # the numpy oracle takes ~1 s per window
+        want = mo.forward_image(st, g.img[wi], dtype=np.float64)
+        got = logits[i].cpu().numpy()[:148]
+        assert np.abs(got - want).max() < 2e-4
+        srt = np.sort(want, axis=-1)
+        decisive = (srt[..., -1] - srt[..., -2]) > 4e-4
+        wp = mo.argmax_first(want)
+        assert np.array_equal(pred[i, :148].cpu().numpy()[decisive], wp[decisive])
+        if decisive.all():
+            assert np.array_equal(calls[i], mo.vote(wp))
