@@ -34,6 +34,16 @@ METRIC = "genomic positions/sec (pileup encode + CNN/GRU infer)"
 UNIT = "positions/s"
 
 
+def traffic_of(kernel):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the named kernel, from the committed `ncu --set full`
+    capture of this bench command (profiles/r1_traffic.json); None when no capture is recorded."""
+    p = os.path.join(ROOT, "profiles", "r1_traffic.json")
+    try:
+        return json.load(open(p))[kernel]["dram_bytes_per_launch"]
+    except Exception:
+        return None
+
+
 def load_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.isfile(p):
@@ -266,7 +276,7 @@ def main():
         o = outs[i & 1]
         n = sb.n_windows
         enc.encode(sb, o["img"][:n], o["rowpos"][:n], o["rowins"][:n], o["status"][:n])
-        launches = 2                                   # prep_reads_kernel + encode_windows_kernel
+        launches = 4                                   # prep_reads, base_codes, encode_windows_v3 (fast), encode_windows (exact, listed windows)
         if with_model:
             rows = o["img"].view(nw * H, W, 4)
             for c0 in range(0, n, mchunk):
@@ -356,8 +366,9 @@ def main():
         alg = sum(algorithmic_bytes(sh) for sh in shards[args.warmup:])
         enc_achieved = alg / args.steps / (enc_ms * 1e-3) / 1e9
         enc_roof = {"bound": "hbm", "achieved": enc_achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                    "frac": enc_achieved / peaks["hbm_gbs"], "traffic": None, "peak_source": peaks["source"],
-                    "kernel": "prep_reads_kernel+encode_windows_kernel", "ms_per_launch": enc_ms,
+                    "frac": enc_achieved / peaks["hbm_gbs"], "peak_source": peaks["source"],
+                    "kernel": "prep_reads_kernel+base_codes_kernel+encode_windows_v3_kernel+encode_windows_kernel",
+                    "ms_per_launch": enc_ms, "traffic": traffic_of("encoder"),
                     "algorithmic_bytes_per_window": alg / max(1, win_timed)}
         h2d = int(np.mean([b.nbytes for b in bufs[args.warmup:]]))
         d2h = int(nw * 4 + nw * H * 4 + (nw * H if with_model else 0))
@@ -380,8 +391,8 @@ def main():
             flop_per_launch = rows_per_launch * ((n_layers * 3 - 1) * FLOP_GRU_STEP_PER_ROW + FLOP_GRU_STEP0_PER_ROW) / (n_layers * 3)
             ach = flop_per_launch / (g_ms / max(1, g_n) * 1e-3) / 1e12
             line["roofline"] = {"bound": "tensor", "achieved": ach, "peak": peaks["bf16_tflops_sustained"],
-                                "unit": "TFLOP/s", "frac": ach / peaks["bf16_tflops_sustained"], "traffic": None,
-                                "peak_source": peaks["source"] + " (sustained bf16)", "kernel": "gru_step_kernel",
+                                "unit": "TFLOP/s", "frac": ach / peaks["bf16_tflops_sustained"], "traffic": traffic_of("gru_step"),
+                                "peak_source": peaks["source"] + " (sustained bf16)", "kernel": "gru_step2_kernel",
                                 "ms_per_launch": g_ms / max(1, g_n), "launches": g_n,
                                 "algorithmic_flop_per_launch": flop_per_launch,
                                 "share_of_step": g_ms / ms_dev}

@@ -108,46 +108,58 @@ __global__ void __launch_bounds__(256) u8_to_bf16_kernel(const uint4 *__restrict
     out[2 * i + 1] = make_uint4(o[4], o[5], o[6], o[7]);
 }
 
-// fc1 (model.py:90,154) + top-1 (test.py:68): one warp per (row, t).  out = hf + hb of the last GRU layer (fp32).
-__global__ void __launch_bounds__(256) fc1_argmax_kernel(const float *__restrict__ hf, const float *__restrict__ hb,
+// fc1 (model.py:90,154) + top-1 (test.py:68).  out = hf + hb of the last GRU layer (fp32, blocked layout of
+// gru_state_off in tc_gemm.cu).  One warp per (32 consecutive rows, t): lane = row, so every load instruction moves 512
+// contiguous bytes of the blocked state; each lane accumulates its own row's dot products (no shuffles), the fc1
+// weights are broadcast from shared memory.
+constexpr int FC1_CMAX = 4;                            // classes per pass over the state
+__global__ void __launch_bounds__(128) fc1_argmax_kernel(const float *__restrict__ hf, const float *__restrict__ hb,
                                                          long long slot_stride, const float *__restrict__ w,
                                                          const float *__restrict__ b, int n_class, int seq_len,
                                                          long long n_rows, float *__restrict__ logits,
                                                          uint8_t *__restrict__ pred) {
-    const long long wid = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    extern __shared__ float s_w[];                     // [n_class][HP]
+    for (int i = threadIdx.x; i < n_class * HP; i += blockDim.x) s_w[i] = w[i];
+    __syncthreads();
+    const long long wid = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
-    if (wid >= n_rows * seq_len) return;
-    const long long m = wid / seq_len;
+    const long long n_rb = (n_rows + 31) >> 5;
+    if (wid >= n_rb * seq_len) return;
+    const long long rb = wid / seq_len;
     const int t = (int)(wid % seq_len);
-    // fp32 states live in the blocked layout of gru_state_off (tc_gemm.cu): lane handles unit groups 4*(lane+32j)
-    const float *pf = hf + t * slot_stride, *pb = hb + t * slot_stride;
-    float x[HP / 32];
-#pragma unroll
-    for (int j = 0; j < HP / 128; j++) {
-        const int u = 4 * (lane + 32 * j);
-        const long long mb = m >> 7;
-        const int r = (int)(m & 127), ub = u >> 6, cb = (u >> 4) & 3, k = (u >> 2) & 3;
-        const long long off = ((((mb * 8 + ub) * 4 + cb) * 4 + k) * 128 + r) * 4;
-        const float4 a = *reinterpret_cast<const float4 *>(pf + off), b4 = *reinterpret_cast<const float4 *>(pb + off);
-        x[4 * j] = a.x + b4.x; x[4 * j + 1] = a.y + b4.y; x[4 * j + 2] = a.z + b4.z; x[4 * j + 3] = a.w + b4.w;
-    }
+    const long long m = rb * 32 + lane;
+    const long long base = (((m >> 7) * 8) * 16 * 128 + (m & 127)) * 4;     // offset of (m, u = 0)
+    const float *pf = hf + t * slot_stride + base, *pb = hb + t * slot_stride + base;
     float best = 0.f;
     int besti = 0;
-    for (int c = 0; c < n_class; c++) {
-        float acc = 0.f;
+    for (int c0 = 0; c0 < n_class; c0 += FC1_CMAX) {
+        float acc[FC1_CMAX];
 #pragma unroll
-        for (int j = 0; j < HP / 128; j++) {
-            const float4 wv = __ldg(reinterpret_cast<const float4 *>(w + c * HP + 4 * (lane + 32 * j)));
-            acc = fmaf(x[4 * j], wv.x, acc); acc = fmaf(x[4 * j + 1], wv.y, acc);
-            acc = fmaf(x[4 * j + 2], wv.z, acc); acc = fmaf(x[4 * j + 3], wv.w, acc);
+        for (int c = 0; c < FC1_CMAX; c++) acc[c] = 0.f;
+#pragma unroll 4
+        for (int q = 0; q < HP / 4; q++) {             // q = (ub*4 + cb)*4 + k: consecutive float4 groups are 128 rows apart
+            const float4 a = *reinterpret_cast<const float4 *>(pf + (long long)q * 512);
+            const float4 b4 = *reinterpret_cast<const float4 *>(pb + (long long)q * 512);
+            const float x0 = a.x + b4.x, x1 = a.y + b4.y, x2 = a.z + b4.z, x3 = a.w + b4.w;
+#pragma unroll
+            for (int c = 0; c < FC1_CMAX; c++) {
+                if (c0 + c < n_class) {
+                    const float4 wv = *reinterpret_cast<const float4 *>(s_w + (c0 + c) * HP + 4 * q);
+                    acc[c] = fmaf(x0, wv.x, acc[c]); acc[c] = fmaf(x1, wv.y, acc[c]);
+                    acc[c] = fmaf(x2, wv.z, acc[c]); acc[c] = fmaf(x3, wv.w, acc[c]);
+                }
+            }
         }
 #pragma unroll
-        for (int d = 16; d > 0; d >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, d);
-        acc += __ldg(b + c);
-        if (lane == 0 && logits) logits[(m * seq_len + t) * n_class + c] = acc;
-        if (c == 0 || acc > best) { best = acc; besti = c; }
+        for (int c = 0; c < FC1_CMAX; c++) {
+            if (c0 + c < n_class) {
+                const float v = acc[c] + __ldg(b + c0 + c);
+                if (m < n_rows && logits) logits[(m * seq_len + t) * n_class + c0 + c] = v;
+                if (c0 + c == 0 || v > best) { best = v; besti = c0 + c; }
+            }
+        }
     }
-    if (lane == 0 && pred) pred[m * seq_len + t] = (uint8_t)besti;
+    if (m < n_rows && pred) pred[m * seq_len + t] = (uint8_t)besti;
 }
 
 // The same over the bf16 rows [row][512] of the arena (one-pass bf16 mode keeps no fp32 state): lane handles 16
@@ -501,7 +513,8 @@ static int forward_rows(Model *m, const uint8_t *img, long long n_rows, float *l
                                                          m->arena + (size_t)bf_slot_hb(k, 0) * mc * HP, mc * HP, m->w_fc1,
                                                          m->b_fc1, m->n_class, S, n_rows, logits, pred);
         else
-            fc1_argmax_kernel<<<blocks, 256, 0, st>>>(m->state + (size_t)f32_slot_hf(k, 0) * mc * HP,
+            fc1_argmax_kernel<<<(unsigned)((((n_rows + 31) / 32) * S + 3) / 4), 128, (size_t)m->n_class * HP * 4, st>>>(
+                                                      m->state + (size_t)f32_slot_hf(k, 0) * mc * HP,
                                                       m->state + (size_t)f32_slot_hb(k, 0) * mc * HP, mc * HP, m->w_fc1,
                                                       m->b_fc1, m->n_class, S, n_rows, logits, pred);
         DP_CUDA_CHECK(cudaGetLastError());
