@@ -176,6 +176,143 @@ def expand_label(label: str, variantLengths: Dict[int, int], rowins_full: np.nda
     return label + noneLabel * blank
 
 
+_CATS = "ACGTDMN"                                   # sortingKey order of Pileup.py:66-73 (category index of the kernels)
+_RGB_OF = {"M": (255, 255, 255), "A": (255, 0, 0), "C": (255, 255, 0), "G": (0, 255, 0), "T": (0, 0, 255),
+           "I": (255, 0, 255), "D": (0, 255, 255), "N": (0, 0, 0)}
+_CAT_OF_RGB = {v: k for k, v in _RGB_OF.items()}
+_TEXT_OF_BITS = [[[" ", "T"], ["G", "D"]], [["A", "_"], ["C", "."]]]     # Pileup.py:77 (decodeRGB alphabet)
+
+
+class Pileup:
+    """Reference surface of Pileup.Pileup (Pileup.py:21-405) over the CUDA encoder: same constructor arguments, the
+    methods generatePileup() calls (`iterateReads`, `generatePileupImage`, `savePileupRGB`, `getOutputLabel`,
+    `decodeRGB`) and the attributes `pileupColumns`, `insertColumns`, `pileupImage`, `refSequence`, `label`.
+
+    `sam` / `fasta` are the handles a `PileUpGenerator` of this package holds (`reads.BamFile`, `reads.FastaFile`).
+    The window is encoded on the GPU in `iterateReads`; the dictionaries are rebuilt from the kernel's rows for the
+    part of the window that reaches the image (the reference keeps every entry, the image keeps the first
+    coverageCutoff-1 per column and the first windowCutoff rows -- what the PNG, the label and the model see)."""
+
+    def __init__(self, sam, fasta, chromosome, queryStart, flankLength, outputFilename, label, variantLengths,
+                 coverageCutoff, mapQualityCutoff, windowCutoff, sortColumns, subsampleRate=0, forceCoverage=False,
+                 arrayInitializationFactor=2):
+        self.length = flankLength * 2 + 1
+        self.label = label
+        self.variantLengths = variantLengths
+        self.subsampleRate = subsampleRate
+        self.coverageCutoff = coverageCutoff
+        self.outputFilename = outputFilename
+        self.queryStart = queryStart
+        self.queryEnd = queryStart + self.length
+        self.chromosome = str(chromosome)
+        self.windowCutoff = windowCutoff
+        self.mapQualityCutoff = mapQualityCutoff
+        self.sortColumns = sortColumns
+        self.forceCoverage = forceCoverage
+        self.flankLength = flankLength
+        self.sam, self.fasta = sam, fasta
+        self.noneChar, self.noneLabel = "_", "0"
+        self.SNPtoRGB = {k: list(v) for k, v in _RGB_OF.items()}
+        self.SNPtoRGB[self.noneChar] = [0, 0, 0]
+        contig = "chr" + self.chromosome
+        ref = fasta.contig(contig)
+        lo, hi = max(0, queryStart), min(ref.shape[0], self.queryEnd + 1)
+        self._ref, self._ref_base = ref[lo:hi], lo
+        self.refSequence = ref[lo:hi].tobytes().decode("ascii")          # 0-based [queryStart, queryEnd] inclusive (:41)
+        self.pileupColumns = dict()
+        self.insertColumns = dict()
+        self.pileupImage = list()
+        self._img = self._rowpos = self._rowins = self._rowins_full = None
+
+    # ---- Pileup.py:152-163 (+ parseRead :174-264): here one CUDA launch for the window
+    def iterateReads(self):
+        contig = "chr" + self.chromosome
+        cache = self.sam.__dict__.setdefault("_dp_batches", {})          # one parsed ReadBatch per contig and handle
+        if contig not in cache:
+            cache[contig] = self.sam.read_contig(contig)
+        rb = cache[contig]
+        wq = np.asarray([self.queryStart], np.int32)
+
+        def run(W, H):
+            img, rowpos, rowins, status = encode_windows(rb, wq, self._ref, self._ref_base, self.flankLength, W, H,
+                                                         self.mapQualityCutoff)
+            st = int(status[0].item())
+            if st != 0:
+                raise _STATUS_EXC.get(st, RuntimeError)("window at chr%s:%d raised status %d"
+                                                        % (self.chromosome, self.queryStart + self.flankLength, st))
+            return img[0].cpu().numpy(), rowpos[0].cpu().numpy(), rowins[0].cpu().numpy()
+
+        self._img, self._rowpos, self._rowins = run(self.coverageCutoff, self.windowCutoff)
+        nrows = int((self._rowpos >= 0).sum())
+        self._rowins_full = self._rowins[:nrows]
+        if nrows == self.windowCutoff and self.windowCutoff < 256:      # rows were cut: the label needs all of them
+            _, rp2, ri2 = run(4, 256)
+            self._rowins_full = ri2[:int((rp2 >= 0).sum())]
+        # dictionaries of the drawn part: position -> category -> [[R,G,B,q], ...] ; anchor -> [k] -> base -> [...]
+        for y in range(nrows):
+            pos, k = int(self._rowpos[y]), int(self._rowins[y])
+            row = self._img[y]
+            filler = (255, 0, 255, 255) if k else (0, 0, 0, 255)
+            cells = dict()
+            for px in row[1:]:
+                t = tuple(int(v) for v in px)
+                if t == filler:
+                    break
+                cells.setdefault(_CAT_OF_RGB[t[:3]], []).append(list(t))
+            if k == 0:
+                self.pileupColumns[pos] = cells
+            else:
+                self.insertColumns.setdefault(pos, []).append(cells)
+
+    # ---- Pileup.py:295-317: rows of RGBA tuples, 'I' spliced into refSequence, label widened at insert rows
+    def generatePileupImage(self):
+        if self._img is None:
+            self.iterateReads()
+        nrows = int((self._rowpos >= 0).sum())
+        self.pileupImage = [[tuple(int(v) for v in px) for px in self._img[y]] for y in range(nrows)]
+        c = 0
+        i = 0
+        full = self._rowins_full
+        while i < len(full):
+            n = 0
+            j = i + 1
+            while j < len(full) and full[j] != 0:
+                n += 1
+                j += 1
+            if n:
+                self.labelInsertRegion(c + 1, n)
+                for _ in range(n):
+                    c += 1
+                    self.refSequence = self.refSequence[:c] + "I" + self.refSequence[c:]
+            c += 1
+            i = j
+
+    def labelInsertRegion(self, c, n):                     # Pileup.py:320-333
+        if c in self.variantLengths:
+            l = self.variantLengths[c] - 1
+            ins = self.label[c - 1] * n if l >= n else self.label[c - 1] * l + self.noneLabel * (n - l)
+        else:
+            ins = self.noneLabel * n
+        self.label = self.label[:int(c)] + ins + self.label[int(c):]
+
+    def savePileupRGB(self, filename):                     # Pileup.py:336-361
+        from PIL import Image
+        if not filename.endswith(".png"):
+            filename += ".png"
+        self.pileupImage = [row[:self.coverageCutoff] for row in self.pileupImage[:self.windowCutoff]]
+        Image.fromarray(np.ascontiguousarray(self._img), "RGBA").save(filename, "PNG")
+
+    def getOutputLabel(self):                              # Pileup.py:374-378
+        self.label += self.noneLabel * (self.windowCutoff - len(self.label))
+        return self.label
+
+    def decodeRGB(self, filename):                         # Pileup.py:381-405 (debug view; generatePileup discards it)
+        from PIL import Image
+        px = np.asarray(Image.open(filename).convert("RGBA"))
+        bits = (px[..., :3] // 255).astype(np.int64)
+        return ["".join(_TEXT_OF_BITS[r][g][b] for r, g, b in row) for row in bits]
+
+
 class PileUpGenerator:
     """Drop-in for Pileup.PileUpGenerator (Pileup.py:408-451)."""
 
@@ -219,20 +356,13 @@ class PileUpGenerator:
     def generatePileup(self, chromosome, position, flankLength, outputFilename, label, variantLengths,
                        forceCoverage=False, coverageCutoff=200, mapQualityCutoff=20, windowCutoff=150,
                        sortColumns=False):
-        from PIL import Image
-        chromosome = str(chromosome)
-        img, rowpos, rowins = self.generatePileupTensor(chromosome, position, flankLength, coverageCutoff,
-                                                        mapQualityCutoff, windowCutoff)
-        fn = outputFilename if outputFilename.endswith(".png") else outputFilename + ".png"
-        Image.fromarray(img, "RGBA").save(fn, "PNG")
-        # the label needs the insert layout of ALL rows, also those past windowCutoff: encode with the tallest
-        # image the kernel supports when the window is cut
-        L = 2 * flankLength + 1
-        if (rowpos >= 0).sum() == windowCutoff:
-            _, rp2, ri2 = self.generatePileupTensor(chromosome, position, flankLength, 4, mapQualityCutoff, 256)
-            nrows = int((rp2 >= 0).sum())
-            rowins_full = ri2[:nrows]
-        else:
-            nrows = int((rowpos >= 0).sum())
-            rowins_full = rowins[:nrows]
-        return expand_label(label, variantLengths, rowins_full, windowCutoff)
+        """Pileup.py:418-451, same call sequence; the dead decodeRGB round trip of :447 is not executed."""
+        queryStart = position - flankLength
+        self.sam.__dict__.setdefault("_dp_batches", {})["chr" + str(chromosome)] = self._batch("chr" + str(chromosome))
+        pileup = Pileup(self.sam, self.fasta, str(chromosome), queryStart, flankLength, outputFilename, label,
+                        variantLengths, windowCutoff=windowCutoff, forceCoverage=forceCoverage,
+                        coverageCutoff=coverageCutoff, mapQualityCutoff=mapQualityCutoff, sortColumns=sortColumns)
+        pileup.iterateReads()
+        pileup.generatePileupImage()
+        pileup.savePileupRGB(outputFilename)
+        return pileup.getOutputLabel()

