@@ -243,10 +243,10 @@ __global__ void __launch_bounds__(256) prep_reads_kernel(dp_reads R, ReadAux *__
     const int64_t so = R.seq_off[r], qo = R.qual_off[r];
     if (carryQ != aln_len || aln_len <= 0 || ref_start != pos || carryR <= 0) dirty = true;
     if (GW == 1) dirty = __any_sync(0xffffffffu, dirty); else dirty = __syncthreads_or(dirty);
-    // ---- checkpoints: ckpt[m] = first op j with RP[j+1] >= m << k ; at most nops/4 + 1 of them per read
-    int k = 6;
-    while ((carryR >> k) > (nops >> 2)) k++;
-    const int64_t ckb = (c0 >> 2) + r;
+    // ---- checkpoints: ckpt[m] = first op j with RP[j+1] >= m << k ; at most nops/2 + 1 of them per read
+    int k = 4;
+    while ((carryR >> k) > (nops >> 1)) k++;
+    const int64_t ckb = (c0 >> 1) + r;
     {
         int cR = 0;
         for (int base = 0; base < nops; base += GT * PK) {
@@ -1172,6 +1172,10 @@ encode_windows_v3_kernel(EncArgs a, int *__restrict__ fb_count, int *__restrict_
     S.refc = p;                                    p += 224;
     int *s_wsum = &S.misc[8], *s_wsum2 = &S.misc[16];
     S.rowcnt = s_rowcnt;
+    // packed bases of slot groups 1..3 [group-1][lo|hi][LS] (G * LS <= 256, so <= 2 KB): handed from a column's group-0 thread to the others
+    // through the staged-op area (3 KB), which is idle between the counting pass and placement -- except in the
+    // multi-batch case, where only group 0 places and the hand-over is not needed
+    uint32_t *s_base = reinterpret_cast<uint32_t *>(S.md);
 
     // ---- setup
     const long long roff = (long long)qs - a.ref_base;
@@ -1233,7 +1237,7 @@ encode_windows_v3_kernel(EncArgs a, int *__restrict__ fb_count, int *__restrict_
         int jc = 0;
         if (T > 0 && (flags & RI_CLEAN)) {
             const int k = (flags >> 8) & 31;
-            jc = __ldg(a.ckpt + (ri->c0 >> 2) + r + (min(T, ri->span) >> k));
+            jc = __ldg(a.ckpt + (ri->c0 >> 1) + r + (min(T, ri->span) >> k));
         }
         S.j0[tid] = jc;
     }
@@ -1321,41 +1325,46 @@ encode_windows_v3_kernel(EncArgs a, int *__restrict__ fb_count, int *__restrict_
     }
     const bool walker = my_row >= 0;
     uint32_t run_lo = 0, run_hi = 0;
-    if (walker) {
+    if (walker && wg == 0) {
+        // the column's group-0 thread derives the packed bases of every group and the totals of the column's rows
+        uint32_t blo[4] = {0, 0, 0, 0}, bhi[4] = {0, 0, 0, 0};
         int acc = 0;
 #pragma unroll
         for (int c = 0; c < NCAT; c++) {
-            int before = 0, tot = 0;
-            for (int g = 0; g < G; g++) {
-                const int gc = c * 256 + g * LS + wc;
-                const int n = (S.cnt[gc >> 1] >> ((gc & 1) << 4)) & 0xffff;
-                if (g < wg) before += n;
-                tot += n;
+            int before = 0;
+#pragma unroll
+            for (int g = 0; g < 4; g++) {
+                if (g < G) {
+                    const int gc = c * 256 + g * LS + wc;
+                    const int n = (S.cnt[gc >> 1] >> ((gc & 1) << 4)) & 0xffff;
+                    const uint32_t bv = (uint32_t)min(acc + before, W - 1);
+                    if (c < 4) blo[g] |= bv << (c << 3); else bhi[g] |= bv << ((c - 4) << 3);
+                    before += n;
+                }
             }
-            const uint32_t bv = (uint32_t)min(acc + before, W - 1);
-            if (c < 4) run_lo |= bv << (c << 3); else run_hi |= bv << ((c - 4) << 3);
-            acc += tot;
+            acc += before;
         }
+        run_lo = blo[0]; run_hi = bhi[0];
+#pragma unroll
+        for (int g = 1; g < 4; g++)
+            if (g < G) { s_base[(g - 1) * 2 * LS + wc] = blo[g]; s_base[((g - 1) * 2 + 1) * LS + wc] = bhi[g]; }
         int mx = min(acc, W - 1);
-        if (wg == 0) s_rowcnt[my_row] = mx;
+        s_rowcnt[my_row] = mx;
         for (int k = 1; k < nown; k++) {             // insert rows of this column
             const int y = my_row + k;
-            int before = 0, tot = 0;
+            int tot = 0;
             for (int g = 0; g < G; g++) {
-                const int n = (S.rowcg[(g * 256 + y) >> 2] >> ((y & 3) << 3)) & 0xff;
-                if (g < wg) before += n;
-                tot += n;
+                s_rowfill[g * 256 + y] = (uint8_t)tot;
+                tot += (S.rowcg[(g * 256 + y) >> 2] >> ((y & 3) << 3)) & 0xff;
             }
-            s_rowfill[wg * 256 + y] = (uint8_t)before;
-            if (wg == 0) {
-                s_rowcnt[y] = tot;
-                if (tot > W - 1) S.misc[0] = 1;       // deeper than the image: the category sort needs every entry
-                mx = max(mx, min(tot, W - 1));
-            }
+            s_rowcnt[y] = tot;
+            if (tot > W - 1) S.misc[0] = 1;           // deeper than the image: the category sort needs every entry
+            mx = max(mx, min(tot, W - 1));
         }
-        if (wg == 0) atomicMax(&S.misc[9], mx);
+        atomicMax(&S.misc[9], mx);
     }
     __syncthreads();
+    if (walker && wg > 0) { run_lo = s_base[(wg - 1) * 2 * LS + wc]; run_hi = s_base[((wg - 1) * 2 + 1) * LS + wc]; }
     const int RS = (S.misc[9] + 4) & ~3;             // pixel 0 + entries, rounded up to whole quads
     const int qbytes = (nrows * RS + 15) & ~15;
     S.q = s_pool0 + V3_POOL_BYTES - qbytes;
@@ -1511,7 +1520,7 @@ int64_t dp_encode_workspace_bytes(int32_t n_reads, int64_t n_cigar, int64_t n_ba
     b += dp::align_up((int64_t)sizeof(int) * (n_cigar + 1), 256);             /* QP */
     b += dp::align_up((int64_t)sizeof(int) * ((n_windows > 0 ? n_windows : 0) + 64), 256);   /* fallback count + list */
     b += dp::align_up((int64_t)sizeof(dp::ReadInfo) * (n_reads > 0 ? n_reads : 1), 256);
-    b += dp::align_up((int64_t)sizeof(int) * ((n_cigar >> 2) + n_reads + 2), 256);           /* checkpoints */
+    b += dp::align_up((int64_t)sizeof(int) * ((n_cigar >> 1) + n_reads + 2), 256);           /* checkpoints */
     b += dp::align_up((int64_t)sizeof(int) * (n_reads > 0 ? n_reads : 1), 256);              /* filtered endpos */
     b += dp::align_up((n_bases > 0 ? n_bases : 0) + 16, 256);                                /* per-base code bytes */
     b += 256;                                                                                /* phase clocks (debug) */
@@ -1564,7 +1573,7 @@ int dp_encode_windows(const dp_reads *reads, int32_t n_windows, const int32_t *w
     dp::ReadInfo *info = (dp::ReadInfo *)wp;
     wp += dp::align_up((int64_t)sizeof(dp::ReadInfo) * (reads->n_reads > 0 ? reads->n_reads : 1), 256);
     int *ckpt = (int *)wp;
-    wp += dp::align_up((int64_t)sizeof(int) * ((n_cigar >> 2) + reads->n_reads + 2), 256);
+    wp += dp::align_up((int64_t)sizeof(int) * ((n_cigar >> 1) + reads->n_reads + 2), 256);
     int *endk = (int *)wp;
     wp += dp::align_up((int64_t)sizeof(int) * (reads->n_reads > 0 ? reads->n_reads : 1), 256);
     uint8_t *code0 = wp;
