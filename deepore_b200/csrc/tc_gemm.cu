@@ -393,13 +393,17 @@ __device__ __forceinline__ void gru_finish16(const GruProblem &P, int M, long lo
     const long long m = m_warp0 + lane;
     const bool row_ok = m < M;
     float hn[16];
+    // biases: per 4 units one float4 per gate (same address in every lane -> broadcast load)
+    float4 bq[4];
 #pragma unroll
     for (int i = 0; i < 16; i++) {
-        float br = 0.f, bz = 0.f, bin = 0.f, bhn = 0.f;
-        if (dbg != 9) {
-            br = __ldg(P.bias + u0 + i); bz = __ldg(P.bias + GRU_HP + u0 + i);
-            bin = __ldg(P.bias + 2 * GRU_HP + u0 + i); bhn = __ldg(P.bias + 3 * GRU_HP + u0 + i);
+        if ((i & 3) == 0) {
+#pragma unroll
+            for (int gt = 0; gt < 4; gt++)
+                bq[gt] = dbg != 9 ? __ldg(reinterpret_cast<const float4 *>(P.bias + gt * GRU_HP + u0 + i)) : make_float4(0.f, 0.f, 0.f, 0.f);
         }
+        const float br = reinterpret_cast<const float *>(&bq[0])[i & 3], bz = reinterpret_cast<const float *>(&bq[1])[i & 3];
+        const float bin = reinterpret_cast<const float *>(&bq[2])[i & 3], bhn = reinterpret_cast<const float *>(&bq[3])[i & 3];
         if (dbg == 8) { hn[i] = __uint_as_float(vr[i]) + __uint_as_float(vz[i]) + __uint_as_float(vx[i]) + br + bz + bin + bhn + hp[i]; continue; }
         const float r = act_sigmoid<FAST_ACT>(__uint_as_float(vr[i]) + br);
         const float z = act_sigmoid<FAST_ACT>(__uint_as_float(vz[i]) + bz);
