@@ -63,7 +63,7 @@ struct Model {
     int fold_tab_off = 0, fold_tab_n = 0;
     int gru_tab_off[3][3][2], gru_tab_n[3][3][2];
     long long kcols_fold = 0, kcols_gru = 0;
-    CUtensorMap tm_img, tm_arena, tm_arena_lo, tm_wfold, tm_wgru, tm_wgru96, tm_wgru64, tm_wgru32;
+    CUtensorMap tm_img, tm_arena, tm_arena_lo, tm_wfold, tm_wgru, tm_wgru96;
     int gru_2cta = 1;              // CTA-pair GRU kernel (env DP_GRU=1cta selects the single-CTA kernel)
     // optional per-kernel timing (bench.py roofline): one event per launch boundary, harvested by dp_model_profile_read
     int profile = 0;
@@ -274,7 +274,14 @@ static int build_model(Model *m, const dp_model_weights *w) {
         rc = upload(&m->b_fold, bias);
         if (rc) return rc;
     }
-    // ---- GRU: rows ((k*2+d)*8 + ub)*192 + gate*64 + j  <- unit u = ub*64+j; columns [W_ih | W_hh] (512 each)
+    // ---- GRU: rows ((k*2+d)*8 + ub)*192 + gate*64 + j  <- unit u = ub*64+j; columns [W_ih | W_hh] (512 each).
+    // For the CTA-pair kernel the W_ih columns hold the gates in the order (n, r, z) instead of (r, z, n), so that the
+    // input chunks fill accumulator columns [W_in x | r | z] and the hidden chunks [r | z | W_hn h] one to the right:
+    // both are ONE contiguous N=192 MMA (gru_step2_kernel).
+    {
+        const char *e = getenv("DP_GRU");
+        m->gru_2cta = (e && !strcmp(e, "1cta")) ? 0 : 1;
+    }
     const long long kgru = 2 * HP;
     m->kcols_gru = kgru * passes_b;
     {
@@ -288,14 +295,15 @@ static int build_model(Model *m, const dp_model_weights *w) {
                 for (int u = 0; u < Hd; u++) {
                     const int ub = u / 64, j = u % 64;
                     for (int gate = 0; gate < 3; gate++) {
-                        const size_t r = ((size_t)(k * 2 + d) * 8 + ub) * 192 + gate * 64 + j;
-                        uint16_t *row = &B[r * m->kcols_gru];
+                        const size_t r0 = ((size_t)(k * 2 + d) * 8 + ub) * 192 + j;
+                        uint16_t *row = &B[(r0 + gate * 64) * m->kcols_gru];                                   // W_hh part
+                        uint16_t *rowi = &B[(r0 + (m->gru_2cta ? (gate + 1) % 3 : gate) * 64) * m->kcols_gru];  // W_ih part
                         const float *si = wih + ((size_t)gate * Hd + u) * Hd, *sh = whh + ((size_t)gate * Hd + u) * Hd;
                         for (int c = 0; c < Hd; c++) {
                             uint16_t hi, lo;
                             split_bf16(si[c], hi, lo);
-                            row[c] = hi;
-                            if (m->precise) row[kgru + c] = lo;
+                            rowi[c] = hi;
+                            if (m->precise) rowi[kgru + c] = lo;
                             split_bf16(sh[c], hi, lo);
                             row[HP + c] = hi;
                             if (m->precise) row[kgru + HP + c] = lo;
@@ -386,13 +394,7 @@ static int build_model(Model *m, const dp_model_weights *w) {
     rc = make_tmap_bf16_2d(&m->tm_wgru96, m->w_gru, (uint64_t)m->n_layers * 2 * 3 * HP, (uint64_t)m->kcols_gru,
                            (uint64_t)m->kcols_gru * 2, 96);
     if (rc) return rc;
-    rc = make_tmap_bf16_2d(&m->tm_wgru32, m->w_gru, (uint64_t)m->n_layers * 2 * 3 * HP, (uint64_t)m->kcols_gru,
-                           (uint64_t)m->kcols_gru * 2, 32);
     if (rc) return rc;
-    rc = make_tmap_bf16_2d(&m->tm_wgru64, m->w_gru, (uint64_t)m->n_layers * 2 * 3 * HP, (uint64_t)m->kcols_gru,
-                           (uint64_t)m->kcols_gru * 2, 64);
-    const char *e = getenv("DP_GRU");
-    m->gru_2cta = (e && !strcmp(e, "1cta")) ? 0 : 1;
     const char *e3 = getenv("DP_GRU_STATE");            // "f32": keep the fp32 state copy also in one-pass bf16 mode
     m->bf_state = 0;
     if (m->gru_2cta && !m->precise && e3) {
@@ -498,7 +500,7 @@ static int forward_rows(Model *m, const uint8_t *img, long long n_rows, float *l
                     }
                 }
             }
-            int rc = m->gru_2cta ? launch_gru_step2(tmA, &m->tm_wgru96, &m->tm_wgru64, &m->tm_wgru32, g, st)
+            int rc = m->gru_2cta ? launch_gru_step2(tmA, &m->tm_wgru96, g, st)
                                  : launch_gru_step(tmA, &m->tm_wgru, g, st);
             if (rc) return rc;
             mark();

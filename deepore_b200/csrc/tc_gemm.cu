@@ -600,20 +600,18 @@ gru_step_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
 // ================================================================================================
 // GRU time step on CTA PAIRS (cta_group::2).  The single-CTA kernel above is shared-memory-bandwidth bound: every
 // 128x192x16 MMA reads 10 KB of operands while TMA writes the next stage into the same shared memory.  Here a cluster
-// of two CTAs computes a 256-row x 64-unit tile with ONE M=256, N=256 instruction per 16-wide k step:
-//   * each CTA stages its own 128 rows of A and only HALF of the B rows, so shared-memory traffic per FLOP halves;
-//   * the weight tile is presented as 256 logical rows so that input and hidden chunks both need a single MMA:
-//       input chunk  [W_ir | W_iz | W_in |  0  ]   hidden chunk  [W_hr | W_hz |  0  | W_hn]
-//     CTA 0 supplies logical rows 0..127 (r,z), CTA 1 rows 128..255: its 64 real rows always sit in the middle of a
-//     192-row region whose outer thirds are zeroed once, and the descriptor starts at row 64 (input) or 0 (hidden).
-//     The zero quarter costs 25 % of the tensor-pipe time, far less than the second MMA + second A read it replaces;
-//   * accumulator columns per CTA: [r 64 | z 64 | W_in x 64 | W_hn h 64], so the epilogue is that of the 1-CTA kernel.
+// of two CTAs computes a 256-row x 64-unit tile with ONE M=256, N=192 instruction per 16-wide k step:
+//   * each CTA stages its own 128 rows of A and only HALF of the weight rows (96 of 192), so shared-memory traffic per
+//     FLOP halves;
+//   * accumulator columns per CTA: [W_in x 64 | r 64 | z 64 | W_hn h 64] (W_hn h stays separate because r multiplies it).
+//     The weight matrix holds the W_ih gates in the order (n, r, z) and the W_hh gates in the order (r, z, n)
+//     (model.cu), so an input chunk is one MMA into columns 0..191 and a hidden chunk one MMA into columns 64..255:
+//     no zero-padded operand rows, no second MMA (an N=128 + N=64 pair for the hidden chunk cost 6 % of the launch);
+//   * the accumulate flag is per instruction, so the hidden chunks always accumulate and columns 192..255 must be zero
+//     when a stage is handed to the MMA issuer: the epilogue warps zero them at kernel start and again right after
+//     reading them (tcgen05.st, free next to the loads); the first input chunk overwrites columns 0..191.
 // Barriers: `full` (leader only; both CTAs' TMA bytes are credited to it), `empty` / `tmem_full` (per CTA, released by
-// the leader's multicast tcgen05.commit), `tmem_empty` (leader, 16 arrivals: 8 epilogue warps of each CTA).
-// Weight rows per CTA and chunk: 96.  Input chunk: ONE N=192 MMA over [r|z|n] rows split 96/96 between the CTAs ->
-// TMEM columns 0..191.  Hidden chunk: an N=128 MMA over [r|z] (64 rows per CTA, region rows 0..63) -> columns 0..127 and
-// an N=64 MMA over [n] (32 rows per CTA, region rows 64..95) -> columns 192..255 (W_hn.h stays separate because r
-// multiplies it).  No zero-padded operand rows: every MMA column is useful work.
+// the leader's multicast tcgen05.commit), `tmem_empty` (leader, 32 arrivals: 16 epilogue warps of each CTA).
 constexpr int GRU2_B_ROWS = 96;
 constexpr int GRU2_STAGE_BYTES = A_STAGE_BYTES + GRU2_B_ROWS * 128;   // 16 KB A + 12 KB B
 constexpr int GRU2_STAGES = 7;
@@ -627,8 +625,7 @@ template <bool FAST_ACT>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GRU2_THREADS, 1)
 gru_step2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1,
                  const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmA3,
-                 const __grid_constant__ CUtensorMap tmB96, const __grid_constant__ CUtensorMap tmB64,
-                 const __grid_constant__ CUtensorMap tmB32, const GruArgs g) {
+                 const __grid_constant__ CUtensorMap tmB96, const GruArgs g) {
     constexpr int STAGES = GRU2_STAGES;
     extern __shared__ uint8_t smem_raw[];
     const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -652,7 +649,7 @@ gru_step2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
 
     if (warp == 0 && lane == 0) {
         prefetch_tmap(&tmA0); prefetch_tmap(&tmA1); prefetch_tmap(&tmA2); prefetch_tmap(&tmA3);
-        prefetch_tmap(&tmB96); prefetch_tmap(&tmB64); prefetch_tmap(&tmB32);
+        prefetch_tmap(&tmB96);
     }
     if (warp == 1 && lane == 0) {
         for (int s = 0; s < STAGES; s++) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
@@ -666,9 +663,16 @@ gru_step2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
                 s_chunks[pi * GRU2_MAX_CHUNKS + i] = g.prob[pi].chunks[i];
     tc_fence_before();
     __syncthreads();
-    cluster_sync_all();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot_ptr;
+    if (warp >= 4) {                                   // W_hn h columns of both accumulator stages start at zero
+        const uint32_t t0 = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + 192 + ((warp - 4) >> 2) * 16;
+        tmem_st16_zero(t0); tmem_st16_zero(t0 + 256);
+        tmem_st_wait();
+    }
+    tc_fence_before();
+    cluster_sync_all();                                // the leader's MMAs write both CTAs' tensor memory
+    tc_fence_after();
 
     if (warp == 0) {
         if (lane == 0) {
@@ -680,7 +684,7 @@ gru_step2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
                 const int brow = P.b_row_base + ub * GRU_BROWS;
                 for (int kc = 0; kc < P.n_chunks; kc++) {
                     const KChunk c = s_chunks[pi * GRU2_MAX_CHUNKS + kc];
-                    const int src = c.a_src & 0xff, kind = (c.a_src >> 8) & 0xff;
+                    const int src = c.a_src & 0xff;
                     const CUtensorMap *ma = src == 0 ? &tmA0 : src == 1 ? &tmA1 : src == 2 ? &tmA2 : &tmA3;
                     mbar_wait(empty_bar(ps.stage), ps.phase ^ 1u);
                     const int xm = g.debug >> 8;              // timing experiments: 1 no A loads, 4 no B loads
@@ -688,20 +692,14 @@ gru_step2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
                     const uint32_t sa = smem_base + ps.stage * GRU2_STAGE_BYTES;
                     const uint32_t sb = sa + A_STAGE_BYTES;
                     if (!(xm & 1)) tma_load_2d_2sm(sa, ma, full_bar(ps.stage), c.a_col, m0 + c.a_drow);
-                    if (xm & 4) { }
-                    else if (kind == 0) tma_load_2d_2sm(sb, &tmB96, full_bar(ps.stage), c.b_col, brow + (int)rank * 96);
-                    else {
-                        tma_load_2d_2sm(sb, &tmB64, full_bar(ps.stage), c.b_col, brow + (int)rank * 64);
-                        tma_load_2d_2sm(sb + 64u * 128u, &tmB32, full_bar(ps.stage), c.b_col, brow + 128 + (int)rank * 32);
-                    }
+                    if (!(xm & 4)) tma_load_2d_2sm(sb, &tmB96, full_bar(ps.stage), c.b_col, brow + (int)rank * 96);
                     ps.advance(STAGES);
                 }
             }
         }
     } else if (warp == 1) {
         if (lane == 0 && rank == 0) {
-            constexpr uint32_t idesc192 = make_idesc_bf16(256, 192), idesc128 = make_idesc_bf16(256, 128);
-            constexpr uint32_t idesc64 = make_idesc_bf16(256, 64);
+            constexpr uint32_t idesc192 = make_idesc_bf16(256, 192);
             PipeState ps{0, 0};
             int as = 0; uint32_t aphase = 0;
             for (int tile = pair; tile < n_tiles; tile += n_pairs) {
@@ -710,7 +708,6 @@ gru_step2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
                 mbar_wait(tempty_bar(as), aphase ^ 1u);
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + as * 256;
-                uint32_t nh_started = 0;                       // columns 192..255 are first written by the first hidden chunk
                 for (int kc = 0; kc < P.n_chunks; kc++) {
                     const int kind = (s_chunks[pi * GRU2_MAX_CHUNKS + kc].a_src >> 8) & 0xff;
                     mbar_wait(full_bar(ps.stage), ps.phase);
@@ -719,18 +716,14 @@ gru_step2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
                     const uint64_t da = make_smem_desc_sw128(sa);
                     const uint64_t db = make_smem_desc_sw128(sa + A_STAGE_BYTES);
                     if ((g.debug >> 8) & 2) {                  // timing experiment: no MMAs
-                    } else if (kind == 0) {                    // input chunks come first (model.cu chunk tables)
-#pragma unroll
+                    } else if (kind == 0) {                    // input chunks come first (model.cu chunk tables):
+#pragma unroll                                                 // columns 0..191 = [W_in x | r | z], started by the first one
                         for (int k = 0; k < BK / 16; k++)
                             umma_bf16_2sm(d_tmem, da + 2u * k, db + 2u * k, idesc192, (uint32_t)(kc | k));
-                    } else {
-                        const uint64_t dbn = make_smem_desc_sw128(sa + A_STAGE_BYTES + 64u * 128u);
-#pragma unroll
-                        for (int k = 0; k < BK / 16; k++) {
-                            umma_bf16_2sm(d_tmem, da + 2u * k, db + 2u * k, idesc128, 1u);
-                            umma_bf16_2sm(d_tmem + 192, da + 2u * k, dbn + 2u * k, idesc64, nh_started | (uint32_t)k);
-                        }
-                        nh_started = 1;
+                    } else {                                   // hidden chunks: columns 64..255 = [r | z | W_hn h]; the
+#pragma unroll                                                 // epilogue left columns 192..255 zeroed
+                        for (int k = 0; k < BK / 16; k++)
+                            umma_bf16_2sm(d_tmem + 64, da + 2u * k, db + 2u * k, idesc192, 1u);
                     }
                     umma_commit_mc(empty_bar(ps.stage), 3);
                     ps.advance(STAGES);
@@ -766,12 +759,14 @@ gru_step2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
             const uint32_t taddr = tmem_base + as * 256 + ((uint32_t)(wq * 32) << 16);
             if (dbg != 1) {
                 uint32_t vr[16], vz[16], vx[16], vh[16];
-                tmem_ld16(taddr + cb * 16, vr);
-                tmem_ld16(taddr + 64 + cb * 16, vz);
-                tmem_ld16(taddr + 128 + cb * 16, vx);
+                tmem_ld16(taddr + cb * 16, vx);
+                tmem_ld16(taddr + 64 + cb * 16, vr);
+                tmem_ld16(taddr + 128 + cb * 16, vz);
                 if (has_h) tmem_ld16(taddr + 192 + cb * 16, vh);
                 tmem_ld_wait();
-                // the accumulator stage is free as soon as its values are in registers
+                // the accumulator stage is free as soon as its values are in registers and the W_hn h columns, which the
+                // hidden chunks only ever accumulate into, are back to zero
+                if (has_h) { tmem_st16_zero(taddr + 192 + cb * 16); tmem_st_wait(); }
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive_cluster(tempty_bar(as), 0);
@@ -790,8 +785,7 @@ gru_step2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
     if (warp == 2) { tc_fence_after(); tmem_dealloc_2sm(tmem_base, 512); }
 }
 
-int launch_gru_step2(const CUtensorMap *tmA, const CUtensorMap *tmB96, const CUtensorMap *tmB64, const CUtensorMap *tmB32,
-                     const GruArgs &g_in, cudaStream_t st) {
+int launch_gru_step2(const CUtensorMap *tmA, const CUtensorMap *tmB96, const GruArgs &g_in, cudaStream_t st) {
     static bool attr_done[64] = {false};
     int dev = 0;
     DP_CUDA_CHECK(cudaGetDevice(&dev));
@@ -815,9 +809,9 @@ int launch_gru_step2(const CUtensorMap *tmA, const CUtensorMap *tmB96, const CUt
     const int max_pairs = device_sm_count() / 2;
     const int pairs = n_tiles < max_pairs ? n_tiles : max_pairs;
     if (g.fast_act)
-        gru_step2_kernel<true><<<2 * pairs, GRU2_THREADS, GRU2_SMEM_BYTES, st>>>(tmA[0], tmA[1], tmA[2], tmA[3], *tmB96, *tmB64, *tmB32, g);
+        gru_step2_kernel<true><<<2 * pairs, GRU2_THREADS, GRU2_SMEM_BYTES, st>>>(tmA[0], tmA[1], tmA[2], tmA[3], *tmB96, g);
     else
-        gru_step2_kernel<false><<<2 * pairs, GRU2_THREADS, GRU2_SMEM_BYTES, st>>>(tmA[0], tmA[1], tmA[2], tmA[3], *tmB96, *tmB64, *tmB32, g);
+        gru_step2_kernel<false><<<2 * pairs, GRU2_THREADS, GRU2_SMEM_BYTES, st>>>(tmA[0], tmA[1], tmA[2], tmA[3], *tmB96, g);
     DP_CUDA_CHECK(cudaGetLastError());
     return DP_OK;
 }

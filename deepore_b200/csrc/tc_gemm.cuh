@@ -73,9 +73,8 @@ struct GruArgs {
 int launch_gemm_bf16(const CUtensorMap *tmA /*[4]*/, const CUtensorMap *tmB, const GemmArgs &g, int block_n,
                      cudaStream_t st);
 int launch_gru_step(const CUtensorMap *tmA /*[4]*/, const CUtensorMap *tmB, const GruArgs &g, cudaStream_t st);
-// CTA-pair (cta_group::2) version: tmB96 / tmB64 / tmB32 are maps of the same weight matrix with 96-, 64- and 32-row boxes
-int launch_gru_step2(const CUtensorMap *tmA /*[4]*/, const CUtensorMap *tmB96, const CUtensorMap *tmB64,
-                     const CUtensorMap *tmB32, const GruArgs &g, cudaStream_t st);
+// CTA-pair (cta_group::2) version: tmB96 is a map of the weight matrix with 96-row boxes (W_ih gates packed n, r, z)
+int launch_gru_step2(const CUtensorMap *tmA /*[4]*/, const CUtensorMap *tmB96, const GruArgs &g, cudaStream_t st);
 int device_sm_count();
 
 }  // namespace dp
