@@ -58,7 +58,10 @@ def load_peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md).  The process is started
+    before the warm-up steps (its start-up -- fork, NVML initialisation -- stalled kernel launches for tens of ms when it
+    fell inside the timed region); mark() is called when the timed region begins and only samples that arrive after it
+    are used."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
@@ -66,11 +69,15 @@ class ClockSampler:
         self.index = index
         self.proc = None
         self.lines = []
+        self.t0 = 0.0
+
+    def mark(self):
+        self.t0 = time.time()
 
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                          "--format=csv,noheader,nounits", "-lms", "50"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._pump, daemon=True)
             self.t.start()
@@ -79,7 +86,7 @@ class ClockSampler:
 
     def _pump(self):
         for ln in self.proc.stdout:
-            self.lines.append(ln.strip())
+            self.lines.append((time.time(), ln.strip()))
 
     def stop(self):
         if self.proc is None:
@@ -92,7 +99,8 @@ class ClockSampler:
             self.proc.kill()
         sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for ln in self.lines:
+        lines = [ln for t, ln in self.lines if t >= self.t0] or [ln for t, ln in self.lines[-2:]]
+        for ln in lines:
             f = [x.strip() for x in ln.split(",")]
             if len(f) < 6:
                 continue
@@ -238,6 +246,9 @@ def main():
     _lib.require_cuda()
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    if sampler:
+        sampler.start()            # long before the timed region: its start-up must not fall inside it
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
 
@@ -316,7 +327,7 @@ def main():
         if profile and eng is not None:
             eng.profile(True)
         if sampler:
-            sampler.start()
+            sampler.mark()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         launches = 0
         enc_evs = []
@@ -351,7 +362,6 @@ def main():
         torch.cuda.synchronize(dev)
         return float(np.mean([a.elapsed_time(b) for a, b in evs]))
 
-    sampler = ClockSampler(local_rank) if rank == 0 else None
     ms_dev, launches, clocks, prof = timed(step_device, sampler, profile=True)
     ms_e2e, _, _, _ = timed(step_e2e)
     enc_ms = time_encoder_alone()

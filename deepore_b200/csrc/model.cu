@@ -63,7 +63,8 @@ struct Model {
     int fold_tab_off = 0, fold_tab_n = 0;
     int gru_tab_off[3][3][2], gru_tab_n[3][3][2];
     long long kcols_fold = 0, kcols_gru = 0;
-    CUtensorMap tm_img, tm_arena, tm_arena_lo, tm_wfold, tm_wgru, tm_wgru96;
+    CUtensorMap tm_img, tm_arena, tm_arena_lo, tm_wfold, tm_wgru, tm_wgru96, tm_arena_mc, tm_arena_lo_mc;
+    int gru_np = 1;                // CTA pairs per cluster of the pair kernel (A tiles multicast between them); env DP_GRU_NP
     int gru_2cta = 1;              // CTA-pair GRU kernel (env DP_GRU=1cta selects the single-CTA kernel)
     // optional per-kernel timing (bench.py roofline): one event per launch boundary, harvested by dp_model_profile_read
     int profile = 0;
@@ -281,6 +282,8 @@ static int build_model(Model *m, const dp_model_weights *w) {
     {
         const char *e = getenv("DP_GRU");
         m->gru_2cta = (e && !strcmp(e, "1cta")) ? 0 : 1;
+        const char *e2 = getenv("DP_GRU_NP");
+        if (e2 && (atoi(e2) == 1 || atoi(e2) == 2 || atoi(e2) == 4)) m->gru_np = atoi(e2);
     }
     const long long kgru = 2 * HP;
     m->kcols_gru = kgru * passes_b;
@@ -386,6 +389,11 @@ static int build_model(Model *m, const dp_model_weights *w) {
     if (m->precise) rc = make_tmap_bf16_2d(&m->tm_arena_lo, m->arena_lo, (uint64_t)NSLOT_BF * mc, HP, HP * 2, 128);
     else m->tm_arena_lo = m->tm_arena;
     if (rc) return rc;
+    rc = make_tmap_bf16_2d(&m->tm_arena_mc, m->arena, (uint64_t)NSLOT_BF * mc, HP, HP * 2, 128 / m->gru_np);
+    if (rc) return rc;
+    if (m->precise) rc = make_tmap_bf16_2d(&m->tm_arena_lo_mc, m->arena_lo, (uint64_t)NSLOT_BF * mc, HP, HP * 2, 128 / m->gru_np);
+    else m->tm_arena_lo_mc = m->tm_arena_mc;
+    if (rc) return rc;
     rc = make_tmap_bf16_2d(&m->tm_wfold, m->w_fold, (uint64_t)S * HP, (uint64_t)m->kcols_fold, (uint64_t)m->kcols_fold * 2, 256);
     if (rc) return rc;
     rc = make_tmap_bf16_2d(&m->tm_wgru, m->w_gru, (uint64_t)m->n_layers * 2 * 3 * HP, (uint64_t)m->kcols_gru,
@@ -431,6 +439,7 @@ static int forward_rows(Model *m, const uint8_t *img, long long n_rows, float *l
     mark();
     const int tiles_m = (int)((n_rows + 127) / 128);
     const CUtensorMap tmA[4] = {m->tm_img, m->tm_arena, m->tm_arena_lo, m->tm_arena};
+    const CUtensorMap tmA_mc[4] = {m->tm_img, m->tm_arena_mc, m->tm_arena_lo_mc, m->tm_arena_mc};   // GRU pair kernel
     // 2. folded CNN + Linear
     {
         GemmArgs g;
@@ -500,7 +509,7 @@ static int forward_rows(Model *m, const uint8_t *img, long long n_rows, float *l
                     }
                 }
             }
-            int rc = m->gru_2cta ? launch_gru_step2(tmA, &m->tm_wgru96, g, st)
+            int rc = m->gru_2cta ? launch_gru_step2(tmA_mc, &m->tm_wgru96, g, m->gru_np, st)
                                  : launch_gru_step(tmA, &m->tm_wgru, g, st);
             if (rc) return rc;
             mark();

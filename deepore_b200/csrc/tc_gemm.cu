@@ -621,8 +621,8 @@ constexpr int GRU2_MAX_CHUNKS = 48;                  // per problem: 16 K-chunks
 constexpr int GRU2_SMEM_BYTES = GRU2_STAGES * GRU2_STAGE_BYTES + 1024 + 256 + 2 * GRU2_MAX_CHUNKS * 16;
 constexpr uint32_t GRU2_TX_BYTES = 2 * A_STAGE_BYTES + 2 * GRU2_B_ROWS * 128;   // both CTAs' A tiles and weight rows
 
-template <bool FAST_ACT>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GRU2_THREADS, 1)
+template <bool FAST_ACT, int NP>
+__global__ void __launch_bounds__(GRU2_THREADS, 1)
 gru_step2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1,
                  const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmA3,
                  const __grid_constant__ CUtensorMap tmB96, const GruArgs g) {
@@ -642,17 +642,23 @@ gru_step2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
     KChunk *s_chunks = reinterpret_cast<KChunk *>(smem_gen + STAGES * GRU2_STAGE_BYTES + 256);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const uint32_t rank = cluster_ctarank();
-    const int pair = blockIdx.x >> 1, n_pairs = gridDim.x >> 1;
-    const int tiles_per_prob = g.tiles_m * GRU_NUB;                           // tiles_m counts 256-row blocks here
+    // cluster = NP CTA pairs working on the SAME 256 rows and NP neighbouring unit blocks: every 128-row A tile is
+    // needed by one CTA of each pair, so each of those CTAs fetches 128/NP of its rows and multicasts them to the others
+    const uint32_t crank = cluster_ctarank();
+    const uint32_t rank = crank & 1u, prk = crank >> 1;                       // rank within the pair, pair within the cluster
+    const int pair = blockIdx.x / (2 * NP), n_pairs = gridDim.x / (2 * NP);   // cluster index / count (tile loop stride)
+    constexpr int UBG = GRU_NUB / NP;                                         // unit-block groups per row block
+    const int tiles_per_prob = g.tiles_m * UBG;                               // tiles_m counts 256-row blocks here
     const int n_tiles = tiles_per_prob * g.n_prob;
+    constexpr uint16_t ALL_CTAS = (uint16_t)((1u << (2 * NP)) - 1u);
 
     if (warp == 0 && lane == 0) {
         prefetch_tmap(&tmA0); prefetch_tmap(&tmA1); prefetch_tmap(&tmA2); prefetch_tmap(&tmA3);
         prefetch_tmap(&tmB96);
     }
     if (warp == 1 && lane == 0) {
-        for (int s = 0; s < STAGES; s++) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
+        // empty: one commit per pair of the cluster (each pair's MMAs read what every CTA of the cluster multicast)
+        for (int s = 0; s < STAGES; s++) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), NP); }
         for (int s = 0; s < 2; s++) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), 2 * GRU2_EPI_WARPS); }
         fence_barrier_init();
     }
@@ -680,8 +686,11 @@ gru_step2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
             for (int tile = pair; tile < n_tiles; tile += n_pairs) {
                 const int pi = tile / tiles_per_prob, rem = tile % tiles_per_prob;
                 const GruProblem &P = g.prob[pi];
-                const int m0 = (rem / GRU_NUB) * 256 + (int)rank * BM, ub = rem % GRU_NUB;
+                const int m0 = (rem / UBG) * 256 + (int)rank * BM, ub = (rem % UBG) * NP + (int)prk;
                 const int brow = P.b_row_base + ub * GRU_BROWS;
+                uint16_t amask = 0;                           // the CTAs of this rank in every pair
+#pragma unroll
+                for (int q = 0; q < NP; q++) amask |= (uint16_t)(1u << (2 * q + (int)rank));
                 for (int kc = 0; kc < P.n_chunks; kc++) {
                     const KChunk c = s_chunks[pi * GRU2_MAX_CHUNKS + kc];
                     const int src = c.a_src & 0xff;
@@ -691,7 +700,10 @@ gru_step2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
                     if (rank == 0) mbar_expect_tx(full_bar(ps.stage), ((xm & 1) ? 0u : 2u * A_STAGE_BYTES) + ((xm & 4) ? 0u : 2u * GRU2_B_ROWS * 128u));
                     const uint32_t sa = smem_base + ps.stage * GRU2_STAGE_BYTES;
                     const uint32_t sb = sa + A_STAGE_BYTES;
-                    if (!(xm & 1)) tma_load_2d_2sm(sa, ma, full_bar(ps.stage), c.a_col, m0 + c.a_drow);
+                    if (xm & 1) { }
+                    else if (NP == 1) tma_load_2d_2sm(sa, ma, full_bar(ps.stage), c.a_col, m0 + c.a_drow);
+                    else tma_load_2d_2sm_mc(sa + prk * (uint32_t)(BM / NP) * 128u, ma, full_bar(ps.stage), c.a_col,
+                                            m0 + (int)prk * (BM / NP) + c.a_drow, amask);
                     if (!(xm & 4)) tma_load_2d_2sm(sb, &tmB96, full_bar(ps.stage), c.b_col, brow + (int)rank * 96);
                     ps.advance(STAGES);
                 }
@@ -725,10 +737,10 @@ gru_step2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
                         for (int k = 0; k < BK / 16; k++)
                             umma_bf16_2sm(d_tmem + 64, da + 2u * k, db + 2u * k, idesc192, 1u);
                     }
-                    umma_commit_mc(empty_bar(ps.stage), 3);
+                    umma_commit_mc(empty_bar(ps.stage), ALL_CTAS);
                     ps.advance(STAGES);
                 }
-                umma_commit_mc(tfull_bar(as), 3);
+                umma_commit_mc(tfull_bar(as), (uint16_t)(3u << (2 * prk)));
                 if (++as == 2) { as = 0; aphase ^= 1u; }
             }
         }
@@ -741,7 +753,7 @@ gru_step2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
         for (int tile = pair; tile < n_tiles; tile += n_pairs) {
             const int pi = tile / tiles_per_prob, rem = tile % tiles_per_prob;
             const GruProblem &P = g.prob[pi];
-            const int m0 = (rem / GRU_NUB) * 256 + (int)rank * BM, ub = rem % GRU_NUB;
+            const int m0 = (rem / UBG) * 256 + (int)rank * BM, ub = (rem % UBG) * NP + (int)prk;
             const long long m_warp0 = m0 + wq * 32;
             const long long m = m_warp0 + lane;
             const bool has_h = P.h_prev != nullptr || P.h_prev_bf != nullptr;   // else no hidden chunks: columns 192..255 are never written
@@ -769,12 +781,12 @@ gru_step2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
                 if (has_h) { tmem_st16_zero(taddr + 192 + cb * 16); tmem_st_wait(); }
                 tc_fence_before();
                 __syncwarp();
-                if (lane == 0) mbar_arrive_cluster(tempty_bar(as), 0);
+                if (lane == 0) mbar_arrive_cluster(tempty_bar(as), crank & ~1u);
                 gru_finish16<FAST_ACT>(P, g.M, m_warp0, lane, ub * GRU_UB + cb * 16, vr, vz, vx, vh, has_h, hp, dbg);
             } else {
                 tc_fence_before();
                 __syncwarp();
-                if (lane == 0) mbar_arrive_cluster(tempty_bar(as), 0);
+                if (lane == 0) mbar_arrive_cluster(tempty_bar(as), crank & ~1u);
             }
             if (++as == 2) { as = 0; aphase ^= 1u; }
         }
@@ -785,15 +797,42 @@ gru_step2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
     if (warp == 2) { tc_fence_after(); tmem_dealloc_2sm(tmem_base, 512); }
 }
 
-int launch_gru_step2(const CUtensorMap *tmA, const CUtensorMap *tmB96, const GruArgs &g_in, cudaStream_t st) {
+template <bool FAST_ACT, int NP>
+static int launch_gru_step2_t(const CUtensorMap *tmA, const CUtensorMap *tmB96, const GruArgs &g, int n_ctiles, cudaStream_t st) {
+    auto kern = gru_step2_kernel<FAST_ACT, NP>;
     static bool attr_done[64] = {false};
+    static int max_clusters[64] = {0};
     int dev = 0;
     DP_CUDA_CHECK(cudaGetDevice(&dev));
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2 * NP; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.blockDim = dim3(GRU2_THREADS, 1, 1);
+    cfg.dynamicSmemBytes = GRU2_SMEM_BYTES;
+    cfg.stream = st;
+    cfg.attrs = attr; cfg.numAttrs = 1;
     if (dev >= 64 || !attr_done[dev]) {
-        DP_CUDA_CHECK(cudaFuncSetAttribute(gru_step2_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, GRU2_SMEM_BYTES));
-        DP_CUDA_CHECK(cudaFuncSetAttribute(gru_step2_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, GRU2_SMEM_BYTES));
-        if (dev < 64) attr_done[dev] = true;
+        DP_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GRU2_SMEM_BYTES));
+        // clusters that fit at once (a GPC whose SM count is not a multiple of the cluster size leaves SMs idle)
+        cfg.gridDim = dim3((unsigned)(2 * NP * (device_sm_count() / (2 * NP))), 1, 1);
+        int nc = 0;
+        DP_CUDA_CHECK(cudaOccupancyMaxActiveClusters(&nc, kern, &cfg));
+        if (nc <= 0) { set_error("gru_step2: no cluster of %d CTAs fits on this device", 2 * NP); return DP_ECUDA; }
+        if (dev < 64) { max_clusters[dev] = nc; attr_done[dev] = true; }
+        else max_clusters[0] = nc;
+        if (getenv("DP_GRU_VERBOSE")) fprintf(stderr, "gru_step2: cluster of %d CTAs, %d clusters resident\n", 2 * NP, nc);
     }
+    const int cap = max_clusters[dev < 64 ? dev : 0];
+    const int clusters = n_ctiles < cap ? n_ctiles : cap;
+    cfg.gridDim = dim3((unsigned)(2 * NP * clusters), 1, 1);
+    DP_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, tmA[0], tmA[1], tmA[2], tmA[3], *tmB96, g));
+    return DP_OK;
+}
+
+// np = CTA pairs per cluster (1, 2 or 4); tmA must have boxes of 128 / np rows
+int launch_gru_step2(const CUtensorMap *tmA, const CUtensorMap *tmB96, const GruArgs &g_in, int np, cudaStream_t st) {
     static int dbg = -1;
     if (dbg < 0) {
         const char *e = getenv("DP_GRU_DEBUG"); dbg = e ? atoi(e) : 0;
@@ -802,18 +841,19 @@ int launch_gru_step2(const CUtensorMap *tmA, const CUtensorMap *tmB96, const Gru
     GruArgs g = g_in;
     g.debug = dbg;
     g.tiles_m = (g.M + 255) / 256;
-    const int n_tiles = g.tiles_m * GRU_NUB * g.n_prob;
-    if (n_tiles <= 0) return DP_OK;
+    if (np != 1 && np != 2 && np != 4) { set_error("gru_step2: pairs per cluster must be 1, 2 or 4"); return DP_EINVAL; }
+    const int n_ctiles = g.tiles_m * (GRU_NUB / np) * g.n_prob;
+    if (n_ctiles <= 0) return DP_OK;
     for (int i = 0; i < g.n_prob; i++)
         if (g.prob[i].n_chunks > GRU2_MAX_CHUNKS) { set_error("gru_step2: too many K chunks"); return DP_EINVAL; }
-    const int max_pairs = device_sm_count() / 2;
-    const int pairs = n_tiles < max_pairs ? n_tiles : max_pairs;
-    if (g.fast_act)
-        gru_step2_kernel<true><<<2 * pairs, GRU2_THREADS, GRU2_SMEM_BYTES, st>>>(tmA[0], tmA[1], tmA[2], tmA[3], *tmB96, g);
-    else
-        gru_step2_kernel<false><<<2 * pairs, GRU2_THREADS, GRU2_SMEM_BYTES, st>>>(tmA[0], tmA[1], tmA[2], tmA[3], *tmB96, g);
-    DP_CUDA_CHECK(cudaGetLastError());
-    return DP_OK;
+    if (g.fast_act) {
+        if (np == 1) return launch_gru_step2_t<true, 1>(tmA, tmB96, g, n_ctiles, st);
+        if (np == 2) return launch_gru_step2_t<true, 2>(tmA, tmB96, g, n_ctiles, st);
+        return launch_gru_step2_t<true, 4>(tmA, tmB96, g, n_ctiles, st);
+    }
+    if (np == 1) return launch_gru_step2_t<false, 1>(tmA, tmB96, g, n_ctiles, st);
+    if (np == 2) return launch_gru_step2_t<false, 2>(tmA, tmB96, g, n_ctiles, st);
+    return launch_gru_step2_t<false, 4>(tmA, tmB96, g, n_ctiles, st);
 }
 
 int launch_gru_step(const CUtensorMap *tmA, const CUtensorMap *tmB, const GruArgs &g_in, cudaStream_t st) {
