@@ -402,7 +402,6 @@ static int build_model(Model *m, const dp_model_weights *w) {
     rc = make_tmap_bf16_2d(&m->tm_wgru96, m->w_gru, (uint64_t)m->n_layers * 2 * 3 * HP, (uint64_t)m->kcols_gru,
                            (uint64_t)m->kcols_gru * 2, 96);
     if (rc) return rc;
-    if (rc) return rc;
     const char *e3 = getenv("DP_GRU_STATE");            // "f32": keep the fp32 state copy also in one-pass bf16 mode
     m->bf_state = 0;
     if (m->gru_2cta && !m->precise && e3) {
@@ -483,8 +482,11 @@ static int forward_rows(Model *m, const uint8_t *img, long long n_rows, float *l
                 if (hs >= 0 && prev_f32) P.h_prev = m->state + (size_t)hs * mc * HP;
                 else if (hsb >= 0) P.h_prev_bf = m->arena + (size_t)hsb * mc * HP;
                 P.h_out = k >= m->bf_state ? m->state + (size_t)os * mc * HP : nullptr;
-                P.h_out_bf = m->arena + (size_t)ob * mc * HP;
-                P.h_out_lo = m->precise ? m->arena_lo + (size_t)ob * mc * HP : nullptr;
+                // the bf16 copy is the next step's / next layer's A operand: nobody reads the last one of the last layer
+                // (fc1 takes the fp32 state)
+                const bool bf_unused = sg == 2 && k + 1 == m->n_layers && k >= m->bf_state;
+                P.h_out_bf = bf_unused ? nullptr : m->arena + (size_t)ob * mc * HP;
+                P.h_out_lo = (m->precise && !bf_unused) ? m->arena_lo + (size_t)ob * mc * HP : nullptr;
                 if (sg == 2 && k + 1 < m->n_layers) {
                     // sum of directions (model.py:131-133) -> bf16 input of the next layer
                     if (d == 0) {
