@@ -132,6 +132,7 @@ def test_bundled_windows_end_to_end_call_set():
     calls, _ = model.vote(pred.view(-1, 3), len(pick), img.shape[1], 3)
     torch.cuda.synchronize()
     calls = calls.cpu().numpy()
+    n_identical, oracle_votes = 0, []
     for i, wi in enumerate(pick[:2]):                       # the numpy oracle takes ~1 s per window
         want = mo.forward_image(st, g.img[wi], dtype=np.float64)
         got = logits[i].cpu().numpy()[:148]
@@ -139,6 +140,21 @@ def test_bundled_windows_end_to_end_call_set():
         srt = np.sort(want, axis=-1)
         decisive = (srt[..., -1] - srt[..., -2]) > 4e-4
         wp = mo.argmax_first(want)
+        oracle_votes.append(mo.vote(wp))
         assert np.array_equal(pred[i, :148].cpu().numpy()[decisive], wp[decisive])
         if decisive.all():
             assert np.array_equal(calls[i], mo.vote(wp))
+            n_identical += 1
+    # the call-set artefact (deepore_b200/calls.py): records from the CUDA outputs == records from the oracle chain
+    import pileup_oracle as po
+    from deepore_b200 import calls as dc
+    lo, hi = g.reads.window_ranges(g.win_qs[pick], 100)
+    _, _, o_rowpos, o_rowins = po.encode_windows(g.reads, g.win_qs[pick], lo, hi, g.ref, g.ref_base, want_rowmap=True)
+    assert np.array_equal(rowpos.cpu().numpy(), o_rowpos) and np.array_equal(rowins.cpu().numpy(), o_rowins)
+    rec = dc.call_records(calls, rowpos.cpu().numpy(), rowins.cpu().numpy())
+    assert rec.shape[0] > 0 and (rec["row"] >= 2).all() and (rec["pos"] >= g.win_qs[pick].min()).all()
+    if n_identical == 2:
+        want = dc.call_records(np.stack(oracle_votes), o_rowpos[:2], o_rowins[:2])
+        assert np.array_equal(rec[rec["window"] < 2], want)
+    merged = dc.merge_records(rec, g.win_qs[pick])
+    assert merged.shape[0] <= rec.shape[0] and np.all(np.diff(merged["pos"]) >= 0)
