@@ -58,61 +58,95 @@ def load_peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md).  The process is started
-    before the warm-up steps (its start-up -- fork, NVML initialisation -- stalled kernel launches for tens of ms when it
-    fell inside the timed region); mark() is called when the timed region begins and only samples that arrive after it
-    are used."""
+    """SM clock and throttle reasons sampled DURING the timed region (B200_PROFILING.md's clocks line).  NVML is polled
+    from a thread of this process (pynvml, every 20 ms; an `nvidia-smi -lms` child is the fallback when pynvml is
+    missing).  start() long before the timed region -- the start-up (NVML initialisation, or fork + exec of nvidia-smi)
+    must not fall inside it -- and mark() when it begins: only samples taken after mark() are used."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    # nvmlClocksEventReason* bits
+    BITS = {"sw_power_cap": 0x4, "hw_slowdown": 0x8, "sw_thermal_slowdown": 0x20, "hw_thermal_slowdown": 0x40}
 
     def __init__(self, index=0):
         self.index = index
         self.proc = None
-        self.lines = []
+        self.nvml = None
+        self.samples = []          # (time, sm_mhz, max_mhz, set of reasons)
         self.t0 = 0.0
+        self.stop_flag = False
 
     def mark(self):
         self.t0 = time.time()
 
     def start(self):
         try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(self.index)
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+            self.nvml = pynvml
+            self.t = threading.Thread(target=self._poll, daemon=True)
+            self.t.start()
+            return
+        except Exception:
+            self.nvml = None
+        try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "50"],
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._pump, daemon=True)
             self.t.start()
         except Exception:
             self.proc = None
 
-    def _pump(self):
-        for ln in self.proc.stdout:
-            self.lines.append((time.time(), ln.strip()))
+    def _poll(self):
+        nv = self.nvml
+        while not self.stop_flag:
+            try:
+                mhz = float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                try:
+                    mask = int(nv.nvmlDeviceGetCurrentClocksEventReasons(self.h))
+                except Exception:
+                    mask = int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h))
+                self.samples.append((time.time(), mhz, self.max_mhz, {n for n, b in self.BITS.items() if mask & b}))
+            except Exception:
+                pass
+            time.sleep(0.02)
 
-    def stop(self):
-        if self.proc is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.05)
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=2)
-        except Exception:
-            self.proc.kill()
-        sm, mx, reasons = [], [], set()
+    def _pump(self):
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        lines = [ln for t, ln in self.lines if t >= self.t0] or [ln for t, ln in self.lines[-2:]]
-        for ln in lines:
-            f = [x.strip() for x in ln.split(",")]
+        for ln in self.proc.stdout:
+            f = [x.strip() for x in ln.strip().split(",")]
             if len(f) < 6:
                 continue
             try:
-                sm.append(float(f[0])); mx.append(float(f[1]))
+                self.samples.append((time.time(), float(f[0]), float(f[1]),
+                                     {n for n, v in zip(names, f[2:6]) if v.lower().startswith("active")}))
             except ValueError:
                 continue
-            for n, v in zip(names, f[2:6]):
-                if v.lower().startswith("active"):
-                    reasons.add(n)
+
+    def stop(self):
+        if self.nvml is None and self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["NVML / nvidia-smi unavailable"]}
+        time.sleep(0.03)
+        self.stop_flag = True
+        if self.proc is not None:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=2)
+            except Exception:
+                self.proc.kill()
+        else:
+            self.t.join(timeout=1)
+        use = [x for x in self.samples if x[0] >= self.t0] or self.samples[-2:]
+        sm = [x[1] for x in use]
+        mx = [x[2] for x in use]
+        reasons = set()
+        for x in use:
+            reasons |= x[3]
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "samples": len(sm), "reasons": sorted(reasons)}
+                "samples": len(sm), "reasons": sorted(reasons),
+                "source": "nvml" if self.nvml is not None else "nvidia-smi"}
 
 
 # ----------------------------------------------------------------------------------------------------
@@ -369,7 +403,14 @@ def main():
         torch.cuda.synchronize(dev)
         return float(np.mean([a.elapsed_time(b) for a, b in evs]))
 
-    ms_dev, launches, clocks, prof = timed(step_device, sampler, profile=True)
+    # instrumented pass (CUDA events around every model kernel -> kernel shares and the roofline's launch time), then the
+    # pass `value` is taken from: the same K steps without the per-kernel events, clocks sampled during it
+    prof = ms_prof = None
+    if with_model:
+        ms_prof, _, _, prof = timed(step_device, None, profile=True)
+    ms_dev, launches, clocks, _ = timed(step_device, sampler, profile=False)
+    if ms_prof is None:
+        ms_prof = ms_dev
     ms_e2e, _, _, _ = timed(step_e2e)
     enc_ms = time_encoder_alone()
 
@@ -412,10 +453,10 @@ def main():
                                 "peak_source": peaks["source"] + " (sustained bf16)", "kernel": "gru_step2_kernel",
                                 "ms_per_launch": g_ms / max(1, g_n), "launches": g_n,
                                 "algorithmic_flop_per_launch": flop_per_launch,
-                                "share_of_step": g_ms / ms_dev}
+                                "share_of_step": g_ms / ms_prof}
             f_ms, f_n = prof["fold_gemm"]
             fach = rows_per_launch * FLOP_FOLD_PER_ROW / (f_ms / max(1, f_n) * 1e-3) / 1e12
-            line["kernels"] = {k: {"ms_total": v[0], "launches": v[1], "share_of_step": v[0] / ms_dev} for k, v in prof.items()}
+            line["kernels"] = {k: {"ms_total": v[0], "launches": v[1], "share_of_step": v[0] / ms_prof} for k, v in prof.items()}
             line["kernels"]["fold_gemm"]["achieved_tflops"] = fach
             line["kernels"]["encoder"] = {"ms_per_launch_pair": enc_ms, "share_of_step": enc_ms * args.steps / ms_dev}
             line["roofline_encoder"] = enc_roof

@@ -65,6 +65,7 @@ struct Model {
     long long kcols_fold = 0, kcols_gru = 0;
     CUtensorMap tm_img, tm_arena, tm_arena_lo, tm_wfold, tm_wgru, tm_wgru96, tm_arena_mc, tm_arena_lo_mc;
     int gru_np = 1;                // CTA pairs per cluster of the pair kernel (A tiles multicast between them); env DP_GRU_NP
+    int gru_wide = 0;              // env DP_GRU=wide: 256 x 128-unit tiles (gru_step2w_kernel)
     int gru_2cta = 1;              // CTA-pair GRU kernel (env DP_GRU=1cta selects the single-CTA kernel)
     // optional per-kernel timing (bench.py roofline): one event per launch boundary, harvested by dp_model_profile_read
     int profile = 0;
@@ -282,6 +283,7 @@ static int build_model(Model *m, const dp_model_weights *w) {
     {
         const char *e = getenv("DP_GRU");
         m->gru_2cta = (e && !strcmp(e, "1cta")) ? 0 : 1;
+        m->gru_wide = (e && !strcmp(e, "wide")) ? 1 : 0;
         const char *e2 = getenv("DP_GRU_NP");
         if (e2 && (atoi(e2) == 1 || atoi(e2) == 2 || atoi(e2) == 4)) m->gru_np = atoi(e2);
     }
@@ -511,7 +513,8 @@ static int forward_rows(Model *m, const uint8_t *img, long long n_rows, float *l
                     }
                 }
             }
-            int rc = m->gru_2cta ? launch_gru_step2(tmA_mc, &m->tm_wgru96, g, m->gru_np, st)
+            int rc = m->gru_wide ? launch_gru_step2w(tmA, &m->tm_wgru96, g, st)
+                   : m->gru_2cta ? launch_gru_step2(tmA_mc, &m->tm_wgru96, g, m->gru_np, st)
                                  : launch_gru_step(tmA, &m->tm_wgru, g, st);
             if (rc) return rc;
             mark();

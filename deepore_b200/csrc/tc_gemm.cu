@@ -797,6 +797,196 @@ gru_step2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
     if (warp == 2) { tc_fence_after(); tmem_dealloc_2sm(tmem_base, 512); }
 }
 
+// ================================================================================================
+// WIDE variant of the CTA-pair kernel: tile = 256 rows x 128 hidden units (two unit blocks).  The pair kernel above pulls
+// (128 + 96) operand rows per CTA and k-chunk out of L2 for a 64-unit tile and is bound by that stream; here one A tile
+// feeds the MMAs of TWO unit blocks, (128 + 2 x 96) rows for twice the FLOPs = 29 % fewer operand bytes per FLOP.  Price:
+// the two accumulator sets [W_in x | r | z | W_hn h] x 64 fill all 512 TMEM columns, so there is no second accumulator
+// stage -- the MMAs of the next tile start when every epilogue warp has its SECOND group of 16 units in registers, i.e.
+// the tensor pipe idles for about one group's gate math per tile.  5-stage ring of (16 KB A + 2 x 12 KB weights).
+constexpr int GRUW_STAGE_BYTES = A_STAGE_BYTES + 2 * GRU2_B_ROWS * 128;
+constexpr int GRUW_STAGES = 5;
+constexpr int GRUW_SMEM_BYTES = GRUW_STAGES * GRUW_STAGE_BYTES + 1024 + 256 + 2 * GRU2_MAX_CHUNKS * 16;
+
+template <bool FAST_ACT>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GRU2_THREADS, 1)
+gru_step2w_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1,
+                  const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmA3,
+                  const __grid_constant__ CUtensorMap tmB96, const GruArgs g) {
+    constexpr int STAGES = GRUW_STAGES;
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    const uint32_t bar_base = smem_base + STAGES * GRUW_STAGE_BYTES;
+    auto full_bar = [&](int s) { return bar_base + 8u * s; };
+    auto empty_bar = [&](int s) { return bar_base + 8u * (STAGES + s); };
+    const uint32_t tfull_bar = bar_base + 8u * (2 * STAGES), tempty_bar = bar_base + 8u * (2 * STAGES + 1);
+    const uint32_t tmem_slot = bar_base + 8u * (2 * STAGES + 2);
+    uint8_t *smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
+    uint32_t *tmem_slot_ptr = reinterpret_cast<uint32_t *>(smem_gen + (tmem_slot - smem_base));
+    KChunk *s_chunks = reinterpret_cast<KChunk *>(smem_gen + STAGES * GRUW_STAGE_BYTES + 256);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t rank = cluster_ctarank();
+    const int pair = blockIdx.x >> 1, n_pairs = gridDim.x >> 1;
+    constexpr int UBG = GRU_NUB / 2;                                          // 128-unit groups per row block
+    const int tiles_per_prob = g.tiles_m * UBG;
+    const int n_tiles = tiles_per_prob * g.n_prob;
+
+    if (warp == 0 && lane == 0) {
+        prefetch_tmap(&tmA0); prefetch_tmap(&tmA1); prefetch_tmap(&tmA2); prefetch_tmap(&tmA3);
+        prefetch_tmap(&tmB96);
+    }
+    if (warp == 1 && lane == 0) {
+        for (int s = 0; s < STAGES; s++) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
+        mbar_init(tfull_bar, 1); mbar_init(tempty_bar, 2 * GRU2_EPI_WARPS);
+        fence_barrier_init();
+    }
+    if (warp == 2) { tmem_alloc_2sm(tmem_slot, 512); tmem_relinquish_2sm(); }
+    if (warp >= 4)
+        for (int pi = 0; pi < g.n_prob; pi++)
+            for (int i = threadIdx.x - 128; i < g.prob[pi].n_chunks && i < GRU2_MAX_CHUNKS; i += GRU2_THREADS - 128)
+                s_chunks[pi * GRU2_MAX_CHUNKS + i] = g.prob[pi].chunks[i];
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot_ptr;
+    if (warp >= 4) {                                   // W_hn h columns of both unit blocks start at zero
+        const uint32_t t0 = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + 192 + ((warp - 4) >> 2) * 16;
+        tmem_st16_zero(t0); tmem_st16_zero(t0 + 256);
+        tmem_st_wait();
+    }
+    tc_fence_before();
+    cluster_sync_all();
+    tc_fence_after();
+
+    if (warp == 0) {
+        if (lane == 0) {
+            PipeState ps{0, 0};
+            for (int tile = pair; tile < n_tiles; tile += n_pairs) {
+                const int pi = tile / tiles_per_prob, rem = tile % tiles_per_prob;
+                const GruProblem &P = g.prob[pi];
+                const int m0 = (rem / UBG) * 256 + (int)rank * BM, ub = (rem % UBG) * 2;
+                const int brow = P.b_row_base + ub * GRU_BROWS;
+                for (int kc = 0; kc < P.n_chunks; kc++) {
+                    const KChunk c = s_chunks[pi * GRU2_MAX_CHUNKS + kc];
+                    const int src = c.a_src & 0xff;
+                    const CUtensorMap *ma = src == 0 ? &tmA0 : src == 1 ? &tmA1 : src == 2 ? &tmA2 : &tmA3;
+                    mbar_wait(empty_bar(ps.stage), ps.phase ^ 1u);
+                    if (rank == 0) mbar_expect_tx(full_bar(ps.stage), 2u * (uint32_t)GRUW_STAGE_BYTES);
+                    const uint32_t sa = smem_base + ps.stage * GRUW_STAGE_BYTES;
+                    const uint32_t sb = sa + A_STAGE_BYTES;
+                    tma_load_2d_2sm(sa, ma, full_bar(ps.stage), c.a_col, m0 + c.a_drow);
+                    tma_load_2d_2sm(sb, &tmB96, full_bar(ps.stage), c.b_col, brow + (int)rank * 96);
+                    tma_load_2d_2sm(sb + GRU2_B_ROWS * 128u, &tmB96, full_bar(ps.stage), c.b_col, brow + GRU_BROWS + (int)rank * 96);
+                    ps.advance(STAGES);
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0 && rank == 0) {
+            constexpr uint32_t idesc192 = make_idesc_bf16(256, 192);
+            PipeState ps{0, 0};
+            uint32_t aphase = 0;
+            for (int tile = pair; tile < n_tiles; tile += n_pairs) {
+                const int pi = tile / tiles_per_prob;
+                const GruProblem &P = g.prob[pi];
+                mbar_wait(tempty_bar, aphase ^ 1u);
+                tc_fence_after();
+                for (int kc = 0; kc < P.n_chunks; kc++) {
+                    const int kind = (s_chunks[pi * GRU2_MAX_CHUNKS + kc].a_src >> 8) & 0xff;
+                    mbar_wait(full_bar(ps.stage), ps.phase);
+                    tc_fence_after();
+                    const uint32_t sa = smem_base + ps.stage * GRUW_STAGE_BYTES;
+                    const uint64_t da = make_smem_desc_sw128(sa);
+                    const uint64_t db0 = make_smem_desc_sw128(sa + A_STAGE_BYTES);
+                    const uint64_t db1 = make_smem_desc_sw128(sa + A_STAGE_BYTES + GRU2_B_ROWS * 128u);
+                    const uint32_t d0 = tmem_base + (kind == 0 ? 0u : 64u);   // input: columns 0..191, hidden: 64..255
+#pragma unroll
+                    for (int k = 0; k < BK / 16; k++) {
+                        const uint32_t acc = kind == 0 ? (uint32_t)(kc | k) : 1u;
+                        umma_bf16_2sm(d0, da + 2u * k, db0 + 2u * k, idesc192, acc);
+                        umma_bf16_2sm(d0 + 256, da + 2u * k, db1 + 2u * k, idesc192, acc);
+                    }
+                    umma_commit_mc(empty_bar(ps.stage), 3);
+                    ps.advance(STAGES);
+                }
+                umma_commit_mc(tfull_bar, 3);
+                aphase ^= 1u;
+            }
+        }
+    } else if (warp >= 4) {
+        // warp w: TMEM lanes 32*(w%4).., units cb = (w-4)/4 of BOTH unit blocks, one after the other; the accumulators are
+        // handed back to the MMA issuer when the second group is in registers
+        const int wq = warp & 3, cb = (warp - 4) >> 2;
+        uint32_t aphase = 0;
+        for (int tile = pair; tile < n_tiles; tile += n_pairs) {
+            const int pi = tile / tiles_per_prob, rem = tile % tiles_per_prob;
+            const GruProblem &P = g.prob[pi];
+            const int m0 = (rem / UBG) * 256 + (int)rank * BM, ub = (rem % UBG) * 2;
+            const long long m_warp0 = m0 + wq * 32;
+            const long long m = m_warp0 + lane;
+            const bool has_h = P.h_prev != nullptr || P.h_prev_bf != nullptr;
+            const int dbg = g.debug & 0xff;
+            const uint32_t taddr = tmem_base + ((uint32_t)(wq * 32) << 16);
+#pragma unroll 1
+            for (int hb = 0; hb < 2; hb++) {
+                const int u0 = (ub + hb) * GRU_UB + cb * 16;
+                float hp[16];
+                if (P.h_prev && m < g.M) state_load16(P.h_prev, m, u0, hp);
+                else if (P.h_prev_bf && m < g.M) rows_load_bf16(P.h_prev_bf, m, u0, hp);
+                else {
+#pragma unroll
+                    for (int i = 0; i < 16; i++) hp[i] = 0.f;
+                }
+                if (hb == 0) { mbar_wait(tfull_bar, aphase); tc_fence_after(); }
+                uint32_t vr[16], vz[16], vx[16], vh[16];
+                const uint32_t t = taddr + hb * 256 + cb * 16;
+                tmem_ld16(t, vx);
+                tmem_ld16(t + 64, vr);
+                tmem_ld16(t + 128, vz);
+                if (has_h) tmem_ld16(t + 192, vh);
+                tmem_ld_wait();
+                if (has_h) { tmem_st16_zero(t + 192); tmem_st_wait(); }
+                if (hb == 1) {
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive_cluster(tempty_bar, 0);
+                }
+                gru_finish16<FAST_ACT>(P, g.M, m_warp0, lane, u0, vr, vz, vx, vh, has_h, hp, dbg);
+            }
+            aphase ^= 1u;
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();
+    if (warp == 2) { tc_fence_after(); tmem_dealloc_2sm(tmem_base, 512); }
+}
+
+int launch_gru_step2w(const CUtensorMap *tmA, const CUtensorMap *tmB96, const GruArgs &g_in, cudaStream_t st) {
+    static bool attr_done[64] = {false};
+    int dev = 0;
+    DP_CUDA_CHECK(cudaGetDevice(&dev));
+    if (dev >= 64 || !attr_done[dev]) {
+        DP_CUDA_CHECK(cudaFuncSetAttribute(gru_step2w_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, GRUW_SMEM_BYTES));
+        DP_CUDA_CHECK(cudaFuncSetAttribute(gru_step2w_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, GRUW_SMEM_BYTES));
+        if (dev < 64) attr_done[dev] = true;
+    }
+    GruArgs g = g_in;
+    g.debug = 0;
+    g.tiles_m = (g.M + 255) / 256;
+    const int n_tiles = g.tiles_m * (GRU_NUB / 2) * g.n_prob;
+    if (n_tiles <= 0) return DP_OK;
+    for (int i = 0; i < g.n_prob; i++)
+        if (g.prob[i].n_chunks > GRU2_MAX_CHUNKS) { set_error("gru_step2w: too many K chunks"); return DP_EINVAL; }
+    const int max_pairs = device_sm_count() / 2;
+    const int pairs = n_tiles < max_pairs ? n_tiles : max_pairs;
+    if (g.fast_act) gru_step2w_kernel<true><<<2 * pairs, GRU2_THREADS, GRUW_SMEM_BYTES, st>>>(tmA[0], tmA[1], tmA[2], tmA[3], *tmB96, g);
+    else gru_step2w_kernel<false><<<2 * pairs, GRU2_THREADS, GRUW_SMEM_BYTES, st>>>(tmA[0], tmA[1], tmA[2], tmA[3], *tmB96, g);
+    DP_CUDA_CHECK(cudaGetLastError());
+    return DP_OK;
+}
+
 template <bool FAST_ACT, int NP>
 static int launch_gru_step2_t(const CUtensorMap *tmA, const CUtensorMap *tmB96, const GruArgs &g, int n_ctiles, cudaStream_t st) {
     auto kern = gru_step2_kernel<FAST_ACT, NP>;

@@ -76,6 +76,8 @@ int launch_gru_step(const CUtensorMap *tmA /*[4]*/, const CUtensorMap *tmB, cons
 // CTA-pair (cta_group::2) version: tmB96 is a map of the weight matrix with 96-row boxes (W_ih gates packed n, r, z);
 // np = CTA pairs per cluster sharing their A tiles by TMA multicast (1, 2 or 4), tmA boxes are 128 / np rows
 int launch_gru_step2(const CUtensorMap *tmA /*[4]*/, const CUtensorMap *tmB96, const GruArgs &g, int np, cudaStream_t st);
+// wide variant: 256 rows x 128 hidden units per tile, one accumulator stage (tmA boxes of 128 rows)
+int launch_gru_step2w(const CUtensorMap *tmA /*[4]*/, const CUtensorMap *tmB96, const GruArgs &g, cudaStream_t st);
 int device_sm_count();
 
 }  // namespace dp

@@ -52,6 +52,20 @@ def test_front_and_logits_vs_reference(gold, precision):
     assert decisive.mean() > 0.9
 
 
+@pytest.mark.parametrize("env", [{"DP_GRU": "wide"}, {"DP_GRU_NP": "2"}, {"DP_GRU_NP": "4"}, {"DP_GRU": "1cta"}])
+def test_gru_kernel_variants_vs_reference(gold, env, monkeypatch):
+    """The opt-in GRU step kernels (256 x 128-unit tiles; clusters of 2 / 4 CTA pairs sharing A tiles by TMA multicast; the
+    single-CTA kernel) against the same golden logits as the default CTA-pair kernel.  The choice is read at model creation."""
+    for k, v in env.items():
+        monkeypatch.setenv(k, v)
+    m = _model("bf16")
+    img = torch.from_numpy(gold["img"]).cuda()
+    logits, pred = m.forward_windows(img)
+    torch.cuda.synchronize()
+    err = np.abs(logits.cpu().numpy()[:, :148] - gold["logits"]).max()
+    assert err < TOL["bf16"], "logits max abs err %g" % err
+
+
 def test_votes_and_confusion(gold):
     import model_oracle as mo
     from deepore_b200 import model
