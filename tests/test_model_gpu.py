@@ -172,3 +172,36 @@ def test_bundled_windows_end_to_end_call_set():
         assert np.array_equal(rec[rec["window"] < 2], want)
     merged = dc.merge_records(rec, g.win_qs[pick])
     assert merged.shape[0] <= rec.shape[0] and np.all(np.diff(merged["pos"]) >= 0)
+
+
+@pytest.mark.parametrize("precision", ["bf16x3", "bf16"])
+def test_bundled_call_set_all_windows_vs_reference(precision):
+    """All 260 windows of the bundled NA12878 fixture: CUDA encoder -> CUDA model -> dp_vote against the call set of the
+    UNMODIFIED reference model over the reference's own pileup images (tests/golden/bundled_calls_seed7.npz, made by
+    oracle/make_calls_golden.py).  Top-1 classes must agree wherever the reference's top-2 margin exceeds twice the logit
+    tolerance, votes wherever that holds for all three contributing (call, t) pairs."""
+    import golden_util as gu
+    from deepore_b200 import calls as dc, model, modelio
+    from deepore_b200.pileup import encode_windows
+    gold = np.load(os.path.join(os.path.dirname(GOLD), "bundled_calls_seed7.npz"))
+    g = gu.load("bundled_na12878")
+    nw = g.win_qs.shape[0]
+    img, rowpos, rowins, status = encode_windows(g.reads, g.win_qs, g.ref, g.ref_base)
+    assert (status.cpu().numpy() == 0).all() and np.array_equal(img.cpu().numpy(), g.img)
+    m = model.from_state(modelio.seeded_state(int(gold["seed"])), "cuda", precision)
+    _, pred = m.forward_windows(img, want_logits=False)
+    votes, _ = model.vote(pred.view(-1, 3), nw, img.shape[1], 3)
+    torch.cuda.synchronize()
+    pr = pred.view(nw, img.shape[1], 3)[:, :148].cpu().numpy()
+    votes = votes.cpu().numpy()
+    decisive = gold["margin"] > 2 * TOL[precision]                       # [nw, 148, 3]
+    assert np.array_equal(pr[decisive], gold["pred"][decisive])
+    dv = np.zeros(votes.shape, bool)
+    dv[:, 2:148] = decisive[:, 0:146, 2] & decisive[:, 1:147, 1] & decisive[:, 2:148, 0]
+    assert np.array_equal(votes[dv], gold["calls"][dv])
+    assert (votes[:, :2] == -1).all() and (votes[:, 148:] == -1).all()
+    frac = dv[:, 2:148].mean()
+    assert frac > (0.99 if precision == "bf16x3" else 0.8), "only %.3f of the votes are decisive" % frac
+    # the artefact itself: one record per scored, populated row
+    rec = dc.call_records(votes, rowpos.cpu().numpy(), rowins.cpu().numpy())
+    assert rec.shape[0] == int(((votes >= 0) & (rowpos.cpu().numpy() >= 0)).sum())

@@ -70,3 +70,19 @@ def test_fold_linearity_and_border_columns(state):
     _, y = mo.forward_image(state, img, calls=[0], return_y=True)
     yf = np.einsum("thswc,swc->th", fw.astype(np.float64), img.astype(np.float64)) + fb
     assert np.abs(yf - y[0]).max() < 1e-6
+
+
+def test_call_set_golden_is_consistent_with_the_logit_golden(gold):
+    """tests/golden/bundled_calls_seed7.npz (all 260 bundled windows through the unmodified reference model) and
+    model_seed7.npz (4 of them, with logits) come from separate runs of the reference: same classes, same votes, and
+    the stored margins are the logits' top-2 margins."""
+    import os
+    full = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "bundled_calls_seed7.npz"))
+    w = gold["windows"]
+    assert np.array_equal(full["pred"][w], gold["pred"])
+    assert np.array_equal(full["calls"][w], gold["calls"])
+    srt = np.sort(gold["logits"], axis=-1)
+    assert np.abs(full["margin"][w] - (srt[..., -1] - srt[..., -2])).max() < 1e-5
+    assert full["pred"].shape == (260, 148, 3) and full["calls"].shape == (260, 150)
+    assert ((full["calls"][:, 2:148] >= 0).all() and (full["calls"][:, :2] == -1).all()
+            and (full["calls"][:, 148:] == -1).all())
