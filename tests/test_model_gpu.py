@@ -205,3 +205,19 @@ def test_bundled_call_set_all_windows_vs_reference(precision):
     # the artefact itself: one record per scored, populated row
     rec = dc.call_records(votes, rowpos.cpu().numpy(), rowins.cpu().numpy())
     assert rec.shape[0] == int(((votes >= 0) & (rowpos.cpu().numpy() >= 0)).sum())
+
+
+def test_batch_composition_does_not_change_a_window(gold):
+    """Size-independent property (SURVEY 8d config 4 sweeps the call batch): a window's logits are bit-identical whatever
+    batch it is forwarded in -- alone (150 rows: one partial 256-row tile), with others (rows straddling tile and chunk
+    boundaries), or repeated up to several thousand rows.  (Calls 148 and 149 of a window read the first rows of the NEXT window and are never scored.)"""
+    m = _model("bf16")
+    img = torch.from_numpy(gold["img"]).cuda()                       # 4 windows
+    base, bpred = m.forward_windows(img)
+    for i in range(img.shape[0]):
+        one, opred = m.forward_windows(img[i:i + 1])
+        assert torch.equal(one[0, :148], base[i, :148]) and torch.equal(opred[0, :148], bpred[i, :148])
+    rep = img.repeat(9, 1, 1, 1)[:35]                                # 35 windows = 5250 rows, not a multiple of 256
+    big, _ = m.forward_windows(rep)
+    for j in range(35):
+        assert torch.equal(big[j, :148], base[j % 4, :148]), "window %d of the repeated batch differs" % j
