@@ -879,7 +879,9 @@ constexpr int V3_WARPS = V3_THREADS / 32;
 constexpr int V3_MAXSLOT = 128;       // most read slots per batch (the pool may hold fewer)
 // One shared-memory pool, carved per window: planes [slots][LS] words from the bottom (LS = drawn columns rounded up
 // to 16), image-row codes [rows][RS] bytes from the top (RS = deepest row rounded up to whole quads).
-constexpr int V3_POOL_BYTES = 36352;
+constexpr int V3_POOL_BYTES = 36352;  // 4 CTAs per SM (64 registers); deep windows
+constexpr int V3_POOL_SMALL = 24576;  // 5 CTAs per SM (48 registers): +3-4 % on 30x windows, -10 % on 100x ones (more of
+                                      // them need a second batch of read slots) -- picked per call by the bases per window
 constexpr int V3_CS = 208;            // column stride of the planes (>= window length)
 constexpr int V3_MAXC = 192;          // surviving reads per window
 constexpr int V3_MD = 48;             // staged M/D ops per read
@@ -1130,7 +1132,8 @@ __device__ __forceinline__ void v3_finish_row(const V3S &S, int y, int tot, bool
     }
 }
 
-__global__ void __launch_bounds__(V3_THREADS, 4)
+template <int MINB, int POOL_BYTES>
+__global__ void __launch_bounds__(V3_THREADS, MINB)
 encode_windows_v3_kernel(EncArgs a, int *__restrict__ fb_count, int *__restrict__ fb_list, int emit_mode,
                          unsigned long long *__restrict__ dbg) {
     extern __shared__ __align__(16) uint8_t smem[];
@@ -1146,7 +1149,7 @@ encode_windows_v3_kernel(EncArgs a, int *__restrict__ fb_count, int *__restrict_
     // ---- shared memory carve-up (16-byte aligned sections first)
     uint8_t *p = smem;
     V3S S;
-    uint8_t *s_pool0 = p;                          p += V3_POOL_BYTES;
+    uint8_t *s_pool0 = p;                          p += POOL_BYTES;
     S.pw = (uint32_t *)s_pool0;
     S.q = s_pool0;                                 // placed at the top of the pool once the row stride is known
     S.cnt = (uint32_t *)p;                         p += 4 * (NCAT * 256 / 2);
@@ -1286,7 +1289,7 @@ encode_windows_v3_kernel(EncArgs a, int *__restrict__ fb_count, int *__restrict_
     const int nrows = min(S.misc[4], H);
     // plane geometry for this window: stride = drawn columns rounded up, as many read slots as the pool holds
     const int LS = max(16, (Lgen + 15) & ~15);
-    int slots = min(V3_MAXSLOT, V3_POOL_BYTES / (4 * LS));   // counting pass: the whole pool is planes
+    int slots = min(V3_MAXSLOT, POOL_BYTES / (4 * LS));   // counting pass: the whole pool is planes
     int nb = (ncand + slots - 1) / slots;
     // placement runs on G slot groups per column in parallel (thread = group * LS + column): counts are kept per group
     const int G = nb == 1 ? max(1, min(4, V3_THREADS / LS)) : 1;
@@ -1367,11 +1370,11 @@ encode_windows_v3_kernel(EncArgs a, int *__restrict__ fb_count, int *__restrict_
     if (walker && wg > 0) { run_lo = s_base[(wg - 1) * 2 * LS + wc]; run_hi = s_base[((wg - 1) * 2 + 1) * LS + wc]; }
     const int RS = (S.misc[9] + 4) & ~3;             // pixel 0 + entries, rounded up to whole quads
     const int qbytes = (nrows * RS + 15) & ~15;
-    S.q = s_pool0 + V3_POOL_BYTES - qbytes;
+    S.q = s_pool0 + POOL_BYTES - qbytes;
     // the counting pass's planes can be placed from directly when every read was in them and they clear the rows
-    const bool multi = !(nb == 1 && ncand * 4 * LS + qbytes <= V3_POOL_BYTES);
+    const bool multi = !(nb == 1 && ncand * 4 * LS + qbytes <= POOL_BYTES);
     if (multi) {
-        slots = min(V3_MAXSLOT, (V3_POOL_BYTES - qbytes) / (4 * LS));
+        slots = min(V3_MAXSLOT, (POOL_BYTES - qbytes) / (4 * LS));
         if (slots < 8 && slots < ncand) { if (tid == 0) S.misc[0] = 1; slots = 8; }
         nb = (ncand + slots - 1) / slots;
     }
@@ -1457,10 +1460,10 @@ encode_windows_v3_kernel(EncArgs a, int *__restrict__ fb_count, int *__restrict_
 #undef V3_MARK
 }
 
-static size_t encoder_v3_smem_bytes(const dp_encode_params *p) {
+static size_t encoder_v3_smem_bytes(const dp_encode_params *p, int pool_bytes) {
     (void)p;
     size_t s = 0;
-    s += V3_POOL_BYTES;
+    s += pool_bytes;
     s += 4 * (NCAT * 256 / 2) + 4 * 256;                                   // cnt, rowcg
     s += sizeof(Md3) * V3_WARPS * V3_MD;
     s += 4 * 256 * 2 + V3_POOL + 4 * V3_MAXC * 2 + 4 * (V3_CS + 8) + 4 * V3_CS + 4 * 32;
@@ -1614,7 +1617,11 @@ int dp_encode_windows(const dp_reads *reads, int32_t n_windows, const int32_t *w
     // fast path (v3) when the geometry fits its shared-memory planes; windows it cannot take are listed for v1
     static int force_v1 = -1;
     if (force_v1 < 0) { const char *e = getenv("DP_ENCODER"); force_v1 = (e && !strcmp(e, "v1")) ? 1 : 0; }
-    const size_t smem3 = dp::encoder_v3_smem_bytes(p);
+    // shallow windows (30x long reads: ~3 k read bases per window at stride 100) run 5 CTAs per SM on a smaller pool
+    static int force_pool = -1;                                /* DP_ENC_POOL = small | large overrides the choice */
+    if (force_pool < 0) { const char *e = getenv("DP_ENC_POOL"); force_pool = !e ? 0 : !strcmp(e, "small") ? 1 : !strcmp(e, "large") ? 2 : 0; }
+    const bool small_pool = force_pool == 1 || (force_pool == 0 && reads->n_bases < (int64_t)6000 * n_windows);
+    const size_t smem3 = dp::encoder_v3_smem_bytes(p, small_pool ? dp::V3_POOL_SMALL : dp::V3_POOL_BYTES);
     const bool use_v3 = !force_v1 && dp::g_lut_flat && L <= dp::V3_CS && p->window_cutoff <= 256 &&
                         p->coverage_cutoff >= 8 && p->coverage_cutoff <= 256 && smem3 <= 100 * 1024;
     if (!use_v3) {
@@ -1624,11 +1631,17 @@ int dp_encode_windows(const dp_reads *reads, int32_t n_windows, const int32_t *w
         return DP_OK;
     }
     DP_CUDA_CHECK(cudaMemsetAsync(fb, 0, sizeof(int), st));
-    DP_CUDA_CHECK(cudaFuncSetAttribute(dp::encode_windows_v3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem3));
+    DP_CUDA_CHECK(cudaFuncSetAttribute(dp::encode_windows_v3_kernel<4, dp::V3_POOL_BYTES>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)dp::encoder_v3_smem_bytes(p, dp::V3_POOL_BYTES)));
+    DP_CUDA_CHECK(cudaFuncSetAttribute(dp::encode_windows_v3_kernel<5, dp::V3_POOL_SMALL>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)dp::encoder_v3_smem_bytes(p, dp::V3_POOL_SMALL)));
     static int emit_mode = -1;                                 /* DP_ENC_EMIT=stg: plain stores instead of bulk copies */
     if (emit_mode < 0) { const char *e = getenv("DP_ENC_EMIT"); emit_mode = (e && !strcmp(e, "stg")) ? 1 : 0; }
     if (timing) cudaMemsetAsync(dbg, 0, 256, st);
-    dp::encode_windows_v3_kernel<<<n_windows, dp::V3_THREADS, smem3, st>>>(a, fb, fb + 64, emit_mode, timing ? dbg : nullptr);
+    if (small_pool)
+        dp::encode_windows_v3_kernel<5, dp::V3_POOL_SMALL><<<n_windows, dp::V3_THREADS, smem3, st>>>(a, fb, fb + 64, emit_mode, timing ? dbg : nullptr);
+    else
+        dp::encode_windows_v3_kernel<4, dp::V3_POOL_BYTES><<<n_windows, dp::V3_THREADS, smem3, st>>>(a, fb, fb + 64, emit_mode, timing ? dbg : nullptr);
     DP_CUDA_CHECK(cudaGetLastError());
     if (timing) cudaEventRecord(ev[3], st);
     dp::encode_windows_kernel<<<n_windows, dp::ENC_THREADS, smem, st>>>(a, fb, fb + 64);
