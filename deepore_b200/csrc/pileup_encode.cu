@@ -1216,6 +1216,7 @@ encode_windows_v3_kernel(EncArgs a, int *__restrict__ fb_count, int *__restrict_
     for (int cb = lo; cb < hi; cb += V3_THREADS) {
         const int r = cb + tid;
         const bool keep = r < hi && a.R.pos[r] < qe && a.endk[r] > qs;
+        if (keep) asm volatile("prefetch.global.L1 [%0];" ::"l"(a.info + r));      // read by the digest below
         const unsigned bal = __ballot_sync(0xffffffffu, keep);
         __syncthreads();
         if (lane == 0) s_wsum[warp] = __popc(bal);
@@ -1243,6 +1244,12 @@ encode_windows_v3_kernel(EncArgs a, int *__restrict__ fb_count, int *__restrict_
             jc = __ldg(a.ckpt + (ri->c0 >> 1) + r + (min(T, ri->span) >> k));
         }
         S.j0[tid] = jc;
+        if ((flags & RI_CLEAN) && jc < ri->nops) {    // the scan and generate passes start here: pull the lines towards L1
+            const long long c0 = ri->c0;
+            asm volatile("prefetch.global.L1 [%0];" ::"l"(a.R.cigar + c0 + jc));
+            asm volatile("prefetch.global.L1 [%0];" ::"l"(a.RP + c0 + r + jc));
+            asm volatile("prefetch.global.L1 [%0];" ::"l"(a.QP + c0 + jc));
+        }
     }
     __syncthreads();
     if (S.misc[0]) ncand = 0;                         // bail out early: the exact kernel takes the window
