@@ -227,3 +227,56 @@ class AlignmentFile(object):
 
     def close(self):
         pass
+
+
+# ----------------------------------------------------------------------------------------------------
+# VariantFile: what /root/reference/src/utils/pileupGenerator.py:40-62,104-112 touches (fetch(region=), str(rec),
+# rec.qual / alleles / ref / start / stop / pos / chrom).  Semantics from the vendored htslib the real pysam wraps:
+# QUAL "." -> missing (dep/htslib/vcf.c: bcf_float_set_missing -> pysam None); ALT "." -> no alternate allele;
+# rlen = INFO/END - POS + 1 when END is present, else len(REF) (dep/htslib/vcf.c, vcf_parse: "END" handling), and
+# pysam's rec.start = POS - 1, rec.stop = start + rlen.
+class VariantRecord(object):
+    def __init__(self, line):
+        self._line = line.rstrip("\n")
+        f = self._line.split("\t")
+        self.chrom = f[0]
+        self.pos = int(f[1])
+        self.start = self.pos - 1
+        self.id = None if f[2] == "." else f[2]
+        self.ref = f[3]
+        alts = () if f[4] == "." else tuple(f[4].split(","))
+        self.alts = alts or None
+        self.alleles = (self.ref,) + alts
+        self.qual = None if f[5] == "." else float(f[5])
+        rlen = len(self.ref)
+        for kv in f[7].split(";"):
+            if kv.startswith("END="):
+                rlen = int(kv[4:]) - self.pos + 1
+        self.rlen = rlen
+        self.stop = self.start + rlen
+
+    def __str__(self):
+        return self._line + "\n"
+
+
+class VariantFile(object):
+    def __init__(self, path, mode="r"):
+        op = gzip.open if str(path).endswith(".gz") else open
+        with op(path, "rt") as fh:
+            self._records = [VariantRecord(ln) for ln in fh if ln.strip() and not ln.startswith("#")]
+
+    def fetch(self, contig=None, start=None, stop=None, region=None):
+        name = region if region is not None else contig
+        lo, hi = start, stop
+        if name is not None and ":" in name:
+            name, span = name.split(":", 1)
+            a, b = span.replace(",", "").split("-")
+            lo, hi = int(a) - 1, int(b)
+        for r in self._records:
+            if name is not None and r.chrom != name:
+                continue
+            if lo is not None and r.stop <= lo:
+                continue
+            if hi is not None and r.start >= hi:
+                continue
+            yield r

@@ -18,3 +18,32 @@ def load(name):
     extra = {k: z[k] for k in z.files}
     return SimpleNamespace(reads=rb, ref=z["ref"], ref_base=int(z["ref_base"]), win_qs=z["win_qs"],
                            img=z["img"], status=z["status"], labels=z["labels"], z=extra)
+
+
+def write_bam(path, rb, contig="chr3", contig_len=9_000_000):
+    """Uncompressed-member BAM of a ReadBatch (record layout of dep/htslib/htslib/sam.h:154-195; names 'r', no aux fields):
+    enough for `reads.BamFile`, which inflates the whole stream with gzip."""
+    import gzip
+    import struct
+    parts = [b"BAM\1", struct.pack("<i", 0), struct.pack("<i", 1),
+             struct.pack("<i", len(contig) + 1), contig.encode() + b"\0", struct.pack("<i", contig_len)]
+    cig = rb.cigar.astype("<u4")
+    for i in range(rb.n_reads):
+        c = cig[rb.cigar_off[i]:rb.cigar_off[i + 1]].tobytes()
+        s = rb.seq4[rb.seq_off[i]:rb.seq_off[i + 1]].tobytes()
+        q = rb.qual[rb.qual_off[i]:rb.qual_off[i + 1]].tobytes()
+        body = struct.pack("<iiBBHHHiiii", 0, int(rb.pos[i]), 2, int(rb.mapq[i]), 0, len(c) // 4, int(rb.flag[i]),
+                           int(rb.l_seq[i]), -1, -1, 0) + b"r\0" + c + s + q
+        parts.append(struct.pack("<i", len(body)))
+        parts.append(body)
+    with gzip.open(path, "wb", compresslevel=1) as fh:
+        fh.write(b"".join(parts))
+
+
+def write_fasta(path, ref, ref_base, contig="chr3", width=60):
+    """FASTA whose contig is `ref` placed at 0-based `ref_base`, N before it."""
+    s = b"N" * int(ref_base) + bytes(ref)
+    with open(path, "wb") as fh:
+        fh.write(b">" + contig.encode() + b"\n")
+        for i in range(0, len(s), width):
+            fh.write(s[i:i + width] + b"\n")

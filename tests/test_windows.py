@@ -1,0 +1,109 @@
+"""Window / label producer (deepore_b200/windows.py) against the unmodified pileupGenerator.py of the reference
+(tests/golden/bundled_windows.npz, made by oracle/make_windows_golden.py): record dictionary, window list, label drafts and
+insert lengths on the CPU; the batched CUDA driver (PNG + summary CSV) on the GPU."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+import golden_util as gu
+from deepore_b200 import windows
+
+VCF = os.path.join(gu.GOLD, "bundled_confident.vcf")
+FULL_VCF = "/root/reference/data/vcf_NA12878_S1.small.vcf"
+
+
+@pytest.fixture()
+def gold():
+    windows.allVariantRecord.clear()
+    yield np.load(os.path.join(gu.GOLD, "bundled_windows.npz"))
+    windows.allVariantRecord.clear()
+
+
+@pytest.mark.parametrize("vcf", [VCF, FULL_VCF, FULL_VCF + ".gz"])
+def test_record_dictionary_and_labels_match_reference(gold, vcf):
+    if not os.path.isfile(vcf):
+        pytest.skip("the full bundled VCF only exists in the build container")
+    d = windows.populateRecordDictionary("3", vcf)
+    keys = np.array(sorted(d), np.int64)
+    assert np.array_equal(keys, gold["record_keys"])
+    vals = np.array([[d[k][0], d[k][1] or 0, d[k][2] or 0] for k in keys], np.int32)
+    assert np.array_equal(vals, gold["record_vals"])
+    recs = windows.qualifying_records("3", vcf)
+    assert [r.pos for r in recs] == gold["vcf_pos"].tolist()
+    for i, r in enumerate(recs):
+        lab, ins, dele = windows.getLabel(r.pos - 100 - 1, r.pos + 100)
+        assert lab == str(gold["label_draft"][i])
+        assert {str(k): v for k, v in ins.items()} == json.loads(str(gold["insert_lengths"][i]))
+        assert {str(k): v for k, v in dele.items()} == json.loads(str(gold["delete_lengths"][i]))
+
+
+def test_genotype_classes_and_record_fields():
+    assert windows.getClassForGenotype(["0", "0"]) == 1
+    assert windows.getClassForGenotype([".", "."]) == 1
+    assert windows.getClassForGenotype(["0", "1"]) == 2
+    assert windows.getClassForGenotype(["1", "2"]) == 2
+    assert windows.getClassForGenotype(["1", "1"]) == 3
+    r = windows.VcfRecord("chr3\t100\t.\tAT\tA,ATTT\t80.5\tPASS\tDP=3\tGT:DP\t1|2:7\n")
+    assert (r.start, r.stop, r.alleles, r.qual) == (99, 101, ("AT", "A", "ATTT"), 80.5)
+    assert windows.getGTField(r) == ["1", "2"]
+    assert windows.getGTField(windows.VcfRecord("chr3\t5\t.\tA\tC\t.\t.\t.\tGT\t0\\1\n")) == ["0", "1"]
+    b = windows.VcfRecord("chr3\t99914\t.\tA\t.\t.\tPASS\tEND=100026;BLOCKAVG_min30p3a\tGT:DP\t0/0:50\n")
+    assert (b.qual, b.alleles, b.start, b.stop) == (None, ("A",), 99913, 100026)
+
+
+def test_insert_and_delete_runs(tmp_path):
+    """An insertion allele marks its anchor with the allele length; a deletion spans len(REF) positions and opens one run."""
+    windows.allVariantRecord.clear()
+    p = tmp_path / "t.vcf"
+    p.write_text("#CHROM\tPOS\tID\tREF\tALT\tQUAL\tFILTER\tINFO\tFORMAT\tS\n"
+                 "chr3\t1010\t.\tA\tACGT\t99\tPASS\t.\tGT\t0/1\n"
+                 "chr3\t1020\t.\tGTTT\tG\t99\tPASS\t.\tGT\t1/1\n"
+                 "chr3\t1030\t.\tC\tT\t12\tPASS\t.\tGT\t1/1\n")
+    try:
+        d = windows.populateRecordDictionary("3", str(p))
+        assert d[1009] == (2, 4, None)
+        assert [d[k] for k in range(1019, 1023)] == [(3, None, 1)] * 4          # longest CALLED allele is "G"
+        assert 1029 not in d                                                      # QUAL 12
+        lab, ins, dele = windows.getLabel(1000, 1030)
+        assert lab == "1" * 9 + "2" + "1" * 9 + "3333" + "1" * 7
+        assert ins == {9: 4} and dele == {19: 1, 20: 1, 21: 1, 22: 1}
+        assert [r.pos for r in windows.qualifying_records("3", str(p))] == [1010, 1020]
+        assert [r.pos for r in windows.read_vcf(str(p), "chr3:1020-1025")] == [1020]
+    finally:
+        windows.allVariantRecord.clear()
+
+
+@pytest.mark.gpu
+def test_batched_driver_writes_the_reference_files(gold, tmp_path):
+    """generatePileupBasedonVCF on the bundled data (BAM and FASTA rebuilt from the committed arrays): the summary CSV lines, the
+    file names and every PNG pixel equal what the unmodified reference driver wrote."""
+    from PIL import Image
+    g = gu.load("bundled_na12878")
+    bam, fa = str(tmp_path / "b.bam"), str(tmp_path / "r.fa")
+    gu.write_bam(bam, g.reads)
+    gu.write_fasta(fa, g.ref, g.ref_base)
+    out = str(tmp_path) + "/"
+    n = windows.generatePileupBasedonVCF("3", bam, fa, VCF, out, 100)
+    assert n == 260
+    lines = [ln.rstrip("\n").split(",") for ln in open(out + "summary-3.csv")]
+    assert [os.path.basename(p) for p, _ in lines] == [str(x) for x in gold["png_name"]]
+    assert [lab for _, lab in lines] == [str(x) for x in gold["label_out"]]
+    for i, (p, _) in enumerate(lines):
+        assert os.path.isabs(p)
+        assert np.array_equal(np.array(Image.open(p)), g.img[i]), "window %d" % i
+
+
+@pytest.mark.gpu
+def test_labelled_batch_any_order(gold):
+    """Window centres in arbitrary order come back in the caller's order, labels included."""
+    g = gu.load("bundled_na12878")
+    pick = [200, 3, 77, 3, 259, 0]
+    pos = [int(gold["vcf_pos"][k]) - 1 for k in pick]
+    drafts = [str(gold["label_draft"][k]) for k in pick]
+    ins = [{int(a): b for a, b in json.loads(str(gold["insert_lengths"][k])).items()} for k in pick]
+    img, labels, rowpos, rowins = windows.encode_labelled_batch(g.reads, g.ref, g.ref_base, pos, drafts, ins)
+    for a, k in enumerate(pick):
+        assert np.array_equal(img[a], g.img[k])
+        assert labels[a] == str(gold["label_out"][k])
