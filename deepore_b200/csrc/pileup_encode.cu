@@ -882,6 +882,8 @@ constexpr int V3_MAXSLOT = 128;       // most read slots per batch (the pool may
 constexpr int V3_POOL_BYTES = 36352;  // 4 CTAs per SM (64 registers); deep windows
 constexpr int V3_POOL_SMALL = 24576;  // 5 CTAs per SM (48 registers): +3-4 % on 30x windows, -10 % on 100x ones (more of
                                       // them need a second batch of read slots) -- picked per call by the bases per window
+constexpr int V3_POOL_DEEP = 55296;   // 3 CTAs per SM: 100x windows (~100 read slots x 48 columns + 150 rows x ~110 codes = 36-40 KB) keep the planes of
+                                      // the counting pass for placement instead of generating every read a second time
 constexpr int V3_CS = 208;            // column stride of the planes (>= window length)
 constexpr int V3_MAXC = 192;          // surviving reads per window
 constexpr int V3_MD = 48;             // staged M/D ops per read
@@ -1625,10 +1627,11 @@ int dp_encode_windows(const dp_reads *reads, int32_t n_windows, const int32_t *w
     static int force_v1 = -1;
     if (force_v1 < 0) { const char *e = getenv("DP_ENCODER"); force_v1 = (e && !strcmp(e, "v1")) ? 1 : 0; }
     // shallow windows (30x long reads: ~3 k read bases per window at stride 100) run 5 CTAs per SM on a smaller pool
-    static int force_pool = -1;                                /* DP_ENC_POOL = small | large overrides the choice */
-    if (force_pool < 0) { const char *e = getenv("DP_ENC_POOL"); force_pool = !e ? 0 : !strcmp(e, "small") ? 1 : !strcmp(e, "large") ? 2 : 0; }
+    static int force_pool = -1;                                /* DP_ENC_POOL = small | large | deep overrides the choice */
+    if (force_pool < 0) { const char *e = getenv("DP_ENC_POOL"); force_pool = !e ? 0 : !strcmp(e, "small") ? 1 : !strcmp(e, "large") ? 2 : !strcmp(e, "deep") ? 3 : 0; }
     const bool small_pool = force_pool == 1 || (force_pool == 0 && reads->n_bases < (int64_t)6000 * n_windows);
-    const size_t smem3 = dp::encoder_v3_smem_bytes(p, small_pool ? dp::V3_POOL_SMALL : dp::V3_POOL_BYTES);
+    const bool deep_pool = force_pool == 3 || (force_pool == 0 && reads->n_bases >= (int64_t)8000 * n_windows);
+    const size_t smem3 = dp::encoder_v3_smem_bytes(p, small_pool ? dp::V3_POOL_SMALL : deep_pool ? dp::V3_POOL_DEEP : dp::V3_POOL_BYTES);
     const bool use_v3 = !force_v1 && dp::g_lut_flat && L <= dp::V3_CS && p->window_cutoff <= 256 &&
                         p->coverage_cutoff >= 8 && p->coverage_cutoff <= 256 && smem3 <= 100 * 1024;
     if (!use_v3) {
@@ -1642,11 +1645,15 @@ int dp_encode_windows(const dp_reads *reads, int32_t n_windows, const int32_t *w
                                        (int)dp::encoder_v3_smem_bytes(p, dp::V3_POOL_BYTES)));
     DP_CUDA_CHECK(cudaFuncSetAttribute(dp::encode_windows_v3_kernel<5, dp::V3_POOL_SMALL>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        (int)dp::encoder_v3_smem_bytes(p, dp::V3_POOL_SMALL)));
+    DP_CUDA_CHECK(cudaFuncSetAttribute(dp::encode_windows_v3_kernel<3, dp::V3_POOL_DEEP>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)dp::encoder_v3_smem_bytes(p, dp::V3_POOL_DEEP)));
     static int emit_mode = -1;                                 /* DP_ENC_EMIT=stg: plain stores instead of bulk copies */
     if (emit_mode < 0) { const char *e = getenv("DP_ENC_EMIT"); emit_mode = (e && !strcmp(e, "stg")) ? 1 : 0; }
     if (timing) cudaMemsetAsync(dbg, 0, 256, st);
     if (small_pool)
         dp::encode_windows_v3_kernel<5, dp::V3_POOL_SMALL><<<n_windows, dp::V3_THREADS, smem3, st>>>(a, fb, fb + 64, emit_mode, timing ? dbg : nullptr);
+    else if (deep_pool)
+        dp::encode_windows_v3_kernel<3, dp::V3_POOL_DEEP><<<n_windows, dp::V3_THREADS, smem3, st>>>(a, fb, fb + 64, emit_mode, timing ? dbg : nullptr);
     else
         dp::encode_windows_v3_kernel<4, dp::V3_POOL_BYTES><<<n_windows, dp::V3_THREADS, smem3, st>>>(a, fb, fb + 64, emit_mode, timing ? dbg : nullptr);
     DP_CUDA_CHECK(cudaGetLastError());

@@ -23,7 +23,8 @@ except Exception:
     PEAK = 6650.0
 NW = 4096
 out = []
-for cov in (30, 100):
+COVS = [int(x) for x in sys.argv[1:]] or [30, 100]
+for cov in COVS:
     ref = synth.random_reference(NW * 100 * 2 + 40_000, seed=1)
     rb = synth.simulate_reads(ref, coverage=cov, seed=2)
     shards = []
