@@ -1626,11 +1626,12 @@ int dp_encode_windows(const dp_reads *reads, int32_t n_windows, const int32_t *w
     // fast path (v3) when the geometry fits its shared-memory planes; windows it cannot take are listed for v1
     static int force_v1 = -1;
     if (force_v1 < 0) { const char *e = getenv("DP_ENCODER"); force_v1 = (e && !strcmp(e, "v1")) ? 1 : 0; }
-    // shallow windows (30x long reads: ~3 k read bases per window at stride 100) run 5 CTAs per SM on a smaller pool
+    // shallow windows (30x long reads: ~3 k read bases per window at stride 100) run 5 CTAs per SM on a smaller pool, deep ones
+    // 3 CTAs on a larger one; thresholds from a coverage sweep (45 / 60 / 75 / 90x: the 4-CTA build wins at 45-75x, the 3-CTA one from 90x)
     static int force_pool = -1;                                /* DP_ENC_POOL = small | large | deep overrides the choice */
     if (force_pool < 0) { const char *e = getenv("DP_ENC_POOL"); force_pool = !e ? 0 : !strcmp(e, "small") ? 1 : !strcmp(e, "large") ? 2 : !strcmp(e, "deep") ? 3 : 0; }
-    const bool small_pool = force_pool == 1 || (force_pool == 0 && reads->n_bases < (int64_t)6000 * n_windows);
-    const bool deep_pool = force_pool == 3 || (force_pool == 0 && reads->n_bases >= (int64_t)8000 * n_windows);
+    const bool small_pool = force_pool == 1 || (force_pool == 0 && reads->n_bases < (int64_t)4000 * n_windows);
+    const bool deep_pool = force_pool == 3 || (force_pool == 0 && reads->n_bases >= (int64_t)8700 * n_windows);
     const size_t smem3 = dp::encoder_v3_smem_bytes(p, small_pool ? dp::V3_POOL_SMALL : deep_pool ? dp::V3_POOL_DEEP : dp::V3_POOL_BYTES);
     const bool use_v3 = !force_v1 && dp::g_lut_flat && L <= dp::V3_CS && p->window_cutoff <= 256 &&
                         p->coverage_cutoff >= 8 && p->coverage_cutoff <= 256 && smem3 <= 100 * 1024;
