@@ -49,7 +49,7 @@ def build(force=False, verbose=False):
         fh.write("\n".join(log))
     if verbose:
         print("\n".join(log))
-    cmd = [nvcc, "-shared", "-o", LIB + ".tmp"] + objs + ["-lcudart", "-lcuda"]
+    cmd = [nvcc, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", LIB + ".tmp"] + objs + ["-lcudart", "-lcuda"]
     subprocess.check_call(cmd)
     os.replace(LIB + ".tmp", LIB)
     return LIB
