@@ -77,3 +77,47 @@ def read_tsv(path: str):
             chroms.append(c)
             rows.append((int(win), int(row), int(pos) - 1, int(ins), int(call)))
     return chroms, np.array(rows, dtype=RECORD) if rows else np.empty(0, dtype=RECORD)
+
+
+# Classes as the reference's labels define them (pileupGenerator.py:23-32 getClassForGenotype; '0' is the pad label of
+# Pileup.py:374-378): 0 = no label, 1 = homozygous reference, 2 = heterozygous, 3 = homozygous alternate.  The reference
+# model is built with class_n = 3 (model.py:60), so class 3 never comes out of it; the map is a parameter for that reason.
+CLASS_GENOTYPES = {1: "0/0", 2: "0/1", 3: "1/1"}
+
+
+def write_vcf(path: str, chrom: str, rec: np.ndarray, ref: bytes, ref_base: int = 0, sample: str = "SAMPLE",
+              class_genotypes: Optional[dict] = None, emit_hom_ref: bool = False) -> int:
+    """Sites-only VCF 4.2 of a merged call set: one line per record whose class maps to a genotype (hom-ref lines only
+    with `emit_hom_ref`).  The model predicts a zygosity class per image row, not an allele (model.py:154-155,
+    test.py:68-89), so ALT is the symbolic <NON_REF>; rows inside an insertion (ins = k > 0) are written at their anchor
+    position with ALT <INS> and INFO INSROW=k.  `ref`: upper-case reference bytes, `ref[p - ref_base]` = base at 0-based p.
+    Records must be sorted by (pos, ins) (merge_records' order); returns the number of lines written."""
+    gmap = CLASS_GENOTYPES if class_genotypes is None else class_genotypes
+    if rec.shape[0] > 1:
+        k = rec["pos"].astype(np.int64) * (1 << 20) + rec["ins"]
+        if np.any(k[1:] < k[:-1]):
+            raise ValueError("records must be sorted by (pos, ins); run merge_records first")
+    n = 0
+    with open(path, "w") as f:
+        f.write("##fileformat=VCFv4.2\n##source=deepore_b200\n")
+        f.write('##ALT=<ID=NON_REF,Description="Any alternate allele (the model scores zygosity, not alleles)">\n')
+        f.write('##ALT=<ID=INS,Description="Row inside an insertion after POS">\n')
+        f.write('##INFO=<ID=INSROW,Number=1,Type=Integer,Description="Index of the inserted base the row stands for">\n')
+        f.write('##INFO=<ID=CLASS,Number=1,Type=Integer,Description="Class voted for the row (test.py:68-89)">\n')
+        f.write('##FORMAT=<ID=GT,Number=1,Type=String,Description="Genotype of the voted class">\n')
+        f.write("#CHROM\tPOS\tID\tREF\tALT\tQUAL\tFILTER\tINFO\tFORMAT\t%s\n" % sample)
+        for x in rec:
+            c = int(x["call"])
+            gt = gmap.get(c)
+            if gt is None or (not emit_hom_ref and set(gt.replace("|", "/").split("/")) == {"0"}):
+                continue
+            p = int(x["pos"])
+            i = p - ref_base
+            if i < 0 or i >= len(ref):
+                raise IndexError("position %d outside the reference slice [%d, %d)" % (p, ref_base, ref_base + len(ref)))
+            rb = chr(ref[i]) if isinstance(ref, (bytes, bytearray, np.ndarray)) else ref[i]
+            ins = int(x["ins"])
+            alt, info = ("<INS>", "CLASS=%d;INSROW=%d" % (c, ins)) if ins > 0 else ("<NON_REF>", "CLASS=%d" % c)
+            f.write("%s\t%d\t.\t%s\t%s\t.\t.\t%s\tGT\t%s\n" % (chrom, p + 1, rb, alt, info, gt))
+            n += 1
+    return n

@@ -69,3 +69,30 @@ def test_tsv_round_trip(tmp_path):
     assert dc.read_tsv(p)[1].shape[0] == n + 2
     k = dc.write_tsv(p, "chr3", rec, only_class=2)
     assert k == int((rec["call"] == 2).sum())
+
+
+def test_vcf_writer_sites_and_genotypes(tmp_path):
+    calls, rowpos, rowins, win_qs = _toy()
+    rec = dc.merge_records(dc.call_records(calls, rowpos, rowins), win_qs)
+    ref = (b"ACGT" * 60)                                 # positions 1000..1239
+    p = str(tmp_path / "calls.vcf")
+    n = dc.write_vcf(p, "chr3", rec, ref, ref_base=1000, sample="NA12878")
+    body = [ln.rstrip("\n").split("\t") for ln in open(p) if not ln.startswith("#")]
+    want = [x for x in rec if int(x["call"]) in (2, 3)]  # hom-ref (1) and unlabelled (0) rows are not variant sites
+    assert n == len(body) == len(want) > 0
+    for ln, x in zip(body, want):
+        assert ln[0] == "chr3" and int(ln[1]) == int(x["pos"]) + 1
+        assert ln[3] == chr(ref[int(x["pos"]) - 1000])
+        assert ln[4] == ("<INS>" if x["ins"] > 0 else "<NON_REF>")
+        assert ("INSROW=%d" % x["ins"] in ln[7]) == bool(x["ins"] > 0)
+        assert ln[9] == dc.CLASS_GENOTYPES[int(x["call"])]
+    head = [ln for ln in open(p) if ln.startswith("#")]
+    assert head[0].startswith("##fileformat=VCFv4.2") and head[-1].rstrip("\n").endswith("FORMAT\tNA12878")
+    # hom-ref lines on request; a custom class map; unsorted records and positions outside the slice are refused
+    assert dc.write_vcf(p, "chr3", rec, ref, 1000, emit_hom_ref=True) == int(np.isin(rec["call"], (1, 2, 3)).sum())
+    assert dc.write_vcf(p, "chr3", rec, ref, 1000, class_genotypes={0: "1/1"}) == int((rec["call"] == 0).sum())
+    import pytest
+    with pytest.raises(ValueError):
+        dc.write_vcf(p, "chr3", rec[::-1], ref, 1000)
+    with pytest.raises(IndexError):
+        dc.write_vcf(p, "chr3", rec, ref, 1100)
