@@ -81,6 +81,14 @@ def lib():
     L.dp_gemm_bf16.restype = C.c_int
     L.dp_gemm_bf16.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32,
                                C.c_int64, C.c_int64, C.c_int64, C.c_int32, C.c_void_p]
+    L.dp_bgzf_index.restype = C.c_int64
+    L.dp_bgzf_index.argtypes = [C.c_void_p, C.c_int64, C.c_int64] + [C.c_void_p] * 5
+    L.dp_bgzf_inflate.restype = C.c_int
+    L.dp_bgzf_inflate.argtypes = [C.c_void_p, C.c_int64] + [C.c_void_p] * 7
+    L.dp_bam_scan.restype = C.c_int
+    L.dp_bam_scan.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_int32, C.c_int64] + [C.c_void_p] * 6
+    L.dp_bam_extract.restype = C.c_int
+    L.dp_bam_extract.argtypes = [C.c_void_p, C.c_int64] + [C.c_void_p] * 12
     _lib = L
     return L
 

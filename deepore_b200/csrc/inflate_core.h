@@ -1,0 +1,228 @@
+/* DEFLATE (RFC 1951) decoder core of the device-side BGZF stage.
+ *
+ * Replaces, per BGZF block, what the reference's host stage does through zlib: dep/htslib/bgzf.c:456-499
+ * (inflate_block: inflateInit2(-15) / inflate(Z_FINISH) on the block payload) -- zlib itself is a third-party
+ * dependency that is not under /root/reference; the algorithm restated here is the published RFC 1951 one
+ * (stored / fixed / dynamic blocks, canonical Huffman codes decoded by the count/first-code walk).
+ *
+ * One decoder instance = one thread decoding one BGZF payload front to back; the caller provides the table
+ * scratch (shared memory on the device).  Everything is bounds-checked: malformed input ends with a negative
+ * code, never with a read or write outside [in, in+in_len) / [out, out+out_cap).
+ *
+ * Plain C so that the same source compiles for the device (nvcc) and, for the CPU test suite only, for the host
+ * (oracle/inflate_host.c).  The product path only ever runs it inside bgzf_inflate_kernel. */
+#ifndef DP_INFLATE_CORE_H
+#define DP_INFLATE_CORE_H
+#include <stdint.h>
+
+#ifdef __CUDACC__
+#define DPI_FN __device__ __forceinline__
+#define DPI_CONST __constant__
+#else
+#define DPI_FN static inline
+#define DPI_CONST static const
+#endif
+
+#define DPI_OK            0
+#define DPI_E_INPUT      -1   /* ran out of input                                  */
+#define DPI_E_OUTPUT     -2   /* output would exceed out_cap                       */
+#define DPI_E_BTYPE      -3   /* reserved block type 3                             */
+#define DPI_E_STORED     -4   /* stored block: LEN != ~NLEN                        */
+#define DPI_E_TABLE      -5   /* over-subscribed / incomplete code, bad repeat     */
+#define DPI_E_SYMBOL     -6   /* no code matches, or symbol out of range           */
+#define DPI_E_DISTANCE   -7   /* distance reaches before the start of the output   */
+#define DPI_E_LENGTH     -8   /* inflated size differs from ISIZE                  */
+
+#define DPI_MAXBITS 15
+#define DPI_NLEN    288
+#define DPI_NDIST   30
+/* scratch per decoder, in uint16 units: counts + symbols of both codes, then the code-length list */
+#define DPI_SCRATCH_U16 (16 + DPI_NLEN + 16 + DPI_NDIST + (DPI_NLEN + DPI_NDIST + 2) / 2 + 1)
+
+DPI_CONST uint16_t dpi_len_base[29] = {3, 4, 5, 6, 7, 8, 9, 10, 11, 13, 15, 17, 19, 23, 27, 31, 35, 43, 51, 59, 67, 83,
+                                       99, 115, 131, 163, 195, 227, 258};
+DPI_CONST uint8_t dpi_len_extra[29] = {0, 0, 0, 0, 0, 0, 0, 0, 1, 1, 1, 1, 2, 2, 2, 2, 3, 3, 3, 3, 4, 4, 4, 4, 5, 5, 5, 5, 0};
+DPI_CONST uint16_t dpi_dist_base[30] = {1, 2, 3, 4, 5, 7, 9, 13, 17, 25, 33, 49, 65, 97, 129, 193, 257, 385, 513, 769,
+                                        1025, 1537, 2049, 3073, 4097, 6145, 8193, 12289, 16385, 24577};
+DPI_CONST uint8_t dpi_dist_extra[30] = {0, 0, 0, 0, 1, 1, 2, 2, 3, 3, 4, 4, 5, 5, 6, 6, 7, 7, 8, 8, 9, 9, 10, 10, 11, 11,
+                                        12, 12, 13, 13};
+DPI_CONST uint8_t dpi_clen_order[19] = {16, 17, 18, 0, 8, 7, 9, 6, 10, 5, 11, 4, 12, 3, 13, 2, 14, 1, 15};
+
+typedef struct dpi_stream {
+    const uint8_t *in;
+    uint32_t in_len, in_pos;
+    uint64_t bitbuf;          /* LSB-first bit reservoir */
+    int32_t bitcnt;
+    uint8_t *out;
+    uint32_t out_cap, out_pos;
+    int32_t err;
+} dpi_stream;
+
+/* Take `need` (<= 16) bits; past the end of the input the stream goes into error and zeros are returned. */
+DPI_FN uint32_t dpi_bits(dpi_stream *s, int need)
+{
+    while (s->bitcnt < need) {
+        if (s->in_pos >= s->in_len) {
+            s->err = DPI_E_INPUT;
+            return 0;
+        }
+        s->bitbuf |= (uint64_t)s->in[s->in_pos++] << s->bitcnt;
+        s->bitcnt += 8;
+    }
+    uint32_t v = (uint32_t)(s->bitbuf & ((1u << need) - 1u));
+    s->bitbuf >>= need;
+    s->bitcnt -= need;
+    return v;
+}
+
+/* Canonical code described by count[len] (codes of each length) and symbol[] (symbols ordered by code). */
+DPI_FN int dpi_decode(dpi_stream *s, const uint16_t *count, const uint16_t *symbol)
+{
+    int32_t code = 0, first = 0, index = 0;
+    for (int len = 1; len <= DPI_MAXBITS; ++len) {
+        code |= (int32_t)dpi_bits(s, 1);
+        if (s->err) return s->err;
+        int32_t c = count[len];
+        if (code - c < first) return symbol[index + (code - first)];
+        index += c;
+        first = (first + c) << 1;
+        code <<= 1;
+    }
+    return DPI_E_SYMBOL;
+}
+
+/* Build count[]/symbol[] from code lengths.  Returns 0 for a complete code, > 0 for an incomplete one (allowed only
+ * where RFC 1951 allows a single code), < 0 for an over-subscribed one. */
+DPI_FN int dpi_build(uint16_t *count, uint16_t *symbol, const uint8_t *length, int n)
+{
+    uint16_t offs[DPI_MAXBITS + 1];
+    for (int len = 0; len <= DPI_MAXBITS; ++len) count[len] = 0;
+    for (int i = 0; i < n; ++i) count[length[i]]++;
+    if (count[0] == n) return 0;
+    int left = 1;
+    for (int len = 1; len <= DPI_MAXBITS; ++len) {
+        left = (left << 1) - count[len];
+        if (left < 0) return left;
+    }
+    offs[1] = 0;
+    for (int len = 1; len < DPI_MAXBITS; ++len) offs[len + 1] = offs[len] + count[len];
+    for (int i = 0; i < n; ++i)
+        if (length[i]) symbol[offs[length[i]]++] = (uint16_t)i;
+    return left;
+}
+
+/* Literal/length + distance loop shared by fixed and dynamic blocks. */
+DPI_FN int dpi_codes(dpi_stream *s, const uint16_t *lcnt, const uint16_t *lsym, const uint16_t *dcnt, const uint16_t *dsym)
+{
+    for (;;) {
+        int sym = dpi_decode(s, lcnt, lsym);
+        if (sym < 0) return sym;
+        if (sym < 256) {
+            if (s->out_pos >= s->out_cap) return DPI_E_OUTPUT;
+            s->out[s->out_pos++] = (uint8_t)sym;
+        } else if (sym == 256) {
+            return DPI_OK;
+        } else {
+            sym -= 257;
+            if (sym >= 29) return DPI_E_SYMBOL;
+            uint32_t len = dpi_len_base[sym] + dpi_bits(s, dpi_len_extra[sym]);
+            int ds = dpi_decode(s, dcnt, dsym);
+            if (ds < 0) return ds;
+            if (ds >= DPI_NDIST) return DPI_E_SYMBOL;
+            uint32_t dist = dpi_dist_base[ds] + dpi_bits(s, dpi_dist_extra[ds]);
+            if (s->err) return s->err;
+            if (dist > s->out_pos) return DPI_E_DISTANCE;
+            if (s->out_pos + len > s->out_cap) return DPI_E_OUTPUT;
+            uint8_t *d = s->out + s->out_pos;
+            const uint8_t *f = d - dist;
+            for (uint32_t i = 0; i < len; ++i) d[i] = f[i];      /* byte order matters: dist < len repeats */
+            s->out_pos += len;
+        }
+    }
+}
+
+/* Inflate one raw DEFLATE stream.  scratch: DPI_SCRATCH_U16 uint16.  Returns DPI_OK or a DPI_E_* code;
+ * *out_len = bytes written. */
+DPI_FN int dpi_inflate(const uint8_t *in, uint32_t in_len, uint8_t *out, uint32_t out_cap, uint16_t *scratch,
+                       uint32_t *out_len)
+{
+    dpi_stream st;
+    st.in = in; st.in_len = in_len; st.in_pos = 0; st.bitbuf = 0; st.bitcnt = 0;
+    st.out = out; st.out_cap = out_cap; st.out_pos = 0; st.err = 0;
+    uint16_t *lcnt = scratch, *lsym = lcnt + 16, *dcnt = lsym + DPI_NLEN, *dsym = dcnt + 16;
+    uint8_t *lengths = (uint8_t *)(dsym + DPI_NDIST);
+    int last, rc = DPI_OK;
+    do {
+        last = (int)dpi_bits(&st, 1);
+        int type = (int)dpi_bits(&st, 2);
+        if (st.err) { rc = st.err; break; }
+        if (type == 0) {
+            st.bitbuf = 0; st.bitcnt = 0;                         /* skip to the byte boundary */
+            if (st.in_pos + 4 > st.in_len) { rc = DPI_E_INPUT; break; }
+            uint32_t len = st.in[st.in_pos] | ((uint32_t)st.in[st.in_pos + 1] << 8);
+            uint32_t nlen = st.in[st.in_pos + 2] | ((uint32_t)st.in[st.in_pos + 3] << 8);
+            st.in_pos += 4;
+            if ((len ^ 0xffffu) != nlen) { rc = DPI_E_STORED; break; }
+            if (st.in_pos + len > st.in_len) { rc = DPI_E_INPUT; break; }
+            if (st.out_pos + len > st.out_cap) { rc = DPI_E_OUTPUT; break; }
+            for (uint32_t i = 0; i < len; ++i) st.out[st.out_pos + i] = st.in[st.in_pos + i];
+            st.in_pos += len; st.out_pos += len;
+        } else if (type == 1) {
+            int i = 0;
+            for (; i < 144; ++i) lengths[i] = 8;
+            for (; i < 256; ++i) lengths[i] = 9;
+            for (; i < 280; ++i) lengths[i] = 7;
+            for (; i < DPI_NLEN; ++i) lengths[i] = 8;
+            dpi_build(lcnt, lsym, lengths, DPI_NLEN);
+            for (i = 0; i < DPI_NDIST; ++i) lengths[i] = 5;
+            dpi_build(dcnt, dsym, lengths, DPI_NDIST);
+            rc = dpi_codes(&st, lcnt, lsym, dcnt, dsym);
+        } else if (type == 2) {
+            int nlen = (int)dpi_bits(&st, 5) + 257, ndist = (int)dpi_bits(&st, 5) + 1, ncode = (int)dpi_bits(&st, 4) + 4;
+            if (st.err) { rc = st.err; break; }
+            if (nlen > 286 || ndist > DPI_NDIST) { rc = DPI_E_TABLE; break; }
+            int i;
+            for (i = 0; i < 19; ++i) lengths[i] = 0;
+            for (i = 0; i < ncode; ++i) lengths[dpi_clen_order[i]] = (uint8_t)dpi_bits(&st, 3);
+            if (st.err) { rc = st.err; break; }
+            if (dpi_build(lcnt, lsym, lengths, 19) != 0) { rc = DPI_E_TABLE; break; }   /* code-length code must be complete */
+            i = 0;
+            while (i < nlen + ndist) {
+                int sym = dpi_decode(&st, lcnt, lsym);
+                if (sym < 0) { rc = sym; break; }
+                if (sym < 16) {
+                    lengths[i++] = (uint8_t)sym;
+                } else {
+                    int prev = 0, rep;
+                    if (sym == 16) {
+                        if (i == 0) { rc = DPI_E_TABLE; break; }
+                        prev = lengths[i - 1];
+                        rep = 3 + (int)dpi_bits(&st, 2);
+                    } else if (sym == 17) {
+                        rep = 3 + (int)dpi_bits(&st, 3);
+                    } else {
+                        rep = 11 + (int)dpi_bits(&st, 7);
+                    }
+                    if (st.err) { rc = st.err; break; }
+                    if (i + rep > nlen + ndist) { rc = DPI_E_TABLE; break; }
+                    while (rep--) lengths[i++] = (uint8_t)prev;
+                }
+            }
+            if (rc != DPI_OK) break;
+            if (lengths[256] == 0) { rc = DPI_E_TABLE; break; }                         /* no end-of-block code */
+            /* the distance lengths must be read before lsym is overwritten: build the distance code first, from a copy
+             * position that dpi_build of the literal code does not touch (lengths[] is separate from both tables) */
+            int e = dpi_build(dcnt, dsym, lengths + nlen, ndist);
+            if (e < 0 || (e > 0 && ndist - dcnt[0] != 1)) { rc = DPI_E_TABLE; break; }
+            e = dpi_build(lcnt, lsym, lengths, nlen);
+            if (e < 0 || (e > 0 && nlen - lcnt[0] != 1)) { rc = DPI_E_TABLE; break; }
+            rc = dpi_codes(&st, lcnt, lsym, dcnt, dsym);
+        } else {
+            rc = DPI_E_BTYPE;
+        }
+    } while (rc == DPI_OK && !last);
+    *out_len = st.out_pos;
+    return rc;
+}
+
+#endif /* DP_INFLATE_CORE_H */

@@ -171,6 +171,38 @@ int dp_model_profile_read(dp_model *m, float ms[4], int32_t launches[4]);
 int dp_gemm_bf16(const void *A, int64_t lda, const void *B, int64_t ldb, const float *bias, void *out, int64_t ldc,
                  int32_t out_fp32, int64_t M, int64_t N, int64_t K, int32_t block_n, void *stream);
 
+/* ---- device-side BAM ingest: BGZF inflate + BAM record -> dp_reads arrays in HBM.
+ * Replaces the host stage behind pysam: dep/htslib/bgzf.c:456-499 (inflate_block, zlib raw inflate of one block),
+ * bgzf.c block header / trailer (18-byte header with the "BC" BSIZE sub-field; CRC32 + ISIZE), and
+ * dep/htslib/sam.c bam_read1 (32-byte core, name, CIGAR, 4-bit bases, qualities). */
+
+/* dp_bgzf_index -- HOST: walks the block headers of a BGZF file image.  Returns the number of blocks (the EOF block
+ * included) or a negative DP_E* code.  With max_blocks == 0 it only counts; otherwise fills, per block, the byte
+ * offset / length of the raw DEFLATE payload, the offset / length (ISIZE) of its inflated bytes (out_off has
+ * n_blocks + 1 entries, the last one = total inflated size) and the trailer CRC32.  Any out pointer may be NULL. */
+int64_t dp_bgzf_index(const uint8_t *file, int64_t n_bytes, int64_t max_blocks, int64_t *in_off, int32_t *in_len,
+                      int64_t *out_off, int32_t *out_len, uint32_t *crc32);
+
+/* dp_bgzf_inflate -- DEVICE pointers throughout: inflates every block of the (device-resident) file image into
+ * out[out_off[b] .. +out_len[b]).  status[b] = 0 or a negative DPI_E_* code (csrc/inflate_core.h); malformed blocks
+ * never read or write out of bounds. */
+int dp_bgzf_inflate(const uint8_t *file, int64_t n_blocks, const int64_t *in_off, const int32_t *in_len,
+                    const int64_t *out_off, const int32_t *out_len, uint8_t *out, int32_t *status, void *stream);
+
+/* dp_bam_scan -- DEVICE pointers: parses the BAM header of the inflated stream, resolves `contig` (contig_len bytes,
+ * device memory; contig_len == 0 keeps every record) to its tid and walks the record chain.  For every kept record i
+ * (< max_records) writes rec_off[i] (byte offset of its length prefix) and the running cigar_off / seq_off / qual_off
+ * of dp_reads (arrays of max_records + 1 entries; entry [kept] closes them).  counts (7 x int64): records kept, CIGAR
+ * ops, packed sequence bytes, quality bytes, tid, records seen, status (0 ok, -1 bad magic, -2 truncated, -3 contig
+ * not in the header). */
+int dp_bam_scan(const uint8_t *bam, int64_t n_bytes, const char *contig, int32_t contig_len, int64_t max_records,
+                int64_t *rec_off, int64_t *cigar_off, int64_t *seq_off, int64_t *qual_off, int64_t *counts, void *stream);
+
+/* dp_bam_extract -- DEVICE pointers: fills the dp_reads arrays of the n_records records found by dp_bam_scan. */
+int dp_bam_extract(const uint8_t *bam, int64_t n_records, const int64_t *rec_off, const int64_t *cigar_off,
+                   const int64_t *seq_off, const int64_t *qual_off, int32_t *pos, uint16_t *flag, uint8_t *mapq,
+                   int32_t *l_seq, uint32_t *cigar, uint8_t *seq4, uint8_t *qual, void *stream);
+
 #ifdef __cplusplus
 }
 #endif
