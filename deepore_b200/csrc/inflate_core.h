@@ -3,7 +3,7 @@
  * Replaces, per BGZF block, what the reference's host stage does through zlib: dep/htslib/bgzf.c:456-499
  * (inflate_block: inflateInit2(-15) / inflate(Z_FINISH) on the block payload) -- zlib itself is a third-party
  * dependency that is not under /root/reference; the algorithm restated here is the published RFC 1951 one
- * (stored / fixed / dynamic blocks, canonical Huffman codes decoded by the count/first-code walk).
+ * (stored / fixed / dynamic blocks, canonical Huffman codes decoded by a 9-bit lookup table with the count/first-code walk behind it).
  *
  * One decoder instance = one thread decoding one BGZF payload front to back; the caller provides the table
  * scratch (shared memory on the device).  Everything is bounds-checked: malformed input ends with a negative
@@ -36,8 +36,13 @@
 #define DPI_MAXBITS 15
 #define DPI_NLEN    288
 #define DPI_NDIST   30
-/* scratch per decoder, in uint16 units: counts + symbols of both codes, then the code-length list */
-#define DPI_SCRATCH_U16 (16 + DPI_NLEN + 16 + DPI_NDIST + (DPI_NLEN + DPI_NDIST + 2) / 2 + 1)
+/* first-level lookup of the literal/length code: DPI_FAST_BITS peeked bits -> (symbol << 4) | code length, 0 = the code
+ * is longer than DPI_FAST_BITS (decoded by the count/first-code walk instead) */
+#define DPI_FAST_BITS 9
+#define DPI_FAST_SIZE (1 << DPI_FAST_BITS)
+/* scratch per decoder, in uint16 units: counts + symbols of both codes, the code-length list, the lookup table */
+#define DPI_SLOW_U16 (16 + DPI_NLEN + 16 + DPI_NDIST + (DPI_NLEN + DPI_NDIST + 2) / 2 + 1)
+#define DPI_SCRATCH_U16 (DPI_SLOW_U16 + DPI_FAST_SIZE)
 
 DPI_CONST uint16_t dpi_len_base[29] = {3, 4, 5, 6, 7, 8, 9, 10, 11, 13, 15, 17, 19, 23, 27, 31, 35, 43, 51, 59, 67, 83,
                                        99, 115, 131, 163, 195, 227, 258};
@@ -111,11 +116,55 @@ DPI_FN int dpi_build(uint16_t *count, uint16_t *symbol, const uint8_t *length, i
     return left;
 }
 
+/* Lookup table of the literal/length code from its code lengths (RFC 1951 3.2.2: codes of one length are consecutive,
+ * shorter codes first; the stream carries them most-significant bit first, so the peeked index is the reversed code). */
+DPI_FN void dpi_build_fast(uint16_t *fast, const uint16_t *count, const uint8_t *length, int n)
+{
+    uint16_t next[DPI_MAXBITS + 1];
+    uint32_t code = 0;
+    next[0] = 0;
+    for (int len = 1; len <= DPI_MAXBITS; ++len) {
+        code = (code + (len > 1 ? count[len - 1] : 0)) << 1;
+        next[len] = (uint16_t)code;
+    }
+    for (int i = 0; i < DPI_FAST_SIZE; ++i) fast[i] = 0;
+    for (int sym = 0; sym < n; ++sym) {
+        const int len = length[sym];
+        if (len == 0) continue;
+        const uint32_t c = next[len]++;
+        if (len > DPI_FAST_BITS) continue;
+        uint32_t rev = 0;
+        for (int b = 0; b < len; ++b) rev |= ((c >> b) & 1u) << (len - 1 - b);
+        const uint16_t e = (uint16_t)((sym << 4) | len);
+        for (uint32_t idx = rev; idx < DPI_FAST_SIZE; idx += 1u << len) fast[idx] = e;
+    }
+}
+
+/* Literal/length symbol: one table lookup when enough input is buffered and the code is short, else the walk. */
+DPI_FN int dpi_decode_len(dpi_stream *s, const uint16_t *fast, const uint16_t *count, const uint16_t *symbol)
+{
+    while (s->bitcnt < DPI_FAST_BITS && s->in_pos < s->in_len) {
+        s->bitbuf |= (uint64_t)s->in[s->in_pos++] << s->bitcnt;
+        s->bitcnt += 8;
+    }
+    if (s->bitcnt >= DPI_FAST_BITS) {
+        const uint16_t e = fast[(uint32_t)s->bitbuf & (DPI_FAST_SIZE - 1)];
+        if (e) {
+            const int len = e & 15;
+            s->bitbuf >>= len;
+            s->bitcnt -= len;
+            return e >> 4;
+        }
+    }
+    return dpi_decode(s, count, symbol);
+}
+
 /* Literal/length + distance loop shared by fixed and dynamic blocks. */
-DPI_FN int dpi_codes(dpi_stream *s, const uint16_t *lcnt, const uint16_t *lsym, const uint16_t *dcnt, const uint16_t *dsym)
+DPI_FN int dpi_codes(dpi_stream *s, const uint16_t *fast, const uint16_t *lcnt, const uint16_t *lsym, const uint16_t *dcnt,
+                     const uint16_t *dsym)
 {
     for (;;) {
-        int sym = dpi_decode(s, lcnt, lsym);
+        int sym = dpi_decode_len(s, fast, lcnt, lsym);
         if (sym < 0) return sym;
         if (sym < 256) {
             if (s->out_pos >= s->out_cap) return DPI_E_OUTPUT;
@@ -151,12 +200,14 @@ DPI_FN int dpi_inflate(const uint8_t *in, uint32_t in_len, uint8_t *out, uint32_
     st.out = out; st.out_cap = out_cap; st.out_pos = 0; st.err = 0;
     uint16_t *lcnt = scratch, *lsym = lcnt + 16, *dcnt = lsym + DPI_NLEN, *dsym = dcnt + 16;
     uint8_t *lengths = (uint8_t *)(dsym + DPI_NDIST);
+    uint16_t *fast = scratch + DPI_SLOW_U16;
     int last, rc = DPI_OK;
     do {
         last = (int)dpi_bits(&st, 1);
         int type = (int)dpi_bits(&st, 2);
         if (st.err) { rc = st.err; break; }
         if (type == 0) {
+            st.in_pos -= (uint32_t)st.bitcnt >> 3;               /* whole bytes the table lookup read ahead go back */
             st.bitbuf = 0; st.bitcnt = 0;                         /* skip to the byte boundary */
             if (st.in_pos + 4 > st.in_len) { rc = DPI_E_INPUT; break; }
             uint32_t len = st.in[st.in_pos] | ((uint32_t)st.in[st.in_pos + 1] << 8);
@@ -174,9 +225,10 @@ DPI_FN int dpi_inflate(const uint8_t *in, uint32_t in_len, uint8_t *out, uint32_
             for (; i < 280; ++i) lengths[i] = 7;
             for (; i < DPI_NLEN; ++i) lengths[i] = 8;
             dpi_build(lcnt, lsym, lengths, DPI_NLEN);
+            dpi_build_fast(fast, lcnt, lengths, DPI_NLEN);
             for (i = 0; i < DPI_NDIST; ++i) lengths[i] = 5;
             dpi_build(dcnt, dsym, lengths, DPI_NDIST);
-            rc = dpi_codes(&st, lcnt, lsym, dcnt, dsym);
+            rc = dpi_codes(&st, fast, lcnt, lsym, dcnt, dsym);
         } else if (type == 2) {
             int nlen = (int)dpi_bits(&st, 5) + 257, ndist = (int)dpi_bits(&st, 5) + 1, ncode = (int)dpi_bits(&st, 4) + 4;
             if (st.err) { rc = st.err; break; }
@@ -216,7 +268,8 @@ DPI_FN int dpi_inflate(const uint8_t *in, uint32_t in_len, uint8_t *out, uint32_
             if (e < 0 || (e > 0 && ndist - dcnt[0] != 1)) { rc = DPI_E_TABLE; break; }
             e = dpi_build(lcnt, lsym, lengths, nlen);
             if (e < 0 || (e > 0 && nlen - lcnt[0] != 1)) { rc = DPI_E_TABLE; break; }
-            rc = dpi_codes(&st, lcnt, lsym, dcnt, dsym);
+            dpi_build_fast(fast, lcnt, lengths, nlen);
+            rc = dpi_codes(&st, fast, lcnt, lsym, dcnt, dsym);
         } else {
             rc = DPI_E_BTYPE;
         }

@@ -76,6 +76,20 @@ def test_inflate_core_multi_block_stream():
     assert rc == 0 and got == raw
 
 
+def test_inflate_core_stored_block_after_huffman_block_at_every_bit_offset():
+    # a Huffman block followed by stored ones: the decoder's look-ahead must hand whole bytes back at the byte boundary
+    run = _host_inflate()
+    rng = np.random.default_rng(23)
+    for k in range(200):
+        a = bytes(rng.integers(65, 65 + 1 + k % 40, 20 + 7 * k, dtype=np.uint8))
+        b = bytes(rng.integers(0, 256, 100 + k, dtype=np.uint8))
+        co = zlib.compressobj(6 if k % 3 else 1, zlib.DEFLATED, -15, 9, zlib.Z_FIXED if k % 5 == 0 else 0)
+        payload = co.compress(a) + co.flush(zlib.Z_SYNC_FLUSH) + _deflate(b, 0, 0)
+        assert zlib.decompress(payload, -15) == a + b
+        rc, got = run(payload, len(a) + len(b))
+        assert rc == 0 and got == a + b, k
+
+
 def test_inflate_core_rejects_malformed_input_in_bounds():
     run = _host_inflate()
     raw = b"the quick brown fox jumps over the lazy dog " * 200
