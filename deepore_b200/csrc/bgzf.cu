@@ -6,9 +6,9 @@
 // what crosses PCIe; the inflated stream and the SoA arrays only ever exist in HBM.
 //
 // Kernels (first correct version; byte work, HBM/latency-bound, no tensor cores):
-//   bgzf_inflate_kernel   one thread per BGZF block (blocks are independent DEFLATE streams of <= 64 KB), 32 per CTA,
-//                         Huffman tables + a 9-bit literal/length lookup table per thread in 64 KB of shared memory
-//                         (inflate_core.h)
+//   bgzf_inflate_kernel   one warp per BGZF block (blocks are independent DEFLATE streams of <= 64 KB): the lanes decode
+//                         in lock step and share the match / stored-block copies;
+//                         Huffman tables + a 9-bit literal/length lookup table per warp in shared memory (inflate_core.h)
 //   bam_scan_kernel       one thread: header (contig name -> tid), then the record chain (each record's length prefix
 //                         gives the next one); writes record offsets and the running CIGAR / sequence / quality offsets
 //   bam_extract_kernel    one warp per kept record: core fields + coalesced copies of CIGAR, packed bases, qualities
@@ -22,23 +22,27 @@
 
 namespace {
 
-constexpr int INFLATE_THREADS = 32;
-constexpr int INFLATE_STRIDE_U16 = DPI_SCRATCH_U16 + 1 + ((DPI_SCRATCH_U16 + 1) % 2 == 0 ? 1 : 0);   // odd stride spreads the banks
-constexpr int INFLATE_SMEM = INFLATE_THREADS * INFLATE_STRIDE_U16 * 2;
+constexpr int INFLATE_WARPS = 4;                                     // BGZF blocks per CTA: one per warp
+constexpr int INFLATE_STRIDE_U16 = DPI_SCRATCH_U16 + 1;
 
-__global__ void __launch_bounds__(INFLATE_THREADS)
+// One BGZF block per WARP.  A thread per block inside one warp (the first version) diverges on every symbol -- 32
+// different streams serialised on one warp scheduler: 0.21 GB/s on the bench file, the speed of ONE host core.  Here the 32
+// lanes of a warp run the same decoder in lock step on the same stream (no divergence) and split only the output bytes of
+// matches and stored blocks between them (inflate_core.h).
+__global__ void __launch_bounds__(INFLATE_WARPS * 32)
 bgzf_inflate_kernel(const uint8_t *__restrict__ file, int64_t n_blocks, const int64_t *__restrict__ in_off,
                     const int32_t *__restrict__ in_len, const int64_t *__restrict__ out_off,
                     const int32_t *__restrict__ out_len, uint8_t *out, int32_t *__restrict__ status)
 {
-    extern __shared__ uint16_t scratch[];                                // INFLATE_THREADS x INFLATE_STRIDE_U16
-    int64_t b = (int64_t)blockIdx.x * INFLATE_THREADS + threadIdx.x;
-    if (b >= n_blocks) return;
+    __shared__ uint16_t scratch[INFLATE_WARPS][INFLATE_STRIDE_U16];
+    const int warp = threadIdx.x >> 5;
+    const int64_t b = (int64_t)blockIdx.x * INFLATE_WARPS + warp;
+    if (b >= n_blocks) return;                                      // warp-uniform
     uint32_t produced = 0;
-    int rc = dpi_inflate(file + in_off[b], (uint32_t)in_len[b], out + out_off[b], (uint32_t)out_len[b],
-                         scratch + (size_t)threadIdx.x * INFLATE_STRIDE_U16, &produced);
+    int rc = dpi_inflate(file + in_off[b], (uint32_t)in_len[b], out + out_off[b], (uint32_t)out_len[b], scratch[warp],
+                         &produced);                                // all 32 lanes, in lock step (inflate_core.h)
     if (rc == DPI_OK && produced != (uint32_t)out_len[b]) rc = DPI_E_LENGTH;
-    status[b] = rc;
+    if ((threadIdx.x & 31) == 0) status[b] = rc;
 }
 
 __device__ __forceinline__ int32_t ld_i32(const uint8_t *p)
@@ -189,10 +193,9 @@ int dp_bgzf_inflate(const uint8_t *file, int64_t n_blocks, const int64_t *in_off
         return DP_EINVAL;
     }
     if (n_blocks == 0) return DP_OK;
-    const int64_t grid = (n_blocks + INFLATE_THREADS - 1) / INFLATE_THREADS;
-    DP_CUDA_CHECK(cudaFuncSetAttribute(bgzf_inflate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, INFLATE_SMEM));
-    bgzf_inflate_kernel<<<(unsigned)grid, INFLATE_THREADS, INFLATE_SMEM, (cudaStream_t)stream>>>(file, n_blocks, in_off, in_len, out_off,
-                                                                                      out_len, out, status);
+    const int64_t grid = (n_blocks + INFLATE_WARPS - 1) / INFLATE_WARPS;
+    bgzf_inflate_kernel<<<(unsigned)grid, INFLATE_WARPS * 32, 0, (cudaStream_t)stream>>>(file, n_blocks, in_off, in_len, out_off,
+                                                                                         out_len, out, status);
     DP_CUDA_CHECK(cudaGetLastError());
     return DP_OK;
 }

@@ -5,8 +5,8 @@
  * dependency that is not under /root/reference; the algorithm restated here is the published RFC 1951 one
  * (stored / fixed / dynamic blocks, canonical Huffman codes decoded by a 9-bit lookup table with the count/first-code walk behind it).
  *
- * One decoder instance = one thread decoding one BGZF payload front to back; the caller provides the table
- * scratch (shared memory on the device).  Everything is bounds-checked: malformed input ends with a negative
+ * One decoder instance = one warp (device) or one thread (host) decoding one BGZF payload front to back; the caller
+ * provides the table scratch (shared memory on the device).  Everything is bounds-checked: malformed input ends with a negative
  * code, never with a read or write outside [in, in+in_len) / [out, out+out_cap).
  *
  * Plain C so that the same source compiles for the device (nvcc) and, for the CPU test suite only, for the host
@@ -18,9 +18,19 @@
 #ifdef __CUDACC__
 #define DPI_FN __device__ __forceinline__
 #define DPI_CONST __constant__
+/* On the device the 32 lanes of a warp run ONE decoder in lock step: every lane holds the same bit reservoir and takes the
+ * same branches (same-address loads broadcast, no divergence), and only the output is split -- lane 0 stores literals,
+ * the lanes stride over the bytes of a match or of a stored block.  DPI_SYNC orders the lanes' earlier stores before a
+ * match reads them back. */
+#define DPI_LANE  ((uint32_t)(threadIdx.x & 31))
+#define DPI_LANES 32u
+#define DPI_SYNC() __syncwarp()
 #else
 #define DPI_FN static inline
 #define DPI_CONST static const
+#define DPI_LANE  0u
+#define DPI_LANES 1u
+#define DPI_SYNC() ((void)0)
 #endif
 
 #define DPI_OK            0
@@ -100,19 +110,28 @@ DPI_FN int dpi_decode(dpi_stream *s, const uint16_t *count, const uint16_t *symb
  * where RFC 1951 allows a single code), < 0 for an over-subscribed one. */
 DPI_FN int dpi_build(uint16_t *count, uint16_t *symbol, const uint8_t *length, int n)
 {
-    uint16_t offs[DPI_MAXBITS + 1];
-    for (int len = 0; len <= DPI_MAXBITS; ++len) count[len] = 0;
-    for (int i = 0; i < n; ++i) count[length[i]]++;
+    /* the tables are shared by the lanes of a warp: lane 0 writes them (read-modify-write on shared memory must not be
+     * repeated by 32 lanes), every lane reads them back behind a DPI_SYNC */
+    DPI_SYNC();                                                  /* nobody still decodes with the previous tables */
+    if (DPI_LANE == 0) {
+        for (int len = 0; len <= DPI_MAXBITS; ++len) count[len] = 0;
+        for (int i = 0; i < n; ++i) count[length[i]]++;
+    }
+    DPI_SYNC();
     if (count[0] == n) return 0;
     int left = 1;
     for (int len = 1; len <= DPI_MAXBITS; ++len) {
         left = (left << 1) - count[len];
         if (left < 0) return left;
     }
-    offs[1] = 0;
-    for (int len = 1; len < DPI_MAXBITS; ++len) offs[len + 1] = offs[len] + count[len];
-    for (int i = 0; i < n; ++i)
-        if (length[i]) symbol[offs[length[i]]++] = (uint16_t)i;
+    if (DPI_LANE == 0) {
+        uint16_t offs[DPI_MAXBITS + 1];
+        offs[1] = 0;
+        for (int len = 1; len < DPI_MAXBITS; ++len) offs[len + 1] = offs[len] + count[len];
+        for (int i = 0; i < n; ++i)
+            if (length[i]) symbol[offs[length[i]]++] = (uint16_t)i;
+    }
+    DPI_SYNC();
     return left;
 }
 
@@ -120,24 +139,29 @@ DPI_FN int dpi_build(uint16_t *count, uint16_t *symbol, const uint8_t *length, i
  * shorter codes first; the stream carries them most-significant bit first, so the peeked index is the reversed code). */
 DPI_FN void dpi_build_fast(uint16_t *fast, const uint16_t *count, const uint8_t *length, int n)
 {
-    uint16_t next[DPI_MAXBITS + 1];
-    uint32_t code = 0;
-    next[0] = 0;
-    for (int len = 1; len <= DPI_MAXBITS; ++len) {
-        code = (code + (len > 1 ? count[len - 1] : 0)) << 1;
-        next[len] = (uint16_t)code;
+    DPI_SYNC();
+    for (uint32_t i = DPI_LANE; i < DPI_FAST_SIZE; i += DPI_LANES) fast[i] = 0;
+    DPI_SYNC();
+    if (DPI_LANE == 0) {
+        uint16_t next[DPI_MAXBITS + 1];
+        uint32_t code = 0;
+        next[0] = 0;
+        for (int len = 1; len <= DPI_MAXBITS; ++len) {
+            code = (code + (len > 1 ? count[len - 1] : 0)) << 1;
+            next[len] = (uint16_t)code;
+        }
+        for (int sym = 0; sym < n; ++sym) {
+            const int len = length[sym];
+            if (len == 0) continue;
+            const uint32_t c = next[len]++;
+            if (len > DPI_FAST_BITS) continue;
+            uint32_t rev = 0;
+            for (int b = 0; b < len; ++b) rev |= ((c >> b) & 1u) << (len - 1 - b);
+            const uint16_t e = (uint16_t)((sym << 4) | len);
+            for (uint32_t idx = rev; idx < DPI_FAST_SIZE; idx += 1u << len) fast[idx] = e;
+        }
     }
-    for (int i = 0; i < DPI_FAST_SIZE; ++i) fast[i] = 0;
-    for (int sym = 0; sym < n; ++sym) {
-        const int len = length[sym];
-        if (len == 0) continue;
-        const uint32_t c = next[len]++;
-        if (len > DPI_FAST_BITS) continue;
-        uint32_t rev = 0;
-        for (int b = 0; b < len; ++b) rev |= ((c >> b) & 1u) << (len - 1 - b);
-        const uint16_t e = (uint16_t)((sym << 4) | len);
-        for (uint32_t idx = rev; idx < DPI_FAST_SIZE; idx += 1u << len) fast[idx] = e;
-    }
+    DPI_SYNC();
 }
 
 /* Literal/length symbol: one table lookup when enough input is buffered and the code is short, else the walk. */
@@ -168,7 +192,8 @@ DPI_FN int dpi_codes(dpi_stream *s, const uint16_t *fast, const uint16_t *lcnt, 
         if (sym < 0) return sym;
         if (sym < 256) {
             if (s->out_pos >= s->out_cap) return DPI_E_OUTPUT;
-            s->out[s->out_pos++] = (uint8_t)sym;
+            if (DPI_LANE == 0) s->out[s->out_pos] = (uint8_t)sym;
+            s->out_pos++;
         } else if (sym == 256) {
             return DPI_OK;
         } else {
@@ -184,7 +209,12 @@ DPI_FN int dpi_codes(dpi_stream *s, const uint16_t *fast, const uint16_t *lcnt, 
             if (s->out_pos + len > s->out_cap) return DPI_E_OUTPUT;
             uint8_t *d = s->out + s->out_pos;
             const uint8_t *f = d - dist;
-            for (uint32_t i = 0; i < len; ++i) d[i] = f[i];      /* byte order matters: dist < len repeats */
+            DPI_SYNC();
+            if (dist >= len) {
+                for (uint32_t i = DPI_LANE; i < len; i += DPI_LANES) d[i] = f[i];
+            } else {                                             /* the match overlaps itself: its first `dist` bytes repeat */
+                for (uint32_t i = DPI_LANE; i < len; i += DPI_LANES) d[i] = f[i % dist];
+            }
             s->out_pos += len;
         }
     }
@@ -216,7 +246,7 @@ DPI_FN int dpi_inflate(const uint8_t *in, uint32_t in_len, uint8_t *out, uint32_
             if ((len ^ 0xffffu) != nlen) { rc = DPI_E_STORED; break; }
             if (st.in_pos + len > st.in_len) { rc = DPI_E_INPUT; break; }
             if (st.out_pos + len > st.out_cap) { rc = DPI_E_OUTPUT; break; }
-            for (uint32_t i = 0; i < len; ++i) st.out[st.out_pos + i] = st.in[st.in_pos + i];
+            for (uint32_t i = DPI_LANE; i < len; i += DPI_LANES) st.out[st.out_pos + i] = st.in[st.in_pos + i];
             st.in_pos += len; st.out_pos += len;
         } else if (type == 1) {
             int i = 0;

@@ -66,4 +66,4 @@ print(json.dumps({"workload": "synthetic 30x nanopore-length reads over %d kb, B
                   "inflate_algorithmic_GBps": (len(data) + image.size) / ms_inf / 1e6,
                   "scan_plus_extract_ms": ms_rec, "records_GBps": len(data) / ms_rec / 1e6,
                   "zlib_one_core_s": cpu_s, "zlib_one_core_GBps": len(data) / cpu_s / 1e9,
-                  "note": "thread-per-block inflate: %d blocks = %d threads on 148 SMs" % (n, n)}))
+                  "note": "warp-per-block inflate: %d blocks = %d warps on 148 SMs" % (n, n)}))
