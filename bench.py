@@ -264,7 +264,7 @@ def main():
                     help="e2e = encode + model + vote (the metric); encode = pileup encoder only")
     ap.add_argument("--windows", type=int, default=2048, help="windows per step (interval shard size)")
     ap.add_argument("--model-chunk", type=int, default=512, help="windows per model forward call")
-    ap.add_argument("--precision", default="bf16", choices=["bf16", "bf16x3"])
+    ap.add_argument("--precision", default="fp16", choices=["bf16", "bf16x3", "fp16", "fp16x3"])
     ap.add_argument("--stride", type=int, default=100)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()

@@ -13,6 +13,7 @@
 //   fc1 + argmax                 logits[row][t][c] (model.py:154-155), first maximum wins (torch.topk, test.py:68)
 //   vote                         3-way majority over (row-2,t=2),(row-1,t=1),(row,t=0), smallest class on a 3-way tie
 //                                (test.py:23-24,71-82)
+#include <cuda_fp16.h>
 #include <math.h>
 #include <stdlib.h>
 
@@ -39,18 +40,47 @@ static inline float bf2f(uint16_t h) {
     memcpy(&f, &u, 4);
     return f;
 }
+// 16-bit operand formats of the tensor-core path: bf16 (8-bit significand) or fp16 (11-bit significand, range kept by
+// power-of-two weight scales that the epilogues divide out again)
+static inline uint16_t f2h16(float f, bool f16) {
+    if (!f16) return f2bf(f);
+    if (f > 65504.f) f = 65504.f;
+    if (f < -65504.f) f = -65504.f;
+    const __half h = __float2half_rn(f);
+    uint16_t u;
+    memcpy(&u, &h, 2);
+    return u;
+}
+static inline float h162f(uint16_t u, bool f16) {
+    if (!f16) return bf2f(u);
+    __half h;
+    memcpy(&h, &u, 2);
+    return __half2float(h);
+}
+// largest power of two s with max|w| * s <= 16384 (fp16: headroom of 4 below the largest finite value); 1 for bf16
+static inline float pow2_scale(float maxabs, bool f16) {
+    if (!f16 || !(maxabs > 0.f)) return 1.f;
+    int e = 0;
+    frexpf(16384.f / maxabs, &e);          // 16384 / maxabs = m * 2^e, m in [0.5, 1)
+    return ldexpf(1.f, e - 1);
+}
 
 struct Model {
     int in_ch, width, hidden, n_class, seq_len, n_layers;
     int row_elems;                 // width * in_ch (800)
     int kfold_pad;                 // per-row-slot K of the folded operator padded to 64 (832)
-    int precise;
+    int f16;                       // 16-bit operand format: 0 = bf16, 1 = fp16
+    int fold_split;                // folded-operator weights as hi + lo (two passes; the u8 image is exact in either format)
+    int gru_split;                 // bit k: GRU layer k runs the three split passes (hi.hi, hi.lo, lo.hi)
+    int alloc_lo;                  // lo copies of the activations exist (gru_split != 0)
+    int fast_act;                  // MUFU.TANH activations instead of exp-based ones
+    float fold_scale = 1.f, gru_scale = 1.f;   // power-of-two scales folded into the 16-bit weights (fp16 range)
     long long mcap;                // row capacity (multiple of 128)
     int device;
     // device buffers
     __nv_bfloat16 *img_bf = nullptr;      // [mcap + 128][row_elems]
     __nv_bfloat16 *arena = nullptr;       // [NSLOT_BF][mcap][HP]
-    __nv_bfloat16 *arena_lo = nullptr;    // precise only
+    __nv_bfloat16 *arena_lo = nullptr;    // split modes only
     float *state = nullptr;               // [NSLOT_F32][mcap][HP]
     int bf_state = 0;                     // one-pass bf16 mode on the CTA-pair kernel: number of leading GRU layers whose state
                                           // lives in the bf16 rows only (no fp32 copy); DP_GRU_STATE = f32 | mixed | bf16
@@ -65,7 +95,8 @@ struct Model {
     long long kcols_fold = 0, kcols_gru = 0;
     CUtensorMap tm_img, tm_arena, tm_arena_lo, tm_wfold, tm_wgru, tm_wgru96, tm_arena_mc, tm_arena_lo_mc;
     int gru_np = 1;                // CTA pairs per cluster of the pair kernel (A tiles multicast between them); env DP_GRU_NP
-    int gru_wide = 0;              // env DP_GRU=wide: 256 x 128-unit tiles (gru_step2w_kernel)
+    int gru_wide = 0;              // env DP_GRU=wide: 256 x 128-unit tiles (gru_step2w_kernel); DP_GRU=stag: the same with
+                                   // staggered halves (gru_step2s_kernel, value 2)
     int gru_2cta = 1;              // CTA-pair GRU kernel (env DP_GRU=1cta selects the single-CTA kernel)
     // optional per-kernel timing (bench.py roofline): one event per launch boundary, harvested by dp_model_profile_read
     int profile = 0;
@@ -92,7 +123,8 @@ static inline int f32_slot_hb(int k, int t) { return 6 * k + 3 + t; }
 // small CUDA-core kernels around the GEMMs
 
 // u8 -> bf16, 16 bytes in / 32 bytes out per thread (exact: integers <= 255 fit the 8-bit bf16 significand)
-__global__ void __launch_bounds__(256) u8_to_bf16_kernel(const uint4 *__restrict__ in, uint4 *__restrict__ out, long long n16) {
+__global__ void __launch_bounds__(256) u8_to_bf16_kernel(const uint4 *__restrict__ in, uint4 *__restrict__ out, long long n16,
+                                                         int f16) {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n16) return;
     const uint4 v = __ldg(in + i);
@@ -102,9 +134,8 @@ __global__ void __launch_bounds__(256) u8_to_bf16_kernel(const uint4 *__restrict
     for (int k = 0; k < 4; k++) {
         const float b0 = (float)(w[k] & 0xff), b1 = (float)((w[k] >> 8) & 0xff);
         const float b2 = (float)((w[k] >> 16) & 0xff), b3 = (float)(w[k] >> 24);
-        __nv_bfloat162 p0 = __floats2bfloat162_rn(b0, b1), p1 = __floats2bfloat162_rn(b2, b3);
-        o[2 * k] = *reinterpret_cast<uint32_t *>(&p0);
-        o[2 * k + 1] = *reinterpret_cast<uint32_t *>(&p1);
+        o[2 * k] = tc::pack16(b0, b1, f16 != 0);       // integers <= 255 are exact in bf16 and in fp16
+        o[2 * k + 1] = tc::pack16(b2, b3, f16 != 0);
     }
     out[2 * i] = make_uint4(o[0], o[1], o[2], o[3]);
     out[2 * i + 1] = make_uint4(o[4], o[5], o[6], o[7]);
@@ -170,7 +201,7 @@ __global__ void __launch_bounds__(256) fc1_argmax_bf_kernel(const __nv_bfloat16 
                                                             const __nv_bfloat16 *__restrict__ hb, long long slot_stride,
                                                             const float *__restrict__ w, const float *__restrict__ b,
                                                             int n_class, int seq_len, long long n_rows,
-                                                            float *__restrict__ logits, uint8_t *__restrict__ pred) {
+                                                            float *__restrict__ logits, uint8_t *__restrict__ pred, int f16) {
     const long long wid = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int lane = threadIdx.x & 31;
     if (wid >= n_rows * seq_len) return;
@@ -184,8 +215,11 @@ __global__ void __launch_bounds__(256) fc1_argmax_bf_kernel(const __nv_bfloat16 
     float x[16];
 #pragma unroll
     for (int i = 0; i < 8; i++) {
-        x[2 * i] = __uint_as_float(fw[i] << 16) + __uint_as_float(bw[i] << 16);
-        x[2 * i + 1] = __uint_as_float(fw[i] & 0xffff0000u) + __uint_as_float(bw[i] & 0xffff0000u);
+        float a0, a1, c0, c1;
+        tc::unpack16(fw[i], a0, a1, f16 != 0);
+        tc::unpack16(bw[i], c0, c1, f16 != 0);
+        x[2 * i] = a0 + c0;
+        x[2 * i + 1] = a1 + c1;
     }
     float best = 0.f;
     int besti = 0;
@@ -244,18 +278,21 @@ static int upload(T **dst, const std::vector<T> &src) {
 }
 
 // bf16 hi part, and the bf16 of the remainder when `lo` is wanted (split precision)
-static inline void split_bf16(float v, uint16_t &hi, uint16_t &lo) {
-    hi = f2bf(v);
-    lo = f2bf(v - bf2f(hi));
+static inline void split16(float v, uint16_t &hi, uint16_t &lo, bool f16) {
+    hi = f2h16(v, f16);
+    lo = f2h16(v - h162f(hi, f16), f16);
 }
 
 static int build_model(Model *m, const dp_model_weights *w) {
     const int S = m->seq_len, Hd = m->hidden, RE = m->row_elems, KP = m->kfold_pad;
-    const int passes_b = m->precise ? 2 : 1;
+    const bool f16 = m->f16 != 0;
     // ---- folded operator: rows t*HP + h, columns s*KP + (w*in_ch + ch); lo copy (precise) after the hi columns
     const long long kfold = (long long)S * KP;
-    m->kcols_fold = kfold * passes_b;
+    m->kcols_fold = kfold * (m->fold_split ? 2 : 1);
     {
+        float mx = 0.f;
+        for (size_t i = 0; i < (size_t)S * Hd * S * RE; i++) mx = fmaxf(mx, fabsf(w->fold_w[i]));
+        m->fold_scale = pow2_scale(mx, f16);
         std::vector<uint16_t> B((size_t)S * HP * m->kcols_fold, 0);
         std::vector<float> bias((size_t)S * HP, 0.f);
         for (int t = 0; t < S; t++)
@@ -265,9 +302,9 @@ static int build_model(Model *m, const dp_model_weights *w) {
                 for (int s = 0; s < S; s++)
                     for (int e = 0; e < RE; e++) {
                         uint16_t hi, lo;
-                        split_bf16(src[(size_t)s * RE + e], hi, lo);
+                        split16(src[(size_t)s * RE + e] * m->fold_scale, hi, lo, f16);
                         row[(size_t)s * KP + e] = hi;
-                        if (m->precise) row[kfold + (size_t)s * KP + e] = lo;
+                        if (m->fold_split) row[kfold + (size_t)s * KP + e] = lo;
                     }
                 bias[(size_t)t * HP + h] = w->fold_b[(size_t)t * Hd + h];
             }
@@ -283,14 +320,20 @@ static int build_model(Model *m, const dp_model_weights *w) {
     {
         const char *e = getenv("DP_GRU");
         m->gru_2cta = (e && !strcmp(e, "1cta")) ? 0 : 1;
-        m->gru_wide = (e && !strcmp(e, "wide")) ? 1 : 0;
+        m->gru_wide = (e && !strcmp(e, "wide")) ? 1 : (e && !strcmp(e, "stag")) ? 2 : 0;
         const char *e2 = getenv("DP_GRU_NP");
         if (e2 && (atoi(e2) == 1 || atoi(e2) == 2 || atoi(e2) == 4)) m->gru_np = atoi(e2);
     }
     const long long kgru = 2 * HP;
-    m->kcols_gru = kgru * passes_b;
+    m->kcols_gru = kgru * (m->gru_split ? 2 : 1);
     {
         const int L = m->n_layers;
+        float mx = 0.f;
+        for (int k = 0; k < L; k++)
+            for (int d = 0; d < 2; d++)
+                for (size_t i = 0; i < (size_t)3 * Hd * Hd; i++)
+                    mx = fmaxf(mx, fmaxf(fabsf(w->gru_w_ih[k][d][i]), fabsf(w->gru_w_hh[k][d][i])));
+        m->gru_scale = pow2_scale(mx, f16);
         std::vector<uint16_t> B((size_t)L * 2 * 3 * HP * m->kcols_gru, 0);
         std::vector<float> bias((size_t)L * 2 * 4 * HP, 0.f);
         for (int k = 0; k < L; k++)
@@ -306,12 +349,12 @@ static int build_model(Model *m, const dp_model_weights *w) {
                         const float *si = wih + ((size_t)gate * Hd + u) * Hd, *sh = whh + ((size_t)gate * Hd + u) * Hd;
                         for (int c = 0; c < Hd; c++) {
                             uint16_t hi, lo;
-                            split_bf16(si[c], hi, lo);
+                            split16(si[c] * m->gru_scale, hi, lo, f16);
                             rowi[c] = hi;
-                            if (m->precise) rowi[kgru + c] = lo;
-                            split_bf16(sh[c], hi, lo);
+                            if (m->gru_split) rowi[kgru + c] = lo;
+                            split16(sh[c] * m->gru_scale, hi, lo, f16);
                             row[HP + c] = hi;
-                            if (m->precise) row[kgru + HP + c] = lo;
+                            if (m->gru_split) row[kgru + HP + c] = lo;
                         }
                     }
                     float *bb = &bias[(size_t)(k * 2 + d) * 4 * HP];
@@ -341,7 +384,7 @@ static int build_model(Model *m, const dp_model_weights *w) {
     std::vector<KChunk> tab;
     const int nfc = KP / 64;
     m->fold_tab_off = 0;
-    for (int pass = 0; pass < passes_b; pass++)      // the u8 image is exact in bf16: only the weights are split
+    for (int pass = 0; pass < (m->fold_split ? 2 : 1); pass++)      // the u8 image is exact: only the weights are split
         for (int s = 0; s < S; s++)
             for (int i = 0; i < nfc; i++) tab.push_back(KChunk{0, 64 * i, s, (int)(pass * kfold) + s * KP + 64 * i});
     m->fold_tab_n = (int)tab.size();
@@ -356,7 +399,7 @@ static int build_model(Model *m, const dp_model_weights *w) {
                 else if (k > 0) hslot = d == 0 ? bf_slot_hf(k - 1, 2) : bf_slot_hb(k - 1, 0);
                 m->gru_tab_off[k][st][d] = (int)tab.size();
                 // input chunks first (the MMA issuer relies on it), then hidden chunks.  a_src: 1 = arena, 2 = arena_lo
-                const int npass = m->precise ? 3 : 1;
+                const int npass = ((m->gru_split >> k) & 1) ? 3 : 1;
                 for (int pass = 0; pass < npass; pass++) {       // (hi,hi) (hi,lo) (lo,hi)
                     const int asrc = pass == 2 ? 2 : 1, boff = pass == 1 ? (int)kgru : 0;
                     for (int i = 0; i < HP / 64; i++)
@@ -377,7 +420,7 @@ static int build_model(Model *m, const dp_model_weights *w) {
     DP_CUDA_CHECK(cudaMemset(m->img_bf, 0, (size_t)(mc + 128) * RE * 2));
     DP_CUDA_CHECK(cudaMalloc((void **)&m->arena, (size_t)NSLOT_BF * mc * HP * 2));
     DP_CUDA_CHECK(cudaMemset(m->arena, 0, (size_t)NSLOT_BF * mc * HP * 2));
-    if (m->precise) {
+    if (m->alloc_lo) {
         DP_CUDA_CHECK(cudaMalloc((void **)&m->arena_lo, (size_t)NSLOT_BF * mc * HP * 2));
         DP_CUDA_CHECK(cudaMemset(m->arena_lo, 0, (size_t)NSLOT_BF * mc * HP * 2));
     }
@@ -388,12 +431,12 @@ static int build_model(Model *m, const dp_model_weights *w) {
     if (rc) return rc;
     rc = make_tmap_bf16_2d(&m->tm_arena, m->arena, (uint64_t)NSLOT_BF * mc, HP, HP * 2, 128);
     if (rc) return rc;
-    if (m->precise) rc = make_tmap_bf16_2d(&m->tm_arena_lo, m->arena_lo, (uint64_t)NSLOT_BF * mc, HP, HP * 2, 128);
+    if (m->alloc_lo) rc = make_tmap_bf16_2d(&m->tm_arena_lo, m->arena_lo, (uint64_t)NSLOT_BF * mc, HP, HP * 2, 128);
     else m->tm_arena_lo = m->tm_arena;
     if (rc) return rc;
     rc = make_tmap_bf16_2d(&m->tm_arena_mc, m->arena, (uint64_t)NSLOT_BF * mc, HP, HP * 2, 128 / m->gru_np);
     if (rc) return rc;
-    if (m->precise) rc = make_tmap_bf16_2d(&m->tm_arena_lo_mc, m->arena_lo, (uint64_t)NSLOT_BF * mc, HP, HP * 2, 128 / m->gru_np);
+    if (m->alloc_lo) rc = make_tmap_bf16_2d(&m->tm_arena_lo_mc, m->arena_lo, (uint64_t)NSLOT_BF * mc, HP, HP * 2, 128 / m->gru_np);
     else m->tm_arena_lo_mc = m->tm_arena_mc;
     if (rc) return rc;
     rc = make_tmap_bf16_2d(&m->tm_wfold, m->w_fold, (uint64_t)S * HP, (uint64_t)m->kcols_fold, (uint64_t)m->kcols_fold * 2, 256);
@@ -406,7 +449,7 @@ static int build_model(Model *m, const dp_model_weights *w) {
     if (rc) return rc;
     const char *e3 = getenv("DP_GRU_STATE");            // "f32": keep the fp32 state copy also in one-pass bf16 mode
     m->bf_state = 0;
-    if (m->gru_2cta && !m->precise && e3) {
+    if (m->gru_2cta && !m->alloc_lo && e3) {
         if (!strcmp(e3, "bf16")) m->bf_state = m->n_layers;
         else if (!strcmp(e3, "mixed")) m->bf_state = m->n_layers - 1;
     }
@@ -433,7 +476,7 @@ static int forward_rows(Model *m, const uint8_t *img, long long n_rows, float *l
     // 1. u8 -> bf16 (plus seq_len-1 zero rows after the last one so trailing windows see zeros, not stale data)
     {
         const long long n16 = n_rows * RE / 16;
-        u8_to_bf16_kernel<<<(unsigned)((n16 + 255) / 256), 256, 0, st>>>((const uint4 *)img, (uint4 *)m->img_bf, n16);
+        u8_to_bf16_kernel<<<(unsigned)((n16 + 255) / 256), 256, 0, st>>>((const uint4 *)img, (uint4 *)m->img_bf, n16, m->f16);
         DP_CUDA_CHECK(cudaGetLastError());
         DP_CUDA_CHECK(cudaMemsetAsync(m->img_bf + n_rows * RE, 0, (size_t)(S - 1) * RE * 2, st));
     }
@@ -449,9 +492,11 @@ static int forward_rows(Model *m, const uint8_t *img, long long n_rows, float *l
         g.n_chunks = m->fold_tab_n;
         g.M = (int)n_rows; g.N = S * HP;
         g.tiles_m = tiles_m; g.tiles_n = (S * HP) / 256;
+        g.f16 = m->f16;
+        g.epi.acc_scale = 1.f / m->fold_scale;
         g.epi.bias = m->b_fold;
         g.epi.out = m->arena;
-        g.epi.out_lo = m->precise ? m->arena_lo : nullptr;
+        g.epi.out_lo = m->alloc_lo ? m->arena_lo : nullptr;
         g.epi.ldc = HP; g.epi.out_fp32 = 0;
         g.epi.nblk = HP; g.epi.nblk_stride = mc * HP;
         int rc = launch_gemm_bf16(tmA, &m->tm_wfold, g, 256, st);
@@ -463,7 +508,8 @@ static int forward_rows(Model *m, const uint8_t *img, long long n_rows, float *l
         for (int sg = 0; sg < 3; sg++) {
             GruArgs g;
             memset(&g, 0, sizeof(g));
-            g.n_prob = 2; g.M = (int)n_rows; g.tiles_m = tiles_m; g.fast_act = m->precise ? 0 : 1;
+            g.n_prob = 2; g.M = (int)n_rows; g.tiles_m = tiles_m; g.fast_act = m->fast_act;
+            g.f16 = m->f16; g.acc_scale = 1.f / m->gru_scale;
             for (int d = 0; d < 2; d++) {
                 GruProblem &P = g.prob[d];
                 const int t = d == 0 ? sg : 2 - sg;
@@ -488,7 +534,7 @@ static int forward_rows(Model *m, const uint8_t *img, long long n_rows, float *l
                 // (fc1 takes the fp32 state)
                 const bool bf_unused = sg == 2 && k + 1 == m->n_layers && k >= m->bf_state;
                 P.h_out_bf = bf_unused ? nullptr : m->arena + (size_t)ob * mc * HP;
-                P.h_out_lo = (m->precise && !bf_unused) ? m->arena_lo + (size_t)ob * mc * HP : nullptr;
+                P.h_out_lo = (m->alloc_lo && !bf_unused) ? m->arena_lo + (size_t)ob * mc * HP : nullptr;
                 if (sg == 2 && k + 1 < m->n_layers) {
                     // sum of directions (model.py:131-133) -> bf16 input of the next layer
                     if (d == 0) {
@@ -501,7 +547,7 @@ static int forward_rows(Model *m, const uint8_t *img, long long n_rows, float *l
                         }
                         P.xsum = m->arena + (size_t)bf_slot_xn(k, 2) * mc * HP;
                         P.xsum2 = m->arena + (size_t)bf_slot_xn(k, 1) * mc * HP;
-                        if (m->precise) {
+                        if (m->alloc_lo) {
                             P.xsum_lo = m->arena_lo + (size_t)bf_slot_xn(k, 2) * mc * HP;
                             P.xsum2_lo = m->arena_lo + (size_t)bf_slot_xn(k, 1) * mc * HP;
                         }
@@ -509,11 +555,12 @@ static int forward_rows(Model *m, const uint8_t *img, long long n_rows, float *l
                         if (k < m->bf_state) P.partner_bf = m->arena + (size_t)bf_slot_hf(k, 0) * mc * HP;
                         else P.partner = m->state + (size_t)f32_slot_hf(k, 0) * mc * HP;
                         P.xsum = m->arena + (size_t)bf_slot_xn(k, 0) * mc * HP;
-                        if (m->precise) P.xsum_lo = m->arena_lo + (size_t)bf_slot_xn(k, 0) * mc * HP;
+                        if (m->alloc_lo) P.xsum_lo = m->arena_lo + (size_t)bf_slot_xn(k, 0) * mc * HP;
                     }
                 }
             }
-            int rc = m->gru_wide ? launch_gru_step2w(tmA, &m->tm_wgru96, g, st)
+            int rc = m->gru_wide == 2 ? launch_gru_step2s(tmA, &m->tm_wgru96, g, st)
+                   : m->gru_wide ? launch_gru_step2w(tmA, &m->tm_wgru96, g, st)
                    : m->gru_2cta ? launch_gru_step2(tmA_mc, &m->tm_wgru96, g, m->gru_np, st)
                                  : launch_gru_step(tmA, &m->tm_wgru, g, st);
             if (rc) return rc;
@@ -527,7 +574,7 @@ static int forward_rows(Model *m, const uint8_t *img, long long n_rows, float *l
         if (k < m->bf_state)
             fc1_argmax_bf_kernel<<<blocks, 256, 0, st>>>(m->arena + (size_t)bf_slot_hf(k, 0) * mc * HP,
                                                          m->arena + (size_t)bf_slot_hb(k, 0) * mc * HP, mc * HP, m->w_fc1,
-                                                         m->b_fc1, m->n_class, S, n_rows, logits, pred);
+                                                         m->b_fc1, m->n_class, S, n_rows, logits, pred, m->f16);
         else
             fc1_argmax_kernel<<<(unsigned)((((n_rows + 31) / 32) * S + 3) / 4), 128, (size_t)m->n_class * HP * 4, st>>>(
                                                       m->state + (size_t)f32_slot_hf(k, 0) * mc * HP,
@@ -557,7 +604,7 @@ int dp_model_create(const dp_model_weights *w, int64_t max_rows, int32_t precisi
     DP_REQUIRE(w->n_class >= 1 && w->n_class <= 16, "n_class must be in [1,16]");
     DP_REQUIRE(w->in_ch >= 1 && w->width >= 1 && (w->in_ch * w->width) % 16 == 0, "width*in_ch must be a multiple of 16");
     DP_REQUIRE(max_rows >= 1 && max_rows <= (1ll << 24), "max_rows out of range");
-    DP_REQUIRE(precision == 0 || precision == 1, "precision must be 0 (bf16) or 1 (split bf16)");
+    DP_REQUIRE(precision >= 0 && precision <= 3, "precision must be 0 (bf16), 1 (split bf16), 2 (fp16) or 3 (split fp16)");
     for (int k = 0; k < w->n_layers; k++)
         for (int d = 0; d < 2; d++)
             DP_REQUIRE(w->gru_w_ih[k][d] && w->gru_w_hh[k][d] && w->gru_b_ih[k][d] && w->gru_b_hh[k][d], "null GRU weight");
@@ -566,7 +613,16 @@ int dp_model_create(const dp_model_weights *w, int64_t max_rows, int32_t precisi
     m->seq_len = w->seq_len; m->n_layers = w->n_layers;
     m->row_elems = w->in_ch * w->width;
     m->kfold_pad = (m->row_elems + 63) / 64 * 64;
-    m->precise = precision;
+    // precision presets; the DP_FOLD_SPLIT / DP_GRU_SPLIT / DP_ACT switches exist for scripts/model_error_attribution.py,
+    // which turns the accurate variant of one error source on at a time
+    m->f16 = precision >> 1;
+    m->fold_split = precision & 1;
+    m->gru_split = (precision & 1) ? (1 << w->n_layers) - 1 : 0;
+    m->fast_act = (precision & 1) ? 0 : 1;
+    if (const char *e = getenv("DP_FOLD_SPLIT")) m->fold_split = atoi(e) ? 1 : 0;
+    if (const char *e = getenv("DP_GRU_SPLIT")) m->gru_split = atoi(e) & ((1 << w->n_layers) - 1);
+    if (const char *e = getenv("DP_ACT")) m->fast_act = !strcmp(e, "fast") ? 1 : !strcmp(e, "accurate") ? 0 : m->fast_act;
+    m->alloc_lo = m->gru_split != 0;
     m->mcap = (max_rows + 127) / 128 * 128;
     // the arena row coordinate (slot * mcap + row) must fit the int32 TMA coordinate
     if ((long long)dp::NSLOT_BF * m->mcap >= (1ll << 31)) { delete m; dp::set_error("max_rows too large"); return DP_EINVAL; }
@@ -617,10 +673,10 @@ int dp_model_peek(dp_model *h, int32_t what, int64_t n_rows, float *host_out) {
     if (what >= 0 && what < 3) {
         std::vector<uint16_t> tmp(n);
         DP_CUDA_CHECK(cudaMemcpy(tmp.data(), m->arena + (size_t)dp::bf_slot_y(what) * m->mcap * dp::HP, n * 2, cudaMemcpyDeviceToHost));
-        for (size_t i = 0; i < n; i++) host_out[i] = dp::bf2f(tmp[i]);
-        if (m->precise) {
+        for (size_t i = 0; i < n; i++) host_out[i] = dp::h162f(tmp[i], m->f16 != 0);
+        if (m->alloc_lo) {
             DP_CUDA_CHECK(cudaMemcpy(tmp.data(), m->arena_lo + (size_t)dp::bf_slot_y(what) * m->mcap * dp::HP, n * 2, cudaMemcpyDeviceToHost));
-            for (size_t i = 0; i < n; i++) host_out[i] += dp::bf2f(tmp[i]);
+            for (size_t i = 0; i < n; i++) host_out[i] += dp::h162f(tmp[i], m->f16 != 0);
         }
         return DP_OK;
     }
@@ -630,7 +686,7 @@ int dp_model_peek(dp_model *h, int32_t what, int64_t n_rows, float *host_out) {
         std::vector<uint16_t> tmp(n);
         const int bslot = d == 0 ? dp::bf_slot_hf(k - 1, t) : dp::bf_slot_hb(k - 1, t);
         DP_CUDA_CHECK(cudaMemcpy(tmp.data(), m->arena + (size_t)bslot * m->mcap * dp::HP, n * 2, cudaMemcpyDeviceToHost));
-        for (size_t i = 0; i < n; i++) host_out[i] = dp::bf2f(tmp[i]);
+        for (size_t i = 0; i < n; i++) host_out[i] = dp::h162f(tmp[i], m->f16 != 0);
         return DP_OK;
     }
     const int slot = d == 0 ? dp::f32_slot_hf(k - 1, t) : dp::f32_slot_hb(k - 1, t);

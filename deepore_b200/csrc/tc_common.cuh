@@ -3,6 +3,7 @@
 #pragma once
 #include <cuda.h>
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -195,6 +196,35 @@ __device__ __forceinline__ uint64_t make_smem_desc_sw128(uint32_t smem_addr) {
 // Instruction descriptor: kind::f16, A = B = bf16, D = fp32, both operands K-major, shape M x N.
 __host__ __device__ constexpr uint32_t make_idesc_bf16(uint32_t M, uint32_t N) {
     return (1u << 4) | (1u << 7) | (1u << 10) | ((N >> 3) << 17) | ((M >> 4) << 24);
+}
+// The same with A = B = fp16 (format code 0 in bits [7,10) and [10,13)): 11-bit significands instead of 8, same
+// tensor-pipe rate; the operands must be kept inside fp16's range by the caller (power-of-two weight scales).
+__host__ __device__ constexpr uint32_t make_idesc_f16(uint32_t M, uint32_t N) {
+    return (1u << 4) | ((N >> 3) << 17) | ((M >> 4) << 24);
+}
+__host__ __device__ constexpr uint32_t make_idesc_16(uint32_t M, uint32_t N, bool f16) {
+    return f16 ? make_idesc_f16(M, N) : make_idesc_bf16(M, N);
+}
+
+// ---- 16-bit operand formats: one flag picks fp16 or bf16 for every conversion of a kernel (warp-uniform branch)
+__device__ __forceinline__ uint32_t pack16(float a, float b, bool f16) {
+    uint32_t r;
+    if (f16) asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(b), "f"(a));   // first source -> upper half
+    else asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(b), "f"(a));
+    return r;
+}
+__device__ __forceinline__ void unpack16(uint32_t w, float &lo, float &hi, bool f16) {
+    if (f16) {
+        const float2 t = __half22float2(*reinterpret_cast<const __half2 *>(&w));
+        lo = t.x; hi = t.y;
+    } else {
+        lo = __uint_as_float(w << 16); hi = __uint_as_float(w & 0xffff0000u);
+    }
+}
+__device__ __forceinline__ float round16(float a, bool f16) {
+    float lo, hi;
+    unpack16(pack16(a, 0.f, f16), lo, hi, f16);
+    return lo;
 }
 
 }  // namespace tc

@@ -75,11 +75,6 @@ struct PipeState {
     }
 };
 
-__device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
-    __nv_bfloat162 t = __floats2bfloat162_rn(a, b);
-    return *reinterpret_cast<uint32_t *>(&t);
-}
-__device__ __forceinline__ float bf16_round(float a) { return __bfloat162float(__float2bfloat16_rn(a)); }
 
 template <int BN>
 struct GemmCfg {
@@ -146,7 +141,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
         }
     } else if (warp == 1) {
         if (lane == 0) {
-            constexpr uint32_t idesc = make_idesc_bf16(BM, BN);
+            const uint32_t idesc = make_idesc_16(BM, BN, g.f16 != 0);
             PipeState ps{0, 0};
             int as = 0; uint32_t aphase = 0;
             for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
@@ -171,6 +166,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
     } else if (warp >= 4) {
         const int wq = warp - 4;
         const GemmEpilogue &e = g.epi;
+        const bool f16 = g.f16 != 0;
+        const float asc = e.acc_scale != 0.f ? e.acc_scale : 1.f;
         int as = 0; uint32_t aphase = 0;
         for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
             const int m0 = (tile / g.tiles_n) * BM, n0 = (tile % g.tiles_n) * BN;
@@ -191,7 +188,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
                 if (!row_ok) continue;
                 float f[16];
 #pragma unroll
-                for (int i = 0; i < 16; i++) f[i] = __uint_as_float(v[i]);
+                for (int i = 0; i < 16; i++) f[i] = __uint_as_float(v[i]) * asc;
                 if (e.bias) {
 #pragma unroll
                     for (int i = 0; i < 16; i += 4) {
@@ -207,9 +204,10 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
                         const uint32_t w[4] = {r.x, r.y, r.z, r.w};
 #pragma unroll
                         for (int i = 0; i < 4; i++) {
-                            const __nv_bfloat162 p = *reinterpret_cast<const __nv_bfloat162 *>(&w[i]);
-                            f[h * 8 + 2 * i] += __low2float(p);
-                            f[h * 8 + 2 * i + 1] += __high2float(p);
+                            float lo, hi;
+                            unpack16(w[i], lo, hi, f16);
+                            f[h * 8 + 2 * i] += lo;
+                            f[h * 8 + 2 * i + 1] += hi;
                         }
                     }
                 }
@@ -226,14 +224,14 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
                 } else {
                     uint32_t p[8];
 #pragma unroll
-                    for (int i = 0; i < 8; i++) p[i] = pack_bf16(f[2 * i], f[2 * i + 1]);
+                    for (int i = 0; i < 8; i++) p[i] = pack16(f[2 * i], f[2 * i + 1], f16);
                     uint4 *op = reinterpret_cast<uint4 *>(reinterpret_cast<__nv_bfloat16 *>(e.out) + off);
                     op[0] = make_uint4(p[0], p[1], p[2], p[3]);
                     op[1] = make_uint4(p[4], p[5], p[6], p[7]);
                     if (e.out_lo) {
 #pragma unroll
                         for (int i = 0; i < 8; i++)
-                            p[i] = pack_bf16(f[2 * i] - bf16_round(f[2 * i]), f[2 * i + 1] - bf16_round(f[2 * i + 1]));
+                            p[i] = pack16(f[2 * i] - round16(f[2 * i], f16), f[2 * i + 1] - round16(f[2 * i + 1], f16), f16);
                         uint4 *lp = reinterpret_cast<uint4 *>(e.out_lo + off);
                         lp[0] = make_uint4(p[0], p[1], p[2], p[3]);
                         lp[1] = make_uint4(p[4], p[5], p[6], p[7]);
@@ -310,26 +308,6 @@ __device__ __forceinline__ float act_sigmoid(float x) {
 template <bool FAST>
 __device__ __forceinline__ float act_tanh(float x) { return FAST ? tanh_fast(x) : tanh_acc(x); }
 
-__device__ __forceinline__ void store_bf16x16(__nv_bfloat16 *dst, const float (&f)[16]) {
-    uint32_t p[8];
-#pragma unroll
-    for (int i = 0; i < 8; i++) p[i] = pack_bf16(f[2 * i], f[2 * i + 1]);
-    uint4 *op = reinterpret_cast<uint4 *>(dst);
-    op[0] = make_uint4(p[0], p[1], p[2], p[3]);
-    op[1] = make_uint4(p[4], p[5], p[6], p[7]);
-}
-__device__ __forceinline__ void store_bf16x16_lo(__nv_bfloat16 *dst, const float (&f)[16]) {
-    float r[16];
-#pragma unroll
-    for (int i = 0; i < 16; i++) r[i] = f[i] - bf16_round(f[i]);
-    store_bf16x16(dst, r);
-}
-__device__ __forceinline__ void load_f32x16(const float *src, float (&f)[16]) {
-    const float4 *p = reinterpret_cast<const float4 *>(src);
-#pragma unroll
-    for (int i = 0; i < 4; i++) { const float4 t = p[i]; f[4 * i] = t.x; f[4 * i + 1] = t.y; f[4 * i + 2] = t.z; f[4 * i + 3] = t.w; }
-}
-
 
 // ---- GRU epilogue, shared by the 1-CTA and the CTA-pair kernel ----------------------------------------------------
 // fp32 state layout (private to these kernels, fc1_argmax_kernel and dp_model_peek): BLOCKED so that one warp
@@ -354,13 +332,13 @@ __device__ __forceinline__ void state_store16(float *base, long long m, int u0, 
 // bf16 row-major [row][512] store of 16 units per row for the warp's 32 rows, full 32-byte sectors per instruction:
 // lanes 2j / 2j+1 write the two halves of row j's 32 bytes (values fetched from lane j by shuffle).  All 32 lanes call.
 __device__ __forceinline__ void rows_store_bf16(__nv_bfloat16 *base, long long m_warp0, int u0, const float (&f)[16], int M,
-                                                int lane, bool lo_part) {
+                                                int lane, bool lo_part, bool f16) {
     uint32_t p[8];
 #pragma unroll
     for (int i = 0; i < 8; i++) {
         float a = f[2 * i], b = f[2 * i + 1];
-        if (lo_part) { a -= bf16_round(a); b -= bf16_round(b); }
-        p[i] = pack_bf16(a, b);
+        if (lo_part) { a -= round16(a, f16); b -= round16(b, f16); }
+        p[i] = pack16(a, b, f16);
     }
 #pragma unroll
     for (int h2 = 0; h2 < 2; h2++) {
@@ -377,19 +355,20 @@ __device__ __forceinline__ void rows_store_bf16(__nv_bfloat16 *base, long long m
 }
 
 // 16 consecutive units of row m from bf16 rows [row][512] (32 bytes, two 16-byte loads)
-__device__ __forceinline__ void rows_load_bf16(const __nv_bfloat16 *base, long long m, int u0, float (&f)[16]) {
+__device__ __forceinline__ void rows_load_bf16(const __nv_bfloat16 *base, long long m, int u0, float (&f)[16], bool f16) {
     const uint4 *p = reinterpret_cast<const uint4 *>(base + m * GRU_HP + u0);
     const uint4 a = p[0], b = p[1];
     const uint32_t w[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
 #pragma unroll
-    for (int i = 0; i < 8; i++) { f[2 * i] = __uint_as_float(w[i] << 16); f[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u); }
+    for (int i = 0; i < 8; i++) unpack16(w[i], f[2 * i], f[2 * i + 1], f16);
 }
 
 // Gate math + state update + stores for one group of 16 hidden units of the warp's 32 rows.
 template <bool FAST_ACT>
 __device__ __forceinline__ void gru_finish16(const GruProblem &P, int M, long long m_warp0, int lane, int u0,
                                              const uint32_t (&vr)[16], const uint32_t (&vz)[16], const uint32_t (&vx)[16],
-                                             const uint32_t (&vh)[16], bool has_h, const float (&hp)[16], int dbg = 0) {
+                                             const uint32_t (&vh)[16], bool has_h, const float (&hp)[16], bool f16, float sc,
+                                             int dbg = 0) {
     const long long m = m_warp0 + lane;
     const bool row_ok = m < M;
     float hn[16];
@@ -405,42 +384,42 @@ __device__ __forceinline__ void gru_finish16(const GruProblem &P, int M, long lo
         const float br = reinterpret_cast<const float *>(&bq[0])[i & 3], bz = reinterpret_cast<const float *>(&bq[1])[i & 3];
         const float bin = reinterpret_cast<const float *>(&bq[2])[i & 3], bhn = reinterpret_cast<const float *>(&bq[3])[i & 3];
         if (dbg == 8) { hn[i] = __uint_as_float(vr[i]) + __uint_as_float(vz[i]) + __uint_as_float(vx[i]) + br + bz + bin + bhn + hp[i]; continue; }
-        const float r = act_sigmoid<FAST_ACT>(__uint_as_float(vr[i]) + br);
-        const float z = act_sigmoid<FAST_ACT>(__uint_as_float(vz[i]) + bz);
-        const float hh = (has_h ? __uint_as_float(vh[i]) : 0.f) + bhn;
-        const float nn = act_tanh<FAST_ACT>(__uint_as_float(vx[i]) + bin + r * hh);
+        const float r = act_sigmoid<FAST_ACT>(fmaf(__uint_as_float(vr[i]), sc, br));
+        const float z = act_sigmoid<FAST_ACT>(fmaf(__uint_as_float(vz[i]), sc, bz));
+        const float hh = has_h ? fmaf(__uint_as_float(vh[i]), sc, bhn) : bhn;
+        const float nn = act_tanh<FAST_ACT>(fmaf(__uint_as_float(vx[i]), sc, bin) + r * hh);
         hn[i] = fmaf(z, hp[i] - nn, nn);                  // (1-z)*n + z*h
     }
     if (dbg == 6) { if (hn[3] == 123.456f) P.h_out[0] = hn[1]; return; }
     if (row_ok && P.h_out) state_store16(P.h_out, m, u0, hn);
     if (dbg == 7) return;
-    if (P.h_out_bf) rows_store_bf16(P.h_out_bf, m_warp0, u0, hn, M, lane, false);
-    if (P.h_out_lo) rows_store_bf16(P.h_out_lo, m_warp0, u0, hn, M, lane, true);
+    if (P.h_out_bf) rows_store_bf16(P.h_out_bf, m_warp0, u0, hn, M, lane, false, f16);
+    if (P.h_out_lo) rows_store_bf16(P.h_out_lo, m_warp0, u0, hn, M, lane, true, f16);
     if (P.partner || P.partner_bf) {                       // sum of directions (model.py:131-133)
         float pt[16];
         if (row_ok && P.partner) state_load16(P.partner, m, u0, pt);
-        else if (row_ok) rows_load_bf16(P.partner_bf, m, u0, pt);
+        else if (row_ok) rows_load_bf16(P.partner_bf, m, u0, pt, f16);
         else {
 #pragma unroll
             for (int i = 0; i < 16; i++) pt[i] = 0.f;
         }
 #pragma unroll
         for (int i = 0; i < 16; i++) pt[i] += hn[i];
-        rows_store_bf16(P.xsum, m_warp0, u0, pt, M, lane, false);
-        if (P.xsum_lo) rows_store_bf16(P.xsum_lo, m_warp0, u0, pt, M, lane, true);
+        rows_store_bf16(P.xsum, m_warp0, u0, pt, M, lane, false, f16);
+        if (P.xsum_lo) rows_store_bf16(P.xsum_lo, m_warp0, u0, pt, M, lane, true, f16);
     }
     if (P.partner2 || P.partner2_bf) {
         float pt[16];
         if (row_ok && P.partner2) state_load16(P.partner2, m, u0, pt);
-        else if (row_ok) rows_load_bf16(P.partner2_bf, m, u0, pt);
+        else if (row_ok) rows_load_bf16(P.partner2_bf, m, u0, pt, f16);
         else {
 #pragma unroll
             for (int i = 0; i < 16; i++) pt[i] = 0.f;
         }
 #pragma unroll
         for (int i = 0; i < 16; i++) pt[i] += hp[i];
-        rows_store_bf16(P.xsum2, m_warp0, u0, pt, M, lane, false);
-        if (P.xsum2_lo) rows_store_bf16(P.xsum2_lo, m_warp0, u0, pt, M, lane, true);
+        rows_store_bf16(P.xsum2, m_warp0, u0, pt, M, lane, false, f16);
+        if (P.xsum2_lo) rows_store_bf16(P.xsum2_lo, m_warp0, u0, pt, M, lane, true, f16);
     }
 }
 
@@ -504,9 +483,10 @@ gru_step_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
         }
     } else if (warp == 1) {
         if (lane == 0) {
-            constexpr uint32_t idesc192 = make_idesc_bf16(BM, 192);
-            constexpr uint32_t idesc128 = make_idesc_bf16(BM, 128);
-            constexpr uint32_t idesc64 = make_idesc_bf16(BM, 64);
+            const bool f16 = g.f16 != 0;
+            const uint32_t idesc192 = make_idesc_16(BM, 192, f16);
+            const uint32_t idesc128 = make_idesc_16(BM, 128, f16);
+            const uint32_t idesc64 = make_idesc_16(BM, 64, f16);
             PipeState ps{0, 0};
             int as = 0; uint32_t aphase = 0;
             for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
@@ -584,7 +564,8 @@ gru_step_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
                 tmem_ld16(taddr + 128 + cb * 16, vx);
                 if (has_h) tmem_ld16(taddr + 192 + cb * 16, vh);
                 tmem_ld_wait();
-                gru_finish16<FAST_ACT>(P, g.M, m_warp0, lane, ub * GRU_UB + cb * 16, vr, vz, vx, vh, has_h, hp[c2], g.debug & 0xff);
+                gru_finish16<FAST_ACT>(P, g.M, m_warp0, lane, ub * GRU_UB + cb * 16, vr, vz, vx, vh, has_h, hp[c2], g.f16 != 0,
+                                       g.acc_scale != 0.f ? g.acc_scale : 1.f, g.debug & 0xff);
             }
             tc_fence_before();
             __syncwarp();
@@ -711,7 +692,7 @@ gru_step2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
         }
     } else if (warp == 1) {
         if (lane == 0 && rank == 0) {
-            constexpr uint32_t idesc192 = make_idesc_bf16(256, 192);
+            const uint32_t idesc192 = make_idesc_16(256, 192, g.f16 != 0);
             PipeState ps{0, 0};
             int as = 0; uint32_t aphase = 0;
             for (int tile = pair; tile < n_tiles; tile += n_pairs) {
@@ -761,7 +742,7 @@ gru_step2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
             // everything that does not depend on the accumulator is fetched BEFORE waiting for the MMAs
             float hp[16];
             if (P.h_prev && m < g.M && dbg != 5 && dbg != 1) state_load16(P.h_prev, m, ub * GRU_UB + cb * 16, hp);
-            else if (P.h_prev_bf && m < g.M && dbg != 5 && dbg != 1) rows_load_bf16(P.h_prev_bf, m, ub * GRU_UB + cb * 16, hp);
+            else if (P.h_prev_bf && m < g.M && dbg != 5 && dbg != 1) rows_load_bf16(P.h_prev_bf, m, ub * GRU_UB + cb * 16, hp, g.f16 != 0);
             else {
 #pragma unroll
                 for (int i = 0; i < 16; i++) hp[i] = 0.f;
@@ -782,7 +763,8 @@ gru_step2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive_cluster(tempty_bar(as), crank & ~1u);
-                gru_finish16<FAST_ACT>(P, g.M, m_warp0, lane, ub * GRU_UB + cb * 16, vr, vz, vx, vh, has_h, hp, dbg);
+                gru_finish16<FAST_ACT>(P, g.M, m_warp0, lane, ub * GRU_UB + cb * 16, vr, vz, vx, vh, has_h, hp, g.f16 != 0,
+                                       g.acc_scale != 0.f ? g.acc_scale : 1.f, dbg);
             } else {
                 tc_fence_before();
                 __syncwarp();
@@ -884,7 +866,7 @@ gru_step2w_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constan
         }
     } else if (warp == 1) {
         if (lane == 0 && rank == 0) {
-            constexpr uint32_t idesc192 = make_idesc_bf16(256, 192);
+            const uint32_t idesc192 = make_idesc_16(256, 192, g.f16 != 0);
             PipeState ps{0, 0};
             uint32_t aphase = 0;
             for (int tile = pair; tile < n_tiles; tile += n_pairs) {
@@ -933,7 +915,7 @@ gru_step2w_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constan
                 const int u0 = (ub + hb) * GRU_UB + cb * 16;
                 float hp[16];
                 if (P.h_prev && m < g.M) state_load16(P.h_prev, m, u0, hp);
-                else if (P.h_prev_bf && m < g.M) rows_load_bf16(P.h_prev_bf, m, u0, hp);
+                else if (P.h_prev_bf && m < g.M) rows_load_bf16(P.h_prev_bf, m, u0, hp, g.f16 != 0);
                 else {
 #pragma unroll
                     for (int i = 0; i < 16; i++) hp[i] = 0.f;
@@ -952,7 +934,8 @@ gru_step2w_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constan
                     __syncwarp();
                     if (lane == 0) mbar_arrive_cluster(tempty_bar, 0);
                 }
-                gru_finish16<FAST_ACT>(P, g.M, m_warp0, lane, u0, vr, vz, vx, vh, has_h, hp, dbg);
+                gru_finish16<FAST_ACT>(P, g.M, m_warp0, lane, u0, vr, vz, vx, vh, has_h, hp, g.f16 != 0,
+                                       g.acc_scale != 0.f ? g.acc_scale : 1.f, dbg);
             }
             aphase ^= 1u;
         }
@@ -983,6 +966,230 @@ int launch_gru_step2w(const CUtensorMap *tmA, const CUtensorMap *tmB96, const Gr
     const int pairs = n_tiles < max_pairs ? n_tiles : max_pairs;
     if (g.fast_act) gru_step2w_kernel<true><<<2 * pairs, GRU2_THREADS, GRUW_SMEM_BYTES, st>>>(tmA[0], tmA[1], tmA[2], tmA[3], *tmB96, g);
     else gru_step2w_kernel<false><<<2 * pairs, GRU2_THREADS, GRUW_SMEM_BYTES, st>>>(tmA[0], tmA[1], tmA[2], tmA[3], *tmB96, g);
+    DP_CUDA_CHECK(cudaGetLastError());
+    return DP_OK;
+}
+
+// ================================================================================================
+// STAGGERED wide variant (DP_GRU=stag): tile = 256 rows x 128 hidden units like gru_step2w_kernel, but the two unit
+// blocks ("halves", 256 accumulator columns each) run their K loops L chunks apart.  The accumulator of half 0 is
+// complete L chunk-times before that of half 1, and while it drains to registers the tensor pipe finishes half 1; half 0
+// of the NEXT tile then starts L chunks ahead of half 1 while half 1 drains.  The two halves therefore act as the two
+// accumulator stages the wide tile had no TMEM columns for, and every A tile still feeds the MMAs of two unit blocks
+// (29 % fewer operand bytes per FLOP out of L2 than the 64-unit tile).  Price: an A tile stays in shared memory for L
+// more chunks, so A and the weight tiles live in separate rings (A: NA x 16 KB released by half 1; weights: NB x 12 KB
+// consumed in issue order B0(c), B1(c - L)).
+constexpr int GRUS_LAG = 6;                      // chunks between the two halves
+constexpr int GRUS_NA = 9;                       // A ring stages (>= LAG + prefetch depth)
+constexpr int GRUS_NB = 6;                       // weight ring stages
+constexpr int GRUS_B_BYTES = GRU2_B_ROWS * 128;  // 12 KB per CTA and weight tile
+constexpr int GRUS_BAR_BYTES = 512;
+constexpr int GRUS_SMEM_BYTES = GRUS_NA * A_STAGE_BYTES + GRUS_NB * GRUS_B_BYTES + 1024 + GRUS_BAR_BYTES + 2 * GRU2_MAX_CHUNKS * 16;
+
+template <bool FAST_ACT>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GRU2_THREADS, 1)
+gru_step2s_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1,
+                  const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmA3,
+                  const __grid_constant__ CUtensorMap tmB96, const GruArgs g) {
+    constexpr int NA = GRUS_NA, NB = GRUS_NB, L = GRUS_LAG;
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    const uint32_t b_base = smem_base + NA * A_STAGE_BYTES;
+    const uint32_t bar_base = b_base + NB * GRUS_B_BYTES;
+    auto a_full = [&](int s) { return bar_base + 8u * s; };
+    auto a_empty = [&](int s) { return bar_base + 8u * (NA + s); };
+    auto b_full = [&](int s) { return bar_base + 8u * (2 * NA + s); };
+    auto b_empty = [&](int s) { return bar_base + 8u * (2 * NA + NB + s); };
+    auto tfull_bar = [&](int h) { return bar_base + 8u * (2 * NA + 2 * NB + h); };
+    auto tempty_bar = [&](int h) { return bar_base + 8u * (2 * NA + 2 * NB + 2 + h); };
+    const uint32_t tmem_slot = bar_base + 8u * (2 * NA + 2 * NB + 4);
+    static_assert(8 * (2 * NA + 2 * NB + 5) <= GRUS_BAR_BYTES, "barrier area too small");
+    uint8_t *smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
+    uint32_t *tmem_slot_ptr = reinterpret_cast<uint32_t *>(smem_gen + (tmem_slot - smem_base));
+    KChunk *s_chunks = reinterpret_cast<KChunk *>(smem_gen + (bar_base - smem_base) + GRUS_BAR_BYTES);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t rank = cluster_ctarank();
+    const int pair = blockIdx.x >> 1, n_pairs = gridDim.x >> 1;
+    constexpr int UBG = GRU_NUB / 2;                                          // 128-unit groups per row block
+    const int tiles_per_prob = g.tiles_m * UBG;
+    const int n_tiles = tiles_per_prob * g.n_prob;
+
+    if (warp == 0 && lane == 0) {
+        prefetch_tmap(&tmA0); prefetch_tmap(&tmA1); prefetch_tmap(&tmA2); prefetch_tmap(&tmA3);
+        prefetch_tmap(&tmB96);
+    }
+    if (warp == 1 && lane == 0) {
+        for (int s = 0; s < NA; s++) { mbar_init(a_full(s), 1); mbar_init(a_empty(s), 1); }
+        for (int s = 0; s < NB; s++) { mbar_init(b_full(s), 1); mbar_init(b_empty(s), 1); }
+        for (int h = 0; h < 2; h++) { mbar_init(tfull_bar(h), 1); mbar_init(tempty_bar(h), 2 * GRU2_EPI_WARPS); }
+        fence_barrier_init();
+    }
+    if (warp == 2) { tmem_alloc_2sm(tmem_slot, 512); tmem_relinquish_2sm(); }
+    if (warp >= 4)
+        for (int pi = 0; pi < g.n_prob; pi++)
+            for (int i = threadIdx.x - 128; i < g.prob[pi].n_chunks && i < GRU2_MAX_CHUNKS; i += GRU2_THREADS - 128)
+                s_chunks[pi * GRU2_MAX_CHUNKS + i] = g.prob[pi].chunks[i];
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot_ptr;
+    if (warp >= 4) {                                   // W_hn h columns of both halves start at zero
+        const uint32_t t0 = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + 192 + ((warp - 4) >> 2) * 16;
+        tmem_st16_zero(t0); tmem_st16_zero(t0 + 256);
+        tmem_st_wait();
+    }
+    tc_fence_before();
+    cluster_sync_all();
+    tc_fence_after();
+
+    if (warp == 0) {
+        if (lane == 0) {
+            PipeState pa{0, 0}, pb{0, 0};
+            for (int tile = pair; tile < n_tiles; tile += n_pairs) {
+                const int pi = tile / tiles_per_prob, rem = tile % tiles_per_prob;
+                const GruProblem &P = g.prob[pi];
+                const int m0 = (rem / UBG) * 256 + (int)rank * BM, ub = (rem % UBG) * 2;
+                const int brow = P.b_row_base + ub * GRU_BROWS + (int)rank * 96;
+                const int n = P.n_chunks;
+                for (int c = 0; c < n + L; c++) {
+                    if (c < n) {
+                        const KChunk ch = s_chunks[pi * GRU2_MAX_CHUNKS + c];
+                        const int src = ch.a_src & 0xff;
+                        const CUtensorMap *ma = src == 0 ? &tmA0 : src == 1 ? &tmA1 : src == 2 ? &tmA2 : &tmA3;
+                        mbar_wait(a_empty(pa.stage), pa.phase ^ 1u);
+                        if (rank == 0) mbar_expect_tx(a_full(pa.stage), 2u * (uint32_t)A_STAGE_BYTES);
+                        tma_load_2d_2sm(smem_base + pa.stage * A_STAGE_BYTES, ma, a_full(pa.stage), ch.a_col, m0 + ch.a_drow);
+                        pa.advance(NA);
+                        mbar_wait(b_empty(pb.stage), pb.phase ^ 1u);
+                        if (rank == 0) mbar_expect_tx(b_full(pb.stage), 2u * (uint32_t)GRUS_B_BYTES);
+                        tma_load_2d_2sm(b_base + pb.stage * GRUS_B_BYTES, &tmB96, b_full(pb.stage), ch.b_col, brow);
+                        pb.advance(NB);
+                    }
+                    if (c >= L) {
+                        const KChunk ch = s_chunks[pi * GRU2_MAX_CHUNKS + c - L];
+                        mbar_wait(b_empty(pb.stage), pb.phase ^ 1u);
+                        if (rank == 0) mbar_expect_tx(b_full(pb.stage), 2u * (uint32_t)GRUS_B_BYTES);
+                        tma_load_2d_2sm(b_base + pb.stage * GRUS_B_BYTES, &tmB96, b_full(pb.stage), ch.b_col, brow + GRU_BROWS);
+                        pb.advance(NB);
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0 && rank == 0) {
+            const uint32_t idesc192 = make_idesc_16(256, 192, g.f16 != 0);
+            PipeState ph{0, 0}, pt{0, 0}, pb{0, 0};          // A ring head (half 0) / tail (half 1, releases), weight ring
+            uint32_t tphase = 0;
+            for (int tile = pair; tile < n_tiles; tile += n_pairs) {
+                const int pi = tile / tiles_per_prob;
+                const int n = g.prob[pi].n_chunks;
+                for (int c = 0; c < n + L; c++) {
+                    if (c < n) {
+                        const int kind = (s_chunks[pi * GRU2_MAX_CHUNKS + c].a_src >> 8) & 0xff;
+                        if (c == 0) { mbar_wait(tempty_bar(0), tphase ^ 1u); tc_fence_after(); }
+                        mbar_wait(a_full(ph.stage), ph.phase);
+                        mbar_wait(b_full(pb.stage), pb.phase);
+                        tc_fence_after();
+                        const uint64_t da = make_smem_desc_sw128(smem_base + ph.stage * A_STAGE_BYTES);
+                        const uint64_t db = make_smem_desc_sw128(b_base + pb.stage * GRUS_B_BYTES);
+                        const uint32_t d0 = tmem_base + (kind == 0 ? 0u : 64u);   // input: columns 0..191, hidden: 64..255
+#pragma unroll
+                        for (int k = 0; k < BK / 16; k++)
+                            umma_bf16_2sm(d0, da + 2u * k, db + 2u * k, idesc192, kind == 0 ? (uint32_t)(c | k) : 1u);
+                        umma_commit_mc(b_empty(pb.stage), 3);
+                        ph.advance(NA); pb.advance(NB);
+                        if (c == n - 1) umma_commit_mc(tfull_bar(0), 3);
+                    }
+                    if (c >= L) {
+                        const int cc = c - L;
+                        const int kind = (s_chunks[pi * GRU2_MAX_CHUNKS + cc].a_src >> 8) & 0xff;
+                        if (cc == 0) { mbar_wait(tempty_bar(1), tphase ^ 1u); tc_fence_after(); }
+                        mbar_wait(b_full(pb.stage), pb.phase);
+                        tc_fence_after();
+                        const uint64_t da = make_smem_desc_sw128(smem_base + pt.stage * A_STAGE_BYTES);   // full since half 0 used it
+                        const uint64_t db = make_smem_desc_sw128(b_base + pb.stage * GRUS_B_BYTES);
+                        const uint32_t d0 = tmem_base + 256u + (kind == 0 ? 0u : 64u);
+#pragma unroll
+                        for (int k = 0; k < BK / 16; k++)
+                            umma_bf16_2sm(d0, da + 2u * k, db + 2u * k, idesc192, kind == 0 ? (uint32_t)(cc | k) : 1u);
+                        umma_commit_mc(b_empty(pb.stage), 3);
+                        umma_commit_mc(a_empty(pt.stage), 3);
+                        pt.advance(NA); pb.advance(NB);
+                        if (cc == n - 1) umma_commit_mc(tfull_bar(1), 3);
+                    }
+                }
+                tphase ^= 1u;
+            }
+        }
+    } else if (warp >= 4) {
+        // warp w: TMEM lanes 32*(w%4).., units cb = (w-4)/4 of half 0, then of half 1; each half's accumulator is handed
+        // back as soon as this warp's share of it is in registers
+        const int wq = warp & 3, cb = (warp - 4) >> 2;
+        uint32_t tphase = 0;
+        for (int tile = pair; tile < n_tiles; tile += n_pairs) {
+            const int pi = tile / tiles_per_prob, rem = tile % tiles_per_prob;
+            const GruProblem &P = g.prob[pi];
+            const int m0 = (rem / UBG) * 256 + (int)rank * BM, ub = (rem % UBG) * 2;
+            const long long m_warp0 = m0 + wq * 32;
+            const long long m = m_warp0 + lane;
+            const bool has_h = P.h_prev != nullptr || P.h_prev_bf != nullptr;
+            const uint32_t taddr = tmem_base + ((uint32_t)(wq * 32) << 16);
+#pragma unroll 1
+            for (int hb = 0; hb < 2; hb++) {
+                const int u0 = (ub + hb) * GRU_UB + cb * 16;
+                float hp[16];
+                if (P.h_prev && m < g.M) state_load16(P.h_prev, m, u0, hp);
+                else if (P.h_prev_bf && m < g.M) rows_load_bf16(P.h_prev_bf, m, u0, hp, g.f16 != 0);
+                else {
+#pragma unroll
+                    for (int i = 0; i < 16; i++) hp[i] = 0.f;
+                }
+                mbar_wait(tfull_bar(hb), tphase);
+                tc_fence_after();
+                uint32_t vr[16], vz[16], vx[16], vh[16];
+                const uint32_t t = taddr + hb * 256 + cb * 16;
+                tmem_ld16(t, vx);
+                tmem_ld16(t + 64, vr);
+                tmem_ld16(t + 128, vz);
+                if (has_h) tmem_ld16(t + 192, vh);
+                tmem_ld_wait();
+                if (has_h) { tmem_st16_zero(t + 192); tmem_st_wait(); }
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive_cluster(tempty_bar(hb), 0);
+                gru_finish16<FAST_ACT>(P, g.M, m_warp0, lane, u0, vr, vz, vx, vh, has_h, hp, g.f16 != 0,
+                                       g.acc_scale != 0.f ? g.acc_scale : 1.f, 0);
+            }
+            tphase ^= 1u;
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();
+    if (warp == 2) { tc_fence_after(); tmem_dealloc_2sm(tmem_base, 512); }
+}
+
+int launch_gru_step2s(const CUtensorMap *tmA, const CUtensorMap *tmB96, const GruArgs &g_in, cudaStream_t st) {
+    static bool attr_done[64] = {false};
+    int dev = 0;
+    DP_CUDA_CHECK(cudaGetDevice(&dev));
+    if (dev >= 64 || !attr_done[dev]) {
+        DP_CUDA_CHECK(cudaFuncSetAttribute(gru_step2s_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, GRUS_SMEM_BYTES));
+        DP_CUDA_CHECK(cudaFuncSetAttribute(gru_step2s_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, GRUS_SMEM_BYTES));
+        if (dev < 64) attr_done[dev] = true;
+    }
+    GruArgs g = g_in;
+    g.debug = 0;
+    g.tiles_m = (g.M + 255) / 256;
+    const int n_tiles = g.tiles_m * (GRU_NUB / 2) * g.n_prob;
+    if (n_tiles <= 0) return DP_OK;
+    for (int i = 0; i < g.n_prob; i++)
+        if (g.prob[i].n_chunks > GRU2_MAX_CHUNKS || g.prob[i].n_chunks < 1) { set_error("gru_step2s: bad K chunk count"); return DP_EINVAL; }
+    const int max_pairs = device_sm_count() / 2;
+    const int pairs = n_tiles < max_pairs ? n_tiles : max_pairs;
+    if (g.fast_act) gru_step2s_kernel<true><<<2 * pairs, GRU2_THREADS, GRUS_SMEM_BYTES, st>>>(tmA[0], tmA[1], tmA[2], tmA[3], *tmB96, g);
+    else gru_step2s_kernel<false><<<2 * pairs, GRU2_THREADS, GRUS_SMEM_BYTES, st>>>(tmA[0], tmA[1], tmA[2], tmA[3], *tmB96, g);
     DP_CUDA_CHECK(cudaGetLastError());
     return DP_OK;
 }

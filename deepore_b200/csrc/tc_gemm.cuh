@@ -33,6 +33,8 @@ struct GemmEpilogue {
     int nblk;                          // >0: column n is stored at (n / nblk) * nblk_stride + n % nblk
     long long nblk_stride;
     int mask_period, mask_lo, mask_hi; // period>0: rows with (m % period) outside [lo,hi) are stored as ZERO (conv padding)
+    float acc_scale;                   // accumulators are multiplied by this before the bias (0 = 1): undoes the power-of-two
+                                       // scale the fp16 weights carry
 };
 
 struct GemmArgs {
@@ -40,6 +42,7 @@ struct GemmArgs {
     int n_chunks;
     int M, N;
     int tiles_m, tiles_n;
+    int f16;                           // 16-bit operand / output format: 0 = bf16, 1 = fp16
     GemmEpilogue epi;
 };
 
@@ -67,7 +70,9 @@ struct GruArgs {
     int M;
     int tiles_m;                       // per problem: tiles_m * 8 unit blocks
     int debug;                         // timing experiments only (env DP_GRU_DEBUG): 1 skip epilogue math, 2 one MMA per k-step
-    int fast_act;                      // 1: MUFU.TANH activations (one-pass bf16 mode); 0: exp-based (split-bf16 mode)
+    int fast_act;                      // 1: MUFU.TANH activations; 0: exp-based
+    int f16;                           // 16-bit operand / state-row format: 0 = bf16, 1 = fp16
+    float acc_scale;                   // accumulators are multiplied by this before the biases (0 = 1)
 };
 
 int launch_gemm_bf16(const CUtensorMap *tmA /*[4]*/, const CUtensorMap *tmB, const GemmArgs &g, int block_n,
@@ -78,6 +83,9 @@ int launch_gru_step(const CUtensorMap *tmA /*[4]*/, const CUtensorMap *tmB, cons
 int launch_gru_step2(const CUtensorMap *tmA /*[4]*/, const CUtensorMap *tmB96, const GruArgs &g, int np, cudaStream_t st);
 // wide variant: 256 rows x 128 hidden units per tile, one accumulator stage (tmA boxes of 128 rows)
 int launch_gru_step2w(const CUtensorMap *tmA /*[4]*/, const CUtensorMap *tmB96, const GruArgs &g, cudaStream_t st);
+// staggered wide variant: the two 64-unit halves of the 128-unit tile run their K loops GRUS_LAG chunks apart, so one half's
+// accumulator drains while the tensor pipe works on the other (tmA boxes of 128 rows)
+int launch_gru_step2s(const CUtensorMap *tmA /*[4]*/, const CUtensorMap *tmB96, const GruArgs &g, cudaStream_t st);
 int device_sm_count();
 
 }  // namespace dp

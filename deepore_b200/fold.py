@@ -68,7 +68,33 @@ def row_map(x, P, affine: bool = True):
     return x
 
 
+FRONT_KEYS = ("batchNorm.weight", "batchNorm.bias", "batchNorm.running_mean", "batchNorm.running_var", "incpConv0.weight",
+              "incpConv1.weight", "conv0.weight", "conv1.weight", "conv2.weight", "conv2.bias", "conv3.weight", "conv3.bias",
+              "cnn_fc_rnn.weight", "cnn_fc_rnn.bias")
+_FOLD_CACHE: Dict[bytes, Tuple[np.ndarray, np.ndarray]] = {}      # content hash of the front tensors -> operator (last 2)
+
+
 def fold_front(state: Dict[str, np.ndarray], in_ch: int, width: int, seq_len: int = 3) -> Tuple[np.ndarray, np.ndarray]:
+    """The folded operator of `state`, memoised on the CONTENT of the tensors it depends on (composing it takes ~20 s of
+    float64 work; an engine that is re-created for a larger batch, another precision or another device reuses it)."""
+    import hashlib
+    h = hashlib.blake2b(digest_size=16)
+    h.update(repr((in_ch, width, seq_len)).encode())
+    for k in FRONT_KEYS:
+        a = np.ascontiguousarray(state[k])
+        h.update(k.encode() + str(a.dtype).encode() + repr(a.shape).encode())
+        h.update(a.view(np.uint8).reshape(-1).data)
+    key = h.digest()
+    hit = _FOLD_CACHE.get(key)
+    if hit is None:
+        hit = _fold_front(state, in_ch, width, seq_len)
+        while len(_FOLD_CACHE) >= 2:
+            _FOLD_CACHE.pop(next(iter(_FOLD_CACHE)))
+        _FOLD_CACHE[key] = hit
+    return hit
+
+
+def _fold_front(state: Dict[str, np.ndarray], in_ch: int, width: int, seq_len: int = 3) -> Tuple[np.ndarray, np.ndarray]:
     """state: numpy arrays keyed like Model.state_dict() (batchNorm.*, incpConv0/1.weight, conv0..3.*, cnn_fc_rnn.*).
 
     Returns (fold_w float32 [seq_len][hidden][seq_len][width][in_ch], fold_b float32 [seq_len][hidden]) acting on RAW

@@ -26,7 +26,11 @@ from . import _lib
 from . import fold as _fold
 from . import modelio
 
-PRECISION = {"bf16": 0, "bf16x3": 1}
+# dp_model_create precision codes.  fp16: fp16 operands (11-bit significands at the bf16 tensor-pipe rate; weights carry a
+# power-of-two scale that the epilogues divide out), fp32 accumulate and fp32 recurrent state -- the default.  *x3: operands
+# split hi + lo, three passes, fp32-class accuracy.
+PRECISION = {"bf16": 0, "bf16x3": 1, "fp16": 2, "fp16x3": 3}
+DEFAULT_PRECISION = "fp16"
 
 
 class _Engine:
@@ -176,7 +180,7 @@ class Model(nn.Module):
         return modelio.state_from_module(self)
 
     def engine(self, n_rows: int, device, precision: Optional[str] = None) -> _Engine:
-        precision = precision or getattr(self, "_precision", "bf16")
+        precision = precision or getattr(self, "_precision", DEFAULT_PRECISION)
         key = (str(device), precision, tuple((p.data_ptr(), p._version) for p in self._all_tensors()))
         eng = self.__dict__.get("_engine")
         if eng is None or self.__dict__.get("_engine_key") != key or eng.max_rows < n_rows:
@@ -229,7 +233,7 @@ class Model(nn.Module):
         return d
 
 
-def from_state(state, device="cuda", precision="bf16") -> Model:
+def from_state(state, device="cuda", precision=DEFAULT_PRECISION) -> Model:
     """Model(input_channel=4, coverage_depth=200) (the parity configuration) filled from a numpy state."""
     width = int(state["cnn_fc_rnn.weight"].shape[1] // state["conv2.weight"].shape[0])
     m = Model(input_channel=int(state["conv0.weight"].shape[1]), output_channel=int(state["conv2.weight"].shape[0]),

@@ -3,9 +3,10 @@ model (/root/reference/src/modules/model.py, torch CPU fp32) over ALL 260 pileup
 following the loop of /root/reference/src/test.py:51-89 (forward per image row, top-1, 3-way vote).
 
 Run in the build container (where /root/reference is mounted):   python oracle/make_calls_golden.py
-Stored per window: top-1 class of every (call, t), the vote of every scored row, and the top-2 logit margin of every
-(call, t) -- the GPU test (tests/test_model_gpu.py) demands identical votes wherever all three contributing margins
-exceed the logit tolerance.  Weights: deepore_b200.modelio.seeded_state(7); no checkpoint ships with the reference.
+Stored per window: the raw logits (float16-rounded copies would hide the differences the tests count, so float32), the
+top-1 class of every (call, t), the vote of every scored row, and the top-2 logit margin of every (call, t) -- the GPU
+tests (tests/test_model_gpu.py) count EVERY top-1 / vote that differs and demand that each difference sits where the
+reference's own margin is below twice the measured logit error.  Weights: deepore_b200.modelio.seeded_state(7); no checkpoint ships with the reference.
 """
 import os
 import sys
@@ -43,6 +44,7 @@ def main():
     seq_len = 3
     pred = np.zeros((nw, H - 2, 3), np.uint8)
     margin = np.zeros((nw, H - 2, 3), np.float32)
+    logits = np.zeros((nw, H - 2, 3, 3), np.float32)
     calls = np.full((nw, H), -1, np.int8)
     t0 = time.time()
     with torch.no_grad():
@@ -52,6 +54,7 @@ def main():
             N = images.size(0)
             for row in range(0, H - seq_len + 1):                                                  # test.py:59-66
                 out = model(images[:, :, row:row + seq_len, :], torch.zeros(2, N, 500))            # (N,3,3)
+                logits[b0:b0 + N, row] = out.numpy()
                 srt = out.sort(dim=-1)[0]
                 margin[b0:b0 + N, row] = (srt[..., -1] - srt[..., -2]).numpy()
                 pred[b0:b0 + N, row] = out.topk(1)[1][:, :, 0].numpy().astype(np.uint8)
@@ -60,7 +63,7 @@ def main():
         for row in range(2, H - 2):
             calls[i, row] = most_common([int(pred[i, row - 2, 2]), int(pred[i, row - 1, 1]), int(pred[i, row, 0])])
     out = os.path.join(ROOT, "tests", "golden", "bundled_calls_seed%d.npz" % SEED)
-    np.savez_compressed(out, seed=SEED, pred=pred, calls=calls, margin=margin)
+    np.savez_compressed(out, seed=SEED, pred=pred, calls=calls, margin=margin, logits=logits)
     print("wrote", out, "class histogram of calls:", np.bincount(calls[calls >= 0].astype(np.int64), minlength=3),
           "min margin", float(margin.min()))
 

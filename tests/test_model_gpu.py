@@ -52,7 +52,7 @@ def test_front_and_logits_vs_reference(gold, precision):
     assert decisive.mean() > 0.9
 
 
-@pytest.mark.parametrize("env", [{"DP_GRU": "wide"}, {"DP_GRU_NP": "2"}, {"DP_GRU_NP": "4"}, {"DP_GRU": "1cta"}])
+@pytest.mark.parametrize("env", [{"DP_GRU": "stag"}, {"DP_GRU": "wide"}, {"DP_GRU_NP": "2"}, {"DP_GRU_NP": "4"}, {"DP_GRU": "1cta"}])
 def test_gru_kernel_variants_vs_reference(gold, env, monkeypatch):
     """The opt-in GRU step kernels (256 x 128-unit tiles; clusters of 2 / 4 CTA pairs sharing A tiles by TMA multicast; the
     single-CTA kernel) against the same golden logits as the default CTA-pair kernel.  The choice is read at model creation."""
