@@ -34,14 +34,24 @@ METRIC = "genomic positions/sec (pileup encode + CNN/GRU infer)"
 UNIT = "positions/s"
 
 
-def traffic_of(kernel):
-    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the named kernel, from the committed `ncu --set full`
-    capture of this bench command (profiles/r1_traffic.json); None when no capture is recorded."""
-    p = os.path.join(ROOT, "profiles", "r1_traffic.json")
-    try:
-        return json.load(open(p))[kernel]["dram_bytes_per_launch"]
-    except Exception:
-        return None
+def traffic_of(kernel, units):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the named kernel from the committed `ncu --set full`
+    captures (profiles/r2_traffic.json, else profiles/r1_traffic.json), for the launch size (`units` = windows per encoder
+    call / image rows per GRU launch) this run uses.  -> (bytes per launch or None, name of the capture or None)."""
+    for name in ("r2_traffic.json", "r1_traffic.json"):
+        try:
+            d = json.load(open(os.path.join(ROOT, "profiles", name)))[kernel]
+        except Exception:
+            continue
+        by = d.get("by_launch_size")
+        if by is not None:
+            e = by.get(str(int(units)))
+            if e is None:
+                continue
+            return e["dram_bytes_per_launch"], e.get("source", name)
+        if d.get("launch_size") in (None, int(units)):
+            return d["dram_bytes_per_launch"], d.get("source", name)
+    return None, None
 
 
 def load_peaks():
@@ -188,19 +198,24 @@ def cpu_encode_rate(shard, seconds_budget=12.0, threads=None):
     return n / dt, n, threads, dt, first
 
 
+def _all_blas_threads():
+    try:                                      # torchrun exports OMP_NUM_THREADS=1: give the BLAS every host core back
+        from threadpoolctl import threadpool_limits
+        return threadpool_limits(limits=os.cpu_count() or 1)
+    except Exception:
+        return None
+
+
 def cpu_model_rate(images, n_windows=2):
     """Oracle port of model.py + the test.py decode (oracle/model_oracle.py, numpy float32 on the BLAS threads):
-    windows/s for whole-image inference (CNN once per image row, the cheapest correct CPU schedule)."""
+    windows/s for whole-image inference with the DE-DUPLICATED schedule (CNN once per image row, the cheapest correct CPU
+    schedule -- the reference itself runs the CNN three times per row, see cpu_torch_rate)."""
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import model_oracle as mo
     from deepore_b200 import modelio
     st = modelio.seeded_state(MODEL_SEED)
     n = min(n_windows, images.shape[0])
-    try:                                      # torchrun exports OMP_NUM_THREADS=1: give the BLAS every host core back
-        from threadpoolctl import threadpool_limits
-        limits = threadpool_limits(limits=os.cpu_count() or 1)
-    except Exception:
-        limits = None
+    limits = _all_blas_threads()
     t = time.perf_counter()
     for i in range(n):
         lg = mo.forward_image(st, images[i], dtype=np.float32)
@@ -211,16 +226,60 @@ def cpu_model_rate(images, n_windows=2):
     return n / dt, n, dt
 
 
-def cpu_path_rate(shard, stage, enc_budget=8.0, model_windows=2):
-    """positions/s of the CPU port for encode (+ model): per-window times of the two stages add up."""
+_TORCH_MODEL = None
+
+
+def cpu_torch_rate(images, seconds_budget=10.0, call_batch=32, min_calls=4):
+    """What the reference's own test.py executes, on the host cores: nn.Conv2d / nn.BatchNorm2d / nn.Linear / nn.GRU modules
+    filled from the same seeded state (oracle/torch_model.py, forward restated from model.py:93-156), torch CPU fp32,
+    torch.set_num_threads(all cores), call batch 32, the reference's NAIVE schedule (every forward call runs the
+    CNN on its three rows, test.py:59-66).  Runs forward calls for `seconds_budget` seconds (at least `min_calls`) and
+    returns windows/s = call_batch / (148 * seconds per call)."""
+    global _TORCH_MODEL
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import torch
+    import torch_model as tm
+    from deepore_b200 import modelio
+    torch.set_num_threads(os.cpu_count() or 1)
+    if _TORCH_MODEL is None:
+        _TORCH_MODEL = tm.build(modelio.seeded_state(MODEL_SEED))
+    m = _TORCH_MODEL
+    reps = -(-call_batch // images.shape[0])
+    batch = np.concatenate([images] * reps, axis=0)[:call_batch]
+    x = (torch.from_numpy(np.ascontiguousarray(batch)).permute(0, 3, 1, 2).float() / 255.0).contiguous()
+    hidden = torch.zeros(2, call_batch, m.hidden_size)
+    calls, row = 0, 0
+    with torch.no_grad():
+        tm.forward(m, x[:, :, 0:3, :], hidden)                 # untimed: thread pool / primitive cache warm-up
+        t = time.perf_counter()
+        while calls < min_calls or time.perf_counter() - t < seconds_budget:
+            tm.forward(m, x[:, :, row:row + 3, :], hidden)
+            row = (row + 1) % 148
+            calls += 1
+        dt = time.perf_counter() - t
+    return call_batch / (148.0 * dt / calls), calls, dt, torch.get_num_threads()
+
+
+def cpu_path_rate(shard, stage, enc_budget=8.0, model_windows=2, torch_budget=10.0):
+    """positions/s of the CPU implementation for encode (+ model): per-window times of the two stages add up.  The model
+    stage is timed twice -- the numpy port with the de-duplicated schedule and the torch-CPU modules with the reference's
+    naive schedule -- and the FASTER of the two enters the value.  -> (windows/s, threads, sample text, legs dict)."""
     wps_e, n_e, threads, dt_e, imgs = cpu_encode_rate(shard, seconds_budget=enc_budget)
     sec_per_window = 1.0 / wps_e
     sample = "%d windows encoded by oracle/pileup_oracle.c on %d threads (%.1f s)" % (n_e, threads, dt_e)
+    legs = {"encoder_c_port_windows_per_s": wps_e}
     if stage != "encode":
         wps_m, n_m, dt_m = cpu_model_rate(imgs, model_windows)
-        sec_per_window += 1.0 / wps_m
-        sample += "; %d of them through oracle/model_oracle.py (numpy fp32, BLAS threads, %.1f s)" % (n_m, dt_m)
-    return 1.0 / sec_per_window, threads, sample
+        wps_t, n_t, dt_t, nth = cpu_torch_rate(imgs, torch_budget)
+        legs.update({"model_numpy_port_windows_per_s": wps_m, "model_numpy_port_schedule": "de-duplicated (CNN once per row)",
+                     "model_torch_cpu_windows_per_s": wps_t, "model_torch_cpu_schedule": "naive 3-row calls, call batch 32",
+                     "model_torch_cpu_threads": nth, "model_leg_used": "numpy_port" if wps_m >= wps_t else "torch_cpu"})
+        sec_per_window += 1.0 / max(wps_m, wps_t)
+        sample += ("; model: %d windows through oracle/model_oracle.py (numpy fp32, de-duplicated schedule, %.1f s) = %.3g "
+                   "windows/s; %d forward calls of batch 32 through oracle/torch_model.py (torch CPU fp32 nn modules, the "
+                   "reference's naive schedule, %d threads, %.1f s) = %.3g windows/s; faster leg used"
+                   % (n_m, dt_m, wps_m, n_t, nth, dt_t, wps_t))
+    return 1.0 / sec_per_window, threads, sample, legs
 
 
 def run_reference(args, rank, world):
@@ -231,12 +290,13 @@ def run_reference(args, rank, world):
     wl = SyntheticWorkload(stride=args.stride)
     sh = wl.shards(0, min(args.windows, 2048), 1)[0]
     total = max(1, args.steps + args.warmup)
-    enc_budget = max(1.0, min(8.0, 60.0 / total))
+    enc_budget = max(1.0, min(8.0, 50.0 / total))
+    torch_budget = max(1.5, min(8.0, 50.0 / total))
     mw = 2 if total <= 6 else 1
-    rates, threads, sample = [], 1, ""
+    rates, threads, sample, legs = [], 1, "", {}
     t0 = time.perf_counter()
     for i in range(args.warmup + args.steps):
-        wps, threads, sample = cpu_path_rate(sh, args.stage, enc_budget, mw)
+        wps, threads, sample, legs = cpu_path_rate(sh, args.stage, enc_budget, mw, torch_budget)
         if i >= args.warmup:
             rates.append(wps)
     wps = float(np.mean(rates))
@@ -246,11 +306,38 @@ def run_reference(args, rank, world):
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "u8" if args.stage == "encode" else "f32", "data": "synthetic",
             "config": {"workload": WORKLOAD % args.stride, "stage": args.stage,
-                       "note": "bounded sample per step; CPU ports of Pileup.py / model.py (the reference is Python and "
-                               "needs /root/reference + pysam, absent on the GPU box)"},
-            "cpu_baseline": {"value": val, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+                       "note": "bounded sample per step; CPU ports of Pileup.py (C) and model.py (numpy port and torch-CPU "
+                               "nn modules); the reference itself is Python + pysam + /root/reference, absent on the GPU box"},
+            "cpu_baseline": {"value": val, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample, "legs": legs},
             "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
+
+
+def parity_block(dev, precision):
+    """Parity of the precision this run is timed in, on the committed goldens (outputs of the UNMODIFIED reference model over
+    the 260 bundled NA12878 pileup images; no oracle/ import): logits max-abs / rms, top-1 classes and votes that differ,
+    counted over all of them.  Outside every timed region."""
+    import torch
+    from deepore_b200 import model as dmodel, modelio
+    gc = np.load(os.path.join(ROOT, "tests", "golden", "bundled_calls_seed7.npz"))
+    img = torch.from_numpy(np.load(os.path.join(ROOT, "tests", "golden", "bundled_na12878.npz"))["img"]).to(dev)
+    m = dmodel.from_state(modelio.seeded_state(int(gc["seed"])), dev, precision)
+    logits, pred = m.forward_windows(img)
+    nw, H = int(img.shape[0]), int(img.shape[1])
+    votes, _ = dmodel.vote(pred.view(-1, 3), nw, H, 3)
+    torch.cuda.synchronize(dev)
+    lg = logits.cpu().numpy()[:, :148]
+    pr = pred.cpu().numpy()[:, :148]
+    v = votes.cpu().numpy()[:, 2:148]
+    d = lg - gc["logits"]
+    out = {"precision": precision, "golden": "tests/golden/bundled_calls_seed7.npz (unmodified reference model, torch CPU fp32, "
+           "260 bundled NA12878 windows x 148 calls)", "logits_max_abs": float(np.abs(d).max()),
+           "logits_rms": float(np.sqrt((d ** 2).mean())), "logit_scale": float(np.abs(gc["logits"]).max()),
+           "n_argmax": int(pr.size), "n_argmax_diff": int((pr != gc["pred"]).sum()),
+           "n_votes": int(v.size), "n_vote_diff": int((v != gc["calls"][:, 2:148]).sum())}
+    del m
+    torch.cuda.empty_cache()
+    return out
 
 
 # ----------------------------------------------------------------------------------------------------
@@ -267,6 +354,8 @@ def main():
     ap.add_argument("--precision", default="fp16", choices=["bf16", "bf16x3", "fp16", "fp16x3"])
     ap.add_argument("--stride", type=int, default=100)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-x3", action="store_true", help="skip the extra pass in the split (x3) precision")
+    ap.add_argument("--no-parity", action="store_true", help="skip the parity block (golden windows through the model)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
 
@@ -293,10 +382,13 @@ def main():
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
 
-    # ---- workload: rank r owns a contiguous run of interval shards (weak scaling: fixed work per GPU, no collective)
+    # ---- workload: rank r owns a contiguous run of interval shards (weak scaling: fixed work per GPU, no data-path
+    # collective; deepore_b200/sharding.py cuts the window axis, results are gathered on the host)
+    from deepore_b200 import sharding
     nsteps = args.steps + args.warmup
     wl = SyntheticWorkload(stride=args.stride)
-    first = rank * nsteps * args.windows
+    first, last = sharding.rank_range(world * nsteps * args.windows, world, rank)
+    assert last - first == nsteps * args.windows
     shards = wl.shards(first, args.windows, nsteps)
     while len(shards) < nsteps:                                   # wrapped past the contig end
         shards += wl.shards(0, args.windows, nsteps - len(shards))
@@ -306,11 +398,17 @@ def main():
     H, W = enc.H, enc.W
     with_model = args.stage == "e2e"
     mchunk = min(args.model_chunk, nw)
-    model = eng = None
+    engines = {}
     if with_model:
         from deepore_b200 import model as dmodel, modelio
-        model = dmodel.from_state(modelio.seeded_state(MODEL_SEED), dev, args.precision)
-        eng = model.engine(mchunk * H, dev)
+        state = modelio.seeded_state(MODEL_SEED)
+
+        def engine_for(precision):
+            if precision not in engines:
+                m = dmodel.from_state(state, dev, precision)
+                engines[precision] = (m, m.engine(mchunk * H, dev))
+            return engines[precision][1]
+        engine_for(args.precision)
     # two rotating output sets (step i+1 may be encoded while step i's results drain to the host)
     outs = [dict(img=torch.empty((nw, H, W, 4), dtype=torch.uint8, device=dev),
                  rowpos=torch.empty((nw, H), dtype=torch.int32, device=dev),
@@ -318,40 +416,43 @@ def main():
                  status=torch.empty((nw,), dtype=torch.int32, device=dev),
                  pred=torch.empty((nw * H, 3), dtype=torch.uint8, device=dev),
                  calls=torch.empty((nw, H), dtype=torch.int8, device=dev)) for _ in range(2)]
-    host_status = torch.empty((nw,), dtype=torch.int32).pin_memory()
+    host_status = torch.empty((nsteps, nw), dtype=torch.int32).pin_memory()
     host_rowpos = torch.empty((nw, H), dtype=torch.int32).pin_memory()
-    host_calls = torch.empty((nw, H), dtype=torch.int8).pin_memory()
+    host_calls = torch.empty((nsteps, nw, H), dtype=torch.int8).pin_memory()
+    host_group = dist.new_group(backend="gloo") if world > 1 else None      # host path of the result gather
     import ctypes as C
 
-    def step_device(i):
-        sb = bufs[i]
-        o = outs[i & 1]
-        n = sb.n_windows
-        enc.encode(sb, o["img"][:n], o["rowpos"][:n], o["rowins"][:n], o["status"][:n])
-        launches = 4                                   # prep_reads, base_codes, encode_windows_v3 (fast), encode_windows (exact, listed windows)
-        if with_model:
-            rows = o["img"].view(nw * H, W, 4)
-            for c0 in range(0, n, mchunk):
-                c1 = min(n, c0 + mchunk)
-                eng.forward_rows(rows[c0 * H:c1 * H], want_logits=False, want_pred=True, pred=o["pred"][c0 * H:c1 * H])
-                launches += 12                         # u8->bf16, folded GEMM, 9 GRU steps, fc1+argmax
-            st = torch.cuda.current_stream(dev)
-            _lib.check(_lib.lib().dp_vote(o["pred"].data_ptr(), n, H, 3, o["calls"].data_ptr(), None, None,
-                                          C.c_void_p(st.cuda_stream)), "dp_vote")
-            launches += 1
-        return launches
+    def make_steps(eng):
+        def step_device(i):
+            sb = bufs[i]
+            o = outs[i & 1]
+            n = sb.n_windows
+            enc.encode(sb, o["img"][:n], o["rowpos"][:n], o["rowins"][:n], o["status"][:n])
+            launches = 4                               # prep_reads, base_codes, encode_windows_v3 (fast), encode_windows (exact, listed windows)
+            if with_model:
+                rows = o["img"].view(nw * H, W, 4)
+                for c0 in range(0, n, mchunk):
+                    c1 = min(n, c0 + mchunk)
+                    eng.forward_rows(rows[c0 * H:c1 * H], want_logits=False, want_pred=True, pred=o["pred"][c0 * H:c1 * H])
+                    launches += 12                     # u8->16-bit, folded GEMM, 9 GRU steps, fc1+argmax
+                st = torch.cuda.current_stream(dev)
+                _lib.check(_lib.lib().dp_vote(o["pred"].data_ptr(), n, H, 3, o["calls"].data_ptr(), None, None,
+                                              C.c_void_p(st.cuda_stream)), "dp_vote")
+                launches += 1
+            return launches
 
-    def step_e2e(i):
-        sb = bufs[i]
-        sb.upload()
-        k = step_device(i)
-        o = outs[i & 1]
-        n = sb.n_windows
-        host_status[:n].copy_(o["status"][:n], non_blocking=True)
-        host_rowpos[:n].copy_(o["rowpos"][:n], non_blocking=True)
-        if with_model:
-            host_calls[:n].copy_(o["calls"][:n], non_blocking=True)
-        return k
+        def step_e2e(i):
+            sb = bufs[i]
+            sb.upload()
+            k = step_device(i)
+            o = outs[i & 1]
+            n = sb.n_windows
+            host_status[i, :n].copy_(o["status"][:n], non_blocking=True)
+            host_rowpos[:n].copy_(o["rowpos"][:n], non_blocking=True)
+            if with_model:
+                host_calls[i, :n].copy_(o["calls"][:n], non_blocking=True)
+            return k
+        return step_device, step_e2e
 
     def barrier():
         torch.cuda.synchronize(dev)
@@ -359,19 +460,18 @@ def main():
             dist.barrier()
         torch.cuda.synchronize(dev)
 
-    def timed(fn, sampler=None, profile=False):
+    def timed(fn, sampler=None, profile_eng=None):
         for b in bufs:
             b.upload()
         for i in range(args.warmup):
             fn(i)
         barrier()
-        if profile and eng is not None:
-            eng.profile(True)
+        if profile_eng is not None:
+            profile_eng.profile(True)
         if sampler:
             sampler.mark()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         launches = 0
-        enc_evs = []
         e0.record()
         for i in range(args.warmup, nsteps):
             launches += fn(i)
@@ -379,9 +479,9 @@ def main():
         barrier()
         clocks = sampler.stop() if sampler else None
         prof = None
-        if profile and eng is not None:
-            prof = eng.profile_read()
-            eng.profile(False)
+        if profile_eng is not None:
+            prof = profile_eng.profile_read()
+            profile_eng.profile(False)
         ms = e0.elapsed_time(e1)
         if world > 1:
             t = torch.tensor([ms], dtype=torch.float64, device=dev)
@@ -389,8 +489,21 @@ def main():
             ms = float(t.item())
         return ms, launches, clocks, prof
 
+    def gather_results():
+        """Host-side gather of the timed steps' call records on rank 0 (interval order = rank order), timed with the host
+        clock, max over ranks: the one piece of the multi-GPU path that is not device work."""
+        if world == 1:
+            return 0.0, None
+        local = host_calls[args.warmup:].numpy().reshape(-1, H)
+        dist.barrier(group=host_group)
+        t0 = time.perf_counter()
+        allc = sharding.gather_on_host(local, group=host_group, dst=0)
+        dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64)
+        dist.all_reduce(dt, op=dist.ReduceOp.MAX, group=host_group)
+        return float(dt.item()) * 1e3, allc
+
     def time_encoder_alone():
-        """Average duration of the encoder launch pair over the timed shards (CUDA events on the launching stream)."""
+        """Average duration of the encoder launch group over the timed shards (CUDA events on the launching stream)."""
         evs = []
         for i in range(args.warmup, nsteps):
             sb, o = bufs[i], outs[i & 1]
@@ -405,29 +518,50 @@ def main():
 
     # instrumented pass (CUDA events around every model kernel -> kernel shares and the roofline's launch time), then the
     # pass `value` is taken from: the same K steps without the per-kernel events, clocks sampled during it
+    eng = engines[args.precision][1] if with_model else None
+    step_device, step_e2e = make_steps(eng)
     prof = ms_prof = None
     if with_model:
-        ms_prof, _, _, prof = timed(step_device, None, profile=True)
-    ms_dev, launches, clocks, _ = timed(step_device, sampler, profile=False)
+        ms_prof, _, _, prof = timed(step_device, None, profile_eng=eng)
+    ms_dev, launches, clocks, _ = timed(step_device, sampler)
     if ms_prof is None:
         ms_prof = ms_dev
     ms_e2e, _, _, _ = timed(step_e2e)
+    gather_ms, gathered = gather_results()
+    fallbacks = enc.fallback_count()                               # of the last timed shard (synchronises)
+    st_host = host_status[args.warmup:].numpy()
+    assert (st_host == 0).all(), "a timed shard returned a non-zero window status: %s" % np.unique(st_host)
+    if with_model:
+        hc = host_calls[args.warmup:].numpy()
+        assert ((hc[:, :, 2:148] >= 0) & (hc[:, :, 2:148] < 3)).all() and (hc[:, :, :2] == -1).all(), "calls out of range"
     enc_ms = time_encoder_alone()
+    # the same path in the parity-grade precision (operands split hi + lo, three passes), fewer words: value / e2e only
+    x3 = None
+    if with_model and not args.precision.endswith("x3") and not args.no_x3:
+        px3 = args.precision + "x3"
+        sd3, se3 = make_steps(engine_for(px3))
+        ms3, _, _, _ = timed(sd3)
+        ms3e, _, _, _ = timed(se3)
+        x3 = (px3, ms3, ms3e)
 
     win_timed = sum(b.n_windows for b in bufs[args.warmup:])
     tot_windows = win_timed * world
     value = tot_windows * args.stride / (ms_dev * 1e-3)
-    e2e_value = tot_windows * args.stride / (ms_e2e * 1e-3)
+    e2e_value = tot_windows * args.stride / ((ms_e2e + gather_ms) * 1e-3)
 
     if rank == 0:
+        if gathered is not None:
+            assert gathered.shape == (tot_windows, H) and np.array_equal(gathered[:win_timed], host_calls[args.warmup:].numpy().reshape(-1, H))
         peaks = load_peaks()
         alg = sum(algorithmic_bytes(sh) for sh in shards[args.warmup:])
         enc_achieved = alg / args.steps / (enc_ms * 1e-3) / 1e9
+        enc_traffic, enc_tsrc = traffic_of("encoder", nw)
         enc_roof = {"bound": "hbm", "achieved": enc_achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
                     "frac": enc_achieved / peaks["hbm_gbs"], "peak_source": peaks["source"],
                     "kernel": "prep_reads_kernel+base_codes_kernel+encode_windows_v3_kernel+encode_windows_kernel",
-                    "ms_per_launch": enc_ms, "traffic": traffic_of("encoder"),
-                    "algorithmic_bytes_per_window": alg / max(1, win_timed)}
+                    "ms_per_launch": enc_ms, "traffic": enc_traffic, "traffic_source": enc_tsrc,
+                    "algorithmic_bytes_per_window": alg / max(1, win_timed), "windows_per_launch": nw,
+                    "fallback_windows_last_shard": fallbacks}
         h2d = int(np.mean([b.nbytes for b in bufs[args.warmup:]]))
         d2h = int(nw * 4 + nw * H * 4 + (nw * H if with_model else 0))
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
@@ -438,35 +572,65 @@ def main():
                            "model_chunk_windows": mchunk if with_model else None,
                            "weights": "random init, modelio.seeded_state(%d)" % MODEL_SEED if with_model else None,
                            "l2": "every step reads a new shard and writes %.0f MB of pileup tensors (> L2)"
-                                 % (nw * H * W * 4 / 1e6)},
+                                 % (nw * H * W * 4 / 1e6),
+                           "sharding": "deepore_b200.sharding.rank_range over %d windows" % (world * nsteps * nw)},
                 "windows_per_s": tot_windows / (ms_dev * 1e-3),
-                "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
-                "gpu_launches": launches, "clocks": clocks}
+                "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                        "host_gather_ms": gather_ms},
+                "gpu_launches": launches, "clocks": clocks, "status_checked": "all timed windows returned status 0; calls in range"}
+        if x3 is not None:
+            line["value_" + x3[0]] = tot_windows * args.stride / (x3[1] * 1e-3)
+            line["e2e_" + x3[0]] = tot_windows * args.stride / ((x3[2] + gather_ms) * 1e-3)
         if with_model and prof:
             g_ms, g_n = prof["gru_step"]
             rows_per_launch = mchunk * H
             n_layers = 3
-            flop_per_launch = rows_per_launch * ((n_layers * 3 - 1) * FLOP_GRU_STEP_PER_ROW + FLOP_GRU_STEP0_PER_ROW) / (n_layers * 3)
+            # FLOPs of the calls test.py scores: 148 of the 150 rows of a window (rows 148, 149 run through the tiles but no
+            # 3-row window starts there), unpadded sizes, hidden product skipped where h_prev == 0
+            calls_per_launch = mchunk * (H - 2)
+            flop_per_launch = calls_per_launch * ((n_layers * 3 - 1) * FLOP_GRU_STEP_PER_ROW + FLOP_GRU_STEP0_PER_ROW) / (n_layers * 3)
             ach = flop_per_launch / (g_ms / max(1, g_n) * 1e-3) / 1e12
+            g_traffic, g_tsrc = traffic_of("gru_step", rows_per_launch)
             line["roofline"] = {"bound": "tensor", "achieved": ach, "peak": peaks["bf16_tflops_sustained"],
-                                "unit": "TFLOP/s", "frac": ach / peaks["bf16_tflops_sustained"], "traffic": traffic_of("gru_step"),
-                                "peak_source": peaks["source"] + " (sustained bf16)", "kernel": "gru_step2_kernel",
+                                "unit": "TFLOP/s", "frac": ach / peaks["bf16_tflops_sustained"], "traffic": g_traffic,
+                                "traffic_source": g_tsrc,
+                                "peak_source": peaks["source"] + " (sustained bf16; fp16 runs at the same tensor-pipe rate)",
+                                "kernel": "gru_step2_kernel",
                                 "ms_per_launch": g_ms / max(1, g_n), "launches": g_n,
-                                "algorithmic_flop_per_launch": flop_per_launch,
+                                "algorithmic_flop_per_launch": flop_per_launch, "rows_per_launch": rows_per_launch,
+                                "calls_per_launch": calls_per_launch,
                                 "share_of_step": g_ms / ms_dev,
                                 "share_of_instrumented_pass": g_ms / ms_prof}
             f_ms, f_n = prof["fold_gemm"]
-            fach = rows_per_launch * FLOP_FOLD_PER_ROW / (f_ms / max(1, f_n) * 1e-3) / 1e12
+            fach = calls_per_launch * FLOP_FOLD_PER_ROW / (f_ms / max(1, f_n) * 1e-3) / 1e12
             line["kernels"] = {k: {"ms_total": v[0], "launches": v[1], "share_of_step": v[0] / ms_dev} for k, v in prof.items()}
             line["kernels"]["fold_gemm"]["achieved_tflops"] = fach
             line["kernels"]["encoder"] = {"ms_per_launch_pair": enc_ms, "share_of_step": enc_ms * args.steps / ms_dev}
             line["roofline_encoder"] = enc_roof
         else:
             line["roofline"] = enc_roof
+        if with_model and not args.no_parity:
+            line["parity"] = parity_block(dev, args.precision)
+            if x3 is not None:
+                line["parity_" + x3[0]] = parity_block(dev, x3[0])
         if not args.no_cpu_baseline and world == 1:            # rank 0 at N=1 only (torchrun pins OMP_NUM_THREADS=1)
-            val, threads, sample = cpu_path_rate(shards[args.warmup], args.stage)
+            sh0 = shards[args.warmup]
+            val, threads, sample, legs = cpu_path_rate(sh0, args.stage)
             line["cpu_baseline"] = {"value": val * args.stride, "unit": UNIT, "cores": threads, "kind": "port",
-                                    "sample": sample}
+                                    "sample": sample, "legs": legs}
+            # the sample the C port just encoded, against what the CUDA encoder wrote for the same windows of that shard
+            sys.path.insert(0, os.path.join(ROOT, "oracle"))
+            import pileup_oracle as po
+            ncheck = min(64, sh0.n_windows)
+            want = po.encode_windows(sh0.reads, sh0.win_qs[:ncheck], sh0.win_lo[:ncheck], sh0.win_hi[:ncheck], sh0.ref,
+                                     sh0.ref_base)[0]
+            o = outs[args.warmup & 1]
+            bufs[args.warmup].upload()
+            enc.encode(bufs[args.warmup], o["img"], o["rowpos"], o["rowins"], o["status"])
+            torch.cuda.synchronize(dev)
+            same = bool(np.array_equal(o["img"][:ncheck].cpu().numpy(), want))
+            assert same, "pileup tensors of the first timed shard differ from the CPU port"
+            line["output_checked"] = "%d windows of the first timed shard byte-identical to the CPU port" % ncheck
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

@@ -91,8 +91,10 @@ struct Model {
     float *w_fc1 = nullptr, *b_fc1 = nullptr;   // [n_class][HP], [n_class]
     KChunk *tables = nullptr;
     int fold_tab_off = 0, fold_tab_n = 0;
+    int fold3_tab_off = 0;         // the same chunks addressing the image as [calls][seq_len * row_elems] (forward_triples)
     int gru_tab_off[3][3][2], gru_tab_n[3][3][2];
     long long kcols_fold = 0, kcols_gru = 0;
+    CUtensorMap tm_img3;           // image buffer viewed as one row of seq_len * row_elems elements per forward call
     CUtensorMap tm_img, tm_arena, tm_arena_lo, tm_wfold, tm_wgru, tm_wgru96, tm_arena_mc, tm_arena_lo_mc;
     int gru_np = 1;                // CTA pairs per cluster of the pair kernel (A tiles multicast between them); env DP_GRU_NP
     int gru_wide = 0;              // env DP_GRU=wide: 256 x 128-unit tiles (gru_step2w_kernel); DP_GRU=stag: the same with
@@ -388,6 +390,13 @@ static int build_model(Model *m, const dp_model_weights *w) {
         for (int s = 0; s < S; s++)
             for (int i = 0; i < nfc; i++) tab.push_back(KChunk{0, 64 * i, s, (int)(pass * kfold) + s * KP + 64 * i});
     m->fold_tab_n = (int)tab.size();
+    // Model.forward(x, hidden) of the reference API hands over ONE 3-row window per sample (test.py:63-66): the image buffer
+    // is then [calls][3 * row_elems] and slot s of call m sits at column s * row_elems of row m.  The padded tail of a slot's
+    // last chunk reads the first pixels of the next slot (or TMA zero fill); the weight columns there are zero.
+    m->fold3_tab_off = (int)tab.size();
+    for (int pass = 0; pass < (m->fold_split ? 2 : 1); pass++)
+        for (int s = 0; s < S; s++)
+            for (int i = 0; i < nfc; i++) tab.push_back(KChunk{3, s * RE + 64 * i, 0, (int)(pass * kfold) + s * KP + 64 * i});
     const long long mc = m->mcap;
     for (int k = 0; k < m->n_layers; k++)
         for (int st = 0; st < 3; st++)
@@ -429,6 +438,8 @@ static int build_model(Model *m, const dp_model_weights *w) {
     // ---- tensor maps
     rc = make_tmap_bf16_2d(&m->tm_img, m->img_bf, (uint64_t)(mc + 128), (uint64_t)RE, (uint64_t)RE * 2, 128);
     if (rc) return rc;
+    rc = make_tmap_bf16_2d(&m->tm_img3, m->img_bf, (uint64_t)((mc + 128) / S), (uint64_t)S * RE, (uint64_t)S * RE * 2, 128);
+    if (rc) return rc;
     rc = make_tmap_bf16_2d(&m->tm_arena, m->arena, (uint64_t)NSLOT_BF * mc, HP, HP * 2, 128);
     if (rc) return rc;
     if (m->alloc_lo) rc = make_tmap_bf16_2d(&m->tm_arena_lo, m->arena_lo, (uint64_t)NSLOT_BF * mc, HP, HP * 2, 128);
@@ -456,7 +467,10 @@ static int build_model(Model *m, const dp_model_weights *w) {
     return rc;
 }
 
-static int forward_rows(Model *m, const uint8_t *img, long long n_rows, float *logits, uint8_t *pred, cudaStream_t st) {
+// triples == 0: img is a stack of n_rows image rows and call r reads rows r .. r+seq_len-1 (every sliding window);
+// triples == 1: img is n_rows independent windows of seq_len rows each (the reference's Model.forward call)
+static int forward_rows(Model *m, const uint8_t *img, long long n_rows, float *logits, uint8_t *pred, cudaStream_t st,
+                        int triples = 0) {
     const int RE = m->row_elems, S = m->seq_len;
     const long long mc = m->mcap;
     size_t prof_base = 0;
@@ -475,20 +489,21 @@ static int forward_rows(Model *m, const uint8_t *img, long long n_rows, float *l
     mark();
     // 1. u8 -> bf16 (plus seq_len-1 zero rows after the last one so trailing windows see zeros, not stale data)
     {
-        const long long n16 = n_rows * RE / 16;
+        const long long n_img_rows = triples ? n_rows * S : n_rows;
+        const long long n16 = n_img_rows * RE / 16;
         u8_to_bf16_kernel<<<(unsigned)((n16 + 255) / 256), 256, 0, st>>>((const uint4 *)img, (uint4 *)m->img_bf, n16, m->f16);
         DP_CUDA_CHECK(cudaGetLastError());
-        DP_CUDA_CHECK(cudaMemsetAsync(m->img_bf + n_rows * RE, 0, (size_t)(S - 1) * RE * 2, st));
+        if (!triples) DP_CUDA_CHECK(cudaMemsetAsync(m->img_bf + n_rows * RE, 0, (size_t)(S - 1) * RE * 2, st));
     }
     mark();
     const int tiles_m = (int)((n_rows + 127) / 128);
-    const CUtensorMap tmA[4] = {m->tm_img, m->tm_arena, m->tm_arena_lo, m->tm_arena};
+    const CUtensorMap tmA[4] = {m->tm_img, m->tm_arena, m->tm_arena_lo, m->tm_img3};
     const CUtensorMap tmA_mc[4] = {m->tm_img, m->tm_arena_mc, m->tm_arena_lo_mc, m->tm_arena_mc};   // GRU pair kernel
     // 2. folded CNN + Linear
     {
         GemmArgs g;
         memset(&g, 0, sizeof(g));
-        g.chunks = m->tables + m->fold_tab_off;
+        g.chunks = m->tables + (triples ? m->fold3_tab_off : m->fold_tab_off);
         g.n_chunks = m->fold_tab_n;
         g.M = (int)n_rows; g.N = S * HP;
         g.tiles_m = tiles_m; g.tiles_n = (S * HP) / 256;
@@ -650,6 +665,15 @@ int dp_model_forward_rows(dp_model *h, const uint8_t *img, int64_t n_rows, float
     DP_REQUIRE(img, "null image");
     DP_REQUIRE(((uintptr_t)img & 15) == 0, "img must be 16-byte aligned");
     return dp::forward_rows(h->m, img, n_rows, logits, pred, (cudaStream_t)stream);
+}
+
+int dp_model_forward_calls(dp_model *h, const uint8_t *img, int64_t n_calls, float *logits, uint8_t *pred, void *stream) {
+    DP_REQUIRE(h && h->m, "null model");
+    DP_REQUIRE(n_calls >= 0 && n_calls * h->m->seq_len <= h->m->mcap, "n_calls * seq_len exceeds the model's max_rows");
+    if (n_calls == 0) return DP_OK;
+    DP_REQUIRE(img, "null image");
+    DP_REQUIRE(((uintptr_t)img & 15) == 0, "img must be 16-byte aligned");
+    return dp::forward_rows(h->m, img, n_calls, logits, pred, (cudaStream_t)stream, 1);
 }
 
 int dp_vote(const uint8_t *pred, int32_t n_windows, int32_t H, int32_t n_class, int8_t *calls, const uint8_t *labels,

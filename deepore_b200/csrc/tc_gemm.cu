@@ -979,19 +979,19 @@ int launch_gru_step2w(const CUtensorMap *tmA, const CUtensorMap *tmB96, const Gr
 // (29 % fewer operand bytes per FLOP out of L2 than the 64-unit tile).  Price: an A tile stays in shared memory for L
 // more chunks, so A and the weight tiles live in separate rings (A: NA x 16 KB released by half 1; weights: NB x 12 KB
 // consumed in issue order B0(c), B1(c - L)).
-constexpr int GRUS_LAG = 6;                      // chunks between the two halves
-constexpr int GRUS_NA = 9;                       // A ring stages (>= LAG + prefetch depth)
-constexpr int GRUS_NB = 6;                       // weight ring stages
+// L = chunks between the two halves, NA = A ring stages (>= L + prefetch depth), NB = weight ring stages
 constexpr int GRUS_B_BYTES = GRU2_B_ROWS * 128;  // 12 KB per CTA and weight tile
 constexpr int GRUS_BAR_BYTES = 512;
-constexpr int GRUS_SMEM_BYTES = GRUS_NA * A_STAGE_BYTES + GRUS_NB * GRUS_B_BYTES + 1024 + GRUS_BAR_BYTES + 2 * GRU2_MAX_CHUNKS * 16;
+__host__ __device__ constexpr int grus_smem_bytes(int na, int nb) {
+    return na * A_STAGE_BYTES + nb * GRUS_B_BYTES + 1024 + GRUS_BAR_BYTES + 2 * GRU2_MAX_CHUNKS * 16;
+}
 
-template <bool FAST_ACT>
+template <bool FAST_ACT, int L, int NA, int NB>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GRU2_THREADS, 1)
 gru_step2s_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1,
                   const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmA3,
                   const __grid_constant__ CUtensorMap tmB96, const GruArgs g) {
-    constexpr int NA = GRUS_NA, NB = GRUS_NB, L = GRUS_LAG;
+    static_assert(grus_smem_bytes(NA, NB) <= 232448 && NA > L, "ring configuration");
     extern __shared__ uint8_t smem_raw[];
     const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     const uint32_t b_base = smem_base + NA * A_STAGE_BYTES;
@@ -1094,9 +1094,11 @@ gru_step2s_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constan
                         const uint64_t da = make_smem_desc_sw128(smem_base + ph.stage * A_STAGE_BYTES);
                         const uint64_t db = make_smem_desc_sw128(b_base + pb.stage * GRUS_B_BYTES);
                         const uint32_t d0 = tmem_base + (kind == 0 ? 0u : 64u);   // input: columns 0..191, hidden: 64..255
+                        if (!((g.debug >> 8) & 2)) {
 #pragma unroll
-                        for (int k = 0; k < BK / 16; k++)
-                            umma_bf16_2sm(d0, da + 2u * k, db + 2u * k, idesc192, kind == 0 ? (uint32_t)(c | k) : 1u);
+                            for (int k = 0; k < BK / 16; k++)
+                                umma_bf16_2sm(d0, da + 2u * k, db + 2u * k, idesc192, kind == 0 ? (uint32_t)(c | k) : 1u);
+                        }
                         umma_commit_mc(b_empty(pb.stage), 3);
                         ph.advance(NA); pb.advance(NB);
                         if (c == n - 1) umma_commit_mc(tfull_bar(0), 3);
@@ -1110,9 +1112,11 @@ gru_step2s_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constan
                         const uint64_t da = make_smem_desc_sw128(smem_base + pt.stage * A_STAGE_BYTES);   // full since half 0 used it
                         const uint64_t db = make_smem_desc_sw128(b_base + pb.stage * GRUS_B_BYTES);
                         const uint32_t d0 = tmem_base + 256u + (kind == 0 ? 0u : 64u);
+                        if (!((g.debug >> 8) & 2)) {
 #pragma unroll
-                        for (int k = 0; k < BK / 16; k++)
-                            umma_bf16_2sm(d0, da + 2u * k, db + 2u * k, idesc192, kind == 0 ? (uint32_t)(cc | k) : 1u);
+                            for (int k = 0; k < BK / 16; k++)
+                                umma_bf16_2sm(d0, da + 2u * k, db + 2u * k, idesc192, kind == 0 ? (uint32_t)(cc | k) : 1u);
+                        }
                         umma_commit_mc(b_empty(pb.stage), 3);
                         umma_commit_mc(a_empty(pt.stage), 3);
                         pt.advance(NA); pb.advance(NB);
@@ -1139,6 +1143,14 @@ gru_step2s_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constan
             for (int hb = 0; hb < 2; hb++) {
                 const int u0 = (ub + hb) * GRU_UB + cb * 16;
                 float hp[16];
+                const int dbg = g.debug & 0xff;
+                if (dbg == 1) {                          // timing experiment: accumulators handed straight back
+                    mbar_wait(tfull_bar(hb), tphase);
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive_cluster(tempty_bar(hb), 0);
+                    continue;
+                }
                 if (P.h_prev && m < g.M) state_load16(P.h_prev, m, u0, hp);
                 else if (P.h_prev_bf && m < g.M) rows_load_bf16(P.h_prev_bf, m, u0, hp, g.f16 != 0);
                 else {
@@ -1159,7 +1171,7 @@ gru_step2s_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constan
                 __syncwarp();
                 if (lane == 0) mbar_arrive_cluster(tempty_bar(hb), 0);
                 gru_finish16<FAST_ACT>(P, g.M, m_warp0, lane, u0, vr, vz, vx, vh, has_h, hp, g.f16 != 0,
-                                       g.acc_scale != 0.f ? g.acc_scale : 1.f, 0);
+                                       g.acc_scale != 0.f ? g.acc_scale : 1.f, dbg);
             }
             tphase ^= 1u;
         }
@@ -1170,17 +1182,30 @@ gru_step2s_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constan
     if (warp == 2) { tc_fence_after(); tmem_dealloc_2sm(tmem_base, 512); }
 }
 
-int launch_gru_step2s(const CUtensorMap *tmA, const CUtensorMap *tmB96, const GruArgs &g_in, cudaStream_t st) {
+template <bool FAST_ACT, int L, int NA, int NB>
+static int launch_gru_step2s_t(const CUtensorMap *tmA, const CUtensorMap *tmB96, const GruArgs &g, int pairs, cudaStream_t st) {
+    constexpr int SMEM = grus_smem_bytes(NA, NB);
     static bool attr_done[64] = {false};
     int dev = 0;
     DP_CUDA_CHECK(cudaGetDevice(&dev));
     if (dev >= 64 || !attr_done[dev]) {
-        DP_CUDA_CHECK(cudaFuncSetAttribute(gru_step2s_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, GRUS_SMEM_BYTES));
-        DP_CUDA_CHECK(cudaFuncSetAttribute(gru_step2s_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, GRUS_SMEM_BYTES));
+        DP_CUDA_CHECK(cudaFuncSetAttribute(gru_step2s_kernel<FAST_ACT, L, NA, NB>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
         if (dev < 64) attr_done[dev] = true;
     }
+    gru_step2s_kernel<FAST_ACT, L, NA, NB><<<2 * pairs, GRU2_THREADS, SMEM, st>>>(tmA[0], tmA[1], tmA[2], tmA[3], *tmB96, g);
+    DP_CUDA_CHECK(cudaGetLastError());
+    return DP_OK;
+}
+
+int launch_gru_step2s(const CUtensorMap *tmA, const CUtensorMap *tmB96, const GruArgs &g_in, cudaStream_t st) {
+    static int dbg = -1, cfg = 0;
+    if (dbg < 0) {
+        const char *e = getenv("DP_GRU_DEBUG"); dbg = e ? atoi(e) : 0;
+        const char *e2 = getenv("DP_GRU_DEBUG2"); if (e2) dbg |= atoi(e2) << 8;
+        const char *e3 = getenv("DP_GRUS_CFG"); cfg = e3 ? atoi(e3) : 0;      // ring configuration (lag, A stages, B stages)
+    }
     GruArgs g = g_in;
-    g.debug = 0;
+    g.debug = dbg;
     g.tiles_m = (g.M + 255) / 256;
     const int n_tiles = g.tiles_m * (GRU_NUB / 2) * g.n_prob;
     if (n_tiles <= 0) return DP_OK;
@@ -1188,10 +1213,17 @@ int launch_gru_step2s(const CUtensorMap *tmA, const CUtensorMap *tmB96, const Gr
         if (g.prob[i].n_chunks > GRU2_MAX_CHUNKS || g.prob[i].n_chunks < 1) { set_error("gru_step2s: bad K chunk count"); return DP_EINVAL; }
     const int max_pairs = device_sm_count() / 2;
     const int pairs = n_tiles < max_pairs ? n_tiles : max_pairs;
-    if (g.fast_act) gru_step2s_kernel<true><<<2 * pairs, GRU2_THREADS, GRUS_SMEM_BYTES, st>>>(tmA[0], tmA[1], tmA[2], tmA[3], *tmB96, g);
-    else gru_step2s_kernel<false><<<2 * pairs, GRU2_THREADS, GRUS_SMEM_BYTES, st>>>(tmA[0], tmA[1], tmA[2], tmA[3], *tmB96, g);
-    DP_CUDA_CHECK(cudaGetLastError());
-    return DP_OK;
+#define DP_GRUS_CASE(id, L_, NA_, NB_)                                                                           \
+    if (cfg == id) return g.fast_act ? launch_gru_step2s_t<true, L_, NA_, NB_>(tmA, tmB96, g, pairs, st)          \
+                                     : launch_gru_step2s_t<false, L_, NA_, NB_>(tmA, tmB96, g, pairs, st);
+    DP_GRUS_CASE(1, 6, 9, 6)
+    DP_GRUS_CASE(2, 4, 8, 7)
+    DP_GRUS_CASE(3, 2, 7, 9)
+    DP_GRUS_CASE(4, 2, 6, 10)
+    DP_GRUS_CASE(5, 1, 6, 10)
+#undef DP_GRUS_CASE
+    return g.fast_act ? launch_gru_step2s_t<true, 3, 7, 8>(tmA, tmB96, g, pairs, st)
+                      : launch_gru_step2s_t<false, 3, 7, 8>(tmA, tmB96, g, pairs, st);
 }
 
 template <bool FAST_ACT, int NP>

@@ -32,7 +32,11 @@ class PileupDataset:
             "Some images referenced in the CSV file were not found"          # dataset.py:34-35
         self.transform = transform
         self.X_train = tmp_df[0]
-        self.y_train = np.array([np.array([int(x) for x in str(label)], dtype=np.int64) for label in tmp_df[1]])
+        # one int64 vector per window; labels grow with the insert rows of their window (Pileup.py:320-333), so the
+        # container is an object array (np.array() of ragged vectors, dataset.py:45, is an error on numpy >= 1.24)
+        self.y_train = np.empty(len(tmp_df.index), dtype=object)
+        for k, label in enumerate(tmp_df[1]):
+            self.y_train[k] = np.array([int(x) for x in str(label)], dtype=np.int64)
 
     def __getitem__(self, index):
         import torch

@@ -88,6 +88,21 @@ class _Engine:
         _lib.check(rc, "dp_model_forward_rows")
         return logits, pred
 
+    def forward_calls(self, img_calls: torch.Tensor):
+        """img_calls uint8 [n_calls, 3, width, in_ch]: independent 3-row windows (Model.forward of the reference API)
+        -> logits fp32 [n_calls, 3, n_class]"""
+        assert img_calls.dtype == torch.uint8 and img_calls.is_cuda and img_calls.is_contiguous()
+        n = int(img_calls.shape[0])
+        if n * 3 > self.max_rows:
+            raise _lib.DeeporeError("forward_calls: %d calls exceed the engine capacity %d rows" % (n, self.max_rows))
+        logits = torch.empty((n, 3, self.n_class), dtype=torch.float32, device=self.device)
+        st = torch.cuda.current_stream(self.device)
+        with torch.cuda.device(self.device):
+            rc = _lib.lib().dp_model_forward_calls(self.handle, img_calls.data_ptr(), n, logits.data_ptr(), None,
+                                                   C.c_void_p(st.cuda_stream))
+        _lib.check(rc, "dp_model_forward_calls")
+        return logits
+
     def profile(self, enable: bool):
         _lib.check(_lib.lib().dp_model_profile(self.handle, 1 if enable else 0), "dp_model_profile")
 
@@ -165,15 +180,26 @@ class Model(nn.Module):
                                     "and pass gpu_mode=True to test.py")
         if x.dim() != 4 or x.size(2) != 3:
             raise _lib.DeeporeError("forward expects (N, C, 3, W): seq_len is 3 on this path (test.py:48)")
-        if hidden is not None and bool((hidden[:2] != 0).any()):
-            raise _lib.DeeporeError("a non-zero initial hidden state is not supported (test.py:53 always passes zeros)")
-        q = torch.round(x * 255.0)
-        if bool(((x * 255.0 - q).abs() > 1e-3).any()) or bool((q < 0).any()) or bool((q > 255).any()):
+        # validity of the inputs, as ONE device reduction read back once per call (test.py calls forward 148 times per
+        # batch): x must hold 8-bit pixels scaled by ToTensor; `hidden` is the constant zero tensor of test.py:53 and is
+        # checked once per tensor version, not once per call
+        q = x * 255.0
+        r = torch.round(q)
+        bad = ((q - r).abs() > 1e-3).any() | (r < 0).any() | (r > 255).any()
+        hkey = None
+        if hidden is not None:
+            hkey = (hidden.data_ptr(), hidden._version, tuple(hidden.shape))
+            if self.__dict__.get("_hidden_ok") != hkey:
+                bad = torch.stack([bad, (hidden[:2] != 0).any().to(bad.device)])
+        flags = bad.reshape(-1).tolist()                  # the only host synchronisation of the call
+        if flags[0]:
             raise _lib.DeeporeError("forward expects 8-bit pileup tensors scaled by ToTensor (values k/255)")
-        rows = q.to(torch.uint8).permute(0, 2, 3, 1).contiguous().view(-1, x.size(3), x.size(1))   # [N*3, W, C]
-        eng = self.engine(rows.shape[0], x.device)
-        logits, _ = eng.forward_rows(rows, want_logits=True, want_pred=False)
-        return logits.view(x.size(0), 3, 3, self.classN)[:, 0].contiguous()
+        if len(flags) > 1 and flags[1]:
+            raise _lib.DeeporeError("a non-zero initial hidden state is not supported (test.py:53 always passes zeros)")
+        self.__dict__["_hidden_ok"] = hkey
+        calls = r.to(torch.uint8).permute(0, 2, 3, 1).contiguous()          # [N, 3, W, C]
+        eng = self.engine(calls.shape[0] * 3, x.device)
+        return eng.forward_calls(calls)
 
     # ------------------------------------------------------------------ B200 path
     def numpy_state(self):
@@ -230,6 +256,7 @@ class Model(nn.Module):
         d = dict(self.__dict__)
         d.pop("_engine", None)
         d.pop("_engine_key", None)
+        d.pop("_hidden_ok", None)
         return d
 
 

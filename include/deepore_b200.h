@@ -147,6 +147,15 @@ int dp_model_destroy(dp_model *m);
 int dp_model_forward_rows(dp_model *m, const uint8_t *img, int64_t n_rows, float *logits, uint8_t *pred, void *stream);
 
 /*
+ * dp_model_forward_calls -- Model.forward(x, hidden) as src/test.py:63-66 calls it: n_calls INDEPENDENT windows of seq_len
+ * rows each (one per sample of the batch), no sliding.
+ *   img      device uint8 [n_calls][seq_len][width][in_ch]   (n_calls * seq_len <= max_rows)
+ *   logits   optional device fp32 [n_calls][seq_len][n_class] = Model.forward's return value (model.py:154-156)
+ *   pred     optional device uint8 [n_calls][seq_len]
+ */
+int dp_model_forward_calls(dp_model *m, const uint8_t *img, int64_t n_calls, float *logits, uint8_t *pred, void *stream);
+
+/*
  * dp_vote -- test.py:71-89: calls[w][row] = mode(pred[w][row-2][2], pred[w][row-1][1], pred[w][row][0]) for
  * 2 <= row <= H-3 (smallest class on a three-way tie), -1 elsewhere; optional confusion[label][call] += 1.
  *   pred [n_windows][H][3] uint8 (dp_model_forward_rows with n_rows = n_windows*H), calls [n_windows][H] int8,

@@ -1,9 +1,13 @@
 """Parity of the CUDA model path (C-ABI dp_model_*) against outputs of the UNMODIFIED reference model
-(tests/golden/model_seed7.npz) and against the numpy oracle.
+(tests/golden/model_seed7.npz, tests/golden/bundled_calls_seed7.npz) and against the numpy oracle.
 
-Tolerances: logits max-abs <= 2e-2 in bf16 mode (bf16 operands, fp32 accumulate; logit scale
-~3) and <= 2e-4 in split-bf16 mode; argmax and votes identical wherever the reference's top-2 margin exceeds twice
-the logit tolerance."""
+Bars (same numbers in DESIGN.md section 2), logits max-abs against the reference's torch-CPU fp32 logits:
+  fp16    (default: fp16 operands, fp32 accumulate, fp32 recurrent state)  <= 1e-3 x logit scale (max |logit| of the golden
+          set, 2.87 -> 2.9e-3; measured 2.2e-3 - 2.5e-3)
+  fp16x3 / bf16x3 (operands split hi + lo, three passes)                   <= 1e-4 (measured 3.2e-5 / 4.0e-5)
+  bf16    (round-1 default, kept for the error attribution)                <= 2.5e-2 (measured 1.8e-2)
+Top-1 classes and 3-way votes are COUNTED over all 260 x 148 x 3 / 37 960 of them; every one that differs from the
+reference must sit where the reference's own top-2 margin is below twice the measured logit error of that run."""
 import os
 
 import numpy as np
@@ -13,7 +17,8 @@ torch = pytest.importorskip("torch")
 pytestmark = pytest.mark.gpu
 
 GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "model_seed7.npz")
-TOL = {"bf16": 2e-2, "bf16x3": 2e-4}
+TOL = {"fp16": 2.9e-3, "fp16x3": 1e-4, "bf16": 2.5e-2, "bf16x3": 1e-4}
+MAX_VOTE_DIFF = {"fp16": 0.003, "fp16x3": 0.0001, "bf16": 0.012, "bf16x3": 0.0001}     # fraction of the 37 960 votes
 
 
 @pytest.fixture(scope="module")
@@ -26,7 +31,7 @@ def _model(precision):
     return model.from_state(modelio.seeded_state(7), "cuda", precision)
 
 
-@pytest.mark.parametrize("precision", ["bf16", "bf16x3"])
+@pytest.mark.parametrize("precision", ["fp16", "fp16x3", "bf16", "bf16x3"])
 def test_front_and_logits_vs_reference(gold, precision):
     m = _model(precision)
     img = torch.from_numpy(gold["img"]).cuda()
@@ -34,7 +39,7 @@ def test_front_and_logits_vs_reference(gold, precision):
     torch.cuda.synchronize()
     # stage 1: folded CNN + Linear (y) of window 0 against the reference's cnn_fc_rnn output
     eng = m.engine(img.shape[0] * img.shape[1], img.device)
-    ytol = 2e-2 if precision == "bf16" else 2e-4
+    ytol = {"fp16": 2e-3, "bf16": 2e-2}.get(precision, 1e-4)
     for t in range(3):
         y = eng.peek(t, 150)[:148, :500]
         err = np.abs(y - gold["y_window0"][:, t]).max()
@@ -49,7 +54,7 @@ def test_front_and_logits_vs_reference(gold, precision):
     decisive = (srt[..., -1] - srt[..., -2]) > 2 * TOL[precision]
     pr = pred.cpu().numpy()[:, :148]
     assert np.array_equal(pr[decisive], gold["pred"][decisive])
-    assert decisive.mean() > 0.9
+    assert decisive.mean() > (0.9 if precision == "bf16" else 0.98)
 
 
 @pytest.mark.parametrize("env", [{"DP_GRU": "stag"}, {"DP_GRU": "wide"}, {"DP_GRU_NP": "2"}, {"DP_GRU_NP": "4"}, {"DP_GRU": "1cta"}])
@@ -87,9 +92,11 @@ def test_votes_and_confusion(gold):
     assert np.array_equal(conf.cpu().numpy(), cw)
 
 
-def test_forward_api_matches_forward_windows(gold):
-    """Model.forward(x, hidden) (the reference call, test.py:63-66) == the batched path, call by call."""
-    m = _model("bf16")
+@pytest.mark.parametrize("precision", ["fp16", "fp16x3", "bf16"])
+def test_forward_api_matches_forward_windows(gold, precision):
+    """Model.forward(x, hidden) (the reference call, test.py:63-66: one independent 3-row window per sample, through
+    dp_model_forward_calls) == the batched sliding-window path, call by call and bit for bit."""
+    m = _model(precision)
     img = torch.from_numpy(gold["img"][:2]).cuda()
     logits, _ = m.forward_windows(img)
     images = (img.permute(0, 3, 1, 2).float() / 255.0).contiguous()
@@ -119,7 +126,7 @@ def test_oracle_on_random_images():
 
 
 def test_empty_and_capacity():
-    m = _model("bf16")
+    m = _model("fp16")
     img = torch.zeros((0, 150, 200, 4), dtype=torch.uint8, device="cuda")
     logits, pred = m.forward_windows(img)
     assert logits.shape == (0, 150, 3, 3)
@@ -174,12 +181,19 @@ def test_bundled_windows_end_to_end_call_set():
     assert merged.shape[0] <= rec.shape[0] and np.all(np.diff(merged["pos"]) >= 0)
 
 
-@pytest.mark.parametrize("precision", ["bf16x3", "bf16"])
-def test_bundled_call_set_all_windows_vs_reference(precision):
-    """All 260 windows of the bundled NA12878 fixture: CUDA encoder -> CUDA model -> dp_vote against the call set of the
-    UNMODIFIED reference model over the reference's own pileup images (tests/golden/bundled_calls_seed7.npz, made by
-    oracle/make_calls_golden.py).  Top-1 classes must agree wherever the reference's top-2 margin exceeds twice the logit
-    tolerance, votes wherever that holds for all three contributing (call, t) pairs."""
+def _votes(pred):
+    """test.py:71-82 over pred [nw, 148, 3] -> [nw, 146] (image rows 2..147)."""
+    a, b, c = pred[:, 0:146, 2].astype(np.int64), pred[:, 1:147, 1].astype(np.int64), pred[:, 2:148, 0].astype(np.int64)
+    return np.where((a == b) | (a == c), a, np.where(b == c, b, np.minimum(a, np.minimum(b, c))))
+
+
+@pytest.mark.parametrize("precision", ["fp16", "fp16x3", "bf16x3", "bf16"])
+def test_bundled_call_set_all_windows_vs_reference(precision, capsys):
+    """All 260 windows of the bundled NA12878 fixture: CUDA encoder -> CUDA model -> dp_vote against the logits, top-1 classes
+    and call set of the UNMODIFIED reference model over the reference's own pileup images
+    (tests/golden/bundled_calls_seed7.npz, made by oracle/make_calls_golden.py).  Nothing is masked: every logit is compared,
+    every top-1 and every vote that differs is counted, and each difference must be explained by a reference margin below
+    twice the logit error measured in this very run."""
     import golden_util as gu
     from deepore_b200 import calls as dc, model, modelio
     from deepore_b200.pileup import encode_windows
@@ -189,19 +203,33 @@ def test_bundled_call_set_all_windows_vs_reference(precision):
     img, rowpos, rowins, status = encode_windows(g.reads, g.win_qs, g.ref, g.ref_base)
     assert (status.cpu().numpy() == 0).all() and np.array_equal(img.cpu().numpy(), g.img)
     m = model.from_state(modelio.seeded_state(int(gold["seed"])), "cuda", precision)
-    _, pred = m.forward_windows(img, want_logits=False)
+    logits, pred = m.forward_windows(img)
     votes, _ = model.vote(pred.view(-1, 3), nw, img.shape[1], 3)
     torch.cuda.synchronize()
+    lg = logits.cpu().numpy()[:, :148]
+    err = float(np.abs(lg - gold["logits"]).max())
+    rms = float(np.sqrt(((lg - gold["logits"]) ** 2).mean()))
+    scale = float(np.abs(gold["logits"]).max())
+    assert err <= TOL[precision], "logits max abs err %g" % err
+    if precision == "fp16":
+        assert err <= 1e-3 * scale                                    # 1e-3 relative to the logit scale
     pr = pred.view(nw, img.shape[1], 3)[:, :148].cpu().numpy()
     votes = votes.cpu().numpy()
-    decisive = gold["margin"] > 2 * TOL[precision]                       # [nw, 148, 3]
-    assert np.array_equal(pr[decisive], gold["pred"][decisive])
-    dv = np.zeros(votes.shape, bool)
-    dv[:, 2:148] = decisive[:, 0:146, 2] & decisive[:, 1:147, 1] & decisive[:, 2:148, 0]
-    assert np.array_equal(votes[dv], gold["calls"][dv])
+    diff = pr != gold["pred"]                                         # [nw, 148, 3], nothing masked
+    n_argmax_diff = int(diff.sum())
+    assert (gold["margin"][diff] < 2 * err).all(), "a top-1 class differs where the reference margin is decisive"
+    v, rv = _votes(pr), gold["calls"][:, 2:148]
+    assert np.array_equal(votes[:, 2:148], v)                         # dp_vote == test.py's vote of the same top-1 classes
+    vdiff = v != rv
+    n_vote_diff = int(vdiff.sum())
+    tight = gold["margin"] < 2 * err                                  # a vote may only flip through a contested top-1
+    contested = tight[:, 0:146, 2] | tight[:, 1:147, 1] | tight[:, 2:148, 0]
+    assert contested[vdiff].all(), "a vote differs although all three contributing margins are decisive"
+    assert n_vote_diff <= MAX_VOTE_DIFF[precision] * v.size, "%d of %d votes differ" % (n_vote_diff, v.size)
     assert (votes[:, :2] == -1).all() and (votes[:, 148:] == -1).all()
-    frac = dv[:, 2:148].mean()
-    assert frac > (0.99 if precision == "bf16x3" else 0.8), "only %.3f of the votes are decisive" % frac
+    with capsys.disabled():
+        print("\n[parity %s] logits max-abs %.3g rms %.3g (logit scale %.3g) | n_argmax_diff %d / %d | n_vote_diff %d / %d"
+              % (precision, err, rms, scale, n_argmax_diff, diff.size, n_vote_diff, v.size))
     # the artefact itself: one record per scored, populated row
     rec = dc.call_records(votes, rowpos.cpu().numpy(), rowins.cpu().numpy())
     assert rec.shape[0] == int(((votes >= 0) & (rowpos.cpu().numpy() >= 0)).sum())
@@ -211,7 +239,7 @@ def test_batch_composition_does_not_change_a_window(gold):
     """Size-independent property (SURVEY 8d config 4 sweeps the call batch): a window's logits are bit-identical whatever
     batch it is forwarded in -- alone (150 rows: one partial 256-row tile), with others (rows straddling tile and chunk
     boundaries), or repeated up to several thousand rows.  (Calls 148 and 149 of a window read the first rows of the NEXT window and are never scored.)"""
-    m = _model("bf16")
+    m = _model("fp16")
     img = torch.from_numpy(gold["img"]).cuda()                       # 4 windows
     base, bpred = m.forward_windows(img)
     for i in range(img.shape[0]):

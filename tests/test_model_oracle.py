@@ -86,3 +86,16 @@ def test_call_set_golden_is_consistent_with_the_logit_golden(gold):
     assert full["pred"].shape == (260, 148, 3) and full["calls"].shape == (260, 150)
     assert ((full["calls"][:, 2:148] >= 0).all() and (full["calls"][:, :2] == -1).all()
             and (full["calls"][:, 148:] == -1).all())
+
+
+def test_torch_restatement_matches_reference_logits(gold, state):
+    """oracle/torch_model.py (the torch-CPU leg of bench.py's CPU baseline: nn.Conv2d / BatchNorm2d / Linear / GRU modules
+    filled from the numpy state, forward restated from model.py:93-156) against the logits of the unmodified reference
+    class -- same torch kernels, so equal up to thread-count dependent summation order."""
+    import torch
+    import torch_model as tm
+    torch.set_num_threads(max(1, min(8, os.cpu_count() or 1)))
+    m = tm.build(state)
+    got = tm.forward_image_rows(m, gold["img"][:2], CALLS)
+    assert got.shape == (2, len(CALLS), 3, 3)
+    assert np.abs(got - gold["logits"][:2][:, CALLS]).max() < 2e-5
