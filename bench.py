@@ -313,6 +313,44 @@ def run_reference(args, rank, world):
     print(json.dumps(line))
 
 
+def bam_path(dev, model, precision, rank, stride, n_chunks=3, windows_per_chunk=8192, level=6):
+    """positions/s from COMPRESSED BAM BYTES IN HOST MEMORY to calls in host memory (deepore_b200/pipeline.py): per chunk one
+    H2D copy of the BGZF image on a side stream, dp_bgzf_inflate, dp_bam_scan / dp_bam_extract, dp_encode_prepare,
+    dp_window_ranges, then batches of dp_encode_prepared -> model -> dp_vote, and one D2H copy per result array.  The ingest
+    of chunk i+1 overlaps the compute of chunk i.  The first chunk is the warm-up; the rest are timed with the host clock
+    (the path spans two streams and a host thread), device idle on both sides."""
+    import torch
+    from deepore_b200 import pipeline, synth
+    from deepore_b200.workload import SyntheticWorkload
+    wl = SyntheticWorkload(stride=stride)
+    chunks, comp, raw = [], 0, 0
+    for k in range(n_chunks):
+        w0 = ((rank * n_chunks + k) * windows_per_chunk) % max(1, wl.n_windows - windows_per_chunk)
+        wq = wl.all_win_qs[w0:w0 + windows_per_chunk]
+        region = (int(wq[0]), int(wq[-1]) + 2 * wl.flank + 2)
+        rb = wl.synth.simulate_reads(wl.ref, coverage=wl.coverage, seed=wl.read_seed, region=region)
+        stream = synth.bam_stream(rb, "chr3", wl.ref_len)
+        image = synth.bgzf_image(stream, level=level, threads=os.cpu_count() or 1)
+        lo, hi = max(0, region[0] - 1), min(wl.ref_len, region[1] + 1)
+        chunks.append(pipeline.ContigChunk(image, "chr3", wl.ref[lo:hi], lo, int(wq[0]), int(wq.shape[0]), stride, tag=k))
+        if k > 0:
+            comp += int(image.size)
+            raw += len(stream)
+    caller = pipeline.ContigCaller(model, dev, windows_per_call=4096, model_chunk=512, precision=precision)
+    list(caller.run(chunks[:1]))                                   # warm-up (allocations, kernel attributes)
+    caller.timing = {"ingest_ms": 0.0, "compute_ms": 0.0, "chunks": 0}
+    torch.cuda.synchronize(dev)
+    t0 = time.perf_counter()
+    outs = list(caller.run(chunks[1:]))
+    torch.cuda.synchronize(dev)
+    dt = time.perf_counter() - t0
+    nwin = sum(int(o.calls.shape[0]) for o in outs)
+    ok = all(((o.calls[:, 2:148] >= 0) & (o.calls[:, 2:148] < 3)).all() for o in outs)
+    return {"seconds": dt, "windows": nwin, "chunks": len(outs), "compressed_bytes": comp, "inflated_bytes": raw,
+            "ingest_ms_on_side_stream": caller.timing["ingest_ms"], "compute_ms_on_compute_stream": caller.timing["compute_ms"],
+            "fallback_windows": int(sum(o.fallback_windows for o in outs)), "calls_in_range": bool(ok)}
+
+
 def parity_block(dev, precision):
     """Parity of the precision this run is timed in, on the committed goldens (outputs of the UNMODIFIED reference model over
     the 260 bundled NA12878 pileup images; no oracle/ import): logits max-abs / rms, top-1 classes and votes that differ,
@@ -356,6 +394,9 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-x3", action="store_true", help="skip the extra pass in the split (x3) precision")
     ap.add_argument("--no-parity", action="store_true", help="skip the parity block (golden windows through the model)")
+    ap.add_argument("--no-bam", action="store_true", help="skip the e2e_from_bam measurement (file image -> calls pipeline)")
+    ap.add_argument("--bam-chunks", type=int, default=4, help="timed contig chunks of the e2e_from_bam measurement")
+    ap.add_argument("--bam-windows", type=int, default=8192, help="windows per contig chunk of the e2e_from_bam measurement")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
 
@@ -544,6 +585,15 @@ def main():
         ms3e, _, _, _ = timed(se3)
         x3 = (px3, ms3, ms3e)
 
+    bam = None
+    if with_model and not args.no_bam:
+        bam = bam_path(dev, engines[args.precision][0], args.precision, rank, args.stride, n_chunks=1 + args.bam_chunks,
+                       windows_per_chunk=args.bam_windows)
+        if world > 1:
+            t = torch.tensor([bam["seconds"]], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            bam["seconds"] = float(t.item())
+
     win_timed = sum(b.n_windows for b in bufs[args.warmup:])
     tot_windows = win_timed * world
     value = tot_windows * args.stride / (ms_dev * 1e-3)
@@ -609,6 +659,19 @@ def main():
             line["roofline_encoder"] = enc_roof
         else:
             line["roofline"] = enc_roof
+        if bam is not None:
+            line["e2e_from_bam"] = {
+                "value": bam["windows"] * world * args.stride / bam["seconds"], "unit": UNIT,
+                "what": "compressed BAM bytes in host memory -> H2D on a side stream -> inflate, record split, window index, encode, "
+                        "model, vote on the device -> calls + row map in host memory; ingest of chunk i+1 overlaps compute of chunk i",
+                "timer": "host clock around the timed chunks, device idle on both sides, max over ranks",
+                "chunks": bam["chunks"], "windows_per_chunk": bam["windows"] // max(1, bam["chunks"]),
+                "h2d_compressed_bytes_per_chunk": bam["compressed_bytes"] // max(1, bam["chunks"]),
+                "inflated_bytes_per_chunk": bam["inflated_bytes"] // max(1, bam["chunks"]),
+                "ingest_share_of_device_time": bam["ingest_ms_on_side_stream"] / max(1e-9, bam["ingest_ms_on_side_stream"] + bam["compute_ms_on_compute_stream"]),
+                "ingest_ms_per_chunk": bam["ingest_ms_on_side_stream"] / max(1, bam["chunks"]),
+                "compute_ms_per_chunk": bam["compute_ms_on_compute_stream"] / max(1, bam["chunks"]),
+                "fallback_windows": bam["fallback_windows"], "calls_in_range": bam["calls_in_range"]}
         if with_model and not args.no_parity:
             line["parity"] = parity_block(dev, args.precision)
             if x3 is not None:

@@ -39,8 +39,9 @@ def index_blocks(image: np.ndarray) -> Dict[str, np.ndarray]:
     return idx
 
 
-def inflate_on_device(image: np.ndarray, device="cuda:0", idx: Optional[dict] = None, stream=None):
-    """BGZF file image (host uint8) -> (inflated bytes as a device uint8 tensor, per-block status on the host)."""
+def inflate_on_device(image: np.ndarray, device="cuda:0", idx: Optional[dict] = None, stream=None, pinned=None):
+    """BGZF file image (host uint8) -> (inflated bytes as a device uint8 tensor, per-block status on the host).
+    `pinned`: the same bytes already staged in a pinned torch tensor (the pipeline's producer thread does that)."""
     import torch
     _lib.require_cuda()
     image = np.ascontiguousarray(image, dtype=np.uint8)
@@ -50,7 +51,9 @@ def inflate_on_device(image: np.ndarray, device="cuda:0", idx: Optional[dict] = 
     dev = torch.device(device)
     st = stream if stream is not None else torch.cuda.current_stream(dev)
     with torch.cuda.stream(st):
-        d_file = torch.from_numpy(image if image.size else np.zeros(1, np.uint8)).pin_memory().to(dev, non_blocking=True)
+        if pinned is None:
+            pinned = torch.from_numpy(image if image.size else np.zeros(1, np.uint8)).pin_memory()
+        d_file = pinned.to(dev, non_blocking=True)
         d = {k: torch.from_numpy(idx[k]).to(dev, non_blocking=True) for k in ("in_off", "in_len", "out_off", "out_len")}
         out = torch.empty(max(total, 1), dtype=torch.uint8, device=dev)
         status = torch.full((max(n, 1),), 1, dtype=torch.int32, device=dev)
@@ -86,7 +89,8 @@ def records_on_device(bam, contig: str = "", stream=None) -> Tuple[dict, dict]:
         if c[6] == -3:
             raise ValueError("contig %r is not in the BAM header" % contig)      # list.index() in reads.BamFile
         if c[6] != 0:
-            raise ValueError("BAM stream is malformed (%s)" % {-1: "bad magic", -2: "truncated"}.get(int(c[6]), int(c[6])))
+            raise ValueError("BAM stream is malformed (%s)" % {-1: "bad magic", -2: "truncated", -4: "record or header field "
+                             "inconsistent with its length (bam_read1 returns -4, dep/htslib/sam.c:403-406)"}.get(int(c[6]), int(c[6])))
         n, ncig, nseq, nqual = (int(x) for x in c[:4])
         d = {"pos": torch.empty(max(n, 1), dtype=torch.int32, device=dev),
              "flag": torch.empty(max(n, 1), dtype=torch.int16, device=dev),

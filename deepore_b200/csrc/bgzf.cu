@@ -51,7 +51,8 @@ __device__ __forceinline__ int32_t ld_i32(const uint8_t *p)
 }
 
 // counts: [0] records kept, [1] CIGAR ops, [2] packed sequence bytes, [3] quality bytes, [4] tid (-1: all / not found),
-//         [5] records seen, [6] status (0 ok, -1 bad magic, -2 truncated, -3 contig not found)
+//         [5] records seen, [6] status (0 ok, -1 bad magic, -2 truncated, -3 contig not found, -4 inconsistent record /
+//         header field: what bam_read1 answers with -4, dep/htslib/sam.c:403-406)
 __global__ void bam_scan_kernel(const uint8_t *__restrict__ bam, int64_t n_bytes, const char *__restrict__ contig,
                                 int32_t contig_len, int64_t max_records, int64_t *__restrict__ rec_off,
                                 int64_t *__restrict__ cigar_off, int64_t *__restrict__ seq_off,
@@ -61,9 +62,12 @@ __global__ void bam_scan_kernel(const uint8_t *__restrict__ bam, int64_t n_bytes
     for (int i = 0; i < 7; ++i) counts[i] = 0;
     counts[4] = -1;
     if (n_bytes < 12 || bam[0] != 'B' || bam[1] != 'A' || bam[2] != 'M' || bam[3] != 1) { counts[6] = -1; return; }
-    int64_t off = 8 + (int64_t)ld_i32(bam + 4);
+    const int32_t l_text = ld_i32(bam + 4);
+    if (l_text < 0) { counts[6] = -4; return; }                  // a negative length would walk backwards
+    int64_t off = 8 + (int64_t)l_text;
     if (off + 4 > n_bytes) { counts[6] = -2; return; }
     int32_t n_ref = ld_i32(bam + off);
+    if (n_ref < 0) { counts[6] = -4; return; }
     off += 4;
     int32_t tid = -1;
     for (int32_t r = 0; r < n_ref; ++r) {
@@ -84,6 +88,14 @@ __global__ void bam_scan_kernel(const uint8_t *__restrict__ bam, int64_t n_bytes
         int32_t block_size = ld_i32(bam + off);
         if (block_size < 32 || off + 4 + block_size > n_bytes) { counts[6] = -2; break; }
         ++seen;
+        {   // the consistency rule of bam_read1 (dep/htslib/sam.c:397-406, which returns -4): the variable-length parts must
+            // fit the record, or dp_bam_extract would read past it and the running offsets would go wrong
+            const int32_t l_name = bam[off + 12];
+            const int32_t n_cig0 = (int32_t)bam[off + 16] | ((int32_t)bam[off + 17] << 8);
+            const int32_t l_seq0 = ld_i32(bam + off + 20);
+            if (l_seq0 < 0 || l_name < 1 ||
+                32ll + l_name + 4ll * n_cig0 + (((int64_t)l_seq0 + 1) >> 1) + l_seq0 > (int64_t)block_size) { counts[6] = -4; break; }
+        }
         if (tid < 0 || ld_i32(bam + off + 4) == tid) {
             int32_t n_cig = (int32_t)bam[off + 16] | ((int32_t)bam[off + 17] << 8);
             int32_t l_seq = ld_i32(bam + off + 20);

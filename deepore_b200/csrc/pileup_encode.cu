@@ -1501,6 +1501,131 @@ static size_t encoder_smem_bytes(const dp_encode_params *p) {
 }  // namespace dp
 
 // ================================================================================================
+namespace dp {
+
+// Workspace of one read batch.  Everything up to `fblist` depends on the READS only, so a batch prepared once
+// (dp_encode_prepare) serves any number of dp_encode_prepared / dp_window_ranges calls of up to `n_windows` windows.
+struct WsLayout {
+    int64_t hdr, aux, RP, QP, info, ckpt, endk, code0, dbg, pmax, tmax, fblist, total;
+};
+constexpr int PM_THREADS = 256, PM_PER = 4, PM_TILE = PM_THREADS * PM_PER;     // prefix-maximum tiles of 1024 reads
+
+static WsLayout ws_layout(int32_t n_reads, int64_t n_cigar, int64_t n_bases, int32_t n_windows) {
+    WsLayout l;
+    const int64_t nr = n_reads > 0 ? n_reads : 1;
+    int64_t b = 0;
+    l.hdr = b;    b += 256;                                                                   /* word 0: fallback count */
+    l.aux = b;    b += align_up((int64_t)sizeof(ReadAux) * nr, 256);
+    l.RP = b;     b += align_up((int64_t)sizeof(int) * (n_cigar + n_reads + 1), 256);          /* nops+1 per read */
+    l.QP = b;     b += align_up((int64_t)sizeof(int) * (n_cigar + 1), 256);
+    l.info = b;   b += align_up((int64_t)sizeof(ReadInfo) * nr, 256);
+    l.ckpt = b;   b += align_up((int64_t)sizeof(int) * ((n_cigar >> 1) + n_reads + 2), 256);   /* checkpoints */
+    l.endk = b;   b += align_up((int64_t)sizeof(int) * nr, 256);                              /* filtered endpos */
+    l.code0 = b;  b += align_up((n_bases > 0 ? n_bases : 0) + 16, 256);                       /* per-base code bytes */
+    l.dbg = b;    b += 256;                                                                   /* phase clocks (debug) */
+    l.pmax = b;   b += align_up((int64_t)sizeof(int) * nr, 256);                              /* running max of endpos */
+    l.tmax = b;   b += align_up((int64_t)sizeof(int) * ((nr + PM_TILE - 1) / PM_TILE + 1), 256);
+    l.fblist = b; b += align_up((int64_t)sizeof(int) * ((n_windows > 0 ? n_windows : 0) + 64), 256);
+    l.total = b;
+    return l;
+}
+
+// ---- candidate read range per window on the device (reads.ReadBatch.window_ranges: lo = number of reads whose RUNNING
+// MAXIMUM of bam_endpos is <= queryStart, hi = number of reads with pos < queryEnd; a superset of what pysam.fetch returns,
+// dep/htslib/hts.c:2242 -- the encoder re-applies the exact rule).  Tile-local inclusive maximum scan + tile maxima ...
+__global__ void __launch_bounds__(PM_THREADS) prefmax_tiles_kernel(const ReadAux *__restrict__ aux, const int32_t *__restrict__ pos,
+                                                                   int n, int *__restrict__ pmax, int *__restrict__ tmax,
+                                                                   int32_t *__restrict__ unsorted) {
+    __shared__ int s_w[PM_THREADS / 32];
+    const int base = blockIdx.x * PM_TILE + threadIdx.x * PM_PER;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int v[PM_PER];
+    int run = INT_MIN;
+    bool bad = false;
+#pragma unroll
+    for (int k = 0; k < PM_PER; k++) {
+        const int i = base + k;
+        int e = INT_MIN;
+        if (i < n) {
+            e = aux[i].endpos;
+            if (i + 1 < n && pos[i + 1] < pos[i]) bad = true;    // pysam.fetch needs a coordinate-sorted file
+        }
+        run = max(run, e);
+        v[k] = run;
+    }
+    if (bad) *unsorted = 1;
+    int incl = run;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d) incl = max(incl, t);
+    }
+    if (lane == 31) s_w[warp] = incl;
+    __syncthreads();
+    int before = INT_MIN;                                        // maximum of all earlier threads of the tile
+    for (int w = 0; w < warp; w++) before = max(before, s_w[w]);
+    const int prev = __shfl_up_sync(0xffffffffu, incl, 1);
+    if (lane > 0) before = max(before, prev);
+#pragma unroll
+    for (int k = 0; k < PM_PER; k++)
+        if (base + k < n) pmax[base + k] = max(v[k], before);
+    if (threadIdx.x == PM_THREADS - 1) tmax[blockIdx.x] = max(incl, before);
+}
+
+// ... exclusive maximum scan of the tile maxima (one block; tmax[t] becomes the maximum of all tiles before t)
+__global__ void __launch_bounds__(1024) prefmax_spine_kernel(int *__restrict__ tmax, int tiles) {
+    __shared__ int s_w[32];
+    __shared__ int s_carry;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) s_carry = INT_MIN;
+    __syncthreads();
+    for (int t0 = 0; t0 < tiles; t0 += 1024) {
+        const int i = t0 + threadIdx.x;
+        const int own = i < tiles ? tmax[i] : INT_MIN;
+        int incl = own;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, incl, d);
+            if (lane >= d) incl = max(incl, t);
+        }
+        if (lane == 31) s_w[warp] = incl;
+        __syncthreads();
+        int before = s_carry;
+        for (int w = 0; w < warp; w++) before = max(before, s_w[w]);
+        const int prev = __shfl_up_sync(0xffffffffu, incl, 1);
+        if (lane > 0) before = max(before, prev);
+        if (i < tiles) tmax[i] = before;
+        __syncthreads();
+        if (threadIdx.x == 1023) s_carry = max(before, own);
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(256) window_ranges_kernel(const int32_t *__restrict__ pos, const int *__restrict__ pmax,
+                                                            const int *__restrict__ tmax, int n,
+                                                            const int32_t *__restrict__ win_qs, int n_windows, int L,
+                                                            int32_t *__restrict__ win_lo, int32_t *__restrict__ win_hi) {
+    const int w = blockIdx.x * blockDim.x + threadIdx.x;
+    if (w >= n_windows) return;
+    const int qs = win_qs[w], qe = qs + L;
+    int lo = 0, hi = n;                                          // first i with runmax(endpos)[i] > qs
+    while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        const int m = max(pmax[mid], tmax[mid / PM_TILE]);
+        if (m <= qs) lo = mid + 1; else hi = mid;
+    }
+    const int first = lo;
+    lo = 0; hi = n;                                              // first i with pos[i] >= qe
+    while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (pos[mid] < qe) lo = mid + 1; else hi = mid;
+    }
+    win_lo[w] = first;
+    win_hi[w] = max(lo, first);
+}
+
+}  // namespace dp
+
 extern "C" {
 
 const char *dp_last_error(void) { return dp::g_err; }
@@ -1526,35 +1651,61 @@ int dp_set_quality_lut(const uint8_t lut[256]) {
 int64_t dp_encode_workspace_bytes(int32_t n_reads, int64_t n_cigar, int64_t n_bases, int32_t n_windows,
                                   const dp_encode_params *p) {
     (void)p;
-    int64_t b = 0;
-    b += dp::align_up((int64_t)sizeof(dp::ReadAux) * (n_reads > 0 ? n_reads : 1), 256);
-    b += dp::align_up((int64_t)sizeof(int) * (n_cigar + n_reads + 1), 256);   /* RP: nops+1 per read */
-    b += dp::align_up((int64_t)sizeof(int) * (n_cigar + 1), 256);             /* QP */
-    b += dp::align_up((int64_t)sizeof(int) * ((n_windows > 0 ? n_windows : 0) + 64), 256);   /* fallback count + list */
-    b += dp::align_up((int64_t)sizeof(dp::ReadInfo) * (n_reads > 0 ? n_reads : 1), 256);
-    b += dp::align_up((int64_t)sizeof(int) * ((n_cigar >> 1) + n_reads + 2), 256);           /* checkpoints */
-    b += dp::align_up((int64_t)sizeof(int) * (n_reads > 0 ? n_reads : 1), 256);              /* filtered endpos */
-    b += dp::align_up((n_bases > 0 ? n_bases : 0) + 16, 256);                                /* per-base code bytes */
-    b += 256;                                                                                /* phase clocks (debug) */
-    return b;
+    return dp::ws_layout(n_reads, n_cigar, n_bases, n_windows).total;
 }
 
 int dp_encode_fallback_count(const void *workspace, int32_t n_reads, int64_t n_cigar, int32_t *out_count, void *stream) {
     DP_REQUIRE(workspace && out_count && n_reads >= 0 && n_cigar >= 0, "bad argument");
-    const uint8_t *wp = (const uint8_t *)workspace;
-    wp += dp::align_up((int64_t)sizeof(dp::ReadAux) * (n_reads > 0 ? n_reads : 1), 256);
-    wp += dp::align_up((int64_t)sizeof(int) * (n_cigar + n_reads + 1), 256);
-    wp += dp::align_up((int64_t)sizeof(int) * (n_cigar + 1), 256);
     cudaStream_t st = (cudaStream_t)stream;
-    DP_CUDA_CHECK(cudaMemcpyAsync(out_count, wp, sizeof(int), cudaMemcpyDeviceToHost, st));
+    DP_CUDA_CHECK(cudaMemcpyAsync(out_count, workspace, sizeof(int), cudaMemcpyDeviceToHost, st));   /* header word 0 */
     DP_CUDA_CHECK(cudaStreamSynchronize(st));
     return DP_OK;
 }
 
-int dp_encode_windows(const dp_reads *reads, int32_t n_windows, const int32_t *win_qs, const int32_t *win_lo,
-                      const int32_t *win_hi, const uint8_t *ref, int64_t ref_base, int64_t ref_len,
-                      const dp_encode_params *p, uint8_t *out_img, int32_t *out_rowpos, int32_t *out_rowins,
-                      int32_t *out_status, void *workspace, int64_t workspace_bytes, void *stream) {
+}  // extern "C"
+
+namespace dp {
+
+// per-read digests + per-base code bytes of every read of `reads` (depends on the reads only, not on the windows)
+static int encode_prepare(const dp_reads *reads, const dp_encode_params *p, uint8_t *ws, const WsLayout &lay, cudaStream_t st,
+                          cudaEvent_t *ev_mid) {
+    int rc = ensure_lut();
+    if (rc) return rc;
+    ReadAux *aux = (ReadAux *)(ws + lay.aux);
+    int *RP = (int *)(ws + lay.RP), *QP = (int *)(ws + lay.QP);
+    ReadInfo *info = (ReadInfo *)(ws + lay.info);
+    int *ckpt = (int *)(ws + lay.ckpt), *endk = (int *)(ws + lay.endk);
+    uint8_t *code0 = ws + lay.code0;
+    if (reads->n_reads > 0) {
+        if (reads->n_cigar / reads->n_reads >= 96) {           /* long CIGARs (long reads): one block per read */
+            prep_reads_kernel<8><<<reads->n_reads, 256, 0, st>>>(*reads, aux, RP, QP, info, ckpt, endk, p->map_quality_cutoff);
+        } else {
+            const int warps_per_block = 8;
+            const int blocks = (reads->n_reads + warps_per_block - 1) / warps_per_block;
+            prep_reads_kernel<1><<<blocks, 256, 0, st>>>(*reads, aux, RP, QP, info, ckpt, endk, p->map_quality_cutoff);
+        }
+        DP_CUDA_CHECK(cudaGetLastError());
+        if (ev_mid) cudaEventRecord(*ev_mid, st);
+        if (reads->n_bases > 0) {
+            const int64_t nb = (reads->n_bases + 256 * 16 - 1) / (256 * 16);
+            base_codes_kernel<<<(unsigned)(nb < 148 * 64 ? nb : 148 * 64), 256, 0, st>>>(*reads, info, code0);
+            DP_CUDA_CHECK(cudaGetLastError());
+        }
+    } else if (ev_mid) {
+        cudaEventRecord(*ev_mid, st);
+    }
+    return DP_OK;
+}
+
+}  // namespace dp
+
+extern "C" {
+
+static int dp_encode_impl(const dp_reads *reads, int32_t n_windows, const int32_t *win_qs, const int32_t *win_lo,
+                          const int32_t *win_hi, const uint8_t *ref, int64_t ref_base, int64_t ref_len,
+                          const dp_encode_params *p, uint8_t *out_img, int32_t *out_rowpos, int32_t *out_rowins,
+                          int32_t *out_status, void *workspace, int64_t workspace_bytes, int32_t ws_windows,
+                          int32_t bases_per_window, int prepared, void *stream) {
     DP_REQUIRE(reads && p && out_img, "null argument");
     DP_REQUIRE(n_windows >= 0 && reads->n_reads >= 0, "negative extent");
     if (n_windows == 0) return DP_OK;
@@ -1571,47 +1722,29 @@ int dp_encode_windows(const dp_reads *reads, int32_t n_windows, const int32_t *w
     const int64_t n_cigar = reads->n_cigar;
     DP_REQUIRE(n_cigar >= 0, "negative n_cigar");
     DP_REQUIRE(reads->n_bases >= 0, "negative n_bases");
-    const int64_t need = dp_encode_workspace_bytes(reads->n_reads, n_cigar, reads->n_bases, n_windows, p);
-    DP_REQUIRE(workspace && workspace_bytes >= need, "workspace too small (dp_encode_workspace_bytes)");
-    uint8_t *wp = (uint8_t *)workspace;
-    dp::ReadAux *aux = (dp::ReadAux *)wp;
-    wp += dp::align_up((int64_t)sizeof(dp::ReadAux) * (reads->n_reads > 0 ? reads->n_reads : 1), 256);
-    int *RP = (int *)wp;
-    wp += dp::align_up((int64_t)sizeof(int) * (n_cigar + reads->n_reads + 1), 256);
-    int *QP = (int *)wp;
-    wp += dp::align_up((int64_t)sizeof(int) * (n_cigar + 1), 256);
-    int *fb = (int *)wp;                                       /* fb[0] = count, fb[64..] = window list */
-    wp += dp::align_up((int64_t)sizeof(int) * (n_windows + 64), 256);
-    dp::ReadInfo *info = (dp::ReadInfo *)wp;
-    wp += dp::align_up((int64_t)sizeof(dp::ReadInfo) * (reads->n_reads > 0 ? reads->n_reads : 1), 256);
-    int *ckpt = (int *)wp;
-    wp += dp::align_up((int64_t)sizeof(int) * ((n_cigar >> 1) + reads->n_reads + 2), 256);
-    int *endk = (int *)wp;
-    wp += dp::align_up((int64_t)sizeof(int) * (reads->n_reads > 0 ? reads->n_reads : 1), 256);
-    uint8_t *code0 = wp;
-    wp += dp::align_up((reads->n_bases > 0 ? reads->n_bases : 0) + 16, 256);
-    unsigned long long *dbg = (unsigned long long *)wp;
+    DP_REQUIRE(ws_windows >= n_windows, "more windows than the workspace was sized for");
+    const dp::WsLayout lay = dp::ws_layout(reads->n_reads, n_cigar, reads->n_bases, ws_windows);
+    DP_REQUIRE(workspace && workspace_bytes >= lay.total, "workspace too small (dp_encode_workspace_bytes)");
+    uint8_t *wsb = (uint8_t *)workspace;
+    dp::ReadAux *aux = (dp::ReadAux *)(wsb + lay.aux);
+    int *RP = (int *)(wsb + lay.RP), *QP = (int *)(wsb + lay.QP);
+    int *fb = (int *)(wsb + lay.hdr);                          /* fb[0] = count of windows listed for the exact kernel */
+    int *fblist = (int *)(wsb + lay.fblist);
+    dp::ReadInfo *info = (dp::ReadInfo *)(wsb + lay.info);
+    int *ckpt = (int *)(wsb + lay.ckpt), *endk = (int *)(wsb + lay.endk);
+    uint8_t *code0 = wsb + lay.code0;
+    unsigned long long *dbg = (unsigned long long *)(wsb + lay.dbg);
 
     /* DP_ENC_TIMING=1: CUDA events around each kernel of this call, printed to stderr (synchronises; debugging aid) */
     static int timing = -1;
     if (timing < 0) { const char *e = getenv("DP_ENC_TIMING"); timing = (e && e[0] == '1') ? 1 : 0; }
     cudaEvent_t ev[5];
     if (timing) { for (int i = 0; i < 5; i++) cudaEventCreate(&ev[i]); cudaEventRecord(ev[0], st); }
-    if (reads->n_reads > 0) {
-        if (n_cigar / reads->n_reads >= 96) {                  /* long CIGARs (long reads): one block per read */
-            dp::prep_reads_kernel<8><<<reads->n_reads, 256, 0, st>>>(*reads, aux, RP, QP, info, ckpt, endk, p->map_quality_cutoff);
-        } else {
-            const int warps_per_block = 8;
-            const int blocks = (reads->n_reads + warps_per_block - 1) / warps_per_block;
-            dp::prep_reads_kernel<1><<<blocks, 256, 0, st>>>(*reads, aux, RP, QP, info, ckpt, endk, p->map_quality_cutoff);
-        }
-        DP_CUDA_CHECK(cudaGetLastError());
-        if (reads->n_bases > 0) {
-            const int64_t nb = (reads->n_bases + 256 * 16 - 1) / (256 * 16);
-            if (timing) cudaEventRecord(ev[1], st);
-            dp::base_codes_kernel<<<(unsigned)(nb < 148 * 64 ? nb : 148 * 64), 256, 0, st>>>(*reads, info, code0);
-            DP_CUDA_CHECK(cudaGetLastError());
-        }
+    if (!prepared) {
+        rc = dp::encode_prepare(reads, p, wsb, lay, st, timing ? &ev[1] : nullptr);
+        if (rc) return rc;
+    } else if (timing) {
+        cudaEventRecord(ev[1], st);
     }
     if (timing) cudaEventRecord(ev[2], st);
     dp::EncArgs a;
@@ -1630,8 +1763,10 @@ int dp_encode_windows(const dp_reads *reads, int32_t n_windows, const int32_t *w
     // 3 CTAs on a larger one; thresholds from a coverage sweep (45 / 60 / 75 / 90x: the 4-CTA build wins at 45-75x, the 3-CTA one from 90x)
     static int force_pool = -1;                                /* DP_ENC_POOL = small | large | deep overrides the choice */
     if (force_pool < 0) { const char *e = getenv("DP_ENC_POOL"); force_pool = !e ? 0 : !strcmp(e, "small") ? 1 : !strcmp(e, "large") ? 2 : !strcmp(e, "deep") ? 3 : 0; }
-    const bool small_pool = force_pool == 1 || (force_pool == 0 && reads->n_bases < (int64_t)4000 * n_windows);
-    const bool deep_pool = force_pool == 3 || (force_pool == 0 && reads->n_bases >= (int64_t)8700 * n_windows);
+    // read bases per window: the caller's figure when the read arrays cover more than this call's windows (prepared mode)
+    const int64_t bpw = bases_per_window > 0 ? bases_per_window : reads->n_bases / n_windows;
+    const bool small_pool = force_pool == 1 || (force_pool == 0 && bpw < 4000);
+    const bool deep_pool = force_pool == 3 || (force_pool == 0 && bpw >= 8700);
     const size_t smem3 = dp::encoder_v3_smem_bytes(p, small_pool ? dp::V3_POOL_SMALL : deep_pool ? dp::V3_POOL_DEEP : dp::V3_POOL_BYTES);
     const bool use_v3 = !force_v1 && dp::g_lut_flat && L <= dp::V3_CS && p->window_cutoff <= 256 &&
                         p->coverage_cutoff >= 8 && p->coverage_cutoff <= 256 && smem3 <= 100 * 1024;
@@ -1652,14 +1787,14 @@ int dp_encode_windows(const dp_reads *reads, int32_t n_windows, const int32_t *w
     if (emit_mode < 0) { const char *e = getenv("DP_ENC_EMIT"); emit_mode = (e && !strcmp(e, "stg")) ? 1 : 0; }
     if (timing) cudaMemsetAsync(dbg, 0, 256, st);
     if (small_pool)
-        dp::encode_windows_v3_kernel<5, dp::V3_POOL_SMALL><<<n_windows, dp::V3_THREADS, smem3, st>>>(a, fb, fb + 64, emit_mode, timing ? dbg : nullptr);
+        dp::encode_windows_v3_kernel<5, dp::V3_POOL_SMALL><<<n_windows, dp::V3_THREADS, smem3, st>>>(a, fb, fblist, emit_mode, timing ? dbg : nullptr);
     else if (deep_pool)
-        dp::encode_windows_v3_kernel<3, dp::V3_POOL_DEEP><<<n_windows, dp::V3_THREADS, smem3, st>>>(a, fb, fb + 64, emit_mode, timing ? dbg : nullptr);
+        dp::encode_windows_v3_kernel<3, dp::V3_POOL_DEEP><<<n_windows, dp::V3_THREADS, smem3, st>>>(a, fb, fblist, emit_mode, timing ? dbg : nullptr);
     else
-        dp::encode_windows_v3_kernel<4, dp::V3_POOL_BYTES><<<n_windows, dp::V3_THREADS, smem3, st>>>(a, fb, fb + 64, emit_mode, timing ? dbg : nullptr);
+        dp::encode_windows_v3_kernel<4, dp::V3_POOL_BYTES><<<n_windows, dp::V3_THREADS, smem3, st>>>(a, fb, fblist, emit_mode, timing ? dbg : nullptr);
     DP_CUDA_CHECK(cudaGetLastError());
     if (timing) cudaEventRecord(ev[3], st);
-    dp::encode_windows_kernel<<<n_windows, dp::ENC_THREADS, smem, st>>>(a, fb, fb + 64);
+    dp::encode_windows_kernel<<<n_windows, dp::ENC_THREADS, smem, st>>>(a, fb, fblist);
     DP_CUDA_CHECK(cudaGetLastError());
     if (timing) {
         cudaEventRecord(ev[4], st);
@@ -1677,6 +1812,57 @@ int dp_encode_windows(const dp_reads *reads, int32_t n_windows, const int32_t *w
         for (int i = 0; i < 10; i++) fprintf(stderr, " %llu", hd[i] / (unsigned long long)n_windows);
         fprintf(stderr, "\n");
     }
+    return DP_OK;
+}
+
+int dp_encode_windows(const dp_reads *reads, int32_t n_windows, const int32_t *win_qs, const int32_t *win_lo,
+                      const int32_t *win_hi, const uint8_t *ref, int64_t ref_base, int64_t ref_len,
+                      const dp_encode_params *p, uint8_t *out_img, int32_t *out_rowpos, int32_t *out_rowins,
+                      int32_t *out_status, void *workspace, int64_t workspace_bytes, void *stream) {
+    return dp_encode_impl(reads, n_windows, win_qs, win_lo, win_hi, ref, ref_base, ref_len, p, out_img, out_rowpos, out_rowins,
+                          out_status, workspace, workspace_bytes, n_windows, 0, 0, stream);
+}
+
+int dp_encode_prepare(const dp_reads *reads, const dp_encode_params *p, int32_t max_windows, void *workspace,
+                      int64_t workspace_bytes, void *stream) {
+    DP_REQUIRE(reads && p && reads->n_reads >= 0 && reads->n_cigar >= 0 && reads->n_bases >= 0 && max_windows >= 0, "bad argument");
+    const dp::WsLayout lay = dp::ws_layout(reads->n_reads, reads->n_cigar, reads->n_bases, max_windows);
+    DP_REQUIRE(workspace && workspace_bytes >= lay.total, "workspace too small (dp_encode_workspace_bytes)");
+    return dp::encode_prepare(reads, p, (uint8_t *)workspace, lay, (cudaStream_t)stream, nullptr);
+}
+
+int dp_encode_prepared(const dp_reads *reads, int32_t n_windows, const int32_t *win_qs, const int32_t *win_lo,
+                       const int32_t *win_hi, const uint8_t *ref, int64_t ref_base, int64_t ref_len,
+                       const dp_encode_params *p, uint8_t *out_img, int32_t *out_rowpos, int32_t *out_rowins,
+                       int32_t *out_status, void *workspace, int64_t workspace_bytes, int32_t max_windows,
+                       int32_t bases_per_window, void *stream) {
+    return dp_encode_impl(reads, n_windows, win_qs, win_lo, win_hi, ref, ref_base, ref_len, p, out_img, out_rowpos, out_rowins,
+                          out_status, workspace, workspace_bytes, max_windows, bases_per_window, 1, stream);
+}
+
+int dp_window_ranges(const dp_reads *reads, const void *workspace, int64_t workspace_bytes, int32_t max_windows,
+                     int32_t n_windows, const int32_t *win_qs, int32_t flank, int32_t *win_lo, int32_t *win_hi,
+                     int32_t *unsorted, void *stream) {
+    DP_REQUIRE(reads && reads->n_reads >= 0 && n_windows >= 0 && flank >= 0 && max_windows >= 0, "bad argument");
+    if (n_windows == 0) return DP_OK;
+    DP_REQUIRE(win_qs && win_lo && win_hi && unsorted, "null argument");
+    const dp::WsLayout lay = dp::ws_layout(reads->n_reads, reads->n_cigar, reads->n_bases, max_windows);
+    DP_REQUIRE(workspace && workspace_bytes >= lay.total, "workspace too small (dp_encode_workspace_bytes)");
+    cudaStream_t st = (cudaStream_t)stream;
+    uint8_t *wsb = (uint8_t *)workspace;
+    const dp::ReadAux *aux = (const dp::ReadAux *)(wsb + lay.aux);
+    int *pmax = (int *)(wsb + lay.pmax), *tmax = (int *)(wsb + lay.tmax);
+    const int n = reads->n_reads;
+    DP_CUDA_CHECK(cudaMemsetAsync(unsorted, 0, sizeof(int32_t), st));
+    if (n > 0) {
+        const int tiles = (n + dp::PM_TILE - 1) / dp::PM_TILE;
+        dp::prefmax_tiles_kernel<<<tiles, dp::PM_THREADS, 0, st>>>(aux, reads->pos, n, pmax, tmax, unsorted);
+        dp::prefmax_spine_kernel<<<1, 1024, 0, st>>>(tmax, tiles);
+        DP_CUDA_CHECK(cudaGetLastError());
+    }
+    dp::window_ranges_kernel<<<(n_windows + 255) / 256, 256, 0, st>>>(reads->pos, pmax, tmax, n, win_qs, n_windows, 2 * flank + 1,
+                                                                       win_lo, win_hi);
+    DP_CUDA_CHECK(cudaGetLastError());
     return DP_OK;
 }
 

@@ -160,3 +160,50 @@ def window_starts(region_lo: int, region_hi: int, stride: int = 100, flank: int 
     """queryStart of windows whose centres tile [region_lo, region_hi) at `stride`."""
     centres = np.arange(region_lo + flank, region_hi - flank - 1, stride, dtype=np.int64)
     return (centres - flank).astype(np.int32)
+
+
+def bam_stream(rb, contig: str = "chr3", contig_len: int = 9_000_000) -> bytes:
+    """Uncompressed BAM stream of a ReadBatch: magic, header with one reference, then one record per read in the layout of
+    dep/htslib/htslib/sam.h:154-195 (name "r", no aux fields) -- the bytes a `samtools view -b` of these alignments holds."""
+    import struct
+    parts = [b"BAM\1", struct.pack("<i", 0), struct.pack("<i", 1), struct.pack("<i", len(contig) + 1),
+             contig.encode() + b"\0", struct.pack("<i", contig_len)]
+    cig = np.ascontiguousarray(rb.cigar, dtype="<u4")
+    for i in range(rb.n_reads):
+        c = cig[rb.cigar_off[i]:rb.cigar_off[i + 1]].tobytes()
+        s = rb.seq4[rb.seq_off[i]:rb.seq_off[i + 1]].tobytes()
+        q = rb.qual[rb.qual_off[i]:rb.qual_off[i + 1]].tobytes()
+        body = struct.pack("<iiBBHHHiiii", 0, int(rb.pos[i]), 2, int(rb.mapq[i]), 0, len(c) // 4, int(rb.flag[i]),
+                           int(rb.l_seq[i]), -1, -1, 0) + b"r\0" + c + s + q
+        parts.append(struct.pack("<i", len(body)))
+        parts.append(body)
+    return b"".join(parts)
+
+
+def bgzf_image(data: bytes, level: int = 6, chunk: int = 0xff00, threads: int = 0) -> np.ndarray:
+    """BGZF file image of `data` as a uint8 array: blocks of `chunk` input bytes (htslib's BGZF_BLOCK_SIZE), 18-byte header
+    with the 'BC' BSIZE sub-field, raw DEFLATE payload from zlib (the library htslib itself calls, dep/htslib/bgzf.c), CRC32 +
+    ISIZE, the empty EOF block last.  zlib releases the GIL, so `threads` > 1 compresses blocks in parallel."""
+    import struct
+    import zlib
+
+    def block(raw: bytes) -> bytes:
+        co = zlib.compressobj(level, zlib.DEFLATED, -15)
+        payload = co.compress(raw) + co.flush()
+        bsize = 18 + len(payload) + 8
+        if bsize > 65536:                                      # incompressible input: a stored block always fits
+            co = zlib.compressobj(0, zlib.DEFLATED, -15)
+            payload = co.compress(raw) + co.flush()
+            bsize = 18 + len(payload) + 8
+        head = struct.pack("<BBBBIBBHBBHH", 31, 139, 8, 4, 0, 0, 255, 6, 66, 67, 2, bsize - 1)
+        return head + payload + struct.pack("<II", zlib.crc32(raw) & 0xffffffff, len(raw))
+
+    pieces = [data[i:i + chunk] for i in range(0, len(data), chunk)]
+    if threads and threads > 1 and len(pieces) > 1:
+        from concurrent.futures import ThreadPoolExecutor
+        with ThreadPoolExecutor(max_workers=threads) as ex:
+            out = list(ex.map(block, pieces))
+    else:
+        out = [block(x) for x in pieces]
+    out.append(block(b""))
+    return np.frombuffer(b"".join(out), dtype=np.uint8)

@@ -88,6 +88,34 @@ int dp_encode_windows(const dp_reads *reads, int32_t n_windows, const int32_t *w
                       uint8_t *out_img, int32_t *out_rowpos, int32_t *out_rowins, int32_t *out_status,
                       void *workspace, int64_t workspace_bytes, void *stream);
 
+/*
+ * Contig-resident form of the same path (the file -> calls pipeline, deepore_b200/pipeline.py): the read arrays of a whole
+ * contig stay in HBM, their per-read digests and per-base codes are built ONCE, and the windows are encoded in batches.
+ *
+ *   dp_encode_prepare    the read-dependent half of dp_encode_windows (per-read CIGAR prefix sums, bam_endpos, checkpoints,
+ *                        per-base category/quality codes) into `workspace`, which must hold
+ *                        dp_encode_workspace_bytes(n_reads, n_cigar, n_bases, max_windows, p) bytes
+ *   dp_window_ranges     replaces the host index of reads.ReadBatch.window_ranges (the `fetch` of Pileup.py:36 /
+ *                        dep/htslib/hts.c:2242 as a candidate range): win_lo[w] = number of reads whose running maximum of
+ *                        bam_endpos is <= win_qs[w], win_hi[w] = number of reads with pos < win_qs[w] + 2*flank + 1.
+ *                        *unsorted is set to 1 when pos[] is not ascending (pysam.fetch needs a coordinate-sorted file).
+ *                        Needs a prepared workspace (it reads the bam_endpos values dp_encode_prepare left there).
+ *   dp_encode_prepared   the window-dependent half: same arguments and results as dp_encode_windows; n_windows <= max_windows;
+ *                        bases_per_window = read bases overlapping an average window (picks the shared-memory build of the
+ *                        kernel; <= 0: n_bases / n_windows, right only when `reads` holds just this batch's reads)
+ * All pointers are device pointers; nothing synchronises.
+ */
+int dp_encode_prepare(const dp_reads *reads, const dp_encode_params *p, int32_t max_windows, void *workspace,
+                      int64_t workspace_bytes, void *stream);
+int dp_window_ranges(const dp_reads *reads, const void *workspace, int64_t workspace_bytes, int32_t max_windows,
+                     int32_t n_windows, const int32_t *win_qs, int32_t flank, int32_t *win_lo, int32_t *win_hi,
+                     int32_t *unsorted, void *stream);
+int dp_encode_prepared(const dp_reads *reads, int32_t n_windows, const int32_t *win_qs, const int32_t *win_lo,
+                       const int32_t *win_hi, const uint8_t *ref, int64_t ref_base, int64_t ref_len,
+                       const dp_encode_params *p, uint8_t *out_img, int32_t *out_rowpos, int32_t *out_rowins,
+                       int32_t *out_status, void *workspace, int64_t workspace_bytes, int32_t max_windows,
+                       int32_t bases_per_window, void *stream);
+
 /* Diagnostics: how many windows of the LAST dp_encode_windows call on this workspace left the fast kernel's
  * envelope and were recomputed by the exact general kernel (results are identical either way).  Synchronises
  * the stream. */
@@ -203,7 +231,8 @@ int dp_bgzf_inflate(const uint8_t *file, int64_t n_blocks, const int64_t *in_off
  * (< max_records) writes rec_off[i] (byte offset of its length prefix) and the running cigar_off / seq_off / qual_off
  * of dp_reads (arrays of max_records + 1 entries; entry [kept] closes them).  counts (7 x int64): records kept, CIGAR
  * ops, packed sequence bytes, quality bytes, tid, records seen, status (0 ok, -1 bad magic, -2 truncated, -3 contig
- * not in the header). */
+ * not in the header, -4 a record whose l_seq / l_read_name / n_cigar_op do not fit its block_size or a negative header
+ * length -- the cases bam_read1 rejects with -4, dep/htslib/sam.c:397-406; nothing is extracted from such a stream). */
 int dp_bam_scan(const uint8_t *bam, int64_t n_bytes, const char *contig, int32_t contig_len, int64_t max_records,
                 int64_t *rec_off, int64_t *cigar_off, int64_t *seq_off, int64_t *qual_off, int64_t *counts, void *stream);
 

