@@ -457,9 +457,9 @@ def main():
                  status=torch.empty((nw,), dtype=torch.int32, device=dev),
                  pred=torch.empty((nw * H, 3), dtype=torch.uint8, device=dev),
                  calls=torch.empty((nw, H), dtype=torch.int8, device=dev)) for _ in range(2)]
-    host_status = torch.empty((nsteps, nw), dtype=torch.int32).pin_memory()
+    host_status = torch.zeros((nsteps, nw), dtype=torch.int32).pin_memory()
     host_rowpos = torch.empty((nw, H), dtype=torch.int32).pin_memory()
-    host_calls = torch.empty((nsteps, nw, H), dtype=torch.int8).pin_memory()
+    host_calls = torch.full((nsteps, nw, H), -1, dtype=torch.int8).pin_memory()
     host_group = dist.new_group(backend="gloo") if world > 1 else None      # host path of the result gather
     import ctypes as C
 
@@ -574,7 +574,9 @@ def main():
     assert (st_host == 0).all(), "a timed shard returned a non-zero window status: %s" % np.unique(st_host)
     if with_model:
         hc = host_calls[args.warmup:].numpy()
-        assert ((hc[:, :, 2:148] >= 0) & (hc[:, :, 2:148] < 3)).all() and (hc[:, :, :2] == -1).all(), "calls out of range"
+        for k, b in enumerate(bufs[args.warmup:]):
+            assert ((hc[k, :b.n_windows, 2:148] >= 0) & (hc[k, :b.n_windows, 2:148] < 3)).all(), "calls out of range"
+        assert (hc[:, :, :2] == -1).all()
     enc_ms = time_encoder_alone()
     # the same path in the parity-grade precision (operands split hi + lo, three passes), fewer words: value / e2e only
     x3 = None

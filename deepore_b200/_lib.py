@@ -100,6 +100,10 @@ def lib():
     L.dp_bam_scan.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_int32, C.c_int64] + [C.c_void_p] * 6
     L.dp_bam_extract.restype = C.c_int
     L.dp_bam_extract.argtypes = [C.c_void_p, C.c_int64] + [C.c_void_p] * 12
+    L.dp_png_size.restype = C.c_int64
+    L.dp_png_size.argtypes = [C.c_int32, C.c_int32]
+    L.dp_png_encode.restype = C.c_int
+    L.dp_png_encode.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_int64, C.c_void_p]
     _lib = L
     return L
 

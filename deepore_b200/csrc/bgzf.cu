@@ -14,6 +14,7 @@
 //   bam_extract_kernel    one warp per kept record: core fields + coalesced copies of CIGAR, packed bases, qualities
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "../../include/deepore_b200.h"
@@ -56,9 +57,10 @@ __device__ __forceinline__ int32_t ld_i32(const uint8_t *p)
 __global__ void bam_scan_kernel(const uint8_t *__restrict__ bam, int64_t n_bytes, const char *__restrict__ contig,
                                 int32_t contig_len, int64_t max_records, int64_t *__restrict__ rec_off,
                                 int64_t *__restrict__ cigar_off, int64_t *__restrict__ seq_off,
-                                int64_t *__restrict__ qual_off, int64_t *__restrict__ counts)
+                                int64_t *__restrict__ qual_off, int64_t *__restrict__ counts, const int *__restrict__ gate)
 {
     if (blockIdx.x != 0 || threadIdx.x != 0) return;
+    if (gate && *gate == 0) return;                              // the parallel scan below already produced the result
     for (int i = 0; i < 7; ++i) counts[i] = 0;
     counts[4] = -1;
     if (n_bytes < 12 || bam[0] != 'B' || bam[1] != 'A' || bam[2] != 'M' || bam[3] != 1) { counts[6] = -1; return; }
@@ -119,6 +121,228 @@ __global__ void bam_scan_kernel(const uint8_t *__restrict__ bam, int64_t n_bytes
         qual_off[kept] = nqual;
     }
     counts[0] = kept; counts[1] = ncig; counts[2] = nseq; counts[3] = nqual; counts[5] = seen;
+}
+
+// ---- parallel scan.  The record chain is sequential (each length prefix gives the next record): one thread chasing it
+// pays a DRAM round trip per record (12.4 ms for the 17 650 records of a 355 MB contig).  Here the stream is cut into
+// segments; a warp per segment GUESSES the first record start inside it (the first offset whose 36 leading bytes look like
+// a record -- htslib's own consistency rule, dep/htslib/sam.c:397-406, plus a NUL-terminated name and reference ids inside
+// the header's range -- and from which the chain stays consistent up to the segment's end) and walks the segment from
+// there.  The guesses are then PROVEN: starting from the true first record behind the header, the exit offset of every
+// segment on the chain must be exactly the guessed entry of the segment it lands in.  If any link fails (or the stream is
+// malformed) the serial kernel above runs instead, so the result is exact either way; on htslib-written files every link
+// holds.
+struct ScanSeg {
+    int64_t entry;                 // first record start inside the segment (-1: none found)
+    int64_t exit;                  // first record start at or behind the segment's end
+    int64_t kept, ncig, nseq, nqual;
+};
+constexpr int SCAN_MAXSEG = 2048;
+constexpr int SCAN_TRIES = 48;     // candidates walked per segment before giving up
+
+__device__ __forceinline__ bool bam_record_plausible(const uint8_t *bam, int64_t n_bytes, int64_t o, int32_t n_ref)
+{
+    if (o + 36 > n_bytes) return false;
+    const int32_t bs = ld_i32(bam + o);
+    if (bs < 32 || o + 4 + (int64_t)bs > n_bytes) return false;
+    const int32_t tid = ld_i32(bam + o + 4), pos = ld_i32(bam + o + 8);
+    const int32_t l_name = bam[o + 12];
+    const int32_t n_cig = (int32_t)bam[o + 16] | ((int32_t)bam[o + 17] << 8);
+    const int32_t l_seq = ld_i32(bam + o + 20);
+    const int32_t mtid = ld_i32(bam + o + 24), mpos = ld_i32(bam + o + 28);
+    if (tid < -1 || tid >= n_ref || mtid < -1 || mtid >= n_ref || pos < -1 || mpos < -1) return false;
+    if (l_seq < 0 || l_name < 1) return false;
+    if (32ll + l_name + 4ll * n_cig + (((int64_t)l_seq + 1) >> 1) + l_seq > (int64_t)bs) return false;
+    return bam[o + 36 + l_name - 1] == 0;                        // read names are NUL-terminated
+}
+
+// hdr: [0] offset of the first record, [1] tid of the wanted contig (-1: all), [2] n_ref, [3] status (0 ok)
+__global__ void bam_header_kernel(const uint8_t *__restrict__ bam, int64_t n_bytes, const char *__restrict__ contig,
+                                  int32_t contig_len, int64_t *__restrict__ hdr)
+{
+    if (blockIdx.x != 0 || threadIdx.x != 0) return;
+    hdr[0] = 0; hdr[1] = -1; hdr[2] = 0; hdr[3] = 0;
+    if (n_bytes < 12 || bam[0] != 'B' || bam[1] != 'A' || bam[2] != 'M' || bam[3] != 1) { hdr[3] = -1; return; }
+    const int32_t l_text = ld_i32(bam + 4);
+    if (l_text < 0) { hdr[3] = -4; return; }
+    int64_t off = 8 + (int64_t)l_text;
+    if (off + 4 > n_bytes) { hdr[3] = -2; return; }
+    const int32_t n_ref = ld_i32(bam + off);
+    if (n_ref < 0) { hdr[3] = -4; return; }
+    off += 4;
+    int32_t tid = -1;
+    for (int32_t r = 0; r < n_ref; ++r) {
+        if (off + 4 > n_bytes) { hdr[3] = -2; return; }
+        const int32_t l_name = ld_i32(bam + off);
+        if (l_name < 1 || off + 8 + l_name > n_bytes) { hdr[3] = -2; return; }
+        if (tid < 0 && contig_len > 0 && l_name - 1 == contig_len) {
+            bool same = true;
+            for (int32_t k = 0; k < contig_len && same; ++k) same = bam[off + 4 + k] == (uint8_t)contig[k];
+            if (same) tid = r;
+        }
+        off += 8 + l_name;
+    }
+    if (contig_len > 0 && tid < 0) { hdr[3] = -3; return; }
+    hdr[0] = off; hdr[1] = tid; hdr[2] = n_ref;
+}
+
+// walks the chain from `o` while it starts inside [.., seg_end); false if a record fails the consistency rule
+__device__ __forceinline__ bool bam_walk_segment(const uint8_t *bam, int64_t n_bytes, int64_t o, int64_t seg_end, int32_t n_ref,
+                                                 int32_t tid, ScanSeg &g)
+{
+    g.kept = g.ncig = g.nseq = g.nqual = 0;
+    while (o < seg_end) {
+        if (o == n_bytes) break;
+        if (!bam_record_plausible(bam, n_bytes, o, n_ref)) return false;
+        if (tid < 0 || ld_i32(bam + o + 4) == tid) {
+            const int32_t n_cig = (int32_t)bam[o + 16] | ((int32_t)bam[o + 17] << 8);
+            const int32_t l_seq = ld_i32(bam + o + 20);
+            g.kept++; g.ncig += n_cig; g.nseq += (l_seq + 1) >> 1; g.nqual += l_seq;
+        }
+        o += 4 + (int64_t)ld_i32(bam + o);
+    }
+    g.exit = o;
+    return true;
+}
+
+__global__ void __launch_bounds__(128)
+bam_seg_kernel(const uint8_t *__restrict__ bam, int64_t n_bytes, int64_t seg_bytes, int n_seg, const int64_t *__restrict__ hdr,
+               ScanSeg *__restrict__ segs)
+{
+    const int lane = threadIdx.x & 31;
+    const int s = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+    if (s >= n_seg || hdr[3] != 0) return;
+    const int64_t first = hdr[0];
+    const int32_t tid = (int32_t)hdr[1], n_ref = (int32_t)hdr[2];
+    const int64_t b = (int64_t)s * seg_bytes, e = min(b + seg_bytes, n_bytes);
+    ScanSeg g;
+    g.entry = -1; g.exit = -1; g.kept = g.ncig = g.nseq = g.nqual = 0;
+    if (e > first) {
+        if (b <= first) {                                        // the segment holding the true first record: no guess needed
+            if (bam_walk_segment(bam, n_bytes, first, e, n_ref, tid, g)) g.entry = first;
+        } else {
+            int tries = 0;
+            for (int64_t base = b; base < e && g.entry < 0 && tries < SCAN_TRIES; base += 32) {
+                const int64_t o = base + lane;
+                unsigned m = __ballot_sync(0xffffffffu, o < e && bam_record_plausible(bam, n_bytes, o, n_ref));
+                while (m && g.entry < 0 && tries < SCAN_TRIES) {
+                    const int k = __ffs(m) - 1;
+                    m &= m - 1;
+                    tries++;
+                    if (bam_walk_segment(bam, n_bytes, base + k, e, n_ref, tid, g)) g.entry = base + k;   // all lanes, same loads
+                }
+            }
+        }
+    }
+    if (lane == 0) segs[s] = g;
+}
+
+// proof + prefix sums.  link[0] = 1 when the serial kernel has to run.  counts as bam_scan_kernel writes them.
+__global__ void __launch_bounds__(1024)
+bam_link_kernel(int64_t n_bytes, int64_t seg_bytes, int n_seg, const int64_t *__restrict__ hdr, ScanSeg *__restrict__ segs,
+                int64_t max_records, int64_t *__restrict__ counts, int *__restrict__ link, int64_t *__restrict__ cigar_off,
+                int64_t *__restrict__ seq_off, int64_t *__restrict__ qual_off)
+{
+    __shared__ int64_t s_entry[SCAN_MAXSEG], s_exit[SCAN_MAXSEG];
+    __shared__ uint8_t s_on[SCAN_MAXSEG];
+    __shared__ int64_t s_w[32][4];
+    __shared__ int64_t s_carry[4];
+    __shared__ int s_ok;
+    const int tid_ = threadIdx.x, lane = tid_ & 31, warp = tid_ >> 5;
+    if (hdr[3] != 0) {                                           // header errors: reported here, nothing else runs
+        if (tid_ == 0) { for (int i = 0; i < 7; ++i) counts[i] = 0; counts[4] = -1; counts[6] = hdr[3]; link[0] = 0; }
+        return;
+    }
+    for (int i = tid_; i < n_seg; i += blockDim.x) { s_entry[i] = segs[i].entry; s_exit[i] = segs[i].exit; s_on[i] = 0; }
+    __syncthreads();
+    if (tid_ == 0) {
+        int64_t cur = hdr[0];
+        bool ok = true;
+        while (cur < n_bytes) {
+            const int s = (int)(cur / seg_bytes);
+            if (s >= n_seg || s_entry[s] != cur) { ok = false; break; }
+            s_on[s] = 1;
+            const int64_t nx = s_exit[s];                       // shared memory: the chase is a chain of dependent reads
+            if (nx <= cur) { ok = false; break; }
+            cur = nx;
+        }
+        if (cur != n_bytes) ok = false;                          // a truncated tail is the serial kernel's to report
+        s_ok = ok ? 1 : 0;
+        for (int k = 0; k < 4; k++) s_carry[k] = 0;
+    }
+    __syncthreads();
+    if (!s_ok) { if (tid_ == 0) link[0] = 1; return; }
+    // exclusive prefix sums of (records kept, CIGAR ops, sequence bytes, quality bytes) over the segments on the chain
+    for (int base = 0; base < n_seg; base += blockDim.x) {
+        const int i = base + tid_;
+        int64_t v[4] = {0, 0, 0, 0};
+        if (i < n_seg && s_on[i]) { v[0] = segs[i].kept; v[1] = segs[i].ncig; v[2] = segs[i].nseq; v[3] = segs[i].nqual; }
+        int64_t inc[4];
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            inc[k] = v[k];
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const int64_t t = __shfl_up_sync(0xffffffffu, inc[k], d);
+                if (lane >= d) inc[k] += t;
+            }
+            if (lane == 31) s_w[warp][k] = inc[k];
+        }
+        __syncthreads();
+        int64_t before[4];
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            before[k] = s_carry[k];
+            for (int w = 0; w < warp; w++) before[k] += s_w[w][k];
+        }
+        if (i < n_seg) {
+            ScanSeg g = segs[i];
+            g.kept = before[0] + inc[0] - v[0]; g.ncig = before[1] + inc[1] - v[1];
+            g.nseq = before[2] + inc[2] - v[2]; g.nqual = before[3] + inc[3] - v[3];
+            if (!s_on[i]) g.entry = -1;                          // a guess inside a record the chain jumps over: not a record
+            segs[i] = g;
+        }
+        __syncthreads();
+        if (tid_ == blockDim.x - 1) {
+#pragma unroll
+            for (int k = 0; k < 4; k++) s_carry[k] = before[k] + inc[k];
+        }
+        __syncthreads();
+    }
+    if (tid_ == 0) {
+        const int64_t kept = s_carry[0];
+        counts[0] = kept; counts[1] = s_carry[1]; counts[2] = s_carry[2]; counts[3] = s_carry[3];
+        counts[4] = hdr[1]; counts[5] = 0; counts[6] = 0;
+        if (kept <= max_records) { cigar_off[kept] = s_carry[1]; seq_off[kept] = s_carry[2]; qual_off[kept] = s_carry[3]; }
+        link[0] = 0;
+    }
+}
+
+// second walk of every segment on the chain: record offsets and running array offsets at their final places
+__global__ void __launch_bounds__(128)
+bam_emit_kernel(const uint8_t *__restrict__ bam, int64_t n_bytes, int64_t seg_bytes, int n_seg, const int64_t *__restrict__ hdr,
+                const ScanSeg *__restrict__ segs, const int *__restrict__ link, int64_t max_records, int64_t *__restrict__ rec_off,
+                int64_t *__restrict__ cigar_off, int64_t *__restrict__ seq_off, int64_t *__restrict__ qual_off,
+                int64_t *__restrict__ counts)
+{
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n_seg || hdr[3] != 0 || link[0] != 0) return;
+    const ScanSeg g = segs[s];
+    if (g.entry < 0) return;
+    const int32_t tid = (int32_t)hdr[1];
+    const int64_t e = min((int64_t)(s + 1) * seg_bytes, n_bytes);
+    int64_t o = g.entry, k = g.kept, ncig = g.ncig, nseq = g.nseq, nqual = g.nqual, seen = 0;
+    while (o < e && o < n_bytes) {
+        ++seen;
+        if (tid < 0 || ld_i32(bam + o + 4) == tid) {
+            const int32_t n_cig = (int32_t)bam[o + 16] | ((int32_t)bam[o + 17] << 8);
+            const int32_t l_seq = ld_i32(bam + o + 20);
+            if (k < max_records) { rec_off[k] = o; cigar_off[k] = ncig; seq_off[k] = nseq; qual_off[k] = nqual; }
+            ++k; ncig += n_cig; nseq += (l_seq + 1) >> 1; nqual += l_seq;
+        }
+        o += 4 + (int64_t)ld_i32(bam + o);
+    }
+    atomicAdd(reinterpret_cast<unsigned long long *>(counts + 5), (unsigned long long)seen);
 }
 
 __global__ void __launch_bounds__(256)
@@ -219,9 +443,34 @@ int dp_bam_scan(const uint8_t *bam, int64_t n_bytes, const char *contig, int32_t
         dp::set_error("dp_bam_scan: null argument");
         return DP_EINVAL;
     }
-    bam_scan_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(bam, n_bytes, contig, contig_len, max_records, rec_off, cigar_off,
-                                                        seq_off, qual_off, counts);
-    DP_CUDA_CHECK(cudaGetLastError());
+    cudaStream_t st = (cudaStream_t)stream;
+    const char *e = getenv("DP_BAM_SCAN");                       // "serial": the one-thread chain walk only
+    if (e && !strcmp(e, "serial")) {
+        bam_scan_kernel<<<1, 32, 0, st>>>(bam, n_bytes, contig, contig_len, max_records, rec_off, cigar_off, seq_off, qual_off,
+                                          counts, nullptr);
+        DP_CUDA_CHECK(cudaGetLastError());
+        return DP_OK;
+    }
+    // segments of >= 64 KB, at most SCAN_MAXSEG of them (the link kernel keeps their entries in shared memory)
+    int64_t seg_bytes = 65536;
+    while ((n_bytes + seg_bytes - 1) / seg_bytes > SCAN_MAXSEG) seg_bytes *= 2;
+    const int n_seg = (int)((n_bytes + seg_bytes - 1) / seg_bytes) > 0 ? (int)((n_bytes + seg_bytes - 1) / seg_bytes) : 1;
+    uint8_t *scratch = nullptr;
+    const size_t bytes = 64 + 16 + sizeof(ScanSeg) * (size_t)n_seg;
+    DP_CUDA_CHECK(cudaMallocAsync((void **)&scratch, bytes, st));
+    int64_t *hdr = (int64_t *)scratch;
+    int *link = (int *)(scratch + 64);
+    ScanSeg *segs = (ScanSeg *)(scratch + 80);
+    bam_header_kernel<<<1, 32, 0, st>>>(bam, n_bytes, contig, contig_len, hdr);
+    bam_seg_kernel<<<(n_seg + 3) / 4, 128, 0, st>>>(bam, n_bytes, seg_bytes, n_seg, hdr, segs);
+    bam_link_kernel<<<1, 1024, 0, st>>>(n_bytes, seg_bytes, n_seg, hdr, segs, max_records, counts, link, cigar_off, seq_off, qual_off);
+    bam_emit_kernel<<<(n_seg + 127) / 128, 128, 0, st>>>(bam, n_bytes, seg_bytes, n_seg, hdr, segs, link, max_records, rec_off,
+                                                         cigar_off, seq_off, qual_off, counts);
+    bam_scan_kernel<<<1, 32, 0, st>>>(bam, n_bytes, contig, contig_len, max_records, rec_off, cigar_off, seq_off, qual_off, counts,
+                                      link);                     // runs only when a link of the proof failed
+    cudaError_t le = cudaGetLastError();
+    cudaFreeAsync(scratch, st);
+    if (le != cudaSuccess) { dp::set_error("dp_bam_scan: %s", cudaGetErrorString(le)); return DP_ECUDA; }
     return DP_OK;
 }
 

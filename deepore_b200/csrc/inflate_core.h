@@ -50,9 +50,10 @@
  * is longer than DPI_FAST_BITS (decoded by the count/first-code walk instead) */
 #define DPI_FAST_BITS 9
 #define DPI_FAST_SIZE (1 << DPI_FAST_BITS)
-/* scratch per decoder, in uint16 units: counts + symbols of both codes, the code-length list, the lookup table */
+/* scratch per decoder, in uint16 units: counts + symbols of both codes, the code-length list, the two lookup tables
+ * (literal/length and distance) */
 #define DPI_SLOW_U16 (16 + DPI_NLEN + 16 + DPI_NDIST + (DPI_NLEN + DPI_NDIST + 2) / 2 + 1)
-#define DPI_SCRATCH_U16 (DPI_SLOW_U16 + DPI_FAST_SIZE)
+#define DPI_SCRATCH_U16 (DPI_SLOW_U16 + 2 * DPI_FAST_SIZE)
 
 DPI_CONST uint16_t dpi_len_base[29] = {3, 4, 5, 6, 7, 8, 9, 10, 11, 13, 15, 17, 19, 23, 27, 31, 35, 43, 51, 59, 67, 83,
                                        99, 115, 131, 163, 195, 227, 258};
@@ -73,16 +74,34 @@ typedef struct dpi_stream {
     int32_t err;
 } dpi_stream;
 
+/* Top the reservoir up: one aligned 32-bit load where the input pointer allows it (every refill after the first few bytes
+ * of a stream; a byte load per 8 bits was a dependent load per output byte), single bytes at unaligned positions and at
+ * the tail.  Never reads outside [in, in + in_len). */
+DPI_FN void dpi_refill(dpi_stream *s)
+{
+    if (s->bitcnt > 32) return;
+    if (s->in_pos + 4 <= s->in_len && ((uintptr_t)(s->in + s->in_pos) & 3u) == 0) {
+        const uint32_t w = *(const uint32_t *)(s->in + s->in_pos);           /* little-endian hosts and devices */
+        s->bitbuf |= (uint64_t)w << s->bitcnt;
+        s->bitcnt += 32;
+        s->in_pos += 4;
+        return;
+    }
+    while (s->bitcnt <= 56 && s->in_pos < s->in_len && (s->bitcnt <= 24 || ((uintptr_t)(s->in + s->in_pos) & 3u) != 0)) {
+        s->bitbuf |= (uint64_t)s->in[s->in_pos++] << s->bitcnt;
+        s->bitcnt += 8;
+    }
+}
+
 /* Take `need` (<= 16) bits; past the end of the input the stream goes into error and zeros are returned. */
 DPI_FN uint32_t dpi_bits(dpi_stream *s, int need)
 {
-    while (s->bitcnt < need) {
-        if (s->in_pos >= s->in_len) {
+    if (s->bitcnt < need) {
+        dpi_refill(s);
+        if (s->bitcnt < need) {
             s->err = DPI_E_INPUT;
             return 0;
         }
-        s->bitbuf |= (uint64_t)s->in[s->in_pos++] << s->bitcnt;
-        s->bitcnt += 8;
     }
     uint32_t v = (uint32_t)(s->bitbuf & ((1u << need) - 1u));
     s->bitbuf >>= need;
@@ -164,13 +183,10 @@ DPI_FN void dpi_build_fast(uint16_t *fast, const uint16_t *count, const uint8_t 
     DPI_SYNC();
 }
 
-/* Literal/length symbol: one table lookup when enough input is buffered and the code is short, else the walk. */
+/* Literal/length or distance symbol: one table lookup when enough input is buffered and the code is short, else the walk. */
 DPI_FN int dpi_decode_len(dpi_stream *s, const uint16_t *fast, const uint16_t *count, const uint16_t *symbol)
 {
-    while (s->bitcnt < DPI_FAST_BITS && s->in_pos < s->in_len) {
-        s->bitbuf |= (uint64_t)s->in[s->in_pos++] << s->bitcnt;
-        s->bitcnt += 8;
-    }
+    if (s->bitcnt < DPI_FAST_BITS) dpi_refill(s);
     if (s->bitcnt >= DPI_FAST_BITS) {
         const uint16_t e = fast[(uint32_t)s->bitbuf & (DPI_FAST_SIZE - 1)];
         if (e) {
@@ -184,23 +200,37 @@ DPI_FN int dpi_decode_len(dpi_stream *s, const uint16_t *fast, const uint16_t *c
 }
 
 /* Literal/length + distance loop shared by fixed and dynamic blocks. */
-DPI_FN int dpi_codes(dpi_stream *s, const uint16_t *fast, const uint16_t *lcnt, const uint16_t *lsym, const uint16_t *dcnt,
-                     const uint16_t *dsym)
+/* A run of literals is kept in registers -- lane i holds the i-th literal of the run -- and written with ONE store
+ * instruction per DPI_LANES literals (a 32-byte sector per warp instruction instead of 32 single-byte stores by lane 0). */
+#define DPI_FLUSH_LITERALS()                                                        \
+    do {                                                                            \
+        if (DPI_LANE < run) s->out[s->out_pos - run + DPI_LANE] = mylit;            \
+        run = 0;                                                                    \
+    } while (0)
+
+DPI_FN int dpi_codes(dpi_stream *s, const uint16_t *fast, const uint16_t *dfast, const uint16_t *lcnt, const uint16_t *lsym,
+                     const uint16_t *dcnt, const uint16_t *dsym)
 {
+    uint32_t run = 0;                                            /* literals decoded but not yet stored */
+    uint8_t mylit = 0;
     for (;;) {
         int sym = dpi_decode_len(s, fast, lcnt, lsym);
-        if (sym < 0) return sym;
+        if (sym < 0) { DPI_FLUSH_LITERALS(); return sym; }
         if (sym < 256) {
-            if (s->out_pos >= s->out_cap) return DPI_E_OUTPUT;
-            if (DPI_LANE == 0) s->out[s->out_pos] = (uint8_t)sym;
+            if (s->out_pos >= s->out_cap) { DPI_FLUSH_LITERALS(); return DPI_E_OUTPUT; }
+            if (DPI_LANE == run) mylit = (uint8_t)sym;
+            run++;
             s->out_pos++;
+            if (run == DPI_LANES) DPI_FLUSH_LITERALS();
         } else if (sym == 256) {
+            DPI_FLUSH_LITERALS();
             return DPI_OK;
         } else {
+            DPI_FLUSH_LITERALS();
             sym -= 257;
             if (sym >= 29) return DPI_E_SYMBOL;
             uint32_t len = dpi_len_base[sym] + dpi_bits(s, dpi_len_extra[sym]);
-            int ds = dpi_decode(s, dcnt, dsym);
+            int ds = dpi_decode_len(s, dfast, dcnt, dsym);
             if (ds < 0) return ds;
             if (ds >= DPI_NDIST) return DPI_E_SYMBOL;
             uint32_t dist = dpi_dist_base[ds] + dpi_bits(s, dpi_dist_extra[ds]);
@@ -230,7 +260,7 @@ DPI_FN int dpi_inflate(const uint8_t *in, uint32_t in_len, uint8_t *out, uint32_
     st.out = out; st.out_cap = out_cap; st.out_pos = 0; st.err = 0;
     uint16_t *lcnt = scratch, *lsym = lcnt + 16, *dcnt = lsym + DPI_NLEN, *dsym = dcnt + 16;
     uint8_t *lengths = (uint8_t *)(dsym + DPI_NDIST);
-    uint16_t *fast = scratch + DPI_SLOW_U16;
+    uint16_t *fast = scratch + DPI_SLOW_U16, *dfast = fast + DPI_FAST_SIZE;
     int last, rc = DPI_OK;
     do {
         last = (int)dpi_bits(&st, 1);
@@ -258,7 +288,8 @@ DPI_FN int dpi_inflate(const uint8_t *in, uint32_t in_len, uint8_t *out, uint32_
             dpi_build_fast(fast, lcnt, lengths, DPI_NLEN);
             for (i = 0; i < DPI_NDIST; ++i) lengths[i] = 5;
             dpi_build(dcnt, dsym, lengths, DPI_NDIST);
-            rc = dpi_codes(&st, fast, lcnt, lsym, dcnt, dsym);
+            dpi_build_fast(dfast, dcnt, lengths, DPI_NDIST);
+            rc = dpi_codes(&st, fast, dfast, lcnt, lsym, dcnt, dsym);
         } else if (type == 2) {
             int nlen = (int)dpi_bits(&st, 5) + 257, ndist = (int)dpi_bits(&st, 5) + 1, ncode = (int)dpi_bits(&st, 4) + 4;
             if (st.err) { rc = st.err; break; }
@@ -296,10 +327,11 @@ DPI_FN int dpi_inflate(const uint8_t *in, uint32_t in_len, uint8_t *out, uint32_
              * position that dpi_build of the literal code does not touch (lengths[] is separate from both tables) */
             int e = dpi_build(dcnt, dsym, lengths + nlen, ndist);
             if (e < 0 || (e > 0 && ndist - dcnt[0] != 1)) { rc = DPI_E_TABLE; break; }
+            dpi_build_fast(dfast, dcnt, lengths + nlen, ndist);
             e = dpi_build(lcnt, lsym, lengths, nlen);
             if (e < 0 || (e > 0 && nlen - lcnt[0] != 1)) { rc = DPI_E_TABLE; break; }
             dpi_build_fast(fast, lcnt, lengths, nlen);
-            rc = dpi_codes(&st, fast, lcnt, lsym, dcnt, dsym);
+            rc = dpi_codes(&st, fast, dfast, lcnt, lsym, dcnt, dsym);
         } else {
             rc = DPI_E_BTYPE;
         }

@@ -313,16 +313,29 @@ __global__ void __launch_bounds__(256) prep_reads_kernel(dp_reads R, ReadAux *__
 // A base outside {A,C,G,T,N} (KeyError in the reference) clears the read's clean flag.
 __global__ void __launch_bounds__(256) base_codes_kernel(dp_reads R, ReadInfo *__restrict__ info,
                                                          uint8_t *__restrict__ code0) {
-    constexpr int BK = 16;                            // consecutive bases per thread: one read lookup, one 16-byte store
+    constexpr int BK = 16;                            // consecutive bases per thread: one 16-byte quality load, one 16-byte store
     const int64_t n = R.n_bases;
+    const int lane = threadIdx.x & 31;
     const int64_t stride = (int64_t)gridDim.x * blockDim.x * BK;
-    for (int64_t k0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * BK; k0 < n; k0 += stride) {
-        int lo = 0, hi = R.n_reads;                   // read r with qual_off[r] <= k0 < qual_off[r+1]
+    // the loop bound is warp-uniform (first base of the warp), so the warp-wide search below always has all 32 lanes
+    for (int64_t kw = ((int64_t)blockIdx.x * blockDim.x + (threadIdx.x & ~31)) * BK; kw < n; kw += stride) {
+        const int64_t k0 = kw + lane * BK;
+        // read holding the warp's first base (qual_off[r] <= kw < qual_off[r+1]) by a 33-ary search: every lane probes one
+        // pivot per round -- 3 rounds for 32 k reads instead of 15 dependent loads per thread
+        int lo = 0, hi = R.n_reads;
         while (hi - lo > 1) {
-            const int mid = (lo + hi) >> 1;
-            if (__ldg(R.qual_off + mid) <= k0) lo = mid; else hi = mid;
+            const int span = hi - lo;
+            const int piv = lo + (int)(((int64_t)span * (lane + 1)) / 33);
+            const bool le = piv <= lo || __ldg(R.qual_off + piv) <= kw;       // qual_off[lo] <= kw by the invariant; piv < hi
+            const unsigned m = __ballot_sync(0xffffffffu, le);               // monotone: a prefix of the lanes
+            const int nle = __popc(m);
+            const int nlo = nle ? lo + (int)(((int64_t)span * nle) / 33) : lo;
+            const int nhi = nle < 32 ? lo + (int)(((int64_t)span * (nle + 1)) / 33) : hi;
+            lo = nlo; hi = max(nhi, nlo + 1);
         }
+        if (k0 >= n) continue;
         int r = lo;
+        while (r + 1 < R.n_reads && k0 >= __ldg(R.qual_off + r + 1)) r++;     // this lane's first read (reads shorter than 512 bases)
         int64_t ro = 0, next = 0;
         int l_seq = 0, aln_start = 0, mq28 = 0;
         const uint8_t *seqp = nullptr;
@@ -335,7 +348,18 @@ __global__ void __launch_bounds__(256) base_codes_kernel(dp_reads R, ReadInfo *_
             illegal = false;
         };
         load_read();
+        uint32_t qw[BK / 4];
+        if (k0 + BK <= n) {
+            const uint4 q4 = __ldg(reinterpret_cast<const uint4 *>(R.qual + k0));
+            qw[0] = q4.x; qw[1] = q4.y; qw[2] = q4.z; qw[3] = q4.w;
+        } else {
+#pragma unroll
+            for (int t = 0; t < BK / 4; t++) qw[t] = 0;
+            for (int t = 0; k0 + t < n; t++) qw[t >> 2] |= (uint32_t)__ldg(R.qual + k0 + t) << ((t & 3) << 3);
+        }
         uint32_t out[BK / 4] = {0, 0, 0, 0};
+        int last_byte_i = -1, last_byte2_i = -1;
+        uint32_t last_byte = 0, last_byte2 = 0;
 #pragma unroll
         for (int t = 0; t < BK; t++) {
             const int64_t k = k0 + t;
@@ -344,19 +368,24 @@ __global__ void __launch_bounds__(256) base_codes_kernel(dp_reads R, ReadInfo *_
                 if (illegal) atomicAnd(&info[r].flags, ~RI_CLEAN);
                 r++;
                 load_read();
+                last_byte_i = last_byte2_i = -1;
             }
             const int idx = (int)(k - ro);
-            const uint8_t b = __ldg(seqp + (idx >> 1));
-            const int nib = (idx & 1) ? (b & 15) : (b >> 4);
+            if ((idx >> 1) != last_byte_i) { last_byte_i = idx >> 1; last_byte = __ldg(seqp + last_byte_i); }
+            const int nib = (idx & 1) ? (last_byte & 15) : (last_byte >> 4);
             if (!((0x8116u >> nib) & 1u)) illegal = true;
             const int kb = idx + aln_start;
             int cat = 0;
             if (kb < l_seq) {
-                const uint8_t b2 = __ldg(seqp + (kb >> 1));
-                const int nib2 = (kb & 1) ? (b2 & 15) : (b2 >> 4);
+                int nib2 = nib;
+                if (aln_start != 0) {
+                    if ((kb >> 1) != last_byte2_i) { last_byte2_i = kb >> 1; last_byte2 = __ldg(seqp + last_byte2_i); }
+                    nib2 = (kb & 1) ? (last_byte2 & 15) : (last_byte2 >> 4);
+                }
                 cat = nib2 == 15 ? CAT_N : ((__ffs(nib2) - 1) & 3);
             }
-            const uint32_t code = (uint32_t)((cat << 5) | min((int)__ldg(R.qual + k), mq28));
+            const int q = (int)((qw[t >> 2] >> ((t & 3) << 3)) & 0xffu);
+            const uint32_t code = (uint32_t)((cat << 5) | min(q, mq28));
             out[t >> 2] |= code << ((t & 3) << 3);
         }
         if (illegal) atomicAnd(&info[r].flags, ~RI_CLEAN);
@@ -1469,6 +1498,380 @@ encode_windows_v3_kernel(EncArgs a, int *__restrict__ fb_count, int *__restrict_
 #undef V3_MARK
 }
 
+// ================================================================================================
+// v4 fast path: ONE WARP PER WINDOW, column sweep.  (v3 above spends ~38 k warp instructions and a dozen CTA barriers on
+// a window whose real content is ~2 300 entries: the passes over shared-memory planes, not the data, set its pace.)
+// Here lane = read (NR rounds of 32 reads); all lanes walk the window's columns left to right in lock step, each with
+// the state of its read's CIGAR (current M/D op, the op after it, query index) in registers.  At a column every lane
+// knows its own entries -- soft-clip step, step 0 of an op that starts here, step >= 1 of the op in progress
+// (parseRead's closed form, header of this file) -- and a packed warp prefix sum over the 7 categories turns them into
+// row positions: base[category] + entries of that category in earlier reads (+ earlier steps of the same read), i.e.
+// sortingKey order, then read order, then step order (Pileup.py:66-73, 268-292) with no sort, no atomics and no barrier
+// wider than a warp.  The row is assembled as code bytes in a 256-byte shared-memory line, turned into RGBA through the
+// code table and stored with 16-byte stores; the all-filler tail of the row leaves the SM as one bulk copy from a
+// constant row.  Insert rows of an anchor column follow immediately (Pileup.py:305-317), and the sweep stops when the
+// image is full (150 rows: ~70 of the 201 columns at 30x with 3 % insertions) -- the row map needs no pass of its own.
+// Windows outside the envelope (a non-clean read, more than 32 * NR reads, an illegal reference character) go to the
+// list of the exact kernel, as in v3.
+constexpr int V4_WARPS = 8;                    // windows per CTA
+constexpr int V4_ROWB = 256;                   // bytes of a row-code line (W <= 256)
+
+struct V4Read {                                // per (lane, round) walk state
+    const uint32_t *cig;                       // next op word to fetch
+    const uint8_t *codep;                      // code bytes of the read (code0 + qual_off)
+    uint32_t wnext;                            // the op after the current one (prefetched); valid while nleft > 0
+    int nleft;                                 // ops not yet started (wnext is the first of them)
+    int cs, ce;                                // current M/D op covers columns [cs, ce); next op starts at column ce
+    int cq;                                    // query index before the current op (parseRead's lagging readPos)
+    int qnext;                                 // query index before the next op
+    int flags;                                 // bit 0: current op is D; bit 1: shift; bit 2: read present
+    int aln_len, l_seq;
+};
+
+__device__ __forceinline__ uint64_t v4_scan_packed(uint64_t v, int lane) {      // inclusive warp prefix sum, 7 x 8-bit fields
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const uint64_t t = __shfl_up_sync(0xffffffffu, v, d);
+        if (lane >= d) v += t;
+    }
+    return v;
+}
+__device__ __forceinline__ int v4_field(uint64_t v, int cat) { return (int)((v >> (cat << 3)) & 0xffu); }
+// per-byte saturating add of packed counters (fields stay <= 255: anything >= W - 1 is off the image anyway)
+__device__ __forceinline__ uint64_t v4_addsat(uint64_t a, uint64_t b) {
+    const uint32_t lo = __vaddus4((uint32_t)a, (uint32_t)b), hi = __vaddus4((uint32_t)(a >> 32), (uint32_t)(b >> 32));
+    return ((uint64_t)hi << 32) | lo;
+}
+
+template <int NR>
+__global__ void __launch_bounds__(V4_WARPS * 32)
+encode_windows_v4_kernel(EncArgs a, int n_windows, int *__restrict__ fb_count, int *__restrict__ fb_list) {
+    __shared__ uint32_t s_lut[256];                          // code -> RGBA
+    __shared__ __align__(16) uint32_t s_fill[2][256];        // constant filler rows: (0,0,0,255) / insert colour
+    __shared__ __align__(16) uint8_t s_row[V4_WARPS][2][V4_ROWB];
+    __shared__ uint8_t s_refc[V4_WARPS][224];
+    __shared__ int s_cand[V4_WARPS][NR * 32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int L = a.L, W = a.W, H = a.H;
+    {
+        const uint32_t rgb[8] = {0x000000FFu, 0x0000FFFFu, 0x0000FF00u, 0x00FF0000u, 0x00FFFF00u, 0x00FFFFFFu, 0x00000000u, 0x00FF00FFu};
+        uint32_t col = 0;
+#pragma unroll
+        for (int k = 0; k < 8; k++) if ((tid >> 5) == k) col = rgb[k];
+        const int qi = tid & 31;
+        s_lut[tid] = col | ((uint32_t)(qi <= V3_QMAX ? c_qlut[qi] : 255) << 24);
+        s_fill[0][tid] = 0xFF000000u; s_fill[1][tid] = 0xFFFF00FFu;
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    __syncthreads();
+    const int w = blockIdx.x * V4_WARPS + warp;
+    if (w >= n_windows) return;                              // warp-uniform; no CTA barrier below
+    const unsigned lt = (1u << lane) - 1u;
+    const int qs = a.win_qs[w], qe = qs + L;
+    const int lo = a.win_lo[w], hi = a.win_hi[w];
+    uint8_t *refc = s_refc[warp];
+    int *cand = s_cand[warp];
+    bool bad = false;
+    // ---- reference categories of the window (Pileup.py:41: L + 1 characters)
+    const long long roff = (long long)qs - a.ref_base;
+    const bool ref_ok = roff >= 0 && roff + L + 1 <= a.ref_len;
+    if (!ref_ok) bad = true;
+    for (int i = lane; i < L + 1; i += 32) {
+        const int ch = ref_ok ? a.ref[roff + i] : 'N';
+        int code = 7;
+        switch (ch) { case 'A': code = CAT_A; break; case 'C': code = CAT_C; break; case 'G': code = CAT_G; break;
+                      case 'T': code = CAT_T; break; case 'N': code = CAT_N; break; default: break; }
+        if (code == 7) bad = true;                           // KeyError at Pileup.py:281 if it becomes a reference pixel
+        refc[i] = (uint8_t)code;
+    }
+    // ---- ordered compaction of the reads pysam.fetch returns and parseRead keeps
+    int ncand = 0;
+    for (int cb = lo; cb < hi; cb += 32) {
+        const int r = cb + lane;
+        const bool keep = r < hi && a.R.pos[r] < qe && a.endk[r] > qs;
+        const unsigned bal = __ballot_sync(0xffffffffu, keep);
+        const int idx = ncand + __popc(bal & lt);
+        if (keep && idx < NR * 32) cand[idx] = r;
+        ncand += __popc(bal);
+    }
+    if (ncand > NR * 32) bad = true;
+    __syncwarp();
+    // ---- per read: digest, entry op (checkpoint + short walk), walk state
+    V4Read rd[NR];
+#pragma unroll
+    for (int r_ = 0; r_ < NR; r_++) {
+        V4Read &R = rd[r_];
+        R.flags = 0; R.nleft = 0; R.cs = INT_MAX / 2; R.ce = INT_MAX; R.cq = 0; R.qnext = 0; R.wnext = 0;
+        R.cig = nullptr; R.codep = nullptr; R.aln_len = 0; R.l_seq = 0;
+        const int ci = r_ * 32 + lane;
+        if (!bad && ci < ncand) {
+            const int r = cand[ci];
+            const ReadInfo *ri = a.info + r;
+            const int flags = ri->flags;
+            if (!(flags & RI_CLEAN)) { bad = true; continue; }
+            const int ref_start = ri->ref_start, nops = ri->nops;
+            const long long c0 = ri->c0;
+            R.codep = a.code0 + ri->qual_off;
+            R.aln_len = ri->aln_len; R.l_seq = ri->l_seq;
+            const int T = qs - ref_start;
+            int j = 0;
+            if (T > 0) j = __ldg(a.ckpt + (c0 >> 1) + r + (min(T, ri->span) >> ((flags >> 8) & 31)));
+            // first op that is not wholly left of the window: sA + (M/D ? n : 0) >= 0
+            int sA = 0, n = 0, op = 0;
+            uint32_t wd = 0;
+            for (; j < nops; j++) {
+                wd = __ldg(a.R.cigar + c0 + j);
+                op = wd & 15; n = (int)(wd >> 4);
+                sA = ref_start + __ldg(a.RP + c0 + r + j) - qs;
+                if (sA + ((op == 0 || op == 2) ? n : 0) >= 0) break;
+            }
+            if (j >= nops) continue;                         // nothing of this read reaches the window (flags stay 0)
+            const int qp = __ldg(a.QP + c0 + j) - 1;
+            R.flags = 4;
+            if ((op == 0 || op == 2) && sA < 0) {            // an M/D op in progress at the window's left edge
+                R.cs = sA; R.ce = sA + n; R.cq = qp;
+                R.flags |= (op == 2) ? 1 : 0;
+                R.qnext = qp + (op == 0 ? n : 0);
+                R.nleft = nops - j - 1;
+                R.cig = a.R.cigar + c0 + j + 1;
+            } else {                                         // the op starts inside the window: it is the "next" one
+                R.ce = sA; R.qnext = qp;
+                R.nleft = nops - j;
+                R.cig = a.R.cigar + c0 + j;
+            }
+            if (R.nleft > 0) { R.wnext = __ldg(R.cig); R.cig++; }
+        }
+    }
+    bad = __any_sync(0xffffffffu, bad);
+    if (bad) {
+        if (lane == 0) {
+            const int k = atomicAdd(fb_count, 1);
+            fb_list[k] = w;
+            if (a.out_status) a.out_status[w] = 0;
+        }
+        return;                                              // the exact kernel recomputes this window
+    }
+    uint8_t *img = a.out_img + (size_t)w * H * W * 4;
+    int32_t *rowpos = a.out_rowpos ? a.out_rowpos + (size_t)w * H : nullptr;
+    int32_t *rowins = a.out_rowins ? a.out_rowins + (size_t)w * H : nullptr;
+    const int Wm1 = W - 1;
+    int y = 0, ord = 0, rb = 0;
+
+    // emits image row y from the code line `line` holding pixel 0 + `tot` entries (tot <= W - 1)
+    auto emit_row = [&](const uint8_t *line, int tot, bool ins) {
+        __syncwarp();
+        const int nq = (tot + 4) >> 2;                       // quads holding pixel 0 .. tot
+        const uint8_t fillc = ins ? V3_FILL_INS : V3_FILL_NONE;
+        uint8_t *orow = img + ((size_t)y * W << 2);
+        for (int q0 = 0; q0 < nq; q0 += 32) {
+            const int q = q0 + lane;
+            if (q < nq) {
+                uint32_t codes = *reinterpret_cast<const uint32_t *>(line + (q << 2));
+                const int over = (q << 2) + 3 - tot;         // bytes of this quad beyond the last entry
+                if (over > 0) {
+                    const uint32_t keep = 0xFFFFFFFFu >> (over << 3);
+                    codes = (codes & keep) | ((fillc * 0x01010101u) & ~keep);
+                }
+                const uint32_t p0 = s_lut[codes & 0xffu], p1 = s_lut[(codes >> 8) & 0xffu];
+                const uint32_t p2 = s_lut[(codes >> 16) & 0xffu], p3 = s_lut[codes >> 24];
+                *reinterpret_cast<uint4 *>(orow + (q << 4)) = make_uint4(p0, p1, p2, p3);
+            }
+        }
+        if (lane == 0) {
+            const int bytes = (W - (nq << 2)) << 2;
+            if (bytes > 0) {
+                const uint32_t src = (uint32_t)__cvta_generic_to_shared(&s_fill[ins ? 1 : 0][0]);
+                asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
+                             :: "l"(orow + (nq << 4)), "r"(src), "r"(bytes) : "memory");
+                asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+            }
+        }
+    };
+
+    for (int c = 0; c < L && y < H; c++) {
+        // ---- every read's entries at column c
+        uint32_t eS[NR], e0[NR], e1[NR];                     // soft-clip step, step 0, step >= 1 (V3_NONE: none)
+        int insn[NR], insq[NR];                              // insertion anchored here: length, first query index
+        uint64_t mine[NR];                                   // packed per-category counts of this lane's entries
+        uint64_t total = 0;
+        int anyins = 0;
+#pragma unroll
+        for (int r_ = 0; r_ < NR; r_++) {
+            V4Read &R = rd[r_];
+            eS[r_] = e0[r_] = e1[r_] = V3_NONE; insn[r_] = 0; insq[r_] = 0; mine[r_] = 0;
+            if (R.flags & 4) {
+                if (c == R.ce) {
+                    // ops that start at this column, in CIGAR order: [S] [I] then an M/D op, or a trailing S
+                    bool started = false;
+#pragma unroll 1
+                    while (R.nleft > 0 && !started) {
+                        const uint32_t wd = R.wnext;
+                        const int op = wd & 15, n = (int)(wd >> 4);
+                        const int qp = R.qnext;
+                        R.nleft--;
+                        if (R.nleft > 0) { R.wnext = __ldg(R.cig); R.cig++; }
+                        if (op == 1) {                       // insertion anchored at c (Pileup.py:220-230: needs A > queryStart)
+                            if (c >= 1) { insn[r_] = n; insq[r_] = qp + 1; }
+                            R.qnext = qp + n;
+                            continue;
+                        }
+                        // an M/D op starts exactly at queryStart (a leading soft clip at column 0 is followed by one): the
+                        // read's reference characters are shifted by one for the rest of the window
+                        if (c == 0 && (op == 0 || op == 2 || (op == 4 && R.nleft > 0))) R.flags |= 2;
+                        // step 0 of an M/D op / the single step of a soft clip: previous query base (index -1 wraps like
+                        // Python), reference character one to the left (+ shift)
+                        const int rel = c - 1 + ((R.flags >> 1) & 1);
+                        if (rel < 0) { bad = true; break; }
+                        int cb;
+                        if (qp >= 0) cb = __ldg(R.codep + qp);
+                        else cb = (__ldg(R.codep + R.aln_len - 1) & 0xE0) | (__ldg(R.codep + R.l_seq - 1) & 31);
+                        int cat = cb >> 5;
+                        if (op == 2) cat = CAT_D; else if (cat == refc[rel]) cat = CAT_M;
+                        const uint32_t code = (uint32_t)((cat << 5) | (cb & 31));
+                        if (op == 4) { eS[r_] = code; continue; }              // S advances nothing; a following M starts here too
+                        e0[r_] = code;
+                        R.cs = c; R.ce = c + n; R.cq = qp;
+                        R.flags = (R.flags & ~1) | (op == 2 ? 1 : 0);
+                        R.qnext = qp + (op == 0 ? n : 0);
+                        started = true;
+                    }
+                    if (!started) R.ce = INT_MAX;            // no further M/D op: the read ends here
+                }
+                if (c >= R.cs && c < R.ce - 1 && R.ce != INT_MAX) {            // step >= 1 of the op in progress
+                    const bool isD = R.flags & 1;
+                    const int cb = __ldg(R.codep + (isD ? R.cq : R.cq + 1 + (c - R.cs)));
+                    int cat = cb >> 5;
+                    if (isD) cat = CAT_D; else if (cat == refc[c + ((R.flags >> 1) & 1)]) cat = CAT_M;
+                    e1[r_] = (uint32_t)((cat << 5) | (cb & 31));
+                }
+                uint64_t m = 0;
+                if (eS[r_] != V3_NONE) m += 1ull << ((eS[r_] >> 5) << 3);
+                if (e0[r_] != V3_NONE) m += 1ull << ((e0[r_] >> 5) << 3);
+                if (e1[r_] != V3_NONE) m += 1ull << ((e1[r_] >> 5) << 3);
+                mine[r_] = m;
+            }
+            anyins |= insn[r_];
+        }
+        if (__any_sync(0xffffffffu, bad)) break;
+        // ---- ranks: inclusive packed scan per round, rounds chained by the (saturating) totals
+        uint64_t incl[NR], before[NR];
+#pragma unroll
+        for (int r_ = 0; r_ < NR; r_++) {
+            incl[r_] = v4_scan_packed(mine[r_], lane);
+            before[r_] = total;
+            total = v4_addsat(total, __shfl_sync(0xffffffffu, incl[r_], 31));
+        }
+        int tot = 0;
+        uint64_t base = 0;                                   // first position of each category
+#pragma unroll
+        for (int k = 0; k < NCAT; k++) {
+            base |= (uint64_t)min(tot, 255) << (k << 3);
+            tot += v4_field(total, k);
+        }
+        const bool haveins = __any_sync(0xffffffffu, anyins != 0);
+        if (tot == 0) continue;                              // unpopulated column: it vanishes, its insertions with it
+        // ---- anchor row
+        uint8_t *line = s_row[warp][rb];
+        rb ^= 1;
+#pragma unroll
+        for (int r_ = 0; r_ < NR; r_++) {
+            if (mine[r_] == 0) continue;
+            const uint64_t ex = v4_addsat(before[r_], incl[r_] - mine[r_]);     // same-category entries of earlier reads
+            int extra[NCAT];
+#pragma unroll
+            for (int k = 0; k < NCAT; k++) extra[k] = 0;
+            const uint32_t es[3] = {eS[r_], e0[r_], e1[r_]};
+#pragma unroll
+            for (int t = 0; t < 3; t++) {
+                if (es[t] == V3_NONE) continue;
+                const int cat = es[t] >> 5;
+                int own = 0;
+#pragma unroll
+                for (int k = 0; k < NCAT; k++) if (k == cat) { own = extra[k]; extra[k]++; }
+                const int pos = v4_field(base, cat) + v4_field(ex, cat) + own;
+                if (pos < Wm1) line[1 + pos] = (uint8_t)es[t];
+            }
+        }
+        if (lane == 0) {
+            line[0] = (uint8_t)((refc[ord] << 5) | 29);
+            if (rowpos) rowpos[y] = qs + c;
+            if (rowins) rowins[y] = 0;
+        }
+        emit_row(line, min(tot, Wm1), false);
+        y++; ord++;
+        // ---- insert rows of this anchor (Pileup.py:305-317): row k holds base k of every insertion longer than k,
+        // categories A,C,G,T,N, read order inside a category; reference pixel and filler in the insert colour
+        if (haveins) {
+            int mx = 0;
+#pragma unroll
+            for (int r_ = 0; r_ < NR; r_++) mx = max(mx, insn[r_]);
+            mx = __reduce_max_sync(0xffffffffu, mx);
+            for (int k = 0; k < mx && y < H; k++) {
+                uint32_t ec[NR];
+                uint64_t im[NR], iincl[NR], ibefore[NR];
+                uint64_t itotal = 0;
+#pragma unroll
+                for (int r_ = 0; r_ < NR; r_++) {
+                    ec[r_] = V3_NONE; im[r_] = 0;
+                    if (insn[r_] > k) {
+                        ec[r_] = __ldg(rd[r_].codep + insq[r_] + k);
+                        im[r_] = 1ull << ((ec[r_] >> 5) << 3);
+                    }
+                    iincl[r_] = v4_scan_packed(im[r_], lane);
+                    ibefore[r_] = itotal;
+                    itotal = v4_addsat(itotal, __shfl_sync(0xffffffffu, iincl[r_], 31));
+                }
+                int itot = 0;
+                uint64_t ibase = 0;
+#pragma unroll
+                for (int kk = 0; kk < NCAT; kk++) {
+                    ibase |= (uint64_t)min(itot, 255) << (kk << 3);
+                    itot += v4_field(itotal, kk);
+                }
+                uint8_t *iline = s_row[warp][rb];
+                rb ^= 1;
+#pragma unroll
+                for (int r_ = 0; r_ < NR; r_++) {
+                    if (ec[r_] == V3_NONE) continue;
+                    const int cat = ec[r_] >> 5;
+                    const uint64_t ex = v4_addsat(ibefore[r_], iincl[r_] - im[r_]);
+                    const int pos = v4_field(ibase, cat) + v4_field(ex, cat);
+                    if (pos < Wm1) iline[1 + pos] = (uint8_t)ec[r_];
+                }
+                if (lane == 0) {
+                    iline[0] = V3_FILL_INS;
+                    if (rowpos) rowpos[y] = qs + c;
+                    if (rowins) rowins[y] = k + 1;
+                }
+                emit_row(iline, min(itot, Wm1), true);
+                y++;
+            }
+        }
+    }
+    if (__any_sync(0xffffffffu, bad)) {
+        // a rule of the closed form broke mid-sweep (reference index -1): the rows written so far are overwritten by the
+        // exact kernel, which takes the whole window
+        if (lane == 0) {
+            const int k = atomicAdd(fb_count, 1);
+            fb_list[k] = w;
+            if (a.out_status) a.out_status[w] = 0;
+            asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+        }
+        return;
+    }
+    // ---- blank rows below the pileup: (0,0,0,255)
+    for (int yy = y + lane; yy < H; yy += 32) {
+        const uint32_t src = (uint32_t)__cvta_generic_to_shared(&s_fill[0][0]);
+        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
+                     :: "l"(img + ((size_t)yy * W << 2)), "r"(src), "r"(W << 2) : "memory");
+        if (rowpos) rowpos[yy] = -1;
+        if (rowins) rowins[yy] = 0;
+    }
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+    if (lane == 0 && a.out_status) a.out_status[w] = 0;
+    asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");      // the constant rows must outlive the copies
+}
+
 static size_t encoder_v3_smem_bytes(const dp_encode_params *p, int pool_bytes) {
     (void)p;
     size_t s = 0;
@@ -1757,16 +2160,23 @@ static int dp_encode_impl(const dp_reads *reads, int32_t n_windows, const int32_
     DP_REQUIRE(smem <= 227 * 1024, "coverageCutoff*windowCutoff too large for shared-memory staging");
     DP_CUDA_CHECK(cudaFuncSetAttribute(dp::encode_windows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     // fast path (v3) when the geometry fits its shared-memory planes; windows it cannot take are listed for v1
-    static int force_v1 = -1;
-    if (force_v1 < 0) { const char *e = getenv("DP_ENCODER"); force_v1 = (e && !strcmp(e, "v1")) ? 1 : 0; }
+    int force_v1 = 0, force_v3 = 0, force_v4 = 0;             /* DP_ENCODER = v1 | v3 | v4 pins the kernel (read per call: tests switch it) */
+    {
+        const char *e = getenv("DP_ENCODER");
+        force_v1 = (e && !strcmp(e, "v1")) ? 1 : 0;
+        force_v3 = (e && !strcmp(e, "v3")) ? 1 : 0;
+        force_v4 = (e && !strcmp(e, "v4")) ? 1 : 0;
+    }
     // shallow windows (30x long reads: ~3 k read bases per window at stride 100) run 5 CTAs per SM on a smaller pool, deep ones
     // 3 CTAs on a larger one; thresholds from a coverage sweep (45 / 60 / 75 / 90x: the 4-CTA build wins at 45-75x, the 3-CTA one from 90x)
     static int force_pool = -1;                                /* DP_ENC_POOL = small | large | deep overrides the choice */
     if (force_pool < 0) { const char *e = getenv("DP_ENC_POOL"); force_pool = !e ? 0 : !strcmp(e, "small") ? 1 : !strcmp(e, "large") ? 2 : !strcmp(e, "deep") ? 3 : 0; }
-    // read bases per window: the caller's figure when the read arrays cover more than this call's windows (prepared mode)
-    const int64_t bpw = bases_per_window > 0 ? bases_per_window : reads->n_bases / n_windows;
-    const bool small_pool = force_pool == 1 || (force_pool == 0 && bpw < 4000);
-    const bool deep_pool = force_pool == 3 || (force_pool == 0 && bpw >= 8700);
+    // depth of the pileup: read bases over an average reference position (the caller's figure in prepared mode, where the read
+    // arrays may cover more than the reference slice), and reads overlapping an average window
+    const double cover = bases_per_window > 0 ? (double)bases_per_window / L : (double)reads->n_bases / (double)(ref_len > 0 ? ref_len : 1);
+    const double reads_per_window = reads->n_bases > 0 ? cover * (1.0 + (double)L * reads->n_reads / (double)reads->n_bases) : 0.0;
+    const bool small_pool = force_pool == 1 || (force_pool == 0 && cover < 40.0);
+    const bool deep_pool = force_pool == 3 || (force_pool == 0 && cover >= 87.0);
     const size_t smem3 = dp::encoder_v3_smem_bytes(p, small_pool ? dp::V3_POOL_SMALL : deep_pool ? dp::V3_POOL_DEEP : dp::V3_POOL_BYTES);
     const bool use_v3 = !force_v1 && dp::g_lut_flat && L <= dp::V3_CS && p->window_cutoff <= 256 &&
                         p->coverage_cutoff >= 8 && p->coverage_cutoff <= 256 && smem3 <= 100 * 1024;
@@ -1777,6 +2187,36 @@ static int dp_encode_impl(const dp_reads *reads, int32_t n_windows, const int32_
         return DP_OK;
     }
     DP_CUDA_CHECK(cudaMemsetAsync(fb, 0, sizeof(int), st));
+    // v4 (a warp per window, lane = read) takes the call when 32 * NR lanes hold the reads of nearly every window; the few
+    // windows beyond that, like windows with a non-clean read, go to the exact kernel's list
+    int v4_nr = reads_per_window <= 18.0 ? 1 : reads_per_window <= 46.0 ? 2 : reads_per_window <= 100.0 ? 4 : 0;
+    if (force_v4 && v4_nr == 0) v4_nr = 4;
+    // v4 is OPT-IN (DP_ENCODER=v4): bit-exact like v3, but measured slower on B200 (0.53 vs 0.23 ms per 4096 windows at 30x):
+    // one warp walks ~70 columns as one dependent chain of ~1 000 instructions each (64-bit packed counters, three entry slots
+    // per lane and round), at 16 warps per SM -- see DESIGN.md section 3
+    if (force_v4 && !force_v3 && v4_nr > 0 && p->coverage_cutoff <= 256 && L + 1 <= 224) {
+        const unsigned grid = (unsigned)((n_windows + dp::V4_WARPS - 1) / dp::V4_WARPS);
+        if (v4_nr == 1) dp::encode_windows_v4_kernel<1><<<grid, dp::V4_WARPS * 32, 0, st>>>(a, n_windows, fb, fblist);
+        else if (v4_nr == 2) dp::encode_windows_v4_kernel<2><<<grid, dp::V4_WARPS * 32, 0, st>>>(a, n_windows, fb, fblist);
+        else dp::encode_windows_v4_kernel<4><<<grid, dp::V4_WARPS * 32, 0, st>>>(a, n_windows, fb, fblist);
+        DP_CUDA_CHECK(cudaGetLastError());
+        if (timing) cudaEventRecord(ev[3], st);
+        dp::encode_windows_kernel<<<n_windows, dp::ENC_THREADS, smem, st>>>(a, fb, fblist);
+        DP_CUDA_CHECK(cudaGetLastError());
+        if (timing) {
+            cudaEventRecord(ev[4], st);
+            cudaEventSynchronize(ev[4]);
+            float t[4] = {0, 0, 0, 0};
+            cudaEventElapsedTime(&t[0], ev[0], ev[1]); cudaEventElapsedTime(&t[1], ev[1], ev[2]);
+            cudaEventElapsedTime(&t[2], ev[2], ev[3]); cudaEventElapsedTime(&t[3], ev[3], ev[4]);
+            int nfb = 0;
+            cudaMemcpy(&nfb, fb, sizeof(int), cudaMemcpyDeviceToHost);
+            fprintf(stderr, "[dp_encode_windows] %d windows (v4, %d rounds): prep %.3f ms, base codes %.3f ms, fast kernel %.3f ms, "
+                            "exact kernel %.3f ms (%d windows)\n", n_windows, v4_nr, t[0], t[1], t[2], t[3], nfb);
+            for (int i = 0; i < 5; i++) cudaEventDestroy(ev[i]);
+        }
+        return DP_OK;
+    }
     DP_CUDA_CHECK(cudaFuncSetAttribute(dp::encode_windows_v3_kernel<4, dp::V3_POOL_BYTES>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        (int)dp::encoder_v3_smem_bytes(p, dp::V3_POOL_BYTES)));
     DP_CUDA_CHECK(cudaFuncSetAttribute(dp::encode_windows_v3_kernel<5, dp::V3_POOL_SMALL>, cudaFuncAttributeMaxDynamicSharedMemorySize,

@@ -4,7 +4,7 @@ The reference walks the VCF, and for every qualifying record (QUAL > 60, genotyp
 again, encodes ONE window, writes its PNG and one line of `summary-<region>.csv` (pileupGenerator.py:97-123).  Here the same
 function names, arguments, file names and CSV lines are kept, but the work is laid out for the GPU: the VCF is parsed once on
 the host, every window of the run goes to the device in ONE interval shard (`dp_encode_windows`, one H2D copy, one launch group),
-the labels are widened from the kernel's insert-row map, and the PNGs are deflated by a pool of host threads.
+the labels are widened from the kernel's insert-row map, and the PNG files are produced on the device (dp_png_encode).
 
 `pysam.VariantFile` is replaced by a plain-text VCF reader (`read_vcf`) with the record semantics the reference relies on:
 `qual` None for ".", `alleles` = REF + ALTs ("." = none), `start` = POS-1, `stop` = start + rlen with rlen = INFO/END-POS+1 when
@@ -143,23 +143,24 @@ def qualifying_records(vcf_region, vcfFile, qualityCutoff=60) -> List[VcfRecord]
 
 
 def encode_labelled_windows(bamFile, refFile, chromosome, positions, labels, variantLengths, flankLength=100,
-                            coverageCutoff=200, mapQualityCutoff=20, windowCutoff=150, device="cuda"):
+                            coverageCutoff=200, mapQualityCutoff=20, windowCutoff=150, device="cuda", keep_device=False):
     """Batched `PileUpGenerator.generatePileup` (Pileup.py:418-451) without the PNG: windows centred on the 0-based
     `positions` of "chr"+chromosome of a BAM + FASTA pair -> see `encode_labelled_batch`."""
     from .pileup import PileUpGenerator
     gen = PileUpGenerator(bamFile, refFile)
     contig = "chr" + str(chromosome)
     return encode_labelled_batch(gen._batch(contig), gen.fasta.contig(contig), 0, positions, labels, variantLengths,
-                                 flankLength, coverageCutoff, mapQualityCutoff, windowCutoff, device, contig)
+                                 flankLength, coverageCutoff, mapQualityCutoff, windowCutoff, device, contig, keep_device)
 
 
 def encode_labelled_batch(rb, ref, ref_base, positions, labels, variantLengths, flankLength=100, coverageCutoff=200,
-                          mapQualityCutoff=20, windowCutoff=150, device="cuda", contig="chr?"):
+                          mapQualityCutoff=20, windowCutoff=150, device="cuda", contig="chr?", keep_device=False):
     """Reads of one contig (`reads.ReadBatch`) + reference bytes starting at genomic `ref_base` + N window centres with their
     label drafts and insert-length dictionaries -> (uint8 [N, windowCutoff, coverageCutoff, 4] host array, list of output
     labels, rowpos, rowins).  One shard, one `dp_encode_windows` call; a second, narrow call (4 px wide, 256 rows) only for
     the windows whose rows were cut at windowCutoff, because the label is widened by ALL insert rows (Pileup.py:309,
-    320-333).  A window the reference would raise on raises the same exception type here."""
+    320-333).  A window the reference would raise on raises the same exception type here.  `keep_device`: the images stay a
+    CUDA tensor (for the device-side PNG encoder, png.write_files) instead of being copied to the host."""
     from . import _lib
     from .pileup import encode_windows, expand_label, _STATUS_EXC
     _lib.require_cuda()
@@ -185,7 +186,7 @@ def encode_labelled_batch(rb, ref, ref_base, positions, labels, variantLengths, 
             k = int(sel[bad[0]])
             raise _STATUS_EXC.get(int(status[bad[0]]), RuntimeError)(
                 "window at %s:%d raised status %d" % (contig, int(positions[order[k]]), int(status[bad[0]])))
-        return img.cpu().numpy(), rowpos.cpu().numpy(), rowins.cpu().numpy()
+        return (img if keep_device else img.cpu().numpy()), rowpos.cpu().numpy(), rowins.cpu().numpy()
 
     every = np.arange(n)
     img_s, rowpos_s, rowins_s = run(every, coverageCutoff, windowCutoff)
@@ -199,12 +200,20 @@ def encode_labelled_batch(rb, ref, ref_base, positions, labels, variantLengths, 
     inv = np.empty(n, dtype=np.int64)
     inv[order] = every
     out_labels = [expand_label(labels[i], variantLengths[i], full[inv[i]], windowCutoff) for i in range(n)]
+    if keep_device:
+        import torch
+        return img_s[torch.from_numpy(inv).to(img_s.device)], out_labels, rowpos_s[inv], rowins_s[inv]
     return img_s[inv], out_labels, rowpos_s[inv], rowins_s[inv]
 
 
 def write_pngs(paths, images, threads: Optional[int] = None):
     """RGBA PNG per window, as savePileupRGB stores it (Pileup.py:336-361: 200 px wide, 150 high, pixel (i, j) = row j, depth
-    i).  zlib releases the GIL, so a thread pool uses the host cores."""
+    i).  A CUDA tensor is encoded on the device (png.write_files: dp_png_encode, only finished files cross PCIe); host arrays
+    -- callers that already hold the pixels on the host -- go through PIL on a thread pool."""
+    if hasattr(images, "is_cuda") and images.is_cuda:
+        from . import png
+        png.write_files(list(paths), images, threads)
+        return
     from PIL import Image
 
     def one(k):
@@ -229,11 +238,13 @@ def generatePileupBasedonVCF(vcf_region, bamFile, refFile, vcfFile, output_dir, 
         drafts.append(lab)
         inserts.append(ins)
     img, labels, _, _ = encode_labelled_windows(bamFile, refFile, vcf_region, [r.pos - 1 for r in recs], drafts, inserts,
-                                                flankLength=window_size, device=device)
+                                                flankLength=window_size, device=device, keep_device=True)
     names = [output_dir + r.chrom + "-" + str(r.pos) for r in recs]
     last = {nm: k for k, nm in enumerate(names)}                     # records sharing a position share a file: last one wins
     keep = sorted(last.values())
-    write_pngs([names[k] + ".png" for k in keep], [img[k] for k in keep])
+    if keep:
+        import torch
+        write_pngs([names[k] + ".png" for k in keep], img[torch.as_tensor(keep, device=img.device)])
     with open(output_dir + 'summary' + '-' + vcf_region + ".csv", 'w') as smry:
         for nm, lab in zip(names, labels):
             smry.write(os.path.abspath(nm) + ".png," + str(lab) + '\n')

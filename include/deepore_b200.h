@@ -241,6 +241,14 @@ int dp_bam_extract(const uint8_t *bam, int64_t n_records, const int64_t *rec_off
                    const int64_t *seq_off, const int64_t *qual_off, int32_t *pos, uint16_t *flag, uint8_t *mapq,
                    int32_t *l_seq, uint32_t *cigar, uint8_t *seq4, uint8_t *qual, void *stream);
 
+/* ---- PNG files of pileup tensors, written on the device.  Replaces the per-window host work of
+ * Pileup.savePileupRGB (src/utils/Pileup.py:336-361: PIL image, 30 000 pixel stores, PNG save): out + i * out_stride
+ * receives the complete PNG byte stream (8-bit RGBA, W x H, filter 0, one IDAT of stored deflate blocks, Adler-32, chunk
+ * CRC-32s) of image i; every file is dp_png_size(H, W) bytes long.  DEVICE pointers; img = uint8 [n_images][H][W][4] as
+ * dp_encode_windows writes it. */
+int64_t dp_png_size(int32_t H, int32_t W);
+int dp_png_encode(const uint8_t *img, int32_t n_images, int32_t H, int32_t W, uint8_t *out, int64_t out_stride, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

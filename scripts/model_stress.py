@@ -1,5 +1,5 @@
 """GPU-box stress run (not part of the test suite): CUDA model forward vs the layer-by-layer numpy oracle for several weight
-seeds and random legal pileup tensors, both precision modes.
+seeds and random legal pileup tensors, the default, the parity-grade and the round-1 precision mode.
 
     python scripts/model_stress.py [n_seeds] [first_seed]
 """
@@ -15,7 +15,7 @@ sys.path.insert(0, os.path.join(ROOT, "oracle"))
 import model_oracle as mo                                     # noqa: E402
 from deepore_b200 import model, modelio                       # noqa: E402
 
-TOL = {"bf16": 2e-2, "bf16x3": 2e-4}
+TOL = {"fp16": 6e-3, "fp16x3": 2e-4, "bf16": 3e-2}      # absolute, logit scales 3 - 5 (1.2e-3 x scale, 1e-4)
 
 
 def main():
@@ -35,7 +35,7 @@ def main():
         calls = sorted(set([0, 1, 146, 147] + [int(x) for x in rng.integers(2, 146, size=4)]))
         want = np.stack([mo.forward_image(st, img[i], calls=calls) for i in range(nw)])
         line = "seed %d, %d windows, %d calls:" % (seed, nw, len(calls))
-        for prec in ("bf16x3", "bf16"):
+        for prec in ("fp16x3", "fp16", "bf16"):
             m = model.from_state(st, "cuda", prec)
             logits, _ = m.forward_windows(torch.from_numpy(img).cuda())
             torch.cuda.synchronize()

@@ -8,6 +8,18 @@ torch = pytest.importorskip("torch")
 pytestmark = pytest.mark.gpu
 
 
+@pytest.fixture(autouse=True, params=["auto", "v4", "v3"])
+def encoder_kernel(request, monkeypatch):
+    """Every test of this file runs with the encoder's own choice of fast kernel (v4: a warp per window, or v3: a CTA per window,
+    picked by the depth of the pileup) and with each of them pinned (DP_ENCODER is read per call); the exact general kernel
+    behind them takes the windows they list.  Results must be identical whichever kernel did the work."""
+    if request.param == "auto":
+        monkeypatch.delenv("DP_ENCODER", raising=False)
+    else:
+        monkeypatch.setenv("DP_ENCODER", request.param)
+    return request.param
+
+
 def _encode(g, win_qs=None, **kw):
     from deepore_b200.pileup import encode_windows
     wq = g.win_qs if win_qs is None else win_qs
@@ -98,7 +110,9 @@ def test_fast_path_takes_the_synthetic_windows():
         bad = [i for i in range(shard.n_windows) if not np.array_equal(img[i].cpu().numpy(), oimg[i])]
         assert not bad, "coverage %d: windows differ: %s" % (cov, bad[:10])
         assert np.array_equal(rowpos.cpu().numpy(), orp) and np.array_equal(rowins.cpu().numpy(), ori)
-        assert 0 <= nfb <= shard.n_windows // 10, "fast path handed %d of %d windows to the fallback" % (nfb, shard.n_windows)
+        import os
+        if os.environ.get("DP_ENCODER") != "v4" or cov <= 30:      # the opt-in warp-per-window kernel holds at most 128 reads per window
+            assert 0 <= nfb <= shard.n_windows // 10, "fast path handed %d of %d windows to the fallback" % (nfb, shard.n_windows)
 
 
 def test_bench_shard_of_config1_vs_oracle():
@@ -119,7 +133,9 @@ def test_bench_shard_of_config1_vs_oracle():
         assert np.array_equal(status.cpu().numpy(), ost)
         assert np.array_equal(img.cpu().numpy(), oimg)
         assert np.array_equal(rowpos.cpu().numpy(), orp) and np.array_equal(rowins.cpu().numpy(), ori)
-        assert enc.fallback_count() <= nwin // 20
+        import os
+        if os.environ.get("DP_ENCODER") != "v4" or cov <= 30.0:
+            assert enc.fallback_count() <= nwin // 20
 
 
 def test_batch_partition_invariance():

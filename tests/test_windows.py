@@ -107,3 +107,38 @@ def test_labelled_batch_any_order(gold):
     for a, k in enumerate(pick):
         assert np.array_equal(img[a], g.img[k])
         assert labels[a] == str(gold["label_out"][k])
+
+
+@pytest.mark.gpu
+def test_device_png_files_decode_to_the_same_pixels(tmp_path):
+    """dp_png_encode (csrc/png.cu): the byte streams written on the device are valid PNG files -- PIL (what
+    modules.dataset.PileupDataset uses, dataset.py:47-52) reads back exactly the encoder's pixels, for the default image
+    shape and for one whose scanline stream does not fill a deflate block; sizes match dp_png_size."""
+    import io
+    import zlib
+    import torch
+    from PIL import Image
+    from deepore_b200 import _lib, png
+    g = gu.load("bundled_na12878")
+    pick = [0, 1, 57, 131, 259]
+    files = png.encode_batch(torch.from_numpy(g.img[pick]).cuda())
+    assert tuple(files.shape) == (len(pick), int(_lib.lib().dp_png_size(150, 200)))
+    for a, k in enumerate(pick):
+        raw = files[a].numpy().tobytes()
+        im = Image.open(io.BytesIO(raw))
+        im.load()
+        assert im.mode == "RGBA" and im.size == (200, 150)
+        assert np.array_equal(np.asarray(im), g.img[k])
+        # the IDAT payload is a well-formed zlib stream (Adler-32 checked by zlib) of filter-0 scanlines
+        n = int.from_bytes(raw[33:37], "big")
+        assert raw[37:41] == b"IDAT" and zlib.crc32(raw[37:41 + n]) == int.from_bytes(raw[41 + n:45 + n], "big")
+        lines = zlib.decompress(raw[41:41 + n])
+        assert len(lines) == 150 * 801 and all(lines[r * 801] == 0 for r in range(150))
+    rng = np.random.default_rng(4)
+    small = rng.integers(0, 256, size=(3, 7, 12, 4), dtype=np.uint8)
+    files = png.encode_batch(torch.from_numpy(small).cuda())
+    for a in range(3):
+        assert np.array_equal(np.asarray(Image.open(io.BytesIO(files[a].numpy().tobytes()))), small[a])
+    paths = [str(tmp_path / ("w%d.png" % i)) for i in range(3)]
+    assert png.write_files(paths, torch.from_numpy(small).cuda()) == 3 * files.shape[1]
+    assert np.array_equal(np.asarray(Image.open(paths[2])), small[2])
