@@ -883,11 +883,13 @@ gru_step2w_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constan
                     const uint64_t db0 = make_smem_desc_sw128(sa + A_STAGE_BYTES);
                     const uint64_t db1 = make_smem_desc_sw128(sa + A_STAGE_BYTES + GRU2_B_ROWS * 128u);
                     const uint32_t d0 = tmem_base + (kind == 0 ? 0u : 64u);   // input: columns 0..191, hidden: 64..255
+                    if (!((g.debug >> 8) & 2)) {
 #pragma unroll
-                    for (int k = 0; k < BK / 16; k++) {
-                        const uint32_t acc = kind == 0 ? (uint32_t)(kc | k) : 1u;
-                        umma_bf16_2sm(d0, da + 2u * k, db0 + 2u * k, idesc192, acc);
-                        umma_bf16_2sm(d0 + 256, da + 2u * k, db1 + 2u * k, idesc192, acc);
+                        for (int k = 0; k < BK / 16; k++) {
+                            const uint32_t acc = kind == 0 ? (uint32_t)(kc | k) : 1u;
+                            umma_bf16_2sm(d0, da + 2u * k, db0 + 2u * k, idesc192, acc);
+                            umma_bf16_2sm(d0 + 256, da + 2u * k, db1 + 2u * k, idesc192, acc);
+                        }
                     }
                     umma_commit_mc(empty_bar(ps.stage), 3);
                     ps.advance(STAGES);
@@ -910,6 +912,14 @@ gru_step2w_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constan
             const bool has_h = P.h_prev != nullptr || P.h_prev_bf != nullptr;
             const int dbg = g.debug & 0xff;
             const uint32_t taddr = tmem_base + ((uint32_t)(wq * 32) << 16);
+            if (dbg == 1) {                              // timing experiment: accumulators handed straight back
+                mbar_wait(tfull_bar, aphase);
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive_cluster(tempty_bar, 0);
+                aphase ^= 1u;
+                continue;
+            }
 #pragma unroll 1
             for (int hb = 0; hb < 2; hb++) {
                 const int u0 = (ub + hb) * GRU_UB + cb * 16;
@@ -955,8 +965,13 @@ int launch_gru_step2w(const CUtensorMap *tmA, const CUtensorMap *tmB96, const Gr
         DP_CUDA_CHECK(cudaFuncSetAttribute(gru_step2w_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, GRUW_SMEM_BYTES));
         if (dev < 64) attr_done[dev] = true;
     }
+    static int dbgw = -1;
+    if (dbgw < 0) {
+        const char *e = getenv("DP_GRU_DEBUG"); dbgw = e ? atoi(e) : 0;
+        const char *e2 = getenv("DP_GRU_DEBUG2"); if (e2) dbgw |= atoi(e2) << 8;
+    }
     GruArgs g = g_in;
-    g.debug = 0;
+    g.debug = dbgw;
     g.tiles_m = (g.M + 255) / 256;
     const int n_tiles = g.tiles_m * (GRU_NUB / 2) * g.n_prob;
     if (n_tiles <= 0) return DP_OK;

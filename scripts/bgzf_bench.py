@@ -55,7 +55,41 @@ def timed(fn):
 
 ms_inf = timed(inflate)
 assert not status.cpu().numpy().any() and out.cpu().numpy().tobytes() == data
-ms_rec = timed(lambda: bamdev.records_on_device(out, "chr3"))
+ms_rec = timed(lambda: bamdev.records_on_device(out, "chr3"))      # the Python wrapper: allocations, the count read-back, slices
+# the two kernels groups by themselves (C-ABI calls, CUDA events on the launching stream)
+n_bytes = int(out.numel())
+cap = n_bytes // 36 + 1
+name = torch.tensor(list(b"chr3"), dtype=torch.uint8, device=dev)
+rec_off = torch.empty(cap + 1, dtype=torch.int64, device=dev)
+offs = [torch.empty(cap + 1, dtype=torch.int64, device=dev) for _ in range(3)]
+counts = torch.zeros(8, dtype=torch.int64, device=dev)
+
+
+def scan():
+    _lib.check(L.dp_bam_scan(out.data_ptr(), n_bytes, name.data_ptr(), 4, cap, rec_off.data_ptr(), offs[0].data_ptr(),
+                             offs[1].data_ptr(), offs[2].data_ptr(), counts.data_ptr(), C.c_void_p(st.cuda_stream)), "scan")
+
+
+ms_scan = timed(scan)
+c = counts.cpu().numpy()
+assert c[6] == 0 and c[0] == rb.n_reads
+nrec, ncig, nseq, nqual = (int(x) for x in c[:4])
+dd2 = {"pos": torch.empty(nrec, dtype=torch.int32, device=dev), "flag": torch.empty(nrec, dtype=torch.int16, device=dev),
+       "mapq": torch.empty(nrec, dtype=torch.uint8, device=dev), "l_seq": torch.empty(nrec, dtype=torch.int32, device=dev),
+       "cigar": torch.empty(max(ncig, 1), dtype=torch.int32, device=dev), "seq4": torch.empty(max(nseq, 1), dtype=torch.uint8, device=dev),
+       "qual": torch.empty(max(nqual, 1), dtype=torch.uint8, device=dev)}
+
+
+def extract():
+    _lib.check(L.dp_bam_extract(out.data_ptr(), nrec, rec_off.data_ptr(), offs[0].data_ptr(), offs[1].data_ptr(), offs[2].data_ptr(),
+                                dd2["pos"].data_ptr(), dd2["flag"].data_ptr(), dd2["mapq"].data_ptr(), dd2["l_seq"].data_ptr(),
+                                dd2["cigar"].data_ptr(), dd2["seq4"].data_ptr(), dd2["qual"].data_ptr(), C.c_void_p(st.cuda_stream)), "extract")
+
+
+ms_extract = timed(extract)
+os.environ["DP_BAM_SCAN"] = "serial"
+ms_scan_serial = timed(scan)
+del os.environ["DP_BAM_SCAN"]
 t0 = time.perf_counter()
 for b in range(n):
     zlib.decompress(image[idx["in_off"][b]:idx["in_off"][b] + idx["in_len"][b]].tobytes(), -15)
@@ -65,5 +99,7 @@ print(json.dumps({"workload": "synthetic 30x nanopore-length reads over %d kb, B
                   "inflate_ms": ms_inf, "inflate_out_GBps": len(data) / ms_inf / 1e6,
                   "inflate_algorithmic_GBps": (len(data) + image.size) / ms_inf / 1e6,
                   "scan_plus_extract_ms": ms_rec, "records_GBps": len(data) / ms_rec / 1e6,
+                  "scan_ms": ms_scan, "scan_serial_chain_walk_ms": ms_scan_serial, "extract_ms": ms_extract,
+                  "extract_GBps": 2 * len(data) / ms_extract / 1e6,
                   "zlib_one_core_s": cpu_s, "zlib_one_core_GBps": len(data) / cpu_s / 1e9,
                   "note": "warp-per-block inflate: %d blocks = %d warps on 148 SMs" % (n, n)}))
