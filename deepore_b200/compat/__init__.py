@@ -13,6 +13,11 @@ install() also provides what the 2017-era script expects from its environment an
 `torchnet.meter.ConfusionMeter` (constructed at test.py:47, never used), `scipy.misc` (imported, never used),
 `np.int` (dataset.py:44) and `torch.load(..., weights_only=False)` as the default (test.py:42 loads a whole object).
 Nothing here touches the reference's files.
+
+TRUST: a whole-object checkpoint is a pickle, and unpickling executes code chosen by whoever wrote the file.  The patched
+`torch.load` default is process-wide, so after install() EVERY torch.load of the process trusts its file the way the
+reference's test.py does; install() says so in a warning.  Load only checkpoints you wrote; `uninstall()` restores
+torch.load, and `trusted_checkpoints()` scopes the patch to a `with` block (pass patch_torch_load=False to install()).
 """
 import os
 import sys
@@ -21,7 +26,49 @@ import types
 HERE = os.path.dirname(os.path.abspath(__file__))
 
 
-def install():
+_ORIG_LOAD = None
+
+
+def _patch_torch_load():
+    global _ORIG_LOAD
+    import torch
+    if getattr(torch.load, "_deepore_patched", False):
+        return
+    _ORIG_LOAD = torch.load
+    orig = torch.load
+
+    def load(*a, **k):
+        k.setdefault("weights_only", False)             # whole-object pickles (train.py:194 / test.py:42)
+        return orig(*a, **k)
+
+    load._deepore_patched = True
+    torch.load = load
+
+
+def uninstall():
+    """Restore torch.load (the module names stay importable)."""
+    global _ORIG_LOAD
+    import torch
+    if _ORIG_LOAD is not None and getattr(torch.load, "_deepore_patched", False):
+        torch.load = _ORIG_LOAD
+    _ORIG_LOAD = None
+
+
+class trusted_checkpoints:
+    """`with trusted_checkpoints(): model = torch.load(path)` -- torch.load unpickles whole objects only inside the block."""
+
+    def __enter__(self):
+        self._was = _ORIG_LOAD is not None
+        _patch_torch_load()
+        return self
+
+    def __exit__(self, *exc):
+        if not self._was:
+            uninstall()
+        return False
+
+
+def install(patch_torch_load=True):
     if HERE not in sys.path:
         sys.path.insert(0, HERE)
     import numpy as np
@@ -51,14 +98,12 @@ def install():
         m = types.ModuleType("scipy.misc")
         scipy.misc = m
         sys.modules["scipy.misc"] = m
-    import torch
-    if not getattr(torch.load, "_deepore_patched", False):
-        _orig = torch.load
-
-        def load(*a, **k):
-            k.setdefault("weights_only", False)         # whole-object pickles (train.py:194 / test.py:42)
-            return _orig(*a, **k)
-
-        load._deepore_patched = True
-        torch.load = load
+    if patch_torch_load:
+        import warnings
+        import torch
+        if not getattr(torch.load, "_deepore_patched", False):
+            warnings.warn("deepore_b200.compat.install(): torch.load now defaults to weights_only=False for this process "
+                          "(the reference's test.py loads whole pickled objects); load only checkpoints you trust, "
+                          "or use compat.trusted_checkpoints() / compat.uninstall()", stacklevel=2)
+        _patch_torch_load()
     return HERE

@@ -433,6 +433,9 @@ struct EncArgs {
     int L, W, H, mapq_cut;
     uint8_t *out_img;
     int32_t *out_rowpos, *out_rowins, *out_status;
+    int32_t *out_colrows;      // optional [n_windows][L]: image rows each window column produces (0: unpopulated, else 1 + its
+                               // insert rows) -- the full row layout, not cut at H (dp_window_layout)
+    int layout_only;           // exact kernel: stop after the row layout
 };
 
 // Stage one round (<= SEG_CAP ops) of read r into slot (hdr, ops).  One warp.
@@ -773,6 +776,13 @@ __global__ void __launch_bounds__(ENC_THREADS) encode_windows_kernel(EncArgs a, 
         const bool active = tid < L;
         run_pass<0>(a, qs, qe, lo, hi, s_hdr, s_ops, s_cand, s_ncand, s_flags, s_ref, tid, 0, active, populated, max_ins,
                     cnt, base, run, nullptr, W - 1, err);
+    }
+    if (a.out_colrows && tid < L) a.out_colrows[(size_t)w * L + tid] = populated ? 1 + max_ins : 0;
+    if (a.layout_only) {                     // dp_window_layout: the label of a window is widened by ALL its insert rows
+        if (err) atomicMin(s_err, err);
+        __syncthreads();
+        if (tid == 0 && a.out_status) a.out_status[w] = *s_err;
+        return;
     }
     // ---- row map: rows = populated columns in ascending order, each followed by its insert rows (:295-317)
     {
@@ -2156,6 +2166,7 @@ static int dp_encode_impl(const dp_reads *reads, int32_t n_windows, const int32_
     a.ref = ref; a.ref_base = ref_base; a.ref_len = ref_len;
     a.L = L; a.W = p->coverage_cutoff; a.H = p->window_cutoff; a.mapq_cut = p->map_quality_cutoff;
     a.out_img = out_img; a.out_rowpos = out_rowpos; a.out_rowins = out_rowins; a.out_status = out_status;
+    a.out_colrows = nullptr; a.layout_only = 0;
     const size_t smem = dp::encoder_smem_bytes(p);
     DP_REQUIRE(smem <= 227 * 1024, "coverageCutoff*windowCutoff too large for shared-memory staging");
     DP_CUDA_CHECK(cudaFuncSetAttribute(dp::encode_windows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -2278,6 +2289,39 @@ int dp_encode_prepared(const dp_reads *reads, int32_t n_windows, const int32_t *
                        int32_t bases_per_window, void *stream) {
     return dp_encode_impl(reads, n_windows, win_qs, win_lo, win_hi, ref, ref_base, ref_len, p, out_img, out_rowpos, out_rowins,
                           out_status, workspace, workspace_bytes, max_windows, bases_per_window, 1, stream);
+}
+
+int dp_window_layout(const dp_reads *reads, int32_t n_windows, const int32_t *win_qs, const int32_t *win_lo,
+                     const int32_t *win_hi, const uint8_t *ref, int64_t ref_base, int64_t ref_len, const dp_encode_params *p,
+                     int32_t *out_colrows, int32_t *out_status, void *workspace, int64_t workspace_bytes, void *stream) {
+    DP_REQUIRE(reads && p && out_colrows, "null argument");
+    DP_REQUIRE(n_windows >= 0 && reads->n_reads >= 0 && reads->n_cigar >= 0 && reads->n_bases >= 0, "negative extent");
+    if (n_windows == 0) return DP_OK;
+    DP_REQUIRE(win_qs && win_lo && win_hi && ref, "null argument");
+    const int L = 2 * p->flank + 1;
+    DP_REQUIRE(p->flank >= 0 && L <= dp::ENC_THREADS, "flankLength must satisfy 2*flank+1 <= 256");
+    cudaStream_t st = (cudaStream_t)stream;
+    const dp::WsLayout lay = dp::ws_layout(reads->n_reads, reads->n_cigar, reads->n_bases, n_windows);
+    DP_REQUIRE(workspace && workspace_bytes >= lay.total, "workspace too small (dp_encode_workspace_bytes)");
+    uint8_t *wsb = (uint8_t *)workspace;
+    int rc = dp::encode_prepare(reads, p, wsb, lay, st, nullptr);
+    if (rc) return rc;
+    dp::EncArgs a;
+    memset(&a, 0, sizeof(a));
+    a.R = *reads;
+    a.aux = (dp::ReadAux *)(wsb + lay.aux); a.RP = (int *)(wsb + lay.RP); a.QP = (int *)(wsb + lay.QP);
+    a.info = (dp::ReadInfo *)(wsb + lay.info); a.ckpt = (int *)(wsb + lay.ckpt); a.endk = (int *)(wsb + lay.endk);
+    a.code0 = wsb + lay.code0;
+    a.win_qs = win_qs; a.win_lo = win_lo; a.win_hi = win_hi;
+    a.ref = ref; a.ref_base = ref_base; a.ref_len = ref_len;
+    a.L = L; a.W = p->coverage_cutoff; a.H = p->window_cutoff; a.mapq_cut = p->map_quality_cutoff;
+    a.out_status = out_status; a.out_colrows = out_colrows; a.layout_only = 1;
+    const size_t smem = dp::encoder_smem_bytes(p);
+    DP_REQUIRE(smem <= 227 * 1024, "coverageCutoff*windowCutoff too large for shared-memory staging");
+    DP_CUDA_CHECK(cudaFuncSetAttribute(dp::encode_windows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    dp::encode_windows_kernel<<<n_windows, dp::ENC_THREADS, smem, st>>>(a, nullptr, nullptr);
+    DP_CUDA_CHECK(cudaGetLastError());
+    return DP_OK;
 }
 
 int dp_window_ranges(const dp_reads *reads, const void *workspace, int64_t workspace_bytes, int32_t max_windows,

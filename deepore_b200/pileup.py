@@ -140,6 +140,40 @@ def encode_windows(reads: ReadBatch, win_qs: np.ndarray, ref: np.ndarray, ref_ba
     return enc.encode(sb, want_rowmap=want_rowmap)
 
 
+def window_layout(reads: ReadBatch, win_qs: np.ndarray, ref: np.ndarray, ref_base: int, flank: int = 100,
+                  coverageCutoff: int = 200, windowCutoff: int = 150, mapQualityCutoff: int = 20, device="cuda"):
+    """dp_window_layout: image rows per window column, NOT cut at windowCutoff -> (int32 [Nw, 2*flank+1] on the host: 0 for a
+    column without entries, else 1 + its insert rows; status int32 [Nw])."""
+    import torch
+    _lib.require_cuda()
+    shard = make_shard(reads, np.ascontiguousarray(ref, dtype=np.uint8), int(ref_base),
+                       np.ascontiguousarray(win_qs, dtype=np.int32), flank)
+    sb = ShardBuffers(shard, device).upload()
+    enc = Encoder(flank, coverageCutoff, windowCutoff, mapQualityCutoff, device)
+    nw = sb.n_windows
+    dev = enc.device
+    colrows = torch.zeros((max(nw, 1), 2 * flank + 1), dtype=torch.int32, device=dev)
+    status = torch.zeros((max(nw, 1),), dtype=torch.int32, device=dev)
+    ws = enc._workspace(sb.rstruct.n_reads, sb.rstruct.n_cigar, sb.rstruct.n_bases, nw)
+    st = torch.cuda.current_stream(dev)
+    with torch.cuda.device(dev):
+        rc = _lib.lib().dp_window_layout(C.byref(sb.rstruct), nw, sb.ptr["win_qs"], sb.ptr["win_lo"], sb.ptr["win_hi"],
+                                         sb.ptr["ref"], sb.ref_base, sb.ref_len, C.byref(enc.params), colrows.data_ptr(),
+                                         status.data_ptr(), ws.data_ptr(), ws.numel(), C.c_void_p(st.cuda_stream))
+    _lib.check(rc, "dp_window_layout")
+    return colrows[:nw].cpu().numpy(), status[:nw].cpu().numpy()
+
+
+def rowins_of_layout(colrows_row: np.ndarray) -> np.ndarray:
+    """Insert index of every image row of a window IN ORDER (0 for an anchor row, k for its k-th insert row) from the rows per
+    column that dp_window_layout returns: what `expand_label` walks."""
+    out = []
+    for n in colrows_row.tolist():
+        if n > 0:
+            out.extend(range(n))
+    return np.asarray(out, dtype=np.int32)
+
+
 _STATUS_EXC = {_lib.DP_EKEY: KeyError, _lib.DP_EINDEX: IndexError, _lib.DP_EINVAL: ValueError}
 
 
@@ -245,9 +279,10 @@ class Pileup:
         self._img, self._rowpos, self._rowins = run(self.coverageCutoff, self.windowCutoff)
         nrows = int((self._rowpos >= 0).sum())
         self._rowins_full = self._rowins[:nrows]
-        if nrows == self.windowCutoff and self.windowCutoff < 256:      # rows were cut: the label needs all of them
-            _, rp2, ri2 = run(4, 256)
-            self._rowins_full = ri2[:int((rp2 >= 0).sum())]
+        if nrows == self.windowCutoff:                                  # rows were cut: the label needs all of them
+            colrows, _ = window_layout(rb, wq, self._ref, self._ref_base, self.flankLength, self.coverageCutoff,
+                                       self.windowCutoff, self.mapQualityCutoff)
+            self._rowins_full = rowins_of_layout(colrows[0])
         # dictionaries of the drawn part: position -> category -> [[R,G,B,q], ...] ; anchor -> [k] -> base -> [...]
         for y in range(nrows):
             pos, k = int(self._rowpos[y]), int(self._rowins[y])

@@ -79,7 +79,10 @@ class ContigCaller:
         self.flank, self.W, self.H = flank, coverageCutoff, windowCutoff
         self.params = _lib.EncodeParams(flank, coverageCutoff, windowCutoff, mapQualityCutoff)
         self.eng = model.engine(self.mchunk * self.H, self.device, precision)
-        self.side = torch.cuda.Stream(self.device)
+        # HIGH priority: the GRU step kernels fill every SM (one 640-thread CTA each, nearly all registers), so the ingest
+        # kernels of the next chunk only run in the gaps between two launches -- their blocks must be first in line there, or
+        # the compute stream's next launch takes the SMs again and a 20 ms ingest stretches over hundreds of ms
+        self.side = torch.cuda.Stream(self.device, priority=-1)
         self.img = torch.empty((self.wpc, self.H, self.W, 4), dtype=torch.uint8, device=self.device)
         self.pred = torch.empty((self.wpc * self.H, 3), dtype=torch.uint8, device=self.device)
         self.timing = {"ingest_ms": 0.0, "compute_ms": 0.0, "chunks": 0}

@@ -157,9 +157,9 @@ def encode_labelled_batch(rb, ref, ref_base, positions, labels, variantLengths, 
                           mapQualityCutoff=20, windowCutoff=150, device="cuda", contig="chr?", keep_device=False):
     """Reads of one contig (`reads.ReadBatch`) + reference bytes starting at genomic `ref_base` + N window centres with their
     label drafts and insert-length dictionaries -> (uint8 [N, windowCutoff, coverageCutoff, 4] host array, list of output
-    labels, rowpos, rowins).  One shard, one `dp_encode_windows` call; a second, narrow call (4 px wide, 256 rows) only for
-    the windows whose rows were cut at windowCutoff, because the label is widened by ALL insert rows (Pileup.py:309,
-    320-333).  A window the reference would raise on raises the same exception type here.  `keep_device`: the images stay a
+    labels, rowpos, rowins).  One shard, one `dp_encode_windows` call; for the windows whose rows were cut at windowCutoff
+    a `dp_window_layout` call returns the uncut row layout, because the label is widened by ALL insert rows of the window
+    (Pileup.py:309, 320-333).  A window the reference would raise on raises the same exception type here.  `keep_device`: the images stay a
     CUDA tensor (for the device-side PNG encoder, png.write_files) instead of being copied to the host."""
     from . import _lib
     from .pileup import encode_windows, expand_label, _STATUS_EXC
@@ -192,11 +192,13 @@ def encode_labelled_batch(rb, ref, ref_base, positions, labels, variantLengths, 
     img_s, rowpos_s, rowins_s = run(every, coverageCutoff, windowCutoff)
     nrows = (rowpos_s >= 0).sum(axis=1)
     full = [rowins_s[k, :nrows[k]] for k in range(n)]
-    cut = np.nonzero(nrows == windowCutoff)[0] if windowCutoff < 256 else np.zeros(0, np.int64)
-    if cut.size:
-        _, rp2, ri2 = run(cut, 4, 256)
+    cut = np.nonzero(nrows == windowCutoff)[0]
+    if cut.size:                                                     # the label is widened by ALL insert rows of the window
+        from .pileup import rowins_of_layout, window_layout
+        colrows, _ = window_layout(rb, qs[cut], ref_cut, lo_g, flankLength, coverageCutoff, windowCutoff, mapQualityCutoff,
+                                   device=device)
         for a, k in enumerate(cut):
-            full[k] = ri2[a, :int((rp2[a] >= 0).sum())]
+            full[k] = rowins_of_layout(colrows[a])
     inv = np.empty(n, dtype=np.int64)
     inv[order] = every
     out_labels = [expand_label(labels[i], variantLengths[i], full[inv[i]], windowCutoff) for i in range(n)]

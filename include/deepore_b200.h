@@ -116,6 +116,18 @@ int dp_encode_prepared(const dp_reads *reads, int32_t n_windows, const int32_t *
                        int32_t *out_status, void *workspace, int64_t workspace_bytes, int32_t max_windows,
                        int32_t bases_per_window, void *stream);
 
+/*
+ * dp_window_layout -- the row layout of whole windows, NOT cut at windowCutoff: out_colrows[w][c] = number of image rows
+ * column c of window w produces (0: no entry lands there, else 1 + the longest insertion anchored there,
+ * Pileup.py:295-317).  The label of a window is widened by every insert row of the window, also those below the image
+ * (Pileup.labelInsertRegion, Pileup.py:309,320-333), so the label code needs this when a window's rows were cut.  Same
+ * arguments as dp_encode_windows; out_colrows is a device int32 [n_windows][2*flank+1]; runs the read preparation and the
+ * first pass of the exact kernel.
+ */
+int dp_window_layout(const dp_reads *reads, int32_t n_windows, const int32_t *win_qs, const int32_t *win_lo,
+                     const int32_t *win_hi, const uint8_t *ref, int64_t ref_base, int64_t ref_len, const dp_encode_params *p,
+                     int32_t *out_colrows, int32_t *out_status, void *workspace, int64_t workspace_bytes, void *stream);
+
 /* Diagnostics: how many windows of the LAST dp_encode_windows call on this workspace left the fast kernel's
  * envelope and were recomputed by the exact general kernel (results are identical either way).  Synchronises
  * the stream. */

@@ -61,3 +61,23 @@ def test_reference_pickle_loads_into_our_class(tmp_path):
     st, want = modelio.state_from_module(m), modelio.seeded_state(3)
     for k, v in want.items():
         assert np.array_equal(np.asarray(st[k]), v), k
+
+
+def test_torch_load_patch_is_scoped_and_reversible():
+    """compat.install() warns that torch.load trusts whole-object pickles from then on; uninstall() and the
+    trusted_checkpoints() context manager put the stock torch.load back."""
+    import warnings
+    import deepore_b200.compat as c
+    c.uninstall()
+    stock = torch.load
+    with c.trusted_checkpoints():
+        assert getattr(torch.load, "_deepore_patched", False)
+    assert torch.load is stock
+    with warnings.catch_warnings(record=True) as w:
+        warnings.simplefilter("always")
+        c.install()
+    assert getattr(torch.load, "_deepore_patched", False) and any("weights_only" in str(x.message) for x in w)
+    c.uninstall()
+    assert torch.load is stock
+    c.install(patch_torch_load=False)
+    assert torch.load is stock

@@ -142,3 +142,26 @@ def test_device_png_files_decode_to_the_same_pixels(tmp_path):
     paths = [str(tmp_path / ("w%d.png" % i)) for i in range(3)]
     assert png.write_files(paths, torch.from_numpy(small).cuda()) == 3 * files.shape[1]
     assert np.array_equal(np.asarray(Image.open(paths[2])), small[2])
+
+
+@pytest.mark.gpu
+def test_labels_of_windows_with_more_than_256_rows_match_the_reference():
+    """Long-read windows with 3 % insertions have 270 .. 340 image rows in total; the image keeps 150 of them but the label
+    is widened by EVERY insert row of the window (Pileup.labelInsertRegion, Pileup.py:309,320-333).  The uncut row layout
+    comes from dp_window_layout; labels must equal what the unmodified reference returned (tests/golden/nanopore_small.npz:
+    label draft '1' * 201, no variant lengths -- oracle/ref_harness.run_reference_window)."""
+    g = gu.load("nanopore_small")
+    n = g.win_qs.shape[0]
+    assert max(len(str(x)) for x in g.labels) > 256
+    pos = [int(q) + 100 for q in g.win_qs]
+    img, labels, rowpos, rowins = windows.encode_labelled_batch(g.reads, g.ref, g.ref_base, pos, ["1" * 201] * n, [{}] * n)
+    assert np.array_equal(img, g.img)
+    assert labels == [str(x) for x in g.labels]
+    # the Pileup class walks the same layout
+    from deepore_b200.pileup import rowins_of_layout, window_layout
+    colrows, status = window_layout(g.reads, g.win_qs[:3], g.ref, g.ref_base)
+    assert (status == 0).all() and colrows.shape == (3, 201)
+    for k in range(3):
+        full = rowins_of_layout(colrows[k])
+        assert len(full) - int((colrows[k] > 0).sum()) == len(str(g.labels[k])) - 201      # one label character per insert row
+        assert np.array_equal(full[:150], rowins[k][:150])
