@@ -535,13 +535,13 @@ def main():
         clock, max over ranks: the one piece of the multi-GPU path that is not device work."""
         if world == 1:
             return 0.0, None
-        local = host_calls[args.warmup:].numpy().reshape(-1, H)
+        local = host_calls[args.warmup:].numpy().reshape(-1, H).copy()      # later passes reuse the pinned buffer
         dist.barrier(group=host_group)
         t0 = time.perf_counter()
         allc = sharding.gather_on_host(local, group=host_group, dst=0)
         dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64)
         dist.all_reduce(dt, op=dist.ReduceOp.MAX, group=host_group)
-        return float(dt.item()) * 1e3, allc
+        return float(dt.item()) * 1e3, (allc, local)
 
     def time_encoder_alone():
         """Average duration of the encoder launch group over the timed shards (CUDA events on the launching stream)."""
@@ -603,7 +603,8 @@ def main():
 
     if rank == 0:
         if gathered is not None:
-            assert gathered.shape == (tot_windows, H) and np.array_equal(gathered[:win_timed], host_calls[args.warmup:].numpy().reshape(-1, H))
+            allc, local = gathered
+            assert allc.shape == (tot_windows, H) and np.array_equal(allc[:win_timed], local), "host gather lost rank 0's rows"
         peaks = load_peaks()
         alg = sum(algorithmic_bytes(sh) for sh in shards[args.warmup:])
         enc_achieved = alg / args.steps / (enc_ms * 1e-3) / 1e9
