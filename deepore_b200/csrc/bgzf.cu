@@ -30,7 +30,7 @@ constexpr int INFLATE_STRIDE_U16 = DPI_SCRATCH_U16 + 1;
 // different streams serialised on one warp scheduler: 0.21 GB/s on the bench file, the speed of ONE host core.  Here the 32
 // lanes of a warp run the same decoder in lock step on the same stream (no divergence) and split only the output bytes of
 // matches and stored blocks between them (inflate_core.h).
-__global__ void __launch_bounds__(INFLATE_WARPS * 32)
+__global__ void
 bgzf_inflate_kernel(const uint8_t *__restrict__ file, int64_t n_blocks, const int64_t *__restrict__ in_off,
                     const int32_t *__restrict__ in_len, const int64_t *__restrict__ out_off,
                     const int32_t *__restrict__ out_len, uint8_t *out, int32_t *__restrict__ status)
@@ -143,6 +143,13 @@ constexpr int SCAN_TRIES = 48;     // candidates walked per segment before givin
 __device__ __forceinline__ bool bam_record_plausible(const uint8_t *bam, int64_t n_bytes, int64_t o, int32_t n_ref)
 {
     if (o + 36 > n_bytes) return false;
+    // cheapest, most selective test first: the lanes of a warp test 32 offsets in lock step, so a round is only as short as
+    // its slowest lane -- random bytes pass "reference id inside the header's range" with probability ~n_ref / 2^32, but
+    // "32 <= block_size <= bytes left" with several per cent
+    {
+        const int32_t tid0 = ld_i32(bam + o + 4);
+        if (tid0 < -1 || tid0 >= n_ref) return false;
+    }
     const int32_t bs = ld_i32(bam + o);
     if (bs < 32 || o + 4 + (int64_t)bs > n_bytes) return false;
     const int32_t tid = ld_i32(bam + o + 4), pos = ld_i32(bam + o + 8);
@@ -222,14 +229,23 @@ bam_seg_kernel(const uint8_t *__restrict__ bam, int64_t n_bytes, int64_t seg_byt
             if (bam_walk_segment(bam, n_bytes, first, e, n_ref, tid, g)) g.entry = first;
         } else {
             int tries = 0;
-            for (int64_t base = b; base < e && g.entry < 0 && tries < SCAN_TRIES; base += 32) {
-                const int64_t o = base + lane;
-                unsigned m = __ballot_sync(0xffffffffu, o < e && bam_record_plausible(bam, n_bytes, o, n_ref));
-                while (m && g.entry < 0 && tries < SCAN_TRIES) {
-                    const int k = __ffs(m) - 1;
-                    m &= m - 1;
-                    tries++;
-                    if (bam_walk_segment(bam, n_bytes, base + k, e, n_ref, tid, g)) g.entry = base + k;   // all lanes, same loads
+            // 128 offsets per iteration (four independent tests per lane: the loop is bound by load latency, not by issue)
+            for (int64_t base = b; base < e && g.entry < 0 && tries < SCAN_TRIES; base += 128) {
+                unsigned m4[4];
+#pragma unroll
+                for (int u = 0; u < 4; u++) {
+                    const int64_t o = base + 32 * u + lane;
+                    m4[u] = __ballot_sync(0xffffffffu, o < e && bam_record_plausible(bam, n_bytes, o, n_ref));
+                }
+#pragma unroll
+                for (int u = 0; u < 4; u++) {
+                    unsigned m = m4[u];
+                    while (m && g.entry < 0 && tries < SCAN_TRIES) {
+                        const int k = __ffs(m) - 1;
+                        m &= m - 1;
+                        tries++;
+                        if (bam_walk_segment(bam, n_bytes, base + 32 * u + k, e, n_ref, tid, g)) g.entry = base + 32 * u + k;   // all lanes, same loads
+                    }
                 }
             }
         }
@@ -457,6 +473,21 @@ int dp_bam_scan(const uint8_t *bam, int64_t n_bytes, const char *contig, int32_t
     const int n_seg = (int)((n_bytes + seg_bytes - 1) / seg_bytes) > 0 ? (int)((n_bytes + seg_bytes - 1) / seg_bytes) : 1;
     uint8_t *scratch = nullptr;
     const size_t bytes = 64 + 16 + sizeof(ScanSeg) * (size_t)n_seg;
+    {   // stream-ordered scratch (~100 KB): keep freed blocks in the device's default pool instead of returning them to the
+        // driver at every synchronisation (the default release threshold is 0, which turns each call into a cudaMalloc)
+        static bool pool_set[64] = {false};
+        int dev = 0;
+        DP_CUDA_CHECK(cudaGetDevice(&dev));
+        if (dev < 64 && !pool_set[dev]) {
+            cudaMemPool_t pool;
+            if (cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) {
+                uint64_t keep = 64ull << 20;
+                cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+            }
+            cudaGetLastError();
+            pool_set[dev] = true;
+        }
+    }
     DP_CUDA_CHECK(cudaMallocAsync((void **)&scratch, bytes, st));
     int64_t *hdr = (int64_t *)scratch;
     int *link = (int *)(scratch + 64);

@@ -200,18 +200,25 @@ DPI_FN int dpi_decode_len(dpi_stream *s, const uint16_t *fast, const uint16_t *c
 }
 
 /* Literal/length + distance loop shared by fixed and dynamic blocks. */
-/* A run of literals is kept in registers -- lane i holds the i-th literal of the run -- and written with ONE store
- * instruction per DPI_LANES literals (a 32-byte sector per warp instruction instead of 32 single-byte stores by lane 0). */
+/* Output goes through a batch of up to DPI_LANES PENDING bytes kept in registers -- lane i holds the i-th pending byte --
+ * and leaves with ONE store instruction per batch (consecutive bytes, a 32-byte run per warp instruction instead of
+ * single-byte stores by lane 0).  Literals append one byte; a match of distance >= DPI_LANES appends its bytes too: the
+ * lanes that receive them load them from the already written output (consecutive addresses; such a source never lies in
+ * the pending batch).  Only matches closer than DPI_LANES -- whose source may be pending or may be the match itself -- flush
+ * the batch and copy directly.  `dirty` remembers that this warp stored since the lanes last synchronised, so that a
+ * source byte written by another lane is ordered before its load. */
 #define DPI_FLUSH_LITERALS()                                                        \
     do {                                                                            \
         if (DPI_LANE < run) s->out[s->out_pos - run + DPI_LANE] = mylit;            \
+        if (run) dirty = 1;                                                         \
         run = 0;                                                                    \
     } while (0)
 
 DPI_FN int dpi_codes(dpi_stream *s, const uint16_t *fast, const uint16_t *dfast, const uint16_t *lcnt, const uint16_t *lsym,
                      const uint16_t *dcnt, const uint16_t *dsym)
 {
-    uint32_t run = 0;                                            /* literals decoded but not yet stored */
+    uint32_t run = 0;                                            /* bytes decoded but not yet stored */
+    uint32_t dirty = 0;
     uint8_t mylit = 0;
     for (;;) {
         int sym = dpi_decode_len(s, fast, lcnt, lsym);
@@ -226,26 +233,43 @@ DPI_FN int dpi_codes(dpi_stream *s, const uint16_t *fast, const uint16_t *dfast,
             DPI_FLUSH_LITERALS();
             return DPI_OK;
         } else {
-            DPI_FLUSH_LITERALS();
             sym -= 257;
-            if (sym >= 29) return DPI_E_SYMBOL;
+            if (sym >= 29) { DPI_FLUSH_LITERALS(); return DPI_E_SYMBOL; }
             uint32_t len = dpi_len_base[sym] + dpi_bits(s, dpi_len_extra[sym]);
             int ds = dpi_decode_len(s, dfast, dcnt, dsym);
-            if (ds < 0) return ds;
-            if (ds >= DPI_NDIST) return DPI_E_SYMBOL;
+            if (ds < 0) { DPI_FLUSH_LITERALS(); return ds; }
+            if (ds >= DPI_NDIST) { DPI_FLUSH_LITERALS(); return DPI_E_SYMBOL; }
             uint32_t dist = dpi_dist_base[ds] + dpi_bits(s, dpi_dist_extra[ds]);
-            if (s->err) return s->err;
-            if (dist > s->out_pos) return DPI_E_DISTANCE;
-            if (s->out_pos + len > s->out_cap) return DPI_E_OUTPUT;
-            uint8_t *d = s->out + s->out_pos;
-            const uint8_t *f = d - dist;
-            DPI_SYNC();
-            if (dist >= len) {
-                for (uint32_t i = DPI_LANE; i < len; i += DPI_LANES) d[i] = f[i];
-            } else {                                             /* the match overlaps itself: its first `dist` bytes repeat */
-                for (uint32_t i = DPI_LANE; i < len; i += DPI_LANES) d[i] = f[i % dist];
+            if (s->err) { DPI_FLUSH_LITERALS(); return s->err; }
+            if (dist > s->out_pos) { DPI_FLUSH_LITERALS(); return DPI_E_DISTANCE; }
+            if (s->out_pos + len > s->out_cap) { DPI_FLUSH_LITERALS(); return DPI_E_OUTPUT; }
+            if (dist >= DPI_LANES) {
+                /* every source byte is already in memory: out_pos + k - dist < out_pos - run for k < DPI_LANES - run */
+                if (dirty) { DPI_SYNC(); dirty = 0; }
+                while (len) {
+                    const uint32_t n = len < DPI_LANES - run ? len : DPI_LANES - run;
+                    if (DPI_LANE >= run && DPI_LANE < run + n) mylit = s->out[s->out_pos + (DPI_LANE - run) - dist];
+                    run += n;
+                    s->out_pos += n;
+                    len -= n;
+                    if (run == DPI_LANES) {
+                        DPI_FLUSH_LITERALS();
+                        if (len && dist < 2 * DPI_LANES) { DPI_SYNC(); dirty = 0; }   /* the next piece may read this batch */
+                    }
+                }
+            } else {
+                DPI_FLUSH_LITERALS();
+                uint8_t *d = s->out + s->out_pos;
+                const uint8_t *f = d - dist;
+                DPI_SYNC();
+                if (dist >= len) {
+                    for (uint32_t i = DPI_LANE; i < len; i += DPI_LANES) d[i] = f[i];
+                } else {                                         /* the match overlaps itself: its first `dist` bytes repeat */
+                    for (uint32_t i = DPI_LANE; i < len; i += DPI_LANES) d[i] = f[i % dist];
+                }
+                dirty = 1;
+                s->out_pos += len;
             }
-            s->out_pos += len;
         }
     }
 }
