@@ -86,6 +86,8 @@ def lib():
     L.dp_model_forward_calls.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]
     L.dp_vote.restype = C.c_int
     L.dp_vote.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.dp_cross_entropy.restype = C.c_int
+    L.dp_cross_entropy.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     L.dp_model_peek.restype = C.c_int
     L.dp_model_peek.argtypes = [C.c_void_p, C.c_int32, C.c_int64, C.c_void_p]
     L.dp_model_profile.restype = C.c_int

@@ -24,7 +24,7 @@
 namespace {
 
 constexpr int INFLATE_WARPS = 4;                                     // BGZF blocks per CTA: one per warp
-constexpr int INFLATE_STRIDE_U16 = DPI_SCRATCH_U16 + 1;
+constexpr int INFLATE_STRIDE_U16 = (DPI_SCRATCH_U16 + 2 + 7) & ~7;   // per-warp scratch stays 16-byte aligned, banks staggered by the +2
 
 // One BGZF block per WARP.  A thread per block inside one warp (the first version) diverges on every symbol -- 32
 // different streams serialised on one warp scheduler: 0.21 GB/s on the bench file, the speed of ONE host core.  Here the 32
@@ -35,7 +35,7 @@ bgzf_inflate_kernel(const uint8_t *__restrict__ file, int64_t n_blocks, const in
                     const int32_t *__restrict__ in_len, const int64_t *__restrict__ out_off,
                     const int32_t *__restrict__ out_len, uint8_t *out, int32_t *__restrict__ status)
 {
-    __shared__ uint16_t scratch[INFLATE_WARPS][INFLATE_STRIDE_U16];
+    __shared__ __align__(16) uint16_t scratch[INFLATE_WARPS][INFLATE_STRIDE_U16];
     const int warp = threadIdx.x >> 5;
     const int64_t b = (int64_t)blockIdx.x * INFLATE_WARPS + warp;
     if (b >= n_blocks) return;                                      // warp-uniform

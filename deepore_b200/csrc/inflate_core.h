@@ -46,14 +46,20 @@
 #define DPI_MAXBITS 15
 #define DPI_NLEN    288
 #define DPI_NDIST   30
-/* first-level lookup of the literal/length code: DPI_FAST_BITS peeked bits -> (symbol << 4) | code length, 0 = the code
- * is longer than DPI_FAST_BITS (decoded by the count/first-code walk instead) */
+/* first-level lookup of a code: DPI_FAST_BITS peeked bits -> 32-bit entry
+ *     bits 0-3 code length | bits 4-7 extra bits | bits 8-23 base value | bits 24-25 kind
+ * with everything the symbol means already resolved (a literal's byte, a length's or distance's base and extra-bit count:
+ * no second table, no symbol-range compares on the hot path); 0 = the code is longer than DPI_FAST_BITS, or the symbol is
+ * not a legal one (decoded by the count/first-code walk instead, which also reports the error) */
 #define DPI_FAST_BITS 9
 #define DPI_FAST_SIZE (1 << DPI_FAST_BITS)
+#define DPI_K_LITERAL 1u
+#define DPI_K_BASE    2u      /* length or distance: base + extra bits */
+#define DPI_K_END     3u
 /* scratch per decoder, in uint16 units: counts + symbols of both codes, the code-length list, the two lookup tables
  * (literal/length and distance) */
 #define DPI_SLOW_U16 (16 + DPI_NLEN + 16 + DPI_NDIST + (DPI_NLEN + DPI_NDIST + 2) / 2 + 1)
-#define DPI_SCRATCH_U16 (DPI_SLOW_U16 + 2 * DPI_FAST_SIZE)
+#define DPI_SCRATCH_U16 (((DPI_SLOW_U16 + 1) & ~1) + 4 * DPI_FAST_SIZE)      /* the two tables hold 32-bit entries, 4-byte aligned */
 
 DPI_CONST uint16_t dpi_len_base[29] = {3, 4, 5, 6, 7, 8, 9, 10, 11, 13, 15, 17, 19, 23, 27, 31, 35, 43, 51, 59, 67, 83,
                                        99, 115, 131, 163, 195, 227, 258};
@@ -156,7 +162,19 @@ DPI_FN int dpi_build(uint16_t *count, uint16_t *symbol, const uint8_t *length, i
 
 /* Lookup table of the literal/length code from its code lengths (RFC 1951 3.2.2: codes of one length are consecutive,
  * shorter codes first; the stream carries them most-significant bit first, so the peeked index is the reversed code). */
-DPI_FN void dpi_build_fast(uint16_t *fast, const uint16_t *count, const uint8_t *length, int n)
+DPI_FN uint32_t dpi_entry(int sym, int len, int is_dist)
+{
+    if (is_dist) {
+        if (sym >= DPI_NDIST) return 0;
+        return (uint32_t)len | ((uint32_t)dpi_dist_extra[sym] << 4) | ((uint32_t)dpi_dist_base[sym] << 8) | (DPI_K_BASE << 24);
+    }
+    if (sym < 256) return (uint32_t)len | ((uint32_t)sym << 8) | (DPI_K_LITERAL << 24);
+    if (sym == 256) return (uint32_t)len | (DPI_K_END << 24);
+    if (sym - 257 >= 29) return 0;
+    return (uint32_t)len | ((uint32_t)dpi_len_extra[sym - 257] << 4) | ((uint32_t)dpi_len_base[sym - 257] << 8) | (DPI_K_BASE << 24);
+}
+
+DPI_FN void dpi_build_fast(uint32_t *fast, const uint16_t *count, const uint8_t *length, int n, int is_dist)
 {
     DPI_SYNC();
     for (uint32_t i = DPI_LANE; i < DPI_FAST_SIZE; i += DPI_LANES) fast[i] = 0;
@@ -176,30 +194,30 @@ DPI_FN void dpi_build_fast(uint16_t *fast, const uint16_t *count, const uint8_t 
             if (len > DPI_FAST_BITS) continue;
             uint32_t rev = 0;
             for (int b = 0; b < len; ++b) rev |= ((c >> b) & 1u) << (len - 1 - b);
-            const uint16_t e = (uint16_t)((sym << 4) | len);
+            const uint32_t e = dpi_entry(sym, len, is_dist);
             for (uint32_t idx = rev; idx < DPI_FAST_SIZE; idx += 1u << len) fast[idx] = e;
         }
     }
     DPI_SYNC();
 }
 
-/* Literal/length or distance symbol: one table lookup when enough input is buffered and the code is short, else the walk. */
-DPI_FN int dpi_decode_len(dpi_stream *s, const uint16_t *fast, const uint16_t *count, const uint16_t *symbol)
+/* One symbol as a table entry (format above): a lookup when the code is short and enough input is buffered, else the walk. */
+DPI_FN uint32_t dpi_symbol(dpi_stream *s, const uint32_t *fast, const uint16_t *count, const uint16_t *symbol, int is_dist)
 {
-    if (s->bitcnt < DPI_FAST_BITS) dpi_refill(s);
-    if (s->bitcnt >= DPI_FAST_BITS) {
-        const uint16_t e = fast[(uint32_t)s->bitbuf & (DPI_FAST_SIZE - 1)];
-        if (e) {
-            const int len = e & 15;
-            s->bitbuf >>= len;
-            s->bitcnt -= len;
-            return e >> 4;
-        }
+    const uint32_t e = fast[(uint32_t)s->bitbuf & (DPI_FAST_SIZE - 1)];
+    const int len = (int)(e & 15u);
+    if (e && len <= s->bitcnt) {
+        s->bitbuf >>= len;
+        s->bitcnt -= len;
+        return e;
     }
-    return dpi_decode(s, count, symbol);
+    const int sym = dpi_decode(s, count, symbol);
+    if (sym < 0) { s->err = sym; return 0; }
+    const uint32_t w = dpi_entry(sym, 1, is_dist);
+    if (!w) s->err = DPI_E_SYMBOL;
+    return w;
 }
 
-/* Literal/length + distance loop shared by fixed and dynamic blocks. */
 /* Output goes through a batch of up to DPI_LANES PENDING bytes kept in registers -- lane i holds the i-th pending byte --
  * and leaves with ONE store instruction per batch (consecutive bytes, a 32-byte run per warp instruction instead of
  * single-byte stores by lane 0).  Literals append one byte; a match of distance >= DPI_LANES appends its bytes too: the
@@ -212,34 +230,35 @@ DPI_FN int dpi_decode_len(dpi_stream *s, const uint16_t *fast, const uint16_t *c
         if (DPI_LANE < run) s->out[s->out_pos - run + DPI_LANE] = mylit;            \
         if (run) dirty = 1;                                                         \
         run = 0;                                                                    \
+        cap = DPI_LANES;                                                            \
     } while (0)
+/* The first batch of a stream is cut so that it ENDS on a DPI_LANES-byte boundary: every later batch then covers one aligned
+ * 32-byte sector and the L2 never has to fill a partly written sector from DRAM. */
+#define DPI_FIRST_CAP(p) (DPI_LANES - (uint32_t)((uintptr_t)(p) & (DPI_LANES - 1u)))
 
-DPI_FN int dpi_codes(dpi_stream *s, const uint16_t *fast, const uint16_t *dfast, const uint16_t *lcnt, const uint16_t *lsym,
+DPI_FN int dpi_codes(dpi_stream *s, const uint32_t *fast, const uint32_t *dfast, const uint16_t *lcnt, const uint16_t *lsym,
                      const uint16_t *dcnt, const uint16_t *dsym)
 {
     uint32_t run = 0;                                            /* bytes decoded but not yet stored */
+    uint32_t cap = DPI_FIRST_CAP(s->out + s->out_pos);           /* bytes the current batch takes */
     uint32_t dirty = 0;
     uint8_t mylit = 0;
     for (;;) {
-        int sym = dpi_decode_len(s, fast, lcnt, lsym);
-        if (sym < 0) { DPI_FLUSH_LITERALS(); return sym; }
-        if (sym < 256) {
+        if (s->bitcnt < 20) dpi_refill(s);                       /* a literal/length code (<= 15 bits) + its extra bits (<= 5) */
+        const uint32_t e = dpi_symbol(s, fast, lcnt, lsym, 0);
+        const uint32_t kind = e >> 24;
+        if (kind == DPI_K_LITERAL) {
             if (s->out_pos >= s->out_cap) { DPI_FLUSH_LITERALS(); return DPI_E_OUTPUT; }
-            if (DPI_LANE == run) mylit = (uint8_t)sym;
+            if (DPI_LANE == run) mylit = (uint8_t)(e >> 8);
             run++;
             s->out_pos++;
-            if (run == DPI_LANES) DPI_FLUSH_LITERALS();
-        } else if (sym == 256) {
-            DPI_FLUSH_LITERALS();
-            return DPI_OK;
-        } else {
-            sym -= 257;
-            if (sym >= 29) { DPI_FLUSH_LITERALS(); return DPI_E_SYMBOL; }
-            uint32_t len = dpi_len_base[sym] + dpi_bits(s, dpi_len_extra[sym]);
-            int ds = dpi_decode_len(s, dfast, dcnt, dsym);
-            if (ds < 0) { DPI_FLUSH_LITERALS(); return ds; }
-            if (ds >= DPI_NDIST) { DPI_FLUSH_LITERALS(); return DPI_E_SYMBOL; }
-            uint32_t dist = dpi_dist_base[ds] + dpi_bits(s, dpi_dist_extra[ds]);
+            if (run == cap) DPI_FLUSH_LITERALS();
+        } else if (kind == DPI_K_BASE) {
+            uint32_t len = ((e >> 8) & 0xffffu) + dpi_bits(s, (int)((e >> 4) & 15u));
+            if (s->bitcnt < 28) dpi_refill(s);                   /* a distance code (<= 15 bits) + its extra bits (<= 13) */
+            const uint32_t de = dpi_symbol(s, dfast, dcnt, dsym, 1);
+            if (!de) { DPI_FLUSH_LITERALS(); return s->err ? s->err : DPI_E_SYMBOL; }
+            const uint32_t dist = ((de >> 8) & 0xffffu) + dpi_bits(s, (int)((de >> 4) & 15u));
             if (s->err) { DPI_FLUSH_LITERALS(); return s->err; }
             if (dist > s->out_pos) { DPI_FLUSH_LITERALS(); return DPI_E_DISTANCE; }
             if (s->out_pos + len > s->out_cap) { DPI_FLUSH_LITERALS(); return DPI_E_OUTPUT; }
@@ -247,12 +266,12 @@ DPI_FN int dpi_codes(dpi_stream *s, const uint16_t *fast, const uint16_t *dfast,
                 /* every source byte is already in memory: out_pos + k - dist < out_pos - run for k < DPI_LANES - run */
                 if (dirty) { DPI_SYNC(); dirty = 0; }
                 while (len) {
-                    const uint32_t n = len < DPI_LANES - run ? len : DPI_LANES - run;
+                    const uint32_t n = len < cap - run ? len : cap - run;
                     if (DPI_LANE >= run && DPI_LANE < run + n) mylit = s->out[s->out_pos + (DPI_LANE - run) - dist];
                     run += n;
                     s->out_pos += n;
                     len -= n;
-                    if (run == DPI_LANES) {
+                    if (run == cap) {
                         DPI_FLUSH_LITERALS();
                         if (len && dist < 2 * DPI_LANES) { DPI_SYNC(); dirty = 0; }   /* the next piece may read this batch */
                     }
@@ -269,7 +288,14 @@ DPI_FN int dpi_codes(dpi_stream *s, const uint16_t *fast, const uint16_t *dfast,
                 }
                 dirty = 1;
                 s->out_pos += len;
+                cap = DPI_FIRST_CAP(s->out + s->out_pos);        /* re-align the batches behind the direct copy */
             }
+        } else if (kind == DPI_K_END) {
+            DPI_FLUSH_LITERALS();
+            return DPI_OK;
+        } else {                                                 /* no code matches / illegal symbol / input exhausted */
+            DPI_FLUSH_LITERALS();
+            return s->err ? s->err : DPI_E_SYMBOL;
         }
     }
 }
@@ -284,7 +310,7 @@ DPI_FN int dpi_inflate(const uint8_t *in, uint32_t in_len, uint8_t *out, uint32_
     st.out = out; st.out_cap = out_cap; st.out_pos = 0; st.err = 0;
     uint16_t *lcnt = scratch, *lsym = lcnt + 16, *dcnt = lsym + DPI_NLEN, *dsym = dcnt + 16;
     uint8_t *lengths = (uint8_t *)(dsym + DPI_NDIST);
-    uint16_t *fast = scratch + DPI_SLOW_U16, *dfast = fast + DPI_FAST_SIZE;
+    uint32_t *fast = (uint32_t *)(scratch + ((DPI_SLOW_U16 + 1) & ~1)), *dfast = fast + DPI_FAST_SIZE;
     int last, rc = DPI_OK;
     do {
         last = (int)dpi_bits(&st, 1);
@@ -309,10 +335,10 @@ DPI_FN int dpi_inflate(const uint8_t *in, uint32_t in_len, uint8_t *out, uint32_
             for (; i < 280; ++i) lengths[i] = 7;
             for (; i < DPI_NLEN; ++i) lengths[i] = 8;
             dpi_build(lcnt, lsym, lengths, DPI_NLEN);
-            dpi_build_fast(fast, lcnt, lengths, DPI_NLEN);
+            dpi_build_fast(fast, lcnt, lengths, DPI_NLEN, 0);
             for (i = 0; i < DPI_NDIST; ++i) lengths[i] = 5;
             dpi_build(dcnt, dsym, lengths, DPI_NDIST);
-            dpi_build_fast(dfast, dcnt, lengths, DPI_NDIST);
+            dpi_build_fast(dfast, dcnt, lengths, DPI_NDIST, 1);
             rc = dpi_codes(&st, fast, dfast, lcnt, lsym, dcnt, dsym);
         } else if (type == 2) {
             int nlen = (int)dpi_bits(&st, 5) + 257, ndist = (int)dpi_bits(&st, 5) + 1, ncode = (int)dpi_bits(&st, 4) + 4;
@@ -351,10 +377,10 @@ DPI_FN int dpi_inflate(const uint8_t *in, uint32_t in_len, uint8_t *out, uint32_
              * position that dpi_build of the literal code does not touch (lengths[] is separate from both tables) */
             int e = dpi_build(dcnt, dsym, lengths + nlen, ndist);
             if (e < 0 || (e > 0 && ndist - dcnt[0] != 1)) { rc = DPI_E_TABLE; break; }
-            dpi_build_fast(dfast, dcnt, lengths + nlen, ndist);
+            dpi_build_fast(dfast, dcnt, lengths + nlen, ndist, 1);
             e = dpi_build(lcnt, lsym, lengths, nlen);
             if (e < 0 || (e > 0 && nlen - lcnt[0] != 1)) { rc = DPI_E_TABLE; break; }
-            dpi_build_fast(fast, lcnt, lengths, nlen);
+            dpi_build_fast(fast, lcnt, lengths, nlen, 0);
             rc = dpi_codes(&st, fast, dfast, lcnt, lsym, dcnt, dsym);
         } else {
             rc = DPI_E_BTYPE;

@@ -266,6 +266,40 @@ __global__ void __launch_bounds__(256) vote_kernel(const uint8_t *__restrict__ p
     calls[i] = (int8_t)call;
 }
 
+// Cross-entropy of raw logits against integer labels, one thread per (call, t) element: loss = logsumexp(logits) - logits[label]
+// (nn.CrossEntropyLoss of the reference's validation pass, src/train.py:36,75 -- the reduction over the batch is the caller's).
+// A label outside [0, n_class) gives +inf and is counted (torch raises on it).
+__global__ void __launch_bounds__(256) cross_entropy_kernel(const float *__restrict__ logits, const uint8_t *__restrict__ labels,
+                                                            long long n, int n_class, float *__restrict__ loss,
+                                                            double *__restrict__ sum, int *__restrict__ bad) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    float l = 0.f;
+    if (i < n) {
+        const float *x = logits + i * n_class;
+        float mx = x[0];
+        for (int c = 1; c < n_class; c++) mx = fmaxf(mx, x[c]);
+        float se = 0.f;
+        for (int c = 0; c < n_class; c++) se += expf(x[c] - mx);
+        const int y = labels[i];
+        if (y < n_class) l = logf(se) + mx - x[y];
+        else { l = INFINITY; if (bad) atomicAdd(bad, 1); }
+        if (loss) loss[i] = l;
+    }
+    if (sum) {                                   // block sum in double, one atomic per block (order-dependent in the last bits)
+        __shared__ double s_part[8];
+        double v = (i < n && isfinite(l)) ? (double)l : 0.0;
+#pragma unroll
+        for (int d = 16; d; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
+        if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = v;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            double t = 0.0;
+            for (int w = 0; w < 8; w++) t += s_part[w];
+            atomicAdd(sum, t);
+        }
+    }
+}
+
 }  // namespace dp
 
 // ================================================================================================
@@ -685,6 +719,17 @@ int dp_vote(const uint8_t *pred, int32_t n_windows, int32_t H, int32_t n_class, 
     const long long n = (long long)n_windows * H;
     dp::vote_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(pred, n_windows, H, calls, labels,
                                                                                   confusion, n_class);
+    DP_CUDA_CHECK(cudaGetLastError());
+    return DP_OK;
+}
+
+int dp_cross_entropy(const float *logits, const uint8_t *labels, int64_t n, int32_t n_class, float *loss, double *sum,
+                     int32_t *bad_labels, void *stream) {
+    DP_REQUIRE(n >= 0 && n_class >= 1 && n_class <= 64, "bad extent");
+    if (n == 0) return DP_OK;
+    DP_REQUIRE(logits && labels && (loss || sum), "null argument");
+    dp::cross_entropy_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(logits, labels, n, n_class, loss, sum,
+                                                                                           bad_labels);
     DP_CUDA_CHECK(cudaGetLastError());
     return DP_OK;
 }

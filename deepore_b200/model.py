@@ -141,6 +141,25 @@ def vote(pred: torch.Tensor, n_windows: int, H: int, n_class: int = 3, labels: O
     return calls, confusion
 
 
+def cross_entropy(logits: torch.Tensor, labels: torch.Tensor):
+    """dp_cross_entropy: element-wise nn.CrossEntropyLoss (src/train.py:36,75) of raw logits [..., n_class] against integer
+    labels [...] on the device -> (loss fp32 [...], sum of the finite losses as a Python float, number of labels >= n_class)."""
+    assert logits.is_cuda and logits.dtype == torch.float32
+    logits = logits.contiguous()
+    n_class = int(logits.shape[-1])
+    lab = labels.to(device=logits.device, dtype=torch.uint8).contiguous()
+    assert tuple(lab.shape) == tuple(logits.shape[:-1]), "one label per logits row"
+    n = int(lab.numel())
+    loss = torch.empty(lab.shape, dtype=torch.float32, device=logits.device)
+    acc = torch.zeros(1, dtype=torch.float64, device=logits.device)
+    bad = torch.zeros(1, dtype=torch.int32, device=logits.device)
+    st = torch.cuda.current_stream(logits.device)
+    with torch.cuda.device(logits.device):
+        _lib.check(_lib.lib().dp_cross_entropy(logits.data_ptr(), lab.data_ptr(), n, n_class, loss.data_ptr(), acc.data_ptr(),
+                                               bad.data_ptr(), C.c_void_p(st.cuda_stream)), "dp_cross_entropy")
+    return loss, float(acc.item()), int(bad.item())
+
+
 class Model(nn.Module):
     def __init__(self, input_channel=3, output_channel=256, coverage_depth=50, hidden_size=500, hidden_layer=3, class_n=3,
                  bidirectional=True):
@@ -251,6 +270,24 @@ class Model(nn.Module):
         nw, H = int(img.shape[0]), int(img.shape[1])
         _, pred = self.forward_windows(img, want_logits=False)
         return vote(pred.view(nw * H, 3), nw, H, self.classN, labels, confusion)
+
+    def validation_loss(self, img: torch.Tensor, labels: torch.Tensor):
+        """The deterministic part of the reference's validation pass (src/train.py:21-78) for a batch of windows: forward of
+        every 3-row call, then CrossEntropyLoss of each call's (N, 3, class_n) outputs against labels[:, row:row+3] averaged
+        over the batch (train.py:75).  img uint8 [N, H, W, C] on the device, labels integer [N, >= H] (class ids < class_n).
+        Returns (per-call batch-mean losses fp32 [H-2] on the device, total_loss / total_images as train.py prints it when no
+        call is skipped: sum of the per-call losses / ((H-2) * N)).  The reference draws random numbers to skip most
+        all-reference calls (train.py:62-67); that sampling is the caller's."""
+        nw, H = int(img.shape[0]), int(img.shape[1])
+        logits, _ = self.forward_windows(img, want_logits=True)                       # [N, H, 3, C]
+        lab = labels.to(img.device)[:, :H].to(torch.uint8)
+        idx = torch.arange(H - 2, device=img.device)[:, None] + torch.arange(3, device=img.device)[None, :]   # rows of call r
+        y = lab[:, idx]                                                              # [N, H-2, 3]
+        loss, _, bad = cross_entropy(logits[:, :H - 2], y)
+        if bad:
+            raise _lib.DeeporeError("%d labels are outside [0, %d): CrossEntropyLoss has no class for them" % (bad, self.classN))
+        per_call = loss.mean(dim=(0, 2))
+        return per_call, float(per_call.sum().item()) / ((H - 2) * nw)
 
     def __getstate__(self):
         d = dict(self.__dict__)

@@ -204,6 +204,17 @@ int dp_model_forward_calls(dp_model *m, const uint8_t *img, int64_t n_calls, flo
 int dp_vote(const uint8_t *pred, int32_t n_windows, int32_t H, int32_t n_class, int8_t *calls, const uint8_t *labels,
             unsigned long long *confusion, void *stream);
 
+/*
+ * dp_cross_entropy -- the loss of the reference's validation pass (src/train.py:21-78: forward, then
+ * nn.CrossEntropyLoss on outputs.view(-1, 3) against the labels of the call's rows, :36,75), element-wise:
+ * loss[i] = logsumexp(logits[i][:]) - logits[i][labels[i]] for n (call, t) elements; the mean over a batch is the caller's.
+ *   logits device fp32 [n][n_class]; labels device uint8 [n]; loss optional device fp32 [n]; sum optional device double
+ *   (accumulated, not cleared); bad_labels optional device int32 counter of labels >= n_class (their loss is +inf and is
+ *   left out of the sum; torch raises on them).  Training itself (backward, SGD: train.py:101-203) is not part of this library.
+ */
+int dp_cross_entropy(const float *logits, const uint8_t *labels, int64_t n, int32_t n_class, float *loss, double *sum,
+                     int32_t *bad_labels, void *stream);
+
 /* Debug/inspection: copy an internal activation of the last forward to the host as fp32 [n_rows][512].
  * what: 0..2 = y[t] (folded CNN+Linear output); 100*k+10*d+t = GRU layer k hidden state, d=0 forward / 1 reverse. */
 int dp_model_peek(dp_model *m, int32_t what, int64_t n_rows, float *host_out);

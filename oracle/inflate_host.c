@@ -5,6 +5,7 @@
 
 int dpo_inflate(const uint8_t *in, uint32_t in_len, uint8_t *out, uint32_t out_cap, uint32_t *out_len)
 {
-    uint16_t scratch[DPI_SCRATCH_U16 + 1];
+    uint32_t scratch32[(DPI_SCRATCH_U16 + 3) / 2];            /* 4-byte aligned: the lookup tables hold 32-bit entries */
+    uint16_t *scratch = (uint16_t *)scratch32;
     return dpi_inflate(in, in_len, out, out_cap, scratch, out_len);
 }

@@ -129,3 +129,41 @@ def test_reference_test_loop_against_the_drop_in(tmp_path, precision):
         assert moved == 0, "the split-precision mode must reproduce the reference's confusion tensor exactly"
     else:
         assert moved <= 2 * int(0.003 * 260 * 146)      # each differing vote (counted in test_model_gpu.py) moves two entries
+
+
+@pytest.mark.parametrize("precision,tol", [("fp16x3", 2e-5), ("fp16", 2e-3)])
+def test_validation_pass_of_train_py(precision, tol):
+    """The validation pass of the reference's train.py (:21-78: forward of every 3-row call + nn.CrossEntropyLoss on
+    outputs.view(-1, 3) vs labels[:, row:row+3], loss summed over the calls, divided by calls x batch) on the CUDA forward
+    (Model.validation_loss -> dp_cross_entropy), against the same quantity computed with torch's own cross_entropy from the
+    UNMODIFIED reference model's logits (tests/golden/bundled_calls_seed7.npz).  Deterministic part only: the reference skips
+    most all-reference calls by drawing random numbers (train.py:62-67).  Labels: first 150 digits, class 3 clipped to 2."""
+    import torch.nn.functional as F
+    from deepore_b200 import model as dmodel, modelio
+    gc = np.load(os.path.join(gu.GOLD, "bundled_calls_seed7.npz"))
+    gw = np.load(os.path.join(gu.GOLD, "bundled_windows.npz"))
+    g = gu.load("bundled_na12878")
+    N = 64
+    labels = np.array([[min(int(c), 2) for c in str(gw["label_out"][i])[:150]] for i in range(N)], np.int64)
+    ref_logits = torch.from_numpy(gc["logits"][:N])                                # [N, 148, 3, 3]
+    want_calls = []
+    for row in range(148):
+        y = torch.from_numpy(labels[:, row:row + 3])
+        want_calls.append(float(F.cross_entropy(ref_logits[:, row].reshape(-1, 3), y.reshape(-1))))
+    want_total = sum(want_calls) / (148 * N)
+    m = dmodel.from_state(modelio.seeded_state(int(gc["seed"])), "cuda", precision)
+    per_call, total = m.validation_loss(torch.from_numpy(g.img[:N]).cuda(), torch.from_numpy(labels).cuda())
+    got = per_call.cpu().numpy()
+    assert got.shape == (148,)
+    assert np.abs(got - np.asarray(want_calls)).max() < tol and abs(total - want_total) < tol
+    # the kernel by itself against torch on the same logits, and its refusal of a label without a class
+    lg = ref_logits.cuda()
+    y = torch.from_numpy(np.stack([labels[:, r:r + 3] for r in range(148)], axis=1)).cuda()      # [N, 148, 3]
+    loss, s, bad = dmodel.cross_entropy(lg, y)
+    ref = F.cross_entropy(lg.reshape(-1, 3), y.reshape(-1), reduction="none").reshape(N, 148, 3)
+    assert bad == 0 and torch.allclose(loss, ref, atol=2e-6) and abs(s - float(ref.double().sum())) < 1e-3
+    y[0, 0, 0] = 3
+    loss, s, bad = dmodel.cross_entropy(lg, y)
+    assert bad == 1 and torch.isinf(loss[0, 0, 0])
+    with pytest.raises(Exception):
+        m.validation_loss(torch.from_numpy(g.img[:2]).cuda(), torch.full((2, 150), 3))
