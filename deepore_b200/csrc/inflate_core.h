@@ -3,7 +3,7 @@
  * Replaces, per BGZF block, what the reference's host stage does through zlib: dep/htslib/bgzf.c:456-499
  * (inflate_block: inflateInit2(-15) / inflate(Z_FINISH) on the block payload) -- zlib itself is a third-party
  * dependency that is not under /root/reference; the algorithm restated here is the published RFC 1951 one
- * (stored / fixed / dynamic blocks, canonical Huffman codes decoded by a 9-bit lookup table with the count/first-code walk behind it).
+ * (stored / fixed / dynamic blocks, canonical Huffman codes decoded by a first-level lookup table with the count/first-code walk behind it).
  *
  * One decoder instance = one warp (device) or one thread (host) decoding one BGZF payload front to back; the caller
  * provides the table scratch (shared memory on the device).  Everything is bounds-checked: malformed input ends with a negative
@@ -19,9 +19,9 @@
 #define DPI_FN __device__ __forceinline__
 #define DPI_CONST __constant__
 /* On the device the 32 lanes of a warp run ONE decoder in lock step: every lane holds the same bit reservoir and takes the
- * same branches (same-address loads broadcast, no divergence), and only the output is split -- lane 0 stores literals,
- * the lanes stride over the bytes of a match or of a stored block.  DPI_SYNC orders the lanes' earlier stores before a
- * match reads them back. */
+ * same branches (same-address loads broadcast, no divergence), and only the output is split -- lane i holds the i-th
+ * pending output byte, the lanes stride over the bytes of a close match or of a stored block.  DPI_SYNC orders the lanes'
+ * earlier stores before a match reads them back. */
 #define DPI_LANE  ((uint32_t)(threadIdx.x & 31))
 #define DPI_LANES 32u
 #define DPI_SYNC() __syncwarp()
@@ -31,6 +31,14 @@
 #define DPI_LANE  0u
 #define DPI_LANES 1u
 #define DPI_SYNC() ((void)0)
+#endif
+
+#if defined(__GNUC__) || defined(__CUDACC__)
+#define DPI_LIKELY(x)   __builtin_expect(!!(x), 1)
+#define DPI_UNLIKELY(x) __builtin_expect(!!(x), 0)
+#else
+#define DPI_LIKELY(x)   (x)
+#define DPI_UNLIKELY(x) (x)
 #endif
 
 #define DPI_OK            0
@@ -46,20 +54,23 @@
 #define DPI_MAXBITS 15
 #define DPI_NLEN    288
 #define DPI_NDIST   30
-/* first-level lookup of a code: DPI_FAST_BITS peeked bits -> 32-bit entry
- *     bits 0-3 code length | bits 4-7 extra bits | bits 8-23 base value | bits 24-25 kind
- * with everything the symbol means already resolved (a literal's byte, a length's or distance's base and extra-bit count:
- * no second table, no symbol-range compares on the hot path); 0 = the code is longer than DPI_FAST_BITS, or the symbol is
- * not a legal one (decoded by the count/first-code walk instead, which also reports the error) */
-#define DPI_FAST_BITS 9
-#define DPI_FAST_SIZE (1 << DPI_FAST_BITS)
-#define DPI_K_LITERAL 1u
-#define DPI_K_BASE    2u      /* length or distance: base + extra bits */
-#define DPI_K_END     3u
+/* First-level lookup of a code: the peeked low bits of the reservoir index a table of 32-bit entries in which everything
+ * the symbol means is already resolved (no second table, no symbol-range compares on the hot path):
+ *     bits 0-7 code length | bits 8-15 number of extra bits | bits 16-30 literal byte / length base / distance base
+ * literal/length table (DPI_LBITS index bits): bit 31 marks a literal (one sign test), bit 30 marks "special": the
+ *     end-of-block code when the code length is non-zero, else a miss (code longer than DPI_LBITS, or an illegal symbol);
+ * distance table (DPI_DBITS index bits): 0 is a miss.
+ * A miss consumes nothing and goes to the count/first-code walk, which also reports the errors. */
+#define DPI_LBITS 10
+#define DPI_DBITS 8
+#define DPI_LSIZE (1 << DPI_LBITS)
+#define DPI_DSIZE (1 << DPI_DBITS)
+#define DPI_F_LITERAL 0x80000000u
+#define DPI_F_SPECIAL 0x40000000u
 /* scratch per decoder, in uint16 units: counts + symbols of both codes, the code-length list, the two lookup tables
- * (literal/length and distance) */
+ * (literal/length and distance; 32-bit entries, 4-byte aligned) */
 #define DPI_SLOW_U16 (16 + DPI_NLEN + 16 + DPI_NDIST + (DPI_NLEN + DPI_NDIST + 2) / 2 + 1)
-#define DPI_SCRATCH_U16 (((DPI_SLOW_U16 + 1) & ~1) + 4 * DPI_FAST_SIZE)      /* the two tables hold 32-bit entries, 4-byte aligned */
+#define DPI_SCRATCH_U16 (((DPI_SLOW_U16 + 1) & ~1) + 2 * (DPI_LSIZE + DPI_DSIZE))
 
 DPI_CONST uint16_t dpi_len_base[29] = {3, 4, 5, 6, 7, 8, 9, 10, 11, 13, 15, 17, 19, 23, 27, 31, 35, 43, 51, 59, 67, 83,
                                        99, 115, 131, 163, 195, 227, 258};
@@ -70,60 +81,107 @@ DPI_CONST uint8_t dpi_dist_extra[30] = {0, 0, 0, 0, 1, 1, 2, 2, 3, 3, 4, 4, 5, 5
                                         12, 12, 13, 13};
 DPI_CONST uint8_t dpi_clen_order[19] = {16, 17, 18, 0, 8, 7, 9, 6, 10, 5, 11, 4, 12, 3, 13, 2, 14, 1, 15};
 
+/* The bit reader works on the aligned 32-bit words that cover [in, in + in_len): `head` = in & 3 bytes of the first word
+ * precede the stream and are dropped at the start.  Past the last word that holds a stream byte that word repeats, so the
+ * hot loop never tests for the end of the input: a stream that runs out keeps decoding those bits until it ends, errs or fills
+ * the output (all bounded), and dpi_exhausted() -- consumed bits > stream bits -- turns that into DPI_E_INPUT afterwards.
+ * Nothing outside the words that hold at least one stream byte is ever read. */
 typedef struct dpi_stream {
-    const uint8_t *in;
-    uint32_t in_len, in_pos;
+    const uint8_t *in;        /* the stream itself (not aligned) */
+    uint32_t in_len;
+    uint32_t head;            /* in & 3 */
+    uint32_t in_last;         /* last aligned word that holds a stream byte */
+    uint32_t in_pos;          /* next word to go into the reservoir */
+    uint32_t ahead;           /* that word, loaded one refill early: its latency is off the decoding chain */
     uint64_t bitbuf;          /* LSB-first bit reservoir */
-    int32_t bitcnt;
+    uint32_t bitcnt;
     uint8_t *out;
     uint32_t out_cap, out_pos;
-    int32_t err;
 } dpi_stream;
 
-/* Top the reservoir up: one aligned 32-bit load where the input pointer allows it (every refill after the first few bytes
- * of a stream; a byte load per 8 bits was a dependent load per output byte), single bytes at unaligned positions and at
- * the tail.  Never reads outside [in, in + in_len). */
+#ifdef __CUDACC__
+#define DPI_LOAD_WORD(s, i) (((const uint32_t *)((s)->in - (s)->head))[i])
+DPI_FN uint32_t dpi_low_bits(uint32_t v, uint32_t n)     /* the low n (< 32) bits of v: a bit-mask instruction and an AND */
+{
+    uint32_t m;
+    asm("bmsk.clamp.b32 %0, 0, %1;" : "=r"(m) : "r"(n));
+    return v & m;
+}
+#else
+DPI_FN uint32_t dpi_load_word_host(const dpi_stream *s, uint32_t i)   /* same bytes, assembled without touching a byte outside the stream */
+{
+    uint32_t w = 0;
+    for (uint32_t k = 0; k < 4; ++k) {
+        const uint64_t at = (uint64_t)i * 4u + k;
+        if (at >= s->head && at - s->head < s->in_len) w |= (uint32_t)s->in[at - s->head] << (8 * k);
+    }
+    return w;
+}
+#define DPI_LOAD_WORD(s, i) dpi_load_word_host(s, i)
+DPI_FN uint32_t dpi_low_bits(uint32_t v, uint32_t n) { return v & ((1u << n) - 1u); }
+#endif
+
+/* Append one word to the reservoir; the caller has seen bitcnt < 32.  Past the end the last word repeats (in_pos keeps
+ * counting, which is what dpi_exhausted looks at): no branch, and what the repeated bits decode to never matters. */
 DPI_FN void dpi_refill(dpi_stream *s)
 {
-    if (s->bitcnt > 32) return;
-    if (s->in_pos + 4 <= s->in_len && ((uintptr_t)(s->in + s->in_pos) & 3u) == 0) {
-        const uint32_t w = *(const uint32_t *)(s->in + s->in_pos);           /* little-endian hosts and devices */
-        s->bitbuf |= (uint64_t)w << s->bitcnt;
-        s->bitcnt += 32;
-        s->in_pos += 4;
-        return;
-    }
-    while (s->bitcnt <= 56 && s->in_pos < s->in_len && (s->bitcnt <= 24 || ((uintptr_t)(s->in + s->in_pos) & 3u) != 0)) {
-        s->bitbuf |= (uint64_t)s->in[s->in_pos++] << s->bitcnt;
-        s->bitcnt += 8;
-    }
+    const uint32_t w = s->ahead;
+    s->in_pos++;
+    s->ahead = DPI_LOAD_WORD(s, s->in_pos < s->in_last ? s->in_pos : s->in_last);
+    s->bitbuf |= (uint64_t)w << s->bitcnt;
+    s->bitcnt += 32;
 }
 
-/* Take `need` (<= 16) bits; past the end of the input the stream goes into error and zeros are returned. */
-DPI_FN uint32_t dpi_bits(dpi_stream *s, int need)
+DPI_FN void dpi_drop(dpi_stream *s, uint32_t n)          /* n <= bitcnt */
 {
-    if (s->bitcnt < need) {
-        dpi_refill(s);
-        if (s->bitcnt < need) {
-            s->err = DPI_E_INPUT;
-            return 0;
-        }
-    }
-    uint32_t v = (uint32_t)(s->bitbuf & ((1u << need) - 1u));
-    s->bitbuf >>= need;
-    s->bitcnt -= need;
+    s->bitbuf >>= n;
+    s->bitcnt -= n;
+}
+
+/* Take `need` (<= 16) bits. */
+DPI_FN uint32_t dpi_bits(dpi_stream *s, uint32_t need)
+{
+    if (s->bitcnt < 32) dpi_refill(s);
+    const uint32_t v = dpi_low_bits((uint32_t)s->bitbuf, need);
+    dpi_drop(s, need);
     return v;
 }
 
-/* Canonical code described by count[len] (codes of each length) and symbol[] (symbols ordered by code). */
+/* Position of the next unread bit as a byte offset from `in` (rounded down), and whether more bits were consumed than
+ * the stream holds. */
+DPI_FN uint32_t dpi_byte_pos(const dpi_stream *s) { return (s->in_pos * 32u - s->bitcnt) / 8u - s->head; }
+DPI_FN int dpi_exhausted(const dpi_stream *s)
+{
+    return (uint64_t)s->in_pos * 32u - s->bitcnt > ((uint64_t)s->head + s->in_len) * 8u;
+}
+
+/* Continue reading at byte `off` of the stream. */
+DPI_FN void dpi_seek(dpi_stream *s, uint32_t off)
+{
+    const uint32_t at = s->head + off;
+    s->in_pos = at >> 2;
+    s->ahead = DPI_LOAD_WORD(s, s->in_pos < s->in_last ? s->in_pos : s->in_last);
+    s->bitbuf = 0;
+    s->bitcnt = 0;
+    dpi_refill(s);
+    dpi_drop(s, (at & 3u) * 8u);
+}
+
+/* Canonical code described by count[len] (codes of each length) and symbol[] (symbols ordered by code): the walk behind
+ * the lookup tables, and the decoder of the code-length code.  Consumes the code; DPI_E_SYMBOL if no code matches. */
 DPI_FN int dpi_decode(dpi_stream *s, const uint16_t *count, const uint16_t *symbol)
 {
+    if (s->bitcnt < 32) dpi_refill(s);
+    uint32_t v = (uint32_t)s->bitbuf;
     int32_t code = 0, first = 0, index = 0;
-    for (int len = 1; len <= DPI_MAXBITS; ++len) {
-        code |= (int32_t)dpi_bits(s, 1);
-        if (s->err) return s->err;
-        int32_t c = count[len];
-        if (code - c < first) return symbol[index + (code - first)];
+    for (uint32_t len = 1; len <= DPI_MAXBITS; ++len) {
+        code |= (int32_t)(v & 1u);
+        v >>= 1;
+        const int32_t c = count[len];
+        if (code - c < first) {
+            dpi_drop(s, len);
+            return symbol[index + (code - first)];
+        }
         index += c;
         first = (first + c) << 1;
         code <<= 1;
@@ -160,198 +218,237 @@ DPI_FN int dpi_build(uint16_t *count, uint16_t *symbol, const uint8_t *length, i
     return left;
 }
 
-/* Lookup table of the literal/length code from its code lengths (RFC 1951 3.2.2: codes of one length are consecutive,
- * shorter codes first; the stream carries them most-significant bit first, so the peeked index is the reversed code). */
-DPI_FN uint32_t dpi_entry(int sym, int len, int is_dist)
+/* Table entry of a symbol (format above) with `len` in the code-length field; 0 for a symbol that must not occur. */
+DPI_FN uint32_t dpi_entry(int sym, uint32_t len, int is_dist)
 {
     if (is_dist) {
         if (sym >= DPI_NDIST) return 0;
-        return (uint32_t)len | ((uint32_t)dpi_dist_extra[sym] << 4) | ((uint32_t)dpi_dist_base[sym] << 8) | (DPI_K_BASE << 24);
+        return len | ((uint32_t)dpi_dist_extra[sym] << 8) | ((uint32_t)dpi_dist_base[sym] << 16);
     }
-    if (sym < 256) return (uint32_t)len | ((uint32_t)sym << 8) | (DPI_K_LITERAL << 24);
-    if (sym == 256) return (uint32_t)len | (DPI_K_END << 24);
+    if (sym < 256) return len | ((uint32_t)sym << 16) | DPI_F_LITERAL;
+    if (sym == 256) return len | DPI_F_SPECIAL;
     if (sym - 257 >= 29) return 0;
-    return (uint32_t)len | ((uint32_t)dpi_len_extra[sym - 257] << 4) | ((uint32_t)dpi_len_base[sym - 257] << 8) | (DPI_K_BASE << 24);
+    return len | ((uint32_t)dpi_len_extra[sym - 257] << 8) | ((uint32_t)dpi_len_base[sym - 257] << 16);
 }
 
-DPI_FN void dpi_build_fast(uint32_t *fast, const uint16_t *count, const uint8_t *length, int n, int is_dist)
+DPI_FN uint32_t dpi_reverse(uint32_t code, uint32_t len)     /* the stream carries codes most-significant bit first */
 {
+#ifdef __CUDACC__
+    return __brev(code) >> (32u - len);
+#else
+    uint32_t r = 0;
+    for (uint32_t b = 0; b < len; ++b) r |= ((code >> b) & 1u) << (len - 1u - b);
+    return r;
+#endif
+}
+
+/* Lookup table of a code from count[]/symbol[] (RFC 1951 3.2.2: codes of one length are consecutive, shorter codes first, so
+ * the i-th symbol in code order has the code first[len] + (i - number of shorter codes)).  The lanes take every DPI_LANES-th
+ * symbol of the code order and write all the replicas of its entry. */
+DPI_FN void dpi_build_fast(uint32_t *fast, uint32_t bits, const uint16_t *count, const uint16_t *symbol, int n, int is_dist)
+{
+    const uint32_t size = 1u << bits;
     DPI_SYNC();
-    for (uint32_t i = DPI_LANE; i < DPI_FAST_SIZE; i += DPI_LANES) fast[i] = 0;
+    for (uint32_t i = DPI_LANE; i < size; i += DPI_LANES) fast[i] = is_dist ? 0u : DPI_F_SPECIAL;
     DPI_SYNC();
-    if (DPI_LANE == 0) {
-        uint16_t next[DPI_MAXBITS + 1];
-        uint32_t code = 0;
-        next[0] = 0;
-        for (int len = 1; len <= DPI_MAXBITS; ++len) {
-            code = (code + (len > 1 ? count[len - 1] : 0)) << 1;
-            next[len] = (uint16_t)code;
+    const uint32_t used = (uint32_t)n - count[0];
+    for (uint32_t i = DPI_LANE; i < used; i += DPI_LANES) {
+        uint32_t first = 0, below = 0, len = 1;
+        for (; len <= DPI_MAXBITS; ++len) {
+            const uint32_t c = count[len];
+            if (i < below + c) break;
+            below += c;
+            first = (first + c) << 1;
         }
-        for (int sym = 0; sym < n; ++sym) {
-            const int len = length[sym];
-            if (len == 0) continue;
-            const uint32_t c = next[len]++;
-            if (len > DPI_FAST_BITS) continue;
-            uint32_t rev = 0;
-            for (int b = 0; b < len; ++b) rev |= ((c >> b) & 1u) << (len - 1 - b);
-            const uint32_t e = dpi_entry(sym, len, is_dist);
-            for (uint32_t idx = rev; idx < DPI_FAST_SIZE; idx += 1u << len) fast[idx] = e;
-        }
+        if (len > bits) break;                                   /* code order is length order: the rest is longer still */
+        const uint32_t e = dpi_entry(symbol[i], len, is_dist);
+        if (!e) continue;
+        for (uint32_t idx = dpi_reverse(first + (i - below), len); idx < size; idx += 1u << len) fast[idx] = e;
     }
     DPI_SYNC();
 }
 
-/* One symbol as a table entry (format above): a lookup when the code is short and enough input is buffered, else the walk. */
-DPI_FN uint32_t dpi_symbol(dpi_stream *s, const uint32_t *fast, const uint16_t *count, const uint16_t *symbol, int is_dist)
-{
-    const uint32_t e = fast[(uint32_t)s->bitbuf & (DPI_FAST_SIZE - 1)];
-    const int len = (int)(e & 15u);
-    if (e && len <= s->bitcnt) {
-        s->bitbuf >>= len;
-        s->bitcnt -= len;
-        return e;
-    }
-    const int sym = dpi_decode(s, count, symbol);
-    if (sym < 0) { s->err = sym; return 0; }
-    const uint32_t w = dpi_entry(sym, 1, is_dist);
-    if (!w) s->err = DPI_E_SYMBOL;
-    return w;
-}
-
-/* Output goes through a batch of up to DPI_LANES PENDING bytes kept in registers -- lane i holds the i-th pending byte --
- * and leaves with ONE store instruction per batch (consecutive bytes, a 32-byte run per warp instruction instead of
- * single-byte stores by lane 0).  Literals append one byte; a match of distance >= DPI_LANES appends its bytes too: the
- * lanes that receive them load them from the already written output (consecutive addresses; such a source never lies in
- * the pending batch).  Only matches closer than DPI_LANES -- whose source may be pending or may be the match itself -- flush
- * the batch and copy directly.  `dirty` remembers that this warp stored since the lanes last synchronised, so that a
- * source byte written by another lane is ordered before its load. */
-#define DPI_FLUSH_LITERALS()                                                        \
-    do {                                                                            \
-        if (DPI_LANE < run) s->out[s->out_pos - run + DPI_LANE] = mylit;            \
-        if (run) dirty = 1;                                                         \
-        run = 0;                                                                    \
-        cap = DPI_LANES;                                                            \
+/* Output goes through a batch of DPI_LANES PENDING bytes kept in registers -- lane i holds slot i -- and leaves with ONE
+ * store instruction per batch (a 32-byte run per warp instruction instead of single-byte stores).  Batches cover aligned
+ * DPI_LANES-byte pieces of the output (the L2 never has to fill a partly written sector from DRAM): where the output
+ * position is not aligned, the first `skip` slots of the batch are dead.
+ *   - a literal writes its byte into the slot: myval = byte (< 256);
+ *   - a match of distance >= DPI_LANES only NOTES its distance in its slots: myval = dist << 8.  Its source bytes lie
+ *     behind the batch (slot j reads out[j - dist]), so they are fetched when the batch is closed: one load instruction
+ *     for all the matches of a batch, issued after the previous batch has been stored;
+ *   - the loaded bytes are stored one batch LATER (`p*` below is the closed batch in flight): the load's latency -- an L2
+ *     round trip -- overlaps the decoding of the next 32 bytes instead of stalling every match;
+ *   - only matches closer than DPI_LANES -- whose source may be pending or may be the match itself -- drain both batches and
+ *     copy directly.
+ * The output bound is checked when a batch is closed.
+ *     base  output position of slot 0 (may be negative by `skip` at the very start)
+ *     run   slots in use, dead ones included;  room = out_cap - base;  optr = out + base + lane */
+#define DPI_REALIGN(pos)                                                                   \
+    do {                                                                                   \
+        skip = (uint32_t)((uintptr_t)(s->out + (pos)) & (DPI_LANES - 1u));                 \
+        base = (int32_t)(pos) - (int32_t)skip;                                             \
+        run = skip;                                                                        \
+        room = s->out_cap - (uint32_t)base;                                                \
+        optr = s->out + base + (int32_t)DPI_LANE;                                          \
     } while (0)
-/* The first batch of a stream is cut so that it ENDS on a DPI_LANES-byte boundary: every later batch then covers one aligned
- * 32-byte sector and the L2 never has to fill a partly written sector from DRAM. */
-#define DPI_FIRST_CAP(p) (DPI_LANES - (uint32_t)((uintptr_t)(p) & (DPI_LANES - 1u)))
+/* store the batch in flight (a no-op range when there is none) and order the stores before the loads that follow */
+#define DPI_RETIRE()                                                                       \
+    do {                                                                                   \
+        if (DPI_LANE - pskip < prun - pskip) *pptr = (uint8_t)pval;                        \
+        prun = pskip = 0;                                                                  \
+        DPI_SYNC();                                                                        \
+    } while (0)
+/* close slots [skip, upto) of the current batch: it becomes the batch in flight, its match bytes being loaded */
+#define DPI_CLOSE(upto)                                                                    \
+    do {                                                                                   \
+        DPI_RETIRE();                                                                      \
+        pval = myval; pptr = optr; pskip = skip; prun = (upto);                            \
+        if (myval >= 256u && DPI_LANE - skip < (upto) - skip) pval = *(optr - (myval >> 8)); \
+    } while (0)
+#define DPI_LEAVE(code)                                                                    \
+    do {                                                                                   \
+        uint32_t ok_ = run < room ? run : room;                                            \
+        if (ok_ < skip) ok_ = skip;                                                        \
+        DPI_CLOSE(ok_);                                                                    \
+        DPI_RETIRE();                                                                      \
+        s->out_pos = (uint32_t)(base + (int32_t)ok_);                                      \
+        return (run > room && (code) == DPI_OK) ? DPI_E_OUTPUT : (code);                   \
+    } while (0)
+#define DPI_FLUSH()                                                                        \
+    do {                                                                                   \
+        if (run > room) DPI_LEAVE(DPI_E_OUTPUT);                                           \
+        DPI_CLOSE(run);                                                                    \
+        optr += run; base += (int32_t)run; room -= run;                                    \
+        run = 0; skip = 0;                                                                 \
+    } while (0)
 
 DPI_FN int dpi_codes(dpi_stream *s, const uint32_t *fast, const uint32_t *dfast, const uint16_t *lcnt, const uint16_t *lsym,
                      const uint16_t *dcnt, const uint16_t *dsym)
 {
-    uint32_t run = 0;                                            /* bytes decoded but not yet stored */
-    uint32_t cap = DPI_FIRST_CAP(s->out + s->out_pos);           /* bytes the current batch takes */
-    uint32_t dirty = 0;
-    uint8_t mylit = 0;
+    uint32_t skip, run, room, myval = 0;
+    uint32_t pskip = 0, prun = 0, pval = 0;
+    int32_t base;
+    uint8_t *optr, *pptr = s->out;
+    DPI_REALIGN(s->out_pos);
     for (;;) {
-        if (s->bitcnt < 20) dpi_refill(s);                       /* a literal/length code (<= 15 bits) + its extra bits (<= 5) */
-        const uint32_t e = dpi_symbol(s, fast, lcnt, lsym, 0);
-        const uint32_t kind = e >> 24;
-        if (kind == DPI_K_LITERAL) {
-            if (s->out_pos >= s->out_cap) { DPI_FLUSH_LITERALS(); return DPI_E_OUTPUT; }
-            if (DPI_LANE == run) mylit = (uint8_t)(e >> 8);
-            run++;
-            s->out_pos++;
-            if (run == cap) DPI_FLUSH_LITERALS();
-        } else if (kind == DPI_K_BASE) {
-            uint32_t len = ((e >> 8) & 0xffffu) + dpi_bits(s, (int)((e >> 4) & 15u));
-            if (s->bitcnt < 28) dpi_refill(s);                   /* a distance code (<= 15 bits) + its extra bits (<= 13) */
-            const uint32_t de = dpi_symbol(s, dfast, dcnt, dsym, 1);
-            if (!de) { DPI_FLUSH_LITERALS(); return s->err ? s->err : DPI_E_SYMBOL; }
-            const uint32_t dist = ((de >> 8) & 0xffffu) + dpi_bits(s, (int)((de >> 4) & 15u));
-            if (s->err) { DPI_FLUSH_LITERALS(); return s->err; }
-            if (dist > s->out_pos) { DPI_FLUSH_LITERALS(); return DPI_E_DISTANCE; }
-            if (s->out_pos + len > s->out_cap) { DPI_FLUSH_LITERALS(); return DPI_E_OUTPUT; }
-            if (dist >= DPI_LANES) {
-                /* every source byte is already in memory: out_pos + k - dist < out_pos - run for k < DPI_LANES - run */
-                if (dirty) { DPI_SYNC(); dirty = 0; }
-                while (len) {
-                    const uint32_t n = len < cap - run ? len : cap - run;
-                    if (DPI_LANE >= run && DPI_LANE < run + n) mylit = s->out[s->out_pos + (DPI_LANE - run) - dist];
-                    run += n;
-                    s->out_pos += n;
-                    len -= n;
-                    if (run == cap) {
-                        DPI_FLUSH_LITERALS();
-                        if (len && dist < 2 * DPI_LANES) { DPI_SYNC(); dirty = 0; }   /* the next piece may read this batch */
-                    }
-                }
-            } else {
-                DPI_FLUSH_LITERALS();
-                uint8_t *d = s->out + s->out_pos;
-                const uint8_t *f = d - dist;
-                DPI_SYNC();
-                if (dist >= len) {
-                    for (uint32_t i = DPI_LANE; i < len; i += DPI_LANES) d[i] = f[i];
-                } else {                                         /* the match overlaps itself: its first `dist` bytes repeat */
-                    for (uint32_t i = DPI_LANE; i < len; i += DPI_LANES) d[i] = f[i % dist];
-                }
-                dirty = 1;
-                s->out_pos += len;
-                cap = DPI_FIRST_CAP(s->out + s->out_pos);        /* re-align the batches behind the direct copy */
+        if (DPI_UNLIKELY(s->bitcnt < 20)) dpi_refill(s);         /* a literal/length code (<= 15 bits) + its extra bits (<= 5) */
+        uint32_t e = fast[(uint32_t)s->bitbuf & (DPI_LSIZE - 1)];
+        dpi_drop(s, e & 0xffu);
+    dispatch:
+        if (DPI_LIKELY((int32_t)e < 0)) {                        /* a literal */
+            if (DPI_LANE == run) myval = (e >> 16) & 0xffu;
+            if (DPI_UNLIKELY(++run == DPI_LANES)) DPI_FLUSH();
+            continue;
+        }
+        if (DPI_UNLIKELY(e & DPI_F_SPECIAL)) {
+            if (e & 0xffu) DPI_LEAVE(DPI_OK);                    /* end of block */
+            const int sym = dpi_decode(s, lcnt, lsym);           /* a miss: the walk */
+            if (sym < 0) DPI_LEAVE(sym);
+            if (sym == 256) DPI_LEAVE(DPI_OK);
+            e = dpi_entry(sym, 0, 0);
+            if (!e) DPI_LEAVE(DPI_E_SYMBOL);
+            goto dispatch;
+        }
+        const uint32_t lx = (e >> 8) & 0xffu;                    /* a match: length, then distance */
+        uint32_t len = (e >> 16) + dpi_low_bits((uint32_t)s->bitbuf, lx);
+        dpi_drop(s, lx);
+        if (DPI_UNLIKELY(s->bitcnt < 28)) dpi_refill(s);         /* a distance code (<= 15 bits) + its extra bits (<= 13) */
+        uint32_t de = dfast[(uint32_t)s->bitbuf & (DPI_DSIZE - 1)];
+        if (DPI_UNLIKELY(!de)) {
+            const int sym = dpi_decode(s, dcnt, dsym);
+            if (sym < 0) DPI_LEAVE(sym);
+            de = dpi_entry(sym, 0, 1);
+            if (!de) DPI_LEAVE(DPI_E_SYMBOL);
+        }
+        dpi_drop(s, de & 0xffu);
+        const uint32_t dx = (de >> 8) & 0xffu;
+        const uint32_t dist = (de >> 16) + dpi_low_bits((uint32_t)s->bitbuf, dx);
+        dpi_drop(s, dx);
+        if (DPI_UNLIKELY(dist > (uint32_t)(base + (int32_t)run))) DPI_LEAVE(DPI_E_DISTANCE);
+        if (DPI_LIKELY(dist >= DPI_LANES)) {
+            for (;;) {
+                const uint32_t n = len < DPI_LANES - run ? len : DPI_LANES - run;
+                if (DPI_LANE - run < n) myval = dist << 8;
+                run += n;
+                len -= n;
+                if (run == DPI_LANES) DPI_FLUSH();
+                if (!len) break;
             }
-        } else if (kind == DPI_K_END) {
-            DPI_FLUSH_LITERALS();
-            return DPI_OK;
-        } else {                                                 /* no code matches / illegal symbol / input exhausted */
-            DPI_FLUSH_LITERALS();
-            return s->err ? s->err : DPI_E_SYMBOL;
+        } else {
+            DPI_FLUSH();                                         /* run = 0: base is the output position */
+            DPI_RETIRE();
+            if (len > room) DPI_LEAVE(DPI_E_OUTPUT);
+            uint8_t *d = s->out + base;
+            const uint8_t *f = d - dist;
+            if (dist >= len) {
+                for (uint32_t i = DPI_LANE; i < len; i += DPI_LANES) d[i] = f[i];
+            } else {                                             /* the match overlaps itself: its first `dist` bytes repeat */
+                for (uint32_t i = DPI_LANE; i < len; i += DPI_LANES) d[i] = f[i % dist];
+            }
+            DPI_SYNC();
+            DPI_REALIGN((uint32_t)base + len);
         }
     }
 }
 
-/* Inflate one raw DEFLATE stream.  scratch: DPI_SCRATCH_U16 uint16.  Returns DPI_OK or a DPI_E_* code;
+/* Inflate one raw DEFLATE stream.  scratch: DPI_SCRATCH_U16 uint16, 4-byte aligned.  Returns DPI_OK or a DPI_E_* code;
  * *out_len = bytes written. */
 DPI_FN int dpi_inflate(const uint8_t *in, uint32_t in_len, uint8_t *out, uint32_t out_cap, uint16_t *scratch,
                        uint32_t *out_len)
 {
     dpi_stream st;
-    st.in = in; st.in_len = in_len; st.in_pos = 0; st.bitbuf = 0; st.bitcnt = 0;
-    st.out = out; st.out_cap = out_cap; st.out_pos = 0; st.err = 0;
+    st.in = in; st.in_len = in_len;
+    st.head = (uint32_t)((uintptr_t)in & 3u);
+    if (in_len == 0) { *out_len = 0; return DPI_E_INPUT; }
+    st.in_last = (st.head + in_len - 1u) >> 2;
+    st.out = out; st.out_cap = out_cap; st.out_pos = 0;
+    dpi_seek(&st, 0);
     uint16_t *lcnt = scratch, *lsym = lcnt + 16, *dcnt = lsym + DPI_NLEN, *dsym = dcnt + 16;
     uint8_t *lengths = (uint8_t *)(dsym + DPI_NDIST);
-    uint32_t *fast = (uint32_t *)(scratch + ((DPI_SLOW_U16 + 1) & ~1)), *dfast = fast + DPI_FAST_SIZE;
+    uint32_t *fast = (uint32_t *)(scratch + ((DPI_SLOW_U16 + 1) & ~1)), *dfast = fast + DPI_LSIZE;
     int last, rc = DPI_OK;
     do {
         last = (int)dpi_bits(&st, 1);
-        int type = (int)dpi_bits(&st, 2);
-        if (st.err) { rc = st.err; break; }
+        const int type = (int)dpi_bits(&st, 2);
         if (type == 0) {
-            st.in_pos -= (uint32_t)st.bitcnt >> 3;               /* whole bytes the table lookup read ahead go back */
-            st.bitbuf = 0; st.bitcnt = 0;                         /* skip to the byte boundary */
-            if (st.in_pos + 4 > st.in_len) { rc = DPI_E_INPUT; break; }
-            uint32_t len = st.in[st.in_pos] | ((uint32_t)st.in[st.in_pos + 1] << 8);
-            uint32_t nlen = st.in[st.in_pos + 2] | ((uint32_t)st.in[st.in_pos + 3] << 8);
-            st.in_pos += 4;
+            dpi_drop(&st, st.bitcnt & 7u);                       /* skip to the byte boundary */
+            const uint32_t len = dpi_bits(&st, 16), nlen = dpi_bits(&st, 16);
+            if (dpi_exhausted(&st)) { rc = DPI_E_INPUT; break; }
             if ((len ^ 0xffffu) != nlen) { rc = DPI_E_STORED; break; }
-            if (st.in_pos + len > st.in_len) { rc = DPI_E_INPUT; break; }
-            if (st.out_pos + len > st.out_cap) { rc = DPI_E_OUTPUT; break; }
-            for (uint32_t i = DPI_LANE; i < len; i += DPI_LANES) st.out[st.out_pos + i] = st.in[st.in_pos + i];
-            st.in_pos += len; st.out_pos += len;
+            const uint32_t at = dpi_byte_pos(&st);
+            if (at + len > in_len) { rc = DPI_E_INPUT; break; }
+            if (st.out_pos + len > out_cap) { rc = DPI_E_OUTPUT; break; }
+            for (uint32_t i = DPI_LANE; i < len; i += DPI_LANES) out[st.out_pos + i] = in[at + i];
+            DPI_SYNC();
+            st.out_pos += len;
+            dpi_seek(&st, at + len);
         } else if (type == 1) {
             int i = 0;
-            for (; i < 144; ++i) lengths[i] = 8;
-            for (; i < 256; ++i) lengths[i] = 9;
-            for (; i < 280; ++i) lengths[i] = 7;
-            for (; i < DPI_NLEN; ++i) lengths[i] = 8;
+            DPI_SYNC();
+            if (DPI_LANE == 0) {
+                for (; i < 144; ++i) lengths[i] = 8;
+                for (; i < 256; ++i) lengths[i] = 9;
+                for (; i < 280; ++i) lengths[i] = 7;
+                for (; i < DPI_NLEN; ++i) lengths[i] = 8;
+            }
             dpi_build(lcnt, lsym, lengths, DPI_NLEN);
-            dpi_build_fast(fast, lcnt, lengths, DPI_NLEN, 0);
-            for (i = 0; i < DPI_NDIST; ++i) lengths[i] = 5;
+            dpi_build_fast(fast, DPI_LBITS, lcnt, lsym, DPI_NLEN, 0);
+            if (DPI_LANE == 0)
+                for (i = 0; i < DPI_NDIST; ++i) lengths[i] = 5;
             dpi_build(dcnt, dsym, lengths, DPI_NDIST);
-            dpi_build_fast(dfast, dcnt, lengths, DPI_NDIST, 1);
+            dpi_build_fast(dfast, DPI_DBITS, dcnt, dsym, DPI_NDIST, 1);
             rc = dpi_codes(&st, fast, dfast, lcnt, lsym, dcnt, dsym);
         } else if (type == 2) {
-            int nlen = (int)dpi_bits(&st, 5) + 257, ndist = (int)dpi_bits(&st, 5) + 1, ncode = (int)dpi_bits(&st, 4) + 4;
-            if (st.err) { rc = st.err; break; }
-            if (nlen > 286 || ndist > DPI_NDIST) { rc = DPI_E_TABLE; break; }
+            const int nlen = (int)dpi_bits(&st, 5) + 257, ndist = (int)dpi_bits(&st, 5) + 1, ncode = (int)dpi_bits(&st, 4) + 4;
+            if (nlen > 286 || ndist > DPI_NDIST) { rc = dpi_exhausted(&st) ? DPI_E_INPUT : DPI_E_TABLE; break; }
             int i;
+            DPI_SYNC();
             for (i = 0; i < 19; ++i) lengths[i] = 0;
             for (i = 0; i < ncode; ++i) lengths[dpi_clen_order[i]] = (uint8_t)dpi_bits(&st, 3);
-            if (st.err) { rc = st.err; break; }
             if (dpi_build(lcnt, lsym, lengths, 19) != 0) { rc = DPI_E_TABLE; break; }   /* code-length code must be complete */
             i = 0;
             while (i < nlen + ndist) {
-                int sym = dpi_decode(&st, lcnt, lsym);
+                const int sym = dpi_decode(&st, lcnt, lsym);
                 if (sym < 0) { rc = sym; break; }
                 if (sym < 16) {
                     lengths[i++] = (uint8_t)sym;
@@ -366,26 +463,27 @@ DPI_FN int dpi_inflate(const uint8_t *in, uint32_t in_len, uint8_t *out, uint32_
                     } else {
                         rep = 11 + (int)dpi_bits(&st, 7);
                     }
-                    if (st.err) { rc = st.err; break; }
                     if (i + rep > nlen + ndist) { rc = DPI_E_TABLE; break; }
                     while (rep--) lengths[i++] = (uint8_t)prev;
                 }
             }
             if (rc != DPI_OK) break;
+            if (dpi_exhausted(&st)) { rc = DPI_E_INPUT; break; }
             if (lengths[256] == 0) { rc = DPI_E_TABLE; break; }                         /* no end-of-block code */
             /* the distance lengths must be read before lsym is overwritten: build the distance code first, from a copy
              * position that dpi_build of the literal code does not touch (lengths[] is separate from both tables) */
             int e = dpi_build(dcnt, dsym, lengths + nlen, ndist);
             if (e < 0 || (e > 0 && ndist - dcnt[0] != 1)) { rc = DPI_E_TABLE; break; }
-            dpi_build_fast(dfast, dcnt, lengths + nlen, ndist, 1);
+            dpi_build_fast(dfast, DPI_DBITS, dcnt, dsym, ndist, 1);
             e = dpi_build(lcnt, lsym, lengths, nlen);
             if (e < 0 || (e > 0 && nlen - lcnt[0] != 1)) { rc = DPI_E_TABLE; break; }
-            dpi_build_fast(fast, lcnt, lengths, nlen, 0);
+            dpi_build_fast(fast, DPI_LBITS, lcnt, lsym, nlen, 0);
             rc = dpi_codes(&st, fast, dfast, lcnt, lsym, dcnt, dsym);
         } else {
             rc = DPI_E_BTYPE;
         }
     } while (rc == DPI_OK && !last);
+    if (dpi_exhausted(&st)) rc = DPI_E_INPUT;
     *out_len = st.out_pos;
     return rc;
 }

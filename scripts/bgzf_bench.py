@@ -21,6 +21,7 @@ from deepore_b200 import _lib, bamdev, synth  # noqa: E402
 ap = argparse.ArgumentParser()
 ap.add_argument("--kb", type=int, default=1500, help="reference length in kb (30x coverage of it is simulated)")
 ap.add_argument("--reps", type=int, default=5)
+ap.add_argument("--sweep", action="store_true", help="only time the inflate kernel over growing prefixes of the block list")
 args = ap.parse_args()
 
 ref = synth.random_reference(args.kb * 1000, seed=1)
@@ -53,6 +54,16 @@ def timed(fn):
     return float(np.median(ms))
 
 
+if args.sweep:
+    rows = []
+    for nb in sorted({int(n * f) for f in (0.02, 0.05, 0.1, 0.2, 0.35, 0.5, 0.65, 0.8, 0.9, 1.0)} | {148 * 4 * k for k in (1, 4, 8, 9, 10) if 148 * 4 * k <= n}):
+        def part(nb=nb):
+            _lib.check(L.dp_bgzf_inflate(d_file.data_ptr(), nb, dd["in_off"].data_ptr(), dd["in_len"].data_ptr(), dd["out_off"].data_ptr(),
+                                         dd["out_len"].data_ptr(), out.data_ptr(), status.data_ptr(), C.c_void_p(st.cuda_stream)), "inflate")
+        ms = timed(part)
+        rows.append({"blocks": nb, "ms": round(ms, 3), "out_GBps": round(float(idx["out_len"][:nb].sum()) / ms / 1e6, 2)})
+    print(json.dumps({"sweep": rows}))
+    raise SystemExit(0)
 ms_inf = timed(inflate)
 assert not status.cpu().numpy().any() and out.cpu().numpy().tobytes() == data
 ms_rec = timed(lambda: bamdev.records_on_device(out, "chr3"))      # the Python wrapper: allocations, the count read-back, slices

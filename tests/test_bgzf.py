@@ -15,9 +15,8 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 
 def _host_inflate():
     so = os.path.join(HERE, "..", "oracle", "_ref", "libinflate_host.so")
-    if not os.path.isfile(so):
-        import subprocess
-        subprocess.check_call(["make", "-C", os.path.join(HERE, "..", "oracle"), "-s"])
+    import subprocess
+    subprocess.check_call(["make", "-C", os.path.join(HERE, "..", "oracle"), "-s"])      # mtime-aware: rebuilds after a core edit
     L = ctypes.CDLL(so)
     L.dpo_inflate.restype = ctypes.c_int
     L.dpo_inflate.argtypes = [ctypes.c_char_p, ctypes.c_uint32, ctypes.c_char_p, ctypes.c_uint32,
