@@ -103,6 +103,8 @@ def lib():
     L.dp_bgzf_inflate.argtypes = [C.c_void_p, C.c_int64] + [C.c_void_p] * 7
     L.dp_bam_scan.restype = C.c_int
     L.dp_bam_scan.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_int32, C.c_int64] + [C.c_void_p] * 6
+    L.dp_bam_scan_static.restype = C.c_int
+    L.dp_bam_scan_static.argtypes = L.dp_bam_scan.argtypes
     L.dp_bam_extract.restype = C.c_int
     L.dp_bam_extract.argtypes = [C.c_void_p, C.c_int64] + [C.c_void_p] * 12
     L.dp_png_size.restype = C.c_int64

@@ -17,6 +17,8 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <mutex>
+
 #include "../../include/deepore_b200.h"
 #include "common.cuh"
 #include "inflate_core.h"
@@ -502,6 +504,71 @@ int dp_bam_scan(const uint8_t *bam, int64_t n_bytes, const char *contig, int32_t
     cudaError_t le = cudaGetLastError();
     cudaFreeAsync(scratch, st);
     if (le != cudaSuccess) { dp::set_error("dp_bam_scan: %s", cudaGetErrorString(le)); return DP_ECUDA; }
+    return DP_OK;
+}
+
+// dp_bam_scan for callers that must not allocate (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc):
+// the same five launches, with the segment scratch in a file-scope device array instead of cudaMallocAsync memory.
+// The array is sized for the scan's own ceiling of SCAN_MAXSEG segments (98 384 bytes; every GPU that loads the library
+// holds it until exit), and the input is capped at DP_BAM_SCAN_STATIC_MAX_BYTES so that a segment stays <= 512 KB.
+// ALL calls on a device share the array: two calls that overlap on the GPU (different streams, no ordering) race.
+// Nothing in it has to start at zero -- the header kernel writes hdr, the segment kernel every segment it is asked for,
+// the link kernel link[0] -- the header words are cleared anyway so that a call never sees the previous call's.
+static __device__ __align__(256) uint8_t g_scan_static[80 + sizeof(ScanSeg) * SCAN_MAXSEG];
+
+static int scan_static_address(uint8_t **out)
+{
+    // the array's name is a host-side stand-in here, not a device address: resolved once per device, that device current
+    static std::mutex mu;
+    static uint8_t *ptr[64] = {nullptr};
+    int dev = 0;
+    DP_CUDA_CHECK(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) { dp::set_error("dp_bam_scan_static: device ordinal %d out of range", dev); return DP_EINVAL; }
+    std::lock_guard<std::mutex> lock(mu);
+    if (!ptr[dev]) {
+        uint8_t *p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress((void **)&p, g_scan_static);
+        if (e != cudaSuccess || !p) {
+            dp::set_error("dp_bam_scan_static: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+            return DP_ECUDA;
+        }
+        ptr[dev] = p;
+    }
+    *out = ptr[dev];
+    return DP_OK;
+}
+
+int dp_bam_scan_static(const uint8_t *bam, int64_t n_bytes, const char *contig, int32_t contig_len, int64_t max_records,
+                       int64_t *rec_off, int64_t *cigar_off, int64_t *seq_off, int64_t *qual_off, int64_t *counts, void *stream)
+{
+    if (!bam || !rec_off || !cigar_off || !seq_off || !qual_off || !counts || max_records < 0 || (contig_len > 0 && !contig)) {
+        dp::set_error("dp_bam_scan_static: null argument");
+        return DP_EINVAL;
+    }
+    if (n_bytes < 0 || n_bytes > DP_BAM_SCAN_STATIC_MAX_BYTES) {
+        dp::set_error("dp_bam_scan_static: %lld bytes exceed the static scratch's limit of %lld (use dp_bam_scan)",
+                      (long long)n_bytes, (long long)DP_BAM_SCAN_STATIC_MAX_BYTES);
+        return DP_EINVAL;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    int64_t seg_bytes = 65536;
+    while ((n_bytes + seg_bytes - 1) / seg_bytes > SCAN_MAXSEG) seg_bytes *= 2;
+    const int n_seg = (int)((n_bytes + seg_bytes - 1) / seg_bytes) > 0 ? (int)((n_bytes + seg_bytes - 1) / seg_bytes) : 1;
+    uint8_t *scratch = nullptr;
+    int rc = scan_static_address(&scratch);
+    if (rc != DP_OK) return rc;
+    DP_CUDA_CHECK(cudaMemsetAsync(scratch, 0, 80, st));
+    int64_t *hdr = (int64_t *)scratch;
+    int *link = (int *)(scratch + 64);
+    ScanSeg *segs = (ScanSeg *)(scratch + 80);
+    bam_header_kernel<<<1, 32, 0, st>>>(bam, n_bytes, contig, contig_len, hdr);
+    bam_seg_kernel<<<(n_seg + 3) / 4, 128, 0, st>>>(bam, n_bytes, seg_bytes, n_seg, hdr, segs);
+    bam_link_kernel<<<1, 1024, 0, st>>>(n_bytes, seg_bytes, n_seg, hdr, segs, max_records, counts, link, cigar_off, seq_off, qual_off);
+    bam_emit_kernel<<<(n_seg + 127) / 128, 128, 0, st>>>(bam, n_bytes, seg_bytes, n_seg, hdr, segs, link, max_records, rec_off,
+                                                         cigar_off, seq_off, qual_off, counts);
+    bam_scan_kernel<<<1, 32, 0, st>>>(bam, n_bytes, contig, contig_len, max_records, rec_off, cigar_off, seq_off, qual_off, counts,
+                                      link);                     // runs only when a link of the proof failed
+    DP_CUDA_CHECK(cudaGetLastError());
     return DP_OK;
 }
 

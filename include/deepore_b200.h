@@ -259,6 +259,16 @@ int dp_bgzf_inflate(const uint8_t *file, int64_t n_blocks, const int64_t *in_off
 int dp_bam_scan(const uint8_t *bam, int64_t n_bytes, const char *contig, int32_t contig_len, int64_t max_records,
                 int64_t *rec_off, int64_t *cigar_off, int64_t *seq_off, int64_t *qual_off, int64_t *counts, void *stream);
 
+/* dp_bam_scan_static -- dp_bam_scan (same arguments, same results) for callers that must not allocate: code under CUDA
+ * graph capture, serving loops, harnesses that forbid cudaMalloc.  No counterpart in the reference.
+ * The segment scratch is a file-scope device array (98 384 bytes per GPU that loads the library,
+ * held until exit) instead of stream-ordered pool memory; the call allocates and frees nothing.  n_bytes above
+ * DP_BAM_SCAN_STATIC_MAX_BYTES is rejected with DP_EINVAL (use dp_bam_scan).  All calls on one device share the array:
+ * calls that overlap on the GPU (different streams without ordering) race -- order them on one stream or with events. */
+#define DP_BAM_SCAN_STATIC_MAX_BYTES ((int64_t)1 << 30)
+int dp_bam_scan_static(const uint8_t *bam, int64_t n_bytes, const char *contig, int32_t contig_len, int64_t max_records,
+                       int64_t *rec_off, int64_t *cigar_off, int64_t *seq_off, int64_t *qual_off, int64_t *counts, void *stream);
+
 /* dp_bam_extract -- DEVICE pointers: fills the dp_reads arrays of the n_records records found by dp_bam_scan. */
 int dp_bam_extract(const uint8_t *bam, int64_t n_records, const int64_t *rec_off, const int64_t *cigar_off,
                    const int64_t *seq_off, const int64_t *qual_off, int32_t *pos, uint16_t *flag, uint8_t *mapq,
