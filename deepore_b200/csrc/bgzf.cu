@@ -25,14 +25,23 @@
 
 namespace {
 
-constexpr int INFLATE_WARPS = 4;                                     // BGZF blocks per CTA: one per warp
+#ifndef INFLATE_WARPS_PER_CTA
+#define INFLATE_WARPS_PER_CTA 4
+#endif
+constexpr int INFLATE_WARPS = INFLATE_WARPS_PER_CTA;                                     // BGZF blocks per CTA: one per warp
 constexpr int INFLATE_STRIDE_U16 = (DPI_SCRATCH_U16 + 2 + 7) & ~7;   // per-warp scratch stays 16-byte aligned, banks staggered by the +2
 
 // One BGZF block per WARP.  A thread per block inside one warp (the first version) diverges on every symbol -- 32
 // different streams serialised on one warp scheduler: 0.21 GB/s on the bench file, the speed of ONE host core.  Here the 32
 // lanes of a warp run the same decoder in lock step on the same stream (no divergence) and split only the output bytes of
 // matches and stored blocks between them (inflate_core.h).
+// no launch bound: ptxas settles on 48 registers by itself; a bound that only RESTATES 48 (128 threads, 10 CTAs) made it
+// recompute the stream's word base at every window slide (+25 % time), and a looser one takes 62 registers
+#ifdef INFLATE_MIN_CTAS
+__global__ void __launch_bounds__(INFLATE_WARPS * 32, INFLATE_MIN_CTAS)
+#else
 __global__ void
+#endif
 bgzf_inflate_kernel(const uint8_t *__restrict__ file, int64_t n_blocks, const int64_t *__restrict__ in_off,
                     const int32_t *__restrict__ in_len, const int64_t *__restrict__ out_off,
                     const int32_t *__restrict__ out_len, uint8_t *out, int32_t *__restrict__ status)

@@ -61,8 +61,12 @@
  *     end-of-block code when the code length is non-zero, else a miss (code longer than DPI_LBITS, or an illegal symbol);
  * distance table (DPI_DBITS index bits): 0 is a miss.
  * A miss consumes nothing and goes to the count/first-code walk, which also reports the errors. */
+#ifndef DPI_LBITS
 #define DPI_LBITS 10
+#endif
+#ifndef DPI_DBITS
 #define DPI_DBITS 8
+#endif
 #define DPI_LSIZE (1 << DPI_LBITS)
 #define DPI_DSIZE (1 << DPI_DBITS)
 #define DPI_F_LITERAL 0x80000000u
@@ -82,30 +86,35 @@ DPI_CONST uint8_t dpi_dist_extra[30] = {0, 0, 0, 0, 1, 1, 2, 2, 3, 3, 4, 4, 5, 5
 DPI_CONST uint8_t dpi_clen_order[19] = {16, 17, 18, 0, 8, 7, 9, 6, 10, 5, 11, 4, 12, 3, 13, 2, 14, 1, 15};
 
 /* The bit reader works on the aligned 32-bit words that cover [in, in + in_len): `head` = in & 3 bytes of the first word
- * precede the stream and are dropped at the start.  Past the last word that holds a stream byte that word repeats, so the
- * hot loop never tests for the end of the input: a stream that runs out keeps decoding those bits until it ends, errs or fills
- * the output (all bounded), and dpi_exhausted() -- consumed bits > stream bits -- turns that into DPI_E_INPUT afterwards.
- * Nothing outside the words that hold at least one stream byte is ever read. */
+ * precede the stream and are skipped at the start.  It keeps a WINDOW of two words (lo, hi) and the bit position `pos`
+ * inside it: nothing is shifted per symbol -- a peek is one funnel shift of the window by pos, consuming a code is an
+ * addition to pos -- and when pos passes 32 the window slides by one word (two moves).  The word behind the window is
+ * loaded one slide early (`ahead`), so the load's latency is off the decoding chain.  Past the last word that holds a
+ * stream byte that word repeats, so the hot loop never tests for the end of the input: a stream that runs out keeps decoding
+ * those bits until it ends, errs or fills the output (all bounded), and dpi_exhausted() -- consumed bits > stream bits --
+ * turns that into DPI_E_INPUT afterwards.  Nothing outside the words that hold at least one stream byte is ever read. */
 typedef struct dpi_stream {
     const uint8_t *in;        /* the stream itself (not aligned) */
     uint32_t in_len;
     uint32_t head;            /* in & 3 */
     uint32_t in_last;         /* last aligned word that holds a stream byte */
-    uint32_t in_pos;          /* next word to go into the reservoir */
-    uint32_t ahead;           /* that word, loaded one refill early: its latency is off the decoding chain */
-    uint64_t bitbuf;          /* LSB-first bit reservoir */
-    uint32_t bitcnt;
+    uint32_t in_pos;          /* index of the word in `ahead`; the window holds words in_pos - 2 and in_pos - 1 */
+    uint32_t lo, hi, ahead;
+    uint32_t pos;             /* next unread bit of the window; < 32 after dpi_slide */
     uint8_t *out;
     uint32_t out_cap, out_pos;
 } dpi_stream;
 
 #ifdef __CUDACC__
 #define DPI_LOAD_WORD(s, i) (((const uint32_t *)((s)->in - (s)->head))[i])
-DPI_FN uint32_t dpi_low_bits(uint32_t v, uint32_t n)     /* the low n (< 32) bits of v: a bit-mask instruction and an AND */
+/* wrap-mode shifts and masks: only the low 5 bits of the count operand are used, so a count may carry other fields above */
+#define DPI_PEEK(lo, hi, n)  __funnelshift_r((lo), (hi), (n))          /* 32 bits of hi:lo from bit (n & 31) */
+#define DPI_SHR(v, n)        __funnelshift_r((v), 0u, (n))             /* v >> (n & 31) */
+DPI_FN uint32_t dpi_mask(uint32_t n)                                   /* (1 << (n & 31)) - 1 */
 {
     uint32_t m;
-    asm("bmsk.clamp.b32 %0, 0, %1;" : "=r"(m) : "r"(n));
-    return v & m;
+    asm("bmsk.wrap.b32 %0, 0, %1;" : "=r"(m) : "r"(n));
+    return m;
 }
 #else
 DPI_FN uint32_t dpi_load_word_host(const dpi_stream *s, uint32_t i)   /* same bytes, assembled without touching a byte outside the stream */
@@ -118,75 +127,79 @@ DPI_FN uint32_t dpi_load_word_host(const dpi_stream *s, uint32_t i)   /* same by
     return w;
 }
 #define DPI_LOAD_WORD(s, i) dpi_load_word_host(s, i)
-DPI_FN uint32_t dpi_low_bits(uint32_t v, uint32_t n) { return v & ((1u << n) - 1u); }
+#define DPI_PEEK(lo, hi, n)  ((uint32_t)(((((uint64_t)(hi)) << 32) | (lo)) >> ((n) & 31u)))
+#define DPI_SHR(v, n)        ((uint32_t)(v) >> ((n) & 31u))
+DPI_FN uint32_t dpi_mask(uint32_t n) { return (1u << (n & 31u)) - 1u; }
 #endif
+#define DPI_WORD_AT(s, i) DPI_LOAD_WORD(s, (i) < (s)->in_last ? (i) : (s)->in_last)
 
-/* Append one word to the reservoir; the caller has seen bitcnt < 32.  Past the end the last word repeats (in_pos keeps
- * counting, which is what dpi_exhausted looks at): no branch, and what the repeated bits decode to never matters. */
-DPI_FN void dpi_refill(dpi_stream *s)
+/* Slide the window word by word until the position is back in its first word. */
+DPI_FN void dpi_slide(dpi_stream *s)
 {
-    const uint32_t w = s->ahead;
-    s->in_pos++;
-    s->ahead = DPI_LOAD_WORD(s, s->in_pos < s->in_last ? s->in_pos : s->in_last);
-    s->bitbuf |= (uint64_t)w << s->bitcnt;
-    s->bitcnt += 32;
-}
-
-DPI_FN void dpi_drop(dpi_stream *s, uint32_t n)          /* n <= bitcnt */
-{
-    s->bitbuf >>= n;
-    s->bitcnt -= n;
+    while (s->pos >= 32u) {
+        s->lo = s->hi;
+        s->hi = s->ahead;
+        s->in_pos++;
+        s->ahead = DPI_WORD_AT(s, s->in_pos);
+        s->pos -= 32u;
+    }
 }
 
 /* Take `need` (<= 16) bits. */
 DPI_FN uint32_t dpi_bits(dpi_stream *s, uint32_t need)
 {
-    if (s->bitcnt < 32) dpi_refill(s);
-    const uint32_t v = dpi_low_bits((uint32_t)s->bitbuf, need);
-    dpi_drop(s, need);
+    dpi_slide(s);
+    const uint32_t v = DPI_PEEK(s->lo, s->hi, s->pos) & dpi_mask(need);
+    s->pos += need;
     return v;
 }
 
-/* Position of the next unread bit as a byte offset from `in` (rounded down), and whether more bits were consumed than
- * the stream holds. */
-DPI_FN uint32_t dpi_byte_pos(const dpi_stream *s) { return (s->in_pos * 32u - s->bitcnt) / 8u - s->head; }
-DPI_FN int dpi_exhausted(const dpi_stream *s)
-{
-    return (uint64_t)s->in_pos * 32u - s->bitcnt > ((uint64_t)s->head + s->in_len) * 8u;
-}
+/* Bits consumed so far, counted from the first aligned word; the position of the next unread bit as a byte offset from
+ * `in` (rounded down); and whether more bits were consumed than the stream holds. */
+DPI_FN uint64_t dpi_consumed(const dpi_stream *s) { return ((uint64_t)s->in_pos - 2u) * 32u + s->pos; }
+DPI_FN uint32_t dpi_byte_pos(const dpi_stream *s) { return (uint32_t)(dpi_consumed(s) / 8u) - s->head; }
+DPI_FN int dpi_exhausted(const dpi_stream *s) { return dpi_consumed(s) > ((uint64_t)s->head + s->in_len) * 8u; }
 
 /* Continue reading at byte `off` of the stream. */
 DPI_FN void dpi_seek(dpi_stream *s, uint32_t off)
 {
-    const uint32_t at = s->head + off;
-    s->in_pos = at >> 2;
-    s->ahead = DPI_LOAD_WORD(s, s->in_pos < s->in_last ? s->in_pos : s->in_last);
-    s->bitbuf = 0;
-    s->bitcnt = 0;
-    dpi_refill(s);
-    dpi_drop(s, (at & 3u) * 8u);
+    const uint32_t at = s->head + off, w = at >> 2;
+    s->lo = DPI_WORD_AT(s, w);
+    s->hi = DPI_WORD_AT(s, w + 1u);
+    s->ahead = DPI_WORD_AT(s, w + 2u);
+    s->in_pos = w + 2u;
+    s->pos = (at & 3u) * 8u;
 }
 
 /* Canonical code described by count[len] (codes of each length) and symbol[] (symbols ordered by code): the walk behind
- * the lookup tables, and the decoder of the code-length code.  Consumes the code; DPI_E_SYMBOL if no code matches. */
-DPI_FN int dpi_decode(dpi_stream *s, const uint16_t *count, const uint16_t *symbol)
+ * the lookup tables, and the decoder of the code-length code.  `v` = the peeked bits (>= 15 valid); *used = the length of
+ * the code found.  DPI_E_SYMBOL if no code matches. */
+DPI_FN int dpi_walk(uint32_t v, const uint16_t *count, const uint16_t *symbol, uint32_t *used)
 {
-    if (s->bitcnt < 32) dpi_refill(s);
-    uint32_t v = (uint32_t)s->bitbuf;
     int32_t code = 0, first = 0, index = 0;
     for (uint32_t len = 1; len <= DPI_MAXBITS; ++len) {
         code |= (int32_t)(v & 1u);
         v >>= 1;
         const int32_t c = count[len];
         if (code - c < first) {
-            dpi_drop(s, len);
+            *used = len;
             return symbol[index + (code - first)];
         }
         index += c;
         first = (first + c) << 1;
         code <<= 1;
     }
+    *used = 0;
     return DPI_E_SYMBOL;
+}
+
+DPI_FN int dpi_decode(dpi_stream *s, const uint16_t *count, const uint16_t *symbol)
+{
+    dpi_slide(s);
+    uint32_t used;
+    const int sym = dpi_walk(DPI_PEEK(s->lo, s->hi, s->pos), count, symbol, &used);
+    s->pos += used;
+    return sym;
 }
 
 /* Build count[]/symbol[] from code lengths.  Returns 0 for a complete code, > 0 for an incomplete one (allowed only
@@ -272,8 +285,9 @@ DPI_FN void dpi_build_fast(uint32_t *fast, uint32_t bits, const uint16_t *count,
  * store instruction per batch (a 32-byte run per warp instruction instead of single-byte stores).  Batches cover aligned
  * DPI_LANES-byte pieces of the output (the L2 never has to fill a partly written sector from DRAM): where the output
  * position is not aligned, the first `skip` slots of the batch are dead.
- *   - a literal writes its byte into the slot: myval = byte (< 256);
- *   - a match of distance >= DPI_LANES only NOTES its distance in its slots: myval = dist << 8.  Its source bytes lie
+ *   - a literal puts its table entry into the slot (bit 31 set, the byte in bits 16-23: one move, unpacked when the
+ *     batch is closed);
+ *   - a match of distance >= DPI_LANES only NOTES its distance in its slots (bit 31 clear).  Its source bytes lie
  *     behind the batch (slot j reads out[j - dist]), so they are fetched when the batch is closed: one load instruction
  *     for all the matches of a batch, issued after the previous batch has been stored;
  *   - the loaded bytes are stored one batch LATER (`p*` below is the closed batch in flight): the load's latency -- an L2
@@ -302,8 +316,8 @@ DPI_FN void dpi_build_fast(uint32_t *fast, uint32_t bits, const uint16_t *count,
 #define DPI_CLOSE(upto)                                                                    \
     do {                                                                                   \
         DPI_RETIRE();                                                                      \
-        pval = myval; pptr = optr; pskip = skip; prun = (upto);                            \
-        if (myval >= 256u && DPI_LANE - skip < (upto) - skip) pval = *(optr - (myval >> 8)); \
+        pval = (myval >> 16) & 0xffu; pptr = optr; pskip = skip; prun = (upto);            \
+        if ((int32_t)myval >= 0 && DPI_LANE - skip < (upto) - skip) pval = *(optr - myval); \
     } while (0)
 #define DPI_LEAVE(code)                                                                    \
     do {                                                                                   \
@@ -312,6 +326,7 @@ DPI_FN void dpi_build_fast(uint32_t *fast, uint32_t bits, const uint16_t *count,
         DPI_CLOSE(ok_);                                                                    \
         DPI_RETIRE();                                                                      \
         s->out_pos = (uint32_t)(base + (int32_t)ok_);                                      \
+        s->lo = lo; s->hi = hi; s->ahead = ahead; s->in_pos = ipos; s->pos = pacc & 127u; \
         return (run > room && (code) == DPI_OK) ? DPI_E_OUTPUT : (code);                   \
     } while (0)
 #define DPI_FLUSH()                                                                        \
@@ -322,53 +337,77 @@ DPI_FN void dpi_build_fast(uint32_t *fast, uint32_t bits, const uint16_t *count,
         run = 0; skip = 0;                                                                 \
     } while (0)
 
+/* the hot loop keeps the reader in locals; `pacc` is pos with other fields of the added table entries above bit 7 (only
+ * its low bits are ever looked at: bit 5 = "pos >= 32", and the wrap-mode shifts take the low 5) */
+#define DPI_HOT_SLIDE()                                                                    \
+    do {                                                                                   \
+        lo = hi; hi = ahead; ipos++;                                                       \
+        ahead = DPI_LOAD_WORD(s, ipos < s->in_last ? ipos : s->in_last);                   \
+        pacc -= 32u;                                                                       \
+    } while (0)
+
 DPI_FN int dpi_codes(dpi_stream *s, const uint32_t *fast, const uint32_t *dfast, const uint16_t *lcnt, const uint16_t *lsym,
                      const uint16_t *dcnt, const uint16_t *dsym)
 {
-    uint32_t skip, run, room, myval = 0;
+    uint32_t skip, run, room, myval = 0x80000000u;
     uint32_t pskip = 0, prun = 0, pval = 0;
     int32_t base;
     uint8_t *optr, *pptr = s->out;
+    dpi_slide(s);
+    uint32_t lo = s->lo, hi = s->hi, ahead = s->ahead, ipos = s->in_pos, pacc = s->pos;
     DPI_REALIGN(s->out_pos);
     for (;;) {
-        if (DPI_UNLIKELY(s->bitcnt < 20)) dpi_refill(s);         /* a literal/length code (<= 15 bits) + its extra bits (<= 5) */
-        uint32_t e = fast[(uint32_t)s->bitbuf & (DPI_LSIZE - 1)];
-        dpi_drop(s, e & 0xffu);
+        if (DPI_UNLIKELY(pacc & 32u)) DPI_HOT_SLIDE();
+        uint32_t p = DPI_PEEK(lo, hi, pacc);                     /* 32 valid bits: a code (<= 15) and its extra bits (<= 13) */
+        uint32_t e = fast[p & (DPI_LSIZE - 1)];
+        pacc += e;                                               /* the code length sits in the low byte */
     dispatch:
         if (DPI_LIKELY((int32_t)e < 0)) {                        /* a literal */
-            if (DPI_LANE == run) myval = (e >> 16) & 0xffu;
+            if (DPI_LANE == run) myval = e;
             if (DPI_UNLIKELY(++run == DPI_LANES)) DPI_FLUSH();
             continue;
         }
         if (DPI_UNLIKELY(e & DPI_F_SPECIAL)) {
             if (e & 0xffu) DPI_LEAVE(DPI_OK);                    /* end of block */
-            const int sym = dpi_decode(s, lcnt, lsym);           /* a miss: the walk */
+            uint32_t used;
+            const int sym = dpi_walk(p, lcnt, lsym, &used);      /* a miss: the walk */
             if (sym < 0) DPI_LEAVE(sym);
+            pacc += used;
             if (sym == 256) DPI_LEAVE(DPI_OK);
             e = dpi_entry(sym, 0, 0);
             if (!e) DPI_LEAVE(DPI_E_SYMBOL);
+            p >>= used;
             goto dispatch;
         }
-        const uint32_t lx = (e >> 8) & 0xffu;                    /* a match: length, then distance */
-        uint32_t len = (e >> 16) + dpi_low_bits((uint32_t)s->bitbuf, lx);
-        dpi_drop(s, lx);
-        if (DPI_UNLIKELY(s->bitcnt < 28)) dpi_refill(s);         /* a distance code (<= 15 bits) + its extra bits (<= 13) */
-        uint32_t de = dfast[(uint32_t)s->bitbuf & (DPI_DSIZE - 1)];
+        uint32_t t = e >> 8;                                     /* a match: length = base + extra bits, then the distance */
+        uint32_t len = (e >> 16) + (DPI_SHR(p, e) & dpi_mask(t));
+        pacc += t;
+        if (DPI_UNLIKELY(pacc & 32u)) DPI_HOT_SLIDE();
+        p = DPI_PEEK(lo, hi, pacc);
+        uint32_t de = dfast[p & (DPI_DSIZE - 1)];
         if (DPI_UNLIKELY(!de)) {
-            const int sym = dpi_decode(s, dcnt, dsym);
+            uint32_t used;
+            const int sym = dpi_walk(p, dcnt, dsym, &used);
             if (sym < 0) DPI_LEAVE(sym);
+            pacc += used;
             de = dpi_entry(sym, 0, 1);
             if (!de) DPI_LEAVE(DPI_E_SYMBOL);
+            p >>= used;
         }
-        dpi_drop(s, de & 0xffu);
-        const uint32_t dx = (de >> 8) & 0xffu;
-        const uint32_t dist = (de >> 16) + dpi_low_bits((uint32_t)s->bitbuf, dx);
-        dpi_drop(s, dx);
+        pacc += de;
+        t = de >> 8;
+        const uint32_t dist = (de >> 16) + (DPI_SHR(p, de) & dpi_mask(t));
+        pacc += t;
         if (DPI_UNLIKELY(dist > (uint32_t)(base + (int32_t)run))) DPI_LEAVE(DPI_E_DISTANCE);
         if (DPI_LIKELY(dist >= DPI_LANES)) {
+            if (DPI_LIKELY(run + len < DPI_LANES)) {             /* the usual case: the match ends inside the batch */
+                if (DPI_LANE - run < len) myval = dist;
+                run += len;
+                continue;
+            }
             for (;;) {
                 const uint32_t n = len < DPI_LANES - run ? len : DPI_LANES - run;
-                if (DPI_LANE - run < n) myval = dist << 8;
+                if (DPI_LANE - run < n) myval = dist;
                 run += n;
                 len -= n;
                 if (run == DPI_LANES) DPI_FLUSH();
@@ -411,7 +450,7 @@ DPI_FN int dpi_inflate(const uint8_t *in, uint32_t in_len, uint8_t *out, uint32_
         last = (int)dpi_bits(&st, 1);
         const int type = (int)dpi_bits(&st, 2);
         if (type == 0) {
-            dpi_drop(&st, st.bitcnt & 7u);                       /* skip to the byte boundary */
+            st.pos = (st.pos + 7u) & ~7u;                        /* skip to the byte boundary */
             const uint32_t len = dpi_bits(&st, 16), nlen = dpi_bits(&st, 16);
             if (dpi_exhausted(&st)) { rc = DPI_E_INPUT; break; }
             if ((len ^ 0xffffu) != nlen) { rc = DPI_E_STORED; break; }

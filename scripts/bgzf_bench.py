@@ -21,8 +21,11 @@ from deepore_b200 import _lib, bamdev, synth  # noqa: E402
 ap = argparse.ArgumentParser()
 ap.add_argument("--kb", type=int, default=1500, help="reference length in kb (30x coverage of it is simulated)")
 ap.add_argument("--reps", type=int, default=5)
+ap.add_argument("--lib", default="", help="load this build of the library instead (scripts/inflate_variants.py)")
 ap.add_argument("--sweep", action="store_true", help="only time the inflate kernel over growing prefixes of the block list")
 args = ap.parse_args()
+if args.lib:
+    _lib.LIB_PATH = os.path.abspath(args.lib)
 
 ref = synth.random_reference(args.kb * 1000, seed=1)
 rb = synth.simulate_reads(ref, coverage=30, seed=2)
