@@ -61,7 +61,9 @@ class ChunkCalls:
 
 
 class _Ingested:
-    pass
+    def release(self):
+        """Drop every device buffer of the chunk (its results live on in the pinned host arrays ChunkCalls views)."""
+        self.__dict__.clear()
 
 
 class ContigCaller:
@@ -220,26 +222,36 @@ class ContigCaller:
             th.start()
             return th
 
-        nxt = next(it, None)
-        if nxt is None:
+        def ingest_next():
+            """Pull the next chunk, ingest it on the side stream, and start staging the one behind it."""
+            nonlocal pending, th
+            ch = pending
+            if ch is None:
+                return None
+            th.join()
+            g = self._ingest(ch, staged.pop(id(ch), None))
+            pending = next(it, None)
+            th = start_stage(pending)
+            return g
+
+        pending = next(it, None)
+        if pending is None:
             return
         with torch.cuda.device(self.device):
-            th = start_stage(nxt)
-            th.join()
-            cur = self._ingest(nxt, staged.pop(id(nxt), None))
-            nxt = next(it, None)
-            th = start_stage(nxt)
+            th = start_stage(pending)
+            cur = ingest_next()
+            self._compute(cur)                                     # asynchronous: the compute stream is now busy with `cur`
+            nxt = ingest_next()                                    # side stream, overlaps `cur`
             while cur is not None:
-                self._compute(cur)                                 # asynchronous: the compute stream is now busy with `cur`
+                # the compute stream's queue never runs dry: the next chunk's work is enqueued behind `cur` BEFORE the host
+                # waits for `cur` and hands it to the consumer, whose own work then overlaps the next chunk's kernels
                 if nxt is not None:
-                    th.join()
-                    ing = self._ingest(nxt, staged.pop(id(nxt), None))     # side stream, overlaps `cur`
-                    nxt = next(it, None)
-                    th = start_stage(nxt)
-                else:
-                    ing = None
-                yield self._collect(cur)
-                cur = ing
+                    self._compute(nxt)
+                out = self._collect(cur)
+                cur.release()
+                yield out
+                cur = nxt
+                nxt = ingest_next() if cur is not None else None   # overlaps `cur`, which is running or queued
 
 
 def bai_chunk_range(bai: bytes, tid: int, beg: int, end: int):
