@@ -49,7 +49,7 @@ def traffic_of(kernel, units):
             if e is None:
                 continue
             return e["dram_bytes_per_launch"], e.get("source", name)
-        if d.get("launch_size") in (None, int(units)):
+        if d.get("launch_size") == int(units):             # a capture that does not name its launch size is not used
             return d["dram_bytes_per_launch"], d.get("source", name)
     return None, None
 
@@ -474,7 +474,7 @@ def main():
                 rows = o["img"].view(nw * H, W, 4)
                 for c0 in range(0, n, mchunk):
                     c1 = min(n, c0 + mchunk)
-                    eng.forward_rows(rows[c0 * H:c1 * H], want_logits=False, want_pred=True, pred=o["pred"][c0 * H:c1 * H])
+                    eng.forward_rows(rows[c0 * H:c1 * H], want_logits=False, want_pred=True, pred=o["pred"][c0 * H:c1 * H], window_rows=H)
                     launches += 12                     # u8->16-bit, folded GEMM, 9 GRU steps, fc1+argmax
                 st = torch.cuda.current_stream(dev)
                 _lib.check(_lib.lib().dp_vote(o["pred"].data_ptr(), n, H, 3, o["calls"].data_ptr(), None, None,
@@ -636,11 +636,12 @@ def main():
             line["e2e_" + x3[0]] = tot_windows * args.stride / ((x3[2] + gather_ms) * 1e-3)
         if with_model and prof:
             g_ms, g_n = prof["gru_step"]
-            rows_per_launch = mchunk * H
             n_layers = 3
-            # FLOPs of the calls test.py scores: 148 of the 150 rows of a window (rows 148, 149 run through the tiles but no
-            # 3-row window starts there), unpadded sizes, hidden product skipped where h_prev == 0
+            # the calls test.py makes: 148 of the 150 rows of a window (no 3-row window starts at rows 148, 149;
+            # dp_model_forward_windows drops them behind the folded GEMM, so a GRU launch works on exactly these rows);
+            # FLOPs at unpadded sizes, hidden product skipped where h_prev == 0
             calls_per_launch = mchunk * (H - 2)
+            rows_per_launch = calls_per_launch
             flop_per_launch = calls_per_launch * ((n_layers * 3 - 1) * FLOP_GRU_STEP_PER_ROW + FLOP_GRU_STEP0_PER_ROW) / (n_layers * 3)
             ach = flop_per_launch / (g_ms / max(1, g_n) * 1e-3) / 1e12
             g_traffic, g_tsrc = traffic_of("gru_step", rows_per_launch)

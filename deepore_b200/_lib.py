@@ -82,6 +82,8 @@ def lib():
     L.dp_model_destroy.argtypes = [C.c_void_p]
     L.dp_model_forward_rows.restype = C.c_int
     L.dp_model_forward_rows.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.dp_model_forward_windows.restype = C.c_int
+    L.dp_model_forward_windows.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]
     L.dp_model_forward_calls.restype = C.c_int
     L.dp_model_forward_calls.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]
     L.dp_vote.restype = C.c_int

@@ -152,7 +152,7 @@ __global__ void __launch_bounds__(128) fc1_argmax_kernel(const float *__restrict
                                                          long long slot_stride, const float *__restrict__ w,
                                                          const float *__restrict__ b, int n_class, int seq_len,
                                                          long long n_rows, float *__restrict__ logits,
-                                                         uint8_t *__restrict__ pred) {
+                                                         uint8_t *__restrict__ pred, int ckeep, int cgap) {
     extern __shared__ float s_w[];                     // [n_class][HP]
     for (int i = threadIdx.x; i < n_class * HP; i += blockDim.x) s_w[i] = w[i];
     __syncthreads();
@@ -164,6 +164,7 @@ __global__ void __launch_bounds__(128) fc1_argmax_kernel(const float *__restrict
     const int t = (int)(wid % seq_len);
     const long long m = rb * 32 + lane;
     const long long base = (((m >> 7) * 8) * 16 * 128 + (m & 127)) * 4;     // offset of (m, u = 0)
+    const long long mo = ckeep > 0 ? m + (long long)cgap * (m / ckeep) : m;   // output row: compacted calls go back to their row
     const float *pf = hf + t * slot_stride + base, *pb = hb + t * slot_stride + base;
     float best = 0.f;
     int besti = 0;
@@ -189,12 +190,12 @@ __global__ void __launch_bounds__(128) fc1_argmax_kernel(const float *__restrict
         for (int c = 0; c < FC1_CMAX; c++) {
             if (c0 + c < n_class) {
                 const float v = acc[c] + __ldg(b + c0 + c);
-                if (m < n_rows && logits) logits[(m * seq_len + t) * n_class + c0 + c] = v;
+                if (m < n_rows && logits) logits[(mo * seq_len + t) * n_class + c0 + c] = v;
                 if (c0 + c == 0 || v > best) { best = v; besti = c0 + c; }
             }
         }
     }
-    if (m < n_rows && pred) pred[m * seq_len + t] = (uint8_t)besti;
+    if (m < n_rows && pred) pred[mo * seq_len + t] = (uint8_t)besti;
 }
 
 // The same over the bf16 rows [row][512] of the arena (one-pass bf16 mode keeps no fp32 state): lane handles 16
@@ -203,12 +204,14 @@ __global__ void __launch_bounds__(256) fc1_argmax_bf_kernel(const __nv_bfloat16 
                                                             const __nv_bfloat16 *__restrict__ hb, long long slot_stride,
                                                             const float *__restrict__ w, const float *__restrict__ b,
                                                             int n_class, int seq_len, long long n_rows,
-                                                            float *__restrict__ logits, uint8_t *__restrict__ pred, int f16) {
+                                                            float *__restrict__ logits, uint8_t *__restrict__ pred, int f16,
+                                                            int ckeep, int cgap) {
     const long long wid = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int lane = threadIdx.x & 31;
     if (wid >= n_rows * seq_len) return;
     const long long m = wid / seq_len;
     const int t = (int)(wid % seq_len);
+    const long long mo = ckeep > 0 ? m + (long long)cgap * (m / ckeep) : m;
     const uint4 *pf = reinterpret_cast<const uint4 *>(hf + t * slot_stride + m * HP + lane * 16);
     const uint4 *pb = reinterpret_cast<const uint4 *>(hb + t * slot_stride + m * HP + lane * 16);
     const uint4 f0 = pf[0], f1 = pf[1], b0 = pb[0], b1 = pb[1];
@@ -236,10 +239,10 @@ __global__ void __launch_bounds__(256) fc1_argmax_bf_kernel(const __nv_bfloat16 
 #pragma unroll
         for (int d = 16; d > 0; d >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, d);
         acc += __ldg(b + c);
-        if (lane == 0 && logits) logits[(m * seq_len + t) * n_class + c] = acc;
+        if (lane == 0 && logits) logits[(mo * seq_len + t) * n_class + c] = acc;
         if (c == 0 || acc > best) { best = acc; besti = c; }
     }
-    if (lane == 0 && pred) pred[m * seq_len + t] = (uint8_t)besti;
+    if (lane == 0 && pred) pred[mo * seq_len + t] = (uint8_t)besti;
 }
 
 // 3-way vote (test.py:71-82, most_common :23-24).  pred [n_windows][H][3]; calls [n_windows][H] int8, -1 where the
@@ -503,9 +506,15 @@ static int build_model(Model *m, const dp_model_weights *w) {
 
 // triples == 0: img is a stack of n_rows image rows and call r reads rows r .. r+seq_len-1 (every sliding window);
 // triples == 1: img is n_rows independent windows of seq_len rows each (the reference's Model.forward call)
+// win_h > 0 (sliding mode only): the stack is n_rows / win_h pileups of win_h rows; the calls at the last seq_len-1 rows of a
+// pileup -- whose rows would run into the NEXT pileup, and which test.py never makes (its row loop stops at H - seq_len,
+// src/test.py:59) -- are dropped behind the folded GEMM: the GRU steps and fc1 run on win_h-seq_len+1 calls per pileup and
+// fc1 writes each call back at its own row; the skipped rows of logits / pred are left untouched
 static int forward_rows(Model *m, const uint8_t *img, long long n_rows, float *logits, uint8_t *pred, cudaStream_t st,
-                        int triples = 0) {
+                        int triples = 0, int win_h = 0) {
     const int RE = m->row_elems, S = m->seq_len;
+    const int ckeep = win_h > 0 ? win_h - (S - 1) : 0, cgap = win_h > 0 ? S - 1 : 0;
+    const long long n_calls = win_h > 0 ? n_rows / win_h * ckeep : n_rows;       // rows the GRU and fc1 work on
     const long long mc = m->mcap;
     size_t prof_base = 0;
     int prof_i = 0;
@@ -531,6 +540,7 @@ static int forward_rows(Model *m, const uint8_t *img, long long n_rows, float *l
     }
     mark();
     const int tiles_m = (int)((n_rows + 127) / 128);
+    const int tiles_mc = (int)((n_calls + 127) / 128);
     const CUtensorMap tmA[4] = {m->tm_img, m->tm_arena, m->tm_arena_lo, m->tm_img3};
     const CUtensorMap tmA_mc[4] = {m->tm_img, m->tm_arena_mc, m->tm_arena_lo_mc, m->tm_arena_mc};   // GRU pair kernel
     // 2. folded CNN + Linear
@@ -548,6 +558,7 @@ static int forward_rows(Model *m, const uint8_t *img, long long n_rows, float *l
         g.epi.out_lo = m->alloc_lo ? m->arena_lo : nullptr;
         g.epi.ldc = HP; g.epi.out_fp32 = 0;
         g.epi.nblk = HP; g.epi.nblk_stride = mc * HP;
+        g.epi.compact_h = win_h; g.epi.compact_keep = ckeep;
         int rc = launch_gemm_bf16(tmA, &m->tm_wfold, g, 256, st);
         if (rc) return rc;
     }
@@ -557,7 +568,7 @@ static int forward_rows(Model *m, const uint8_t *img, long long n_rows, float *l
         for (int sg = 0; sg < 3; sg++) {
             GruArgs g;
             memset(&g, 0, sizeof(g));
-            g.n_prob = 2; g.M = (int)n_rows; g.tiles_m = tiles_m; g.fast_act = m->fast_act;
+            g.n_prob = 2; g.M = (int)n_calls; g.tiles_m = tiles_mc; g.fast_act = m->fast_act;
             g.f16 = m->f16; g.acc_scale = 1.f / m->gru_scale;
             for (int d = 0; d < 2; d++) {
                 GruProblem &P = g.prob[d];
@@ -618,17 +629,17 @@ static int forward_rows(Model *m, const uint8_t *img, long long n_rows, float *l
     // 4. fc1 + argmax on the fp32 states of the last layer
     if (logits || pred) {
         const int k = m->n_layers - 1;
-        const long long warps = n_rows * S;
+        const long long warps = n_calls * S;
         const unsigned blocks = (unsigned)((warps * 32 + 255) / 256);
         if (k < m->bf_state)
             fc1_argmax_bf_kernel<<<blocks, 256, 0, st>>>(m->arena + (size_t)bf_slot_hf(k, 0) * mc * HP,
                                                          m->arena + (size_t)bf_slot_hb(k, 0) * mc * HP, mc * HP, m->w_fc1,
-                                                         m->b_fc1, m->n_class, S, n_rows, logits, pred, m->f16);
+                                                         m->b_fc1, m->n_class, S, n_calls, logits, pred, m->f16, ckeep, cgap);
         else
-            fc1_argmax_kernel<<<(unsigned)((((n_rows + 31) / 32) * S + 3) / 4), 128, (size_t)m->n_class * HP * 4, st>>>(
+            fc1_argmax_kernel<<<(unsigned)((((n_calls + 31) / 32) * S + 3) / 4), 128, (size_t)m->n_class * HP * 4, st>>>(
                                                       m->state + (size_t)f32_slot_hf(k, 0) * mc * HP,
                                                       m->state + (size_t)f32_slot_hb(k, 0) * mc * HP, mc * HP, m->w_fc1,
-                                                      m->b_fc1, m->n_class, S, n_rows, logits, pred);
+                                                      m->b_fc1, m->n_class, S, n_calls, logits, pred, ckeep, cgap);
         DP_CUDA_CHECK(cudaGetLastError());
     }
     while (m->profile && prof_i < PROF_MARKS) mark();     // unused marks collapse onto the end
@@ -700,6 +711,17 @@ int dp_model_forward_rows(dp_model *h, const uint8_t *img, int64_t n_rows, float
     DP_REQUIRE(img, "null image");
     DP_REQUIRE(((uintptr_t)img & 15) == 0, "img must be 16-byte aligned");
     return dp::forward_rows(h->m, img, n_rows, logits, pred, (cudaStream_t)stream);
+}
+
+int dp_model_forward_windows(dp_model *h, const uint8_t *img, int64_t n_windows, int32_t H, float *logits, uint8_t *pred,
+                             void *stream) {
+    DP_REQUIRE(h && h->m, "null model");
+    DP_REQUIRE(n_windows >= 0 && H >= h->m->seq_len, "H must be at least seq_len");
+    DP_REQUIRE(n_windows * (int64_t)H <= h->m->mcap, "n_windows * H exceeds the model's max_rows");
+    if (n_windows == 0) return DP_OK;
+    DP_REQUIRE(img, "null image");
+    DP_REQUIRE(((uintptr_t)img & 15) == 0, "img must be 16-byte aligned");
+    return dp::forward_rows(h->m, img, n_windows * (int64_t)H, logits, pred, (cudaStream_t)stream, 0, H);
 }
 
 int dp_model_forward_calls(dp_model *h, const uint8_t *img, int64_t n_calls, float *logits, uint8_t *pred, void *stream) {

@@ -174,7 +174,13 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
             const int m = m0 + wq * 32 + lane;
             mbar_wait(tfull_bar(as), aphase);
             tc_fence_after();
-            const bool row_ok = m < g.M;
+            bool row_ok = m < g.M;
+            long long m_out = m;
+            if (e.compact_h > 0) {
+                const int w = m / e.compact_h, r = m - w * e.compact_h;
+                row_ok = row_ok && r < e.compact_keep;
+                m_out = (long long)m - (long long)(e.compact_h - e.compact_keep) * w;
+            }
             bool row_zero = false;
             if (e.mask_period > 0) { const int r = m % e.mask_period; row_zero = r < e.mask_lo || r >= e.mask_hi; }
             const uint32_t taddr = tmem_base + as * BN + ((uint32_t)(wq * 32) << 16);
@@ -215,7 +221,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant
 #pragma unroll
                     for (int i = 0; i < 16; i++) f[i] = 0.f;
                 }
-                long long off = (long long)m * e.ldc;
+                long long off = m_out * e.ldc;
                 if (e.nblk > 0) off += (long long)(n / e.nblk) * e.nblk_stride + (n % e.nblk); else off += n;
                 if (e.out_fp32) {
                     float4 *op = reinterpret_cast<float4 *>(reinterpret_cast<float *>(e.out) + off);

@@ -35,6 +35,9 @@ struct GemmEpilogue {
     int mask_period, mask_lo, mask_hi; // period>0: rows with (m % period) outside [lo,hi) are stored as ZERO (conv padding)
     float acc_scale;                   // accumulators are multiplied by this before the bias (0 = 1): undoes the power-of-two
                                        // scale the fp16 weights carry
+    int compact_h, compact_keep;       // compact_h > 0: rows with (m % compact_h) >= compact_keep are NOT stored and the others move
+                                       // up: row m lands at m - (compact_h - compact_keep) * (m / compact_h)  (the calls of a
+                                       // pileup whose 3-row window would run into the next pileup are dropped here)
 };
 
 struct GemmArgs {

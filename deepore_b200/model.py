@@ -69,23 +69,32 @@ class _Engine:
         except Exception:
             pass
 
-    def forward_rows(self, img_rows: torch.Tensor, want_logits=True, want_pred=True, logits=None, pred=None):
-        """img_rows uint8 [n_rows, width, in_ch] on this device -> (logits fp32 [n_rows,3,n_class], pred u8 [n_rows,3])"""
+    def forward_rows(self, img_rows: torch.Tensor, want_logits=True, want_pred=True, logits=None, pred=None, window_rows=None):
+        """img_rows uint8 [n_rows, width, in_ch] on this device -> (logits fp32 [n_rows,3,n_class], pred u8 [n_rows,3]).
+        window_rows = H: the rows are whole pileups of H rows; the calls at the last two rows of each (never made by
+        test.py:59, their windows run into the next pileup) are skipped -- dp_model_forward_windows -- and their entries stay
+        as they were (zero in buffers allocated here)."""
         assert img_rows.dtype == torch.uint8 and img_rows.is_cuda and img_rows.is_contiguous()
         n = int(img_rows.shape[0])
         if n > self.max_rows:
             raise _lib.DeeporeError("forward_rows: %d rows exceed the engine capacity %d" % (n, self.max_rows))
+        if window_rows is not None and (window_rows < 3 or n % int(window_rows)):
+            raise _lib.DeeporeError("forward_rows: %d rows are not whole windows of %r rows" % (n, window_rows))
+        alloc = torch.zeros if window_rows is not None else torch.empty
         if want_logits and logits is None:
-            logits = torch.empty((n, 3, self.n_class), dtype=torch.float32, device=self.device)
+            logits = alloc((n, 3, self.n_class), dtype=torch.float32, device=self.device)
         if want_pred and pred is None:
-            pred = torch.empty((n, 3), dtype=torch.uint8, device=self.device)
+            pred = alloc((n, 3), dtype=torch.uint8, device=self.device)
         st = torch.cuda.current_stream(self.device)
+        lp = logits.data_ptr() if logits is not None else None
+        pp = pred.data_ptr() if pred is not None else None
         with torch.cuda.device(self.device):
-            rc = _lib.lib().dp_model_forward_rows(self.handle, img_rows.data_ptr(), n,
-                                                  logits.data_ptr() if logits is not None else None,
-                                                  pred.data_ptr() if pred is not None else None,
-                                                  C.c_void_p(st.cuda_stream))
-        _lib.check(rc, "dp_model_forward_rows")
+            if window_rows is not None:
+                H = int(window_rows)
+                rc = _lib.lib().dp_model_forward_windows(self.handle, img_rows.data_ptr(), n // H, H, lp, pp, C.c_void_p(st.cuda_stream))
+            else:
+                rc = _lib.lib().dp_model_forward_rows(self.handle, img_rows.data_ptr(), n, lp, pp, C.c_void_p(st.cuda_stream))
+        _lib.check(rc, "dp_model_forward_windows" if window_rows is not None else "dp_model_forward_rows")
         return logits, pred
 
     def forward_calls(self, img_calls: torch.Tensor):
@@ -261,7 +270,7 @@ class Model(nn.Module):
         nw, H = int(img.shape[0]), int(img.shape[1])
         rows = img.contiguous().view(nw * H, img.shape[2], img.shape[3])
         eng = self.engine(nw * H, img.device)
-        logits, pred = eng.forward_rows(rows, want_logits=want_logits, want_pred=True)
+        logits, pred = eng.forward_rows(rows, want_logits=want_logits, want_pred=True, window_rows=H)
         return (logits.view(nw, H, 3, self.classN) if logits is not None else None), pred.view(nw, H, 3)
 
     def call_windows(self, img: torch.Tensor, labels: Optional[torch.Tensor] = None,

@@ -7,7 +7,7 @@ Here one CONTIG CHUNK (the records of one genomic interval, as a BGZF file image
 
   side stream     pinned file image --cudaMemcpyAsync--> HBM -> dp_bgzf_inflate -> dp_bam_scan / dp_bam_extract (read arrays in
                   HBM) -> dp_encode_prepare (per-read digests, per-base codes) -> dp_window_ranges (candidate reads per window)
-  compute stream  per batch of windows: dp_encode_prepared -> dp_model_forward_rows -> dp_vote; calls + row -> position map of
+  compute stream  per batch of windows: dp_encode_prepared -> dp_model_forward_windows -> dp_vote; calls + row -> position map of
                   the whole chunk leave the device in ONE copy per array
 
 The ingest of chunk i+1 runs on the side stream while chunk i is on the compute stream (two buffer sets); a host thread
@@ -162,7 +162,8 @@ class ContigCaller:
                 self.wpc, g.bases_per_window, st), "dp_encode_prepared")
             for c0 in range(0, n, self.mchunk):
                 c1 = min(n, c0 + self.mchunk)
-                self.eng.forward_rows(rows[c0 * H:c1 * H], want_logits=False, want_pred=True, pred=self.pred[c0 * H:c1 * H])
+                self.eng.forward_rows(rows[c0 * H:c1 * H], want_logits=False, want_pred=True, pred=self.pred[c0 * H:c1 * H],
+                                      window_rows=H)
             _lib.check(L.dp_vote(self.pred.data_ptr(), n, H, 3, g.calls[w0:].data_ptr(), None, None, st), "dp_vote")
         g.c1.record(cur)
         # results of the whole chunk: one copy per array into pinned host memory

@@ -187,6 +187,18 @@ int dp_model_destroy(dp_model *m);
 int dp_model_forward_rows(dp_model *m, const uint8_t *img, int64_t n_rows, float *logits, uint8_t *pred, void *stream);
 
 /*
+ * dp_model_forward_windows -- dp_model_forward_rows for a stack of n_windows WHOLE pileups of H rows each: the calls of
+ * src/test.py:59-66 (`for row in range(0, H - seq_len + 1)`: rows 0 .. H-seq_len of every pileup) and nothing else.  The
+ * calls at the last seq_len-1 rows of a pileup, whose 3-row window would run into the next pileup and which the reference
+ * never makes, are not computed (1.35 % of every GRU launch at H = 150): their entries of logits / pred are left
+ * untouched; all other entries equal dp_model_forward_rows' bit for bit.  dp_vote reads none of the skipped entries.
+ *   img      device uint8 [n_windows][H][width][in_ch]
+ *   logits   optional device fp32 [n_windows * H][seq_len][n_class];  pred optional device uint8 [n_windows * H][seq_len]
+ */
+int dp_model_forward_windows(dp_model *m, const uint8_t *img, int64_t n_windows, int32_t H, float *logits, uint8_t *pred,
+                             void *stream);
+
+/*
  * dp_model_forward_calls -- Model.forward(x, hidden) as src/test.py:63-66 calls it: n_calls INDEPENDENT windows of seq_len
  * rows each (one per sample of the batch), no sliding.
  *   img      device uint8 [n_calls][seq_len][width][in_ch]   (n_calls * seq_len <= max_rows)

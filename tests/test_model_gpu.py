@@ -250,3 +250,34 @@ def test_batch_composition_does_not_change_a_window(gold):
     big, _ = m.forward_windows(rep)
     for j in range(35):
         assert torch.equal(big[j, :148], base[j % 4, :148]), "window %d of the repeated batch differs" % j
+
+
+@pytest.mark.parametrize("precision", ["fp16", "fp16x3", "bf16"])
+def test_forward_windows_entry_equals_forward_rows_on_the_calls_test_py_makes(gold, precision):
+    """dp_model_forward_windows drops the calls at rows 148, 149 of every pileup behind the folded GEMM (test.py:59 never
+    makes them).  Every other entry must equal dp_model_forward_rows' BIT FOR BIT (a row's arithmetic does not depend on the
+    tile it sits in), the skipped entries must stay untouched, and the votes must be identical."""
+    import ctypes as C
+    from deepore_b200 import _lib
+    m = _model(precision)
+    img = torch.from_numpy(gold["img"]).cuda().repeat(3, 1, 1, 1)[:11]            # 11 windows: 1650 rows -> 1628 calls
+    nw, H = int(img.shape[0]), int(img.shape[1])
+    eng = m.engine(nw * H, img.device)
+    rows = img.contiguous().view(nw * H, img.shape[2], img.shape[3])
+    want_l, want_p = eng.forward_rows(rows)
+    got_l = torch.full((nw * H, 3, 3), -77.0, dtype=torch.float32, device="cuda")
+    got_p = torch.full((nw * H, 3), 99, dtype=torch.uint8, device="cuda")
+    eng.forward_rows(rows, logits=got_l, pred=got_p, window_rows=H)
+    torch.cuda.synchronize()
+    wl, gl = want_l.view(nw, H, 3, 3), got_l.view(nw, H, 3, 3)
+    wp, gp = want_p.view(nw, H, 3), got_p.view(nw, H, 3)
+    assert torch.equal(gl[:, :H - 2], wl[:, :H - 2]) and torch.equal(gp[:, :H - 2], wp[:, :H - 2])
+    assert bool((gl[:, H - 2:] == -77.0).all()) and bool((gp[:, H - 2:] == 99).all())
+    calls = [torch.empty((nw, H), dtype=torch.int8, device="cuda") for _ in range(2)]
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    for p, c in ((want_p, calls[0]), (got_p, calls[1])):
+        _lib.check(_lib.lib().dp_vote(p.data_ptr(), nw, H, 3, c.data_ptr(), None, None, st), "dp_vote")
+    torch.cuda.synchronize()
+    assert torch.equal(calls[0], calls[1])
+    with pytest.raises(_lib.DeeporeError):
+        eng.forward_rows(rows[:H + 1], window_rows=H)                             # not whole windows
