@@ -20,6 +20,20 @@ def load(name):
                            img=z["img"], status=z["status"], labels=z["labels"], z=extra)
 
 
+def trained_state(path=None):
+    """modelio.seeded_state(seed) with the small tensors that oracle/make_trained_golden.py's SGD steps changed (stored under
+    `state/<name>` in tests/golden/bundled_calls_trained.npz) put in place -> (state, the npz)."""
+    from deepore_b200 import modelio
+    z = np.load(path or os.path.join(GOLD, "bundled_calls_trained.npz"))
+    st = dict(modelio.seeded_state(int(z["seed"])))
+    for k in z.files:
+        if k.startswith("state/"):
+            name = k[len("state/"):]
+            assert name in st and st[name].shape == z[k].shape, name
+            st[name] = z[k]
+    return st, z
+
+
 def write_bam(path, rb, contig="chr3", contig_len=9_000_000):
     """Uncompressed-member BAM of a ReadBatch (record layout of dep/htslib/htslib/sam.h:154-195; names 'r', no aux fields):
     enough for `reads.BamFile`, which inflates the whole stream with gzip."""

@@ -99,3 +99,29 @@ def test_torch_restatement_matches_reference_logits(gold, state):
     got = tm.forward_image_rows(m, gold["img"][:2], CALLS)
     assert got.shape == (2, len(CALLS), 3, 3)
     assert np.abs(got - gold["logits"][:2][:, CALLS]).max() < 2e-5
+
+
+TRAINED = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "bundled_calls_trained.npz")
+
+
+@pytest.mark.skipif(not os.path.isfile(TRAINED), reason="tests/golden/bundled_calls_trained.npz not generated")
+def test_trained_checkpoint_golden_is_reproduced_by_the_torch_restatement():
+    """SURVEY 8(f4) slice: the goldens of the SGD-stepped checkpoint (oracle/make_trained_golden.py, unmodified reference
+    model) are reproduced by the restated torch model from seeded_state + the committed small tensors -- i.e. the fixture
+    holds everything the training changed -- and the steps did move the model: fewer calls disagree with the labels."""
+    import golden_util as gu
+    import torch
+    import torch_model as tm
+    torch.set_num_threads(max(1, min(8, os.cpu_count() or 1)))
+    st, z = gu.trained_state(TRAINED)
+    changed = [k for k in z.files if k.startswith("state/")]
+    assert "state/fc1.weight" in changed and "state/batchNorm.running_mean" in changed and int(z["steps"]) > 0
+    assert sum(z[k].size for k in changed) < 20000
+    g = gu.load("bundled_na12878")
+    rows = [0, 1, 73, 146, 147]
+    m = tm.build(st)
+    got = tm.forward_image_rows(m, g.img[:2], rows)
+    assert np.abs(got - z["logits"][:2][:, rows]).max() < 2e-5
+    seeded = np.load(os.path.join(os.path.dirname(TRAINED), "bundled_calls_seed7.npz"))
+    lab = np.array([[int(c) for c in str(s)[:150].ljust(150, "0")] for s in g.labels])[:, 2:148]
+    assert (z["calls"][:, 2:148] == lab).mean() > (seeded["calls"][:, 2:148] == lab).mean()
