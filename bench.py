@@ -351,15 +351,25 @@ def bam_path(dev, model, precision, rank, stride, n_chunks=3, windows_per_chunk=
             "fallback_windows": int(sum(o.fallback_windows for o in outs)), "calls_in_range": bool(ok)}
 
 
-def parity_block(dev, precision):
+def parity_block(dev, precision, trained=False):
     """Parity of the precision this run is timed in, on the committed goldens (outputs of the UNMODIFIED reference model over
     the 260 bundled NA12878 pileup images; no oracle/ import): logits max-abs / rms, top-1 classes and votes that differ,
-    counted over all of them.  Outside every timed region."""
+    counted over all of them.  trained: the golden of the checkpoint that took SGD steps on these windows
+    (oracle/make_trained_golden.py; seeded state + the tensors the steps changed, stored in the fixture).  Outside every
+    timed region."""
     import torch
     from deepore_b200 import model as dmodel, modelio
-    gc = np.load(os.path.join(ROOT, "tests", "golden", "bundled_calls_seed7.npz"))
+    name = "bundled_calls_trained.npz" if trained else "bundled_calls_seed7.npz"
+    path = os.path.join(ROOT, "tests", "golden", name)
+    if not os.path.isfile(path):
+        return None
+    gc = np.load(path)
+    state = dict(modelio.seeded_state(int(gc["seed"])))
+    for k in gc.files:
+        if k.startswith("state/"):
+            state[k[len("state/"):]] = gc[k]
     img = torch.from_numpy(np.load(os.path.join(ROOT, "tests", "golden", "bundled_na12878.npz"))["img"]).to(dev)
-    m = dmodel.from_state(modelio.seeded_state(int(gc["seed"])), dev, precision)
+    m = dmodel.from_state(state, dev, precision)
     logits, pred = m.forward_windows(img)
     nw, H = int(img.shape[0]), int(img.shape[1])
     votes, _ = dmodel.vote(pred.view(-1, 3), nw, H, 3)
@@ -368,8 +378,9 @@ def parity_block(dev, precision):
     pr = pred.cpu().numpy()[:, :148]
     v = votes.cpu().numpy()[:, 2:148]
     d = lg - gc["logits"]
-    out = {"precision": precision, "golden": "tests/golden/bundled_calls_seed7.npz (unmodified reference model, torch CPU fp32, "
-           "260 bundled NA12878 windows x 148 calls)", "logits_max_abs": float(np.abs(d).max()),
+    what = ("after %d SGD steps of train.py's loop on these windows" % int(gc["steps"])) if trained else "seeded weights"
+    out = {"precision": precision, "golden": "tests/golden/%s (unmodified reference model, torch CPU fp32, %s, "
+           "260 bundled NA12878 windows x 148 calls)" % (name, what), "logits_max_abs": float(np.abs(d).max()),
            "logits_rms": float(np.sqrt((d ** 2).mean())), "logit_scale": float(np.abs(gc["logits"]).max()),
            "n_argmax": int(pr.size), "n_argmax_diff": int((pr != gc["pred"]).sum()),
            "n_votes": int(v.size), "n_vote_diff": int((v != gc["calls"][:, 2:148]).sum())}
@@ -678,6 +689,9 @@ def main():
                 "fallback_windows": bam["fallback_windows"], "calls_in_range": bam["calls_in_range"]}
         if with_model and not args.no_parity:
             line["parity"] = parity_block(dev, args.precision)
+            pt = parity_block(dev, args.precision, trained=True)
+            if pt is not None:
+                line["parity_trained_checkpoint"] = pt
             if x3 is not None:
                 line["parity_" + x3[0]] = parity_block(dev, x3[0])
         if not args.no_cpu_baseline and world == 1:            # rank 0 at N=1 only (torchrun pins OMP_NUM_THREADS=1)
